@@ -1,0 +1,319 @@
+/*
+ * b2vp.h -- C-ABI of the B200-native `volpath` hot path (mono variants).
+ *
+ * This is the drop-in boundary.  Everything below is
+ * plain C: POD structs, pointers and sizes.  The reference has no FFI for this
+ * path (it is a C++ plugin, `plugins/volpath.so`); the entry points here are
+ * what the replacement plugin's `render()` override binds to.  Reference
+ * interfaces replaced (paths relative to the reference tree):
+ *
+ *   b2vp_scene_create    <- the object graph an integrator sees in
+ *                           SamplingIntegrator::render(Scene*, Sensor*)
+ *                           src/librender/integrator.cpp:51, built by
+ *                           Scene::Scene src/librender/scene.cpp:22-108
+ *   b2vp_render          <- SamplingIntegrator::render / render_block /
+ *                           render_sample src/librender/integrator.cpp:51-288
+ *                           + VolumetricPathIntegrator::sample
+ *                           src/integrators/volpath.cpp:38-257
+ *   b2vp_scene_update    <- Object::parameters_changed, e.g.
+ *                           src/textures/grid3d.cpp:370-391 and
+ *                           TraversalCallback::put_parameter("scale"...)
+ *                           src/media/heterogeneous.cpp:56-61
+ *   b2vp_cancel          <- Integrator::cancel include/mitsuba/render/integrator.h:51
+ *   b2vp_last_error      <- Throw()/std::runtime_error include/mitsuba/core/logger.h
+ *
+ * Real-valued scene parameters are carried as `double`.  For the fp32 variant
+ * (scalar_mono) the host computes them in float and stores the float value
+ * exactly in the double slot; the device narrows them back without rounding.
+ *
+ * All structs start with {abi_version, struct_size} so that a plugin built
+ * against an older header is rejected instead of mis-read.
+ */
+#ifndef B2VP_H
+#define B2VP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2VP_ABI_VERSION 1u
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+    B2VP_OK              = 0,
+    B2VP_ERR_INVALID     = 1, /* malformed descriptor / argument            */
+    B2VP_ERR_UNSUPPORTED = 2, /* scene content outside SURVEY.md section 8  */
+    B2VP_ERR_CUDA        = 3, /* CUDA runtime error (message in last_error) */
+    B2VP_ERR_NO_DEVICE   = 4, /* no usable sm_100 device: there is NO CPU fallback */
+    B2VP_ERR_CANCELLED   = 5
+};
+
+/* ---- enumerations ------------------------------------------------------ */
+enum { B2VP_PREC_F32 = 0 /* scalar_mono */, B2VP_PREC_F64 = 1 /* scalar_mono_double */ };
+
+enum { B2VP_SHAPE_RECTANGLE = 0, B2VP_SHAPE_SPHERE = 1, B2VP_SHAPE_MESH = 2 };
+enum { B2VP_BSDF_DIFFUSE = 0, B2VP_BSDF_NULL = 1, B2VP_BSDF_RPV = 2 };
+enum { B2VP_MEDIUM_HOMOGENEOUS = 0, B2VP_MEDIUM_HETEROGENEOUS = 1 };
+enum { B2VP_VOLUME_CONST = 0, B2VP_VOLUME_GRID = 1 };
+enum { B2VP_FILTER_NEAREST = 0, B2VP_FILTER_TRILINEAR = 1 };
+enum { B2VP_WRAP_REPEAT = 0, B2VP_WRAP_MIRROR = 1, B2VP_WRAP_CLAMP = 2 };
+enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2 };
+enum { B2VP_EMITTER_DIRECTIONAL = 0 };
+enum {
+    B2VP_SENSOR_DISTANT        = 0, /* src/sensors/distant.cpp        */
+    B2VP_SENSOR_MDISTANT       = 1, /* src/sensors/mdistant.cpp       */
+    B2VP_SENSOR_RADIANCEMETER  = 2, /* src/sensors/radiancemeter.cpp  */
+    B2VP_SENSOR_MRADIANCEMETER = 3  /* src/sensors/mradiancemeter.cpp */
+};
+enum { B2VP_DIR_SINGLE = 0, B2VP_DIR_SAMPLE_WIDTH = 1, B2VP_DIR_SAMPLE_ALL = 2 };
+enum { B2VP_TARGET_NONE = 0, B2VP_TARGET_POINT = 1, B2VP_TARGET_SHAPE = 2 };
+enum { B2VP_ORIGIN_BSPHERE = 0, B2VP_ORIGIN_SHAPE = 1 };
+
+/* Seeding of the per-stream PCG32 generators. */
+enum {
+    /* reference scalar_* modes: one stream per pixel, seed = block_id*bs^2 +
+       morton index, all spp drawn serially (src/librender/integrator.cpp:197-208) */
+    B2VP_SEED_SCALAR_BLOCKS = 0,
+    /* reference wavefront mode: stream i = (tea64(seed,i), tea64(i,seed)),
+       pixel = i / samples_per_pass (src/librender/sampler.cpp:89-92,
+       src/librender/integrator.cpp:147-153) */
+    B2VP_SEED_WAVEFRONT = 1,
+    /* parity harness: caller supplies (state, inc) and the pixel per stream */
+    B2VP_SEED_EXPLICIT = 2
+};
+
+/* ---- scene description -------------------------------------------------- */
+
+/* Column-major 4x4, m[c*4+r], like enoki::Matrix (transform.h:110-116). */
+typedef struct B2vpMat4 { double m[16]; } B2vpMat4;
+
+typedef struct B2vpShape {
+    int32_t type;              /* B2VP_SHAPE_*                                 */
+    int32_t bsdf;              /* index into bsdfs                             */
+    int32_t interior_medium;   /* index into media or -1                       */
+    int32_t exterior_medium;   /* index into media or -1                       */
+    B2vpMat4 to_world;         /* rectangle / sphere                           */
+    B2vpMat4 to_object;        /* inverse of to_world                          */
+    double frame_s[3];         /* rectangle: dp_du  (rectangle.cpp:86-90)      */
+    double frame_t[3];         /* rectangle: dp_dv                             */
+    double frame_n[3];         /* rectangle: unit normal                       */
+    double inv_surface_area;   /* rectangle / sphere                           */
+    double center[3];          /* sphere (sphere.cpp:118)                      */
+    double radius;             /* sphere                                       */
+    int32_t flip_normals;      /* sphere                                       */
+    /* mesh: ranges into the scene-wide vertex/face pools                      */
+    uint32_t vertex_offset, vertex_count;
+    uint32_t face_offset, face_count;
+    int32_t has_vertex_normals, has_vertex_texcoords;
+    int32_t reserved0;
+} B2vpShape;
+
+typedef struct B2vpBsdf {
+    int32_t type;              /* B2VP_BSDF_*                                  */
+    int32_t reserved0;
+    /* diffuse: p[0]=reflectance.  rpv: p[0]=rho_0 p[1]=k p[2]=g p[3]=rho_c   */
+    double p[4];
+} B2vpBsdf;
+
+typedef struct B2vpVolume {
+    int32_t type;              /* B2VP_VOLUME_*                                */
+    int32_t filter;            /* B2VP_FILTER_*                                */
+    int32_t wrap;              /* B2VP_WRAP_*                                  */
+    int32_t channels;          /* 1 or 3 (3 => luminance in mono, grid3d.cpp:178) */
+    int32_t res[3];            /* nx, ny, nz                                   */
+    int32_t reserved0;
+    double value;              /* constvolume value (constant3d.cpp)           */
+    double max_value;          /* Volume::max()                                */
+    double bbox_min[3], bbox_max[3];
+    B2vpMat4 world_to_local;
+    /* grid data, always float32 as on disk (volume_data.h:85-90), laid out
+       [((z*ny+y)*nx+x)*channels+c].  Host pointer; copied by scene_create.   */
+    const float *data;
+} B2vpVolume;
+
+typedef struct B2vpPhase {
+    int32_t type;              /* B2VP_PHASE_*                                 */
+    int32_t reserved0;
+    double g;                  /* hg asymmetry (hg.cpp:41)                     */
+} B2vpPhase;
+
+typedef struct B2vpMedium {
+    int32_t type;              /* B2VP_MEDIUM_*                                */
+    int32_t sigma_t;           /* index into volumes                           */
+    int32_t albedo;            /* index into volumes                           */
+    int32_t phase;             /* index into phases                            */
+    int32_t has_spectral_extinction; /* medium.h:79, default true             */
+    int32_t sample_emitters;   /* medium.cpp:29                                */
+    double scale;              /* heterogeneous.cpp:27 / homogeneous.cpp:27    */
+} B2vpMedium;
+
+typedef struct B2vpEmitter {
+    int32_t type;              /* B2VP_EMITTER_DIRECTIONAL                     */
+    int32_t reserved0;
+    double direction[3];       /* to_world * (0,0,1) (directional.cpp:112)     */
+    double irradiance;
+} B2vpEmitter;
+
+typedef struct B2vpSensor {
+    int32_t type;              /* B2VP_SENSOR_*                                */
+    int32_t direction_type;    /* distant: B2VP_DIR_*                          */
+    int32_t target_type;       /* distant/mdistant: B2VP_TARGET_*              */
+    int32_t origin_type;       /* distant: B2VP_ORIGIN_*                       */
+    int32_t target_shape;      /* shape index (rectangle) when TARGET_SHAPE    */
+    int32_t origin_shape;      /* shape index when ORIGIN_SHAPE                */
+    int32_t flip_directions;   /* distant.cpp:229                              */
+    int32_t needs_aperture_sample; /* sensor.h:79                             */
+    int32_t medium;            /* sensor->medium(): index or -1                */
+    int32_t n_transforms;      /* mdistant / mradiancemeter sensor count       */
+    B2vpMat4 to_world;         /* distant / radiancemeter world transform      */
+    double target_point[3];
+    double shutter_open, shutter_open_time;
+    const double *transforms;  /* n_transforms * 16, column-major              */
+    /* film (hdrfilm.cpp / film.cpp) */
+    int32_t film_size[2];
+    int32_t crop_offset[2];
+    int32_t crop_size[2];
+    uint32_t sample_count;     /* sampler->sample_count()                      */
+    uint32_t reserved0;
+    uint64_t sampler_seed;     /* independent sampler `seed` property          */
+} B2vpSensor;
+
+typedef struct B2vpIntegrator {
+    int32_t max_depth;         /* -1 => unbounded (integrator.cpp:305-314)     */
+    int32_t rr_depth;          /* default 5                                    */
+    int32_t hide_emitters;
+    uint32_t block_size;       /* 0 => choose like integrator.cpp:89-97        */
+    uint32_t samples_per_pass; /* 0xffffffff => all                            */
+    /* phase->sample(.., next_1d(), next_2d(), ..) and bsdf->sample(..) draw their
+       two sample arguments in compiler-chosen order (volpath.cpp:171,215): 0 =
+       right-to-left (GCC, the build SURVEY.md probed), 1 = left-to-right (clang) */
+    uint32_t arg_order_ltr;
+} B2vpIntegrator;
+
+typedef struct B2vpSceneDesc {
+    uint32_t abi_version;
+    uint32_t struct_size;
+    int32_t precision;         /* B2VP_PREC_* the host computed parameters in  */
+    int32_t reserved0;
+
+    uint32_t n_shapes, n_bsdfs, n_media, n_volumes, n_phases, n_emitters;
+    const B2vpShape *shapes;
+    const B2vpBsdf *bsdfs;
+    const B2vpMedium *media;
+    const B2vpVolume *volumes;
+    const B2vpPhase *phases;
+    const B2vpEmitter *emitters;
+
+    /* triangle pools (mesh.h:22-28: positions/normals/texcoords always f32)  */
+    uint32_t n_vertices, n_faces;
+    const float *vertex_positions;  /* 3 per vertex                            */
+    const float *vertex_normals;    /* 3 per vertex or NULL                    */
+    const float *vertex_texcoords;  /* 2 per vertex or NULL                    */
+    const uint32_t *faces;          /* 3 per face, indices local to the shape  */
+
+    /* Scene::bbox() (scene.cpp:38) and the derived bounding sphere with the
+       epsilon padding of distant.cpp:292-297 / directional.cpp:68-73.        */
+    double bbox_min[3], bbox_max[3];
+    double bsphere_center[3];
+    double bsphere_radius;
+
+    B2vpSensor sensor;
+    B2vpIntegrator integrator;
+} B2vpSceneDesc;
+
+/* ---- render arguments & outputs ----------------------------------------- */
+
+/* Per-stream event counters: summed over the samples
+   the stream drew.  segments = n_medium_steps + n_intersect.                  */
+typedef struct B2vpPathCounters {
+    uint32_t n_rng_draws;      /* PCG32 advances                               */
+    uint32_t n_medium_steps;   /* Medium::sample_interaction calls             */
+    uint32_t n_null;           /* null collisions (main loop + both marches)   */
+    uint32_t n_real;           /* real medium scattering events                */
+    uint32_t n_intersect;      /* Scene::ray_intersect calls                   */
+    uint32_t n_surface;        /* surface events in the main loop              */
+} B2vpPathCounters;
+
+/* Whole-launch totals. */
+typedef struct B2vpCounters {
+    uint64_t n_paths;
+    uint64_t n_rng_draws, n_medium_steps, n_null, n_real, n_intersect, n_surface;
+    uint64_t n_invalid_samples; /* dropped by ImageBlock::put (imageblock.cpp:85-109) */
+    double gpu_ms;              /* CUDA-event time of the render kernels       */
+    uint32_t n_launches;        /* kernels launched by this call               */
+    uint32_t reserved0;
+} B2vpCounters;
+
+typedef struct B2vpRenderArgs {
+    uint32_t abi_version;
+    uint32_t struct_size;
+    int32_t precision;          /* B2VP_PREC_*: arithmetic of the kernels      */
+    int32_t seed_mode;          /* B2VP_SEED_*                                 */
+    int32_t device;             /* CUDA device ordinal                         */
+    int32_t film_on_device;     /* film pointer is a device pointer            */
+    void *cuda_stream;          /* cudaStream_t or NULL for the default stream */
+
+    /* Stream range rendered by this call: [first_stream, first_stream+n_streams)
+       of the mode's global stream index space (see b2vp_stream_count).  Sharding
+       across GPUs = disjoint ranges + one film sum-reduce.   */
+    uint64_t first_stream;
+    uint64_t n_streams;         /* 0 => all remaining                          */
+
+    /* B2VP_SEED_EXPLICIT only: per-stream start state, increment and pixel.   */
+    const uint64_t *explicit_state;
+    const uint64_t *explicit_inc;
+    const uint32_t *explicit_pixel;   /* x + y*width                           */
+    uint32_t explicit_samples_per_stream;
+    uint32_t clear_film;        /* zero the film before accumulating           */
+
+    /* Optional per-stream / per-sample outputs for the parity harness (host
+       pointers, may be NULL).  out_radiance is float or double by precision
+       and holds samples_per_stream entries per stream.                        */
+    uint64_t *out_state;
+    B2vpPathCounters *out_counters;
+    void *out_radiance;
+    B2vpCounters *totals;       /* may be NULL                                 */
+} B2vpRenderArgs;
+
+typedef struct b2vp_scene b2vp_scene_t;
+
+/* Patch for spectral sweeps: new per-wavelength scalars without re-uploading
+   grids or rebuilding the BVH.  Entries with index < 0 are ignored.           */
+typedef struct B2vpParamPatch {
+    uint32_t abi_version;
+    uint32_t struct_size;
+    int32_t medium;  double medium_scale;       /* media[medium].scale         */
+    int32_t bsdf;    double bsdf_p[4];          /* bsdfs[bsdf].p               */
+    int32_t emitter; double emitter_irradiance; /* emitters[emitter].irradiance */
+    int32_t volume;  double volume_value;       /* const volume value          */
+} B2vpParamPatch;
+
+/* Number of PCG32 streams of a (scene, seed_mode) pair and samples per stream. */
+int b2vp_stream_count(const b2vp_scene_t *scene, int32_t seed_mode,
+                      uint64_t *n_streams, uint32_t *samples_per_stream);
+
+int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **out);
+int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch);
+void b2vp_scene_destroy(b2vp_scene_t *scene);
+
+/* Renders the stream range into `film` (crop_w*crop_h*5 reals, XYZAW
+   interleaved like ImageBlock storage, float for F32 / double for F64).       */
+int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film);
+
+/* Asynchronous cancel (Integrator::cancel): polled between kernel launches.   */
+void b2vp_cancel(b2vp_scene_t *scene);
+
+/* Thread-local message of the last failing call on this thread.               */
+const char *b2vp_last_error(void);
+
+/* Library / device introspection. */
+uint32_t b2vp_abi_version(void);
+int b2vp_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2VP_H */
