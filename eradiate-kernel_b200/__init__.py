@@ -1,0 +1,10 @@
+"""B200-native `volpath` (mono) hot path of eradiate-kernel: host-side mirror of the
+reference's load_dict / render entry points over the C-ABI of include/b2vp.h."""
+from . import abi
+from .abi import B2vpError
+from .render import DeviceScene, RenderResult, render
+from .scene import Scene, load_dict, read_vol, write_vol
+from .transform import Transform
+
+__all__ = ["abi", "B2vpError", "DeviceScene", "RenderResult", "render", "Scene", "load_dict", "read_vol", "write_vol",
+           "Transform"]

@@ -1,0 +1,726 @@
+/*
+ * b2vp_api.cu -- the C-ABI of include/b2vp.h on top of the CUDA kernels.
+ *
+ * There is no CPU fallback: every entry point that computes needs an sm_100
+ * device and fails with B2VP_ERR_NO_DEVICE / B2VP_ERR_CUDA otherwise.
+ */
+#include "../../include/b2vp.h"
+#include "bvh_build.h"
+#include "vp_kernels.cuh"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace {
+
+using namespace vp;
+
+thread_local std::string g_error;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_error = buf;
+    return code;
+}
+
+#define CU_CHECK(expr)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t e_ = (expr);                                                                             \
+        if (e_ != cudaSuccess)                                                                               \
+            return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? B2VP_ERR_NO_DEVICE    \
+                                                                                     : B2VP_ERR_CUDA,        \
+                        "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__);         \
+    } while (0)
+
+/* RAII device buffer */
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    cudaError_t alloc(size_t n) {
+        release();
+        if (n == 0) n = 16;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    cudaError_t upload(const void *src, size_t n, size_t padded = 0) {
+        cudaError_t e = alloc(padded > n ? padded : n);
+        if (e != cudaSuccess) return e;
+        if (padded > n) { e = cudaMemset(p, 0, padded); if (e != cudaSuccess) return e; }
+        return n ? cudaMemcpy(p, src, n, cudaMemcpyHostToDevice) : cudaSuccess;
+    }
+    template <typename T> T *as() const { return (T *) p; }
+};
+
+/* Device copy of a scene in one arithmetic precision. */
+template <typename F> struct DeviceScene {
+    DScene<F> g{};
+    DevBuf blob, vpos, vnrm, vuv, faces, bvh, bvh_prims, sensor_xf;
+    std::vector<std::unique_ptr<DevBuf>> grids;
+    std::vector<unsigned char> host_blob;  /* kept for scene_update */
+    uint32_t smem_static = 0;              /* blob + staged grids */
+    bool ready = false;
+};
+
+} // namespace
+
+struct b2vp_scene {
+    int device = 0;
+    B2vpSceneDesc desc{};
+    std::vector<B2vpShape> shapes;
+    std::vector<B2vpBsdf> bsdfs;
+    std::vector<B2vpMedium> media;
+    std::vector<B2vpVolume> volumes;
+    std::vector<std::vector<float>> volume_data;
+    std::vector<B2vpPhase> phases;
+    std::vector<B2vpEmitter> emitters;
+    std::vector<float> vpos, vnrm, vuv;
+    std::vector<uint32_t> faces;
+    std::vector<double> sensor_xf;
+    std::vector<BvhNode> bvh_nodes;
+    std::vector<BvhPrim> bvh_prims;
+    DeviceScene<float> dev32;
+    DeviceScene<double> dev64;
+    DevBuf film_buf, totals_buf, counter_buf, blocks_buf;
+    DevBuf ex_state, ex_inc, ex_pixel, o_state, o_counters, o_radiance;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    std::atomic<int> cancelled{ 0 };
+};
+
+namespace {
+
+/* ---- validation + deep copy --------------------------------------------- */
+int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
+    s->desc = *d;
+    s->shapes.assign(d->shapes, d->shapes + d->n_shapes);
+    s->bsdfs.assign(d->bsdfs, d->bsdfs + d->n_bsdfs);
+    s->media.assign(d->media, d->media + d->n_media);
+    s->volumes.assign(d->volumes, d->volumes + d->n_volumes);
+    s->phases.assign(d->phases, d->phases + d->n_phases);
+    s->emitters.assign(d->emitters, d->emitters + d->n_emitters);
+    s->volume_data.resize(d->n_volumes);
+    for (uint32_t i = 0; i < d->n_volumes; ++i) {
+        const B2vpVolume &v = d->volumes[i];
+        if (v.type == B2VP_VOLUME_GRID) {
+            if (!v.data || v.res[0] <= 0 || v.res[1] <= 0 || v.res[2] <= 0 || (v.channels != 1 && v.channels != 3))
+                return fail(B2VP_ERR_INVALID, "volume %u: bad grid (res/channels/data)", i);
+            size_t n = (size_t) v.res[0] * v.res[1] * v.res[2] * v.channels;
+            s->volume_data[i].assign(v.data, v.data + n);
+        } else if (v.type != B2VP_VOLUME_CONST)
+            return fail(B2VP_ERR_UNSUPPORTED, "volume %u: type %d not supported by the B200 volpath", i, v.type);
+        s->volumes[i].data = nullptr;
+    }
+    for (uint32_t i = 0; i < d->n_media; ++i) {
+        const B2vpMedium &m = d->media[i];
+        if (m.sigma_t < 0 || m.sigma_t >= (int) d->n_volumes || m.albedo < 0 || m.albedo >= (int) d->n_volumes ||
+            m.phase < 0 || m.phase >= (int) d->n_phases)
+            return fail(B2VP_ERR_INVALID, "medium %u: volume/phase index out of range", i);
+        if (m.type == B2VP_MEDIUM_HETEROGENEOUS && d->volumes[m.sigma_t].type != B2VP_VOLUME_GRID)
+            return fail(B2VP_ERR_UNSUPPORTED,
+                        "heterogeneous medium needs a gridvolume sigma_t (ConstVolume::max is not implemented, "
+                        "constant3d.cpp:39)");
+        if (m.type != B2VP_MEDIUM_HOMOGENEOUS && m.type != B2VP_MEDIUM_HETEROGENEOUS)
+            return fail(B2VP_ERR_UNSUPPORTED, "medium %u: type %d not supported by the B200 volpath", i, m.type);
+    }
+    for (uint32_t i = 0; i < d->n_shapes; ++i) {
+        const B2vpShape &a = d->shapes[i];
+        if (a.type < 0 || a.type > B2VP_SHAPE_MESH)
+            return fail(B2VP_ERR_UNSUPPORTED, "shape %u: type %d not supported by the B200 volpath", i, a.type);
+        if (a.bsdf < 0 || a.bsdf >= (int) d->n_bsdfs || a.interior_medium >= (int) d->n_media ||
+            a.exterior_medium >= (int) d->n_media)
+            return fail(B2VP_ERR_INVALID, "shape %u: bsdf/medium index out of range", i);
+        if (a.type == B2VP_SHAPE_MESH &&
+            ((uint64_t) a.vertex_offset + a.vertex_count > d->n_vertices ||
+             (uint64_t) a.face_offset + a.face_count > d->n_faces))
+            return fail(B2VP_ERR_INVALID, "shape %u: vertex/face range out of the pools", i);
+    }
+    for (uint32_t i = 0; i < d->n_bsdfs; ++i)
+        if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_RPV)
+            return fail(B2VP_ERR_UNSUPPORTED, "bsdf %u: type %d not supported by the B200 volpath", i, d->bsdfs[i].type);
+    for (uint32_t i = 0; i < d->n_phases; ++i)
+        if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_HG)
+            return fail(B2VP_ERR_UNSUPPORTED, "phase %u: type %d not supported by the B200 volpath", i, d->phases[i].type);
+    for (uint32_t i = 0; i < d->n_emitters; ++i)
+        if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
+            return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
+    const B2vpSensor &sn = d->sensor;
+    if (sn.type < 0 || sn.type > B2VP_SENSOR_MRADIANCEMETER)
+        return fail(B2VP_ERR_UNSUPPORTED, "sensor type %d not supported by the B200 volpath", sn.type);
+    if (sn.type == B2VP_SENSOR_DISTANT && sn.origin_type == B2VP_ORIGIN_SHAPE)
+        return fail(B2VP_ERR_UNSUPPORTED, "distant sensor with a ray_origin shape is not supported");
+    if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_MDISTANT) && sn.target_type == B2VP_TARGET_SHAPE &&
+        (sn.target_shape < 0 || sn.target_shape >= (int) d->n_shapes ||
+         d->shapes[sn.target_shape].type != B2VP_SHAPE_RECTANGLE))
+        return fail(B2VP_ERR_UNSUPPORTED, "sensor ray_target shape must be a rectangle");
+    if ((sn.type == B2VP_SENSOR_MDISTANT || sn.type == B2VP_SENSOR_MRADIANCEMETER) &&
+        (sn.n_transforms <= 0 || !sn.transforms))
+        return fail(B2VP_ERR_INVALID, "multi-sensor without transforms");
+    if (sn.medium >= (int) d->n_media)
+        return fail(B2VP_ERR_INVALID, "sensor medium index out of range");
+    if (sn.crop_size[0] <= 0 || sn.crop_size[1] <= 0)
+        return fail(B2VP_ERR_INVALID, "empty film");
+    if (sn.n_transforms > 0 && sn.transforms)
+        s->sensor_xf.assign(sn.transforms, sn.transforms + (size_t) sn.n_transforms * 16);
+    s->desc.sensor.transforms = nullptr;
+    if (d->n_vertices) {
+        s->vpos.assign(d->vertex_positions, d->vertex_positions + (size_t) d->n_vertices * 3);
+        if (d->vertex_normals) s->vnrm.assign(d->vertex_normals, d->vertex_normals + (size_t) d->n_vertices * 3);
+        if (d->vertex_texcoords) s->vuv.assign(d->vertex_texcoords, d->vertex_texcoords + (size_t) d->n_vertices * 2);
+    }
+    if (d->n_faces) s->faces.assign(d->faces, d->faces + (size_t) d->n_faces * 3);
+    for (uint32_t i = 0; i < d->n_shapes; ++i) {
+        const B2vpShape &a = d->shapes[i];
+        if (a.type != B2VP_SHAPE_MESH) continue;
+        if ((a.has_vertex_normals && s->vnrm.empty()) || (a.has_vertex_texcoords && s->vuv.empty()))
+            return fail(B2VP_ERR_INVALID, "shape %u declares vertex normals/texcoords but the pool is NULL", i);
+        for (uint32_t f = 0; f < a.face_count; ++f)
+            for (int k = 0; k < 3; ++k)
+                if (s->faces[3 * (size_t) (a.face_offset + f) + k] >= a.vertex_count)
+                    return fail(B2VP_ERR_INVALID, "shape %u face %u: vertex index out of range", i, f);
+    }
+    s->desc.shapes = nullptr; s->desc.bsdfs = nullptr; s->desc.media = nullptr; s->desc.volumes = nullptr;
+    s->desc.phases = nullptr; s->desc.emitters = nullptr;
+    s->desc.vertex_positions = s->desc.vertex_normals = s->desc.vertex_texcoords = nullptr;
+    s->desc.faces = nullptr;
+    return B2VP_OK;
+}
+
+void build_bvh(b2vp_scene *s) {
+    std::vector<BuildTri> tris;
+    for (size_t i = 0; i < s->shapes.size(); ++i) {
+        const B2vpShape &a = s->shapes[i];
+        if (a.type != B2VP_SHAPE_MESH) continue;
+        for (uint32_t f = 0; f < a.face_count; ++f) {
+            BuildTri t;
+            t.shape = (uint32_t) i; t.face = f;
+            for (int k = 0; k < 3; ++k) { t.bmin[k] = INFINITY; t.bmax[k] = -INFINITY; }
+            for (int v = 0; v < 3; ++v) {
+                const float *p = &s->vpos[3 * (size_t) (a.vertex_offset + s->faces[3 * (size_t) (a.face_offset + f) + v])];
+                for (int k = 0; k < 3; ++k) { t.bmin[k] = std::min(t.bmin[k], p[k]); t.bmax[k] = std::max(t.bmax[k], p[k]); }
+            }
+            for (int k = 0; k < 3; ++k) t.c[k] = 0.5f * (t.bmin[k] + t.bmax[k]);
+            tris.push_back(t);
+        }
+    }
+    /* pad: ~16 float ulps of the largest coordinate a ray origin can have
+       (sensors and emitters sit up to 2 bounding-sphere radii from the centre) */
+    double scale = 0;
+    for (int k = 0; k < 3; ++k)
+        scale = std::max(scale, std::max(std::fabs(s->desc.bbox_min[k]), std::fabs(s->desc.bbox_max[k])));
+    scale += 3.0 * s->desc.bsphere_radius;
+    float pad = (float) (scale * 2e-6);
+    bvh_build(tris, pad, s->bvh_nodes, s->bvh_prims);
+}
+
+} // namespace
+
+namespace {
+
+/* ---- device upload in precision F ---------------------------------------- */
+template <typename F> void cvt(const double *src, F *dst, int n) { for (int i = 0; i < n; ++i) dst[i] = (F) src[i]; }
+
+inline uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
+
+/* shared-memory budget that still lets two CTAs share an SM */
+constexpr uint32_t SMEM_BUDGET = 100 * 1024;
+constexpr uint32_t FILM_SMEM_MAX = 16 * 1024;
+
+template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
+    const B2vpSceneDesc &d = s->desc;
+    DScene<F> &g = ds.g;
+    std::memset(&g, 0, sizeof(g));
+    const uint32_t n_shapes = (uint32_t) s->shapes.size();
+
+    std::vector<DShape<F>> shapes(n_shapes);
+    std::vector<int> analytic;
+    for (uint32_t i = 0; i < n_shapes; ++i) {
+        const B2vpShape &a = s->shapes[i];
+        DShape<F> &o = shapes[i];
+        std::memset(&o, 0, sizeof(o));
+        o.type = a.type; o.bsdf = a.bsdf; o.interior = a.interior_medium; o.exterior = a.exterior_medium;
+        cvt(a.to_world.m, o.to_world, 16); cvt(a.to_object.m, o.to_object, 16);
+        cvt(a.frame_s, o.fs, 3); cvt(a.frame_t, o.ft, 3); cvt(a.frame_n, o.fn, 3);
+        for (int k = 0; k < 3; ++k) o.translation[k] = o.to_world[12 + k];
+        o.inv_surface_area = (F) a.inv_surface_area;
+        cvt(a.center, o.center, 3);
+        o.radius = (F) a.radius; o.flip_normals = a.flip_normals;
+        o.vofs = a.vertex_offset; o.fofs = a.face_offset; o.fcount = a.face_count;
+        o.has_normals = a.has_vertex_normals; o.has_uv = a.has_vertex_texcoords;
+        if (a.type != B2VP_SHAPE_MESH) analytic.push_back((int) i);
+    }
+    std::vector<DBsdf<F>> bsdfs(s->bsdfs.size());
+    for (size_t i = 0; i < bsdfs.size(); ++i) {
+        bsdfs[i].type = s->bsdfs[i].type; bsdfs[i].pad = 0;
+        cvt(s->bsdfs[i].p, bsdfs[i].p, 4);
+    }
+    std::vector<DPhase<F>> phases(s->phases.size());
+    for (size_t i = 0; i < phases.size(); ++i) {
+        phases[i].type = s->phases[i].type; phases[i].pad = 0; phases[i].g = (F) s->phases[i].g;
+    }
+    std::vector<DEmitter<F>> emitters(s->emitters.size());
+    for (size_t i = 0; i < emitters.size(); ++i) {
+        cvt(s->emitters[i].direction, emitters[i].dir, 3);
+        emitters[i].irradiance = (F) s->emitters[i].irradiance;
+    }
+
+    /* volumes: grids are widened to F at load like the reference (volume_data.h:85-90) */
+    std::vector<DVolume<F>> volumes(s->volumes.size());
+    ds.grids.clear();
+    for (size_t i = 0; i < volumes.size(); ++i) {
+        const B2vpVolume &a = s->volumes[i];
+        DVolume<F> &o = volumes[i];
+        std::memset(&o, 0, sizeof(o));
+        o.type = a.type; o.filter = a.filter; o.wrap = a.wrap; o.channels = a.channels;
+        o.nx = a.res[0]; o.ny = a.res[1]; o.nz = a.res[2]; o.smem_offset = -1;
+        o.value = (F) a.value; o.max_value = (F) a.max_value;
+        cvt(a.bbox_min, o.bmin, 3); cvt(a.bbox_max, o.bmax, 3);
+        cvt(a.world_to_local.m, o.w2l, 16);
+        ds.grids.emplace_back(new DevBuf());
+        if (a.type == B2VP_VOLUME_GRID) {
+            const std::vector<float> &src = s->volume_data[i];
+            size_t bytes = src.size() * sizeof(F), padded = (bytes + 15) & ~(size_t) 15;
+            cudaError_t e;
+            if (sizeof(F) == sizeof(float)) {
+                e = ds.grids.back()->upload(src.data(), bytes, padded);
+            } else {
+                std::vector<F> wide(src.begin(), src.end());
+                e = ds.grids.back()->upload(wide.data(), bytes, padded);
+            }
+            if (e != cudaSuccess) return fail(B2VP_ERR_CUDA, "grid upload failed: %s", cudaGetErrorString(e));
+            o.data = ds.grids.back()->template as<F>();
+            o.data_bytes = padded;
+        }
+    }
+    std::vector<DMedium<F>> media(s->media.size());
+    for (size_t i = 0; i < media.size(); ++i) {
+        const B2vpMedium &a = s->media[i];
+        DMedium<F> &o = media[i];
+        std::memset(&o, 0, sizeof(o));
+        o.type = a.type; o.sigma_t = a.sigma_t; o.albedo = a.albedo; o.phase = a.phase;
+        o.spectral = a.has_spectral_extinction; o.sample_emitters = a.sample_emitters;
+        o.scale = (F) a.scale;
+        if (a.type == B2VP_MEDIUM_HETEROGENEOUS) {
+            const DVolume<F> &v = volumes[a.sigma_t];
+            o.max_density = o.scale * v.max_value; /* heterogeneous.cpp:29 */
+            for (int k = 0; k < 3; ++k) { o.amin[k] = v.bmin[k]; o.amax[k] = v.bmax[k]; }
+        }
+    }
+
+    /* blob layout */
+    uint32_t off = 0;
+    auto place = [&](size_t bytes) { uint32_t o = off; off = align16(off + (uint32_t) bytes); return o; };
+    g.ofs_shapes = place(shapes.size() * sizeof(DShape<F>));
+    g.ofs_analytic = place(analytic.size() * sizeof(int));
+    g.ofs_bsdfs = place(bsdfs.size() * sizeof(DBsdf<F>));
+    g.ofs_media = place(media.size() * sizeof(DMedium<F>));
+    g.ofs_volumes = place(volumes.size() * sizeof(DVolume<F>));
+    g.ofs_phases = place(phases.size() * sizeof(DPhase<F>));
+    g.ofs_emitters = place(emitters.size() * sizeof(DEmitter<F>));
+    g.blob_bytes = align16(off ? off : 16);
+    if (g.blob_bytes > 64 * 1024)
+        return fail(B2VP_ERR_UNSUPPORTED, "scene tables (%u bytes) exceed the shared-memory table budget", g.blob_bytes);
+
+    /* decide which grids are staged in shared memory */
+    uint32_t grid_off = 0;
+    for (size_t i = 0; i < volumes.size(); ++i) {
+        DVolume<F> &v = volumes[i];
+        if (v.type != 1) continue;
+        if (g.blob_bytes + FILM_SMEM_MAX + grid_off + v.data_bytes <= SMEM_BUDGET) {
+            v.smem_offset = (int) grid_off;
+            grid_off += (uint32_t) v.data_bytes;
+        }
+    }
+    g.grid_smem_bytes = grid_off;
+
+    ds.host_blob.assign(g.blob_bytes, 0);
+    auto put = [&](uint32_t o, const void *p, size_t n) { if (n) std::memcpy(ds.host_blob.data() + o, p, n); };
+    put(g.ofs_shapes, shapes.data(), shapes.size() * sizeof(DShape<F>));
+    put(g.ofs_analytic, analytic.data(), analytic.size() * sizeof(int));
+    put(g.ofs_bsdfs, bsdfs.data(), bsdfs.size() * sizeof(DBsdf<F>));
+    put(g.ofs_media, media.data(), media.size() * sizeof(DMedium<F>));
+    put(g.ofs_volumes, volumes.data(), volumes.size() * sizeof(DVolume<F>));
+    put(g.ofs_phases, phases.data(), phases.size() * sizeof(DPhase<F>));
+    put(g.ofs_emitters, emitters.data(), emitters.size() * sizeof(DEmitter<F>));
+    CU_CHECK(ds.blob.upload(ds.host_blob.data(), ds.host_blob.size()));
+    g.blob = ds.blob.template as<unsigned char>();
+
+    g.n_shapes = (int) n_shapes; g.n_analytic = (int) analytic.size(); g.n_media = (int) media.size();
+    g.n_volumes = (int) volumes.size(); g.n_emitters = (int) emitters.size();
+    g.n_bvh_nodes = (int) s->bvh_nodes.size();
+    if (!s->vpos.empty()) { CU_CHECK(ds.vpos.upload(s->vpos.data(), s->vpos.size() * 4)); g.vpos = ds.vpos.template as<float>(); }
+    if (!s->vnrm.empty()) { CU_CHECK(ds.vnrm.upload(s->vnrm.data(), s->vnrm.size() * 4)); g.vnrm = ds.vnrm.template as<float>(); }
+    if (!s->vuv.empty()) { CU_CHECK(ds.vuv.upload(s->vuv.data(), s->vuv.size() * 4)); g.vuv = ds.vuv.template as<float>(); }
+    if (!s->faces.empty()) { CU_CHECK(ds.faces.upload(s->faces.data(), s->faces.size() * 4)); g.faces = ds.faces.template as<uint32_t>(); }
+    if (!s->bvh_nodes.empty()) {
+        CU_CHECK(ds.bvh.upload(s->bvh_nodes.data(), s->bvh_nodes.size() * sizeof(BvhNode)));
+        CU_CHECK(ds.bvh_prims.upload(s->bvh_prims.data(), s->bvh_prims.size() * sizeof(BvhPrim)));
+        g.bvh = ds.bvh.template as<BvhNode>(); g.bvh_prims = ds.bvh_prims.template as<BvhPrim>();
+    }
+    if (!s->sensor_xf.empty()) {
+        std::vector<F> xf(s->sensor_xf.begin(), s->sensor_xf.end());
+        CU_CHECK(ds.sensor_xf.upload(xf.data(), xf.size() * sizeof(F)));
+        g.sensor_xf = ds.sensor_xf.template as<F>();
+    }
+
+    /* kd-tree box: scene bbox padded by (extents + 1) * eps (kdtree.h:1811-1813) */
+    for (int k = 0; k < 3; ++k) {
+        F bmin = (F) d.bbox_min[k], bmax = (F) d.bbox_max[k];
+        F extra = ((bmax - bmin) + (F) 1) * K<F>::Epsilon;
+        g.kd_min[k] = bmin - extra; g.kd_max[k] = bmax + extra;
+        g.bs_center[k] = (F) d.bsphere_center[k];
+    }
+    g.bs_radius = (F) d.bsphere_radius;
+
+    const B2vpSensor &sn = d.sensor;
+    DSensor<F> &o = g.sensor;
+    o.type = sn.type; o.direction_type = sn.direction_type; o.target_type = sn.target_type;
+    o.origin_type = sn.origin_type; o.target_shape = sn.target_shape; o.flip_directions = sn.flip_directions;
+    o.needs_aperture_sample = sn.needs_aperture_sample; o.medium = sn.medium; o.n_transforms = sn.n_transforms;
+    o.has_shutter = sn.shutter_open_time > 0 ? 1 : 0;
+    cvt(sn.to_world.m, o.to_world, 16); cvt(sn.target_point, o.target_point, 3);
+    for (int k = 0; k < 2; ++k) { o.crop_offset[k] = sn.crop_offset[k]; o.crop_size[k] = sn.crop_size[k]; }
+
+    g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;
+    g.rr_depth = (uint32_t) d.integrator.rr_depth;
+    g.hide_emitters = d.integrator.hide_emitters; g.ltr = (int) d.integrator.arg_order_ltr;
+    ds.ready = true;
+    return B2VP_OK;
+}
+
+/* ---- stream space (host mirror of integrator.cpp:51-110, spiral.cpp:8-72) -- */
+std::vector<SpiralBlockD> spiral_blocks(int w, int h, int offx, int offy, int bs) {
+    int bx = (int) std::ceil((float) w / (float) bs), by = (int) std::ceil((float) h / (float) bs);
+    int count = bx * by, counter = 0;
+    int px = bx / 2, py = by / 2, dir = 0, steps_left = 1, steps = 1;
+    std::vector<SpiralBlockD> out;
+    while (counter < count) {
+        SpiralBlockD b;
+        b.ox = px * bs; b.oy = py * bs;
+        b.sx = std::min(bs, w - b.ox); b.sy = std::min(bs, h - b.oy);
+        b.ox += offx; b.oy += offy;
+        out.push_back(b);
+        if (++counter == count) break;
+        do {
+            switch (dir) { case 0: ++px; break; case 1: ++py; break; case 2: --px; break; default: --py; break; }
+            if (--steps_left == 0) {
+                dir = (dir + 1) % 4;
+                if (dir == 2 || dir == 0) ++steps;
+                steps_left = steps;
+            }
+        } while (px < 0 || py < 0 || px >= bx || py >= by);
+    }
+    return out;
+}
+
+struct StreamSpace {
+    DStreams d{};
+    std::vector<SpiralBlockD> blocks;
+    uint64_t n_streams = 0;
+};
+
+int make_stream_space(const b2vp_scene *s, int32_t seed_mode, uint64_t explicit_n, uint32_t explicit_per,
+                      StreamSpace &sp) {
+    const B2vpSceneDesc &d = s->desc;
+    DStreams &o = sp.d;
+    o.mode = seed_mode;
+    o.w = d.sensor.crop_size[0]; o.h = d.sensor.crop_size[1];
+    o.ox = d.sensor.crop_offset[0]; o.oy = d.sensor.crop_offset[1];
+    o.seed = d.sensor.sampler_seed;
+    uint32_t spp = d.sensor.sample_count;
+    o.spp_pass = d.integrator.samples_per_pass == 0xffffffffu ? spp : std::min(d.integrator.samples_per_pass, spp);
+    if (o.spp_pass == 0 || spp % o.spp_pass != 0) /* integrator.cpp:61-63 */
+        return fail(B2VP_ERR_INVALID, "sample_count must be a multiple of samples_per_pass");
+    o.n_passes = spp / o.spp_pass;
+    o.bs = 0;
+    if (seed_mode == B2VP_SEED_SCALAR_BLOCKS) {
+        uint32_t bs = d.integrator.block_size;
+        if (bs == 0) { /* integrator.cpp:89-97 with one thread */
+            bs = 32;
+            while (!(bs == 1 || (uint64_t) ((o.w + bs - 1) / bs) * ((o.h + bs - 1) / bs) >= 1)) bs /= 2;
+        }
+        o.bs = bs;
+        sp.blocks = spiral_blocks(o.w, o.h, o.ox, o.oy, (int) bs);
+        o.n_blocks = (uint32_t) sp.blocks.size();
+        sp.n_streams = (uint64_t) o.n_passes * sp.blocks.size() * bs * bs;
+        o.samples_per_stream = o.spp_pass;
+    } else if (seed_mode == B2VP_SEED_WAVEFRONT) {
+        sp.n_streams = (uint64_t) o.w * o.h * o.spp_pass;
+        o.samples_per_stream = o.n_passes;
+    } else if (seed_mode == B2VP_SEED_EXPLICIT) {
+        sp.n_streams = explicit_n;
+        o.samples_per_stream = explicit_per;
+    } else
+        return fail(B2VP_ERR_INVALID, "unknown seed mode %d", seed_mode);
+    return B2VP_OK;
+}
+
+} // namespace
+
+namespace {
+
+template <typename F> DeviceScene<F> &dev_of(b2vp_scene *s);
+template <> DeviceScene<float> &dev_of<float>(b2vp_scene *s) { return s->dev32; }
+template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64; }
+
+inline uint32_t align128(uint32_t x) { return (x + 127u) & ~127u; }
+
+template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
+    CU_CHECK(cudaSetDevice(s->device));
+    DeviceScene<F> &ds = dev_of<F>(s);
+    if (!ds.ready) {
+        int rc = upload_scene<F>(s, ds);
+        if (rc != B2VP_OK) return rc;
+    }
+    StreamSpace sp;
+    int rc = make_stream_space(s, a->seed_mode, a->n_streams, a->explicit_samples_per_stream, sp);
+    if (rc != B2VP_OK) return rc;
+    uint64_t first = a->first_stream;
+    uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
+    if (a->seed_mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
+    if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+    if (a->seed_mode == B2VP_SEED_EXPLICIT && count &&
+        (!a->explicit_state || !a->explicit_inc || !a->explicit_pixel))
+        return fail(B2VP_ERR_INVALID, "explicit seeding needs state, inc and pixel arrays");
+    sp.d.first = first;
+    sp.d.count = count;
+    cudaStream_t stream = (cudaStream_t) a->cuda_stream;
+
+    const int W = sp.d.w, H = sp.d.h;
+    const size_t film_n = (size_t) W * H * 5, film_bytes = film_n * sizeof(F);
+    F *d_film;
+    if (a->film_on_device) {
+        d_film = (F *) film_user;
+        if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
+    } else {
+        if (s->film_buf.bytes < film_bytes) CU_CHECK(s->film_buf.alloc(film_bytes));
+        d_film = s->film_buf.as<F>();
+        if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
+        else CU_CHECK(cudaMemcpyAsync(d_film, film_user, film_bytes, cudaMemcpyHostToDevice, stream));
+    }
+
+    if (!s->totals_buf.p) CU_CHECK(s->totals_buf.alloc(TOT_N * sizeof(unsigned long long)));
+    if (!s->counter_buf.p) CU_CHECK(s->counter_buf.alloc(sizeof(unsigned long long)));
+    CU_CHECK(cudaMemsetAsync(s->totals_buf.p, 0, TOT_N * sizeof(unsigned long long), stream));
+    CU_CHECK(cudaMemsetAsync(s->counter_buf.p, 0, sizeof(unsigned long long), stream));
+
+    if (a->seed_mode == B2VP_SEED_SCALAR_BLOCKS) {
+        CU_CHECK(s->blocks_buf.upload(sp.blocks.data(), sp.blocks.size() * sizeof(SpiralBlockD)));
+        sp.d.blocks = s->blocks_buf.as<SpiralBlockD>();
+    }
+    if (a->seed_mode == B2VP_SEED_EXPLICIT && count) {
+        for (uint64_t k = 0; k < count; ++k)
+            if (a->explicit_pixel[k] >= (uint32_t) (W * H))
+                return fail(B2VP_ERR_INVALID, "explicit_pixel[%llu] outside the film", (unsigned long long) k);
+        CU_CHECK(s->ex_state.upload(a->explicit_state, count * 8));
+        CU_CHECK(s->ex_inc.upload(a->explicit_inc, count * 8));
+        CU_CHECK(s->ex_pixel.upload(a->explicit_pixel, count * 4));
+        sp.d.ex_state = s->ex_state.as<uint64_t>(); sp.d.ex_inc = s->ex_inc.as<uint64_t>();
+        sp.d.ex_pixel = s->ex_pixel.as<uint32_t>();
+    }
+
+    RenderOut<F> out{};
+    out.film = d_film;
+    out.totals = s->totals_buf.as<unsigned long long>();
+    out.work_counter = s->counter_buf.as<unsigned long long>();
+    const uint32_t sps = sp.d.samples_per_stream;
+    if (a->out_state && count) { CU_CHECK(s->o_state.alloc(count * 8)); out.out_state = s->o_state.as<uint64_t>(); }
+    if (a->out_counters && count) {
+        static_assert(sizeof(PathCounters) == sizeof(B2vpPathCounters), "counter layout");
+        CU_CHECK(s->o_counters.alloc(count * sizeof(PathCounters)));
+        out.out_counters = s->o_counters.as<PathCounters>();
+    }
+    if (a->out_radiance && count) {
+        CU_CHECK(s->o_radiance.alloc(count * sps * sizeof(F)));
+        CU_CHECK(cudaMemsetAsync(s->o_radiance.p, 0, count * sps * sizeof(F), stream));
+        out.out_radiance = s->o_radiance.as<F>();
+    }
+
+    /* shared memory: [tables][grids][film] */
+    out.grid_smem_offset = align128(ds.g.blob_bytes);
+    out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
+    out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
+    size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
+    auto kern = volpath_kernel<F>;
+    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    int per_sm = 0;
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+    if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
+    uint64_t want = (count + 255) / 256;
+    int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+
+    if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
+    uint32_t launches = 0;
+    CU_CHECK(cudaEventRecord(s->ev0, stream));
+    if (count) {
+        kern<<<grid, 256, smem, stream>>>(ds.g, sp.d, out);
+        launches++;
+    }
+    CU_CHECK(cudaEventRecord(s->ev1, stream));
+    CU_CHECK(cudaGetLastError());
+
+    unsigned long long tot[TOT_N];
+    CU_CHECK(cudaMemcpyAsync(tot, s->totals_buf.p, sizeof(tot), cudaMemcpyDeviceToHost, stream));
+    if (!a->film_on_device)
+        CU_CHECK(cudaMemcpyAsync(film_user, d_film, film_bytes, cudaMemcpyDeviceToHost, stream));
+    if (out.out_state) CU_CHECK(cudaMemcpyAsync(a->out_state, out.out_state, count * 8, cudaMemcpyDeviceToHost, stream));
+    if (out.out_counters)
+        CU_CHECK(cudaMemcpyAsync(a->out_counters, out.out_counters, count * sizeof(PathCounters),
+                                 cudaMemcpyDeviceToHost, stream));
+    if (out.out_radiance)
+        CU_CHECK(cudaMemcpyAsync(a->out_radiance, out.out_radiance, count * sps * sizeof(F), cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaStreamSynchronize(stream));
+    if (a->totals) {
+        B2vpCounters &t = *a->totals;
+        std::memset(&t, 0, sizeof(t));
+        t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
+        t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
+        t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        t.gpu_ms = ms;
+        t.n_launches = launches;
+    }
+    return B2VP_OK;
+}
+
+} // namespace
+
+/* ======================================================================== */
+extern "C" {
+
+uint32_t b2vp_abi_version(void) { return B2VP_ABI_VERSION; }
+
+const char *b2vp_last_error(void) { return g_error.c_str(); }
+
+int b2vp_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **out) {
+    if (!desc || !out) return fail(B2VP_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (desc->abi_version != B2VP_ABI_VERSION || desc->struct_size != sizeof(B2vpSceneDesc))
+        return fail(B2VP_ERR_INVALID, "B2vpSceneDesc ABI mismatch (version %u size %u, library %u/%zu)",
+                    desc->abi_version, desc->struct_size, B2VP_ABI_VERSION, sizeof(B2vpSceneDesc));
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(B2VP_ERR_NO_DEVICE, "no CUDA device available (%s); the B200 volpath has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    }
+    if (device < 0 || device >= n) return fail(B2VP_ERR_INVALID, "device ordinal %d out of range", device);
+    cudaDeviceProp prop;
+    CU_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(B2VP_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                    prop.major, prop.minor);
+    std::unique_ptr<b2vp_scene> s(new b2vp_scene());
+    s->device = device;
+    s->sm_count = prop.multiProcessorCount;
+    s->smem_optin = prop.sharedMemPerBlockOptin;
+    int rc = copy_desc(desc, s.get());
+    if (rc != B2VP_OK) return rc;
+    build_bvh(s.get());
+    CU_CHECK(cudaSetDevice(device));
+    CU_CHECK(cudaEventCreate(&s->ev0));
+    CU_CHECK(cudaEventCreate(&s->ev1));
+    *out = s.release();
+    return B2VP_OK;
+}
+
+void b2vp_scene_destroy(b2vp_scene_t *scene) {
+    if (!scene) return;
+    cudaSetDevice(scene->device);
+    if (scene->ev0) cudaEventDestroy(scene->ev0);
+    if (scene->ev1) cudaEventDestroy(scene->ev1);
+    delete scene;
+}
+
+int b2vp_stream_count(const b2vp_scene_t *scene, int32_t seed_mode, uint64_t *n_streams, uint32_t *samples_per_stream) {
+    if (!scene || !n_streams || !samples_per_stream) return fail(B2VP_ERR_INVALID, "null argument");
+    StreamSpace sp;
+    int rc = make_stream_space(scene, seed_mode, 0, 0, sp);
+    if (rc != B2VP_OK) return rc;
+    *n_streams = sp.n_streams;
+    *samples_per_stream = sp.d.samples_per_stream;
+    return B2VP_OK;
+}
+
+int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch) {
+    if (!scene || !patch) return fail(B2VP_ERR_INVALID, "null argument");
+    if (patch->abi_version != B2VP_ABI_VERSION || patch->struct_size != sizeof(B2vpParamPatch))
+        return fail(B2VP_ERR_INVALID, "B2vpParamPatch ABI mismatch");
+    if (patch->medium >= (int) scene->media.size() || patch->bsdf >= (int) scene->bsdfs.size() ||
+        patch->emitter >= (int) scene->emitters.size() || patch->volume >= (int) scene->volumes.size())
+        return fail(B2VP_ERR_INVALID, "patch index out of range");
+    if (patch->medium >= 0) scene->media[patch->medium].scale = patch->medium_scale;
+    if (patch->bsdf >= 0) std::memcpy(scene->bsdfs[patch->bsdf].p, patch->bsdf_p, sizeof(patch->bsdf_p));
+    if (patch->emitter >= 0) scene->emitters[patch->emitter].irradiance = patch->emitter_irradiance;
+    if (patch->volume >= 0) {
+        if (scene->volumes[patch->volume].type != B2VP_VOLUME_CONST)
+            return fail(B2VP_ERR_INVALID, "volume patch targets a grid volume");
+        scene->volumes[patch->volume].value = patch->volume_value;
+    }
+    /* only the small tables change: rebuild and re-upload the blob, grids and BVH stay resident */
+    CU_CHECK(cudaSetDevice(scene->device));
+    auto patch_dev = [&](auto &ds) -> int {
+        using DS = std::remove_reference_t<decltype(ds)>;
+        using F = decltype(ds.g.bs_radius);
+        (void) sizeof(DS);
+        if (!ds.ready) return B2VP_OK;
+        unsigned char *b = ds.host_blob.data();
+        auto *media = reinterpret_cast<DMedium<F> *>(b + ds.g.ofs_media);
+        auto *volumes = reinterpret_cast<DVolume<F> *>(b + ds.g.ofs_volumes);
+        auto *bsdfs = reinterpret_cast<DBsdf<F> *>(b + ds.g.ofs_bsdfs);
+        auto *emitters = reinterpret_cast<DEmitter<F> *>(b + ds.g.ofs_emitters);
+        if (patch->medium >= 0) {
+            DMedium<F> &m = media[patch->medium];
+            m.scale = (F) patch->medium_scale;
+            if (m.type == B2VP_MEDIUM_HETEROGENEOUS) m.max_density = m.scale * volumes[m.sigma_t].max_value;
+        }
+        if (patch->bsdf >= 0) for (int k = 0; k < 4; ++k) bsdfs[patch->bsdf].p[k] = (F) patch->bsdf_p[k];
+        if (patch->emitter >= 0) emitters[patch->emitter].irradiance = (F) patch->emitter_irradiance;
+        if (patch->volume >= 0) volumes[patch->volume].value = (F) patch->volume_value;
+        CU_CHECK(cudaMemcpy(ds.blob.p, b, ds.host_blob.size(), cudaMemcpyHostToDevice));
+        return B2VP_OK;
+    };
+    int rc = patch_dev(scene->dev32);
+    if (rc != B2VP_OK) return rc;
+    return patch_dev(scene->dev64);
+}
+
+int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film) {
+    if (!scene || !args || !film) return fail(B2VP_ERR_INVALID, "null argument");
+    if (args->abi_version != B2VP_ABI_VERSION || args->struct_size != sizeof(B2vpRenderArgs))
+        return fail(B2VP_ERR_INVALID, "B2vpRenderArgs ABI mismatch");
+    if (args->device != scene->device)
+        return fail(B2VP_ERR_INVALID, "scene lives on device %d, render asked for %d", scene->device, args->device);
+    if (args->precision == B2VP_PREC_F32) return render_typed<float>(scene, args, film);
+    if (args->precision == B2VP_PREC_F64) return render_typed<double>(scene, args, film);
+    return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
+}
+
+void b2vp_cancel(b2vp_scene_t *scene) {
+    if (scene) scene->cancelled.store(1);
+}
+
+} /* extern "C" */

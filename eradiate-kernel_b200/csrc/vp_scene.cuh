@@ -1,0 +1,646 @@
+/*
+ * vp_scene.cuh -- device-side shapes, BVH traversal, volumes, media, phase
+ * functions, BSDFs, emitter and sensors of the volpath hot path (mono).
+ *
+ * Each function cites the reference code whose result it reproduces (paths
+ * relative to the reference tree).  The reference's bugs are part of the
+ * contract: they are reproduced, not fixed.
+ */
+#pragma once
+#include "vp_types.cuh"
+
+namespace vp {
+
+/* Per-thread view of the scene: table pointers resolved to shared memory when
+   the CTA staged them there. */
+template <typename F> struct SceneView {
+    const DScene<F> *g;             /* kernel parameter (constant bank) */
+    const DShape<F> *shapes;
+    const int *analytic;
+    const DBsdf<F> *bsdfs;
+    const DMedium<F> *media;
+    const DVolume<F> *volumes;
+    const DPhase<F> *phases;
+    const DEmitter<F> *emitters;
+    const unsigned char *grid_smem; /* base of the staged grids */
+};
+
+template <typename F> struct SurfaceHit {
+    F t;
+    V3<F> p, n, wi;
+    Frame<F> sh;
+    int shape;
+    VP_D bool valid() const { return t != inf_<F>(); }
+};
+
+/* ------------------------------------------------------------------ shapes */
+
+/* Rectangle::ray_intersect_preliminary (src/shapes/rectangle.cpp:139-159) */
+template <typename F> VP_D F rectangle_intersect(const DShape<F> &sh, const Ray<F> &r) {
+    V3<F> o = xf_point_affine(sh.to_object, r.o), d = xf_vector(sh.to_object, r.d);
+    F drz = rcp_(d.z);
+    F t = -o.z * drz;
+    F lx = fma_(d.x, t, o.x), ly = fma_(d.y, t, o.y);
+    bool active = t >= r.mint && t <= r.maxt && abs_(lx) <= (F) 1 && abs_(ly) <= (F) 1;
+    return active ? t : inf_<F>();
+}
+
+/* math::solve_quadratic (include/mitsuba/core/math.h) in double */
+VP_D bool solve_quadratic(double a, double b, double c, double &x0, double &x1) {
+    bool linear_case = a == 0.0;
+    bool valid_linear = linear_case && b != 0.0;
+    x0 = x1 = -c / b;
+    double discrim = fma_(b, b, -(4.0 * a) * c);
+    bool valid_quadratic = !linear_case && discrim >= 0.0;
+    if (valid_quadratic) {
+        double root = sqrt_(discrim);
+        double temp = -0.5 * (b + (signbit_(b) ? -root : root));
+        double x0p = temp / a, x1p = c / temp;
+        x0 = min_(x0p, x1p);
+        x1 = max_(x0p, x1p);
+    }
+    return valid_linear || valid_quadratic;
+}
+
+/* Sphere::ray_intersect_preliminary (src/shapes/sphere.cpp:272-306): always double */
+template <typename F> VP_D F sphere_intersect(const DShape<F> &sh, const Ray<F> &r) {
+    double mint = (double) r.mint, maxt = (double) r.maxt;
+    V3<double> o = mk3<double>((double) r.o.x - (double) sh.center[0], (double) r.o.y - (double) sh.center[1],
+                               (double) r.o.z - (double) sh.center[2]);
+    V3<double> d = mk3<double>((double) r.d.x, (double) r.d.y, (double) r.d.z);
+    double A = dot(d, d), B = 2.0 * dot(o, d), C = dot(o, o) - sqr((double) sh.radius);
+    double near_t, far_t;
+    bool found = solve_quadratic(A, B, C, near_t, far_t);
+    bool out_bounds = !(near_t <= maxt && far_t >= mint);
+    bool in_bounds = near_t < mint && far_t > maxt;
+    bool active = found && !out_bounds && !in_bounds;
+    return active ? (near_t < mint ? (F) far_t : (F) near_t) : inf_<F>();
+}
+
+template <typename F> VP_D V3<F> load_vertex(const DScene<F> &g, const DShape<F> &sh, uint32_t i) {
+    const float *p = g.vpos + 3 * (size_t) (sh.vofs + i);
+    return mk3<F>((F) __ldg(p), (F) __ldg(p + 1), (F) __ldg(p + 2));
+}
+
+/* Mesh::ray_intersect_triangle (include/mitsuba/render/mesh.h:195-226), Moeller-Trumbore */
+template <typename F>
+VP_D F triangle_intersect(V3<F> p0, V3<F> p1, V3<F> p2, const Ray<F> &r, F &u_out, F &v_out) {
+    V3<F> e1 = p1 - p0, e2 = p2 - p0;
+    V3<F> pvec = cross(r.d, e2);
+    F inv_det = rcp_(dot(e1, pvec));
+    V3<F> tvec = r.o - p0;
+    F u = dot(tvec, pvec) * inv_det;
+    bool active = u >= 0 && u <= (F) 1;
+    V3<F> qvec = cross(tvec, e1);
+    F v = dot(r.d, qvec) * inv_det;
+    active = active && v >= 0 && u + v <= (F) 1;
+    F t = dot(e2, qvec) * inv_det;
+    active = active && t >= r.mint && t <= r.maxt;
+    u_out = u;
+    v_out = v;
+    return active ? t : inf_<F>();
+}
+
+/* SurfaceInteraction::initialize_sh_frame (include/mitsuba/render/interaction.h:153-156) */
+template <typename F> VP_D void initialize_sh_frame(SurfaceHit<F> &si, V3<F> dp_du) {
+    F d = dot(si.sh.n, dp_du);
+    V3<F> v = mk3<F>(fma_(-si.sh.n.x, d, dp_du.x), fma_(-si.sh.n.y, d, dp_du.y), fma_(-si.sh.n.z, d, dp_du.z));
+    si.sh.s = normalize(v);
+    si.sh.t = cross(si.sh.n, si.sh.s);
+}
+
+/* Scene::ray_intersect (src/librender/scene.cpp:117-125): closest hit with
+   ray.mint <= t <= ray.maxt after clipping against the padded scene box
+   (kdtree.h:2078-2171).  Exact ties go to the primitive that comes later in
+   (shape, face) order -- the outcome of the reference's `t <= maxt` update rule
+   when primitives are visited in that order.  Triangles go through a BVH; its
+   slab test is conservative so the candidate set always contains the winner.  */
+template <typename F>
+__device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si,
+                                           PathCounters &cnt) {
+    const DScene<F> &g = *sv.g;
+    cnt.n_intersect++;
+    si.t = inf_<F>();
+    si.shape = -1;
+    si.wi = -ray_in.d; /* scene_native.inl:36-38 */
+    si.p = mk3<F>(0, 0, 0); si.n = si.p; si.sh.s = si.p; si.sh.t = si.p; si.sh.n = si.p;
+    Ray<F> ray = ray_in;
+    F bmin, bmax;
+    bbox_ray_intersect(g.kd_min, g.kd_max, ray, bmin, bmax);
+    F mint = max_(ray.mint, bmin), maxt = min_(ray.maxt, bmax);
+    if (!(mint <= maxt))
+        return;
+
+    int best_shape = -1;
+    uint32_t best_prim = 0;
+    F best_u = 0, best_v = 0;
+
+    /* analytic shapes, in shape order */
+    for (int k = 0; k < g.n_analytic; ++k) {
+        int i = sv.analytic[k];
+        const DShape<F> &sh = sv.shapes[i];
+        F t = sh.type == 0 ? rectangle_intersect(sh, ray) : sphere_intersect(sh, ray);
+        if (t != inf_<F>() && (t < ray.maxt || i > best_shape)) {
+            best_shape = i;
+            ray.maxt = t;
+        }
+    }
+
+    /* triangles */
+    if (g.n_bvh_nodes > 0) {
+        uint32_t stack[48];
+        int sp = 0;
+        uint32_t node = 0;
+        /* conservative slab test in float: widen by a few ulps */
+        const float ox = (float) ray.o.x, oy = (float) ray.o.y, oz = (float) ray.o.z;
+        const float ix = (float) ray.d_rcp.x, iy = (float) ray.d_rcp.y, iz = (float) ray.d_rcp.z;
+        const float rmint = (float) ray.mint;
+        const float lo_s = 1.f - 8.f * 1.1920929e-7f, hi_s = 1.f + 8.f * 1.1920929e-7f;
+        while (true) {
+            const float4 a = __ldg(reinterpret_cast<const float4 *>(g.bvh + node));
+            const float4 b = __ldg(reinterpret_cast<const float4 *>(g.bvh + node) + 1);
+            const uint32_t child = __float_as_uint(a.w), count = __float_as_uint(b.w);
+            float t1x = (a.x - ox) * ix, t2x = (b.x - ox) * ix;
+            float t1y = (a.y - oy) * iy, t2y = (b.y - oy) * iy;
+            float t1z = (a.z - oz) * iz, t2z = (b.z - oz) * iz;
+            /* NaN (0 * inf) never rejects: fminf/fmaxf drop NaN operands */
+            float tn = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
+            float tf = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
+            tn = tn > 0.f ? tn * lo_s : tn * hi_s;
+            tf = tf > 0.f ? tf * hi_s : tf * lo_s;
+            float cur_max = (float) ray.maxt;
+            cur_max = cur_max > 0.f ? cur_max * hi_s : cur_max * lo_s;
+            bool hit = tn <= tf && tf >= rmint * lo_s && tn <= cur_max;
+            if (hit) {
+                if (count == 0) {
+                    /* descend; push the second child */
+                    stack[sp++] = child + 1;
+                    node = child;
+                    continue;
+                }
+                for (uint32_t k = 0; k < count; ++k) {
+                    const BvhPrim pr = g.bvh_prims[child + k];
+                    const DShape<F> &sh = sv.shapes[pr.shape];
+                    const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + pr.face);
+                    V3<F> p0 = load_vertex(g, sh, __ldg(fi)), p1 = load_vertex(g, sh, __ldg(fi + 1)),
+                          p2 = load_vertex(g, sh, __ldg(fi + 2));
+                    F u, v;
+                    F t = triangle_intersect(p0, p1, p2, ray, u, v);
+                    if (t != inf_<F>()) {
+                        bool later = (int) pr.shape > best_shape ||
+                                     ((int) pr.shape == best_shape && pr.face > best_prim);
+                        if (t < ray.maxt || later) {
+                            best_shape = (int) pr.shape; best_prim = pr.face; best_u = u; best_v = v;
+                            ray.maxt = t;
+                        }
+                    }
+                }
+            }
+            if (sp == 0) break;
+            node = stack[--sp];
+        }
+    }
+    if (best_shape < 0)
+        return;
+
+    /* PreliminaryIntersection::compute_surface_interaction (interaction.h:571-596) */
+    const DShape<F> &sh = sv.shapes[best_shape];
+    F t = ray.maxt;
+    si.t = t;
+    si.shape = best_shape;
+    V3<F> dp_du;
+    if (sh.type == 0) { /* rectangle.cpp:175-212 */
+        V3<F> p = ray_in.at(t);
+        V3<F> fn = ld3(sh.fn);
+        F dist = dot(ld3(sh.translation) - p, fn);
+        si.p = fmadd3(fn, dist, p);
+        si.n = fn;
+        si.sh.n = fn;
+        dp_du = ld3(sh.fs);
+    } else if (sh.type == 1) { /* sphere.cpp:335-400 */
+        V3<F> c = ld3(sh.center);
+        si.sh.n = normalize(ray_in.at(t) - c);
+        si.p = fmadd3(si.sh.n, sh.radius, c);
+        V3<F> local = xf_point_affine(sh.to_object, si.p);
+        dp_du = mk3<F>(-local.y, local.x, (F) 0);
+        dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
+        if (sh.flip_normals) si.sh.n = -si.sh.n;
+        si.n = si.sh.n;
+    } else { /* src/librender/mesh.cpp:450-545 */
+        F b1 = best_u, b2 = best_v, b0 = (F) 1 - b1 - b2;
+        const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + best_prim);
+        uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
+        V3<F> p0 = load_vertex(g, sh, i0), p1 = load_vertex(g, sh, i1), p2 = load_vertex(g, sh, i2);
+        V3<F> dp0 = p1 - p0, dp1 = p2 - p0;
+        si.p = p0 * b0 + p1 * b1 + p2 * b2;
+        si.n = normalize(cross(dp0, dp1));
+        V3<F> dp_dv;
+        coordinate_system(si.n, dp_du, dp_dv);
+        if (sh.has_uv) {
+            const float *t0 = g.vuv + 2 * (size_t) (sh.vofs + i0), *t1 = g.vuv + 2 * (size_t) (sh.vofs + i1),
+                        *t2 = g.vuv + 2 * (size_t) (sh.vofs + i2);
+            F du0 = (F) t1[0] - (F) t0[0], dv0 = (F) t1[1] - (F) t0[1];
+            F du1 = (F) t2[0] - (F) t0[0], dv1 = (F) t2[1] - (F) t0[1];
+            F det = fma_(du0, dv1, -(dv0 * du1)), inv_det = rcp_(det);
+            if (det != 0) {
+                dp_du = mk3<F>(fma_(dv1, dp0.x, -(dv0 * dp1.x)) * inv_det, fma_(dv1, dp0.y, -(dv0 * dp1.y)) * inv_det,
+                               fma_(dv1, dp0.z, -(dv0 * dp1.z)) * inv_det);
+            }
+        }
+        if (sh.has_normals) {
+            const float *q0 = g.vnrm + 3 * (size_t) (sh.vofs + i0), *q1 = g.vnrm + 3 * (size_t) (sh.vofs + i1),
+                        *q2 = g.vnrm + 3 * (size_t) (sh.vofs + i2);
+            V3<F> n0 = mk3<F>((F) q0[0], (F) q0[1], (F) q0[2]), n1 = mk3<F>((F) q1[0], (F) q1[1], (F) q1[2]),
+                  n2 = mk3<F>((F) q2[0], (F) q2[1], (F) q2[2]);
+            si.sh.n = normalize(n0 * b0 + n1 * b1 + n2 * b2);
+        } else {
+            si.sh.n = si.n;
+        }
+    }
+    initialize_sh_frame(si, dp_du);
+    si.wi = si.sh.to_local(-ray_in.d);
+}
+
+/* ----------------------------------------------------------------- volumes */
+
+/* GridVolumeImpl::wrap (src/textures/grid3d.cpp:234-250), one coordinate */
+VP_D int wrap_coord(int v, int res, int mode) {
+    if (mode == 2 /* clamp */)
+        return min(max(v, 0), res - 1);
+    int dv = v / res, md = v - dv * res; /* enoki::divisor<int32_t> truncates */
+    if (md < 0) md += res;
+    if (mode == 1 /* mirror */) {
+        bool keep = ((dv & 1) == 0) != (v < 0);
+        md = keep ? md : res - 1 - md;
+    }
+    return md;
+}
+
+template <typename F> VP_D int floor2int(F x) { return (int) floor_(x); }
+
+/* GridVolumeImpl::eval (src/textures/grid3d.cpp:163-185,220-360) and
+   ConstVolume::eval (src/textures/constant3d.cpp:31-37) */
+template <typename F> VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
+    if (v.type == 0)
+        return v.value;
+    V3<F> p = xf_point(v.w2l, p_world); /* grid3d.cpp:227: full 4x4 with the w divide */
+    const int nx = v.nx, ny = v.ny, nz = v.nz, ch = v.channels;
+    const F *data = v.smem_offset >= 0 ? reinterpret_cast<const F *>(sv.grid_smem + v.smem_offset) : v.data;
+    F res[3];
+    if (v.filter == 1) { /* trilinear, grid3d.cpp:271-341 */
+        p = mk3<F>(fma_(p.x, (F) nx, (F) -0.5), fma_(p.y, (F) ny, (F) -0.5), fma_(p.z, (F) nz, (F) -0.5));
+        int ix = floor2int(p.x), iy = floor2int(p.y), iz = floor2int(p.z);
+        F w1x = p.x - (F) ix, w1y = p.y - (F) iy, w1z = p.z - (F) iz;
+        F w0x = (F) 1 - w1x, w0y = (F) 1 - w1y, w0z = (F) 1 - w1z;
+        int x0 = wrap_coord(ix, nx, v.wrap), x1 = wrap_coord(ix + 1, nx, v.wrap);
+        int y0 = wrap_coord(iy, ny, v.wrap), y1 = wrap_coord(iy + 1, ny, v.wrap);
+        int z0 = wrap_coord(iz, nz, v.wrap), z1 = wrap_coord(iz + 1, nz, v.wrap);
+        size_t r00 = ((size_t) z0 * ny + y0) * nx, r10 = ((size_t) z0 * ny + y1) * nx,
+               r01 = ((size_t) z1 * ny + y0) * nx, r11 = ((size_t) z1 * ny + y1) * nx;
+#pragma unroll 1
+        for (int c = 0; c < ch; ++c) {
+            F d000 = data[(r00 + x0) * ch + c], d100 = data[(r00 + x1) * ch + c];
+            F d010 = data[(r10 + x0) * ch + c], d110 = data[(r10 + x1) * ch + c];
+            F d001 = data[(r01 + x0) * ch + c], d101 = data[(r01 + x1) * ch + c];
+            F d011 = data[(r11 + x0) * ch + c], d111 = data[(r11 + x1) * ch + c];
+            F v00 = fma_(w0x, d000, w1x * d100), v01 = fma_(w0x, d001, w1x * d101);
+            F v10 = fma_(w0x, d010, w1x * d110), v11 = fma_(w0x, d011, w1x * d111);
+            F v0 = fma_(w0y, v00, w1y * v10), v1 = fma_(w0y, v01, w1y * v11);
+            res[c] = fma_(w0z, v0, w1z * v1);
+        }
+    } else { /* nearest, grid3d.cpp:342-356 */
+        p = mk3<F>(p.x * (F) nx, p.y * (F) ny, p.z * (F) nz);
+        int x = wrap_coord(floor2int(p.x), nx, v.wrap), y = wrap_coord(floor2int(p.y), ny, v.wrap),
+            z = wrap_coord(floor2int(p.z), nz, v.wrap);
+        size_t idx = (((size_t) z * ny + y) * nx + x) * ch;
+#pragma unroll 1
+        for (int c = 0; c < ch; ++c) res[c] = data[idx + c];
+    }
+    if (ch == 1) return res[0];
+    /* mitsuba::luminance(Color3f) with float literals (include/mitsuba/core/spectrum.h:247) */
+    return res[0] * (F) 0.212671f + res[1] * (F) 0.715160f + res[2] * (F) 0.072169f;
+}
+
+/* ------------------------------------------------------------------- media */
+template <typename F> struct MediumHit {
+    F t, mint;
+    V3<F> p;
+    F sigma_s, sigma_n, sigma_t, combined;
+    VP_D bool valid() const { return t != inf_<F>(); }
+};
+
+/* Medium::sample_interaction (src/librender/medium.cpp:36-75) over
+   HeterogeneousMedium / HomogeneousMedium (src/media/*.cpp).  The shading frame
+   Frame3f(ray.d) and wi = -ray.d that the reference stores per step are pure
+   functions of ray.d and are rebuilt where a scattering event needs them. */
+template <typename F>
+VP_D void sample_interaction(const SceneView<F> &sv, const DMedium<F> &m, const Ray<F> &ray, F sample,
+                             MediumHit<F> &mi, PathCounters &cnt) {
+    cnt.medium_steps++;
+    bool aabb_its;
+    F mint, maxt;
+    if (m.type == 0) { /* homogeneous.cpp:51-54 */
+        aabb_its = true; mint = 0; maxt = inf_<F>();
+    } else {           /* heterogeneous.cpp:50-53 */
+        aabb_its = bbox_ray_intersect(m.amin, m.amax, ray, mint, maxt);
+    }
+    aabb_its = aabb_its && (finite_(mint) || finite_(maxt));
+    bool active = aabb_its;
+    if (!active) { mint = 0; maxt = inf_<F>(); }
+    mint = max_(ray.mint, mint);
+    maxt = min_(ray.maxt, maxt);
+    F combined;
+    if (m.type == 0)
+        combined = volume_eval(sv, sv.volumes[m.sigma_t], ray.o) * m.scale; /* homogeneous.cpp:30-38 */
+    else
+        combined = m.max_density;
+    F sampled_t = mint + (-log_((F) 1 - sample) / combined);
+    bool valid_mi = active && (sampled_t <= maxt);
+    mi.t = valid_mi ? sampled_t : inf_<F>();
+    mi.p = ray.at(sampled_t);
+    mi.mint = mint;
+    mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0;
+    if (valid_mi) {
+        F albedo = volume_eval(sv, sv.volumes[m.albedo], mi.p);
+        F sigmat;
+        if (m.type == 0) {
+            sigmat = volume_eval(sv, sv.volumes[m.sigma_t], mi.p) * m.scale;
+            mi.sigma_n = 0;
+        } else {
+            sigmat = m.scale * volume_eval(sv, sv.volumes[m.sigma_t], mi.p);
+            mi.sigma_n = combined - sigmat;
+        }
+        mi.sigma_t = sigmat;
+        mi.sigma_s = sigmat * albedo;
+    }
+    mi.combined = combined;
+}
+
+/* Medium::eval_tr_and_pdf (medium.cpp:77-89) followed by tr / tr_pdf
+   (src/integrators/volpath.cpp:113-117,402-404) */
+template <typename F> VP_D F tr_over_pdf(const MediumHit<F> &mi, F si_t) {
+    F t = min_(mi.t, si_t) - mi.mint;
+    F tr = exp_(-t * mi.combined);
+    F pdf = si_t < mi.t ? tr : tr * mi.combined;
+    return pdf > 0 ? tr / pdf : (F) 0;
+}
+
+/* ------------------------------------------------------------------- warps */
+/* warp::square_to_uniform_disk_concentric (include/mitsuba/core/warp.h:54-90) */
+template <typename F> VP_D void square_to_uniform_disk_concentric(F sx, F sy, F &ox, F &oy) {
+    F x = fma_((F) 2, sx, (F) -1), y = fma_((F) 2, sy, (F) -1);
+    bool is_zero = x == 0 && y == 0, quadrant_1_or_3 = abs_(x) < abs_(y);
+    F r = quadrant_1_or_3 ? y : x, rp = quadrant_1_or_3 ? x : y;
+    F phi = (F) 0.25 * K<F>::Pi * rp / r;
+    if (quadrant_1_or_3) phi = (F) 0.5 * K<F>::Pi - phi;
+    if (is_zero) phi = 0;
+    F s, c;
+    sincos_(phi, s, c);
+    ox = r * c;
+    oy = r * s;
+}
+/* warp::square_to_cosine_hemisphere (warp.h:325-334) */
+template <typename F> VP_D V3<F> square_to_cosine_hemisphere(F sx, F sy) {
+    F px, py;
+    square_to_uniform_disk_concentric(sx, sy, px, py);
+    F z = safe_sqrt_((F) 1 - (px * px + py * py));
+    return mk3<F>(px, py, z);
+}
+/* warp::square_to_uniform_hemisphere (warp.h:298-303) */
+template <typename F> VP_D V3<F> square_to_uniform_hemisphere(F sx, F sy) {
+    F px, py;
+    square_to_uniform_disk_concentric(sx, sy, px, py);
+    F z = (F) 1 - (px * px + py * py);
+    F k = sqrt_(z + (F) 1);
+    return mk3<F>(px * k, py * k, z);
+}
+/* warp::square_to_uniform_sphere (warp.h:255-260) */
+template <typename F> VP_D V3<F> square_to_uniform_sphere(F sx, F sy) {
+    F z = fma_((F) -2, sy, (F) 1);
+    F r = safe_sqrt_(fma_(-z, z, (F) 1));
+    F s, c;
+    sincos_((F) 2 * K<F>::Pi * sx, s, c);
+    return mk3<F>(r * c, r * s, z);
+}
+
+/* ------------------------------------------------------------------- phase */
+/* PhaseFunction::eval (src/phase/rayleigh.cpp:42-45,68-74, hg.cpp:47-50,78-84, isotropic.cpp:41) */
+template <typename F> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo) {
+    if (ph.type == 0) return K<F>::InvFourPi;
+    F cos_theta = dot(wo, wi);
+    if (ph.type == 1)
+        return ((F) 3 / (F) 16) * K<F>::InvPi * ((F) 1 + sqr(cos_theta));
+    F g = ph.g;
+    F temp = (F) 1 + g * g + (F) 2 * g * cos_theta;
+    return K<F>::InvFourPi * ((F) 1 - g * g) / (temp * sqrt_(temp));
+}
+/* PhaseFunction::sample (rayleigh.cpp:47-66, hg.cpp:52-76, isotropic.cpp:31-39);
+   `d` is the incoming ray direction, the local frame is Frame3f(d) (medium.cpp:42) */
+template <typename F> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2x, F s2y) {
+    if (ph.type == 0)
+        return square_to_uniform_sphere(s2x, s2y);
+    F cos_theta;
+    if (ph.type == 1) {
+        F z = (F) 2 * ((F) 2 * s2x - (F) 1);
+        F tmp = sqrt_(sqr(z) + (F) 1);
+        F A = cbrt_(z + tmp), B = cbrt_(z - tmp);
+        cos_theta = A + B;
+    } else {
+        F g = ph.g;
+        if (abs_(g) < K<F>::Epsilon) {
+            cos_theta = (F) 1 - (F) 2 * s2x;
+        } else {
+            F sqr_term = ((F) 1 - g * g) / ((F) 1 - g + (F) 2 * g * s2x);
+            cos_theta = ((F) 1 + g * g - sqr_term * sqr_term) / ((F) 2 * g);
+        }
+    }
+    F sin_theta = safe_sqrt_((F) 1 - cos_theta * cos_theta);
+    F s, c;
+    sincos_((F) 2 * K<F>::Pi * s2y, s, c);
+    V3<F> wo = mk3<F>(sin_theta * c, sin_theta * s, cos_theta);
+    return make_frame(d).to_world(wo);
+}
+
+/* ------------------------------------------------------------------- BSDFs */
+enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
+    BF_Null = 0x1, BF_DiffuseReflection = 0x2, BF_GlossyReflection = 0x8,
+    BF_Smooth = 0x2 | 0x4 | 0x8 | 0x10, BF_Delta = 0x1 | 0x20 | 0x40
+};
+VP_D uint32_t bsdf_flags(int type) { return type == 1 ? BF_Null : (type == 0 ? BF_DiffuseReflection : BF_GlossyReflection); }
+
+/* Frame::sincos_phi (include/mitsuba/core/frame.h:107-118) */
+template <typename F> VP_D void sincos_phi(V3<F> v, F &s, F &c) {
+    F sin_theta_2 = fma_(v.x, v.x, sqr(v.y));
+    F inv_sin_theta = rsqrt_(sin_theta_2);
+    F rx = v.x * inv_sin_theta, ry = v.y * inv_sin_theta;
+    if (abs_(sin_theta_2) <= (F) 4 * K<F>::Epsilon) { rx = 1; ry = 0; }
+    else { rx = min_(max_(rx, (F) -1), (F) 1); ry = min_(max_(ry, (F) -1), (F) 1); }
+    s = ry;
+    c = rx;
+}
+template <typename F> VP_D F frame_sin_theta(V3<F> v) { return safe_sqrt_(fma_(v.x, v.x, sqr(v.y))); }
+template <typename F> VP_D F frame_tan_theta(V3<F> v) { return safe_sqrt_(fma_(-v.z, v.z, (F) 1)) / v.z; }
+
+/* RPV::eval_rpv (src/bsdfs/rpv.cpp:107-141); pow = exp(log(x)*y) as enoki evaluates it */
+template <typename F> __device__ __noinline__ F eval_rpv(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
+    F rho_0 = b.p[0], k = b.p[1], g = b.p[2], rho_c = b.p[3];
+    F sin_phi1, cos_phi1, sin_phi2, cos_phi2;
+    sincos_phi(wi, sin_phi1, cos_phi1);
+    sincos_phi(wo, sin_phi2, cos_phi2);
+    F cos_dphi = cos_phi1 * cos_phi2 + sin_phi1 * sin_phi2;
+    F sin_theta1 = frame_sin_theta(wi), cos_theta1 = wi.z, tan_theta1 = frame_tan_theta(wi);
+    F sin_theta2 = frame_sin_theta(wo), cos_theta2 = wo.z, tan_theta2 = frame_tan_theta(wo);
+    F G = safe_sqrt_(sqr(tan_theta1) + sqr(tan_theta2) - (F) 2 * tan_theta1 * tan_theta2 * cos_dphi);
+    F cos_g = cos_theta1 * cos_theta2 + sin_theta1 * sin_theta2 * cos_dphi;
+    F Fg = ((F) 1 - sqr(g)) / pow_(((F) 1 + sqr(g) + (F) 2 * g * cos_g), (F) 1.5);
+    return rho_0 * (pow_(cos_theta1 * cos_theta2 * (cos_theta1 + cos_theta2), k - (F) 1) * Fg *
+                    ((F) 1 + ((F) 1 - rho_c) / ((F) 1 + G))) * K<F>::InvPi;
+}
+
+/* BSDF::sample (src/bsdfs/diffuse.cpp:78-102, rpv.cpp:85-105 [weight = f, F8], null.cpp:41-57) */
+template <typename F>
+VP_D void bsdf_sample(const DBsdf<F> &b, V3<F> wi, F s2x, F s2y, V3<F> &wo, F &pdf, F &eta, uint32_t &sampled_type,
+                      F &weight) {
+    wo = mk3<F>(0, 0, 0); pdf = 0; eta = 0; sampled_type = 0; weight = 0;
+    if (b.type == 1) {
+        wo = -wi; sampled_type = BF_Null; eta = 1; pdf = 1; weight = 1;
+        return;
+    }
+    bool active = wi.z > 0;
+    if (b.type == 0) {
+        if (!active) return; /* zero-initialised sample (diffuse.cpp:90-92) */
+        wo = square_to_cosine_hemisphere(s2x, s2y);
+        pdf = K<F>::InvPi * wo.z;
+        eta = 1; sampled_type = BF_DiffuseReflection;
+        weight = (active && pdf > 0) ? b.p[0] : (F) 0;
+        return;
+    }
+    wo = square_to_cosine_hemisphere(s2x, s2y);
+    pdf = K<F>::InvPi * wo.z;
+    eta = 1; sampled_type = BF_GlossyReflection;
+    F value = eval_rpv(b, wi, wo);
+    weight = (active && pdf > 0) ? value : (F) 0;
+}
+/* BSDF::eval (diffuse.cpp:104-120, rpv.cpp:143-155, null.cpp:59-62) */
+template <typename F> VP_D F bsdf_eval(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
+    if (b.type == 1) return 0;
+    bool active = wi.z > 0 && wo.z > 0;
+    if (b.type == 0) {
+        F value = b.p[0] * K<F>::InvPi * wo.z;
+        return active ? value : (F) 0;
+    }
+    F value = eval_rpv(b, wi, wo);
+    return active ? value * abs_(wo.z) : (F) 0;
+}
+/* BSDF::pdf (diffuse.cpp:122-135, rpv.cpp:157-168) */
+template <typename F> VP_D F bsdf_pdf(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
+    if (b.type == 1) return 0;
+    F pdf = K<F>::InvPi * wo.z;
+    return (wi.z > 0 && wo.z > 0) ? pdf : (F) 0;
+}
+
+/* ----------------------------------------------------------------- emitter */
+template <typename F> struct DirSample { V3<F> d; F dist, pdf; bool delta; };
+
+/* Scene::sample_emitter_direction (src/librender/scene.cpp:168-218) over
+   DirectionalEmitter::sample_direction (src/emitters/directional.cpp:108-135) */
+template <typename F> VP_D DirSample<F> sample_emitter_direction(const SceneView<F> &sv, F sx, F &spec) {
+    DirSample<F> ds;
+    ds.d = mk3<F>(0, 0, 0); ds.dist = 0; ds.pdf = 0; ds.delta = false;
+    spec = 0;
+    int n = sv.g->n_emitters;
+    if (n == 0) return ds;
+    int index = 0;
+    F emitter_pdf = 1;
+    if (n > 1) {
+        emitter_pdf = (F) 1 / (F) n;
+        uint32_t idx = (uint32_t) (sx * (F) n);
+        index = (int) (idx < (uint32_t) (n - 1) ? idx : (uint32_t) (n - 1));
+    }
+    const DEmitter<F> &e = sv.emitters[index];
+    ds.d = -ld3(e.dir);
+    ds.dist = (F) 2 * sv.g->bs_radius;
+    ds.pdf = 1;
+    ds.delta = true;
+    spec = e.irradiance;
+    if (n > 1) { ds.pdf *= emitter_pdf; spec *= rcp_(emitter_pdf); }
+    return ds;
+}
+
+/* ------------------------------------------------------------------ sensors */
+template <typename F> VP_D F rect_area(const DShape<F> &sh) { return norm(cross(ld3(sh.fs), ld3(sh.ft))); }
+
+/* Sensor::sample_ray_differential (src/sensors/distant.cpp:299-386, mdistant.cpp:216-266,
+   radiancemeter.cpp:106-139, mradiancemeter.cpp:134-159); returns the ray weight */
+template <typename F> VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> &ray) {
+    const DScene<F> &g = *sv.g;
+    const DSensor<F> &sn = g.sensor;
+    ray.mint = K<F>::RayEpsilon;
+    ray.maxt = inf_<F>();
+    F weight = 0;
+    V3<F> bs_c = ld3(g.bs_center);
+    F bs_r = g.bs_radius;
+    if (sn.type == 0) {
+        V3<F> v0 = mk3<F>(0, 0, 1);
+        if (sn.direction_type == 2)
+            v0 = square_to_uniform_hemisphere(fx, fy);
+        else if (sn.direction_type == 1) {
+            F s, c;
+            sincos_(K<F>::Pi * fx, s, c);
+            v0.x = c; v0.z = s;
+        }
+        ray.d = sn.flip_directions ? xf_vector(sn.to_world, v0) : xf_vector(sn.to_world, -v0);
+        V3<F> ray_target = ld3(sn.target_point);
+        if (sn.target_type == 1) {
+            weight = 1;
+        } else if (sn.target_type == 2) {
+            const DShape<F> &sh = sv.shapes[sn.target_shape]; /* rectangle.cpp:111-125 */
+            ray_target = xf_point_affine(sh.to_world, mk3<F>(ax * (F) 2 - (F) 1, ay * (F) 2 - (F) 1, (F) 0));
+            weight = (F) 1 / sh.inv_surface_area / rect_area(sh);
+        } else {
+            F ox, oy;
+            square_to_uniform_disk_concentric(ax, ay, ox, oy);
+            V3<F> perp = xf_vector(sn.to_world, mk3<F>(ox, oy, (F) 0));
+            ray_target = bs_c + perp * bs_r;
+            weight = (F) 1;
+            weight /= dot(-ray.d, mk3<F>(0, 0, 1));
+        }
+        if (sn.target_type == 0)
+            ray.o = ray_target - ray.d * bs_r;
+        else
+            ray.o = ray_target - ray.d * (F) 2 * bs_r;
+    } else if (sn.type == 1) {
+        int idx = (int) (fx * (F) sn.n_transforms);
+        const F *trafo = g.sensor_xf + 16 * (size_t) idx;
+        ray.d = xf_vector(trafo, mk3<F>(0, 0, 1));
+        if (sn.target_type == 1) {
+            ray.o = ld3(sn.target_point) - (F) 2 * ray.d * bs_r;
+            weight = 1;
+        } else if (sn.target_type == 2) {
+            const DShape<F> &sh = sv.shapes[sn.target_shape];
+            V3<F> p = xf_point_affine(sh.to_world, mk3<F>(ax * (F) 2 - (F) 1, ay * (F) 2 - (F) 1, (F) 0));
+            ray.o = p - (F) 2 * ray.d * bs_r;
+            weight = (F) 1 / (sh.inv_surface_area * rect_area(sh));
+        } else {
+            F ox, oy;
+            square_to_uniform_disk_concentric(ax, ay, ox, oy);
+            V3<F> perp = xf_vector(trafo, mk3<F>(ox, oy, (F) 0));
+            ray.o = bs_c + perp * bs_r - ray.d * bs_r;
+            weight = 1;
+        }
+    } else if (sn.type == 2) {
+        ray.o = xf_point_affine(sn.to_world, mk3<F>(0, 0, 0));
+        ray.d = xf_vector(sn.to_world, mk3<F>(0, 0, 1));
+        weight = 1;
+    } else {
+        int idx = (int) (fx * (F) sn.n_transforms);
+        const F *trafo = g.sensor_xf + 16 * (size_t) idx;
+        ray.o = xf_point_affine(trafo, mk3<F>(0, 0, 0));
+        ray.d = xf_vector(trafo, mk3<F>(0, 0, 1));
+        weight = 1;
+    }
+    ray.update();
+    return weight;
+}
+
+} // namespace vp

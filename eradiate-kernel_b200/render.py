@@ -1,0 +1,120 @@
+"""Integrator-level entry points: the Python counterpart of `scene.integrator().render(scene, sensor)`
+(src/librender/python/integrator_v.cpp:124-153) on top of the C-ABI in include/b2vp.h."""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class RenderResult:
+    def __init__(self, film, totals, state=None, counters=None, radiance=None):
+        self.film = film            # (H, W, 5) XYZAW sums, like the hdrfilm storage ImageBlock
+        self.totals = totals        # abi.Counters
+        self.state, self.counters, self.radiance = state, counters, radiance
+
+    def bitmap(self):
+        """HDRFilm::bitmap for pixel_format=luminance: Y / W (src/films/hdrfilm.cpp:251-321)."""
+        w = self.film[..., 4]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return np.where(w > 0, self.film[..., 1] / w, 0).astype(self.film.dtype)
+
+    @property
+    def segments(self):
+        return self.totals.n_medium_steps + self.totals.n_intersect
+
+
+class DeviceScene:
+    """A scene resident on one CUDA device (b2vp_scene_create .. b2vp_scene_destroy)."""
+
+    def __init__(self, scene, device=0):
+        self.scene = scene
+        self.device = device
+        self._h = C.c_void_p()
+        abi.check(abi.lib().b2vp_scene_create(C.byref(scene.desc), device, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            abi.lib().b2vp_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def stream_count(self, seed_mode):
+        n, per = C.c_uint64(), C.c_uint32()
+        abi.check(abi.lib().b2vp_stream_count(self._h, seed_mode, C.byref(n), C.byref(per)))
+        return n.value, per.value
+
+    def update(self, medium=-1, medium_scale=0.0, bsdf=-1, bsdf_p=(0, 0, 0, 0), emitter=-1, emitter_irradiance=0.0,
+               volume=-1, volume_value=0.0):
+        p = abi.ParamPatch()
+        p.abi_version, p.struct_size = abi.ABI_VERSION, C.sizeof(abi.ParamPatch)
+        p.medium, p.medium_scale, p.bsdf, p.emitter, p.emitter_irradiance = medium, medium_scale, bsdf, emitter, emitter_irradiance
+        p.bsdf_p[:] = list(bsdf_p)
+        p.volume, p.volume_value = volume, volume_value
+        abi.check(abi.lib().b2vp_scene_update(self._h, C.byref(p)))
+
+    def cancel(self):
+        abi.lib().b2vp_cancel(self._h)
+
+    def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None,
+               want_paths=False, film=None, stream=None):
+        """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
+        `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film)."""
+        prec = self.scene.precision if precision is None else precision
+        dtype = np.float32 if prec == abi.PREC_F32 else np.float64
+        w, h = self.scene.film_size
+        a = abi.RenderArgs()
+        a.abi_version, a.struct_size = abi.ABI_VERSION, C.sizeof(abi.RenderArgs)
+        a.precision, a.seed_mode, a.device = prec, seed_mode, self.device
+        a.cuda_stream = stream
+        a.first_stream, a.n_streams = first_stream, n_streams
+        keep = []
+        if seed_mode == abi.SEED_EXPLICIT:
+            st, inc, pix, per = explicit
+            st = np.ascontiguousarray(st, dtype=np.uint64); inc = np.ascontiguousarray(inc, dtype=np.uint64)
+            pix = np.ascontiguousarray(pix, dtype=np.uint32)
+            keep += [st, inc, pix]
+            a.explicit_state = st.ctypes.data_as(C.POINTER(C.c_uint64))
+            a.explicit_inc = inc.ctypes.data_as(C.POINTER(C.c_uint64))
+            a.explicit_pixel = pix.ctypes.data_as(C.POINTER(C.c_uint32))
+            a.explicit_samples_per_stream = per
+            a.n_streams = len(st)
+            count, sps = len(st), per
+        else:
+            total, sps = self.stream_count(seed_mode)
+            count = n_streams if n_streams else total - first_stream
+        if film is None:
+            film = np.zeros((h, w, 5), dtype=dtype)
+            a.clear_film = 1
+        else:
+            assert film.dtype == dtype and film.shape == (h, w, 5) and film.flags.c_contiguous
+            a.clear_film = 0
+        tot = abi.Counters()
+        a.totals = C.pointer(tot)
+        state = counters = radiance = None
+        if want_paths:
+            state = np.zeros(count, dtype=np.uint64)
+            counters = np.zeros((count, 6), dtype=np.uint32)
+            radiance = np.zeros((count, sps), dtype=dtype)
+            a.out_state = state.ctypes.data_as(C.POINTER(C.c_uint64))
+            a.out_counters = C.cast(counters.ctypes.data, C.POINTER(abi.PathCounters))
+            a.out_radiance = radiance.ctypes.data
+        abi.check(abi.lib().b2vp_render(self._h, C.byref(a), film.ctypes.data))
+        return RenderResult(film, tot, state, counters, radiance)
+
+
+def render(scene, device=0, **kw):
+    """One-shot `integrator.render(scene, sensor)`."""
+    with DeviceScene(scene, device) as ds:
+        return ds.render(**kw)

@@ -1,0 +1,583 @@
+"""Host-side scene loading for the B200 volpath: Mitsuba-style scene dictionaries
+(the shape `mitsuba.core.xml.load_dict` takes, src/libcore/python/xml_v.cpp:100-240)
+-> the flat B2vpSceneDesc of include/b2vp.h.
+
+Each plugin parser below reads the same properties, with the same defaults, as the
+reference plugin of that name (file:line cited per parser) and evaluates derived
+quantities in the variant's scalar type (float32 for scalar_mono, float64 for
+scalar_mono_double).  Content outside SURVEY.md section 8 raises, like an unknown
+plugin name does in the reference.
+"""
+import ctypes as C
+import struct
+
+import numpy as np
+
+from . import abi
+from .transform import Transform, coordinate_system
+
+VARIANTS = {"scalar_mono": (np.float32, abi.PREC_F32), "scalar_mono_double": (np.float64, abi.PREC_F64)}
+
+
+def read_vol(path):
+    """.vol reader (src/textures/volume_data.h:42-102): returns (data[z,y,x,c] float32, bbox 6 floats)."""
+    with open(path, "rb") as f:
+        raw = f.read()
+    if raw[:3] != b"VOL" or raw[3] != 3:
+        raise RuntimeError("%s: not a version-3 VOL file" % path)
+    typ, nx, ny, nz, ch = struct.unpack_from("<5i", raw, 4)
+    if typ != 1:
+        raise RuntimeError("%s: only float32 volumes are supported (type %d)" % (path, typ))
+    if nx * ny * nz < 8:
+        raise RuntimeError("%s: invalid grid dimensions: %d x %d x %d < 8 (must have at least one value at each corner)" %
+                           (path, nx, ny, nz))
+    bbox = struct.unpack_from("<6f", raw, 24)
+    data = np.frombuffer(raw, dtype="<f4", count=nx * ny * nz * ch, offset=48).reshape(nz, ny, nx, ch).copy()
+    return data, bbox
+
+
+def write_vol(path, data, bbox=(0, 0, 0, 1, 1, 1)):
+    """Writes data[z,y,x(,c)] as a version-3 float32 VOL file."""
+    data = np.asarray(data, dtype="<f4")
+    if data.ndim == 3:
+        data = data[..., None]
+    nz, ny, nx, ch = data.shape
+    with open(path, "wb") as f:
+        f.write(b"VOL\x03")
+        f.write(struct.pack("<5i", 1, nx, ny, nz, ch))
+        f.write(struct.pack("<6f", *bbox))
+        f.write(data.tobytes())
+
+
+class _Builder:
+    def __init__(self, variant):
+        if variant not in VARIANTS:
+            raise RuntimeError("variant %r is not supported by the B200 volpath (mono only)" % (variant,))
+        self.variant = variant
+        self.dtype, self.precision = VARIANTS[variant]
+        self.dt = np.dtype(self.dtype).type
+        self.shapes, self.bsdfs, self.media, self.volumes, self.phases, self.emitters = [], [], [], [], [], []
+        self.volume_arrays = []
+        self.vpos, self.vnrm, self.vuv, self.faces = [], [], [], []
+        self.n_vertices = 0
+        self.n_faces = 0
+        self.ids = {}        # id -> ("medium"|"bsdf"|"shape", index)
+        self.bbox_min = np.full(3, np.inf, dtype=self.dtype)
+        self.bbox_max = np.full(3, -np.inf, dtype=self.dtype)
+        self.sensor = None
+        self.integrator = None
+        self.keep = []
+
+    # ------------------------------------------------------------ helpers
+    def xf(self, v):
+        if v is None:
+            return Transform(dtype=self.dtype)
+        if isinstance(v, Transform):
+            return v.astype(self.dtype)
+        return Transform(np.asarray(v, dtype=np.float64).reshape(4, 4), dtype=self.dtype)
+
+    def mat(self, t):
+        m = abi.Mat4()
+        m.m[:] = t.colmajor()
+        return m
+
+    def expand(self, p):
+        p = np.asarray(p, dtype=self.dtype)
+        self.bbox_min = np.minimum(self.bbox_min, p)
+        self.bbox_max = np.maximum(self.bbox_max, p)
+
+    def resolve(self, node, kind, parser):
+        if isinstance(node, dict) and node.get("type") == "ref":
+            k, idx = self.ids[node["id"]]
+            if k != kind:
+                raise RuntimeError("reference %r is a %s, expected a %s" % (node["id"], k, kind))
+            return idx
+        return parser(node)
+
+    # ------------------------------------------------------------ plugins
+    def volume(self, node, default):
+        """props.volume(): a float becomes a constvolume (src/libcore/properties.cpp); gridvolume =
+        src/textures/grid3d.cpp:43-160; constvolume = src/textures/constant3d.cpp:13-55."""
+        v = abi.Volume()
+        if node is None:
+            node = default
+        if isinstance(node, (int, float)):
+            node = {"type": "constvolume", "value": float(node)}
+        t = node["type"]
+        to_world = self.xf(node.get("to_world"))
+        w2l = to_world.inverse()
+        arr = None
+        if t == "constvolume":
+            v.type = abi.VOLUME_CONST
+            v.value = float(self.dt(node.get("value", 1.0)))
+            v.max_value = v.value
+            v.channels = 1
+        elif t == "gridvolume":
+            v.type = abi.VOLUME_GRID
+            if "filename" in node:
+                data, file_bbox = read_vol(node["filename"])
+            else:  # in-memory grid: data[z, y, x(, c)]
+                data = np.asarray(node["data"], dtype=np.float32)
+                if data.ndim == 3:
+                    data = data[..., None]
+                file_bbox = node.get("bbox", (0, 0, 0, 1, 1, 1))
+            nz, ny, nx, ch = data.shape
+            if ch not in (1, 3):
+                raise RuntimeError("Unsupported channel count: %d (expected 1 or 3)" % ch)
+            if node.get("raw", False):
+                raise RuntimeError("gridvolume raw=true is not supported in mono variants")
+            ft = node.get("filter_type", "trilinear")
+            wm = node.get("wrap_mode", "clamp")
+            try:
+                v.filter = {"nearest": abi.FILTER_NEAREST, "trilinear": abi.FILTER_TRILINEAR}[ft]
+                v.wrap = {"repeat": abi.WRAP_REPEAT, "mirror": abi.WRAP_MIRROR, "clamp": abi.WRAP_CLAMP}[wm]
+            except KeyError:
+                raise RuntimeError("Invalid filter type / wrap mode %r / %r" % (ft, wm))
+            v.channels = ch
+            v.res[:] = [nx, ny, nz]
+            arr = np.ascontiguousarray(data, dtype=np.float32)
+            v.max_value = float(self.dt(node["max_value"])) if "max_value" in node else float(arr.max())
+            if node.get("use_grid_bbox", False):  # grid3d.cpp:152-155
+                mn = np.asarray(file_bbox[:3], dtype=self.dtype)
+                mx = np.asarray(file_bbox[3:], dtype=self.dtype)
+                meta = (Transform.scale(self.dt(1) / (mx - mn), self.dtype) @ Transform.translate(-mn, self.dtype))
+                w2l = meta @ w2l
+            v.data = arr.ctypes.data_as(C.POINTER(C.c_float))
+        else:
+            raise RuntimeError("volume plugin %r is not supported by the B200 volpath" % t)
+        v.world_to_local = self.mat(w2l)
+        l2w = w2l.inverse()  # texture.h:265-272
+        a, b = l2w.point([0, 0, 0]), l2w.point([1, 1, 1])
+        v.bbox_min[:] = [float(x) for x in np.minimum(a, b)]
+        v.bbox_max[:] = [float(x) for x in np.maximum(a, b)]
+        self.volumes.append(v)
+        self.volume_arrays.append(arr)
+        return len(self.volumes) - 1
+
+    def phase(self, node):
+        """src/phase/{isotropic,rayleigh,hg}.cpp"""
+        p = abi.Phase()
+        t = "isotropic" if node is None else node["type"]
+        if t == "isotropic":
+            p.type = abi.PHASE_ISOTROPIC
+        elif t == "rayleigh":
+            p.type = abi.PHASE_RAYLEIGH
+        elif t == "hg":
+            p.type = abi.PHASE_HG
+            g = self.dt(node.get("g", 0.8))  # hg.cpp:41
+            if not (-1 < g < 1):
+                raise RuntimeError("The asymmetry parameter must lie in the interval (-1, 1)!")
+            p.g = float(g)
+        else:
+            raise RuntimeError("phase function %r is not supported by the B200 volpath" % t)
+        self.phases.append(p)
+        return len(self.phases) - 1
+
+    def medium(self, node):
+        """src/media/homogeneous.cpp:21-54, heterogeneous.cpp:21-54, src/librender/medium.cpp:12-30"""
+        m = abi.Medium()
+        t = node["type"]
+        if t == "homogeneous":
+            m.type = abi.MEDIUM_HOMOGENEOUS
+        elif t == "heterogeneous":
+            m.type = abi.MEDIUM_HETEROGENEOUS
+        else:
+            raise RuntimeError("medium plugin %r is not supported by the B200 volpath" % t)
+        m.albedo = self.volume(node.get("albedo"), 0.75)
+        m.sigma_t = self.volume(node.get("sigma_t"), 1.0)
+        m.scale = float(self.dt(node.get("scale", 1.0)))
+        m.has_spectral_extinction = int(bool(node.get("has_spectral_extinction", True)))
+        m.sample_emitters = int(bool(node.get("sample_emitters", True)))
+        m.phase = self.phase(node.get("phase"))
+        if m.type == abi.MEDIUM_HETEROGENEOUS and self.volumes[m.sigma_t].type != abi.VOLUME_GRID:
+            raise RuntimeError("heterogeneous medium needs a gridvolume sigma_t (ConstVolume::max is not implemented)")
+        self.media.append(m)
+        idx = len(self.media) - 1
+        if "id" in node:
+            self.ids[node["id"]] = ("medium", idx)
+        return idx
+
+    def bsdf(self, node):
+        """src/bsdfs/diffuse.cpp:70-76, rpv.cpp:66-83, null.cpp:30-39"""
+        b = abi.Bsdf()
+        if node is None:
+            node = {"type": "diffuse"}  # shape.cpp: default BSDF
+        t = node["type"]
+
+        def scalar(key, default):
+            val = node.get(key, default)
+            if isinstance(val, dict):
+                if val.get("type") != "uniform":
+                    raise RuntimeError("only uniform (constant) textures are supported for %r" % key)
+                val = val.get("value", default)
+            return float(self.dt(val))
+        if t == "diffuse":
+            b.type = abi.BSDF_DIFFUSE
+            b.p[0] = scalar("reflectance", 0.5)
+        elif t == "null":
+            b.type = abi.BSDF_NULL
+        elif t == "rpv":
+            b.type = abi.BSDF_RPV
+            b.p[0] = scalar("rho_0", 0.1)
+            b.p[1] = scalar("k", 0.1)
+            b.p[2] = scalar("g", 0.0)
+            b.p[3] = scalar("rho_c", b.p[0]) if "rho_c" in node else b.p[0]  # rpv.cpp:72-80
+        else:
+            raise RuntimeError("BSDF plugin %r is not supported by the B200 volpath" % t)
+        self.bsdfs.append(b)
+        idx = len(self.bsdfs) - 1
+        if "id" in node:
+            self.ids[node["id"]] = ("bsdf", idx)
+        return idx
+
+    def add_mesh(self, s, positions, faces, normals=None, texcoords=None):
+        positions = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        faces = np.ascontiguousarray(faces, dtype=np.uint32).reshape(-1, 3)
+        s.type = abi.SHAPE_MESH
+        s.vertex_offset, s.vertex_count = self.n_vertices, len(positions)
+        s.face_offset, s.face_count = self.n_faces, len(faces)
+        s.has_vertex_normals = int(normals is not None)
+        s.has_vertex_texcoords = int(texcoords is not None)
+        self.vpos.append(positions)
+        self.vnrm.append(np.zeros_like(positions) if normals is None else
+                         np.ascontiguousarray(normals, dtype=np.float32).reshape(-1, 3))
+        self.vuv.append(np.zeros((len(positions), 2), np.float32) if texcoords is None else
+                        np.ascontiguousarray(texcoords, dtype=np.float32).reshape(-1, 2))
+        self.faces.append(faces)
+        self.n_vertices += len(positions)
+        self.n_faces += len(faces)
+        if len(positions):
+            self.expand(positions.min(axis=0))
+            self.expand(positions.max(axis=0))
+
+    def shape(self, node):
+        s = abi.Shape()
+        t = node["type"]
+        dt = self.dt
+        to_world = self.xf(node.get("to_world"))
+        s.bsdf = self.resolve(node.get("bsdf"), "bsdf", self.bsdf)
+        s.interior_medium = self.resolve(node["interior"], "medium", self.medium) if "interior" in node else -1
+        s.exterior_medium = self.resolve(node["exterior"], "medium", self.medium) if "exterior" in node else -1
+        if "emitter" in node or "sensor" in node:
+            raise RuntimeError("area emitters / shape sensors are not supported by the B200 volpath")
+        if t == "rectangle":  # src/shapes/rectangle.cpp:75-104
+            s.type = abi.SHAPE_RECTANGLE
+            if node.get("flip_normals", False):
+                to_world = to_world @ Transform.scale([1, 1, -1], self.dtype)
+            dp_du, dp_dv = to_world.vector([2, 0, 0]), to_world.vector([0, 2, 0])
+            n = to_world.normal([0, 0, 1])
+            n = (n / np.sqrt(np.dot(n, n))).astype(self.dtype)
+            s.frame_s[:] = [float(x) for x in dp_du]
+            s.frame_t[:] = [float(x) for x in dp_dv]
+            s.frame_n[:] = [float(x) for x in n]
+            area = np.sqrt(np.sum(np.cross(dp_du, dp_dv).astype(self.dtype) ** 2, dtype=self.dtype))
+            s.inv_surface_area = float(dt(1) / dt(area))
+            for c in ([-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]):
+                self.expand(to_world.point_affine(c))
+        elif t == "sphere":  # src/shapes/sphere.cpp:95-160
+            s.type = abi.SHAPE_SPHERE
+            to_world = to_world @ Transform.translate(node.get("center", [0, 0, 0]), self.dtype)
+            to_world = to_world @ Transform.scale(node.get("radius", 1.0), self.dtype)
+            m = to_world.matrix.astype(np.float64)
+            # polar decomposition of the upper 3x3 (transform_decompose): S symmetric, Q rotation
+            u, sv, vt = np.linalg.svd(m[:3, :3])
+            q = u @ vt
+            smat = vt.T @ np.diag(sv) @ vt
+            if np.linalg.det(q) < 0:
+                q, smat = -q, -smat
+            radius = dt(smat[0, 0])
+            flip = bool(node.get("flip_normals", False))
+            if radius <= 0:
+                radius, flip = dt(abs(radius)), not flip
+            center = m[:3, 3].astype(self.dtype)
+            m2 = np.eye(4)
+            m2[:3, :3] = q * float(radius)
+            m2[:3, 3] = center
+            to_world = Transform(m2, dtype=self.dtype)
+            s.center[:] = [float(x) for x in center]
+            s.radius = float(radius)
+            s.flip_normals = int(flip)
+            s.inv_surface_area = float(dt(1) / (dt(4) * dt(np.pi) * radius * radius))
+            self.expand(center - radius)
+            self.expand(center + radius)
+        elif t == "cube":  # src/shapes/cube.cpp:54-116
+            verts = np.array([[1, -1, -1], [1, -1, 1], [-1, -1, 1], [-1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, 1, 1],
+                              [1, 1, 1], [1, -1, -1], [1, 1, -1], [1, 1, 1], [1, -1, 1], [1, -1, 1], [1, 1, 1],
+                              [-1, 1, 1], [-1, -1, 1], [-1, -1, 1], [-1, 1, 1], [-1, 1, -1], [-1, -1, -1], [1, 1, -1],
+                              [1, -1, -1], [-1, -1, -1], [-1, 1, -1]], dtype=np.float32)
+            nrms = np.repeat(np.array([[0, -1, 0], [0, 1, 0], [1, 0, 0], [0, 0, 1], [-1, 0, 0], [0, 0, -1]],
+                                      dtype=np.float32), 4, axis=0)
+            uvs = np.tile(np.array([[0, 1], [1, 1], [1, 0], [0, 0]], dtype=np.float32), (6, 1))
+            tris = np.array([[0, 1, 2], [3, 0, 2], [4, 5, 6], [7, 4, 6], [8, 9, 10], [11, 8, 10], [12, 13, 14],
+                             [15, 12, 14], [16, 17, 18], [19, 16, 18], [20, 21, 22], [23, 20, 22]], dtype=np.uint32)
+            # Mesh buffers are always float32 (mesh.h:22-28): transform in float32
+            tw = to_world.astype(np.float32)
+            p = np.stack([tw.point_affine(v) for v in verts])
+            n = np.stack([tw.normal(v) for v in nrms])
+            n = (n / np.sqrt(np.sum(n * n, axis=1, dtype=np.float32))[:, None]).astype(np.float32)
+            if node.get("flip_normals", False):
+                n = -n
+            self.add_mesh(s, p, tris, n, uvs)
+        elif t == "mesh":  # in-memory triangle mesh (what obj/ply/serialized loaders produce, src/librender/mesh.cpp)
+            tw = to_world.astype(np.float32)
+            pos = np.asarray(node["vertex_positions"], dtype=np.float32).reshape(-1, 3)
+            pos = (pos @ tw.matrix[:3, :3].T + tw.matrix[:3, 3]).astype(np.float32)
+            nrm = node.get("vertex_normals")
+            if nrm is not None:
+                nrm = np.asarray(nrm, dtype=np.float32).reshape(-1, 3) @ tw.inverse_transpose[:3, :3].T
+                nrm = (nrm / np.sqrt(np.sum(nrm * nrm, axis=1))[:, None]).astype(np.float32)
+            self.add_mesh(s, pos, node["faces"], nrm, node.get("vertex_texcoords"))
+        else:
+            raise RuntimeError("shape plugin %r is not supported by the B200 volpath" % t)
+        s.to_world = self.mat(to_world)
+        s.to_object = self.mat(to_world.inverse())
+        self.shapes.append(s)
+        idx = len(self.shapes) - 1
+        if "id" in node:
+            self.ids[node["id"]] = ("shape", idx)
+        return idx
+
+    def emitter(self, node):
+        """src/emitters/directional.cpp:45-73"""
+        if node["type"] != "directional":
+            raise RuntimeError("emitter plugin %r is not supported by the B200 volpath" % node["type"])
+        e = abi.Emitter()
+        e.type = abi.EMITTER_DIRECTIONAL
+        if "direction" in node:
+            if "to_world" in node:
+                raise RuntimeError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!")
+            d = np.asarray(node["direction"], dtype=self.dtype)
+            d = (d / np.sqrt(np.dot(d, d))).astype(self.dtype)
+            up, _ = coordinate_system(d, self.dtype)
+            tw = Transform.look_at([0, 0, 0], d, up, self.dtype)
+        else:
+            tw = self.xf(node.get("to_world"))
+        e.direction[:] = [float(x) for x in tw.vector([0, 0, 1])]
+        irr = node.get("irradiance", 1.0)
+        if isinstance(irr, dict):
+            irr = irr.get("value", 1.0)
+        e.irradiance = float(self.dt(irr))
+        self.emitters.append(e)
+
+    def parse_sensor(self, node):
+        """src/sensors/{distant,mdistant,radiancemeter,mradiancemeter}.cpp ctors, src/librender/sensor.cpp:15-55,
+        src/librender/film.cpp, src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp"""
+        sn = abi.Sensor()
+        t = node["type"]
+        dtp, dt = self.dtype, self.dt
+        film = node.get("film", {"type": "hdrfilm"})
+        if film.get("type", "hdrfilm") != "hdrfilm":
+            raise RuntimeError("film plugin %r is not supported by the B200 volpath" % film["type"])
+        rf = film.get("rfilter", {"type": "box"})
+        if rf.get("type", "box") != "box":
+            raise RuntimeError("only the box reconstruction filter is supported by the B200 volpath")
+        w, h = int(film.get("width", 768)), int(film.get("height", 576))
+        sn.film_size[:] = [w, h]
+        sn.crop_offset[:] = [int(film.get("crop_offset_x", 0)), int(film.get("crop_offset_y", 0))]
+        sn.crop_size[:] = [int(film.get("crop_width", w)), int(film.get("crop_height", h))]
+        sampler = node.get("sampler", {"type": "independent", "sample_count": 4})
+        if sampler.get("type", "independent") != "independent":
+            raise RuntimeError("sampler plugin %r is not supported by the B200 volpath" % sampler["type"])
+        sn.sample_count = int(sampler.get("sample_count", 4))
+        sn.sampler_seed = int(sampler.get("seed", 0))
+        sn.shutter_open = float(node.get("shutter_open", 0.0))
+        sn.shutter_open_time = float(node.get("shutter_close", 0.0)) - sn.shutter_open
+        if sn.shutter_open_time < 0:
+            raise RuntimeError("Shutter opening time must be less than or equal to the shutter closing time!")
+        sn.medium = self.resolve(node["medium"], "medium", self.medium) if "medium" in node else -1
+        sn.target_shape = sn.origin_shape = -1
+        to_world = self.xf(node.get("to_world"))
+        xfs = None
+
+        def target(key):
+            tgt = node.get(key)
+            if tgt is None:
+                sn.target_type = abi.TARGET_NONE
+            elif isinstance(tgt, dict):
+                sn.target_type = abi.TARGET_SHAPE
+                sn.target_shape = self.resolve(tgt, "shape", self.shape)
+                if self.shapes[sn.target_shape].type != abi.SHAPE_RECTANGLE:
+                    raise RuntimeError("sensor target shape must be a rectangle in the B200 volpath")
+            else:
+                sn.target_type = abi.TARGET_POINT
+                sn.target_point[:] = [float(dt(x)) for x in tgt]
+
+        if t == "distant":  # distant.cpp:225-290
+            sn.type = abi.SENSOR_DISTANT
+            sn.flip_directions = int(bool(node.get("flip_directions", False)))
+            sn.direction_type = (abi.DIR_SINGLE if (w, h) == (1, 1) else
+                                 abi.DIR_SAMPLE_WIDTH if h == 1 else abi.DIR_SAMPLE_ALL)
+            if "direction" in node:
+                if "to_world" in node:
+                    raise RuntimeError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!")
+                d = np.asarray(node["direction"], dtype=dtp)
+                d = (d / np.sqrt(np.dot(d, d))).astype(dtp)
+                if "orientation" in node:
+                    up = np.cross(d, np.asarray(node["orientation"], dtype=dtp)).astype(dtp)
+                    up = (up / np.sqrt(np.dot(up, up))).astype(dtp)
+                else:
+                    _, up = coordinate_system(d, dtp)
+                to_world = Transform.look_at([0, 0, 0], d, up, dtp)
+            target("ray_target")
+            if "ray_origin" in node:
+                raise RuntimeError("distant sensor with a ray_origin shape is not supported by the B200 volpath")
+            sn.origin_type = abi.ORIGIN_BSPHERE
+            sn.needs_aperture_sample = 1
+        elif t == "mdistant":  # mdistant.cpp:146-207
+            sn.type = abi.SENSOR_MDISTANT
+            dirs = np.asarray(node["directions"], dtype=np.float32).reshape(-1, 3)  # std::stof
+            if (w, h) != (len(dirs), 1):
+                raise RuntimeError("Film size must be [sensor_count, 1]. Expected [%d, 1], got [%d, %d]" % (len(dirs), w, h))
+            xfs = []
+            for d in dirs.astype(dtp):
+                _, up = coordinate_system(d, dtp)
+                xfs.append(Transform.look_at([0, 0, 0], d, up, dtp))
+            target("target")
+            sn.needs_aperture_sample = 1
+        elif t == "radiancemeter":  # radiancemeter.cpp:61-104
+            sn.type = abi.SENSOR_RADIANCEMETER
+            if "to_world" not in node and ("direction" in node) != ("origin" in node):
+                raise RuntimeError("If the sensor is specified through origin and direction both values must be set!")
+            if "to_world" not in node and "direction" in node:
+                o = np.asarray(node["origin"], dtype=dtp)
+                d = np.asarray(node["direction"], dtype=dtp)
+                up, _ = coordinate_system(d, dtp)
+                to_world = Transform.look_at(o, o + d, up, dtp)
+            if (w, h) != (1, 1):
+                raise RuntimeError("This sensor only supports films of size 1x1 Pixels!")
+            sn.needs_aperture_sample = 0
+        elif t == "mradiancemeter":  # mradiancemeter.cpp:75-131
+            sn.type = abi.SENSOR_MRADIANCEMETER
+            if "to_world" in node:
+                raise RuntimeError("This sensor is specified through a set of origin and direction values and "
+                                   "cannot use the to_world transform.")
+            origins = np.asarray(node["origins"], dtype=np.float32).reshape(-1, 3).astype(dtp)
+            dirs = np.asarray(node["directions"], dtype=np.float32).reshape(-1, 3).astype(dtp)
+            if origins.shape != dirs.shape:
+                raise RuntimeError("Invalid specification! Number of parameters for origins and directions are not equal.")
+            if (w, h) != (len(dirs), 1):
+                raise RuntimeError("Film size must be [sensor_count, 1]. Expected [%d, 1], got [%d, %d]" % (len(dirs), w, h))
+            xfs = []
+            for o, d in zip(origins, dirs):
+                up, _ = coordinate_system(d, dtp)
+                xfs.append(Transform.look_at(o, o + d, up, dtp))
+            sn.needs_aperture_sample = 0
+        else:
+            raise RuntimeError("sensor plugin %r is not supported by the B200 volpath" % t)
+        sn.to_world = self.mat(to_world)
+        if xfs is not None:
+            arr = np.ascontiguousarray(np.stack([x.matrix.T.reshape(-1) for x in xfs]), dtype=np.float64)
+            self.keep.append(arr)
+            sn.n_transforms = len(xfs)
+            sn.transforms = arr.ctypes.data_as(C.POINTER(C.c_double))
+        self.sensor = sn
+
+    def parse_integrator(self, node):
+        """src/librender/integrator.cpp:23-39,302-315"""
+        if node.get("type", "volpath") != "volpath":
+            raise RuntimeError("integrator plugin %r is not supported by the B200 volpath" % node["type"])
+        it = abi.Integrator()
+        it.max_depth = int(node.get("max_depth", -1))
+        if it.max_depth < 0 and it.max_depth != -1:
+            raise RuntimeError("\"max_depth\" must be set to -1 (infinite) or a value >= 0")
+        it.rr_depth = int(node.get("rr_depth", 5))
+        if it.rr_depth <= 0:
+            raise RuntimeError("\"rr_depth\" must be set to a value greater than zero!")
+        it.hide_emitters = int(bool(node.get("hide_emitters", False)))
+        it.block_size = int(node.get("block_size", 0))
+        it.samples_per_pass = int(node.get("samples_per_pass", 0xffffffff)) & 0xffffffff
+        it.arg_order_ltr = int(node.get("arg_order_ltr", 0))
+        self.integrator = it
+
+
+class Scene:
+    """A loaded scene: owns the B2vpSceneDesc and every array it points to."""
+
+    def __init__(self, desc, variant, precision, keep):
+        self.desc, self.variant, self.precision, self._keep = desc, variant, precision, keep
+        self.film_size = (desc.sensor.crop_size[0], desc.sensor.crop_size[1])
+
+
+def load_dict(d, variant="scalar_mono"):
+    """Mirror of mitsuba.core.xml.load_dict for the scoped plugin set."""
+    if d.get("type", "scene") != "scene":
+        raise RuntimeError("load_dict: the top-level dictionary must be a scene")
+    b = _Builder(variant)
+    sensor_node = integrator_node = None
+    emitters = []
+    shape_kinds = ("rectangle", "sphere", "cube", "mesh")
+    # children are visited in key order, as Properties::objects() does (std::map)
+    items = [(k, v) for k, v in sorted(d.items()) if isinstance(v, dict)]
+    # first pass: named media / bsdfs so that references resolve regardless of order
+    for k, v in items:
+        v = dict(v)
+        v.setdefault("id", k)
+        if v["type"] in ("homogeneous", "heterogeneous"):
+            b.medium(v)
+        elif v["type"] in ("diffuse", "rpv", "null"):
+            b.bsdf(v)
+    for k, v in items:
+        t = v["type"]
+        if t in shape_kinds:
+            v = dict(v)
+            v.setdefault("id", k)
+            b.shape(v)
+        elif t == "directional":
+            emitters.append(v)
+        elif t in ("distant", "mdistant", "radiancemeter", "mradiancemeter"):
+            if sensor_node is not None:
+                raise RuntimeError("the B200 volpath renders one sensor per scene")
+            sensor_node = v
+        elif t == "volpath":
+            integrator_node = v
+        elif t in ("homogeneous", "heterogeneous", "diffuse", "rpv", "null"):
+            pass
+        else:
+            raise RuntimeError("plugin %r is not supported by the B200 volpath" % t)
+    for e in emitters:
+        b.emitter(e)
+    if sensor_node is None:
+        raise RuntimeError("scene has no sensor")
+    b.parse_sensor(sensor_node)
+    b.parse_integrator(integrator_node or {"type": "volpath"})
+
+    desc = abi.SceneDesc()
+    desc.abi_version, desc.struct_size, desc.precision = abi.ABI_VERSION, C.sizeof(abi.SceneDesc), b.precision
+    keep = [b.keep, b.volume_arrays]
+
+    def arr(cls, items):
+        a = (cls * max(len(items), 1))(*items)
+        keep.append(a)
+        return a
+    desc.n_shapes, desc.shapes = len(b.shapes), arr(abi.Shape, b.shapes)
+    desc.n_bsdfs, desc.bsdfs = len(b.bsdfs), arr(abi.Bsdf, b.bsdfs)
+    desc.n_media, desc.media = len(b.media), arr(abi.Medium, b.media)
+    desc.n_volumes, desc.volumes = len(b.volumes), arr(abi.Volume, b.volumes)
+    desc.n_phases, desc.phases = len(b.phases), arr(abi.Phase, b.phases)
+    desc.n_emitters, desc.emitters = len(b.emitters), arr(abi.Emitter, b.emitters)
+    if b.n_vertices:
+        vpos, vnrm, vuv = np.concatenate(b.vpos), np.concatenate(b.vnrm), np.concatenate(b.vuv)
+        faces = np.concatenate(b.faces)
+        keep += [vpos, vnrm, vuv, faces]
+        desc.n_vertices, desc.n_faces = b.n_vertices, b.n_faces
+        desc.vertex_positions = vpos.ctypes.data_as(C.POINTER(C.c_float))
+        desc.vertex_normals = vnrm.ctypes.data_as(C.POINTER(C.c_float))
+        desc.vertex_texcoords = vuv.ctypes.data_as(C.POINTER(C.c_float))
+        desc.faces = faces.ctypes.data_as(C.POINTER(C.c_uint32))
+    dt = b.dt
+    if not np.all(np.isfinite(b.bbox_min)):
+        b.bbox_min[:] = 0
+        b.bbox_max[:] = 0
+    desc.bbox_min[:] = [float(x) for x in b.bbox_min]
+    desc.bbox_max[:] = [float(x) for x in b.bbox_max]
+    # BoundingBox::bounding_sphere (bbox.h:329-332) + the padding of distant.cpp:292-297 / directional.cpp:68-73
+    center = ((b.bbox_max + b.bbox_min) * dt(0.5)).astype(b.dtype)
+    diff = (center - b.bbox_max).astype(b.dtype)
+    radius = dt(np.sqrt(dt(diff[0] * diff[0] + diff[1] * diff[1]) + diff[2] * diff[2]))
+    ray_eps = dt(np.finfo(b.dtype).eps) / dt(2) * dt(1500)
+    radius = max(ray_eps, dt(radius * (dt(1) + ray_eps)))
+    desc.bsphere_center[:] = [float(x) for x in center]
+    desc.bsphere_radius = float(radius)
+    desc.sensor = b.sensor
+    desc.integrator = b.integrator
+    return Scene(desc, variant, b.precision, keep)

@@ -1,0 +1,110 @@
+"""TEST INFRASTRUCTURE: ctypes wrapper of the CPU oracle (oracle/volpath_oracle.cpp).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / reference arm may
+import this module; the product package never does."""
+import ctypes as C
+import os
+import subprocess
+import threading
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb2vp_oracle.so")
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-C", HERE, "-s"])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        L.b2vp_oracle_last_error.restype = C.c_char_p
+        L.b2vp_oracle_tea32.restype = C.c_uint32
+        L.b2vp_oracle_tea32.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+        L.b2vp_oracle_tea64.restype = C.c_uint64
+        L.b2vp_oracle_tea64.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+        L.b2vp_oracle_tea64_u64.restype = C.c_uint64
+        L.b2vp_oracle_tea64_u64.argtypes = [C.c_uint64, C.c_uint64]
+        L.b2vp_oracle_tea_float32.restype = C.c_float
+        L.b2vp_oracle_tea_float32.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+        L.b2vp_oracle_tea_float64.restype = C.c_double
+        L.b2vp_oracle_tea_float64.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+        L.b2vp_oracle_rpv_eval.restype = C.c_double
+        L.b2vp_oracle_rpv_eval.argtypes = [C.c_double] * 4 + [C.POINTER(C.c_double)] * 2
+        L.b2vp_oracle_pcg32.argtypes = [C.c_uint64, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.b2vp_oracle_pcg32.restype = None
+        L.b2vp_oracle_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, explicit=None, want_paths=False):
+    """Same contract as eradiate_kernel_b200.DeviceScene.render, computed by the CPU oracle.
+    `pkg` is the loaded product package (for its ctypes struct definitions only)."""
+    abi = pkg.abi
+    prec = scene.precision if precision is None else precision
+    dtype = np.float32 if prec == abi.PREC_F32 else np.float64
+    w, h = scene.film_size
+    a = abi.RenderArgs()
+    a.abi_version, a.struct_size = abi.ABI_VERSION, C.sizeof(abi.RenderArgs)
+    a.precision, a.seed_mode = prec, seed_mode
+    a.first_stream, a.n_streams = first_stream, n_streams
+    keep = []
+    if seed_mode == abi.SEED_EXPLICIT:
+        st, inc, pix, per = explicit
+        st = np.ascontiguousarray(st, dtype=np.uint64); inc = np.ascontiguousarray(inc, dtype=np.uint64)
+        pix = np.ascontiguousarray(pix, dtype=np.uint32)
+        keep += [st, inc, pix]
+        a.explicit_state = st.ctypes.data_as(C.POINTER(C.c_uint64))
+        a.explicit_inc = inc.ctypes.data_as(C.POINTER(C.c_uint64))
+        a.explicit_pixel = pix.ctypes.data_as(C.POINTER(C.c_uint32))
+        a.explicit_samples_per_stream = per
+        a.n_streams = len(st)
+        count, sps = len(st), per
+    else:
+        n, per = C.c_uint64(), C.c_uint32()
+        rc = lib().b2vp_oracle_stream_count(C.byref(scene.desc), seed_mode, C.byref(n), C.byref(per))
+        if rc:
+            raise RuntimeError(lib().b2vp_oracle_last_error().decode())
+        count = n_streams if n_streams else n.value - first_stream
+        sps = per.value
+    film = np.zeros((h, w, 5), dtype=dtype)
+    a.clear_film = 1
+    tot = abi.Counters()
+    a.totals = C.pointer(tot)
+    state = counters = radiance = None
+    if want_paths:
+        state = np.zeros(count, dtype=np.uint64)
+        counters = np.zeros((count, 6), dtype=np.uint32)
+        radiance = np.zeros((count, sps), dtype=dtype)
+        a.out_state = state.ctypes.data_as(C.POINTER(C.c_uint64))
+        a.out_counters = C.cast(counters.ctypes.data, C.POINTER(abi.PathCounters))
+        a.out_radiance = radiance.ctypes.data
+    rc = lib().b2vp_oracle_render(C.byref(scene.desc), C.byref(a), film.ctypes.data)
+    if rc:
+        raise RuntimeError("oracle error %d: %s" % (rc, lib().b2vp_oracle_last_error().decode()))
+    return pkg.RenderResult(film, tot, state, counters, radiance)
+
+
+def render_parallel(pkg, scene, seed_mode, first_stream, n_streams, n_threads, precision=None):
+    """Splits a stream range over host threads (ctypes releases the GIL).  Returns (film, totals list)."""
+    chunk = (n_streams + n_threads - 1) // n_threads
+    results = [None] * n_threads
+
+    def work(i):
+        lo = first_stream + i * chunk
+        n = min(chunk, first_stream + n_streams - lo)
+        if n > 0:
+            results[i] = render(pkg, scene, seed_mode, precision, lo, n)
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(n_threads)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    results = [r for r in results if r is not None]
+    film = sum(r.film.astype(np.float64) for r in results)
+    return film, [r.totals for r in results]
