@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""bench.py -- volpath (mono) throughput on BASELINE.json configs[1]: the 1D plane-parallel heterogeneous
+Rayleigh atmosphere (gridvolume 1x1x1000, rpv surface, distant 256x1 film), 2^14 spp = 4 194 304 paths
+per GPU per step.  One JSON line on stdout (see the task's bench contract).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--spp S]
+
+A "step" is one full render of the workload (one pass of the hot path over one batch of paths).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+FLOP_PER_SEGMENT = 150  # FP32 flop-equivalents per tentative collision
+WIDTH = 256
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def workload(spp):
+    import scenes
+    return scenes.c2(spp=spp, width=WIDTH, tau=0.5, nz=1000)
+
+
+def config(spp, n_gpus, extra=None):
+    c = {"workload": "BASELINE configs[1]: 1D plane-parallel heterogeneous atmosphere, gridvolume sigma_t "
+                     "1x1x1000 (trilinear, exp profile, tau=0.5), rayleigh, rpv, distant %dx1 film, volpath "
+                     "max_depth=-1 rr_depth=5, scalar_mono (fp32)" % WIDTH,
+         "spp_per_gpu": spp, "paths_per_step": WIDTH * spp * n_gpus, "seeding": "wavefront (sampler.cpp:89-92)",
+         "sharding": "disjoint stream ranges per GPU + one NCCL film reduce" if n_gpus > 1 else "single GPU",
+         "l2": "flushed between steps (256 MiB write); the 4 KB grid is staged in shared memory"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+# ----------------------------------------------------------------------------- CPU (oracle) timing
+def cpu_time_sample(pkg, scene, budget_s, threads):
+    """Times the CPU oracle on a bounded prefix of the workload's stream space with `threads` host threads."""
+    from oracle import oracle
+    abi = pkg.abi
+    t0 = time.perf_counter()
+    pilot = oracle.render(pkg, scene, abi.SEED_WAVEFRONT, first_stream=0, n_streams=4096)
+    rate1 = 4096 / max(time.perf_counter() - t0, 1e-6)      # paths/s on one thread
+    total = scene.film_size[0] * scene.film_size[1] * scene.desc.sensor.sample_count
+    n = int(min(total, max(4096, rate1 * threads * budget_s)))
+    # spread the sample over the stream space so that every sensor direction is represented
+    chunks = max(threads * 4, 64)
+    per = max(1, n // chunks)
+    ranges = [(int(i * (total - per) / max(chunks - 1, 1)), per) for i in range(chunks)]
+    n = per * chunks
+    t0 = time.perf_counter()
+    film, tots = oracle.render_parallel(pkg, scene, abi.SEED_WAVEFRONT, ranges, threads)
+    dt = time.perf_counter() - t0
+    segs = sum(t.n_medium_steps + t.n_intersect for t in tots)
+    return {"paths": n, "seconds": dt, "mpaths_s": n / dt / 1e6, "segments_s": segs / dt,
+            "pilot_mpaths_s_1thread": rate1 / 1e6, "pilot": pilot}
+
+
+class ClockSampler:
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [int(r[0]) for r in self.rows if r and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- arms
+def run_reference(args):
+    """Reference arm: the CPU restatement of the reference's scalar_mono volpath (oracle/, kind 'port': the
+    reference itself needs its cmake build system) on all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import b2vp_import
+    pkg = b2vp_import.load()
+    threads = host_threads()
+    scene = pkg.load_dict(workload(args.spp))
+    per_step = max(2.0, min(10.0, 120.0 / (args.steps + args.warmup)))
+    res = []
+    for i in range(args.warmup + args.steps):
+        r = cpu_time_sample(pkg, scene, per_step, threads)
+        if i >= args.warmup:
+            res.append(r)
+    paths = sum(r["paths"] for r in res)
+    secs = sum(r["seconds"] for r in res)
+    v = paths / secs / 1e6
+    seg = sum(r["segments_s"] * r["seconds"] for r in res) / secs
+    sample = "%d of %d streams of the workload per step (64+ chunks spread evenly over the film), %d threads" % (res[0]["paths"], WIDTH * args.spp, threads)
+    print(json.dumps({
+        "impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / len(res) * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "segments_per_s": seg, "config": config(args.spp, args.gpus),
+        "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import b2vp_import
+    pkg = b2vp_import.load()
+    abi = pkg.abi
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the B200 volpath has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_gpus = world
+
+    # weak scaling: every GPU renders `spp` samples per pixel; the global stream space has spp * N
+    spp_total = args.spp * n_gpus
+    scene = pkg.load_dict(workload(spp_total))
+    per_gpu = WIDTH * args.spp
+    first = rank * per_gpu
+    ds = pkg.DeviceScene(scene, device=local)
+    film = torch.zeros((1, WIDTH, 5), dtype=torch.float32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, first_stream=first, n_streams=per_gpu,
+                      device_film=film.data_ptr(), clear=True, stream=stream)
+        if world > 1:
+            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
+        return r.totals
+
+    for _ in range(args.warmup):
+        flush.fill_(1)
+        step()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    step_ms, kern_ms, launches, tot_last = [], [], 0, None
+    for _ in range(args.steps):
+        flush.fill_(1)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        tot = step()
+        e1.record()
+        barrier()
+        step_ms.append(e0.elapsed_time(e1))
+        kern_ms.append(tot.gpu_ms)
+        launches += tot.n_launches
+        tot_last = tot
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
+    segs = torch.tensor([float(tot_last.n_medium_steps + tot_last.n_intersect), float(tot_last.n_medium_steps),
+                         float(sum(kern_ms) / len(kern_ms))], dtype=torch.float64, device="cuda")
+    seg_sum = segs.clone()
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(seg_sum, op=dist.ReduceOp.SUM)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    paths_per_step = per_gpu * n_gpus
+    value = paths_per_step / (ms_per_step * 1e-3) / 1e6
+    seg_per_s = float(seg_sum[0].item()) / (ms_per_step * 1e-3)
+
+    # ---- e2e: through the public API with HOST buffers: scene upload (H2D) + render + film read-back (D2H)
+    host_film = np.zeros((1, WIDTH, 5), dtype=np.float32)
+    grid_bytes = sum(a.nbytes for a in scene._keep[1] if a is not None)
+    h2d = grid_bytes + 4096
+    e2e_ms = []
+    for i in range(0 if args.profile else 2 + min(args.steps, 5)):
+        barrier()
+        t0 = time.perf_counter()
+        with pkg.DeviceScene(scene, device=local) as ds2:
+            r = ds2.render(seed_mode=abi.SEED_WAVEFRONT, first_stream=first, n_streams=per_gpu, film=host_film * 0)
+            if world > 1:
+                f = torch.from_numpy(r.film).cuda()
+                dist.reduce(f, dst=0, op=dist.ReduceOp.SUM)
+                r.film[...] = f.cpu().numpy()
+        barrier()
+        if i >= 2:
+            e2e_ms.append((time.perf_counter() - t0) * 1e3)
+    e2e_t = torch.tensor([sum(e2e_ms) / max(len(e2e_ms), 1) if e2e_ms else float("nan")], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_val = paths_per_step / (float(e2e_t.item()) * 1e-3) / 1e6
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (volpath_kernel<float>): FP32 issue bound on this workload
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        fp32 = abi.c_d()
+        abi.check(abi.lib().b2vp_measure_fp32_peak(local, abi.C.byref(fp32)))
+        k_ms = sum(kern_ms) / len(kern_ms)
+        flops = tot_last.n_medium_steps * FLOP_PER_SEGMENT
+        achieved = flops / (k_ms * 1e-3) / 1e12
+        roofline = {"bound": "fp32", "achieved": achieved, "peak": fp32.value, "unit": "TFLOP/s",
+                    "frac": achieved / fp32.value if fp32.value else None, "traffic": None,
+                    "kernel": "vp::volpath_kernel<float>", "kernel_ms": k_ms,
+                    "algorithmic": "%d medium steps x %d flop" % (tot_last.n_medium_steps, FLOP_PER_SEGMENT),
+                    "peak_source": "b2vp_measure_fp32_peak (FMA microbenchmark, measured in this run); "
+                                   "HBM peak %s GB/s (MEASURED_PEAKS.json) is not the bound here: the grid "
+                                   "lives in shared memory, algorithmic HBM bytes ~ 0" % peaks.get("hbm_gbs")}
+        # ---- CPU baseline beside it (bounded sample, all host threads)
+        threads = host_threads()
+        cb = cpu_time_sample(pkg, pkg.load_dict(workload(args.spp)), 0.2 if args.profile else 8.0, threads)
+        out = {
+            "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "segments_per_s": seg_per_s, "config": config(args.spp, n_gpus),
+            "clocks": clk, "gpu_launches": launches,
+            "e2e": {"value": e2e_val, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(host_film.nbytes), "ms_per_step": float(e2e_t.item())},
+            "roofline": roofline,
+            "cpu_baseline": {"value": cb["mpaths_s"], "unit": "Mpaths/s", "cores": threads, "kind": "port",
+                             "sample": "%d streams of the workload spread evenly over the film, %.1f s" % (cb["paths"], cb["seconds"]),
+                             "segments_per_s": cb["segments_s"],
+                             "one_thread_mpaths_s": cb["pilot_mpaths_s_1thread"]},
+        }
+        print(json.dumps(out))
+    ds.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--profile", action="store_true", help="kernel-only run for ncu: no e2e leg, no CPU baseline")
+    ap.add_argument("--spp", type=int, default=16384, help="samples per pixel per GPU (BASELINE: 2^14)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -474,6 +474,21 @@ int make_stream_space(const b2vp_scene *s, int32_t seed_mode, uint64_t explicit_
 
 namespace {
 
+/* 16 independent FMA chains per thread: the non-tensor FP32 roofline denominator */
+__global__ void fma_peak_kernel(float *sink, int iters, float m) {
+    float a[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[k] = (float) (threadIdx.x + k);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) a[k] = __fmaf_rn(a[k], m, 0.5f);
+    }
+    float r = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) r += a[k];
+    if (r == 123.456f) sink[threadIdx.x] = r;
+}
+
 template <typename F> DeviceScene<F> &dev_of(b2vp_scene *s);
 template <> DeviceScene<float> &dev_of<float>(b2vp_scene *s) { return s->dev32; }
 template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64; }
@@ -717,6 +732,34 @@ int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film) {
     if (args->precision == B2VP_PREC_F32) return render_typed<float>(scene, args, film);
     if (args->precision == B2VP_PREC_F64) return render_typed<double>(scene, args, film);
     return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
+}
+
+int b2vp_measure_fp32_peak(int32_t device, double *tflops) {
+    if (!tflops) return fail(B2VP_ERR_INVALID, "null argument");
+    CU_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU_CHECK(cudaGetDeviceProperties(&prop, device));
+    DevBuf sink;
+    CU_CHECK(sink.alloc(sizeof(float) * 1024));
+    cudaEvent_t e0, e1;
+    CU_CHECK(cudaEventCreate(&e0));
+    CU_CHECK(cudaEventCreate(&e1));
+    const int iters = 1 << 15, blocks = prop.multiProcessorCount * 8, threads = 256;
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        CU_CHECK(cudaEventRecord(e0));
+        fma_peak_kernel<<<blocks, threads>>>(sink.as<float>(), iters, 1.0001f);
+        CU_CHECK(cudaEventRecord(e1));
+        CU_CHECK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        double flop = 2.0 * 16 * (double) iters * blocks * threads;
+        if (rep > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops = best;
+    return B2VP_OK;
 }
 
 void b2vp_cancel(b2vp_scene_t *scene) {

@@ -68,7 +68,7 @@ class DeviceScene:
         abi.lib().b2vp_cancel(self._h)
 
     def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None,
-               want_paths=False, film=None, stream=None):
+               want_paths=False, film=None, stream=None, device_film=None, clear=True):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
         `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film)."""
         prec = self.scene.precision if precision is None else precision
@@ -94,7 +94,10 @@ class DeviceScene:
         else:
             total, sps = self.stream_count(seed_mode)
             count = n_streams if n_streams else total - first_stream
-        if film is None:
+        if device_film is not None:
+            # film stays resident in HBM: `device_film` is a device pointer to H*W*5 reals (e.g. tensor.data_ptr())
+            a.film_on_device, a.clear_film = 1, int(clear)
+        elif film is None:
             film = np.zeros((h, w, 5), dtype=dtype)
             a.clear_film = 1
         else:
@@ -110,7 +113,8 @@ class DeviceScene:
             a.out_state = state.ctypes.data_as(C.POINTER(C.c_uint64))
             a.out_counters = C.cast(counters.ctypes.data, C.POINTER(abi.PathCounters))
             a.out_radiance = radiance.ctypes.data
-        abi.check(abi.lib().b2vp_render(self._h, C.byref(a), film.ctypes.data))
+        abi.check(abi.lib().b2vp_render(self._h, C.byref(a), device_film if device_film is not None
+                                        else film.ctypes.data))
         return RenderResult(film, tot, state, counters, radiance)
 
 

@@ -313,6 +313,11 @@ const char *b2vp_last_error(void);
 uint32_t b2vp_abi_version(void);
 int b2vp_device_count(void);
 
+/* Roofline denominator for the FP32-bound configurations (not in
+   MEASURED_PEAKS.json): runs a dependent-free FMA loop on every SM of `device` and
+   returns the achieved non-tensor FP32 rate in TFLOP/s (FMA = 2 flop).           */
+int b2vp_measure_fp32_peak(int32_t device, double *tflops);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,19 +92,22 @@ def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, e
     return pkg.RenderResult(film, tot, state, counters, radiance)
 
 
-def render_parallel(pkg, scene, seed_mode, first_stream, n_streams, n_threads, precision=None):
-    """Splits a stream range over host threads (ctypes releases the GIL).  Returns (film, totals list)."""
-    chunk = (n_streams + n_threads - 1) // n_threads
-    results = [None] * n_threads
+def render_parallel(pkg, scene, seed_mode, ranges, n_threads, precision=None):
+    """Renders a list of (first_stream, n_streams) ranges on `n_threads` host threads (ctypes releases the
+    GIL).  Returns (summed film in float64, list of totals)."""
+    results, lock, todo = [], threading.Lock(), list(ranges)
 
-    def work(i):
-        lo = first_stream + i * chunk
-        n = min(chunk, first_stream + n_streams - lo)
-        if n > 0:
-            results[i] = render(pkg, scene, seed_mode, precision, lo, n)
-    ts = [threading.Thread(target=work, args=(i,)) for i in range(n_threads)]
+    def work():
+        while True:
+            with lock:
+                if not todo:
+                    return
+                lo, n = todo.pop()
+            r = render(pkg, scene, seed_mode, precision, lo, n)
+            with lock:
+                results.append(r)
+    ts = [threading.Thread(target=work) for _ in range(n_threads)]
     [t.start() for t in ts]
     [t.join() for t in ts]
-    results = [r for r in results if r is not None]
     film = sum(r.film.astype(np.float64) for r in results)
     return film, [r.totals for r in results]
