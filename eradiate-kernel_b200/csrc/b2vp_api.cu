@@ -7,6 +7,9 @@
 #include "../../include/b2vp.h"
 #include "bvh_build.h"
 #include "vp_kernels.cuh"
+#include "vp_wavefront.cuh"
+
+#include <cstdlib>
 
 #include <atomic>
 #include <cstdarg>
@@ -571,7 +574,17 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
     out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
     size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
-    auto kern = volpath_kernel<F>;
+    /* kernel selection: the wavefront kernel is the product; B2VP_KERNEL=mega selects the
+       one-thread-per-path twin (same results, kept as the correctness reference on the device) */
+    typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
+    Kern kern = volpath_wf_kernel<F, 12>;
+    if (const char *e = std::getenv("B2VP_KERNEL")) {
+        if (!std::strcmp(e, "mega")) kern = volpath_kernel<F>;
+        else if (!std::strcmp(e, "wf4")) kern = volpath_wf_kernel<F, 4>;
+        else if (!std::strcmp(e, "wf8")) kern = volpath_wf_kernel<F, 8>;
+        else if (!std::strcmp(e, "wf16")) kern = volpath_wf_kernel<F, 16>;
+        else if (!std::strcmp(e, "wf24")) kern = volpath_wf_kernel<F, 24>;
+    }
     CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = 0;
     CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
