@@ -577,13 +577,12 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     /* kernel selection: the wavefront kernel is the product; B2VP_KERNEL=mega selects the
        one-thread-per-path twin (same results, kept as the correctness reference on the device) */
     typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
-    Kern kern = volpath_wf_kernel<F, 12>;
+    Kern kern = volpath_wf_kernel<F, 2>;
     if (const char *e = std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) kern = volpath_kernel<F>;
+        else if (!std::strcmp(e, "wf1")) kern = volpath_wf_kernel<F, 1>;
+        else if (!std::strcmp(e, "wf3")) kern = volpath_wf_kernel<F, 3>;
         else if (!std::strcmp(e, "wf4")) kern = volpath_wf_kernel<F, 4>;
-        else if (!std::strcmp(e, "wf8")) kern = volpath_wf_kernel<F, 8>;
-        else if (!std::strcmp(e, "wf16")) kern = volpath_wf_kernel<F, 16>;
-        else if (!std::strcmp(e, "wf24")) kern = volpath_wf_kernel<F, 24>;
     }
     CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int per_sm = 0;

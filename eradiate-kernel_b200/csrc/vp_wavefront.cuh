@@ -1,16 +1,23 @@
 /*
  * vp_wavefront.cuh -- the production render kernel: a register-resident
  * wavefront.  Every lane owns one path and runs it as an explicit state machine;
- * the warp schedules itself so that lanes execute the SAME piece of code
- * together:
+ * each warp schedules itself so that its lanes execute the SAME piece of code
+ * together.  Work is cut into five phases:
  *
- *   hot  iteration: one tentative-collision step (Medium::sample_interaction +
- *                   bookkeeping) for every lane that is marching -- the main
- *                   path, the emitter-sampling march (sample_emitter) and the
- *                   direct-light march (evaluate_direct_light) all share it;
- *   rare iteration: ray/scene intersection, scattering, surface shading, path
- *                   termination + film splat, path regeneration -- entered
- *                   when enough lanes wait for one of them (warp ballot).
+ *   STEP     one tentative-collision step (Medium::sample_interaction and its
+ *            bookkeeping).  The main path, the emitter-sampling march
+ *            (sample_emitter) and the direct-light march (evaluate_direct_light)
+ *            all share this code, so lanes in different marches stay converged;
+ *   ISECT    Scene::ray_intersect;
+ *   SCATTER  real medium scattering: albedo weight, emitter sample, phase sample;
+ *   SURFACE  surface event: emitter sample + BSDF eval, BSDF sample;
+ *   END      film splat of a finished path and path regeneration.
+ *
+ * Per iteration the warp counts (ballot) how many lanes wait for each phase and
+ * runs the one with the most lanes; the others keep their state in registers
+ * and wait.  Running one phase per iteration keeps the instruction stream of
+ * an iteration compact (the kernel is instruction-fetch bound otherwise, see
+ * profiles/) and gives every phase a large active mask.
  *
  * Arithmetic and random-number order are exactly those of vp_integrator.cuh (the
  * one-thread-per-path twin, reference src/integrators/volpath.cpp:38-483); only
@@ -24,18 +31,18 @@ namespace vp {
 enum LaneState : int {
     L_STEP_A = 0,   /* loop top + free-flight sampling                         */
     L_STEP_B,       /* rest of the tentative-collision step                    */
-    L_PATH_END,
-    L_NEW,          /* next sample of the stream / next stream                 */
+    L_ISECT,        /* Scene::ray_intersect                                    */
     L_SCATTER,      /* real medium scattering: albedo, start emitter march     */
     L_SCATTER_B,    /* phase function sampling                                 */
     L_SURFACE,      /* surface hit: start emitter march                        */
     L_SURF_B,       /* BSDF sampling, second intersection                      */
-    L_ISECT,        /* Scene::ray_intersect                                    */
-    L_SURF_C,       /* start the direct-light march                            */
-    L_SURF_D,       /* medium transition                                       */
+    L_PATH_END,
+    L_NEW,          /* next sample of the stream / next stream                 */
     L_DONE
 };
 enum MarchMode : int { M_MAIN = 0, M_NEE = 1, M_DL = 2 };
+/* what follows a march / an intersection */
+enum Continuation : int { C_STEP_B = 0, C_SCATTER_B, C_SURF_B, C_START_DL, C_AFTER_DL };
 
 /* what a march needs from a surface hit (spawn point, normal, shape) */
 template <typename F> struct MarchHit {
@@ -44,8 +51,8 @@ template <typename F> struct MarchHit {
     int shape;
 };
 
-template <typename F, int RARE_MIN>
-__global__ void __launch_bounds__(256)
+template <typename F, int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS)
 volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStreams sp,
                   const __grid_constant__ RenderOut<F> out) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -58,13 +65,14 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     const uint32_t max_depth = g.max_depth, rr_depth = g.rr_depth;
     const bool ltr = g.ltr != 0;
     const F INF = inf_<F>();
+    const unsigned FULL = 0xffffffffu;
 
     unsigned long long tot[TOT_N];
 #pragma unroll
     for (int i = 0; i < TOT_N; ++i) tot[i] = 0;
 
     /* ---- lane state ------------------------------------------------------ */
-    int state = L_NEW, mode = M_MAIN, cont = L_DONE, isect_ret = L_STEP_B;
+    int state = L_NEW, mode = M_MAIN, cont = C_STEP_B, isect_ret = C_STEP_B;
     bool isect_march = false;
     /* stream */
     unsigned long long k = 0;
@@ -98,19 +106,30 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     mi.t = INF; mi.mint = 0; mi.p = ray.o; mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
 
     auto next_1d = [&](bool m) { return rng.next(F(), m); };
-    auto null_transmission = [&](int shape) -> F {
-        return sv.bsdfs[sv.shapes[shape].bsdf].type == 1 ? (F) 1 : (F) 0;
-    };
     auto mis_weight = [&](F pdf_a, F pdf_b) -> F {
         pdf_a *= pdf_a; pdf_b *= pdf_b;
         return pdf_a > 0 ? pdf_a / (pdf_a + pdf_b) : (F) 0;
+    };
+    /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the new hit */
+    auto start_dl = [&]() {
+        ray2 = ray;
+        medium2 = medium;
+        si2.t = si.t; si2.p = si.p; si2.n = si.n; si2.shape = si.shape;
+        needs_isect2 = false;
+        transmittance = 1;
+        emitter_val = 0;
+        mode = M_DL;
+        cont = C_AFTER_DL;
+        state = L_STEP_A;
     };
     /* end of a march: hand the result back to the main path */
     auto march_done = [&]() {
         if (mode == M_NEE) result += nee_w * (transmittance * emitter_val);
         /* M_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
         mode = M_MAIN;
-        state = cont;
+        if (cont == C_SCATTER_B) state = L_SCATTER_B;
+        else if (cont == C_SURF_B) state = L_SURF_B;
+        else { medium = medium_next; state = L_STEP_A; } /* C_AFTER_DL: medium switch (volpath.cpp:249-250) */
     };
     /* sample_emitter prologue (volpath.cpp:261-283): returns false when no march is needed */
     auto begin_nee = [&](V3<F> ref_p, bool is_medium_interaction, DirSample<F> &ds) -> bool {
@@ -133,14 +152,24 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     };
 
     for (;;) {
-        const unsigned hot = __ballot_sync(0xffffffffu, state <= L_STEP_B);
-        const unsigned rare = __ballot_sync(0xffffffffu, state > L_STEP_B && state != L_DONE);
-        if ((hot | rare) == 0) break;
+        /* ---- warp scheduler: run the phase most lanes are waiting for ---- */
+        const int n_step = __popc(__ballot_sync(FULL, state <= L_STEP_B));
+        const int n_isect = __popc(__ballot_sync(FULL, state == L_ISECT));
+        const int n_scat = __popc(__ballot_sync(FULL, state == L_SCATTER || state == L_SCATTER_B));
+        const int n_surf = __popc(__ballot_sync(FULL, state == L_SURFACE || state == L_SURF_B));
+        const int n_end = __popc(__ballot_sync(FULL, state == L_PATH_END || state == L_NEW));
+        if ((n_step | n_isect | n_scat | n_surf | n_end) == 0) break;
+        int phase = 0, best = n_step;
+        if (n_isect > best) { best = n_isect; phase = 1; }
+        if (n_surf > best) { best = n_surf; phase = 3; }
+        if (n_scat > best) { best = n_scat; phase = 2; }
+        if (n_end > best) { best = n_end; phase = 4; }
 
-        if (rare == 0 || (hot != 0 && __popc(rare) < RARE_MIN)) {
-            /* =========================== hot iteration ========================== */
-            if (state == L_STEP_A) {
-                bool go = true;
+        if (phase == 0) {
+            /* ================================ STEP ================================ */
+            const bool do_a = state == L_STEP_A;
+            bool go = do_a;
+            if (do_a) {
                 if (mode == M_MAIN) {
                     /* termination / Russian roulette (volpath.cpp:72-87) */
                     bool active = throughput != 0;
@@ -155,120 +184,215 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                     ray2.maxt = remaining;
                     if (!(remaining > 0)) { march_done(); go = false; }
                 }
-                if (go) {
-                    /* one free-flight sample for whichever ray this lane is marching */
-                    const bool main_mode = mode == M_MAIN;
-                    const int med = main_mode ? medium : medium2;
-                    a_in_medium = med >= 0;
-                    if (a_in_medium) {
-                        const DMedium<F> &m = sv.media[med];
-                        Ray<F> r;
-                        r.o = main_mode ? ray.o : ray2.o;
-                        r.d = main_mode ? ray.d : ray2.d;
-                        r.d_rcp = main_mode ? ray.d_rcp : ray2.d_rcp;
-                        r.mint = main_mode ? ray.mint : ray2.mint;
-                        r.maxt = main_mode ? ray.maxt : ray2.maxt;
-                        sample_interaction(sv, m, r, next_1d(true), mi, cnt);
-                        if (m.type == 0 && mi.valid()) {
-                            if (main_mode) ray.maxt = mi.t;
-                            else ray2.maxt = mode == M_NEE ? min_(mi.t, remaining) : mi.t;
-                        }
-                    }
-                    const bool need = main_mode ? needs_isect : needs_isect2;
-                    if (need) { state = L_ISECT; isect_ret = L_STEP_B; isect_march = !main_mode; }
-                    else state = L_STEP_B;
+            }
+            __syncwarp();
+            /* one free-flight sample for whichever ray this lane is marching */
+            const bool main_mode = mode == M_MAIN;
+            const int med = main_mode ? medium : medium2;
+            if (go) a_in_medium = med >= 0;
+            if (go && a_in_medium) {
+                const DMedium<F> &m = sv.media[med];
+                Ray<F> r;
+                r.o = main_mode ? ray.o : ray2.o;
+                r.d = main_mode ? ray.d : ray2.d;
+                r.d_rcp = main_mode ? ray.d_rcp : ray2.d_rcp;
+                r.mint = main_mode ? ray.mint : ray2.mint;
+                r.maxt = main_mode ? ray.maxt : ray2.maxt;
+                sample_interaction(sv, m, r, next_1d(true), mi, cnt);
+                if (m.type == 0 && mi.valid()) {
+                    if (main_mode) ray.maxt = mi.t;
+                    else ray2.maxt = mode == M_NEE ? min_(mi.t, remaining) : mi.t;
                 }
             }
-            if (state == L_STEP_B) {
-                /* common part: surface-vs-collision ordering and the transmittance / pdf ratio
-                   (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
-                const bool main_mode = mode == M_MAIN, nee = mode == M_NEE;
-                bool spectral = false;
-                F ratio = 1;
+            __syncwarp();
+            if (go) {
+                const bool need = main_mode ? needs_isect : needs_isect2;
+                if (need) { state = L_ISECT; isect_ret = C_STEP_B; isect_march = !main_mode; }
+                else state = L_STEP_B;
+            }
+            const bool do_b = state == L_STEP_B;
+            /* common part of step B: surface-vs-collision ordering and the transmittance / pdf ratio
+               (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
+            const bool nee = mode == M_NEE;
+            bool spectral = false;
+            F ratio = 1;
+            if (do_b && a_in_medium) {
+                const F si_t = main_mode ? si.t : si2.t;
+                spectral = sv.media[med].spectral != 0;
+                if (si_t < mi.t) mi.t = INF;
+                if (spectral) {
+                    F tt = min_(mi.t, si_t);
+                    if (nee) tt = min_(remaining, tt);
+                    F t = tt - mi.mint;
+                    F tr = exp_(-t * mi.combined);
+                    bool surface_first = si_t < mi.t || (nee && mi.t > remaining);
+                    F pdf = surface_first ? tr : tr * mi.combined;
+                    ratio = pdf > 0 ? tr / pdf : (F) 0;
+                }
+            }
+            __syncwarp();
+            if (do_b && main_mode) {
+                bool act_null = false, act_real = false, escaped = false;
                 if (a_in_medium) {
-                    const F si_t = main_mode ? si.t : si2.t;
-                    spectral = sv.media[main_mode ? medium : medium2].spectral != 0;
-                    if (si_t < mi.t) mi.t = INF;
-                    if (spectral) {
-                        F tt = min_(mi.t, si_t);
-                        if (nee) tt = min_(remaining, tt);
-                        F t = tt - mi.mint;
-                        F tr = exp_(-t * mi.combined);
-                        bool surface_first = si_t < mi.t || (nee && mi.t > remaining);
-                        F pdf = surface_first ? tr : tr * mi.combined;
-                        ratio = pdf > 0 ? tr / pdf : (F) 0;
+                    if (spectral) throughput *= ratio;
+                    escaped = !mi.valid();
+                    const bool active_medium = mi.valid();
+                    F u = next_1d(active_medium);
+                    bool null_scatter = u >= mi.sigma_t / mi.combined;
+                    act_null = null_scatter && active_medium;
+                    act_real = !act_null && active_medium;
+                    if (spectral && act_null) throughput *= mi.sigma_n * mi.combined / mi.sigma_n;
+                    if (act_real) depth += 1;
+                }
+                const bool active = depth < max_depth;
+                act_real = act_real && active;
+                if (act_null) { /* volpath.cpp:140-144 */
+                    cnt.n_null++;
+                    ray.o = mi.p;
+                    ray.mint = 0;
+                    si.t = si.t - mi.t;
+                    state = L_STEP_A;
+                } else if (act_real) {
+                    state = L_SCATTER;
+                } else if ((!a_in_medium || escaped) && si.valid()) {
+                    state = L_SURFACE;
+                } else {
+                    state = L_PATH_END;
+                }
+            } else if (do_b) {
+                /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
+                bool escaped = false, active_medium = false;
+                if (a_in_medium) {
+                    if (spectral) transmittance *= ratio;
+                    if (nee) {
+                        if (mi.t > remaining && mi.valid()) total_dist = ds_dist;
+                        if (mi.t > remaining) mi.t = INF;
+                    }
+                    escaped = !mi.valid();
+                    active_medium = mi.valid();
+                    if (active_medium) {
+                        if (nee) total_dist += mi.t;
+                        cnt.n_null++;
+                        ray2.o = mi.p;
+                        ray2.mint = 0;
+                        si2.t = si2.t - mi.t;
+                        if (spectral) transmittance *= mi.sigma_n;
+                        else transmittance *= mi.sigma_n / mi.combined;
                     }
                 }
-                if (main_mode) {
-                    bool act_null = false, act_real = false, escaped = false;
-                    if (a_in_medium) {
-                        if (spectral) throughput *= ratio;
-                        escaped = !mi.valid();
-                        const bool active_medium = mi.valid();
-                        F u = next_1d(active_medium);
-                        bool null_scatter = u >= mi.sigma_t / mi.combined;
-                        act_null = null_scatter && active_medium;
-                        act_real = !act_null && active_medium;
-                        if (spectral && act_null) throughput *= mi.sigma_n * mi.combined / mi.sigma_n;
-                        if (act_real) depth += 1;
-                    }
-                    const bool active = depth < max_depth;
-                    act_real = act_real && active;
-                    if (act_null) { /* volpath.cpp:140-144 */
-                        cnt.n_null++;
-                        ray.o = mi.p;
-                        ray.mint = 0;
-                        si.t = si.t - mi.t;
-                        state = L_STEP_A;
-                    } else if (act_real) {
-                        state = L_SCATTER;
-                    } else if ((!a_in_medium || escaped) && si.valid()) {
-                        state = L_SURFACE;
-                    } else {
-                        state = L_PATH_END;
-                    }
+                bool active_surface = !a_in_medium || escaped;
+                if (nee && active_surface) total_dist += si2.t;
+                active_surface = active_surface && si2.t != INF && !active_medium;
+                if (active_surface) {
+                    const DShape<F> &sh = sv.shapes[si2.shape];
+                    /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
+                    transmittance *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
+                    ray2 = spawn_ray(si2.p, ray2.d);
+                    if (sh.interior >= 0 || sh.exterior >= 0)
+                        medium2 = dot(ray2.d, si2.n) > 0 ? sh.exterior : sh.interior;
+                }
+                if (nee) ray2.maxt = remaining;
+                needs_isect2 = needs_isect2 || active_surface;
+                const bool active = (active_medium || active_surface) && transmittance != 0;
+                if (active) state = L_STEP_A;
+                else march_done();
+            }
+        } else if (phase == 1) {
+            /* ================================ ISECT =============================== */
+            if (state == L_ISECT) {
+                Ray<F> r;
+                r.o = isect_march ? ray2.o : ray.o;
+                r.d = isect_march ? ray2.d : ray.d;
+                r.d_rcp = isect_march ? ray2.d_rcp : ray.d_rcp;
+                r.mint = isect_march ? ray2.mint : ray.mint;
+                r.maxt = isect_march ? ray2.maxt : ray.maxt;
+                SurfaceHit<F> h;
+                ray_intersect(sv, r, h, cnt);
+                if (isect_march) {
+                    si2.t = h.t; si2.p = h.p; si2.n = h.n; si2.shape = h.shape;
+                    needs_isect2 = false;
                 } else {
-                    /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
-                    bool escaped = false, active_medium = false;
-                    if (a_in_medium) {
-                        if (spectral) transmittance *= ratio;
-                        if (nee) {
-                            if (mi.t > remaining && mi.valid()) total_dist = ds_dist;
-                            if (mi.t > remaining) mi.t = INF;
-                        }
-                        escaped = !mi.valid();
-                        active_medium = mi.valid();
-                        if (active_medium) {
-                            if (nee) total_dist += mi.t;
-                            cnt.n_null++;
-                            ray2.o = mi.p;
-                            ray2.mint = 0;
-                            si2.t = si2.t - mi.t;
-                            if (spectral) transmittance *= mi.sigma_n;
-                            else transmittance *= mi.sigma_n / mi.combined;
-                        }
-                    }
-                    bool active_surface = !a_in_medium || escaped;
-                    if (nee && active_surface) total_dist += si2.t;
-                    active_surface = active_surface && si2.t != INF && !active_medium;
-                    if (active_surface) {
-                        transmittance *= null_transmission(si2.shape);
-                        ray2 = spawn_ray(si2.p, ray2.d);
-                    }
-                    if (nee) ray2.maxt = remaining;
-                    needs_isect2 = needs_isect2 || active_surface;
-                    const bool active = (active_medium || active_surface) && transmittance != 0;
-                    if (active_surface) {
-                        const DShape<F> &sh = sv.shapes[si2.shape];
-                        if (sh.interior >= 0 || sh.exterior >= 0)
-                            medium2 = dot(ray2.d, si2.n) > 0 ? sh.exterior : sh.interior;
-                    }
-                    if (active) state = L_STEP_A;
-                    else march_done();
+                    si = h;
+                    needs_isect = false;
+                }
+                if (isect_ret == C_START_DL) start_dl();
+                else state = L_STEP_B;
+            }
+        } else if (phase == 2) {
+            /* =============================== SCATTER ============================== */
+            if (state == L_SCATTER) { /* volpath.cpp:146-168 */
+                cnt.n_real++;
+                const DMedium<F> &m = sv.media[medium];
+                if (m.spectral) throughput *= mi.sigma_s * mi.combined / mi.sigma_t;
+                else throughput *= mi.sigma_s / mi.sigma_t;
+                valid_ray = true;
+                ray.o = mi.p; /* the old origin is dead: keep the scattering position here */
+                state = L_SCATTER_B;
+                if (m.sample_emitters) {
+                    DirSample<F> ds;
+                    bool march = begin_nee(mi.p, true, ds);
+                    nee_w = throughput * phase_eval(sv.phases[m.phase], -ray.d, ds.d);
+                    cont = C_SCATTER_B;
+                    if (march) { mode = M_NEE; state = L_STEP_A; }
+                    else result += nee_w * emitter_val;
+                }
+            } else if (state == L_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
+                const DPhase<F> &phase_fn = sv.phases[sv.media[medium].phase];
+                F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
+                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                V3<F> wo = phase_sample(phase_fn, ray.d, s2x, s2y);
+                ray = spawn_ray(ray.o, wo);
+                ray.mint = 0;
+                needs_isect = true;
+                state = L_STEP_A;
+            }
+        } else if (phase == 3) {
+            /* =============================== SURFACE ============================== */
+            if (state == L_SURFACE) { /* volpath.cpp:192-212 */
+                cnt.n_surface++;
+                const DBsdf<F> &bsdf = sv.bsdfs[sv.shapes[si.shape].bsdf];
+                bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
+                state = L_SURF_B;
+                if (active_e) {
+                    DirSample<F> ds;
+                    bool march = begin_nee(si.p, false, ds);
+                    V3<F> wo = si.sh.to_local(ds.d);
+                    F bsdf_val = bsdf_eval(bsdf, si.wi, wo);
+                    F bpdf = bsdf_pdf(bsdf, si.wi, wo);
+                    nee_w = throughput * bsdf_val * mis_weight(ds.pdf, ds.delta ? (F) 0 : bpdf);
+                    cont = C_SURF_B;
+                    if (march) { mode = M_NEE; state = L_STEP_A; }
+                    else result += nee_w * emitter_val;
+                }
+            } else if (state == L_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
+                const DShape<F> &sh = sv.shapes[si.shape];
+                const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
+                F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
+                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                V3<F> bwo;
+                F bs_pdf, bs_eta, bsdf_val;
+                uint32_t sampled_type;
+                bsdf_sample(bsdf, si.wi, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
+                throughput *= bsdf_val;
+                eta *= bs_eta;
+                ray = spawn_ray(si.p, si.sh.to_world(bwo));
+                needs_isect = true;
+                bool non_null = !(sampled_type & BF_Null);
+                if (non_null) depth += 1;
+                valid_ray = valid_ray || non_null;
+                bool add_emitter = !(sampled_type & BF_Delta) && throughput != 0 && (depth < max_depth);
+                /* medium switch (volpath.cpp:249-250), applied after the direct-light march */
+                medium_next = (sh.interior >= 0 || sh.exterior >= 0) ? (dot(ray.d, si.n) > 0 ? sh.exterior : sh.interior)
+                                                                     : medium;
+                if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
+                    state = L_ISECT; isect_ret = C_START_DL; isect_march = false;
+                } else {
+                    medium = medium_next;
+                    state = L_STEP_A;
                 }
             }
         } else {
-            /* =========================== rare iteration ========================= */
+            /* ================================= END ================================ */
             if (state == L_PATH_END) {
                 /* render_sample tail (integrator.cpp:267-287) + ImageBlock::put (imageblock.cpp:85-169) */
                 F value = ray_weight * result;
@@ -328,128 +452,28 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                         have_stream = true;
                     }
                 }
-                if (state == L_NEW && have_stream) {
-                    if (j >= st.n_samples || st.empty) {
-                        /* empty stream (pixel outside the block): finish it next time round */
-                    } else {
-                        /* render_sample prologue (integrator.cpp:233-264) */
-                        posx = (F) (uint32_t) st.px + rng.next(F(), true);
-                        posy = (F) (uint32_t) st.py + rng.next(F(), true);
-                        F apx = (F) 0.5, apy = (F) 0.5;
-                        if (sn.needs_aperture_sample) { apx = rng.next(F(), true); apy = rng.next(F(), true); }
-                        if (sn.has_shutter) (void) rng.next(F(), true);
-                        (void) rng.next(F(), true); /* wavelength sample (integrator.cpp:252) */
-                        F ax = (posx - (F) sn.crop_offset[0]) / (F) sn.crop_size[0];
-                        F ay = (posy - (F) sn.crop_offset[1]) / (F) sn.crop_size[1];
-                        ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
-                        /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */
-                        valid_ray = false;
-                        eta = 1; throughput = 1; result = 0;
-                        medium = sn.medium;
-                        depth = 0;
-                        si.t = INF; si.shape = -1;
-                        needs_isect = true;
-                        mode = M_MAIN;
-                        state = L_STEP_A;
-                    }
+                if (state == L_NEW && have_stream && !(j >= st.n_samples || st.empty)) {
+                    /* render_sample prologue (integrator.cpp:233-264); an empty stream (pixel outside
+                       its block) is finished on the next visit */
+                    posx = (F) (uint32_t) st.px + rng.next(F(), true);
+                    posy = (F) (uint32_t) st.py + rng.next(F(), true);
+                    F apx = (F) 0.5, apy = (F) 0.5;
+                    if (sn.needs_aperture_sample) { apx = rng.next(F(), true); apy = rng.next(F(), true); }
+                    if (sn.has_shutter) (void) rng.next(F(), true);
+                    (void) rng.next(F(), true); /* wavelength sample (integrator.cpp:252) */
+                    F ax = (posx - (F) sn.crop_offset[0]) / (F) sn.crop_size[0];
+                    F ay = (posy - (F) sn.crop_offset[1]) / (F) sn.crop_size[1];
+                    ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
+                    /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */
+                    valid_ray = false;
+                    eta = 1; throughput = 1; result = 0;
+                    medium = sn.medium;
+                    depth = 0;
+                    si.t = INF; si.shape = -1;
+                    needs_isect = true;
+                    mode = M_MAIN;
+                    state = L_STEP_A;
                 }
-            }
-            if (state == L_SCATTER) { /* volpath.cpp:146-168 */
-                cnt.n_real++;
-                const DMedium<F> &m = sv.media[medium];
-                if (m.spectral) throughput *= mi.sigma_s * mi.combined / mi.sigma_t;
-                else throughput *= mi.sigma_s / mi.sigma_t;
-                valid_ray = true;
-                ray.o = mi.p; /* the old origin is dead: keep the scattering position here */
-                state = L_SCATTER_B;
-                if (m.sample_emitters) {
-                    DirSample<F> ds;
-                    bool march = begin_nee(mi.p, true, ds);
-                    nee_w = throughput * phase_eval(sv.phases[m.phase], -ray.d, ds.d);
-                    cont = L_SCATTER_B;
-                    if (march) { mode = M_NEE; state = L_STEP_A; }
-                    else result += nee_w * emitter_val;
-                }
-            }
-            if (state == L_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
-                const DPhase<F> &phase = sv.phases[sv.media[medium].phase];
-                F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> wo = phase_sample(phase, ray.d, s2x, s2y);
-                ray = spawn_ray(ray.o, wo);
-                ray.mint = 0;
-                needs_isect = true;
-                state = L_STEP_A;
-            }
-            if (state == L_SURFACE) { /* volpath.cpp:192-212 */
-                cnt.n_surface++;
-                const DBsdf<F> &bsdf = sv.bsdfs[sv.shapes[si.shape].bsdf];
-                bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
-                state = L_SURF_B;
-                if (active_e) {
-                    DirSample<F> ds;
-                    bool march = begin_nee(si.p, false, ds);
-                    V3<F> wo = si.sh.to_local(ds.d);
-                    F bsdf_val = bsdf_eval(bsdf, si.wi, wo);
-                    F bpdf = bsdf_pdf(bsdf, si.wi, wo);
-                    nee_w = throughput * bsdf_val * mis_weight(ds.pdf, ds.delta ? (F) 0 : bpdf);
-                    cont = L_SURF_B;
-                    if (march) { mode = M_NEE; state = L_STEP_A; }
-                    else result += nee_w * emitter_val;
-                }
-            }
-            if (state == L_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
-                const DShape<F> &sh = sv.shapes[si.shape];
-                const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
-                F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> bwo;
-                F bs_pdf, bs_eta, bsdf_val;
-                uint32_t sampled_type;
-                bsdf_sample(bsdf, si.wi, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
-                throughput *= bsdf_val;
-                eta *= bs_eta;
-                ray = spawn_ray(si.p, si.sh.to_world(bwo));
-                needs_isect = true;
-                bool non_null = !(sampled_type & BF_Null);
-                if (non_null) depth += 1;
-                valid_ray = valid_ray || non_null;
-                bool add_emitter = !(sampled_type & BF_Delta) && throughput != 0 && (depth < max_depth);
-                /* medium switch (volpath.cpp:249-250), applied after the direct-light march */
-                medium_next = (sh.interior >= 0 || sh.exterior >= 0) ? (dot(ray.d, si.n) > 0 ? sh.exterior : sh.interior)
-                                                                     : medium;
-                if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
-                    state = L_ISECT; isect_ret = L_SURF_C; isect_march = false;
-                } else {
-                    state = L_SURF_D;
-                }
-            }
-            if (state == L_ISECT) {
-                if (isect_march) {
-                    SurfaceHit<F> h;
-                    ray_intersect(sv, ray2, h, cnt);
-                    si2.t = h.t; si2.p = h.p; si2.n = h.n; si2.shape = h.shape;
-                    needs_isect2 = false;
-                } else {
-                    ray_intersect(sv, ray, si, cnt);
-                    needs_isect = false;
-                }
-                state = isect_ret;
-            }
-            if (state == L_SURF_C) { /* evaluate_direct_light prologue (volpath.cpp:370-383) */
-                ray2 = ray;
-                medium2 = medium;
-                si2.t = si.t; si2.p = si.p; si2.n = si.n; si2.shape = si.shape;
-                needs_isect2 = false;
-                transmittance = 1;
-                emitter_val = 0;
-                mode = M_DL;
-                cont = L_SURF_D;
-                state = L_STEP_A;
-            }
-            if (state == L_SURF_D) {
-                medium = medium_next;
-                state = L_STEP_A;
             }
         }
     }
@@ -458,7 +482,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
 #pragma unroll
     for (int i = 0; i < TOT_N; ++i) {
         unsigned long long v = tot[i];
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(FULL, v, o);
         if ((threadIdx.x & 31) == 0 && v) atomicAdd(out.totals + i, v);
     }
     if (out.film_in_smem) {
