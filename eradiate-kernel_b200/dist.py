@@ -1,0 +1,28 @@
+"""Multi-GPU sharding of a render: one process per GPU, disjoint contiguous stream
+ranges, one sum-reduce of the film (torch.distributed: NCCL over NVLink on GPUs, gloo in CPU tests).
+There is no other collective on this path."""
+import numpy as np
+
+
+def shard_range(n_streams, rank, world_size):
+    """Contiguous, balanced [first, first + count) range of `rank`."""
+    base, rem = divmod(int(n_streams), int(world_size))
+    first = rank * base + min(rank, rem)
+    return first, base + (1 if rank < rem else 0)
+
+
+def reduce_film(film, dst=0):
+    """Sum-reduces per-rank films (numpy array or torch tensor) onto `dst`; returns the reduced film on
+    `dst` and the local film elsewhere.  The W channel sums too, so normalisation stays exact."""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return film
+    if isinstance(film, np.ndarray):
+        t = torch.from_numpy(film)
+        if dist.get_backend() == "nccl":
+            t = t.cuda()
+        dist.reduce(t, dst=dst, op=dist.ReduceOp.SUM)
+        return t.cpu().numpy()
+    dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+    return film

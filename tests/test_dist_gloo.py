@@ -1,0 +1,51 @@
+"""world_size-2 gloo test of the sharding + film-reduce host logic (the N>1 path of bench.py), on CPU.
+The per-rank renderer here is the oracle (this is a test); on GPUs it is the CUDA path."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, %(root)r); sys.path.insert(0, os.path.join(%(root)r, "tests"))
+import numpy as np, torch.distributed as dist
+import scenes
+from oracle import oracle
+pkg = scenes.pkg
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+sc = pkg.load_dict(scenes.c2(spp=6, width=8, nz=50))
+total = 8 * 6
+first, count = pkg.shard_range(total, rank, world)
+r = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, first_stream=first, n_streams=count)
+film = pkg.reduce_film(r.film.astype(np.float64))
+if rank == 0:
+    np.save(os.path.join(%(out)r, "film.npy"), film)
+dist.destroy_process_group()
+'''
+
+
+def test_two_rank_sharded_render_matches_single(pkg, oracle, tmp_path):
+    import scenes
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER % {"root": ROOT, "out": str(tmp_path)})
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                           "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)], env=env, timeout=600)
+    film = np.load(tmp_path / "film.npy")
+    sc = pkg.load_dict(scenes.c2(spp=6, width=8, nz=50))
+    full = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT)
+    assert np.allclose(film, full.film, rtol=1e-5, atol=1e-7)
+    assert film[..., 4].sum() == 48
+
+
+def test_shard_range_partitions(pkg):
+    for n in (0, 1, 7, 48, 4194304):
+        for w in (1, 2, 3, 8):
+            r = [pkg.shard_range(n, k, w) for k in range(w)]
+            assert r[0][0] == 0 and sum(c for _, c in r) == n
+            assert all(r[i][0] + r[i][1] == r[i + 1][0] for i in range(w - 1))
+            assert max(c for _, c in r) - min(c for _, c in r) <= 1

@@ -104,3 +104,18 @@ def test_scene_update_matches_fresh_scene(pkg, oracle):
     assert sc2.desc.bsdfs[1].type == pkg.abi.BSDF_RPV
     ref = oracle.render(pkg, sc2, pkg.abi.SEED_WAVEFRONT, want_paths=True)
     assert np.array_equal(got.radiance, ref.radiance) and np.array_equal(got.state, ref.state)
+
+
+def test_cuda_matches_golden_fixtures(pkg):
+    """The CUDA path against the committed golden vectors (no oracle involved)."""
+    import json
+    import os
+    import make_golden
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden.json")))
+    for name, g in gold.items():
+        sc = pkg.load_dict(make_golden.CASES[name](g["variant"]), g["variant"])
+        r = pkg.render(sc, seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        assert [int(x) for x in r.state] == g["state"], name
+        assert r.counters.tolist() == g["counters"], name
+        bits = r.radiance.view(np.uint32 if r.radiance.dtype == np.float32 else np.uint64).ravel()
+        assert [int(x) for x in bits] == g["radiance_bits"], name
