@@ -8,6 +8,7 @@
 #include "bvh_build.h"
 #include "vp_kernels.cuh"
 #include "vp_wavefront.cuh"
+#include "vp_queue.cuh"
 
 #include <cstdlib>
 
@@ -574,28 +575,50 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
     out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
     size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
-    /* kernel selection: the wavefront kernel is the product; B2VP_KERNEL=mega selects the
-       one-thread-per-path twin (same results, kept as the correctness reference on the device) */
+    /* kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues
+       (vp_queue.cuh).  B2VP_KERNEL=lanes selects the register-resident warp-voting wavefront
+       (vp_wavefront.cuh), B2VP_KERNEL=mega the one-thread-per-path twin (vp_kernels.cuh): same results. */
     typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
-    Kern kern = volpath_wf_kernel<F, 2>;
+    Kern kern = volpath_q_kernel<F, 512>;
+    int threads = 512;
+    bool queue_kernel = true;
+    double oversub = 2.0;   /* path slots per thread */
     if (const char *e = std::getenv("B2VP_KERNEL")) {
-        if (!std::strcmp(e, "mega")) kern = volpath_kernel<F>;
-        else if (!std::strcmp(e, "wf1")) kern = volpath_wf_kernel<F, 1>;
-        else if (!std::strcmp(e, "wf3")) kern = volpath_wf_kernel<F, 3>;
-        else if (!std::strcmp(e, "wf4")) kern = volpath_wf_kernel<F, 4>;
+        if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
+        else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
+        else if (!std::strcmp(e, "q256")) { kern = volpath_q_kernel<F, 256>; threads = 256; }
+        else if (!std::strcmp(e, "q384")) { kern = volpath_q_kernel<F, 512>; threads = 384; }
+    }
+    if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= 512 && t % 32 == 0 && (threads == 512 || t <= 256)) threads = t; }
+    if (const char *e = std::getenv("B2VP_OVERSUB")) { double v = std::atof(e); if (v >= 1.0 && v <= 8.0) oversub = v; }
+    int per_sm = 0;
+    if (queue_kernel) {
+        /* shared memory: [tables][grids][film][queue control + stacks][path slots] */
+        size_t base = (smem + 127) & ~(size_t) 127;
+        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
+        size_t per_slot = sizeof(PathSlot<F>) + PH_N * sizeof(unsigned short);
+        size_t max_slots = (avail - sizeof(QueueCtl) - 64) / per_slot;
+        size_t n_slots = std::min<size_t>((size_t) (threads * oversub), max_slots) & ~(size_t) 31;
+        if (avail == 0 || n_slots < 64)
+            return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
+        n_slots = std::min<size_t>(n_slots, 32768);
+        out.q_ctl_offset = (uint32_t) base;
+        size_t qbytes = (sizeof(QueueCtl) + PH_N * n_slots * sizeof(unsigned short) + 15) & ~(size_t) 15;
+        out.q_slots_offset = (uint32_t) (base + qbytes);
+        out.q_n_slots = (uint32_t) n_slots;
+        smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
     }
     CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    int per_sm = 0;
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
     if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
-    uint64_t want = (count + 255) / 256;
+    uint64_t want = (count + threads - 1) / threads;
     int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
 
     if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     uint32_t launches = 0;
     CU_CHECK(cudaEventRecord(s->ev0, stream));
     if (count) {
-        kern<<<grid, 256, smem, stream>>>(ds.g, sp.d, out);
+        kern<<<grid, threads, smem, stream>>>(ds.g, sp.d, out);
         launches++;
     }
     CU_CHECK(cudaEventRecord(s->ev1, stream));

@@ -27,6 +27,8 @@ template <typename F> struct RenderOut {
     uint32_t film_in_smem;          /* CTA-private film accumulated in shared memory */
     uint32_t film_smem_offset;
     uint32_t grid_smem_offset;
+    /* queue kernel (vp_queue.cuh): path-slot pool and phase queues in shared memory */
+    uint32_t q_slots_offset, q_ctl_offset, q_n_slots;
 };
 
 struct StreamInfo {

@@ -84,7 +84,6 @@ template <typename F> struct PathSlot {
     F total_dist, ds_dist, emitter_val, nee_w, remaining;
     F mi_t, mi_mint, mi_p[3], mi_ss, mi_sn, mi_st, mi_comb; /* MediumInteraction carried from A to B */
     F acc0, acc3, acc4, posx, posy, ray_weight;
-    uint32_t pad_to_odd;                  /* odd word stride: consecutive slots fall in distinct banks */
 };
 
 struct QueueCtl {
@@ -141,3 +140,578 @@ VP_D void stream_pixel(const DStreams &sp, uint64_t k, int &px, int &py, int &bo
         box = sp.ox; boy = sp.oy; bsx = sp.w; bsy = sp.h;
     }
 }
+
+template <typename F, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
+volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStreams sp,
+                 const __grid_constant__ RenderOut<F> out) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    SceneView<F> sv;
+    stage_scene(g, out, smem, sv);
+
+    const DSensor<F> &sn = g.sensor;
+    const int W = sn.crop_size[0];
+    F *film = out.film_in_smem ? reinterpret_cast<F *>(smem + out.film_smem_offset) : out.film;
+    const uint32_t max_depth = g.max_depth, rr_depth = g.rr_depth;
+    const bool ltr = g.ltr != 0;
+    const F INF = inf_<F>();
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    PathSlot<F> *S = reinterpret_cast<PathSlot<F> *>(smem + out.q_slots_offset);
+    QueueCtl *ctl = reinterpret_cast<QueueCtl *>(smem + out.q_ctl_offset);
+    unsigned short *Q = reinterpret_cast<unsigned short *>(ctl + 1); /* [PH_N][P] stacks of slot ids */
+    const int P = (int) out.q_n_slots;
+
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        S[i].flags = Q_NEW;
+        Q[PH_END * P + i] = (unsigned short) i;
+    }
+    if (threadIdx.x == 0) {
+        ctl->lock = 0;
+        for (int p = 0; p < PH_N; ++p) ctl->count[p] = 0;
+        ctl->count[PH_END] = P;
+        ctl->n_live = P;
+    }
+    __syncthreads();
+
+    unsigned long long tot[TOT_N];
+#pragma unroll
+    for (int i = 0; i < TOT_N; ++i) tot[i] = 0;
+
+    int last_phase = PH_END;
+    for (;;) {
+        /* ---------------- pop a batch: prefer the phase run last, else the fullest queue ---------------- */
+        if (lane == 0) q_lock(&ctl->lock);
+        __syncwarp();
+        int phase = -1, n = 0, base = 0;
+        {
+            volatile int *cq = ctl->count;
+            int best = 0;
+#pragma unroll
+            for (int p = 0; p < PH_N; ++p) {
+                int c = cq[p];
+                if (c > best) { best = c; phase = p; }
+            }
+            int cl = cq[last_phase];
+            if (cl >= 32) { phase = last_phase; best = cl; }
+            n = best < 32 ? best : 32;
+            base = best - n;
+        }
+        int slot = -1;
+        if (phase >= 0 && lane < n) slot = Q[phase * P + base + lane];
+        __syncwarp();
+        int live = 0;
+        if (lane == 0) {
+            if (phase >= 0) ctl->count[phase] = base;
+            live = *((volatile int *) &ctl->n_live);
+            q_unlock(&ctl->lock);
+        }
+        live = __shfl_sync(FULL, live, 0);
+        if (phase < 0) {
+            if (live == 0) break;
+            __nanosleep(200);
+            continue;
+        }
+        last_phase = phase;
+        const bool has = slot >= 0;
+        PathSlot<F> &s = S[has ? slot : 0];
+        int state = Q_DEAD;
+        PathCounters cnt;
+        cnt.draws = 0; cnt.medium_steps = 0; cnt.n_null = 0; cnt.n_real = 0; cnt.n_intersect = 0; cnt.n_surface = 0;
+
+        if (phase == PH_STEP) {
+            /* ================================ STEP ================================ */
+            uint32_t fl = has ? s.flags : (uint32_t) Q_DEAD;
+            state = (int) (fl & QF_STATE);
+            const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
+            const bool main_mode = mode == QM_MAIN, nee = mode == QM_NEE;
+            Pcg32 rng;
+            Ray<F> r;
+            int med = -1;
+            F w = 0, hit_t = INF, remaining = 0;
+            MediumHit<F> mi;
+            mi.t = INF; mi.mint = 0; mi.p = mk3<F>(0, 0, 0); mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
+            r.o = mi.p; r.d = mi.p; r.d_rcp = mi.p; r.mint = 0; r.maxt = 0;
+            rng.state = 0; rng.inc = 1; rng.draws = 0;
+            if (has) {
+                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                ld_ray(s.cur, r);
+                med = s.cur.medium;
+                w = s.cur.w;
+                hit_t = s.cur.hit_t;
+            }
+            bool go = has && state == Q_STEP_A;
+            bool in_medium = (fl & QF_IN_MEDIUM) != 0;
+            bool march_end = false;   /* the march is over: restore the main context */
+            if (go) {
+                if (main_mode) {
+                    /* termination / Russian roulette (volpath.cpp:72-87) */
+                    F eta = s.eta;
+                    uint32_t depth = s.depth;
+                    bool active = w != 0;
+                    F q = min_(w * sqr(eta), (F) 0.95);
+                    bool perform_rr = depth > rr_depth;
+                    F rr_sample = rng.next(F(), active);
+                    active = active && (rr_sample < q || !perform_rr);
+                    if (perform_rr) w *= rcp_(q);
+                    if (!active || depth >= max_depth) { state = Q_PATH_END; go = false; }
+                } else if (nee) {
+                    remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
+                    r.maxt = remaining;
+                    s.remaining = remaining;
+                    if (!(remaining > 0)) { march_end = true; go = false; }
+                }
+            } else if (has && nee) {
+                remaining = s.remaining;
+            }
+            __syncwarp();
+            /* one free-flight sample for whichever ray this path is marching (medium.cpp:36-75) */
+            if (go) in_medium = med >= 0;
+            if (go && in_medium) {
+                const DMedium<F> &m = sv.media[med];
+                sample_interaction(sv, m, r, rng.next(F(), true), mi, cnt);
+                if (m.type == 0 && mi.valid())
+                    r.maxt = nee ? min_(mi.t, remaining) : mi.t;
+            }
+            __syncwarp();
+            if (go) {
+                if (fl & QF_NEEDS_ISECT) {
+                    /* park for Scene::ray_intersect; the free-flight sample waits in the slot */
+                    state = Q_ISECT;
+                    fl &= ~QF_ISECT_DL;
+                    s.mi_t = mi.t; s.mi_mint = mi.mint; st3(s.mi_p, mi.p);
+                    s.mi_ss = mi.sigma_s; s.mi_sn = mi.sigma_n; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
+                } else {
+                    state = Q_STEP_B;
+                }
+            } else if (has && state == Q_STEP_B) {
+                mi.t = s.mi_t; mi.mint = s.mi_mint; mi.p = ld3(s.mi_p);
+                mi.sigma_s = s.mi_ss; mi.sigma_n = s.mi_sn; mi.sigma_t = s.mi_st; mi.combined = s.mi_comb;
+            }
+            const bool do_b = has && state == Q_STEP_B;
+            /* common part of step B: surface-vs-collision ordering and the transmittance / pdf ratio
+               (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
+            bool spectral = false;
+            F ratio = 1;
+            if (do_b && in_medium) {
+                spectral = sv.media[med].spectral != 0;
+                if (hit_t < mi.t) mi.t = INF;
+                if (spectral) {
+                    F tt = min_(mi.t, hit_t);
+                    if (nee) tt = min_(remaining, tt);
+                    F t = tt - mi.mint;
+                    F tr = exp_(-t * mi.combined);
+                    bool surface_first = hit_t < mi.t || (nee && mi.t > remaining);
+                    F pdf = surface_first ? tr : tr * mi.combined;
+                    ratio = pdf > 0 ? tr / pdf : (F) 0;
+                }
+            }
+            __syncwarp();
+            if (do_b && main_mode) {
+                bool act_null = false, act_real = false, escaped = false;
+                uint32_t depth = s.depth;
+                if (in_medium) {
+                    if (spectral) w *= ratio;
+                    escaped = !mi.valid();
+                    const bool active_medium = mi.valid();
+                    F u = rng.next(F(), active_medium);
+                    bool null_scatter = u >= mi.sigma_t / mi.combined;
+                    act_null = null_scatter && active_medium;
+                    act_real = !act_null && active_medium;
+                    if (spectral && act_null) w *= mi.sigma_n * mi.combined / mi.sigma_n;
+                    if (act_real) { depth += 1; s.depth = depth; }
+                }
+                const bool active = depth < max_depth;
+                act_real = act_real && active;
+                if (act_null) { /* volpath.cpp:140-144 */
+                    cnt.n_null++;
+                    r.o = mi.p;
+                    r.mint = 0;
+                    hit_t = hit_t - mi.t;
+                    state = Q_STEP_A;
+                } else if (act_real) {
+                    /* the scattering event needs the interaction: leave it in the slot */
+                    st3(s.mi_p, mi.p);
+                    s.mi_ss = mi.sigma_s; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
+                    state = Q_SCATTER;
+                } else if ((!in_medium || escaped) && hit_t != INF) {
+                    state = Q_SURFACE;
+                } else {
+                    state = Q_PATH_END;
+                }
+            } else if (do_b) {
+                /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
+                bool escaped = false, active_medium = false;
+                F total_dist = nee ? s.total_dist : (F) 0;
+                if (in_medium) {
+                    if (spectral) w *= ratio;
+                    if (nee) {
+                        if (mi.t > remaining && mi.valid()) total_dist = s.ds_dist;
+                        if (mi.t > remaining) mi.t = INF;
+                    }
+                    escaped = !mi.valid();
+                    active_medium = mi.valid();
+                    if (active_medium) {
+                        if (nee) total_dist += mi.t;
+                        cnt.n_null++;
+                        r.o = mi.p;
+                        r.mint = 0;
+                        hit_t = hit_t - mi.t;
+                        if (spectral) w *= mi.sigma_n;
+                        else w *= mi.sigma_n / mi.combined;
+                    }
+                }
+                bool active_surface = !in_medium || escaped;
+                if (nee && active_surface) total_dist += hit_t;
+                active_surface = active_surface && hit_t != INF && !active_medium;
+                if (active_surface) {
+                    const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
+                    /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
+                    w *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
+                    r = spawn_ray(ld3(s.cur.hit_p), r.d);
+                    if (sh.interior >= 0 || sh.exterior >= 0)
+                        med = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
+                    fl |= QF_NEEDS_ISECT;
+                }
+                if (nee) { r.maxt = remaining; s.total_dist = total_dist; }
+                const bool active = (active_medium || active_surface) && w != 0;
+                if (active) state = Q_STEP_A;
+                else march_end = true;
+            }
+            if (has) {
+                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
+                fl = in_medium ? (fl | QF_IN_MEDIUM) : (fl & ~QF_IN_MEDIUM);
+                if (march_end) {
+                    /* end of a march: hand the result back and restore the main path's context */
+                    if (nee) s.result += s.nee_w * (w * s.emitter_val);
+                    /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
+                    copy_ctx(s.cur, s.saved);
+                    const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
+                    if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
+                    else if (cont == QC_SURF_B) state = Q_SURF_B;
+                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250) */
+                        s.cur.medium = s.medium_next;
+                        fl &= ~QF_NEEDS_ISECT;
+                        state = Q_STEP_A;
+                    }
+                    fl &= ~QF_MODE;
+                } else {
+                    st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
+                    if (!main_mode) { st3(s.cur.d_rcp, r.d_rcp); s.cur.medium = med; }
+                    s.cur.w = w;
+                    s.cur.hit_t = hit_t;
+                }
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        } else if (phase == PH_ISECT) {
+            /* ================================ ISECT =============================== */
+            if (has) {
+                uint32_t fl = s.flags;
+                const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
+                Ray<F> r;
+                ld_ray(s.cur, r);
+                SurfaceHit<F> h;
+                ray_intersect(sv, r, h, cnt);
+                s.c_isect += cnt.n_intersect;
+                s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
+                if (mode == QM_MAIN) { /* the main path keeps the whole SurfaceInteraction */
+                    st3(s.wi, h.wi); st3(s.sh_s, h.sh.s); st3(s.sh_t, h.sh.t); st3(s.sh_n, h.sh.n);
+                }
+                fl &= ~QF_NEEDS_ISECT;
+                if (fl & QF_ISECT_DL) {
+                    /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the
+                       new hit; the main path (same ray, new hit, throughput) waits in `saved` */
+                    copy_ctx(s.saved, s.cur);
+                    s.cur.w = 1;
+                    s.emitter_val = 0;
+                    fl = (fl & ~(QF_MODE | QF_CONT | QF_ISECT_DL)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
+                         ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
+                    state = Q_STEP_A;
+                } else {
+                    state = Q_STEP_B;
+                }
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        } else if (phase == PH_SCATTER) {
+            /* =============================== SCATTER ============================== */
+            if (has) {
+                uint32_t fl = s.flags;
+                state = (int) (fl & QF_STATE);
+                Pcg32 rng;
+                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                const int med = s.cur.medium;
+                const DMedium<F> &m = sv.media[med];
+                const V3<F> d = ld3(s.cur.d);
+                if (state == Q_SCATTER) { /* volpath.cpp:146-168 */
+                    s.c_real += 1;
+                    F throughput = s.cur.w;
+                    const V3<F> p = ld3(s.mi_p);
+                    if (m.spectral) throughput *= s.mi_ss * s.mi_comb / s.mi_st;
+                    else throughput *= s.mi_ss / s.mi_st;
+                    fl |= QF_VALID_RAY;
+                    s.cur.w = throughput;
+                    st3(s.cur.o, p); /* the old origin is dead: keep the scattering position here */
+                    state = Q_SCATTER_B;
+                    if (m.sample_emitters) { /* sample_emitter prologue (volpath.cpp:261-283) */
+                        F sx = rng.next(F(), true);
+                        (void) rng.next(F(), true);
+                        F ev;
+                        DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
+                        if (ds.pdf == 0) ev = 0;
+                        F nee_w = throughput * phase_eval(sv.phases[m.phase], -d, ds.d);
+                        if (ds.pdf != 0) {
+                            copy_ctx(s.saved, s.cur);
+                            Ray<F> r2 = spawn_ray(p, ds.d);
+                            r2.mint = 0;
+                            st_ray(s.cur, r2);
+                            s.cur.hit_t = INF; s.cur.hit_shape = -1;
+                            s.cur.w = 1;
+                            s.total_dist = 0; s.ds_dist = ds.dist; s.emitter_val = ev; s.nee_w = nee_w;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SCATTER_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
+                            state = Q_STEP_A;
+                        } else {
+                            s.result += nee_w * ev;
+                        }
+                    }
+                } else { /* Q_SCATTER_B: phase function sampling (volpath.cpp:170-176) */
+                    const DPhase<F> &phase_fn = sv.phases[m.phase];
+                    F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
+                    F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> wo = phase_sample(phase_fn, d, s2x, s2y);
+                    Ray<F> r = spawn_ray(ld3(s.cur.o), wo);
+                    r.mint = 0;
+                    st_ray(s.cur, r);
+                    fl |= QF_NEEDS_ISECT;
+                    state = Q_STEP_A;
+                }
+                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        } else if (phase == PH_SURFACE) {
+            /* =============================== SURFACE ============================== */
+            if (has) {
+                uint32_t fl = s.flags;
+                state = (int) (fl & QF_STATE);
+                Pcg32 rng;
+                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
+                const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
+                const V3<F> sp_ = ld3(s.cur.hit_p), wi = ld3(s.wi);
+                Frame<F> fr;
+                fr.s = ld3(s.sh_s); fr.t = ld3(s.sh_t); fr.n = ld3(s.sh_n);
+                F throughput = s.cur.w;
+                uint32_t depth = s.depth;
+                if (state == Q_SURFACE) { /* volpath.cpp:192-212 */
+                    s.c_surf += 1;
+                    bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
+                    state = Q_SURF_B;
+                    if (active_e) { /* sample_emitter prologue (volpath.cpp:261-283) */
+                        F sx = rng.next(F(), true);
+                        (void) rng.next(F(), true);
+                        F ev;
+                        DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
+                        if (ds.pdf == 0) ev = 0;
+                        V3<F> wo = fr.to_local(ds.d);
+                        F bsdf_val = bsdf_eval(bsdf, wi, wo);
+                        F bpdf = bsdf_pdf(bsdf, wi, wo);
+                        F pa = ds.pdf, pb = ds.delta ? (F) 0 : bpdf;
+                        pa *= pa; pb *= pb;
+                        F mis = pa > 0 ? pa / (pa + pb) : (F) 0; /* mis_weight (volpath.cpp:479-483) */
+                        F nee_w = throughput * bsdf_val * mis;
+                        if (ds.pdf != 0) {
+                            copy_ctx(s.saved, s.cur);
+                            Ray<F> r2 = spawn_ray(sp_, ds.d);
+                            st_ray(s.cur, r2);
+                            s.cur.hit_t = INF; s.cur.hit_shape = -1;
+                            s.cur.w = 1;
+                            s.total_dist = 0; s.ds_dist = ds.dist; s.emitter_val = ev; s.nee_w = nee_w;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SURF_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
+                            state = Q_STEP_A;
+                        } else {
+                            s.result += nee_w * ev;
+                        }
+                    }
+                } else { /* Q_SURF_B: BSDF sampling (volpath.cpp:214-241) */
+                    F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
+                    F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> bwo;
+                    F bs_pdf, bs_eta, bsdf_val;
+                    uint32_t sampled_type;
+                    bsdf_sample(bsdf, wi, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
+                    throughput *= bsdf_val;
+                    s.eta *= bs_eta;
+                    Ray<F> r = spawn_ray(sp_, fr.to_world(bwo));
+                    st_ray(s.cur, r);
+                    s.cur.w = throughput;
+                    fl |= QF_NEEDS_ISECT;
+                    bool non_null = !(sampled_type & BF_Null);
+                    if (non_null) { depth += 1; s.depth = depth; fl |= QF_VALID_RAY; }
+                    bool add_emitter = !(sampled_type & BF_Delta) && throughput != 0 && (depth < max_depth);
+                    /* medium switch (volpath.cpp:249-250), applied after the direct-light march */
+                    const int medium = s.cur.medium;
+                    const int medium_next = (sh.interior >= 0 || sh.exterior >= 0)
+                                                ? (dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior) : medium;
+                    if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
+                        s.medium_next = medium_next;
+                        fl |= QF_ISECT_DL;
+                        state = Q_ISECT;
+                    } else {
+                        s.cur.medium = medium_next;
+                        state = Q_STEP_A;
+                    }
+                }
+                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        } else {
+            /* ================================= END ================================ */
+            if (has) {
+                uint32_t fl = s.flags;
+                state = (int) (fl & QF_STATE);
+                const uint32_t n_samples = sp.samples_per_stream;
+                unsigned long long k = s.k;
+                uint32_t j = s.j;
+                int px = 0, py = 0, box = 0, boy = 0, bsx = 0, bsy = 0;
+                bool empty = true;
+                if (fl & QF_HAVE_STREAM) stream_pixel(sp, sp.first + k, px, py, box, boy, bsx, bsy, empty);
+                if (state == Q_PATH_END) {
+                    /* render_sample tail (integrator.cpp:267-287) + ImageBlock::put (imageblock.cpp:85-169) */
+                    F value = s.ray_weight * s.result;
+                    tot[TOT_PATHS]++;
+                    if (out.out_radiance) out.out_radiance[k * n_samples + j] = value;
+                    F alpha = (fl & QF_VALID_RAY) ? (F) 1 : (F) 0;
+                    bool ok = value >= (F) -1e-5f && finite_(value);
+                    if (!ok) {
+                        tot[TOT_INVALID]++;
+                    } else {
+                        F bx = s.posx - ((F) box + (F) 0.5), by = s.posy - ((F) boy + (F) 0.5);
+                        int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
+                        if (!(lx < 0 || ly < 0 || lx >= bsx || ly >= bsy)) {
+                            int fx = lx + box - sp.ox, fy = ly + boy - sp.oy;
+                            if (fx == px - sp.ox && fy == py - sp.oy) {
+                                s.acc0 += value; s.acc3 += alpha; s.acc4 += (F) 1;
+                                fl |= QF_ACC_USED;
+                            } else {
+                                F *p = film + ((size_t) fy * W + fx) * 5;
+                                film_add(p, value); film_add(p + 1, value); film_add(p + 2, value);
+                                film_add(p + 3, alpha); film_add(p + 4, (F) 1);
+                            }
+                        }
+                    }
+                    j++;
+                    state = Q_NEW;
+                }
+                /* Q_NEW */
+                if ((fl & QF_HAVE_STREAM) && (j >= n_samples || empty)) {
+                    /* stream finished: splat its accumulator, write the parity outputs */
+                    if (fl & QF_ACC_USED) {
+                        F *p = film + ((size_t) (py - sp.oy) * W + (px - sp.ox)) * 5;
+                        F a0 = s.acc0;
+                        film_add(p, a0); film_add(p + 1, a0); film_add(p + 2, a0);
+                        film_add(p + 3, s.acc3); film_add(p + 4, s.acc4);
+                    }
+                    if (out.out_state) out.out_state[k] = s.rng_state;
+                    if (out.out_counters) {
+                        PathCounters o;
+                        o.draws = s.rng_draws; o.medium_steps = s.c_steps; o.n_null = s.c_null; o.n_real = s.c_real;
+                        o.n_intersect = s.c_isect; o.n_surface = s.c_surf;
+                        out.out_counters[k] = o;
+                    }
+                    tot[TOT_DRAWS] += s.rng_draws; tot[TOT_STEPS] += s.c_steps; tot[TOT_NULL] += s.c_null;
+                    tot[TOT_REAL] += s.c_real; tot[TOT_ISECT] += s.c_isect; tot[TOT_SURF] += s.c_surf;
+                    fl &= ~(QF_HAVE_STREAM | QF_ACC_USED);
+                }
+                if (!(fl & QF_HAVE_STREAM)) {
+                    k = atomicAdd(out.work_counter, 1ull);
+                    if (k >= sp.count) {
+                        state = Q_DEAD;
+                    } else {
+                        StreamInfo st = make_stream(sp, sp.first + k);
+                        s.k = k;
+                        s.rng_state = st.state; s.rng_inc = st.inc; s.rng_draws = 0;
+                        s.c_steps = 0; s.c_null = 0; s.c_real = 0; s.c_isect = 0; s.c_surf = 0;
+                        s.acc0 = 0; s.acc3 = 0; s.acc4 = 0;
+                        j = 0;
+                        px = st.px; py = st.py; empty = st.empty;
+                        fl |= QF_HAVE_STREAM;
+                    }
+                }
+                s.j = j;
+                if (state == Q_NEW && (fl & QF_HAVE_STREAM) && !(j >= n_samples || empty)) {
+                    /* render_sample prologue (integrator.cpp:233-264); an empty stream (pixel outside its
+                       block) is finished on the next visit */
+                    Pcg32 rng;
+                    rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                    F posx = (F) (uint32_t) px + rng.next(F(), true);
+                    F posy = (F) (uint32_t) py + rng.next(F(), true);
+                    F apx = (F) 0.5, apy = (F) 0.5;
+                    if (sn.needs_aperture_sample) { apx = rng.next(F(), true); apy = rng.next(F(), true); }
+                    if (sn.has_shutter) (void) rng.next(F(), true);
+                    (void) rng.next(F(), true); /* wavelength sample (integrator.cpp:252) */
+                    F ax = (posx - (F) sn.crop_offset[0]) / (F) sn.crop_size[0];
+                    F ay = (posy - (F) sn.crop_offset[1]) / (F) sn.crop_size[1];
+                    Ray<F> ray;
+                    s.ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
+                    s.posx = posx; s.posy = posy;
+                    s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                    /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */
+                    st_ray(s.cur, ray);
+                    s.cur.hit_t = INF; s.cur.hit_shape = -1;
+                    s.cur.medium = sn.medium;
+                    s.cur.w = 1;
+                    s.result = 0; s.eta = 1; s.depth = 0;
+                    fl = (fl & ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_ISECT_DL | QF_IN_MEDIUM)) | QF_NEEDS_ISECT;
+                    state = Q_STEP_A;
+                }
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        }
+
+        /* ---------------- push every slot onto the queue of its next phase ---------------- */
+        const int dest = (has && state != Q_DEAD) ? phase_of(state) : -1;
+        unsigned m[PH_N];
+#pragma unroll
+        for (int p = 0; p < PH_N; ++p) m[p] = __ballot_sync(FULL, dest == p);
+        const unsigned dead = __ballot_sync(FULL, has && state == Q_DEAD);
+        if (lane == 0) q_lock(&ctl->lock);
+        __syncwarp();
+        {
+            volatile int *cq = ctl->count;
+#pragma unroll
+            for (int p = 0; p < PH_N; ++p) {
+                if (dest == p) Q[p * P + cq[p] + __popc(m[p] & lt_mask)] = (unsigned short) slot;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int p = 0; p < PH_N; ++p) ctl->count[p] += __popc(m[p]);
+            ctl->n_live -= __popc(dead);
+            q_unlock(&ctl->lock);
+        }
+    }
+
+    /* totals: warp reduce, one atomic per warp and counter */
+#pragma unroll
+    for (int i = 0; i < TOT_N; ++i) {
+        unsigned long long v = tot[i];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(FULL, v, o);
+        if (lane == 0 && v) atomicAdd(out.totals + i, v);
+    }
+    if (out.film_in_smem) {
+        __syncthreads();
+        const F *f = reinterpret_cast<const F *>(smem + out.film_smem_offset);
+        uint32_t n = (uint32_t) W * sn.crop_size[1] * 5;
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+            F v = f[i];
+            if (v != (F) 0) film_add(out.film + i, v);
+        }
+    }
+}
+
+} // namespace vp

@@ -37,9 +37,10 @@ def compare(pkg, oracle, sc, mode, **kw):
     return got
 
 
-@pytest.fixture(params=["wavefront", "mega", "wf1", "wf4"])
+@pytest.fixture(params=["queue", "q256", "lanes", "mega"])
 def kernel(request, monkeypatch):
-    """B2VP_KERNEL selects the device kernel: the wavefront product kernel (default and two other occupancy targets) or its one-thread-per-path twin.  All must give identical results."""
+    """B2VP_KERNEL selects the device kernel: the queue-based wavefront product kernel (two CTA sizes), the
+    register-resident warp-voting wavefront or its one-thread-per-path twin.  All must give identical results."""
     monkeypatch.setenv("B2VP_KERNEL", request.param)
     return request.param
 
@@ -47,8 +48,8 @@ def kernel(request, monkeypatch):
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_wavefront_seeding_bit_exact(pkg, oracle, case, variant, kernel):
-    if kernel in ("wf1", "wf4") and variant == "scalar_mono_double":
-        pytest.skip("occupancy variants are covered in fp32")
+    if kernel in ("q256", "lanes") and variant == "scalar_mono_double":
+        pytest.skip("variant covered in fp32")
     sc = pkg.load_dict(CASES[case](variant), variant)
     compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
 
