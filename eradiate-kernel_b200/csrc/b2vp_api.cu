@@ -596,16 +596,19 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         /* shared memory: [tables][grids][film][queue control + stacks][path slots] */
         size_t base = (smem + 127) & ~(size_t) 127;
         size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
-        size_t per_slot = sizeof(PathSlot<F>) + PH_N * sizeof(unsigned short);
-        size_t max_slots = (avail - sizeof(QueueCtl) - 64) / per_slot;
+        size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
+        size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
         size_t n_slots = std::min<size_t>((size_t) (threads * oversub), max_slots) & ~(size_t) 31;
-        if (avail == 0 || n_slots < 64)
+        if (n_slots < 64)
             return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
         n_slots = std::min<size_t>(n_slots, 32768);
+        size_t cap = 64;
+        while (cap < n_slots) cap *= 2;
         out.q_ctl_offset = (uint32_t) base;
-        size_t qbytes = (sizeof(QueueCtl) + PH_N * n_slots * sizeof(unsigned short) + 15) & ~(size_t) 15;
+        size_t qbytes = (sizeof(QueueCtl) + PH_N * cap * sizeof(unsigned short) + 15) & ~(size_t) 15;
         out.q_slots_offset = (uint32_t) (base + qbytes);
         out.q_n_slots = (uint32_t) n_slots;
+        out.q_ring_cap = (uint32_t) cap;
         smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
     }
     CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));

@@ -86,21 +86,15 @@ template <typename F> struct PathSlot {
     F acc0, acc3, acc4, posx, posy, ray_weight;
 };
 
+/* Lock-free phase queues: one ring of slot ids per phase.  A pusher reserves positions at `tail`, writes the
+   ids, then publishes them by raising `avail`; a popper first takes entries out of `avail` (compare-and-swap),
+   then reserves positions at `head` and waits for each id to appear (the pusher that reserved a position is
+   already writing it).  Entries are reset to Q_EMPTY when read, so a ring position is never read twice. */
 struct QueueCtl {
-    int lock;
-    int count[PH_N];
+    int head[PH_N], tail[PH_N], avail[PH_N];
     int n_live;
-    int pad;
 };
-
-VP_D void q_lock(int *lock) {
-    while (atomicCAS(lock, 0, 1) != 0) __nanosleep(20);
-    __threadfence_block();
-}
-VP_D void q_unlock(int *lock) {
-    __threadfence_block();
-    atomicExch(lock, 0);
-}
+#define Q_EMPTY 0xffffu
 
 template <typename F> VP_D void ld_ray(const MarchCtx<F> &c, Ray<F> &r) {
     r.o = ld3(c.o); r.d = ld3(c.d); r.d_rcp = ld3(c.d_rcp); r.mint = c.mint; r.maxt = c.maxt;
@@ -161,17 +155,20 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
     PathSlot<F> *S = reinterpret_cast<PathSlot<F> *>(smem + out.q_slots_offset);
     QueueCtl *ctl = reinterpret_cast<QueueCtl *>(smem + out.q_ctl_offset);
-    unsigned short *Q = reinterpret_cast<unsigned short *>(ctl + 1); /* [PH_N][P] stacks of slot ids */
+    unsigned short *Q = reinterpret_cast<unsigned short *>(ctl + 1); /* [PH_N][cap] rings of slot ids */
     const int P = (int) out.q_n_slots;
 
+    const int cap = (int) out.q_ring_cap, cap_mask = cap - 1;  /* power of two >= P */
+    for (int i = threadIdx.x; i < PH_N * cap; i += blockDim.x) Q[i] = (unsigned short) Q_EMPTY;
+    __syncthreads();
     for (int i = threadIdx.x; i < P; i += blockDim.x) {
         S[i].flags = Q_NEW;
-        Q[PH_END * P + i] = (unsigned short) i;
+        Q[PH_END * cap + i] = (unsigned short) i;
     }
     if (threadIdx.x == 0) {
-        ctl->lock = 0;
-        for (int p = 0; p < PH_N; ++p) ctl->count[p] = 0;
-        ctl->count[PH_END] = P;
+        for (int p = 0; p < PH_N; ++p) { ctl->head[p] = 0; ctl->tail[p] = 0; ctl->avail[p] = 0; }
+        ctl->tail[PH_END] = P;
+        ctl->avail[PH_END] = P;
         ctl->n_live = P;
     }
     __syncthreads();
@@ -183,37 +180,47 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     int last_phase = PH_END;
     for (;;) {
         /* ---------------- pop a batch: prefer the phase run last, else the fullest queue ---------------- */
-        if (lane == 0) q_lock(&ctl->lock);
-        __syncwarp();
-        int phase = -1, n = 0, base = 0;
-        {
-            volatile int *cq = ctl->count;
-            int best = 0;
-#pragma unroll
-            for (int p = 0; p < PH_N; ++p) {
-                int c = cq[p];
-                if (c > best) { best = c; phase = p; }
-            }
-            int cl = cq[last_phase];
-            if (cl >= 32) { phase = last_phase; best = cl; }
-            n = best < 32 ? best : 32;
-            base = best - n;
-        }
-        int slot = -1;
-        if (phase >= 0 && lane < n) slot = Q[phase * P + base + lane];
-        __syncwarp();
-        int live = 0;
+        int phase = -1, n = 0, h = 0, live = 1;
         if (lane == 0) {
-            if (phase >= 0) ctl->count[phase] = base;
+            volatile int *av = ctl->avail;
+            for (int attempt = 0; attempt < 8; ++attempt) {
+                int best = 0, ph = -1;
+#pragma unroll
+                for (int p = 0; p < PH_N; ++p) {
+                    int c = av[p];
+                    if (c > best) { best = c; ph = p; }
+                }
+                int cl = av[last_phase];
+                if (cl >= 32) { ph = last_phase; best = cl; }
+                if (ph < 0) break;
+                int take = best < 32 ? best : 32;
+                if (atomicCAS(&ctl->avail[ph], best, best - take) == best) {
+                    phase = ph; n = take;
+                    h = atomicAdd(&ctl->head[ph], take);
+                    break;
+                }
+            }
             live = *((volatile int *) &ctl->n_live);
-            q_unlock(&ctl->lock);
         }
+        phase = __shfl_sync(FULL, phase, 0);
+        n = __shfl_sync(FULL, n, 0);
+        h = __shfl_sync(FULL, h, 0);
         live = __shfl_sync(FULL, live, 0);
         if (phase < 0) {
             if (live == 0) break;
-            __nanosleep(200);
+            __nanosleep(100);
             continue;
         }
+        int slot = -1;
+        if (lane < n) {
+            volatile unsigned short *e = Q + phase * cap + ((h + lane) & cap_mask);
+            unsigned v;
+            while ((v = *e) == Q_EMPTY) { }
+            *e = (unsigned short) Q_EMPTY;
+            slot = (int) v;
+        }
+        __threadfence_block();
+        __syncwarp();
         last_phase = phase;
         const bool has = slot >= 0;
         PathSlot<F> &s = S[has ? slot : 0];
@@ -678,21 +685,26 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 #pragma unroll
         for (int p = 0; p < PH_N; ++p) m[p] = __ballot_sync(FULL, dest == p);
         const unsigned dead = __ballot_sync(FULL, has && state == Q_DEAD);
-        if (lane == 0) q_lock(&ctl->lock);
-        __syncwarp();
-        {
-            volatile int *cq = ctl->count;
+        __threadfence_block(); /* slot state before the id becomes visible */
 #pragma unroll
-            for (int p = 0; p < PH_N; ++p) {
-                if (dest == p) Q[p * P + cq[p] + __popc(m[p] & lt_mask)] = (unsigned short) slot;
+        for (int p = 0; p < PH_N; ++p) {
+            if (m[p] == 0) continue;
+            int t = 0;
+            if (lane == 0) t = atomicAdd(&ctl->tail[p], __popc(m[p]));
+            t = __shfl_sync(FULL, t, 0);
+            if (dest == p) {
+                volatile unsigned short *e = Q + p * cap + ((t + __popc(m[p] & lt_mask)) & cap_mask);
+                while (*e != Q_EMPTY) { }
+                *e = (unsigned short) slot;
             }
         }
+        __threadfence_block();
         __syncwarp();
         if (lane == 0) {
 #pragma unroll
-            for (int p = 0; p < PH_N; ++p) ctl->count[p] += __popc(m[p]);
-            ctl->n_live -= __popc(dead);
-            q_unlock(&ctl->lock);
+            for (int p = 0; p < PH_N; ++p)
+                if (m[p]) atomicAdd(&ctl->avail[p], __popc(m[p]));
+            if (dead) atomicSub(&ctl->n_live, __popc(dead));
         }
     }
 
