@@ -326,6 +326,28 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         }
     }
 
+    /* scene features: lets render() pick a kernel instance without code for unused features */
+    uint32_t ft = 0;
+    for (size_t i = 0; i < media.size(); ++i) {
+        const DMedium<F> &m = media[i];
+        if (m.type == B2VP_MEDIUM_HOMOGENEOUS) {
+            ft |= FT_HOMOG;
+            if (volumes[m.sigma_t].type == 1) ft |= FT_GRID_HOMOG;
+        } else {
+            ft |= FT_HETERO;
+        }
+        if (volumes[m.albedo].type == 1) ft |= FT_GRID_ALBEDO;
+    }
+    for (size_t i = 0; i < volumes.size(); ++i) {
+        const DVolume<F> &v = volumes[i];
+        if (v.type != 1) continue;
+        ft |= v.filter == B2VP_FILTER_TRILINEAR ? FT_TRILINEAR : FT_NEAREST;
+        if (v.wrap != B2VP_WRAP_CLAMP) ft |= FT_WRAP;
+        if (v.channels != 1) ft |= FT_CH3;
+        if (!(v.w2l[3] == 0 && v.w2l[7] == 0 && v.w2l[11] == 0 && v.w2l[15] == 1)) ft |= FT_PROJECTIVE;
+    }
+    g.features = ft;
+
     /* blob layout */
     uint32_t off = 0;
     auto place = [&](size_t bytes) { uint32_t o = off; off = align16(off + (uint32_t) bytes); return o; };
@@ -499,6 +521,21 @@ template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64
 
 inline uint32_t align128(uint32_t x) { return (x + 127u) & ~127u; }
 
+/* queue-kernel instances: the generic one and presets for the common scene classes */
+constexpr uint32_t PRE_HOMOG = FT_HOMOG;
+constexpr uint32_t PRE_HET = FT_HETERO | FT_TRILINEAR;
+constexpr uint32_t PRE_HET_ALB = FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO;
+
+template <typename F, int MAXT>
+void (*pick_queue_kernel(uint32_t ft, const char **name))(const DScene<F>, const DStreams, const RenderOut<F>) {
+    if (std::getenv("B2VP_GENERIC")) ft = FT_ALL;
+    if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return volpath_q_kernel<F, MAXT, PRE_HOMOG>; }
+    if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return volpath_q_kernel<F, MAXT, PRE_HET>; }
+    if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return volpath_q_kernel<F, MAXT, PRE_HET_ALB>; }
+    *name = "generic";
+    return volpath_q_kernel<F, MAXT, FT_ALL>;
+}
+
 template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
     CU_CHECK(cudaSetDevice(s->device));
     DeviceScene<F> &ds = dev_of<F>(s);
@@ -579,15 +616,16 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
        (vp_queue.cuh).  B2VP_KERNEL=lanes selects the register-resident warp-voting wavefront
        (vp_wavefront.cuh), B2VP_KERNEL=mega the one-thread-per-path twin (vp_kernels.cuh): same results. */
     typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
-    Kern kern = volpath_q_kernel<F, 512>;
+    const char *preset = "";
+    Kern kern = pick_queue_kernel<F, 512>(ds.g.features, &preset);
     int threads = 512;
     bool queue_kernel = true;
     double oversub = 2.0;   /* path slots per thread */
     if (const char *e = std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
-        else if (!std::strcmp(e, "q256")) { kern = volpath_q_kernel<F, 256>; threads = 256; }
-        else if (!std::strcmp(e, "q384")) { kern = volpath_q_kernel<F, 512>; threads = 384; }
+        else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(ds.g.features, &preset); threads = 256; }
+        else if (!std::strcmp(e, "q384")) { threads = 384; }
     }
     if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= 512 && t % 32 == 0 && (threads == 512 || t <= 256)) threads = t; }
     if (const char *e = std::getenv("B2VP_OVERSUB")) { double v = std::atof(e); if (v >= 1.0 && v <= 8.0) oversub = v; }

@@ -135,7 +135,7 @@ VP_D void stream_pixel(const DStreams &sp, uint64_t k, int &px, int &py, int &bo
     }
 }
 
-template <typename F, int MAXT>
+template <typename F, int MAXT, uint32_t FEAT>
 __global__ void __launch_bounds__(MAXT, 1)
 volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStreams sp,
                  const __grid_constant__ RenderOut<F> out) {
@@ -278,7 +278,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             if (go) in_medium = med >= 0;
             if (go && in_medium) {
                 const DMedium<F> &m = sv.media[med];
-                sample_interaction(sv, m, r, rng.next(F(), true), mi, cnt);
+                sample_interaction<F, FEAT>(sv, m, r, rng.next(F(), true), mi, cnt);
                 if (m.type == 0 && mi.valid())
                     r.maxt = nee ? min_(mi.t, remaining) : mi.t;
             }

@@ -278,23 +278,46 @@ VP_D int wrap_coord(int v, int res, int mode) {
 
 template <typename F> VP_D int floor2int(F x) { return (int) floor_(x); }
 
+/* Scene features a kernel instance is compiled for.  The generic instance (FT_ALL) handles everything;
+   the host picks the smallest preset that covers the scene (b2vp_api.cu) so that the tentative-collision
+   step -- the instruction-fetch-bound inner loop -- carries no code for features the scene does not use.
+   Every preset computes bit-identical results to FT_ALL on the scenes it accepts. */
+enum : uint32_t {
+    FT_HOMOG = 1u << 0,        /* a homogeneous medium is present                         */
+    FT_HETERO = 1u << 1,       /* a heterogeneous medium is present                       */
+    FT_GRID_ALBEDO = 1u << 2,  /* some medium's albedo is a grid                          */
+    FT_GRID_HOMOG = 1u << 3,   /* a homogeneous medium reads a grid volume                */
+    FT_NEAREST = 1u << 4,      /* a grid uses the nearest filter                          */
+    FT_TRILINEAR = 1u << 5,    /* a grid uses the trilinear filter                        */
+    FT_WRAP = 1u << 6,         /* a grid uses repeat / mirror wrapping                    */
+    FT_CH3 = 1u << 7,          /* a grid has 3 channels                                   */
+    FT_PROJECTIVE = 1u << 8,   /* a grid's world_to_local has a non-trivial last row      */
+    FT_ALL = 0x1ffu
+};
+
 /* GridVolumeImpl::eval (src/textures/grid3d.cpp:163-185,220-360) and
    ConstVolume::eval (src/textures/constant3d.cpp:31-37) */
-template <typename F> VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
-    if (v.type == 0)
+template <typename F, uint32_t FEAT, bool MAY_BE_GRID = true>
+VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
+    if (!MAY_BE_GRID || v.type == 0)
         return v.value;
-    V3<F> p = xf_point(v.w2l, p_world); /* grid3d.cpp:227: full 4x4 with the w divide */
-    const int nx = v.nx, ny = v.ny, nz = v.nz, ch = v.channels;
+    /* grid3d.cpp:227: full 4x4 with the w divide.  With a last row of (0,0,0,1) the divisor is exactly 1
+       and x / 1 == x, so the affine product gives the same bits. */
+    V3<F> p = (FEAT & FT_PROJECTIVE) ? xf_point(v.w2l, p_world) : xf_point_affine(v.w2l, p_world);
+    const int nx = v.nx, ny = v.ny, nz = v.nz;
+    const int ch = (FEAT & FT_CH3) ? v.channels : 1;
+    const int wrap = (FEAT & FT_WRAP) ? v.wrap : 2;
     const F *data = v.smem_offset >= 0 ? reinterpret_cast<const F *>(sv.grid_smem + v.smem_offset) : v.data;
     F res[3];
-    if (v.filter == 1) { /* trilinear, grid3d.cpp:271-341 */
+    const bool trilinear = (FEAT & FT_TRILINEAR) && (!(FEAT & FT_NEAREST) || v.filter == 1);
+    if (trilinear) { /* trilinear, grid3d.cpp:271-341 */
         p = mk3<F>(fma_(p.x, (F) nx, (F) -0.5), fma_(p.y, (F) ny, (F) -0.5), fma_(p.z, (F) nz, (F) -0.5));
         int ix = floor2int(p.x), iy = floor2int(p.y), iz = floor2int(p.z);
         F w1x = p.x - (F) ix, w1y = p.y - (F) iy, w1z = p.z - (F) iz;
         F w0x = (F) 1 - w1x, w0y = (F) 1 - w1y, w0z = (F) 1 - w1z;
-        int x0 = wrap_coord(ix, nx, v.wrap), x1 = wrap_coord(ix + 1, nx, v.wrap);
-        int y0 = wrap_coord(iy, ny, v.wrap), y1 = wrap_coord(iy + 1, ny, v.wrap);
-        int z0 = wrap_coord(iz, nz, v.wrap), z1 = wrap_coord(iz + 1, nz, v.wrap);
+        int x0 = wrap_coord(ix, nx, wrap), x1 = wrap_coord(ix + 1, nx, wrap);
+        int y0 = wrap_coord(iy, ny, wrap), y1 = wrap_coord(iy + 1, ny, wrap);
+        int z0 = wrap_coord(iz, nz, wrap), z1 = wrap_coord(iz + 1, nz, wrap);
         size_t r00 = ((size_t) z0 * ny + y0) * nx, r10 = ((size_t) z0 * ny + y1) * nx,
                r01 = ((size_t) z1 * ny + y0) * nx, r11 = ((size_t) z1 * ny + y1) * nx;
 #pragma unroll 1
@@ -310,8 +333,8 @@ template <typename F> VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F
         }
     } else { /* nearest, grid3d.cpp:342-356 */
         p = mk3<F>(p.x * (F) nx, p.y * (F) ny, p.z * (F) nz);
-        int x = wrap_coord(floor2int(p.x), nx, v.wrap), y = wrap_coord(floor2int(p.y), ny, v.wrap),
-            z = wrap_coord(floor2int(p.z), nz, v.wrap);
+        int x = wrap_coord(floor2int(p.x), nx, wrap), y = wrap_coord(floor2int(p.y), ny, wrap),
+            z = wrap_coord(floor2int(p.z), nz, wrap);
         size_t idx = (((size_t) z * ny + y) * nx + x) * ch;
 #pragma unroll 1
         for (int c = 0; c < ch; ++c) res[c] = data[idx + c];
@@ -333,15 +356,18 @@ template <typename F> struct MediumHit {
    HeterogeneousMedium / HomogeneousMedium (src/media/*.cpp).  The shading frame
    Frame3f(ray.d) and wi = -ray.d that the reference stores per step are pure
    functions of ray.d and are rebuilt where a scattering event needs them. */
-template <typename F>
+template <typename F, uint32_t FEAT = FT_ALL>
 VP_D void sample_interaction(const SceneView<F> &sv, const DMedium<F> &m, const Ray<F> &ray, F sample,
                              MediumHit<F> &mi, PathCounters &cnt) {
     cnt.medium_steps++;
+    /* a preset without FT_HOMOG / FT_HETERO knows the medium type at compile time */
+    const bool homog = (FEAT & FT_HOMOG) && (!(FEAT & FT_HETERO) || m.type == 0);
+    constexpr bool HGRID = (FEAT & FT_GRID_HOMOG) != 0;
     bool aabb_its;
     F mint, maxt;
-    if (m.type == 0) { /* homogeneous.cpp:51-54 */
+    if (homog) { /* homogeneous.cpp:51-54 */
         aabb_its = true; mint = 0; maxt = inf_<F>();
-    } else {           /* heterogeneous.cpp:50-53 */
+    } else {     /* heterogeneous.cpp:50-53 */
         aabb_its = bbox_ray_intersect(m.amin, m.amax, ray, mint, maxt);
     }
     aabb_its = aabb_its && (finite_(mint) || finite_(maxt));
@@ -350,8 +376,8 @@ VP_D void sample_interaction(const SceneView<F> &sv, const DMedium<F> &m, const 
     mint = max_(ray.mint, mint);
     maxt = min_(ray.maxt, maxt);
     F combined;
-    if (m.type == 0)
-        combined = volume_eval(sv, sv.volumes[m.sigma_t], ray.o) * m.scale; /* homogeneous.cpp:30-38 */
+    if (homog)
+        combined = volume_eval<F, FEAT, HGRID>(sv, sv.volumes[m.sigma_t], ray.o) * m.scale; /* homogeneous.cpp:30-38 */
     else
         combined = m.max_density;
     F sampled_t = mint + (-log_((F) 1 - sample) / combined);
@@ -361,13 +387,13 @@ VP_D void sample_interaction(const SceneView<F> &sv, const DMedium<F> &m, const 
     mi.mint = mint;
     mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0;
     if (valid_mi) {
-        F albedo = volume_eval(sv, sv.volumes[m.albedo], mi.p);
+        F albedo = volume_eval<F, FEAT, (FEAT & FT_GRID_ALBEDO) != 0>(sv, sv.volumes[m.albedo], mi.p);
         F sigmat;
-        if (m.type == 0) {
-            sigmat = volume_eval(sv, sv.volumes[m.sigma_t], mi.p) * m.scale;
+        if (homog) {
+            sigmat = volume_eval<F, FEAT, HGRID>(sv, sv.volumes[m.sigma_t], mi.p) * m.scale;
             mi.sigma_n = 0;
         } else {
-            sigmat = m.scale * volume_eval(sv, sv.volumes[m.sigma_t], mi.p);
+            sigmat = m.scale * volume_eval<F, FEAT, true>(sv, sv.volumes[m.sigma_t], mi.p);
             mi.sigma_n = combined - sigmat;
         }
         mi.sigma_t = sigmat;

@@ -281,6 +281,7 @@ template <typename F> struct DScene {
     uint32_t blob_bytes;
     uint32_t ofs_shapes, ofs_analytic, ofs_bsdfs, ofs_media, ofs_volumes, ofs_phases, ofs_emitters;
     uint32_t grid_smem_bytes;       /* total bytes of grids staged in shared memory */
+    uint32_t features;              /* FT_* bits the scene uses (vp_scene.cuh) */
 };
 
 /* stream space (integrator.cpp:51-231, sampler.cpp:83-96, spiral.cpp:8-72) */
