@@ -181,31 +181,24 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     for (;;) {
         /* ---------------- pop a batch: prefer the phase run last, else the fullest queue ---------------- */
         int phase = -1, n = 0, h = 0, live = 1;
-        if (lane == 0) {
-            volatile int *av = ctl->avail;
-            for (int attempt = 0; attempt < 8; ++attempt) {
-                int best = 0, ph = -1;
-#pragma unroll
-                for (int p = 0; p < PH_N; ++p) {
-                    int c = av[p];
-                    if (c > best) { best = c; ph = p; }
-                }
-                int cl = av[last_phase];
-                if (cl >= 32) { ph = last_phase; best = cl; }
-                if (ph < 0) break;
-                int take = best < 32 ? best : 32;
-                if (atomicCAS(&ctl->avail[ph], best, best - take) == best) {
-                    phase = ph; n = take;
-                    h = atomicAdd(&ctl->head[ph], take);
-                    break;
-                }
+        for (int attempt = 0; attempt < 4 && phase < 0; ++attempt) {
+            /* lanes 0..4 look at one queue each; a max-reduction picks the fullest (or the sticky one) */
+            const int c = lane < PH_N ? ((volatile int *) ctl->avail)[lane] : 0;
+            int key = lane < PH_N ? ((c << 3) | lane) : 0;
+            if (lane == last_phase && c >= 32) key |= 1 << 29;
+            const int top = __reduce_max_sync(FULL, key);
+            const int ph = top & 7, cnt = (top & ~(1 << 29)) >> 3;
+            if (cnt == 0) break;
+            const int take = cnt < 32 ? cnt : 32;
+            int ok = 0;
+            if (lane == 0 && atomicCAS(&ctl->avail[ph], cnt, cnt - take) == cnt) {
+                ok = 1;
+                h = atomicAdd(&ctl->head[ph], take);
             }
-            live = *((volatile int *) &ctl->n_live);
+            ok = __shfl_sync(FULL, ok, 0);
+            if (ok) { phase = ph; n = take; h = __shfl_sync(FULL, h, 0); }
         }
-        phase = __shfl_sync(FULL, phase, 0);
-        n = __shfl_sync(FULL, n, 0);
-        h = __shfl_sync(FULL, h, 0);
-        live = __shfl_sync(FULL, live, 0);
+        if (phase < 0) live = *((volatile int *) &ctl->n_live);
         if (phase < 0) {
             if (live == 0) break;
             __nanosleep(100);
@@ -681,31 +674,22 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
         /* ---------------- push every slot onto the queue of its next phase ---------------- */
         const int dest = (has && state != Q_DEAD) ? phase_of(state) : -1;
-        unsigned m[PH_N];
-#pragma unroll
-        for (int p = 0; p < PH_N; ++p) m[p] = __ballot_sync(FULL, dest == p);
+        const unsigned peers = __match_any_sync(FULL, dest);      /* lanes going to the same queue */
+        const int leader = __ffs(peers) - 1;
         const unsigned dead = __ballot_sync(FULL, has && state == Q_DEAD);
         __threadfence_block(); /* slot state before the id becomes visible */
-#pragma unroll
-        for (int p = 0; p < PH_N; ++p) {
-            if (m[p] == 0) continue;
-            int t = 0;
-            if (lane == 0) t = atomicAdd(&ctl->tail[p], __popc(m[p]));
-            t = __shfl_sync(FULL, t, 0);
-            if (dest == p) {
-                volatile unsigned short *e = Q + p * cap + ((t + __popc(m[p] & lt_mask)) & cap_mask);
-                while (*e != Q_EMPTY) { }
-                *e = (unsigned short) slot;
-            }
+        int t = 0;
+        if (lane == leader && dest >= 0) t = atomicAdd(&ctl->tail[dest], __popc(peers));
+        t = __shfl_sync(FULL, t, leader);
+        if (dest >= 0) {
+            volatile unsigned short *e = Q + dest * cap + ((t + __popc(peers & lt_mask)) & cap_mask);
+            while (*e != Q_EMPTY) { }
+            *e = (unsigned short) slot;
         }
         __threadfence_block();
         __syncwarp();
-        if (lane == 0) {
-#pragma unroll
-            for (int p = 0; p < PH_N; ++p)
-                if (m[p]) atomicAdd(&ctl->avail[p], __popc(m[p]));
-            if (dead) atomicSub(&ctl->n_live, __popc(dead));
-        }
+        if (lane == leader && dest >= 0) atomicAdd(&ctl->avail[dest], __popc(peers));
+        if (lane == 0 && dead) atomicSub(&ctl->n_live, __popc(dead));
     }
 
     /* totals: warp reduce, one atomic per warp and counter */
