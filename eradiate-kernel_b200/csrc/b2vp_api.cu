@@ -100,7 +100,7 @@ struct b2vp_scene {
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf;
-    DevBuf ex_state, ex_inc, ex_pixel, o_state, o_counters, o_radiance;
+    DevBuf ex_state, ex_inc, ex_pixel, o_state, o_counters, o_radiance, q_cold;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -620,7 +620,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     Kern kern = pick_queue_kernel<F, 512>(ds.g.features, &preset);
     int threads = 512;
     bool queue_kernel = true;
-    double oversub = 2.0;   /* path slots per thread */
+    double oversub = 2.4;   /* path slots per thread (capped by the shared memory left) */
     if (const char *e = std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
@@ -654,6 +654,12 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
     uint64_t want = (count + threads - 1) / threads;
     int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+    if (queue_kernel) {
+        /* cold per-path state: one PathCold array per CTA in global memory (L2-resident) */
+        const size_t cold_bytes = (size_t) grid * out.q_n_slots * sizeof(PathCold<F>);
+        if (s->q_cold.bytes < cold_bytes) CU_CHECK(s->q_cold.alloc(cold_bytes));
+        out.q_cold = s->q_cold.p;
+    }
 
     if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     uint32_t launches = 0;

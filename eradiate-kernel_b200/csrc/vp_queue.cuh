@@ -71,18 +71,30 @@ template <typename F> struct MarchCtx {
     F w;                                  /* throughput / transmittance             */
 };
 
+/* Per-path state is split by how often it is touched.  PathSlot (shared memory) holds what the
+   tentative-collision step reads and writes every iteration; PathCold (global memory, L2-resident, one
+   array per CTA) holds what only the rarer phases need.  The smaller the shared-memory slot, the more paths
+   a CTA keeps in flight and the fuller its batches. */
 template <typename F> struct PathSlot {
-    unsigned long long rng_state, rng_inc, k;
-    uint32_t rng_draws, j;
-    uint32_t c_steps, c_null, c_real, c_isect, c_surf;
+    unsigned long long rng_state, rng_inc;
+    uint32_t rng_draws;
+    uint32_t c_steps, c_null;
     uint32_t flags;
-    MarchCtx<F> cur, saved;
-    F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* shading frame of the main path's hit   */
-    F result, eta;
+    MarchCtx<F> cur;
+    F eta;
     uint32_t depth;
-    int medium_next;
-    F total_dist, ds_dist, emitter_val, nee_w, remaining;
+    F total_dist, ds_dist, remaining;
     F mi_t, mi_mint, mi_p[3], mi_ss, mi_sn, mi_st, mi_comb; /* MediumInteraction carried from A to B */
+};
+template <typename F> struct PathCold {
+    unsigned long long k;
+    uint32_t j;
+    uint32_t c_real, c_isect, c_surf;
+    MarchCtx<F> saved;                    /* the main path's context during a march */
+    F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* shading frame of the main path's hit   */
+    F result;
+    int medium_next;
+    F emitter_val, nee_w;
     F acc0, acc3, acc4, posx, posy, ray_weight;
 };
 
@@ -154,6 +166,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     const unsigned lt_mask = (1u << lane) - 1u;
 
     PathSlot<F> *S = reinterpret_cast<PathSlot<F> *>(smem + out.q_slots_offset);
+    PathCold<F> *C = reinterpret_cast<PathCold<F> *>(out.q_cold) + (size_t) blockIdx.x * out.q_n_slots;
     QueueCtl *ctl = reinterpret_cast<QueueCtl *>(smem + out.q_ctl_offset);
     unsigned short *Q = reinterpret_cast<unsigned short *>(ctl + 1); /* [PH_N][cap] rings of slot ids */
     const int P = (int) out.q_n_slots;
@@ -217,6 +230,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
         last_phase = phase;
         const bool has = slot >= 0;
         PathSlot<F> &s = S[has ? slot : 0];
+        PathCold<F> &c = C[has ? slot : 0];
         int state = Q_DEAD;
         PathCounters cnt;
         cnt.draws = 0; cnt.medium_steps = 0; cnt.n_null = 0; cnt.n_real = 0; cnt.n_intersect = 0; cnt.n_surface = 0;
@@ -386,14 +400,14 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 fl = in_medium ? (fl | QF_IN_MEDIUM) : (fl & ~QF_IN_MEDIUM);
                 if (march_end) {
                     /* end of a march: hand the result back and restore the main path's context */
-                    if (nee) s.result += s.nee_w * (w * s.emitter_val);
+                    if (nee) c.result += c.nee_w * (w * c.emitter_val);
                     /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
-                    copy_ctx(s.cur, s.saved);
+                    copy_ctx(s.cur, c.saved);
                     const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
                     if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
                     else if (cont == QC_SURF_B) state = Q_SURF_B;
                     else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250) */
-                        s.cur.medium = s.medium_next;
+                        s.cur.medium = c.medium_next;
                         fl &= ~QF_NEEDS_ISECT;
                         state = Q_STEP_A;
                     }
@@ -415,18 +429,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 ld_ray(s.cur, r);
                 SurfaceHit<F> h;
                 ray_intersect(sv, r, h, cnt);
-                s.c_isect += cnt.n_intersect;
+                c.c_isect += cnt.n_intersect;
                 s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
                 if (mode == QM_MAIN) { /* the main path keeps the whole SurfaceInteraction */
-                    st3(s.wi, h.wi); st3(s.sh_s, h.sh.s); st3(s.sh_t, h.sh.t); st3(s.sh_n, h.sh.n);
+                    st3(c.wi, h.wi); st3(c.sh_s, h.sh.s); st3(c.sh_t, h.sh.t); st3(c.sh_n, h.sh.n);
                 }
                 fl &= ~QF_NEEDS_ISECT;
                 if (fl & QF_ISECT_DL) {
                     /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the
                        new hit; the main path (same ray, new hit, throughput) waits in `saved` */
-                    copy_ctx(s.saved, s.cur);
+                    copy_ctx(c.saved, s.cur);
                     s.cur.w = 1;
-                    s.emitter_val = 0;
+                    c.emitter_val = 0;
                     fl = (fl & ~(QF_MODE | QF_CONT | QF_ISECT_DL)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
                          ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
                     state = Q_STEP_A;
@@ -446,7 +460,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 const DMedium<F> &m = sv.media[med];
                 const V3<F> d = ld3(s.cur.d);
                 if (state == Q_SCATTER) { /* volpath.cpp:146-168 */
-                    s.c_real += 1;
+                    c.c_real += 1;
                     F throughput = s.cur.w;
                     const V3<F> p = ld3(s.mi_p);
                     if (m.spectral) throughput *= s.mi_ss * s.mi_comb / s.mi_st;
@@ -463,18 +477,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         if (ds.pdf == 0) ev = 0;
                         F nee_w = throughput * phase_eval(sv.phases[m.phase], -d, ds.d);
                         if (ds.pdf != 0) {
-                            copy_ctx(s.saved, s.cur);
+                            copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(p, ds.d);
                             r2.mint = 0;
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
-                            s.total_dist = 0; s.ds_dist = ds.dist; s.emitter_val = ev; s.nee_w = nee_w;
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
                             fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
                                  ((uint32_t) QC_SCATTER_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
                             state = Q_STEP_A;
                         } else {
-                            s.result += nee_w * ev;
+                            c.result += nee_w * ev;
                         }
                     }
                 } else { /* Q_SCATTER_B: phase function sampling (volpath.cpp:170-176) */
@@ -500,13 +514,13 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
                 const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
                 const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
-                const V3<F> sp_ = ld3(s.cur.hit_p), wi = ld3(s.wi);
+                const V3<F> sp_ = ld3(s.cur.hit_p), wi = ld3(c.wi);
                 Frame<F> fr;
-                fr.s = ld3(s.sh_s); fr.t = ld3(s.sh_t); fr.n = ld3(s.sh_n);
+                fr.s = ld3(c.sh_s); fr.t = ld3(c.sh_t); fr.n = ld3(c.sh_n);
                 F throughput = s.cur.w;
                 uint32_t depth = s.depth;
                 if (state == Q_SURFACE) { /* volpath.cpp:192-212 */
-                    s.c_surf += 1;
+                    c.c_surf += 1;
                     bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
                     state = Q_SURF_B;
                     if (active_e) { /* sample_emitter prologue (volpath.cpp:261-283) */
@@ -523,17 +537,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         F mis = pa > 0 ? pa / (pa + pb) : (F) 0; /* mis_weight (volpath.cpp:479-483) */
                         F nee_w = throughput * bsdf_val * mis;
                         if (ds.pdf != 0) {
-                            copy_ctx(s.saved, s.cur);
+                            copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(sp_, ds.d);
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
-                            s.total_dist = 0; s.ds_dist = ds.dist; s.emitter_val = ev; s.nee_w = nee_w;
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
                             fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
                                  ((uint32_t) QC_SURF_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
                             state = Q_STEP_A;
                         } else {
-                            s.result += nee_w * ev;
+                            c.result += nee_w * ev;
                         }
                     }
                 } else { /* Q_SURF_B: BSDF sampling (volpath.cpp:214-241) */
@@ -557,7 +571,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     const int medium_next = (sh.interior >= 0 || sh.exterior >= 0)
                                                 ? (dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior) : medium;
                     if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
-                        s.medium_next = medium_next;
+                        c.medium_next = medium_next;
                         fl |= QF_ISECT_DL;
                         state = Q_ISECT;
                     } else {
@@ -574,14 +588,14 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 uint32_t fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 const uint32_t n_samples = sp.samples_per_stream;
-                unsigned long long k = s.k;
-                uint32_t j = s.j;
+                unsigned long long k = c.k;
+                uint32_t j = c.j;
                 int px = 0, py = 0, box = 0, boy = 0, bsx = 0, bsy = 0;
                 bool empty = true;
                 if (fl & QF_HAVE_STREAM) stream_pixel(sp, sp.first + k, px, py, box, boy, bsx, bsy, empty);
                 if (state == Q_PATH_END) {
                     /* render_sample tail (integrator.cpp:267-287) + ImageBlock::put (imageblock.cpp:85-169) */
-                    F value = s.ray_weight * s.result;
+                    F value = c.ray_weight * c.result;
                     tot[TOT_PATHS]++;
                     if (out.out_radiance) out.out_radiance[k * n_samples + j] = value;
                     F alpha = (fl & QF_VALID_RAY) ? (F) 1 : (F) 0;
@@ -589,12 +603,12 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     if (!ok) {
                         tot[TOT_INVALID]++;
                     } else {
-                        F bx = s.posx - ((F) box + (F) 0.5), by = s.posy - ((F) boy + (F) 0.5);
+                        F bx = c.posx - ((F) box + (F) 0.5), by = c.posy - ((F) boy + (F) 0.5);
                         int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
                         if (!(lx < 0 || ly < 0 || lx >= bsx || ly >= bsy)) {
                             int fx = lx + box - sp.ox, fy = ly + boy - sp.oy;
                             if (fx == px - sp.ox && fy == py - sp.oy) {
-                                s.acc0 += value; s.acc3 += alpha; s.acc4 += (F) 1;
+                                c.acc0 += value; c.acc3 += alpha; c.acc4 += (F) 1;
                                 fl |= QF_ACC_USED;
                             } else {
                                 F *p = film + ((size_t) fy * W + fx) * 5;
@@ -611,19 +625,19 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     /* stream finished: splat its accumulator, write the parity outputs */
                     if (fl & QF_ACC_USED) {
                         F *p = film + ((size_t) (py - sp.oy) * W + (px - sp.ox)) * 5;
-                        F a0 = s.acc0;
+                        F a0 = c.acc0;
                         film_add(p, a0); film_add(p + 1, a0); film_add(p + 2, a0);
-                        film_add(p + 3, s.acc3); film_add(p + 4, s.acc4);
+                        film_add(p + 3, c.acc3); film_add(p + 4, c.acc4);
                     }
                     if (out.out_state) out.out_state[k] = s.rng_state;
                     if (out.out_counters) {
                         PathCounters o;
-                        o.draws = s.rng_draws; o.medium_steps = s.c_steps; o.n_null = s.c_null; o.n_real = s.c_real;
-                        o.n_intersect = s.c_isect; o.n_surface = s.c_surf;
+                        o.draws = s.rng_draws; o.medium_steps = s.c_steps; o.n_null = s.c_null; o.n_real = c.c_real;
+                        o.n_intersect = c.c_isect; o.n_surface = c.c_surf;
                         out.out_counters[k] = o;
                     }
                     tot[TOT_DRAWS] += s.rng_draws; tot[TOT_STEPS] += s.c_steps; tot[TOT_NULL] += s.c_null;
-                    tot[TOT_REAL] += s.c_real; tot[TOT_ISECT] += s.c_isect; tot[TOT_SURF] += s.c_surf;
+                    tot[TOT_REAL] += c.c_real; tot[TOT_ISECT] += c.c_isect; tot[TOT_SURF] += c.c_surf;
                     fl &= ~(QF_HAVE_STREAM | QF_ACC_USED);
                 }
                 if (!(fl & QF_HAVE_STREAM)) {
@@ -632,16 +646,16 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         state = Q_DEAD;
                     } else {
                         StreamInfo st = make_stream(sp, sp.first + k);
-                        s.k = k;
+                        c.k = k;
                         s.rng_state = st.state; s.rng_inc = st.inc; s.rng_draws = 0;
-                        s.c_steps = 0; s.c_null = 0; s.c_real = 0; s.c_isect = 0; s.c_surf = 0;
-                        s.acc0 = 0; s.acc3 = 0; s.acc4 = 0;
+                        s.c_steps = 0; s.c_null = 0; c.c_real = 0; c.c_isect = 0; c.c_surf = 0;
+                        c.acc0 = 0; c.acc3 = 0; c.acc4 = 0;
                         j = 0;
                         px = st.px; py = st.py; empty = st.empty;
                         fl |= QF_HAVE_STREAM;
                     }
                 }
-                s.j = j;
+                c.j = j;
                 if (state == Q_NEW && (fl & QF_HAVE_STREAM) && !(j >= n_samples || empty)) {
                     /* render_sample prologue (integrator.cpp:233-264); an empty stream (pixel outside its
                        block) is finished on the next visit */
@@ -656,15 +670,15 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F ax = (posx - (F) sn.crop_offset[0]) / (F) sn.crop_size[0];
                     F ay = (posy - (F) sn.crop_offset[1]) / (F) sn.crop_size[1];
                     Ray<F> ray;
-                    s.ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
-                    s.posx = posx; s.posy = posy;
+                    c.ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
+                    c.posx = posx; c.posy = posy;
                     s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                     /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */
                     st_ray(s.cur, ray);
                     s.cur.hit_t = INF; s.cur.hit_shape = -1;
                     s.cur.medium = sn.medium;
                     s.cur.w = 1;
-                    s.result = 0; s.eta = 1; s.depth = 0;
+                    c.result = 0; s.eta = 1; s.depth = 0;
                     fl = (fl & ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_ISECT_DL | QF_IN_MEDIUM)) | QF_NEEDS_ISECT;
                     state = Q_STEP_A;
                 }
