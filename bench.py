@@ -232,7 +232,7 @@ def run_ours(args):
     e2e_val = paths_per_step / (float(e2e_t.item()) * 1e-3) / 1e6
 
     if rank == 0:
-        # ---- roofline of the dominant kernel (volpath_kernel<float>): FP32 issue bound on this workload
+        # ---- roofline of the dominant kernel (the queue kernel, vp_queue.cuh): FP32 issue bound on this workload
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -243,9 +243,19 @@ def run_ours(args):
         k_ms = sum(kern_ms) / len(kern_ms)
         flops = tot_last.n_medium_steps * FLOP_PER_SEGMENT
         achieved = flops / (k_ms * 1e-3) / 1e12
+        # DRAM traffic of one launch of this kernel on this workload, from the committed `ncu --set full`
+        # capture (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); None if the
+        # capture is for another spp
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            if int(tr.get("spp", -1)) == args.spp:
+                traffic = tr["dram_bytes_per_launch"]
+        except (OSError, ValueError, KeyError):
+            pass
         roofline = {"bound": "fp32", "achieved": achieved, "peak": fp32.value, "unit": "TFLOP/s",
-                    "frac": achieved / fp32.value if fp32.value else None, "traffic": None,
-                    "kernel": "vp::volpath_kernel<float>", "kernel_ms": k_ms,
+                    "frac": achieved / fp32.value if fp32.value else None, "traffic": traffic,
+                    "kernel": "vp::volpath_q_kernel<float, 512, FT_HETERO|FT_TRILINEAR>", "kernel_ms": k_ms,
                     "algorithmic": "%d medium steps x %d flop" % (tot_last.n_medium_steps, FLOP_PER_SEGMENT),
                     "peak_source": "b2vp_measure_fp32_peak (FMA microbenchmark, measured in this run); "
                                    "HBM peak %s GB/s (MEASURED_PEAKS.json) is not the bound here: the grid "
