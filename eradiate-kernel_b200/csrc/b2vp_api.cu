@@ -647,6 +647,9 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         out.q_slots_offset = (uint32_t) (base + qbytes);
         out.q_n_slots = (uint32_t) n_slots;
         out.q_ring_cap = (uint32_t) cap;
+        out.q_stay_min = 20; out.q_max_iter = 8;
+        if (const char *e = std::getenv("B2VP_STAY")) { int v = std::atoi(e); if (v >= 1 && v <= 33) out.q_stay_min = (uint32_t) v; }
+        if (const char *e = std::getenv("B2VP_ITER")) { int v = std::atoi(e); if (v >= 1 && v <= 1024) out.q_max_iter = (uint32_t) v; }
         smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
     }
     CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));

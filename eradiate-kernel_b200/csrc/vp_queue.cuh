@@ -39,17 +39,19 @@ enum QState : int {
     Q_SCATTER_B,    /* phase function sampling                                 */
     Q_SURFACE,      /* surface hit: start emitter march                        */
     Q_SURF_B,       /* BSDF sampling, second intersection                      */
+    Q_MARCH_SURF,   /* a march crosses a surface (null-BSDF boundary or blocker) */
+    Q_MARCH_END,    /* a march is over: hand back its result, restore the path */
     Q_PATH_END,
     Q_NEW,          /* next sample of the stream / next stream                 */
     Q_DEAD
 };
-enum QPhase : int { PH_STEP = 0, PH_ISECT, PH_SCATTER, PH_SURFACE, PH_END, PH_N };
+enum QPhase : int { PH_STEP = 0, PH_ISECT, PH_SCATTER, PH_SURFACE, PH_MARCH, PH_END, PH_N };
 enum QMode : int { QM_MAIN = 0, QM_NEE = 1, QM_DL = 2 };
 enum QCont : int { QC_STEP_B = 0, QC_SCATTER_B, QC_SURF_B, QC_START_DL, QC_AFTER_DL };
 
 VP_D int phase_of(int state) {
     return state <= Q_STEP_B ? PH_STEP : state == Q_ISECT ? PH_ISECT : state <= Q_SCATTER_B ? PH_SCATTER
-           : state <= Q_SURF_B ? PH_SURFACE : PH_END;
+           : state <= Q_SURF_B ? PH_SURFACE : state <= Q_MARCH_END ? PH_MARCH : PH_END;
 }
 
 /* flag word of a slot */
@@ -237,8 +239,13 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
         if (phase == PH_STEP) {
             /* ================================ STEP ================================ */
-            uint32_t fl = has ? s.flags : (uint32_t) Q_DEAD;
-            state = (int) (fl & QF_STATE);
+            /* A warp keeps its batch for several steps while most of its lanes stay in this phase (null
+               collisions come in runs): the pop / push cost is paid once per run, not once per step. */
+            bool mine = has;
+            for (int it = 1;; ++it) {
+            cnt.medium_steps = 0; cnt.n_null = 0;
+            uint32_t fl = mine ? s.flags : (uint32_t) Q_DEAD;
+            int st = (int) (fl & QF_STATE);
             const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
             const bool main_mode = mode == QM_MAIN, nee = mode == QM_NEE;
             Pcg32 rng;
@@ -249,16 +256,15 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             mi.t = INF; mi.mint = 0; mi.p = mk3<F>(0, 0, 0); mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
             r.o = mi.p; r.d = mi.p; r.d_rcp = mi.p; r.mint = 0; r.maxt = 0;
             rng.state = 0; rng.inc = 1; rng.draws = 0;
-            if (has) {
+            if (mine) {
                 rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
                 ld_ray(s.cur, r);
                 med = s.cur.medium;
                 w = s.cur.w;
                 hit_t = s.cur.hit_t;
             }
-            bool go = has && state == Q_STEP_A;
+            bool go = mine && st == Q_STEP_A;
             bool in_medium = (fl & QF_IN_MEDIUM) != 0;
-            bool march_end = false;   /* the march is over: restore the main context */
             if (go) {
                 if (main_mode) {
                     /* termination / Russian roulette (volpath.cpp:72-87) */
@@ -270,14 +276,14 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F rr_sample = rng.next(F(), active);
                     active = active && (rr_sample < q || !perform_rr);
                     if (perform_rr) w *= rcp_(q);
-                    if (!active || depth >= max_depth) { state = Q_PATH_END; go = false; }
+                    if (!active || depth >= max_depth) { st = Q_PATH_END; go = false; }
                 } else if (nee) {
                     remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
                     r.maxt = remaining;
                     s.remaining = remaining;
-                    if (!(remaining > 0)) { march_end = true; go = false; }
+                    if (!(remaining > 0)) { st = Q_MARCH_END; go = false; }
                 }
-            } else if (has && nee) {
+            } else if (mine && nee) {
                 remaining = s.remaining;
             }
             __syncwarp();
@@ -293,18 +299,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             if (go) {
                 if (fl & QF_NEEDS_ISECT) {
                     /* park for Scene::ray_intersect; the free-flight sample waits in the slot */
-                    state = Q_ISECT;
+                    st = Q_ISECT;
                     fl &= ~QF_ISECT_DL;
                     s.mi_t = mi.t; s.mi_mint = mi.mint; st3(s.mi_p, mi.p);
                     s.mi_ss = mi.sigma_s; s.mi_sn = mi.sigma_n; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
                 } else {
-                    state = Q_STEP_B;
+                    st = Q_STEP_B;
                 }
-            } else if (has && state == Q_STEP_B) {
+            } else if (mine && st == Q_STEP_B) {
                 mi.t = s.mi_t; mi.mint = s.mi_mint; mi.p = ld3(s.mi_p);
                 mi.sigma_s = s.mi_ss; mi.sigma_n = s.mi_sn; mi.sigma_t = s.mi_st; mi.combined = s.mi_comb;
             }
-            const bool do_b = has && state == Q_STEP_B;
+            const bool do_b = mine && st == Q_STEP_B;
             /* common part of step B: surface-vs-collision ordering and the transmittance / pdf ratio
                (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
             bool spectral = false;
@@ -344,16 +350,16 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     r.o = mi.p;
                     r.mint = 0;
                     hit_t = hit_t - mi.t;
-                    state = Q_STEP_A;
+                    st = Q_STEP_A;
                 } else if (act_real) {
                     /* the scattering event needs the interaction: leave it in the slot */
                     st3(s.mi_p, mi.p);
                     s.mi_ss = mi.sigma_s; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
-                    state = Q_SCATTER;
+                    st = Q_SCATTER;
                 } else if ((!in_medium || escaped) && hit_t != INF) {
-                    state = Q_SURFACE;
+                    st = Q_SURFACE;
                 } else {
-                    state = Q_PATH_END;
+                    st = Q_PATH_END;
                 }
             } else if (do_b) {
                 /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
@@ -380,45 +386,26 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 bool active_surface = !in_medium || escaped;
                 if (nee && active_surface) total_dist += hit_t;
                 active_surface = active_surface && hit_t != INF && !active_medium;
-                if (active_surface) {
-                    const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
-                    /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
-                    w *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
-                    r = spawn_ray(ld3(s.cur.hit_p), r.d);
-                    if (sh.interior >= 0 || sh.exterior >= 0)
-                        med = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
-                    fl |= QF_NEEDS_ISECT;
-                }
                 if (nee) { r.maxt = remaining; s.total_dist = total_dist; }
-                const bool active = (active_medium || active_surface) && w != 0;
-                if (active) state = Q_STEP_A;
-                else march_end = true;
+                /* a surface on the march (null.cpp:69-72 lets it through, anything else blocks it) and the
+                   end of the march are rare: they run as their own phase, in full batches */
+                if (active_surface) st = Q_MARCH_SURF;
+                else if (active_medium && w != 0) st = Q_STEP_A;
+                else st = Q_MARCH_END;
             }
-            if (has) {
+            if (mine) {
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                 s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
                 fl = in_medium ? (fl | QF_IN_MEDIUM) : (fl & ~QF_IN_MEDIUM);
-                if (march_end) {
-                    /* end of a march: hand the result back and restore the main path's context */
-                    if (nee) c.result += c.nee_w * (w * c.emitter_val);
-                    /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
-                    copy_ctx(s.cur, c.saved);
-                    const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
-                    if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
-                    else if (cont == QC_SURF_B) state = Q_SURF_B;
-                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250) */
-                        s.cur.medium = c.medium_next;
-                        fl &= ~QF_NEEDS_ISECT;
-                        state = Q_STEP_A;
-                    }
-                    fl &= ~QF_MODE;
-                } else {
-                    st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
-                    if (!main_mode) { st3(s.cur.d_rcp, r.d_rcp); s.cur.medium = med; }
-                    s.cur.w = w;
-                    s.cur.hit_t = hit_t;
-                }
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+                st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
+                s.cur.w = w;
+                s.cur.hit_t = hit_t;
+                s.flags = (fl & ~QF_STATE) | (uint32_t) st;
+                state = st;
+            }
+            mine = mine && st <= Q_STEP_B;
+            const int stay = __popc(__ballot_sync(FULL, mine));
+            if (stay < (int) out.q_stay_min || it >= (int) out.q_max_iter) break;
             }
         } else if (phase == PH_ISECT) {
             /* ================================ ISECT =============================== */
@@ -580,6 +567,43 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                 }
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        } else if (phase == PH_MARCH) {
+            /* ================================ MARCH =============================== */
+            if (has) {
+                uint32_t fl = s.flags;
+                state = (int) (fl & QF_STATE);
+                const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;
+                F w = s.cur.w;
+                if (state == Q_MARCH_SURF) { /* volpath.cpp:329-352, 427-450 */
+                    const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
+                    /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
+                    w *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
+                    Ray<F> r = spawn_ray(ld3(s.cur.hit_p), ld3(s.cur.d));
+                    if (sh.interior >= 0 || sh.exterior >= 0)
+                        s.cur.medium = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
+                    if (nee) r.maxt = s.remaining;
+                    st_ray(s.cur, r);
+                    s.cur.w = w;
+                    fl |= QF_NEEDS_ISECT;
+                    state = w != 0 ? Q_STEP_A : Q_MARCH_END;
+                }
+                if (state == Q_MARCH_END) {
+                    /* hand the result back and restore the main path's context */
+                    if (nee) c.result += c.nee_w * (w * c.emitter_val);
+                    /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
+                    copy_ctx(s.cur, c.saved);
+                    const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
+                    if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
+                    else if (cont == QC_SURF_B) state = Q_SURF_B;
+                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250) */
+                        s.cur.medium = c.medium_next;
+                        fl &= ~QF_NEEDS_ISECT;
+                        state = Q_STEP_A;
+                    }
+                    fl &= ~QF_MODE;
+                }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else {
