@@ -626,8 +626,12 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(ds.g.features, &preset); threads = 256; }
         else if (!std::strcmp(e, "q384")) { threads = 384; }
+#ifdef B2VP_EXPERIMENT
+        else if (!std::strcmp(e, "q768")) { kern = volpath_q_kernel<F, 768, PRE_HET>; threads = 768; }
+        else if (!std::strcmp(e, "q1024")) { kern = volpath_q_kernel<F, 1024, PRE_HET>; threads = 1024; }
+#endif
     }
-    if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= 512 && t % 32 == 0 && (threads == 512 || t <= 256)) threads = t; }
+    if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= threads && t % 32 == 0) threads = t; }
     if (const char *e = std::getenv("B2VP_OVERSUB")) { double v = std::atof(e); if (v >= 1.0 && v <= 8.0) oversub = v; }
     int per_sm = 0;
     if (queue_kernel) {
@@ -648,6 +652,8 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         out.q_n_slots = (uint32_t) n_slots;
         out.q_ring_cap = (uint32_t) cap;
         out.q_stay_min = 20; out.q_max_iter = 8;
+        out.q_cta_phase = 1;
+        if (const char *e = std::getenv("B2VP_CTA_PHASE")) out.q_cta_phase = std::atoi(e) ? 1u : 0u;
         if (const char *e = std::getenv("B2VP_STAY")) { int v = std::atoi(e); if (v >= 1 && v <= 33) out.q_stay_min = (uint32_t) v; }
         if (const char *e = std::getenv("B2VP_ITER")) { int v = std::atoi(e); if (v >= 1 && v <= 1024) out.q_max_iter = (uint32_t) v; }
         smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);

@@ -29,6 +29,7 @@ template <typename F> struct RenderOut {
     uint32_t grid_smem_offset;
     /* queue kernel (vp_queue.cuh): path-slot pool and phase queues in shared memory */
     uint32_t q_slots_offset, q_ctl_offset, q_n_slots, q_ring_cap;
+    uint32_t q_cta_phase;           /* 1: the sticky phase is shared by the CTA's warps, 0: per warp */
     uint32_t q_stay_min, q_max_iter; /* STEP keeps its batch while >= q_stay_min lanes stay, <= q_max_iter steps */
     void *q_cold;                   /* grid * q_n_slots PathCold records */
 };

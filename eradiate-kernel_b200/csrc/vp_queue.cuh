@@ -107,6 +107,7 @@ template <typename F> struct PathCold {
 struct QueueCtl {
     int head[PH_N], tail[PH_N], avail[PH_N];
     int n_live;
+    int cur;   /* the phase the CTA is working on (see the pop) */
 };
 #define Q_EMPTY 0xffffu
 
@@ -185,6 +186,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
         ctl->tail[PH_END] = P;
         ctl->avail[PH_END] = P;
         ctl->n_live = P;
+        ctl->cur = PH_END;
     }
     __syncthreads();
 
@@ -198,9 +200,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
         int phase = -1, n = 0, h = 0, live = 1;
         for (int attempt = 0; attempt < 4 && phase < 0; ++attempt) {
             /* lanes 0..4 look at one queue each; a max-reduction picks the fullest (or the sticky one) */
+            const int cur_phase = out.q_cta_phase ? *((volatile int *) &ctl->cur) : last_phase;
             const int c = lane < PH_N ? ((volatile int *) ctl->avail)[lane] : 0;
             int key = lane < PH_N ? ((c << 3) | lane) : 0;
-            if (lane == last_phase && c >= 32) key |= 1 << 29;
+            if (lane == cur_phase && c >= 32) key |= 1 << 29;
             const int top = __reduce_max_sync(FULL, key);
             const int ph = top & 7, cnt = (top & ~(1 << 29)) >> 3;
             if (cnt == 0) break;
@@ -211,7 +214,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 h = atomicAdd(&ctl->head[ph], take);
             }
             ok = __shfl_sync(FULL, ok, 0);
-            if (ok) { phase = ph; n = take; h = __shfl_sync(FULL, h, 0); }
+            if (ok) {
+                phase = ph; n = take; h = __shfl_sync(FULL, h, 0);
+                if (lane == 0 && ph != cur_phase) *((volatile int *) &ctl->cur) = ph;
+            }
         }
         if (phase < 0) live = *((volatile int *) &ctl->n_live);
         if (phase < 0) {
