@@ -346,6 +346,11 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         if (v.channels != 1) ft |= FT_CH3;
         if (!(v.w2l[3] == 0 && v.w2l[7] == 0 && v.w2l[11] == 0 && v.w2l[15] == 1)) ft |= FT_PROJECTIVE;
     }
+    for (uint32_t i = 0; i < n_shapes; ++i) {
+        const B2vpShape &a = s->shapes[i];
+        ft |= a.type == B2VP_SHAPE_MESH ? FT_MESH : a.type == B2VP_SHAPE_SPHERE ? FT_SPHERE : FT_RECT;
+        if (a.type == B2VP_SHAPE_MESH && (a.has_vertex_normals || a.has_vertex_texcoords)) ft |= FT_MESH_ATTR;
+    }
     g.features = ft;
 
     /* blob layout */
@@ -522,9 +527,10 @@ template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64
 inline uint32_t align128(uint32_t x) { return (x + 127u) & ~127u; }
 
 /* queue-kernel instances: the generic one and presets for the common scene classes */
-constexpr uint32_t PRE_HOMOG = FT_HOMOG;
-constexpr uint32_t PRE_HET = FT_HETERO | FT_TRILINEAR;
-constexpr uint32_t PRE_HET_ALB = FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO;
+constexpr uint32_t PRE_FLAT = FT_RECT | FT_MESH | FT_MESH_ATTR;   /* rectangles and meshes, no sphere (double-precision quadratic) */
+constexpr uint32_t PRE_HOMOG = PRE_FLAT | FT_HOMOG;
+constexpr uint32_t PRE_HET = PRE_FLAT | FT_HETERO | FT_TRILINEAR;
+constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO;
 
 template <typename F, int MAXT>
 void (*pick_queue_kernel(uint32_t ft, const char **name))(const DScene<F>, const DStreams, const RenderOut<F>) {

@@ -421,7 +421,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 Ray<F> r;
                 ld_ray(s.cur, r);
                 SurfaceHit<F> h;
-                ray_intersect(sv, r, h, cnt);
+                ray_intersect<F, FEAT>(sv, r, h, cnt);
                 c.c_isect += cnt.n_intersect;
                 s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
                 if (mode == QM_MAIN) { /* the main path keeps the whole SurfaceInteraction */

@@ -35,6 +35,28 @@ template <typename F> struct SurfaceHit {
 
 /* ------------------------------------------------------------------ shapes */
 
+/* Scene features a kernel instance is compiled for.  The generic instance (FT_ALL) handles everything;
+   the host picks the smallest preset that covers the scene (b2vp_api.cu) so that the hot
+   phases -- the kernel is instruction-fetch bound -- carry no code for features the scene does not use.
+   Every preset computes bit-identical results to FT_ALL on the scenes it accepts. */
+enum : uint32_t {
+    FT_HOMOG = 1u << 0,        /* a homogeneous medium is present                         */
+    FT_HETERO = 1u << 1,       /* a heterogeneous medium is present                       */
+    FT_GRID_ALBEDO = 1u << 2,  /* some medium's albedo is a grid                          */
+    FT_GRID_HOMOG = 1u << 3,   /* a homogeneous medium reads a grid volume                */
+    FT_NEAREST = 1u << 4,      /* a grid uses the nearest filter                          */
+    FT_TRILINEAR = 1u << 5,    /* a grid uses the trilinear filter                        */
+    FT_WRAP = 1u << 6,         /* a grid uses repeat / mirror wrapping                    */
+    FT_CH3 = 1u << 7,          /* a grid has 3 channels                                   */
+    FT_PROJECTIVE = 1u << 8,   /* a grid's world_to_local has a non-trivial last row      */
+    FT_RECT = 1u << 9,         /* a rectangle is present                                  */
+    FT_SPHERE = 1u << 10,      /* a sphere is present                                     */
+    FT_MESH = 1u << 11,        /* a triangle mesh is present                              */
+    FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
+    FT_ALL = 0x1fffu
+};
+
+
 /* Rectangle::ray_intersect_preliminary (src/shapes/rectangle.cpp:139-159) */
 template <typename F> VP_D F rectangle_intersect(const DShape<F> &sh, const Ray<F> &r) {
     V3<F> o = xf_point_affine(sh.to_object, r.o), d = xf_vector(sh.to_object, r.d);
@@ -115,7 +137,7 @@ template <typename F> VP_D void initialize_sh_frame(SurfaceHit<F> &si, V3<F> dp_
    (shape, face) order -- the outcome of the reference's `t <= maxt` update rule
    when primitives are visited in that order.  Triangles go through a BVH; its
    slab test is conservative so the candidate set always contains the winner.  */
-template <typename F>
+template <typename F, uint32_t FEAT = FT_ALL>
 __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si,
                                            PathCounters &cnt) {
     const DScene<F> &g = *sv.g;
@@ -136,10 +158,12 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
     F best_u = 0, best_v = 0;
 
     /* analytic shapes, in shape order */
-    for (int k = 0; k < g.n_analytic; ++k) {
+    for (int k = 0; (FEAT & (FT_RECT | FT_SPHERE)) && k < g.n_analytic; ++k) {
         int i = sv.analytic[k];
         const DShape<F> &sh = sv.shapes[i];
-        F t = sh.type == 0 ? rectangle_intersect(sh, ray) : sphere_intersect(sh, ray);
+        F t;
+        if ((FEAT & FT_RECT) && (!(FEAT & FT_SPHERE) || sh.type == 0)) t = rectangle_intersect(sh, ray);
+        else t = sphere_intersect(sh, ray);
         if (t != inf_<F>() && (t < ray.maxt || i > best_shape)) {
             best_shape = i;
             ray.maxt = t;
@@ -147,7 +171,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
     }
 
     /* triangles */
-    if (g.n_bvh_nodes > 0) {
+    if ((FEAT & FT_MESH) && g.n_bvh_nodes > 0) {
         uint32_t stack[48];
         int sp = 0;
         uint32_t node = 0;
@@ -209,7 +233,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
     si.t = t;
     si.shape = best_shape;
     V3<F> dp_du;
-    if (sh.type == 0) { /* rectangle.cpp:175-212 */
+    if ((FEAT & FT_RECT) && sh.type == 0) { /* rectangle.cpp:175-212 */
         V3<F> p = ray_in.at(t);
         V3<F> fn = ld3(sh.fn);
         F dist = dot(ld3(sh.translation) - p, fn);
@@ -217,7 +241,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         si.n = fn;
         si.sh.n = fn;
         dp_du = ld3(sh.fs);
-    } else if (sh.type == 1) { /* sphere.cpp:335-400 */
+    } else if ((FEAT & FT_SPHERE) && sh.type == 1) { /* sphere.cpp:335-400 */
         V3<F> c = ld3(sh.center);
         si.sh.n = normalize(ray_in.at(t) - c);
         si.p = fmadd3(si.sh.n, sh.radius, c);
@@ -226,7 +250,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
         if (sh.flip_normals) si.sh.n = -si.sh.n;
         si.n = si.sh.n;
-    } else { /* src/librender/mesh.cpp:450-545 */
+    } else if (FEAT & FT_MESH) { /* src/librender/mesh.cpp:450-545 */
         F b1 = best_u, b2 = best_v, b0 = (F) 1 - b1 - b2;
         const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + best_prim);
         uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
@@ -236,7 +260,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         si.n = normalize(cross(dp0, dp1));
         V3<F> dp_dv;
         coordinate_system(si.n, dp_du, dp_dv);
-        if (sh.has_uv) {
+        if ((FEAT & FT_MESH_ATTR) && sh.has_uv) {
             const float *t0 = g.vuv + 2 * (size_t) (sh.vofs + i0), *t1 = g.vuv + 2 * (size_t) (sh.vofs + i1),
                         *t2 = g.vuv + 2 * (size_t) (sh.vofs + i2);
             F du0 = (F) t1[0] - (F) t0[0], dv0 = (F) t1[1] - (F) t0[1];
@@ -247,7 +271,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
                                fma_(dv1, dp0.z, -(dv0 * dp1.z)) * inv_det);
             }
         }
-        if (sh.has_normals) {
+        if ((FEAT & FT_MESH_ATTR) && sh.has_normals) {
             const float *q0 = g.vnrm + 3 * (size_t) (sh.vofs + i0), *q1 = g.vnrm + 3 * (size_t) (sh.vofs + i1),
                         *q2 = g.vnrm + 3 * (size_t) (sh.vofs + i2);
             V3<F> n0 = mk3<F>((F) q0[0], (F) q0[1], (F) q0[2]), n1 = mk3<F>((F) q1[0], (F) q1[1], (F) q1[2]),
@@ -278,22 +302,6 @@ VP_D int wrap_coord(int v, int res, int mode) {
 
 template <typename F> VP_D int floor2int(F x) { return (int) floor_(x); }
 
-/* Scene features a kernel instance is compiled for.  The generic instance (FT_ALL) handles everything;
-   the host picks the smallest preset that covers the scene (b2vp_api.cu) so that the tentative-collision
-   step -- the instruction-fetch-bound inner loop -- carries no code for features the scene does not use.
-   Every preset computes bit-identical results to FT_ALL on the scenes it accepts. */
-enum : uint32_t {
-    FT_HOMOG = 1u << 0,        /* a homogeneous medium is present                         */
-    FT_HETERO = 1u << 1,       /* a heterogeneous medium is present                       */
-    FT_GRID_ALBEDO = 1u << 2,  /* some medium's albedo is a grid                          */
-    FT_GRID_HOMOG = 1u << 3,   /* a homogeneous medium reads a grid volume                */
-    FT_NEAREST = 1u << 4,      /* a grid uses the nearest filter                          */
-    FT_TRILINEAR = 1u << 5,    /* a grid uses the trilinear filter                        */
-    FT_WRAP = 1u << 6,         /* a grid uses repeat / mirror wrapping                    */
-    FT_CH3 = 1u << 7,          /* a grid has 3 channels                                   */
-    FT_PROJECTIVE = 1u << 8,   /* a grid's world_to_local has a non-trivial last row      */
-    FT_ALL = 0x1ffu
-};
 
 /* GridVolumeImpl::eval (src/textures/grid3d.cpp:163-185,220-360) and
    ConstVolume::eval (src/textures/constant3d.cpp:31-37) */
