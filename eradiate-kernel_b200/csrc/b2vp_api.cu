@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -46,6 +47,51 @@ int fail(int code, const char *fmt, ...) {
     } while (0)
 
 /* RAII device buffer */
+/* Freed device blocks are kept for the next scene instead of going back to the driver: cudaFree
+   synchronises the device and costs 1-30 ms, which is most of the end-to-end overhead of a short render.
+   Blocks are reused only for requests of exactly the same (256-byte rounded) size on the same device; every
+   user synchronises its stream before releasing, so a cached block is idle.  At most CACHE_MAX bytes stay
+   cached per process. */
+class DeviceCache {
+public:
+    void *take(size_t n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lock(m_);
+        for (size_t i = 0; i < blocks_.size(); ++i)
+            if (blocks_[i].bytes == n && blocks_[i].device == dev) {
+                void *p = blocks_[i].p;
+                total_ -= n;
+                blocks_.erase(blocks_.begin() + (long) i);
+                return p;
+            }
+        return nullptr;
+    }
+    void put(void *p, size_t n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) == cudaSuccess) dev = at.device; else cudaGetLastError();
+        std::lock_guard<std::mutex> lock(m_);
+        if (n > CACHE_MAX / 2 || total_ + n > CACHE_MAX) { cudaFree(p); return; }
+        blocks_.push_back({p, n, dev});
+        total_ += n;
+    }
+    void trim() {
+        std::lock_guard<std::mutex> lock(m_);
+        for (auto &b : blocks_) cudaFree(b.p);
+        blocks_.clear();
+        total_ = 0;
+    }
+private:
+    static constexpr size_t CACHE_MAX = (size_t) 1 << 30;
+    struct Block { void *p; size_t bytes; int device; };
+    std::mutex m_;
+    std::vector<Block> blocks_;
+    size_t total_ = 0;
+};
+inline DeviceCache &device_cache() { static DeviceCache *c = new DeviceCache(); return *c; } /* never destroyed: outlives the CUDA context teardown order */
+
 struct DevBuf {
     void *p = nullptr;
     size_t bytes = 0;
@@ -53,12 +99,20 @@ struct DevBuf {
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
     ~DevBuf() { release(); }
-    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    void release() { if (p) device_cache().put(p, bytes); p = nullptr; bytes = 0; }
     cudaError_t alloc(size_t n) {
         release();
         if (n == 0) n = 16;
+        n = (n + 255) & ~(size_t) 255;
+        p = device_cache().take(n);
+        if (p) { bytes = n; return cudaSuccess; }
         cudaError_t e = cudaMalloc(&p, n);
-        if (e == cudaSuccess) bytes = n;
+        if (e != cudaSuccess) { /* give cached blocks back to the driver and retry once */
+            cudaGetLastError();
+            device_cache().trim();
+            e = cudaMalloc(&p, n);
+        }
+        if (e == cudaSuccess) bytes = n; else p = nullptr;
         return e;
     }
     cudaError_t upload(const void *src, size_t n, size_t padded = 0) {
@@ -576,9 +630,9 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         else CU_CHECK(cudaMemcpyAsync(d_film, film_user, film_bytes, cudaMemcpyHostToDevice, stream));
     }
 
-    if (!s->totals_buf.p) CU_CHECK(s->totals_buf.alloc(TOT_N * sizeof(unsigned long long)));
+    if (!s->totals_buf.p) CU_CHECK(s->totals_buf.alloc((TOT_N + 32) * sizeof(unsigned long long)));
     if (!s->counter_buf.p) CU_CHECK(s->counter_buf.alloc(sizeof(unsigned long long)));
-    CU_CHECK(cudaMemsetAsync(s->totals_buf.p, 0, TOT_N * sizeof(unsigned long long), stream));
+    CU_CHECK(cudaMemsetAsync(s->totals_buf.p, 0, (TOT_N + 32) * sizeof(unsigned long long), stream));
     CU_CHECK(cudaMemsetAsync(s->counter_buf.p, 0, sizeof(unsigned long long), stream));
 
     if (a->seed_mode == B2VP_SEED_SCALAR_BLOCKS) {
@@ -599,6 +653,8 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     RenderOut<F> out{};
     out.film = d_film;
     out.totals = s->totals_buf.as<unsigned long long>();
+    const bool want_qstats = std::getenv("B2VP_QSTATS") != nullptr;
+    if (want_qstats) out.q_stats = out.totals + TOT_N;
     out.work_counter = s->counter_buf.as<unsigned long long>();
     const uint32_t sps = sp.d.samples_per_stream;
     if (a->out_state && count) { CU_CHECK(s->o_state.alloc(count * 8)); out.out_state = s->o_state.as<uint64_t>(); }
@@ -686,7 +742,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     CU_CHECK(cudaEventRecord(s->ev1, stream));
     CU_CHECK(cudaGetLastError());
 
-    unsigned long long tot[TOT_N];
+    unsigned long long tot[TOT_N + 32];
     CU_CHECK(cudaMemcpyAsync(tot, s->totals_buf.p, sizeof(tot), cudaMemcpyDeviceToHost, stream));
     if (!a->film_on_device)
         CU_CHECK(cudaMemcpyAsync(film_user, d_film, film_bytes, cudaMemcpyDeviceToHost, stream));
@@ -697,6 +753,14 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     if (out.out_radiance)
         CU_CHECK(cudaMemcpyAsync(a->out_radiance, out.out_radiance, count * sps * sizeof(F), cudaMemcpyDeviceToHost, stream));
     CU_CHECK(cudaStreamSynchronize(stream));
+    if (want_qstats) {
+        const unsigned long long *q = tot + TOT_N;
+        static const char *names[PH_N] = {"STEP", "ISECT", "SCATTER", "SURFACE", "MARCH", "END"};
+        std::fprintf(stderr, "[b2vp qstats] phase switches %llu, idle polls %llu\n", q[16], q[17]);
+        for (int p = 0; p < PH_N; ++p)
+            std::fprintf(stderr, "[b2vp qstats]   %-8s batches %10llu  slots %12llu  fill %.1f\n", names[p], q[p], q[8 + p],
+                         q[p] ? (double) q[8 + p] / (double) q[p] : 0.0);
+    }
     if (a->totals) {
         B2vpCounters &t = *a->totals;
         std::memset(&t, 0, sizeof(t));
@@ -740,15 +804,19 @@ int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **
                     e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
     }
     if (device < 0 || device >= n) return fail(B2VP_ERR_INVALID, "device ordinal %d out of range", device);
-    cudaDeviceProp prop;
-    CU_CHECK(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10)
+    /* single attributes, not cudaGetDeviceProperties: that call costs milliseconds on every scene */
+    int cc_major = 0, cc_minor = 0, sm_count = 0, smem_optin = 0;
+    CU_CHECK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+    CU_CHECK(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, device));
+    CU_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    CU_CHECK(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    if (cc_major != 10)
         return fail(B2VP_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
-                    prop.major, prop.minor);
+                    cc_major, cc_minor);
     std::unique_ptr<b2vp_scene> s(new b2vp_scene());
     s->device = device;
-    s->sm_count = prop.multiProcessorCount;
-    s->smem_optin = prop.sharedMemPerBlockOptin;
+    s->sm_count = sm_count;
+    s->smem_optin = (size_t) smem_optin;
     int rc = copy_desc(desc, s.get());
     if (rc != B2VP_OK) return rc;
     build_bvh(s.get());

@@ -31,6 +31,7 @@ template <typename F> struct RenderOut {
     uint32_t q_slots_offset, q_ctl_offset, q_n_slots, q_ring_cap;
     uint32_t q_cta_phase;           /* 1: the sticky phase is shared by the CTA's warps, 0: per warp */
     uint32_t q_stay_min, q_max_iter; /* STEP keeps its batch while >= q_stay_min lanes stay, <= q_max_iter steps */
+    unsigned long long *q_stats;    /* optional scheduler statistics (B2VP_QSTATS): pops[8], slots[8], switches, idle polls */
     void *q_cold;                   /* grid * q_n_slots PathCold records */
 };
 

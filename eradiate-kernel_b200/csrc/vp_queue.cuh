@@ -93,7 +93,8 @@ template <typename F> struct PathCold {
     uint32_t j;
     uint32_t c_real, c_isect, c_surf;
     MarchCtx<F> saved;                    /* the main path's context during a march */
-    F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* shading frame of the main path's hit   */
+    uint32_t prim; F bu, bv;              /* mesh face and barycentrics of the main path's hit */
+    F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* its shading frame, completed at the surface event  */
     F result;
     int medium_next;
     F emitter_val, nee_w;
@@ -216,12 +217,20 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             ok = __shfl_sync(FULL, ok, 0);
             if (ok) {
                 phase = ph; n = take; h = __shfl_sync(FULL, h, 0);
-                if (lane == 0 && ph != cur_phase) *((volatile int *) &ctl->cur) = ph;
+                if (lane == 0 && ph != cur_phase) {
+                    *((volatile int *) &ctl->cur) = ph;
+                    if (out.q_stats) atomicAdd(out.q_stats + 16, 1ull);
+                }
+                if (lane == 0 && out.q_stats) {
+                    atomicAdd(out.q_stats + ph, 1ull);
+                    atomicAdd(out.q_stats + 8 + ph, (unsigned long long) take);
+                }
             }
         }
         if (phase < 0) live = *((volatile int *) &ctl->n_live);
         if (phase < 0) {
             if (live == 0) break;
+            if (lane == 0 && out.q_stats) atomicAdd(out.q_stats + 17, 1ull);
             __nanosleep(100);
             continue;
         }
@@ -421,11 +430,12 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 Ray<F> r;
                 ld_ray(s.cur, r);
                 SurfaceHit<F> h;
-                ray_intersect<F, FEAT>(sv, r, h, cnt);
+                ray_intersect<F, FEAT, false>(sv, r, h, cnt);
                 c.c_isect += cnt.n_intersect;
                 s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
-                if (mode == QM_MAIN) { /* the main path keeps the whole SurfaceInteraction */
-                    st3(c.wi, h.wi); st3(c.sh_s, h.sh.s); st3(c.sh_t, h.sh.t); st3(c.sh_n, h.sh.n);
+                if (mode == QM_MAIN) { /* the main path will want the whole SurfaceInteraction if it scatters here:
+                                          keep what surface_frame() needs to finish it */
+                    c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
                 }
                 fl &= ~QF_NEEDS_ISECT;
                 if (fl & QF_ISECT_DL) {
@@ -507,9 +517,21 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
                 const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
                 const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
-                const V3<F> sp_ = ld3(s.cur.hit_p), wi = ld3(c.wi);
+                const V3<F> sp_ = ld3(s.cur.hit_p);
+                V3<F> wi;
                 Frame<F> fr;
-                fr.s = ld3(c.sh_s); fr.t = ld3(c.sh_t); fr.n = ld3(c.sh_n);
+                if (state == Q_SURFACE) {
+                    /* finish the SurfaceInteraction of the hit found in ISECT (interaction.h:571-596) */
+                    SurfaceHit<F> h;
+                    h.shape = s.cur.hit_shape; h.prim = c.prim; h.bu = c.bu; h.bv = c.bv;
+                    h.p = sp_; h.n = ld3(s.cur.hit_n);
+                    surface_frame<F, FEAT>(sv, ld3(s.cur.d), h);
+                    wi = h.wi; fr = h.sh;
+                    st3(c.wi, wi); st3(c.sh_s, fr.s); st3(c.sh_t, fr.t); st3(c.sh_n, fr.n);
+                } else {
+                    wi = ld3(c.wi);
+                    fr.s = ld3(c.sh_s); fr.t = ld3(c.sh_t); fr.n = ld3(c.sh_n);
+                }
                 F throughput = s.cur.w;
                 uint32_t depth = s.depth;
                 if (state == Q_SURFACE) { /* volpath.cpp:192-212 */

@@ -30,6 +30,8 @@ template <typename F> struct SurfaceHit {
     V3<F> p, n, wi;
     Frame<F> sh;
     int shape;
+    uint32_t prim;   /* mesh face */
+    F bu, bv;        /* barycentric coordinates on it */
     VP_D bool valid() const { return t != inf_<F>(); }
 };
 
@@ -137,13 +139,17 @@ template <typename F> VP_D void initialize_sh_frame(SurfaceHit<F> &si, V3<F> dp_
    (shape, face) order -- the outcome of the reference's `t <= maxt` update rule
    when primitives are visited in that order.  Triangles go through a BVH; its
    slab test is conservative so the candidate set always contains the winner.  */
-template <typename F, uint32_t FEAT = FT_ALL>
+/* SHADING = false stops after position and geometric normal (all a march needs, and all the main path needs
+   until it actually scatters on the surface); surface_frame() below completes the interaction later from
+   (shape, prim, bu, bv). */
+template <typename F, uint32_t FEAT = FT_ALL, bool SHADING = true>
 __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si,
                                            PathCounters &cnt) {
     const DScene<F> &g = *sv.g;
     cnt.n_intersect++;
     si.t = inf_<F>();
     si.shape = -1;
+    si.prim = 0; si.bu = 0; si.bv = 0;
     si.wi = -ray_in.d; /* scene_native.inl:36-38 */
     si.p = mk3<F>(0, 0, 0); si.n = si.p; si.sh.s = si.p; si.sh.t = si.p; si.sh.n = si.p;
     Ray<F> ray = ray_in;
@@ -232,6 +238,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
     F t = ray.maxt;
     si.t = t;
     si.shape = best_shape;
+    si.prim = best_prim; si.bu = best_u; si.bv = best_v;
     V3<F> dp_du;
     if ((FEAT & FT_RECT) && sh.type == 0) { /* rectangle.cpp:175-212 */
         V3<F> p = ray_in.at(t);
@@ -240,14 +247,16 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         si.p = fmadd3(fn, dist, p);
         si.n = fn;
         si.sh.n = fn;
-        dp_du = ld3(sh.fs);
+        if (SHADING) dp_du = ld3(sh.fs);
     } else if ((FEAT & FT_SPHERE) && sh.type == 1) { /* sphere.cpp:335-400 */
         V3<F> c = ld3(sh.center);
         si.sh.n = normalize(ray_in.at(t) - c);
         si.p = fmadd3(si.sh.n, sh.radius, c);
-        V3<F> local = xf_point_affine(sh.to_object, si.p);
-        dp_du = mk3<F>(-local.y, local.x, (F) 0);
-        dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
+        if (SHADING) {
+            V3<F> local = xf_point_affine(sh.to_object, si.p);
+            dp_du = mk3<F>(-local.y, local.x, (F) 0);
+            dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
+        }
         if (sh.flip_normals) si.sh.n = -si.sh.n;
         si.n = si.sh.n;
     } else if (FEAT & FT_MESH) { /* src/librender/mesh.cpp:450-545 */
@@ -258,6 +267,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         V3<F> dp0 = p1 - p0, dp1 = p2 - p0;
         si.p = p0 * b0 + p1 * b1 + p2 * b2;
         si.n = normalize(cross(dp0, dp1));
+        if (!SHADING) return;
         V3<F> dp_dv;
         coordinate_system(si.n, dp_du, dp_dv);
         if ((FEAT & FT_MESH_ATTR) && sh.has_uv) {
@@ -281,8 +291,59 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
             si.sh.n = si.n;
         }
     }
+    if (!SHADING) return;
     initialize_sh_frame(si, dp_du);
     si.wi = si.sh.to_local(-ray_in.d);
+}
+
+/* The rest of PreliminaryIntersection::compute_surface_interaction (interaction.h:571-596) for a hit found by
+   ray_intersect<.., false>: shading normal, dp_du, shading frame and wi -- the same operations on the same
+   inputs, so the same bits.  `si` carries t-independent inputs: shape, prim, bu, bv, p, n; `d` is the
+   direction of the ray that hit. */
+template <typename F, uint32_t FEAT = FT_ALL>
+__device__ __noinline__ void surface_frame(const SceneView<F> &sv, V3<F> d, SurfaceHit<F> &si) {
+    const DScene<F> &g = *sv.g;
+    const DShape<F> &sh = sv.shapes[si.shape];
+    V3<F> dp_du;
+    if ((FEAT & FT_RECT) && sh.type == 0) {
+        si.sh.n = si.n;
+        dp_du = ld3(sh.fs);
+    } else if ((FEAT & FT_SPHERE) && sh.type == 1) {
+        si.sh.n = si.n;
+        V3<F> local = xf_point_affine(sh.to_object, si.p);
+        dp_du = mk3<F>(-local.y, local.x, (F) 0);
+        dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
+    } else if (FEAT & FT_MESH) {
+        F b1 = si.bu, b2 = si.bv, b0 = (F) 1 - b1 - b2;
+        const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + si.prim);
+        uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
+        V3<F> dp_dv;
+        coordinate_system(si.n, dp_du, dp_dv);
+        if ((FEAT & FT_MESH_ATTR) && sh.has_uv) {
+            V3<F> p0 = load_vertex(g, sh, i0), p1 = load_vertex(g, sh, i1), p2 = load_vertex(g, sh, i2);
+            V3<F> dp0 = p1 - p0, dp1 = p2 - p0;
+            const float *t0 = g.vuv + 2 * (size_t) (sh.vofs + i0), *t1 = g.vuv + 2 * (size_t) (sh.vofs + i1),
+                        *t2 = g.vuv + 2 * (size_t) (sh.vofs + i2);
+            F du0 = (F) t1[0] - (F) t0[0], dv0 = (F) t1[1] - (F) t0[1];
+            F du1 = (F) t2[0] - (F) t0[0], dv1 = (F) t2[1] - (F) t0[1];
+            F det = fma_(du0, dv1, -(dv0 * du1)), inv_det = rcp_(det);
+            if (det != 0) {
+                dp_du = mk3<F>(fma_(dv1, dp0.x, -(dv0 * dp1.x)) * inv_det, fma_(dv1, dp0.y, -(dv0 * dp1.y)) * inv_det,
+                               fma_(dv1, dp0.z, -(dv0 * dp1.z)) * inv_det);
+            }
+        }
+        if ((FEAT & FT_MESH_ATTR) && sh.has_normals) {
+            const float *q0 = g.vnrm + 3 * (size_t) (sh.vofs + i0), *q1 = g.vnrm + 3 * (size_t) (sh.vofs + i1),
+                        *q2 = g.vnrm + 3 * (size_t) (sh.vofs + i2);
+            V3<F> n0 = mk3<F>((F) q0[0], (F) q0[1], (F) q0[2]), n1 = mk3<F>((F) q1[0], (F) q1[1], (F) q1[2]),
+                  n2 = mk3<F>((F) q2[0], (F) q2[1], (F) q2[2]);
+            si.sh.n = normalize(n0 * b0 + n1 * b1 + n2 * b2);
+        } else {
+            si.sh.n = si.n;
+        }
+    }
+    initialize_sh_frame(si, dp_du);
+    si.wi = si.sh.to_local(-d);
 }
 
 /* ----------------------------------------------------------------- volumes */
