@@ -755,7 +755,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     CU_CHECK(cudaStreamSynchronize(stream));
     if (want_qstats) {
         const unsigned long long *q = tot + TOT_N;
-        static const char *names[PH_N] = {"STEP", "ISECT", "SCATTER", "SURFACE", "MARCH", "END"};
+        static const char *names[PH_N] = {"STEP", "SCATTER", "SURFACE", "MARCH", "END"};
         std::fprintf(stderr, "[b2vp qstats] phase switches %llu, idle polls %llu\n", q[16], q[17]);
         for (int p = 0; p < PH_N; ++p)
             std::fprintf(stderr, "[b2vp qstats]   %-8s batches %10llu  slots %12llu  fill %.1f\n", names[p], q[p], q[8 + p],

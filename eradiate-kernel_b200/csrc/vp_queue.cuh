@@ -2,25 +2,29 @@
  * vp_queue.cuh -- the production render kernel: a CTA-resident wavefront with
  * shared-memory phase queues.
  *
- * A CTA owns a pool of path slots (about twice its thread count) whose state
- * lives in shared memory.  A path is always in exactly one of five phase queues
- * (also shared memory) or in flight in a warp:
+ * A CTA owns a pool of path slots (about 2.4 per thread) whose hot state lives in
+ * shared memory.  A path is always in exactly one of five phase queues (also
+ * shared memory) or in flight in a warp:
  *
- *   STEP     one tentative-collision step (Medium::sample_interaction and its
- *            bookkeeping) -- shared by the main path, the emitter-sampling march
- *            (sample_emitter) and the direct-light march (evaluate_direct_light);
- *   ISECT    Scene::ray_intersect;
- *   SCATTER  real medium scattering: albedo weight, emitter sample, phase sample;
+ *   STEP     one tentative-collision step (loop top, Medium::sample_interaction,
+ *            null / real / surface decision) -- shared by the main path, the
+ *            emitter-sampling march (sample_emitter) and the direct-light march
+ *            (evaluate_direct_light);
+ *   SCATTER  real medium scattering: emitter sample + phase eval, phase sample;
  *   SURFACE  surface event: emitter sample + BSDF eval, BSDF sample;
+ *   MARCH    a march crosses a surface or ends;
  *   END      film splat of a finished path and path regeneration.
  *
- * Each warp repeatedly pops up to 32 slots of ONE phase (it prefers the phase it
- * ran last, then the fullest queue), loads the fields that phase needs into
- * registers, runs the phase for all 32 lanes together, stores the fields back
- * and pushes every slot onto the queue of its next phase.  This is the
- * compaction / sorting by event type: warps always execute full, converged
- * batches, and a warp tends to stay inside one phase's code (the kernel is
- * instruction-fetch bound otherwise, see profiles/).
+ * Every phase but STEP makes rays; Scene::ray_intersect runs at the end of the
+ * visit that made the ray (one shared call site), so a path never queues for it.
+ *
+ * Each warp repeatedly pops up to 32 slots of ONE phase (the phase the whole CTA
+ * is working on while that queue holds a full batch, else the fullest queue),
+ * loads the fields that phase needs into registers, runs the phase for all 32
+ * lanes together, stores the fields back and pushes every slot onto the queue of
+ * its next phase.  This is the compaction / sorting by event type: warps execute
+ * full, converged batches, and an SM's instruction cache sees one phase's code at
+ * a time (the kernel is instruction-fetch bound otherwise, see profiles/).
  *
  * Arithmetic and random-number order are exactly those of vp_integrator.cuh (the
  * one-thread-per-path twin, reference src/integrators/volpath.cpp:38-483); only
@@ -32,9 +36,7 @@
 namespace vp {
 
 enum QState : int {
-    Q_STEP_A = 0,   /* loop top + free-flight sampling                         */
-    Q_STEP_B,       /* rest of the tentative-collision step                    */
-    Q_ISECT,        /* Scene::ray_intersect                                    */
+    Q_STEP = 0,     /* one tentative-collision step                            */
     Q_SCATTER,      /* real medium scattering: albedo, start emitter march     */
     Q_SCATTER_B,    /* phase function sampling                                 */
     Q_SURFACE,      /* surface hit: start emitter march                        */
@@ -45,20 +47,21 @@ enum QState : int {
     Q_NEW,          /* next sample of the stream / next stream                 */
     Q_DEAD
 };
-enum QPhase : int { PH_STEP = 0, PH_ISECT, PH_SCATTER, PH_SURFACE, PH_MARCH, PH_END, PH_N };
+enum QPhase : int { PH_STEP = 0, PH_SCATTER, PH_SURFACE, PH_MARCH, PH_END, PH_N };
 enum QMode : int { QM_MAIN = 0, QM_NEE = 1, QM_DL = 2 };
 enum QCont : int { QC_STEP_B = 0, QC_SCATTER_B, QC_SURF_B, QC_START_DL, QC_AFTER_DL };
 
 VP_D int phase_of(int state) {
-    return state <= Q_STEP_B ? PH_STEP : state == Q_ISECT ? PH_ISECT : state <= Q_SCATTER_B ? PH_SCATTER
+    return state == Q_STEP ? PH_STEP : state <= Q_SCATTER_B ? PH_SCATTER
            : state <= Q_SURF_B ? PH_SURFACE : state <= Q_MARCH_END ? PH_MARCH : PH_END;
 }
 
 /* flag word of a slot */
 enum : uint32_t {
     QF_STATE = 0xfu, QF_MODE_SHIFT = 4, QF_MODE = 0x3u << 4, QF_CONT_SHIFT = 6, QF_CONT = 0x7u << 6,
-    QF_ISECT_DL = 1u << 9,   /* the pending intersection is intersect2: start the direct-light march after it */
-    QF_NEEDS_ISECT = 1u << 10, QF_VALID_RAY = 1u << 11, QF_IN_MEDIUM = 1u << 12, QF_HAVE_STREAM = 1u << 13,
+    QF_TOP_DONE = 1u << 10,  /* the part of this loop iteration that precedes the step (roulette / remaining
+                                distance, intersection) was done where the ray was made */
+    QF_VALID_RAY = 1u << 11, QF_HAVE_STREAM = 1u << 13,
     QF_ACC_USED = 1u << 14
 };
 
@@ -86,7 +89,6 @@ template <typename F> struct PathSlot {
     F eta;
     uint32_t depth;
     F total_dist, ds_dist, remaining;
-    F mi_t, mi_mint, mi_p[3], mi_ss, mi_sn, mi_st, mi_comb; /* MediumInteraction carried from A to B */
 };
 template <typename F> struct PathCold {
     unsigned long long k;
@@ -127,6 +129,18 @@ template <typename F> VP_D void copy_ctx(MarchCtx<F> &dst, const MarchCtx<F> &sr
     }
     dst.mint = src.mint; dst.maxt = src.maxt; dst.hit_t = src.hit_t; dst.hit_shape = src.hit_shape;
     dst.medium = src.medium; dst.w = src.w;
+}
+
+/* Top of the main loop: termination and Russian roulette (volpath.cpp:72-87).  False: the path ends. */
+template <typename F>
+VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth, uint32_t max_depth) {
+    bool active = w != 0;
+    F q = min_(w * sqr(eta), (F) 0.95);
+    bool perform_rr = depth > rr_depth;
+    F rr_sample = rng.next(F(), active);
+    active = active && (rr_sample < q || !perform_rr);
+    if (perform_rr) w *= rcp_(q);
+    return active && depth < max_depth;
 }
 
 /* pixel and image block of stream k, without seeding a generator (see make_stream) */
@@ -252,6 +266,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
         PathCounters cnt;
         cnt.draws = 0; cnt.medium_steps = 0; cnt.n_null = 0; cnt.n_real = 0; cnt.n_intersect = 0; cnt.n_surface = 0;
 
+        /* Rays are intersected where they are made (scatter, surface, march, end phases all end in one call of the
+           shared, out-of-line ray_intersect), together with the part of the next loop iteration that precedes the
+           intersection in the reference -- Russian roulette for the main path (volpath.cpp:72-87), the
+           remaining-distance test for an emitter march (volpath.cpp:285-291).  QF_TOP_DONE tells STEP that this
+           has happened.  Random numbers are drawn in the reference's order (ray_intersect draws none), and it is
+           called exactly when the reference calls it, so the per-path counters agree. */
+        Ray<F> ir;                 /* ray to intersect at the end of this visit */
+        bool do_isect = false;
+        bool isect_main = false;   /* it is the main path's ray: keep (prim, u, v) for surface_frame() */
+        bool start_dl = false;     /* it is intersect2: the direct-light march starts from the new hit */
+        ir.o = mk3<F>(0, 0, 0); ir.d = ir.o; ir.d_rcp = ir.o; ir.mint = 0; ir.maxt = 0;
+
         if (phase == PH_STEP) {
             /* ================================ STEP ================================ */
             /* A warp keeps its batch for several steps while most of its lanes stay in this phase (null
@@ -278,59 +304,39 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 w = s.cur.w;
                 hit_t = s.cur.hit_t;
             }
-            bool go = mine && st == Q_STEP_A;
-            bool in_medium = (fl & QF_IN_MEDIUM) != 0;
+            bool go = mine;
             if (go) {
-                if (main_mode) {
+                if (fl & QF_TOP_DONE) {
+                    if (nee) remaining = s.remaining;
+                } else if (main_mode) {
                     /* termination / Russian roulette (volpath.cpp:72-87) */
-                    F eta = s.eta;
-                    uint32_t depth = s.depth;
-                    bool active = w != 0;
-                    F q = min_(w * sqr(eta), (F) 0.95);
-                    bool perform_rr = depth > rr_depth;
-                    F rr_sample = rng.next(F(), active);
-                    active = active && (rr_sample < q || !perform_rr);
-                    if (perform_rr) w *= rcp_(q);
-                    if (!active || depth >= max_depth) { st = Q_PATH_END; go = false; }
+                    if (!loop_top_rr(rng, w, s.eta, s.depth, rr_depth, max_depth)) { st = Q_PATH_END; go = false; }
                 } else if (nee) {
                     remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
                     r.maxt = remaining;
                     s.remaining = remaining;
                     if (!(remaining > 0)) { st = Q_MARCH_END; go = false; }
                 }
-            } else if (mine && nee) {
-                remaining = s.remaining;
+                fl &= ~QF_TOP_DONE;
             }
             __syncwarp();
-            /* one free-flight sample for whichever ray this path is marching (medium.cpp:36-75) */
-            if (go) in_medium = med >= 0;
-            if (go && in_medium) {
+            /* one free-flight sample for whichever ray this path is marching (medium.cpp:36-75).  For a
+               homogeneous medium the reference shortens ray.maxt to mi.t before it intersects; the hit found
+               here over the full range differs from that only when it lies beyond a valid mi.t, and then it is
+               never looked at (a homogeneous medium has no null collisions: the path scatters, a march ends). */
+            const bool in_medium = go && med >= 0;
+            if (in_medium) {
                 const DMedium<F> &m = sv.media[med];
                 sample_interaction<F, FEAT>(sv, m, r, rng.next(F(), true), mi, cnt);
                 if (m.type == 0 && mi.valid())
                     r.maxt = nee ? min_(mi.t, remaining) : mi.t;
             }
             __syncwarp();
-            if (go) {
-                if (fl & QF_NEEDS_ISECT) {
-                    /* park for Scene::ray_intersect; the free-flight sample waits in the slot */
-                    st = Q_ISECT;
-                    fl &= ~QF_ISECT_DL;
-                    s.mi_t = mi.t; s.mi_mint = mi.mint; st3(s.mi_p, mi.p);
-                    s.mi_ss = mi.sigma_s; s.mi_sn = mi.sigma_n; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
-                } else {
-                    st = Q_STEP_B;
-                }
-            } else if (mine && st == Q_STEP_B) {
-                mi.t = s.mi_t; mi.mint = s.mi_mint; mi.p = ld3(s.mi_p);
-                mi.sigma_s = s.mi_ss; mi.sigma_n = s.mi_sn; mi.sigma_t = s.mi_st; mi.combined = s.mi_comb;
-            }
-            const bool do_b = mine && st == Q_STEP_B;
-            /* common part of step B: surface-vs-collision ordering and the transmittance / pdf ratio
+            /* surface-vs-collision ordering and the transmittance / pdf ratio
                (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
             bool spectral = false;
             F ratio = 1;
-            if (do_b && in_medium) {
+            if (in_medium) {
                 spectral = sv.media[med].spectral != 0;
                 if (hit_t < mi.t) mi.t = INF;
                 if (spectral) {
@@ -344,7 +350,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 }
             }
             __syncwarp();
-            if (do_b && main_mode) {
+            if (go && main_mode) {
                 bool act_null = false, act_real = false, escaped = false;
                 uint32_t depth = s.depth;
                 if (in_medium) {
@@ -365,18 +371,19 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     r.o = mi.p;
                     r.mint = 0;
                     hit_t = hit_t - mi.t;
-                    st = Q_STEP_A;
                 } else if (act_real) {
-                    /* the scattering event needs the interaction: leave it in the slot */
-                    st3(s.mi_p, mi.p);
-                    s.mi_ss = mi.sigma_s; s.mi_st = mi.sigma_t; s.mi_comb = mi.combined;
+                    /* real collision: the albedo weight (volpath.cpp:148-152); the scattering event itself
+                       needs only the position, which becomes the ray origin */
+                    if (spectral) w *= mi.sigma_s * mi.combined / mi.sigma_t;
+                    else w *= mi.sigma_s / mi.sigma_t;
+                    r.o = mi.p;
                     st = Q_SCATTER;
                 } else if ((!in_medium || escaped) && hit_t != INF) {
                     st = Q_SURFACE;
                 } else {
                     st = Q_PATH_END;
                 }
-            } else if (do_b) {
+            } else if (go) {
                 /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
                 bool escaped = false, active_medium = false;
                 F total_dist = nee ? s.total_dist : (F) 0;
@@ -405,52 +412,21 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 /* a surface on the march (null.cpp:69-72 lets it through, anything else blocks it) and the
                    end of the march are rare: they run as their own phase, in full batches */
                 if (active_surface) st = Q_MARCH_SURF;
-                else if (active_medium && w != 0) st = Q_STEP_A;
+                else if (active_medium && w != 0) st = Q_STEP;
                 else st = Q_MARCH_END;
             }
             if (mine) {
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                 s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
-                fl = in_medium ? (fl | QF_IN_MEDIUM) : (fl & ~QF_IN_MEDIUM);
                 st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
                 s.cur.w = w;
                 s.cur.hit_t = hit_t;
                 s.flags = (fl & ~QF_STATE) | (uint32_t) st;
                 state = st;
             }
-            mine = mine && st <= Q_STEP_B;
+            mine = mine && st == Q_STEP;
             const int stay = __popc(__ballot_sync(FULL, mine));
             if (stay < (int) out.q_stay_min || it >= (int) out.q_max_iter) break;
-            }
-        } else if (phase == PH_ISECT) {
-            /* ================================ ISECT =============================== */
-            if (has) {
-                uint32_t fl = s.flags;
-                const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
-                Ray<F> r;
-                ld_ray(s.cur, r);
-                SurfaceHit<F> h;
-                ray_intersect<F, FEAT, false>(sv, r, h, cnt);
-                c.c_isect += cnt.n_intersect;
-                s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
-                if (mode == QM_MAIN) { /* the main path will want the whole SurfaceInteraction if it scatters here:
-                                          keep what surface_frame() needs to finish it */
-                    c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
-                }
-                fl &= ~QF_NEEDS_ISECT;
-                if (fl & QF_ISECT_DL) {
-                    /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the
-                       new hit; the main path (same ray, new hit, throughput) waits in `saved` */
-                    copy_ctx(c.saved, s.cur);
-                    s.cur.w = 1;
-                    c.emitter_val = 0;
-                    fl = (fl & ~(QF_MODE | QF_CONT | QF_ISECT_DL)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
-                         ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
-                    state = Q_STEP_A;
-                } else {
-                    state = Q_STEP_B;
-                }
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else if (phase == PH_SCATTER) {
             /* =============================== SCATTER ============================== */
@@ -462,15 +438,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 const int med = s.cur.medium;
                 const DMedium<F> &m = sv.media[med];
                 const V3<F> d = ld3(s.cur.d);
+                const V3<F> p = ld3(s.cur.o); /* the scattering position (STEP left it as the ray origin) */
                 if (state == Q_SCATTER) { /* volpath.cpp:146-168 */
                     c.c_real += 1;
-                    F throughput = s.cur.w;
-                    const V3<F> p = ld3(s.mi_p);
-                    if (m.spectral) throughput *= s.mi_ss * s.mi_comb / s.mi_st;
-                    else throughput *= s.mi_ss / s.mi_st;
+                    const F throughput = s.cur.w;
                     fl |= QF_VALID_RAY;
-                    s.cur.w = throughput;
-                    st3(s.cur.o, p); /* the old origin is dead: keep the scattering position here */
                     state = Q_SCATTER_B;
                     if (m.sample_emitters) { /* sample_emitter prologue (volpath.cpp:261-283) */
                         F sx = rng.next(F(), true);
@@ -483,13 +455,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                             copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(p, ds.d);
                             r2.mint = 0;
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SCATTER_B << QF_CONT_SHIFT);
+                            /* top of the march's first iteration (volpath.cpp:285-291) */
+                            const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
+                            r2.maxt = remaining;
+                            s.remaining = remaining;
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
-                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
-                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
-                                 ((uint32_t) QC_SCATTER_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
-                            state = Q_STEP_A;
+                            if (remaining > 0) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r2; }
+                            else state = Q_MARCH_END;
                         } else {
                             c.result += nee_w * ev;
                         }
@@ -499,11 +476,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> wo = phase_sample(phase_fn, d, s2x, s2y);
-                    Ray<F> r = spawn_ray(ld3(s.cur.o), wo);
+                    Ray<F> r = spawn_ray(p, wo);
                     r.mint = 0;
                     st_ray(s.cur, r);
-                    fl |= QF_NEEDS_ISECT;
-                    state = Q_STEP_A;
+                    /* top of the next loop iteration */
+                    F w = s.cur.w;
+                    if (loop_top_rr(rng, w, s.eta, s.depth, rr_depth, max_depth)) {
+                        state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = r;
+                    } else {
+                        state = Q_PATH_END;
+                    }
+                    s.cur.w = w;
                 }
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
@@ -521,7 +504,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 V3<F> wi;
                 Frame<F> fr;
                 if (state == Q_SURFACE) {
-                    /* finish the SurfaceInteraction of the hit found in ISECT (interaction.h:571-596) */
+                    /* finish the SurfaceInteraction of the hit (interaction.h:571-596) */
                     SurfaceHit<F> h;
                     h.shape = s.cur.hit_shape; h.prim = c.prim; h.bu = c.bu; h.bv = c.bv;
                     h.p = sp_; h.n = ld3(s.cur.hit_n);
@@ -554,13 +537,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         if (ds.pdf != 0) {
                             copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(sp_, ds.d);
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SURF_B << QF_CONT_SHIFT);
+                            const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
+                            r2.maxt = remaining;
+                            s.remaining = remaining;
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
-                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = nee_w;
-                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
-                                 ((uint32_t) QC_SURF_B << QF_CONT_SHIFT) | QF_NEEDS_ISECT;
-                            state = Q_STEP_A;
+                            if (remaining > 0) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r2; }
+                            else state = Q_MARCH_END;
                         } else {
                             c.result += nee_w * ev;
                         }
@@ -576,8 +563,6 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.eta *= bs_eta;
                     Ray<F> r = spawn_ray(sp_, fr.to_world(bwo));
                     st_ray(s.cur, r);
-                    s.cur.w = throughput;
-                    fl |= QF_NEEDS_ISECT;
                     bool non_null = !(sampled_type & BF_Null);
                     if (non_null) { depth += 1; s.depth = depth; fl |= QF_VALID_RAY; }
                     bool add_emitter = !(sampled_type & BF_Delta) && throughput != 0 && (depth < max_depth);
@@ -587,12 +572,18 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                                                 ? (dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior) : medium;
                     if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
                         c.medium_next = medium_next;
-                        fl |= QF_ISECT_DL;
-                        state = Q_ISECT;
+                        do_isect = true; isect_main = true; start_dl = true; ir = r;
+                        state = Q_STEP;
                     } else {
                         s.cur.medium = medium_next;
-                        state = Q_STEP_A;
+                        /* top of the next loop iteration */
+                        if (loop_top_rr(rng, throughput, s.eta, depth, rr_depth, max_depth)) {
+                            state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = r;
+                        } else {
+                            state = Q_PATH_END;
+                        }
                     }
+                    s.cur.w = throughput;
                 }
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
@@ -611,11 +602,20 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     Ray<F> r = spawn_ray(ld3(s.cur.hit_p), ld3(s.cur.d));
                     if (sh.interior >= 0 || sh.exterior >= 0)
                         s.cur.medium = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
-                    if (nee) r.maxt = s.remaining;
-                    st_ray(s.cur, r);
                     s.cur.w = w;
-                    fl |= QF_NEEDS_ISECT;
-                    state = w != 0 ? Q_STEP_A : Q_MARCH_END;
+                    state = Q_MARCH_END;
+                    if (w != 0) {
+                        /* top of the march's next iteration */
+                        bool cont = true;
+                        if (nee) {
+                            const F remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
+                            r.maxt = remaining;
+                            s.remaining = remaining;
+                            cont = remaining > 0;
+                        }
+                        if (cont) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r; }
+                    }
+                    st_ray(s.cur, r);
                 }
                 if (state == Q_MARCH_END) {
                     /* hand the result back and restore the main path's context */
@@ -625,12 +625,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
                     if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
                     else if (cont == QC_SURF_B) state = Q_SURF_B;
-                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250) */
+                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250); the hit of intersect2 is current */
                         s.cur.medium = c.medium_next;
-                        fl &= ~QF_NEEDS_ISECT;
-                        state = Q_STEP_A;
+                        state = Q_STEP;
                     }
-                    fl &= ~QF_MODE;
+                    fl &= ~(QF_MODE | QF_TOP_DONE);
                 }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
@@ -731,10 +730,41 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.medium = sn.medium;
                     s.cur.w = 1;
                     c.result = 0; s.eta = 1; s.depth = 0;
-                    fl = (fl & ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_ISECT_DL | QF_IN_MEDIUM)) | QF_NEEDS_ISECT;
-                    state = Q_STEP_A;
+                    fl &= ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_TOP_DONE);
+                    /* top of the first loop iteration */
+                    F w0 = 1;
+                    if (loop_top_rr(rng, w0, (F) 1, 0u, rr_depth, max_depth)) {
+                        state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = ray;
+                    } else {
+                        state = Q_PATH_END;
+                    }
+                    s.cur.w = w0;
+                    s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                 }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
+            }
+        }
+
+        /* ---------------- Scene::ray_intersect for the rays made in this visit ---------------- */
+        if (phase != PH_STEP && __any_sync(FULL, do_isect)) {
+            if (do_isect) {
+                SurfaceHit<F> h;
+                ray_intersect<F, FEAT, false>(sv, ir, h, cnt);
+                c.c_isect += cnt.n_intersect;
+                s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
+                if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here:
+                                     keep what surface_frame() needs to finish it */
+                    c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
+                }
+                if (start_dl) {
+                    /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the
+                       new hit; the main path (same ray, new hit, throughput) waits in `saved` */
+                    copy_ctx(c.saved, s.cur);
+                    s.cur.w = 1;
+                    c.emitter_val = 0;
+                    s.flags = (s.flags & ~(QF_MODE | QF_CONT | QF_TOP_DONE)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
+                              ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
+                }
             }
         }
 
