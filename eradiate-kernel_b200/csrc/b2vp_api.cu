@@ -127,7 +127,7 @@ struct DevBuf {
 /* Device copy of a scene in one arithmetic precision. */
 template <typename F> struct DeviceScene {
     DScene<F> g{};
-    DevBuf blob, vpos, vnrm, vuv, faces, bvh, bvh_prims, sensor_xf;
+    DevBuf blob, vpos, vnrm, vuv, faces, bvh, bvh_prims, bvh_tris, sensor_xf;
     std::vector<std::unique_ptr<DevBuf>> grids;
     std::vector<unsigned char> host_blob;  /* kept for scene_update */
     uint32_t smem_static = 0;              /* blob + staged grids */
@@ -456,6 +456,18 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         CU_CHECK(ds.bvh.upload(s->bvh_nodes.data(), s->bvh_nodes.size() * sizeof(BvhNode)));
         CU_CHECK(ds.bvh_prims.upload(s->bvh_prims.data(), s->bvh_prims.size() * sizeof(BvhPrim)));
         g.bvh = ds.bvh.template as<BvhNode>(); g.bvh_prims = ds.bvh_prims.template as<BvhPrim>();
+        std::vector<BvhTri> soup(s->bvh_prims.size());
+        for (size_t i = 0; i < soup.size(); ++i) {
+            const BvhPrim &pr = s->bvh_prims[i];
+            const B2vpShape &a = s->shapes[pr.shape];
+            const uint32_t *fi = &s->faces[3 * (size_t) (a.face_offset + pr.face)];
+            float *dst[3] = {soup[i].p0, soup[i].p1, soup[i].p2};
+            for (int v = 0; v < 3; ++v)
+                std::memcpy(dst[v], &s->vpos[3 * (size_t) (a.vertex_offset + fi[v])], 3 * sizeof(float));
+            soup[i].shape = pr.shape; soup[i].face = pr.face; soup[i].pad = 0;
+        }
+        CU_CHECK(ds.bvh_tris.upload(soup.data(), soup.size() * sizeof(BvhTri)));
+        g.bvh_tris = ds.bvh_tris.template as<BvhTri>();
     }
     if (!s->sensor_xf.empty()) {
         std::vector<F> xf(s->sensor_xf.begin(), s->sensor_xf.end());
@@ -713,7 +725,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         out.q_slots_offset = (uint32_t) (base + qbytes);
         out.q_n_slots = (uint32_t) n_slots;
         out.q_ring_cap = (uint32_t) cap;
-        out.q_stay_min = 20; out.q_max_iter = 8;
+        out.q_stay_min = 28; out.q_max_iter = 8;
         out.q_cta_phase = 1;
         if (const char *e = std::getenv("B2VP_CTA_PHASE")) out.q_cta_phase = std::atoi(e) ? 1u : 0u;
         if (const char *e = std::getenv("B2VP_STAY")) { int v = std::atoi(e); if (v >= 1 && v <= 33) out.q_stay_min = (uint32_t) v; }

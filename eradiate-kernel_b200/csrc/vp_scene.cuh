@@ -106,6 +106,18 @@ template <typename F> VP_D V3<F> load_vertex(const DScene<F> &g, const DShape<F>
     return mk3<F>((F) __ldg(p), (F) __ldg(p + 1), (F) __ldg(p + 2));
 }
 
+/* One leaf triangle of the BVH: the three vertex positions (always f32, mesh.h:22-28) and its (shape, face). */
+template <typename F>
+VP_D void load_bvh_tri(const DScene<F> &g, uint32_t i, V3<F> &p0, V3<F> &p1, V3<F> &p2, BvhPrim &pr) {
+    const float4 *t = reinterpret_cast<const float4 *>(g.bvh_tris + i);
+    const float4 a = __ldg(t), b = __ldg(t + 1), c = __ldg(t + 2);
+    p0 = mk3<F>((F) a.x, (F) a.y, (F) a.z);
+    p1 = mk3<F>((F) a.w, (F) b.x, (F) b.y);
+    p2 = mk3<F>((F) b.z, (F) b.w, (F) c.x);
+    pr.shape = __float_as_uint(c.y);
+    pr.face = __float_as_uint(c.z);
+}
+
 /* Mesh::ray_intersect_triangle (include/mitsuba/render/mesh.h:195-226), Moeller-Trumbore */
 template <typename F>
 VP_D F triangle_intersect(V3<F> p0, V3<F> p1, V3<F> p2, const Ray<F> &r, F &u_out, F &v_out) {
@@ -160,7 +172,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         return;
 
     int best_shape = -1;
-    uint32_t best_prim = 0;
+    uint32_t best_prim = 0, best_tri = 0;
     F best_u = 0, best_v = 0;
 
     /* analytic shapes, in shape order */
@@ -209,11 +221,10 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
                     continue;
                 }
                 for (uint32_t k = 0; k < count; ++k) {
-                    const BvhPrim pr = g.bvh_prims[child + k];
-                    const DShape<F> &sh = sv.shapes[pr.shape];
-                    const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + pr.face);
-                    V3<F> p0 = load_vertex(g, sh, __ldg(fi)), p1 = load_vertex(g, sh, __ldg(fi + 1)),
-                          p2 = load_vertex(g, sh, __ldg(fi + 2));
+                    /* leaf triangles are stored by value in leaf order: three 16-byte loads per test */
+                    V3<F> p0, p1, p2;
+                    BvhPrim pr;
+                    load_bvh_tri(g, child + k, p0, p1, p2, pr);
                     F u, v;
                     F t = triangle_intersect(p0, p1, p2, ray, u, v);
                     if (t != inf_<F>()) {
@@ -221,6 +232,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
                                      ((int) pr.shape == best_shape && pr.face > best_prim);
                         if (t < ray.maxt || later) {
                             best_shape = (int) pr.shape; best_prim = pr.face; best_u = u; best_v = v;
+                            best_tri = child + k;
                             ray.maxt = t;
                         }
                     }
@@ -261,13 +273,15 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         si.n = si.sh.n;
     } else if (FEAT & FT_MESH) { /* src/librender/mesh.cpp:450-545 */
         F b1 = best_u, b2 = best_v, b0 = (F) 1 - b1 - b2;
-        const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + best_prim);
-        uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
-        V3<F> p0 = load_vertex(g, sh, i0), p1 = load_vertex(g, sh, i1), p2 = load_vertex(g, sh, i2);
+        V3<F> p0, p1, p2;
+        BvhPrim pr;
+        load_bvh_tri(g, best_tri, p0, p1, p2, pr);
         V3<F> dp0 = p1 - p0, dp1 = p2 - p0;
         si.p = p0 * b0 + p1 * b1 + p2 * b2;
         si.n = normalize(cross(dp0, dp1));
         if (!SHADING) return;
+        const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + best_prim);
+        const uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
         V3<F> dp_dv;
         coordinate_system(si.n, dp_du, dp_dv);
         if ((FEAT & FT_MESH_ATTR) && sh.has_uv) {

@@ -254,6 +254,7 @@ struct BvhNode {
     uint32_t count;
 };
 struct BvhPrim { uint32_t shape, face; };
+struct alignas(16) BvhTri { float p0[3], p1[3], p2[3]; uint32_t shape, face, pad; };  /* 48 B */
 
 struct SpiralBlockD { int ox, oy, sx, sy; };
 
@@ -270,6 +271,7 @@ template <typename F> struct DScene {
     const uint32_t *faces;
     const BvhNode *bvh;
     const BvhPrim *bvh_prims;
+    const BvhTri *bvh_tris;         /* leaf triangles by value, in leaf order */
     const F *sensor_xf;
     F kd_min[3], kd_max[3];         /* scene bbox padded as in kdtree.h:1811-1813 */
     F bs_center[3], bs_radius;

@@ -37,18 +37,22 @@ def compare(pkg, oracle, sc, mode, **kw):
     return got
 
 
-@pytest.fixture(params=["queue", "q256", "lanes", "mega"])
+@pytest.fixture(params=["queue", "generic", "q256", "lanes", "mega"])
 def kernel(request, monkeypatch):
     """B2VP_KERNEL selects the device kernel: the queue-based wavefront product kernel (two CTA sizes), the
-    register-resident warp-voting wavefront or its one-thread-per-path twin.  All must give identical results."""
-    monkeypatch.setenv("B2VP_KERNEL", request.param)
+    register-resident warp-voting wavefront or its one-thread-per-path twin; "generic" forces the product
+    kernel's all-features instance instead of the scene-class preset.  All must give identical results."""
+    if request.param == "generic":
+        monkeypatch.setenv("B2VP_GENERIC", "1")
+    else:
+        monkeypatch.setenv("B2VP_KERNEL", request.param)
     return request.param
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_wavefront_seeding_bit_exact(pkg, oracle, case, variant, kernel):
-    if kernel in ("q256", "lanes") and variant == "scalar_mono_double":
+    if kernel in ("q256", "lanes", "generic") and variant == "scalar_mono_double":
         pytest.skip("variant covered in fp32")
     sc = pkg.load_dict(CASES[case](variant), variant)
     compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
