@@ -143,6 +143,43 @@ VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth
     return active && depth < max_depth;
 }
 
+/* Scene::ray_intersect for a ray made in this visit, and what follows from the hit without any further draw.
+   START_DL: the ray is intersect2 (volpath.cpp:238-252) and the direct-light march starts from the new hit. */
+template <typename F, uint32_t FEAT, bool START_DL>
+VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> &c, const Ray<F> &ir, bool isect_main,
+                            PathCounters &cnt, uint32_t &fl, int &state) {
+    SurfaceHit<F> h;
+    ray_intersect<F, FEAT, false>(sv, ir, h, cnt);
+    c.c_isect += 1;
+    s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
+    if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here: keep what
+                         surface_frame() needs to finish it */
+        c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
+    }
+    if (START_DL) {
+        /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the new hit; the
+           main path (same ray, new hit, throughput) waits in `saved` */
+        copy_ctx(c.saved, s.cur);
+        s.cur.w = 1;
+        c.emitter_val = 0;
+        fl = (fl & ~(QF_MODE | QF_CONT | QF_TOP_DONE)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
+             ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
+    }
+    if (s.cur.medium < 0) {
+        /* outside every medium the step that follows is trivial -- no draw, no collision, just "did the ray hit
+           something" (volpath.cpp:178-190, 336-345, 417-425) -- so take it here */
+        const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
+        const bool valid = h.t != inf_<F>();
+        if (mode == QM_MAIN) {
+            state = valid ? Q_SURFACE : Q_PATH_END;
+        } else {
+            if (mode == QM_NEE) s.total_dist += h.t;
+            state = valid ? Q_MARCH_SURF : Q_MARCH_END;
+        }
+        fl &= ~QF_TOP_DONE;
+    }
+}
+
 /* pixel and image block of stream k, without seeding a generator (see make_stream) */
 VP_D void stream_pixel(const DStreams &sp, uint64_t k, int &px, int &py, int &box, int &boy, int &bsx, int &bsy,
                        bool &empty) {
@@ -489,6 +526,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.w = w;
                 }
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else if (phase == PH_SURFACE) {
@@ -586,6 +624,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.w = throughput;
                 }
                 s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                if (do_isect) {
+                    if (start_dl) intersect_new_ray<F, FEAT, true>(sv, s, c, ir, isect_main, cnt, fl, state);
+                    else intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
+                }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else if (phase == PH_MARCH) {
@@ -616,6 +658,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         if (cont) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r; }
                     }
                     st_ray(s.cur, r);
+                    /* the new ray is intersected at once; outside the medium that settles what the march does
+                       next, often that it is over (the ray left the atmosphere towards the sun) */
+                    if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, false, cnt, fl, state);
                 }
                 if (state == Q_MARCH_END) {
                     /* hand the result back and restore the main path's context */
@@ -740,31 +785,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                     s.cur.w = w0;
                     s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                    if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, true, cnt, fl, state);
                 }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
-            }
-        }
-
-        /* ---------------- Scene::ray_intersect for the rays made in this visit ---------------- */
-        if (phase != PH_STEP && __any_sync(FULL, do_isect)) {
-            if (do_isect) {
-                SurfaceHit<F> h;
-                ray_intersect<F, FEAT, false>(sv, ir, h, cnt);
-                c.c_isect += cnt.n_intersect;
-                s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
-                if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here:
-                                     keep what surface_frame() needs to finish it */
-                    c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
-                }
-                if (start_dl) {
-                    /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the
-                       new hit; the main path (same ray, new hit, throughput) waits in `saved` */
-                    copy_ctx(c.saved, s.cur);
-                    s.cur.w = 1;
-                    c.emitter_val = 0;
-                    s.flags = (s.flags & ~(QF_MODE | QF_CONT | QF_TOP_DONE)) | ((uint32_t) QM_DL << QF_MODE_SHIFT) |
-                              ((uint32_t) QC_AFTER_DL << QF_CONT_SHIFT);
-                }
             }
         }
 
