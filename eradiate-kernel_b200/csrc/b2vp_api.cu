@@ -208,6 +208,8 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
              (uint64_t) a.face_offset + a.face_count > d->n_faces))
             return fail(B2VP_ERR_INVALID, "shape %u: vertex/face range out of the pools", i);
     }
+    if (d->n_faces >= (1ull << 28))
+        return fail(B2VP_ERR_UNSUPPORTED, "more than 2^28 triangles (the BVH node reference holds 29 bits)");
     for (uint32_t i = 0; i < d->n_bsdfs; ++i)
         if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_RPV)
             return fail(B2VP_ERR_UNSUPPORTED, "bsdf %u: type %d not supported by the B200 volpath", i, d->bsdfs[i].type);

@@ -49,13 +49,16 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
             nodes[t.node].count = cnt;
             for (uint32_t i = t.lo; i < t.hi; ++i) prims.push_back(BvhPrim{ tris[i].shape, tris[i].face });
         };
-        /* the device traversal stack holds 48 entries: one per level */
-        if (cnt <= (uint32_t) MAX_LEAF || t.depth >= 44) { make_leaf(); continue; }
+        /* Leaves hold at most MAX_LEAF triangles (the device packs the count into 3 bits).  The device traversal
+           stack holds 64 entries, one per level: SAH splits may be lopsided, so from depth 24 on the split is the
+           index median, which bounds the depth by 24 + log2(n). */
+        if (cnt <= (uint32_t) MAX_LEAF) { make_leaf(); continue; }
+        const bool force_median = t.depth >= 24;
 
         /* binned SAH over the three axes */
         int best_axis = -1, best_split = -1;
         float best_cost = INFINITY;
-        for (int a = 0; a < 3; ++a) {
+        for (int a = 0; a < 3 && !force_median; ++a) {
             float ext = cmax[a] - cmin[a];
             if (!(ext > 0.f)) continue;
             float scale = NB / ext;
@@ -99,7 +102,7 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
         }
         uint32_t mid;
         if (best_axis < 0) {
-            /* all centroids coincide: split by index */
+            /* all centroids coincide, or the tree is getting deep: split by index */
             mid = t.lo + cnt / 2;
         } else {
             float ext = cmax[best_axis] - cmin[best_axis], scale = NB / ext, c0 = cmin[best_axis];

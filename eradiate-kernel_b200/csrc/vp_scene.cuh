@@ -188,43 +188,67 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         }
     }
 
-    /* triangles */
+    /* triangles: near-child-first traversal.  An inner node's two children are adjacent (64 bytes, four 16-byte
+       loads); both boxes are tested, the nearer one is entered and the farther one pushed with its entry
+       distance, so that it can be skipped once a closer hit is known.  Visiting order does not change the
+       answer: the winner is the smallest t, ties going to the later (shape, face), and boxes that touch the
+       current maxt are still visited. */
     if ((FEAT & FT_MESH) && g.n_bvh_nodes > 0) {
-        uint32_t stack[48];
+        uint32_t stack_n[64];
+        float stack_t[64];
         int sp = 0;
-        uint32_t node = 0;
         /* conservative slab test in float: widen by a few ulps */
         const float ox = (float) ray.o.x, oy = (float) ray.o.y, oz = (float) ray.o.z;
         const float ix = (float) ray.d_rcp.x, iy = (float) ray.d_rcp.y, iz = (float) ray.d_rcp.z;
-        const float rmint = (float) ray.mint;
         const float lo_s = 1.f - 8.f * 1.1920929e-7f, hi_s = 1.f + 8.f * 1.1920929e-7f;
-        while (true) {
-            const float4 a = __ldg(reinterpret_cast<const float4 *>(g.bvh + node));
-            const float4 b = __ldg(reinterpret_cast<const float4 *>(g.bvh + node) + 1);
-            const uint32_t child = __float_as_uint(a.w), count = __float_as_uint(b.w);
+        const float rmint_lo = (float) ray.mint * lo_s;
+        auto inflate_max = [&](float m) { return m > 0.f ? m * hi_s : m * lo_s; };
+        auto slab = [&](const float4 a, const float4 b, float cur_max, float &tn) {
             float t1x = (a.x - ox) * ix, t2x = (b.x - ox) * ix;
             float t1y = (a.y - oy) * iy, t2y = (b.y - oy) * iy;
             float t1z = (a.z - oz) * iz, t2z = (b.z - oz) * iz;
             /* NaN (0 * inf) never rejects: fminf/fmaxf drop NaN operands */
-            float tn = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
+            tn = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
             float tf = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
             tn = tn > 0.f ? tn * lo_s : tn * hi_s;
             tf = tf > 0.f ? tf * hi_s : tf * lo_s;
-            float cur_max = (float) ray.maxt;
-            cur_max = cur_max > 0.f ? cur_max * hi_s : cur_max * lo_s;
-            bool hit = tn <= tf && tf >= rmint * lo_s && tn <= cur_max;
-            if (hit) {
-                if (count == 0) {
-                    /* descend; push the second child */
-                    stack[sp++] = child + 1;
-                    node = child;
+            return tn <= tf && tf >= rmint_lo && tn <= cur_max;
+        };
+        /* a node reference: first child / first triangle in the low 29 bits, triangle count above */
+        auto ref_of = [](const float4 a, const float4 b) { return __float_as_uint(a.w) | (__float_as_uint(b.w) << 29); };
+        uint32_t cur;
+        bool have;
+        {
+            const float4 *n = reinterpret_cast<const float4 *>(g.bvh);
+            const float4 a = __ldg(n), b = __ldg(n + 1);
+            float tn;
+            have = slab(a, b, inflate_max((float) ray.maxt), tn);
+            cur = ref_of(a, b);
+        }
+        while (have) {
+            const uint32_t count = cur >> 29, first = cur & 0x1fffffffu;
+            if (count == 0) {
+                const float4 *n = reinterpret_cast<const float4 *>(g.bvh + first);
+                const float4 a0 = __ldg(n), b0 = __ldg(n + 1), a1 = __ldg(n + 2), b1 = __ldg(n + 3);
+                const float cur_max = inflate_max((float) ray.maxt);
+                float t0, t1;
+                const bool h0 = slab(a0, b0, cur_max, t0), h1 = slab(a1, b1, cur_max, t1);
+                const uint32_t r0 = ref_of(a0, b0), r1 = ref_of(a1, b1);
+                if (h0 && h1) {
+                    const bool swap = t1 < t0;
+                    stack_n[sp] = swap ? r0 : r1;
+                    stack_t[sp] = swap ? t0 : t1;
+                    sp++;
+                    cur = swap ? r1 : r0;
                     continue;
                 }
+                if (h0 || h1) { cur = h0 ? r0 : r1; continue; }
+            } else {
                 for (uint32_t k = 0; k < count; ++k) {
                     /* leaf triangles are stored by value in leaf order: three 16-byte loads per test */
                     V3<F> p0, p1, p2;
                     BvhPrim pr;
-                    load_bvh_tri(g, child + k, p0, p1, p2, pr);
+                    load_bvh_tri(g, first + k, p0, p1, p2, pr);
                     F u, v;
                     F t = triangle_intersect(p0, p1, p2, ray, u, v);
                     if (t != inf_<F>()) {
@@ -232,14 +256,19 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
                                      ((int) pr.shape == best_shape && pr.face > best_prim);
                         if (t < ray.maxt || later) {
                             best_shape = (int) pr.shape; best_prim = pr.face; best_u = u; best_v = v;
-                            best_tri = child + k;
+                            best_tri = first + k;
                             ray.maxt = t;
                         }
                     }
                 }
             }
-            if (sp == 0) break;
-            node = stack[--sp];
+            /* next: the nearest pending node that can still hold a hit */
+            have = false;
+            const float cur_max = inflate_max((float) ray.maxt);
+            while (sp > 0) {
+                --sp;
+                if (stack_t[sp] <= cur_max) { cur = stack_n[sp]; have = true; break; }
+            }
         }
     }
     if (best_shape < 0)
