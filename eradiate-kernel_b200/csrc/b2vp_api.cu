@@ -696,7 +696,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     Kern kern = pick_queue_kernel<F, 512>(ds.g.features, &preset);
     int threads = 512;
     bool queue_kernel = true;
-    double oversub = 2.4;   /* path slots per thread (capped by the shared memory left) */
+    double oversub = 4.0;   /* path slots per thread; in practice the shared memory left sets the pool size */
     if (const char *e = std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
