@@ -111,3 +111,28 @@ def render_parallel(pkg, scene, seed_mode, ranges, n_threads, precision=None):
     [t.join() for t in ts]
     film = sum(r.film.astype(np.float64) for r in results)
     return film, [r.totals for r in results]
+
+
+def sensor_ray(scene, fx, fy, ax=0.5, ay=0.5):
+    """One Sensor::sample_ray of the scene's sensor: film position (fx, fy) in [0,1)^2, aperture sample
+    (ax, ay).  Returns (origin, direction, weight)."""
+    o, d, w = (C.c_double * 3)(), (C.c_double * 3)(), C.c_double()
+    f = lib().b2vp_oracle_probe_sensor_ray
+    f.argtypes = [C.c_void_p, C.c_int] + [C.c_double] * 4 + [C.c_void_p] * 3
+    rc = f(C.byref(scene.desc), scene.precision, fx, fy, ax, ay, o, d, C.byref(w))
+    if rc:
+        raise RuntimeError("oracle error %d" % rc)
+    return np.array(o[:]), np.array(d[:]), w.value
+
+
+def ray_intersect(scene, o, d, mint=-1.0, maxt=-1.0):
+    """One Scene::ray_intersect.  Returns dict(t (None if no hit), p, n, wi, shape)."""
+    oo, dd = (C.c_double * 3)(*o), (C.c_double * 3)(*d)
+    t, p, n, wi, shape = C.c_double(), (C.c_double * 3)(), (C.c_double * 3)(), (C.c_double * 3)(), C.c_int()
+    f = lib().b2vp_oracle_probe_ray_intersect
+    f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double] + [C.c_void_p] * 5
+    rc = f(C.byref(scene.desc), scene.precision, oo, dd, mint, maxt, C.byref(t), p, n, C.byref(shape), wi)
+    if rc:
+        raise RuntimeError("oracle error %d" % rc)
+    return {"t": None if t.value < 0 else t.value, "p": np.array(p[:]), "n": np.array(n[:]),
+            "wi": np.array(wi[:]), "shape": shape.value}

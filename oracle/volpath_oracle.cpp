@@ -1483,6 +1483,38 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
 /* ======================================================================
  *  C entry points (loaded with ctypes by tests/ and bench.py only)
  * ====================================================================== */
+/* Probes for the known-answer tests (tests/test_oracle_golden.py): one sensor ray / one Scene::ray_intersect
+   of a described scene, in the given precision.  Outputs are doubles. */
+template <typename F>
+static int probe_sensor_ray_t(const B2vpSceneDesc *desc, double fx, double fy, double ax, double ay, double *o,
+                              double *d, double *weight) {
+    OScene<F> sc;
+    if (!build_scene<F>(desc, sc)) return B2VP_ERR_INVALID;
+    Ray<F> ray;
+    bool ok = true;
+    F w = sensor_sample_ray<F>(sc, (F) fx, (F) fy, (F) ax, (F) ay, ray, ok);
+    o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z;
+    d[0] = ray.d.x; d[1] = ray.d.y; d[2] = ray.d.z;
+    *weight = ok ? (double) w : 0.0;
+    return B2VP_OK;
+}
+template <typename F>
+static int probe_ray_intersect_t(const B2vpSceneDesc *desc, const double *o, const double *d, double mint,
+                                 double maxt, double *t, double *p, double *n, int *shape, double *wi) {
+    OScene<F> sc;
+    if (!build_scene<F>(desc, sc)) return B2VP_ERR_INVALID;
+    Ray<F> ray = make_ray<F>(V3<F>{ (F) o[0], (F) o[1], (F) o[2] }, V3<F>{ (F) d[0], (F) d[1], (F) d[2] },
+                             mint < 0 ? Consts<F>::RayEpsilon : (F) mint, maxt < 0 ? Consts<F>::Inf : (F) maxt);
+    Counters cnt;
+    SurfaceInteraction<F> si = ray_intersect<F>(sc, ray, cnt);
+    *t = si.is_valid() ? (double) si.t : -1.0;
+    p[0] = si.p.x; p[1] = si.p.y; p[2] = si.p.z;
+    n[0] = si.n.x; n[1] = si.n.y; n[2] = si.n.z;
+    wi[0] = si.wi.x; wi[1] = si.wi.y; wi[2] = si.wi.z;
+    *shape = si.shape;
+    return B2VP_OK;
+}
+
 extern "C" {
 
 int b2vp_oracle_render(const B2vpSceneDesc *desc, const B2vpRenderArgs *args, void *film) {
@@ -1552,5 +1584,16 @@ void b2vp_oracle_math_f64(int fn, int n, const double *x, const double *y, doubl
 double b2vp_oracle_rpv_eval(double rho_0, double k, double g, double rho_c, const double *wi, const double *wo) {
     B2vpBsdf b{}; b.type = B2VP_BSDF_RPV; b.p[0] = rho_0; b.p[1] = k; b.p[2] = g; b.p[3] = rho_c;
     return bsdf_eval<double>(b, V3<double>{ wi[0], wi[1], wi[2] }, V3<double>{ wo[0], wo[1], wo[2] });
+}
+
+int b2vp_oracle_probe_sensor_ray(const B2vpSceneDesc *desc, int precision, double fx, double fy, double ax, double ay,
+                                 double *o, double *d, double *weight) {
+    return precision == B2VP_PREC_F32 ? probe_sensor_ray_t<float>(desc, fx, fy, ax, ay, o, d, weight)
+                                      : probe_sensor_ray_t<double>(desc, fx, fy, ax, ay, o, d, weight);
+}
+int b2vp_oracle_probe_ray_intersect(const B2vpSceneDesc *desc, int precision, const double *o, const double *d,
+                                    double mint, double maxt, double *t, double *p, double *n, int *shape, double *wi) {
+    return precision == B2VP_PREC_F32 ? probe_ray_intersect_t<float>(desc, o, d, mint, maxt, t, p, n, shape, wi)
+                                      : probe_ray_intersect_t<double>(desc, o, d, mint, maxt, t, p, n, shape, wi);
 }
 }
