@@ -1,0 +1,469 @@
+/*
+ * b2vp.hpp -- C++17 host layer above the C-ABI of b2vp.h (header only).
+ *
+ * The reference's host language is C++: scenes are trees of plugins configured through
+ * `Properties` (include/mitsuba/core/properties.h) and rendered with
+ * `Integrator::render(Scene*, Sensor*)` (include/mitsuba/render/integrator.h:42).  This header gives
+ * C++ callers the same vocabulary without the reference's build: one small struct per scoped plugin
+ * with the plugin's property names and defaults (file:line per struct), a `SceneBuilder<Float>` that
+ * flattens them into the POD `B2vpSceneDesc`, and RAII wrappers of the device scene and the render
+ * call that turn error codes into exceptions, as `Throw` does in the reference.
+ *
+ *   b2vp::SceneBuilder<float> sb;                       // scalar_mono   (double: scalar_mono_double)
+ *   int atm = sb.add_medium(b2vp::Homogeneous{.5, 1.0}, b2vp::Phase::rayleigh());
+ *   sb.add_cube(b2vp::Mat4<float>::translate(0, 0, .45f) * b2vp::Mat4<float>::scale(1, 1, .55f),
+ *               sb.add_bsdf(b2vp::Null{}), atm);
+ *   ...
+ *   b2vp::DeviceScene dev(sb.finish(), 0);              // b2vp_scene_create
+ *   b2vp::Film film = dev.render();                     // b2vp_render
+ *
+ * Derived quantities (frames, areas, look-at matrices, the bounding sphere) are computed in `Float`,
+ * like the reference computes them in the variant's scalar type.
+ */
+#pragma once
+#include "b2vp.h"
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace b2vp {
+
+/* `Throw(...)` of the reference (include/mitsuba/core/logger.h) becomes this exception. */
+class Error : public std::runtime_error {
+public:
+    Error(int code, const std::string &what) : std::runtime_error(what), code_(code) {}
+    int code() const { return code_; }
+private:
+    int code_;
+};
+inline void check(int rc) {
+    if (rc != B2VP_OK) throw Error(rc, std::string("b2vp: ") + b2vp_last_error());
+}
+
+template <typename F> using Vec3 = std::array<F, 3>;
+template <typename F> inline Vec3<F> cross(const Vec3<F> &a, const Vec3<F> &b) {
+    return { a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0] };
+}
+template <typename F> inline F dot(const Vec3<F> &a, const Vec3<F> &b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename F> inline Vec3<F> normalize(const Vec3<F> &a) {
+    F n = std::sqrt(dot(a, a));
+    return { a[0] / n, a[1] / n, a[2] / n };
+}
+/* coordinate_system (include/mitsuba/core/vector.h:116-136) */
+template <typename F> inline void coordinate_system(const Vec3<F> &n, Vec3<F> &s, Vec3<F> &t) {
+    F sign = std::copysign((F) 1, n[2]);
+    F a = -(F) 1 / (sign + n[2]);
+    F b = n[0] * n[1] * a;
+    s = { n[0] * n[0] * a * sign + (F) 1, b * sign, -n[0] * sign };
+    t = { b, n[1] * n[1] * a + sign, -n[1] };
+}
+
+/* Column-major 4x4 (m[c*4+r]), the layout of enoki::Matrix and of B2vpMat4. */
+template <typename F> struct Mat4 {
+    F m[16];
+    Mat4() { for (int i = 0; i < 16; ++i) m[i] = (i % 5 == 0) ? (F) 1 : (F) 0; }
+    F &operator()(int r, int c) { return m[c * 4 + r]; }
+    F operator()(int r, int c) const { return m[c * 4 + r]; }
+    static Mat4 translate(F x, F y, F z) { Mat4 t; t(0, 3) = x; t(1, 3) = y; t(2, 3) = z; return t; }
+    static Mat4 scale(F x, F y, F z) { Mat4 t; t(0, 0) = x; t(1, 1) = y; t(2, 2) = z; return t; }
+    /* Transform::look_at (include/mitsuba/core/transform.h:262-283) */
+    static Mat4 look_at(const Vec3<F> &origin, const Vec3<F> &target, const Vec3<F> &up) {
+        Vec3<F> dir = normalize(Vec3<F>{ target[0] - origin[0], target[1] - origin[1], target[2] - origin[2] });
+        Vec3<F> left = normalize(cross(up, dir));
+        Vec3<F> new_up = cross(dir, left);
+        Mat4 t;
+        for (int r = 0; r < 3; ++r) { t(r, 0) = left[r]; t(r, 1) = new_up[r]; t(r, 2) = dir[r]; t(r, 3) = origin[r]; }
+        return t;
+    }
+    Mat4 operator*(const Mat4 &o) const {
+        Mat4 r;
+        for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 4; ++j) {
+                F s = 0;
+                for (int k = 0; k < 4; ++k) s += (*this)(i, k) * o(k, j);
+                r(i, j) = s;
+            }
+        return r;
+    }
+    Vec3<F> point(const Vec3<F> &p) const {   /* affine */
+        return { (*this)(0, 0) * p[0] + (*this)(0, 1) * p[1] + (*this)(0, 2) * p[2] + (*this)(0, 3),
+                 (*this)(1, 0) * p[0] + (*this)(1, 1) * p[1] + (*this)(1, 2) * p[2] + (*this)(1, 3),
+                 (*this)(2, 0) * p[0] + (*this)(2, 1) * p[1] + (*this)(2, 2) * p[2] + (*this)(2, 3) };
+    }
+    Vec3<F> vector(const Vec3<F> &v) const {
+        return { (*this)(0, 0) * v[0] + (*this)(0, 1) * v[1] + (*this)(0, 2) * v[2],
+                 (*this)(1, 0) * v[0] + (*this)(1, 1) * v[1] + (*this)(1, 2) * v[2],
+                 (*this)(2, 0) * v[0] + (*this)(2, 1) * v[1] + (*this)(2, 2) * v[2] };
+    }
+    /* general inverse by Gauss-Jordan with partial pivoting, evaluated in double */
+    Mat4 inverse() const {
+        double a[4][8];
+        for (int r = 0; r < 4; ++r)
+            for (int c = 0; c < 4; ++c) { a[r][c] = (double) (*this)(r, c); a[r][4 + c] = r == c ? 1.0 : 0.0; }
+        for (int c = 0; c < 4; ++c) {
+            int piv = c;
+            for (int r = c + 1; r < 4; ++r) if (std::fabs(a[r][c]) > std::fabs(a[piv][c])) piv = r;
+            if (a[piv][c] == 0.0) throw Error(B2VP_ERR_INVALID, "b2vp: singular transform");
+            if (piv != c) for (int k = 0; k < 8; ++k) std::swap(a[piv][k], a[c][k]);
+            double inv = 1.0 / a[c][c];
+            for (int k = 0; k < 8; ++k) a[c][k] *= inv;
+            for (int r = 0; r < 4; ++r)
+                if (r != c) { double f = a[r][c]; for (int k = 0; k < 8; ++k) a[r][k] -= f * a[c][k]; }
+        }
+        Mat4 o;
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) o(r, c) = (F) a[r][4 + c];
+        return o;
+    }
+    /* normals transform with the inverse transpose */
+    Vec3<F> normal(const Vec3<F> &n) const {
+        Mat4 it = inverse();
+        return { it(0, 0) * n[0] + it(1, 0) * n[1] + it(2, 0) * n[2], it(0, 1) * n[0] + it(1, 1) * n[1] + it(2, 1) * n[2],
+                 it(0, 2) * n[0] + it(1, 2) * n[1] + it(2, 2) * n[2] };
+    }
+    B2vpMat4 pod() const { B2vpMat4 o; for (int i = 0; i < 16; ++i) o.m[i] = (double) m[i]; return o; }
+};
+
+/* ---------------------------------------------------------------- plugins ----
+   One struct per scoped plugin: members are the plugin's properties with the reference's defaults. */
+
+/* src/phase/isotropic.cpp, rayleigh.cpp, hg.cpp:41 (g defaults to 0.8) */
+struct Phase {
+    int type = B2VP_PHASE_ISOTROPIC;
+    double g = 0.8;
+    static Phase isotropic() { return {}; }
+    static Phase rayleigh() { Phase p; p.type = B2VP_PHASE_RAYLEIGH; return p; }
+    static Phase hg(double g) {
+        if (!(g > -1 && g < 1)) throw Error(B2VP_ERR_INVALID, "The asymmetry parameter must lie in the interval (-1, 1)!");
+        Phase p; p.type = B2VP_PHASE_HG; p.g = g; return p;
+    }
+};
+/* src/textures/constant3d.cpp:13-55 */
+struct ConstVolume { double value = 1.0; };
+/* src/textures/grid3d.cpp:43-160: in-memory grid data[((z*ny+y)*nx+x)*channels+c], float32 as on disk */
+struct GridVolume {
+    std::vector<float> data;
+    int nx = 0, ny = 0, nz = 0, channels = 1;
+    std::string filter_type = "trilinear", wrap_mode = "clamp";
+    double max_value = -1;   /* < 0: the maximum of the data (grid3d.cpp:157-160) */
+};
+/* src/media/homogeneous.cpp:21-54 / heterogeneous.cpp:21-54, src/librender/medium.cpp:12-30 */
+struct Homogeneous { double sigma_t = 1.0, albedo = 0.75, scale = 1.0; bool has_spectral_extinction = true, sample_emitters = true; };
+struct Heterogeneous { double scale = 1.0; bool has_spectral_extinction = true, sample_emitters = true; };
+/* src/bsdfs/diffuse.cpp:70-76, null.cpp:30-39, rpv.cpp:66-83 (rho_c defaults to rho_0) */
+struct Diffuse { double reflectance = 0.5; };
+struct Null {};
+struct Rpv { double rho_0 = 0.1, k = 0.1, g = 0.0, rho_c = -1.0; };
+/* src/emitters/directional.cpp:45-73 */
+struct Directional { std::array<double, 3> direction{ 0, 0, 1 }; double irradiance = 1.0; };
+/* src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp */
+struct HdrFilm { int width = 768, height = 576; };
+struct IndependentSampler { uint32_t sample_count = 4; uint64_t seed = 0; };
+/* src/sensors/distant.cpp:225-290 */
+struct Distant {
+    std::array<double, 3> direction{ 0, 0, 1 };
+    bool has_orientation = false; std::array<double, 3> orientation{ 1, 0, 0 };
+    bool has_ray_target = false; std::array<double, 3> ray_target{ 0, 0, 0 };
+    bool flip_directions = false;
+    int medium = -1;
+};
+/* src/sensors/radiancemeter.cpp:61-104 */
+struct RadianceMeter { std::array<double, 3> origin{ 0, 0, 0 }, direction{ 0, 0, 1 }; int medium = -1; };
+/* src/integrators/volpath.cpp:19-25, src/librender/integrator.cpp:23-39,302-315 */
+struct Volpath { int max_depth = -1, rr_depth = 5; bool hide_emitters = false; uint32_t block_size = 0, samples_per_pass = 0xffffffffu; };
+
+/* A finished scene: owns the descriptor and every array it points to. */
+struct Scene {
+    B2vpSceneDesc desc{};
+    std::vector<B2vpShape> shapes; std::vector<B2vpBsdf> bsdfs; std::vector<B2vpMedium> media;
+    std::vector<B2vpVolume> volumes; std::vector<B2vpPhase> phases; std::vector<B2vpEmitter> emitters;
+    std::vector<float> vpos, vnrm, vuv; std::vector<uint32_t> faces;
+    std::vector<std::vector<float>> grids;
+    int width() const { return desc.sensor.crop_size[0]; }
+    int height() const { return desc.sensor.crop_size[1]; }
+};
+
+template <typename F> class SceneBuilder {
+public:
+    SceneBuilder() : sc_(new Scene()) {
+        for (int k = 0; k < 3; ++k) { bmin_[k] = std::numeric_limits<F>::infinity(); bmax_[k] = -bmin_[k]; }
+    }
+    int add_bsdf(const Diffuse &b) { return push_bsdf(B2VP_BSDF_DIFFUSE, (F) b.reflectance, 0, 0, 0); }
+    int add_bsdf(const Null &) { return push_bsdf(B2VP_BSDF_NULL, 0, 0, 0, 0); }
+    int add_bsdf(const Rpv &b) { return push_bsdf(B2VP_BSDF_RPV, (F) b.rho_0, (F) b.k, (F) b.g, (F) (b.rho_c < 0 ? b.rho_0 : b.rho_c)); }
+
+    int add_medium(const Homogeneous &m, const Phase &ph) {
+        B2vpMedium o{};
+        o.type = B2VP_MEDIUM_HOMOGENEOUS;
+        o.albedo = add_volume(ConstVolume{ m.albedo }); o.sigma_t = add_volume(ConstVolume{ m.sigma_t });
+        return push_medium(o, (F) m.scale, m.has_spectral_extinction, m.sample_emitters, ph);
+    }
+    /* sigma_t must be a grid (ConstVolume::max is not implemented in the reference, heterogeneous.cpp:29) */
+    int add_medium(const Heterogeneous &m, const GridVolume &sigma_t, const Mat4<F> &sigma_t_to_world, double albedo,
+                   const Phase &ph) {
+        B2vpMedium o{};
+        o.type = B2VP_MEDIUM_HETEROGENEOUS;
+        o.albedo = add_volume(ConstVolume{ albedo }); o.sigma_t = add_volume(sigma_t, sigma_t_to_world);
+        return push_medium(o, (F) m.scale, m.has_spectral_extinction, m.sample_emitters, ph);
+    }
+    int add_volume(const ConstVolume &v) {
+        B2vpVolume o{};
+        o.type = B2VP_VOLUME_CONST; o.channels = 1; o.value = (double) (F) v.value; o.max_value = o.value;
+        finish_volume(o, Mat4<F>());
+        return (int) sc_->volumes.size() - 1;
+    }
+    int add_volume(const GridVolume &v, const Mat4<F> &to_world) {
+        if ((size_t) v.nx * v.ny * v.nz * v.channels != v.data.size() || v.data.empty())
+            throw Error(B2VP_ERR_INVALID, "gridvolume: data size does not match the resolution");
+        if (v.channels != 1 && v.channels != 3) throw Error(B2VP_ERR_UNSUPPORTED, "Unsupported channel count (expected 1 or 3)");
+        B2vpVolume o{};
+        o.type = B2VP_VOLUME_GRID; o.channels = v.channels; o.res[0] = v.nx; o.res[1] = v.ny; o.res[2] = v.nz;
+        if (v.filter_type == "nearest") o.filter = B2VP_FILTER_NEAREST;
+        else if (v.filter_type == "trilinear") o.filter = B2VP_FILTER_TRILINEAR;
+        else throw Error(B2VP_ERR_INVALID, "Invalid filter type \"" + v.filter_type + "\"");
+        if (v.wrap_mode == "repeat") o.wrap = B2VP_WRAP_REPEAT;
+        else if (v.wrap_mode == "mirror") o.wrap = B2VP_WRAP_MIRROR;
+        else if (v.wrap_mode == "clamp") o.wrap = B2VP_WRAP_CLAMP;
+        else throw Error(B2VP_ERR_INVALID, "Invalid wrap mode \"" + v.wrap_mode + "\"");
+        sc_->grids.push_back(v.data);
+        o.data = sc_->grids.back().data();
+        o.max_value = v.max_value >= 0 ? (double) (F) v.max_value : (double) *std::max_element(v.data.begin(), v.data.end());
+        finish_volume(o, to_world);
+        return (int) sc_->volumes.size() - 1;
+    }
+
+    /* src/shapes/rectangle.cpp:75-104 */
+    int add_rectangle(const Mat4<F> &to_world, int bsdf, int interior = -1, int exterior = -1) {
+        B2vpShape s{};
+        s.type = B2VP_SHAPE_RECTANGLE; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
+        Vec3<F> dp_du = to_world.vector({ 2, 0, 0 }), dp_dv = to_world.vector({ 0, 2, 0 });
+        Vec3<F> n = normalize(to_world.normal({ 0, 0, 1 }));
+        Vec3<F> cr = cross(dp_du, dp_dv);
+        F area = std::sqrt(dot(cr, cr));
+        for (int k = 0; k < 3; ++k) { s.frame_s[k] = dp_du[k]; s.frame_t[k] = dp_dv[k]; s.frame_n[k] = n[k]; }
+        s.inv_surface_area = (double) ((F) 1 / area);
+        const F corners[4][3] = { { -1, -1, 0 }, { 1, -1, 0 }, { 1, 1, 0 }, { -1, 1, 0 } };
+        for (auto &c : corners) expand(to_world.point({ c[0], c[1], c[2] }));
+        s.to_world = to_world.pod(); s.to_object = to_world.inverse().pod();
+        sc_->shapes.push_back(s);
+        return (int) sc_->shapes.size() - 1;
+    }
+    /* in-memory triangle mesh in world space (what the obj / ply / serialized loaders produce,
+       src/librender/mesh.cpp): positions 3 floats per vertex, faces 3 indices per triangle */
+    int add_mesh(const std::vector<float> &positions, const std::vector<uint32_t> &faces, int bsdf, int interior = -1,
+                 int exterior = -1, const std::vector<float> *normals = nullptr, const std::vector<float> *texcoords = nullptr) {
+        if (positions.size() % 3 || faces.size() % 3) throw Error(B2VP_ERR_INVALID, "mesh: positions / faces must come in triples");
+        B2vpShape s{};
+        s.type = B2VP_SHAPE_MESH; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
+        const uint32_t nv = (uint32_t) (positions.size() / 3), nf = (uint32_t) (faces.size() / 3);
+        for (uint32_t i : faces) if (i >= nv) throw Error(B2VP_ERR_INVALID, "mesh: face index out of range");
+        s.vertex_offset = (uint32_t) (sc_->vpos.size() / 3); s.vertex_count = nv;
+        s.face_offset = (uint32_t) (sc_->faces.size() / 3); s.face_count = nf;
+        s.has_vertex_normals = normals != nullptr; s.has_vertex_texcoords = texcoords != nullptr;
+        sc_->vpos.insert(sc_->vpos.end(), positions.begin(), positions.end());
+        if (normals) sc_->vnrm.insert(sc_->vnrm.end(), normals->begin(), normals->end());
+        else sc_->vnrm.insert(sc_->vnrm.end(), positions.size(), 0.f);
+        if (texcoords) sc_->vuv.insert(sc_->vuv.end(), texcoords->begin(), texcoords->end());
+        else sc_->vuv.insert(sc_->vuv.end(), (size_t) nv * 2, 0.f);
+        sc_->faces.insert(sc_->faces.end(), faces.begin(), faces.end());
+        for (uint32_t v = 0; v < nv; ++v) expand({ (F) positions[3 * v], (F) positions[3 * v + 1], (F) positions[3 * v + 2] });
+        Mat4<F> id;
+        s.to_world = id.pod(); s.to_object = id.pod();
+        sc_->shapes.push_back(s);
+        return (int) sc_->shapes.size() - 1;
+    }
+    /* src/shapes/cube.cpp:54-116: 24 vertices, 12 triangles, face normals and texcoords; transformed in f32 */
+    int add_cube(const Mat4<F> &to_world, int bsdf, int interior = -1, int exterior = -1) {
+        static const float V[24][3] = { { 1, -1, -1 }, { 1, -1, 1 }, { -1, -1, 1 }, { -1, -1, -1 }, { 1, 1, -1 }, { -1, 1, -1 },
+            { -1, 1, 1 }, { 1, 1, 1 }, { 1, -1, -1 }, { 1, 1, -1 }, { 1, 1, 1 }, { 1, -1, 1 }, { 1, -1, 1 }, { 1, 1, 1 },
+            { -1, 1, 1 }, { -1, -1, 1 }, { -1, -1, 1 }, { -1, 1, 1 }, { -1, 1, -1 }, { -1, -1, -1 }, { 1, 1, -1 },
+            { 1, -1, -1 }, { -1, -1, -1 }, { -1, 1, -1 } };
+        static const float N[6][3] = { { 0, -1, 0 }, { 0, 1, 0 }, { 1, 0, 0 }, { 0, 0, 1 }, { -1, 0, 0 }, { 0, 0, -1 } };
+        static const float UV[4][2] = { { 0, 1 }, { 1, 1 }, { 1, 0 }, { 0, 0 } };
+        static const uint32_t T[12][3] = { { 0, 1, 2 }, { 3, 0, 2 }, { 4, 5, 6 }, { 7, 4, 6 }, { 8, 9, 10 }, { 11, 8, 10 },
+            { 12, 13, 14 }, { 15, 12, 14 }, { 16, 17, 18 }, { 19, 16, 18 }, { 20, 21, 22 }, { 23, 20, 22 } };
+        Mat4<float> tw;
+        for (int i = 0; i < 16; ++i) tw.m[i] = (float) to_world.m[i];
+        std::vector<float> p, n, uv;
+        std::vector<uint32_t> f;
+        for (int v = 0; v < 24; ++v) {
+            Vec3<float> q = tw.point({ V[v][0], V[v][1], V[v][2] });
+            Vec3<float> m = normalize(tw.normal({ N[v / 4][0], N[v / 4][1], N[v / 4][2] }));
+            p.insert(p.end(), q.begin(), q.end()); n.insert(n.end(), m.begin(), m.end());
+            uv.push_back(UV[v % 4][0]); uv.push_back(UV[v % 4][1]);
+        }
+        for (auto &t : T) f.insert(f.end(), t, t + 3);
+        return add_mesh(p, f, bsdf, interior, exterior, &n, &uv);
+    }
+    void add_emitter(const Directional &e) {
+        Vec3<F> d = normalize(Vec3<F>{ (F) e.direction[0], (F) e.direction[1], (F) e.direction[2] });
+        Vec3<F> up, t;
+        coordinate_system(d, up, t);
+        Mat4<F> tw = Mat4<F>::look_at({ 0, 0, 0 }, d, up);
+        Vec3<F> z = tw.vector({ 0, 0, 1 });
+        B2vpEmitter o{};
+        o.type = B2VP_EMITTER_DIRECTIONAL; o.irradiance = (double) (F) e.irradiance;
+        for (int k = 0; k < 3; ++k) o.direction[k] = z[k];
+        sc_->emitters.push_back(o);
+    }
+    void set_sensor(const Distant &sn, const HdrFilm &film, const IndependentSampler &sampler) {
+        B2vpSensor o = base_sensor(film, sampler, sn.medium);
+        o.type = B2VP_SENSOR_DISTANT; o.flip_directions = sn.flip_directions; o.needs_aperture_sample = 1;
+        o.direction_type = (film.width == 1 && film.height == 1) ? B2VP_DIR_SINGLE
+                           : film.height == 1 ? B2VP_DIR_SAMPLE_WIDTH : B2VP_DIR_SAMPLE_ALL;
+        Vec3<F> d = normalize(Vec3<F>{ (F) sn.direction[0], (F) sn.direction[1], (F) sn.direction[2] });
+        Vec3<F> up, tmp;
+        if (sn.has_orientation)
+            up = normalize(cross(d, Vec3<F>{ (F) sn.orientation[0], (F) sn.orientation[1], (F) sn.orientation[2] }));
+        else
+            coordinate_system(d, tmp, up);
+        o.to_world = Mat4<F>::look_at({ 0, 0, 0 }, d, up).pod();
+        o.target_type = sn.has_ray_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
+        for (int k = 0; k < 3; ++k) o.target_point[k] = (double) (F) sn.ray_target[k];
+        o.origin_type = B2VP_ORIGIN_BSPHERE;
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
+    void set_sensor(const RadianceMeter &sn, const IndependentSampler &sampler) {
+        B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
+        o.type = B2VP_SENSOR_RADIANCEMETER; o.needs_aperture_sample = 0;
+        Vec3<F> org{ (F) sn.origin[0], (F) sn.origin[1], (F) sn.origin[2] }, d{ (F) sn.direction[0], (F) sn.direction[1], (F) sn.direction[2] };
+        Vec3<F> up, tmp;
+        coordinate_system(d, up, tmp);
+        o.to_world = Mat4<F>::look_at(org, { org[0] + d[0], org[1] + d[1], org[2] + d[2] }, up).pod();
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
+    void set_integrator(const Volpath &v) {
+        if (v.max_depth < -1) throw Error(B2VP_ERR_INVALID, "\"max_depth\" must be set to -1 (infinite) or a value >= 0");
+        if (v.rr_depth <= 0) throw Error(B2VP_ERR_INVALID, "\"rr_depth\" must be set to a value greater than zero!");
+        B2vpIntegrator &it = sc_->desc.integrator;
+        it.max_depth = v.max_depth; it.rr_depth = v.rr_depth; it.hide_emitters = v.hide_emitters;
+        it.block_size = v.block_size; it.samples_per_pass = v.samples_per_pass; it.arg_order_ltr = 0;
+        have_integrator_ = true;
+    }
+
+    /* Scene::bbox() and its bounding sphere with the padding of distant.cpp:292-297 / directional.cpp:68-73 */
+    std::unique_ptr<Scene> finish() {
+        if (!have_sensor_) throw Error(B2VP_ERR_INVALID, "scene has no sensor");
+        if (!have_integrator_) set_integrator(Volpath{});
+        Scene &s = *sc_;
+        B2vpSceneDesc &d = s.desc;
+        d.abi_version = B2VP_ABI_VERSION; d.struct_size = (uint32_t) sizeof(B2vpSceneDesc);
+        d.precision = std::is_same<F, float>::value ? B2VP_PREC_F32 : B2VP_PREC_F64;
+        d.n_shapes = (uint32_t) s.shapes.size(); d.shapes = s.shapes.data();
+        d.n_bsdfs = (uint32_t) s.bsdfs.size(); d.bsdfs = s.bsdfs.data();
+        d.n_media = (uint32_t) s.media.size(); d.media = s.media.data();
+        d.n_volumes = (uint32_t) s.volumes.size(); d.volumes = s.volumes.data();
+        d.n_phases = (uint32_t) s.phases.size(); d.phases = s.phases.data();
+        d.n_emitters = (uint32_t) s.emitters.size(); d.emitters = s.emitters.data();
+        d.n_vertices = (uint32_t) (s.vpos.size() / 3); d.n_faces = (uint32_t) (s.faces.size() / 3);
+        if (d.n_vertices) {
+            d.vertex_positions = s.vpos.data(); d.vertex_normals = s.vnrm.data();
+            d.vertex_texcoords = s.vuv.data(); d.faces = s.faces.data();
+        }
+        /* grid pointers: the vectors may have moved while volumes were added */
+        size_t gi = 0;
+        for (auto &v : s.volumes) if (v.type == B2VP_VOLUME_GRID) v.data = s.grids[gi++].data();
+        if (!(bmin_[0] <= bmax_[0])) for (int k = 0; k < 3; ++k) bmin_[k] = bmax_[k] = 0;
+        Vec3<F> c, df;
+        for (int k = 0; k < 3; ++k) { c[k] = (bmax_[k] + bmin_[k]) * (F) 0.5; df[k] = c[k] - bmax_[k]; }
+        F radius = std::sqrt(df[0] * df[0] + df[1] * df[1] + df[2] * df[2]);
+        const F ray_eps = std::numeric_limits<F>::epsilon() / (F) 2 * (F) 1500;
+        radius = std::max(ray_eps, radius * ((F) 1 + ray_eps));
+        for (int k = 0; k < 3; ++k) { d.bbox_min[k] = bmin_[k]; d.bbox_max[k] = bmax_[k]; d.bsphere_center[k] = c[k]; }
+        d.bsphere_radius = radius;
+        return std::move(sc_);
+    }
+
+private:
+    int push_bsdf(int type, F p0, F p1, F p2, F p3) {
+        B2vpBsdf b{};
+        b.type = type; b.p[0] = p0; b.p[1] = p1; b.p[2] = p2; b.p[3] = p3;
+        sc_->bsdfs.push_back(b);
+        return (int) sc_->bsdfs.size() - 1;
+    }
+    int push_medium(B2vpMedium o, F scale, bool spectral, bool sample_emitters, const Phase &ph) {
+        B2vpPhase p{};
+        p.type = ph.type; p.g = (double) (F) ph.g;
+        sc_->phases.push_back(p);
+        o.phase = (int) sc_->phases.size() - 1;
+        o.scale = scale; o.has_spectral_extinction = spectral; o.sample_emitters = sample_emitters;
+        sc_->media.push_back(o);
+        return (int) sc_->media.size() - 1;
+    }
+    /* Volume base class: world_to_local = to_world^-1, bbox = image of the unit cube (texture.h:265-272) */
+    void finish_volume(B2vpVolume &o, const Mat4<F> &to_world) {
+        Mat4<F> w2l = to_world.inverse();
+        o.world_to_local = w2l.pod();
+        Vec3<F> a = to_world.point({ 0, 0, 0 }), b = to_world.point({ 1, 1, 1 });
+        for (int k = 0; k < 3; ++k) { o.bbox_min[k] = std::min(a[k], b[k]); o.bbox_max[k] = std::max(a[k], b[k]); }
+        sc_->volumes.push_back(o);
+    }
+    B2vpSensor base_sensor(const HdrFilm &film, const IndependentSampler &sampler, int medium) {
+        B2vpSensor o{};
+        o.film_size[0] = o.crop_size[0] = film.width; o.film_size[1] = o.crop_size[1] = film.height;
+        o.sample_count = sampler.sample_count; o.sampler_seed = sampler.seed;
+        o.medium = medium; o.target_shape = o.origin_shape = -1;
+        o.to_world = Mat4<F>().pod();
+        return o;
+    }
+    void expand(const Vec3<F> &p) { for (int k = 0; k < 3; ++k) { bmin_[k] = std::min(bmin_[k], p[k]); bmax_[k] = std::max(bmax_[k], p[k]); } }
+
+    std::unique_ptr<Scene> sc_;
+    F bmin_[3], bmax_[3];
+    bool have_sensor_ = false, have_integrator_ = false;
+};
+
+/* The film of one render: crop_size x 5 channels (X, Y, Z, A, W), ImageBlock layout (imageblock.cpp). */
+struct Film {
+    int width = 0, height = 0, precision = B2VP_PREC_F32;
+    std::vector<float> f32; std::vector<double> f64;
+    B2vpCounters totals{};
+    double at(int x, int y, int ch) const {
+        size_t i = ((size_t) y * width + x) * 5 + ch;
+        return precision == B2VP_PREC_F32 ? (double) f32[i] : f64[i];
+    }
+    /* HDRFilm::bitmap for pixel_format=luminance: Y / W (hdrfilm.cpp:251-321) */
+    double luminance(int x, int y) const { double w = at(x, y, 4); return w > 0 ? at(x, y, 1) / w : 0.0; }
+};
+
+/* A scene resident on one CUDA device: b2vp_scene_create .. b2vp_scene_destroy. */
+class DeviceScene {
+public:
+    DeviceScene(std::unique_ptr<Scene> scene, int device = 0) : scene_(std::move(scene)), device_(device) {
+        check(b2vp_scene_create(&scene_->desc, device, &h_));
+    }
+    ~DeviceScene() { if (h_) b2vp_scene_destroy(h_); }
+    DeviceScene(const DeviceScene &) = delete;
+    DeviceScene &operator=(const DeviceScene &) = delete;
+    const Scene &scene() const { return *scene_; }
+    /* Integrator::render: all streams of the seeding mode, or the range [first, first + n) */
+    Film render(int seed_mode = B2VP_SEED_WAVEFRONT, uint64_t first_stream = 0, uint64_t n_streams = 0) {
+        Film f;
+        f.width = scene_->width(); f.height = scene_->height(); f.precision = scene_->desc.precision;
+        size_t n = (size_t) f.width * f.height * 5;
+        void *buf;
+        if (f.precision == B2VP_PREC_F32) { f.f32.assign(n, 0.f); buf = f.f32.data(); }
+        else { f.f64.assign(n, 0.0); buf = f.f64.data(); }
+        B2vpRenderArgs a{};
+        a.abi_version = B2VP_ABI_VERSION; a.struct_size = (uint32_t) sizeof(a);
+        a.precision = f.precision; a.seed_mode = seed_mode; a.device = device_;
+        a.first_stream = first_stream; a.n_streams = n_streams; a.clear_film = 1; a.totals = &f.totals;
+        check(b2vp_render(h_, &a, buf));
+        return f;
+    }
+    void cancel() { b2vp_cancel(h_); }   /* Integrator::cancel (integrator.h:51) */
+private:
+    std::unique_ptr<Scene> scene_;
+    int device_ = 0;
+    b2vp_scene_t *h_ = nullptr;
+};
+
+} // namespace b2vp
