@@ -590,7 +590,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                             c.result += nee_w * ev;
                         }
                     }
-                } else { /* Q_SURF_B: BSDF sampling (volpath.cpp:214-241) */
+                }
+                /* no emitter march was started (null BSDF, or nothing to sample): go on in the same visit */
+                if (state == Q_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> bwo;
