@@ -508,7 +508,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                             c.result += nee_w * ev;
                         }
                     }
-                } else { /* Q_SCATTER_B: phase function sampling (volpath.cpp:170-176) */
+                }
+                /* no emitter march was started: sample the phase function in the same visit */
+                if (state == Q_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
                     const DPhase<F> &phase_fn = sv.phases[m.phase];
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s2x = ltr ? db : da, s2y = ltr ? dc : db;

@@ -124,3 +124,44 @@ def test_cuda_matches_golden_fixtures(pkg):
         assert r.counters.tolist() == g["counters"], name
         bits = r.radiance.view(np.uint32 if r.radiance.dtype == np.float32 else np.uint64).ravel()
         assert [int(x) for x in bits] == g["radiance_bits"], name
+
+
+def test_full_size_c2_properties(pkg, oracle):
+    """BASELINE configs[1] at the size bench.py times (256 x 1 film, 2^14 spp = 4 194 304 paths), checked through
+    size-independent properties: the event counters of any partition of the stream space add up exactly to those
+    of the whole render, the films add up to summation accuracy, every pixel received exactly spp samples, and the
+    image agrees with the oracle's estimate from an independent subsample of the same streams."""
+    abi = pkg.abi
+    spp, width = 16384, 256
+    sc = pkg.load_dict(scenes.c2(spp=spp, width=width))
+    keys = ("n_paths", "n_rng_draws", "n_medium_steps", "n_null", "n_real", "n_intersect", "n_surface", "n_invalid_samples")
+    with pkg.DeviceScene(sc) as ds:
+        n, _ = ds.stream_count(abi.SEED_WAVEFRONT)
+        assert n == spp * width
+        full = ds.render(seed_mode=abi.SEED_WAVEFRONT)
+        cuts = [0, n // 3, n // 3 + 12345, n]
+        parts = [ds.render(seed_mode=abi.SEED_WAVEFRONT, first_stream=a, n_streams=b - a) for a, b in zip(cuts, cuts[1:])]
+        again = ds.render(seed_mode=abi.SEED_WAVEFRONT)
+    for k in keys:
+        assert sum(getattr(p.totals, k) for p in parts) == getattr(full.totals, k), k
+        assert getattr(again.totals, k) == getattr(full.totals, k), k          # idempotent
+    assert full.totals.n_paths == n and full.totals.n_invalid_samples == 0
+    # W counts samples: spp per pixel, except that in float32 `pixel + u` rounds up to the next pixel for u close
+    # to 1 (integrator.cpp:240-246 adds them in Float), which moves a sample to the neighbour -- the total is exact
+    assert float(full.film[..., 4].astype(np.float64).sum()) == n
+    assert np.all(np.abs(full.film[..., 4] - spp) <= 4)
+    assert np.all(full.film[..., 3] <= full.film[..., 4])                           # alpha <= weight
+    assert np.allclose(sum(p.film.astype(np.float64) for p in parts), full.film, rtol=2e-4, atol=1e-6)
+    assert np.allclose(again.film, full.film, rtol=2e-4, atol=1e-6)
+    # oracle estimate from every 64th sample of each pixel (same streams, so the same expectation)
+    sub = 256
+    ranges = [(px * spp + j * (spp // sub), 1) for px in range(0, width, 16) for j in range(sub)]
+    est = {}
+    for a, cnt in ranges:
+        r = oracle.render(pkg, sc, abi.SEED_WAVEFRONT, first_stream=a, n_streams=cnt)
+        px = a // spp
+        est.setdefault(px, []).append(float(r.film[0, px, 1]))
+    for px, vals in est.items():
+        mean, sem = np.mean(vals), np.std(vals) / np.sqrt(len(vals))
+        got = full.film[0, px, 1] / spp
+        assert abs(got - mean) < 5 * sem + 1e-4, (px, got, mean, sem)

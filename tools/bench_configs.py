@@ -1,6 +1,6 @@
 """Full-size runs of the BASELINE configurations other than the one `bench.py` quotes (C1, C3, C5).
 GPU box only.  Prints one JSON line per configuration: device-timed Mpaths/s, ray segments/s, algorithmic
-grid bytes (C3) and the wall time of scene upload.  usage: python tools/bench_configs.py [c1] [c3] [c5]"""
+grid bytes (C3) and the wall time of scene upload.  usage: python tools/bench_configs.py [c1] [c3] [c4] [c5]"""
 import json, os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -11,9 +11,9 @@ import scenes
 abi = pkg.abi
 
 
-def run(name, desc, scene_dict, reps=2, extra=None):
+def run(name, desc, scene_dict, reps=2, extra=None, variant="scalar_mono"):
     t0 = time.perf_counter()
-    scene = pkg.load_dict(scene_dict)
+    scene = pkg.load_dict(scene_dict, variant)
     t1 = time.perf_counter()
     with pkg.DeviceScene(scene, device=0) as ds:
         t2 = time.perf_counter()
@@ -51,3 +51,33 @@ if "c3" in which:
 if "c5" in which:
     run("C5", "canopy 1e6 triangles (BVH), homogeneous Rayleigh slab, diffuse leaves, mradiancemeter 4096, 256 spp",
         scenes.c5(spp=256, n_leaves=500000, n_sensors=4096))
+if "c4" in which:
+    # mono spectral sweep: 64 wavelengths x the C2 atmosphere; per wavelength only scalars change (Rayleigh
+    # extinction ~ lambda^-4, RPV rho_0(lambda)), applied with b2vp_scene_update -- no re-upload, no rebuild.
+    # 2^20 paths per wavelength here (BASELINE: 1e8 per wavelength over 8 GPUs; the rate is what is measured).
+    import time as _t
+    spp, width, n_wl = 4096, 256, 64
+    d = scenes.c2(spp=spp, width=width)
+    scene = pkg.load_dict(d)
+    base_scale = d["atm"]["scale"]
+    wl = np.linspace(400.0, 1000.0, n_wl)
+    films = np.zeros((n_wl, width, 5), np.float32)
+    rho0 = lambda lam: float(np.float32(0.05 + 0.25 * (lam - 400.0) / 600.0))
+    with pkg.DeviceScene(scene, device=0) as ds:
+        ds.render(seed_mode=abi.SEED_WAVEFRONT)
+        t0 = _t.perf_counter()
+        k_ms, paths, segs = 0.0, 0, 0
+        for i, lam in enumerate(wl):
+            ds.update(medium=0, medium_scale=float(np.float32(base_scale * (550.0 / lam) ** 4)),
+                      bsdf=1, bsdf_p=(rho0(lam), 0.7, -0.1, rho0(lam)))
+            r = ds.render(seed_mode=abi.SEED_WAVEFRONT)
+            films[i] = r.film[0]
+            k_ms += r.totals.gpu_ms; paths += r.totals.n_paths; segs += r.totals.n_medium_steps + r.totals.n_intersect
+        wall = _t.perf_counter() - t0
+    print(json.dumps({"config": "C4", "workload": "%d wavelengths x C2 (256x1, %d spp), scene_update per wavelength" % (n_wl, spp),
+                      "paths": paths, "kernel_ms": k_ms, "wall_ms": wall * 1e3, "mpaths_s": paths / (k_ms * 1e-3) / 1e6,
+                      "mpaths_s_wall": paths / wall / 1e6, "segments_per_s": segs / (k_ms * 1e-3),
+                      "mean_radiance_400nm": float(films[0, :, 1].sum() / films[0, :, 4].sum()),
+                      "mean_radiance_1000nm": float(films[-1, :, 1].sum() / films[-1, :, 4].sum())}), flush=True)
+if "c2f64" in which:
+    run("C2-f64", "C2 in scalar_mono_double, 256x1, 2048 spp", scenes.c2(spp=2048, width=256, variant="scalar_mono_double"), variant="scalar_mono_double")
