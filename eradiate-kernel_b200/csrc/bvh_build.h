@@ -20,11 +20,11 @@ namespace vp {
 struct BuildTri { float bmin[3], bmax[3], c[3]; uint32_t shape, face; };
 
 inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNode> &nodes,
-                      std::vector<BvhPrim> &prims) {
+                      std::vector<BvhPrim> &prims, int max_leaf = 4) {
     nodes.clear();
     prims.clear();
     if (tris.empty()) return;
-    const int NB = 16, MAX_LEAF = 4;
+    const int NB = 16, MAX_LEAF = std::min(std::max(max_leaf, 1), 7);
     nodes.reserve(tris.size());
     prims.reserve(tris.size());
     struct Task { uint32_t node, lo, hi, depth; };
