@@ -131,6 +131,7 @@ template <typename F> struct DeviceScene {
     std::vector<std::unique_ptr<DevBuf>> grids;
     std::vector<unsigned char> host_blob;  /* kept for scene_update */
     uint32_t smem_static = 0;              /* blob + staged grids */
+    size_t global_grid_bytes = 0;          /* grids gathered from HBM / L2 (not staged in shared memory) */
     bool ready = false;
 };
 
@@ -427,12 +428,15 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
 
     /* decide which grids are staged in shared memory */
     uint32_t grid_off = 0;
+    ds.global_grid_bytes = 0;
     for (size_t i = 0; i < volumes.size(); ++i) {
         DVolume<F> &v = volumes[i];
         if (v.type != 1) continue;
         if (g.blob_bytes + FILM_SMEM_MAX + grid_off + v.data_bytes <= SMEM_BUDGET) {
             v.smem_offset = (int) grid_off;
             grid_off += (uint32_t) v.data_bytes;
+        } else {
+            ds.global_grid_bytes += v.data_bytes;
         }
     }
     g.grid_smem_bytes = grid_off;
@@ -698,15 +702,19 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     Kern kern = pick_queue_kernel<F, 512>(ds.g.features, &preset);
     int threads = 512;
     bool queue_kernel = true;
-    double oversub = 4.0;   /* path slots per thread; in practice the shared memory left sets the pool size */
+    /* path slots per thread.  With everything hot on chip the shared memory left sets the pool size (the more
+       paths, the longer a CTA stays in one phase).  When large grids are gathered through L2 the cold path
+       records compete with them for it: measured on 2 x 256^3 grids, 2 slots per thread give 90 Mpaths/s,
+       3 and more 56. */
+    double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
     if (const char *e = std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(ds.g.features, &preset); threads = 256; }
         else if (!std::strcmp(e, "q384")) { threads = 384; }
 #ifdef B2VP_EXPERIMENT
-        else if (!std::strcmp(e, "q768")) { kern = volpath_q_kernel<F, 768, PRE_HET>; threads = 768; }
-        else if (!std::strcmp(e, "q1024")) { kern = volpath_q_kernel<F, 1024, PRE_HET>; threads = 1024; }
+        else if (!std::strcmp(e, "q768")) { kern = volpath_q_kernel<F, 768, PRE_HET_ALB>; threads = 768; }
+        else if (!std::strcmp(e, "q1024")) { kern = volpath_q_kernel<F, 1024, PRE_HET_ALB>; threads = 1024; }
 #endif
     }
     if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= threads && t % 32 == 0) threads = t; }
