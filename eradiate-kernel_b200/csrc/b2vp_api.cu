@@ -382,6 +382,11 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
             const DVolume<F> &v = volumes[a.sigma_t];
             o.max_density = o.scale * v.max_value; /* heterogeneous.cpp:29 */
             for (int k = 0; k < 3; ++k) { o.amin[k] = v.bmin[k]; o.amax[k] = v.bmax[k]; }
+            /* same grid geometry for sigma_t and albedo: one index computation serves both (volume_eval_pair) */
+            const DVolume<F> &b = volumes[a.albedo];
+            o.paired = v.type == 1 && b.type == 1 && v.filter == B2VP_FILTER_TRILINEAR && b.filter == B2VP_FILTER_TRILINEAR &&
+                       v.channels == 1 && b.channels == 1 && v.wrap == b.wrap && v.nx == b.nx && v.ny == b.ny &&
+                       v.nz == b.nz && std::memcmp(v.w2l, b.w2l, sizeof(v.w2l)) == 0;
         }
     }
 

@@ -233,6 +233,7 @@ template <typename F> struct DVolume {
 template <typename F> struct DMedium {
     int type, sigma_t, albedo, phase;
     int spectral, sample_emitters;
+    int paired, pad0;                /* sigma_t and albedo are single-channel trilinear grids of the same geometry */
     F scale, max_density;            /* heterogeneous.cpp:29 */
     F amin[3], amax[3];              /* heterogeneous.cpp:30 */
 };
