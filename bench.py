@@ -255,7 +255,7 @@ def run_ours(args):
             pass
         roofline = {"bound": "fp32", "achieved": achieved, "peak": fp32.value, "unit": "TFLOP/s",
                     "frac": achieved / fp32.value if fp32.value else None, "traffic": traffic,
-                    "kernel": "vp::volpath_q_kernel<float, 512, FT_HETERO|FT_TRILINEAR>", "kernel_ms": k_ms,
+                    "kernel": "vp::volpath_q_kernel<float, 512, FT_HETERO|FT_TRILINEAR|FT_RECT|FT_MESH|FT_MESH_ATTR>", "kernel_ms": k_ms,
                     "algorithmic": "%d medium steps x %d flop" % (tot_last.n_medium_steps, FLOP_PER_SEGMENT),
                     "peak_source": "b2vp_measure_fp32_peak (FMA microbenchmark, measured in this run); "
                                    "HBM peak %s GB/s (MEASURED_PEAKS.json) is not the bound here: the grid "
