@@ -198,12 +198,13 @@ def run_ours(args):
     clk = clocks.stop() if rank == 0 else None
     t = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
     segs = torch.tensor([float(tot_last.n_medium_steps + tot_last.n_intersect), float(tot_last.n_medium_steps),
-                         float(sum(kern_ms) / len(kern_ms))], dtype=torch.float64, device="cuda")
+                         float(sum(kern_ms) / len(kern_ms)), float(launches)], dtype=torch.float64, device="cuda")
     seg_sum = segs.clone()
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(seg_sum, op=dist.ReduceOp.SUM)
     total_ms = float(t.item())
+    launches = int(seg_sum[3].item())   # kernels launched by all ranks inside the timed region
     ms_per_step = total_ms / args.steps
     paths_per_step = per_gpu * n_gpus
     value = paths_per_step / (ms_per_step * 1e-3) / 1e6

@@ -256,8 +256,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             const int c = lane < PH_N ? ((volatile int *) ctl->avail)[lane] : 0;
             int key = lane < PH_N ? ((c << 3) | lane) : 0;
             if (lane == cur_phase && c >= 32) key |= 1 << 29;
+            /* when the CTA has to move on, full batches of the ray-making phases go before STEP: they run back
+               to back (they share ray_intersect's code) and STEP then runs long on everything they fed it */
+            if (out.q_cta_phase == 2 && lane != PH_STEP && lane < PH_N && c >= 32) key |= 1 << 28;
             const int top = __reduce_max_sync(FULL, key);
-            const int ph = top & 7, cnt = (top & ~(1 << 29)) >> 3;
+            const int ph = top & 7, cnt = (top & ~(3 << 28)) >> 3;
             if (cnt == 0) break;
             const int take = cnt < 32 ? cnt : 32;
             int ok = 0;
