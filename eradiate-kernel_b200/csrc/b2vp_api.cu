@@ -742,7 +742,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         out.q_slots_offset = (uint32_t) (base + qbytes);
         out.q_n_slots = (uint32_t) n_slots;
         out.q_ring_cap = (uint32_t) cap;
-        out.q_stay_min = 28; out.q_max_iter = 8;
+        out.q_stay_min = 26; out.q_max_iter = 8;
         /* 2: when the CTA moves on, the ray-making phases are served before STEP (+4 % with everything on chip);
            1: plain fullest-queue order, better when STEP is bound by gather latency (large grids: 93 vs 84 Mpaths/s) */
         out.q_cta_phase = ds.global_grid_bytes > ((size_t) 16 << 20) ? 1u : 2u;
