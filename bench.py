@@ -72,6 +72,29 @@ def cpu_time_sample(pkg, scene, budget_s, threads):
             "pilot_mpaths_s_1thread": rate1 / 1e6, "pilot": pilot}
 
 
+def ref_time_sample(pkg, budget_s, threads):
+    """Times the UNMODIFIED reference (oracle/_ref/refprobe, compiled from /root/reference by oracle/Makefile.ref;
+    scalar_mono, TBB with `threads` threads) on the workload at a reduced sample count chosen to take about
+    `budget_s` seconds.  The time is that of Integrator::render (the reference's "Processing finished (took ..)"
+    interval): scene loading and kd-tree build are outside it.  Returns None where the reference is not built."""
+    from oracle import ref_xml
+    if not ref_xml.available():
+        return None
+    import tempfile
+    with tempfile.TemporaryDirectory(prefix="b2vp_refbench_") as tmp:
+        def run(spp):
+            d = ref_xml.round_f32(workload(spp))
+            _, sec = ref_xml.render(d, "scalar_mono", threads=threads, write_vol=pkg.scene.write_vol, keep_dir=tmp)
+            return sec
+        pilot_spp = 64
+        t = max(run(pilot_spp), 1e-4)
+        spp = int(min(16384, max(pilot_spp, pilot_spp * budget_s / t)))
+        spp = 1 << (spp.bit_length() - 1)   # a power of two like the workload's 2^14
+        sec = run(spp)
+    n = WIDTH * spp
+    return {"paths": n, "seconds": sec, "mpaths_s": n / sec / 1e6, "spp": spp}
+
+
 class ClockSampler:
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
@@ -107,8 +130,9 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- arms
 def run_reference(args):
-    """Reference arm: the CPU restatement of the reference's scalar_mono volpath (oracle/, kind 'port': the
-    reference itself needs its cmake build system) on all host threads."""
+    """Reference arm: the reference's own CPU implementation of the path on all host threads.  Where oracle/_ref
+    is built (kind 'reference') that is the unmodified reference binary; otherwise the CPU restatement (oracle/,
+    kind 'port')."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -117,22 +141,34 @@ def run_reference(args):
     threads = host_threads()
     scene = pkg.load_dict(workload(args.spp))
     per_step = max(2.0, min(10.0, 120.0 / (args.steps + args.warmup)))
-    res = []
+    res, kind = [], "port"
     for i in range(args.warmup + args.steps):
-        r = cpu_time_sample(pkg, scene, per_step, threads)
+        r = ref_time_sample(pkg, per_step, threads)
+        if r is not None:
+            kind = "reference"
+        else:
+            r = cpu_time_sample(pkg, scene, per_step, threads)
         if i >= args.warmup:
             res.append(r)
     paths = sum(r["paths"] for r in res)
     secs = sum(r["seconds"] for r in res)
     v = paths / secs / 1e6
-    seg = sum(r["segments_s"] * r["seconds"] for r in res) / secs
-    sample = "%d of %d streams of the workload per step (64+ chunks spread evenly over the film), %d threads" % (res[0]["paths"], WIDTH * args.spp, threads)
+    # ray segments per path of this workload, counted by the instrumented restatement on a small sample
+    from oracle import oracle
+    pilot = oracle.render(pkg, scene, pkg.abi.SEED_WAVEFRONT, first_stream=0, n_streams=8192).totals
+    seg = v * 1e6 * (pilot.n_medium_steps + pilot.n_intersect) / pilot.n_paths
+    if kind == "reference":
+        sample = ("the workload at %d spp (%d paths) per step, unmodified reference binary (oracle/_ref/refprobe, "
+                  "scalar_mono, TBB %d threads), time of Integrator::render" % (res[0]["spp"], res[0]["paths"], threads))
+    else:
+        sample = "%d of %d streams of the workload per step (64+ chunks spread evenly over the film), %d threads" % (
+            res[0]["paths"], WIDTH * args.spp, threads)
     print(json.dumps({
         "impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / len(res) * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "segments_per_s": seg, "config": config(args.spp, args.gpus),
-        "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -264,6 +300,7 @@ def run_ours(args):
         # ---- CPU baseline beside it (bounded sample, all host threads)
         threads = host_threads()
         cb = cpu_time_sample(pkg, pkg.load_dict(workload(args.spp)), 0.2 if args.profile else 8.0, threads)
+        rb = None if args.profile else ref_time_sample(pkg, 8.0, threads)
         out = {
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -278,6 +315,13 @@ def run_ours(args):
                              "segments_per_s": cb["segments_s"],
                              "one_thread_mpaths_s": cb["pilot_mpaths_s_1thread"]},
         }
+        if rb is not None:  # the unmodified reference binary is built on this box: it is the baseline, the port is kept beside it
+            out["cpu_baseline"] = {"value": rb["mpaths_s"], "unit": "Mpaths/s", "cores": threads, "kind": "reference",
+                                   "sample": "the workload at %d spp (%d paths), unmodified reference binary "
+                                             "(oracle/_ref/refprobe, scalar_mono, TBB %d threads), %.1f s of "
+                                             "Integrator::render" % (rb["spp"], rb["paths"], threads, rb["seconds"]),
+                                   "port_mpaths_s": cb["mpaths_s"], "port_segments_per_s": cb["segments_s"],
+                                   "port_one_thread_mpaths_s": cb["pilot_mpaths_s_1thread"]}
         print(json.dumps(out))
     ds.close()
     if world > 1:

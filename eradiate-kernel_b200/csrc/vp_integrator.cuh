@@ -201,7 +201,7 @@ template <typename F> struct PathCtx {
         for (;;) {
             /* termination / Russian roulette (volpath.cpp:72-87) */
             active = active && throughput != 0;
-            F q = min_(throughput * sqr(eta), (F) 0.95);
+            F q = min_(throughput * sqr(eta), (F) 0.95f);
             bool perform_rr = depth > rr_depth;
             F rr_sample = next_1d(active);
             active = active && (rr_sample < q || !perform_rr);

@@ -135,7 +135,7 @@ template <typename F> VP_D void copy_ctx(MarchCtx<F> &dst, const MarchCtx<F> &sr
 template <typename F>
 VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth, uint32_t max_depth) {
     bool active = w != 0;
-    F q = min_(w * sqr(eta), (F) 0.95);
+    F q = min_(w * sqr(eta), (F) 0.95f);
     bool perform_rr = depth > rr_depth;
     F rr_sample = rng.next(F(), active);
     active = active && (rr_sample < q || !perform_rr);

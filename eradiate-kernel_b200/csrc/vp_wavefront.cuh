@@ -173,7 +173,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 if (mode == M_MAIN) {
                     /* termination / Russian roulette (volpath.cpp:72-87) */
                     bool active = throughput != 0;
-                    F q = min_(throughput * sqr(eta), (F) 0.95);
+                    F q = min_(throughput * sqr(eta), (F) 0.95f);
                     bool perform_rr = depth > rr_depth;
                     F rr_sample = next_1d(active);
                     active = active && (rr_sample < q || !perform_rr);

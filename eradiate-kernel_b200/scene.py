@@ -69,12 +69,21 @@ class _Builder:
         self.keep = []
 
     # ------------------------------------------------------------ helpers
+    def prop(self, v):
+        """A float property as a plugin reads it: Properties stores floats, 3-vectors and transforms in single
+        precision in every variant (include/mitsuba/core/properties.h:55-56), the plugin then widens it."""
+        return self.dt(np.float32(v))
+
+    def prop3(self, v):
+        return np.asarray(v, dtype=np.float32).astype(self.dtype)
+
     def xf(self, v):
+        """props.transform(): a Transform4f in single precision (matrix and inverse transpose), widened."""
         if v is None:
             return Transform(dtype=self.dtype)
         if isinstance(v, Transform):
-            return v.astype(self.dtype)
-        return Transform(np.asarray(v, dtype=np.float64).reshape(4, 4), dtype=self.dtype)
+            return v.astype(np.float32).astype(self.dtype)
+        return Transform(np.asarray(v, dtype=np.float64).reshape(4, 4), dtype=np.float32).astype(self.dtype)
 
     def mat(self, t):
         m = abi.Mat4()
@@ -109,7 +118,7 @@ class _Builder:
         arr = None
         if t == "constvolume":
             v.type = abi.VOLUME_CONST
-            v.value = float(self.dt(node.get("value", 1.0)))
+            v.value = float(self.prop(node.get("value", 1.0)))
             v.max_value = v.value
             v.channels = 1
         elif t == "gridvolume":
@@ -136,7 +145,7 @@ class _Builder:
             v.channels = ch
             v.res[:] = [nx, ny, nz]
             arr = np.ascontiguousarray(data, dtype=np.float32)
-            v.max_value = float(self.dt(node["max_value"])) if "max_value" in node else float(arr.max())
+            v.max_value = float(self.prop(node["max_value"])) if "max_value" in node else float(arr.max())
             if node.get("use_grid_bbox", False):  # grid3d.cpp:152-155
                 mn = np.asarray(file_bbox[:3], dtype=self.dtype)
                 mx = np.asarray(file_bbox[3:], dtype=self.dtype)
@@ -164,7 +173,7 @@ class _Builder:
             p.type = abi.PHASE_RAYLEIGH
         elif t == "hg":
             p.type = abi.PHASE_HG
-            g = self.dt(node.get("g", 0.8))  # hg.cpp:41
+            g = self.prop(node.get("g", 0.8))  # hg.cpp:41
             if not (-1 < g < 1):
                 raise RuntimeError("The asymmetry parameter must lie in the interval (-1, 1)!")
             p.g = float(g)
@@ -185,7 +194,7 @@ class _Builder:
             raise RuntimeError("medium plugin %r is not supported by the B200 volpath" % t)
         m.albedo = self.volume(node.get("albedo"), 0.75)
         m.sigma_t = self.volume(node.get("sigma_t"), 1.0)
-        m.scale = float(self.dt(node.get("scale", 1.0)))
+        m.scale = float(self.prop(node.get("scale", 1.0)))
         m.has_spectral_extinction = int(bool(node.get("has_spectral_extinction", True)))
         m.sample_emitters = int(bool(node.get("sample_emitters", True)))
         m.phase = self.phase(node.get("phase"))
@@ -210,7 +219,7 @@ class _Builder:
                 if val.get("type") != "uniform":
                     raise RuntimeError("only uniform (constant) textures are supported for %r" % key)
                 val = val.get("value", default)
-            return float(self.dt(val))
+            return float(self.prop(val))
         if t == "diffuse":
             b.type = abi.BSDF_DIFFUSE
             b.p[0] = scalar("reflectance", 0.5)
@@ -276,8 +285,8 @@ class _Builder:
                 self.expand(to_world.point_affine(c))
         elif t == "sphere":  # src/shapes/sphere.cpp:95-160
             s.type = abi.SHAPE_SPHERE
-            to_world = to_world @ Transform.translate(node.get("center", [0, 0, 0]), self.dtype)
-            to_world = to_world @ Transform.scale(node.get("radius", 1.0), self.dtype)
+            to_world = to_world @ Transform.translate(self.prop3(node.get("center", [0, 0, 0])), self.dtype)
+            to_world = to_world @ Transform.scale(self.prop(node.get("radius", 1.0)), self.dtype)
             m = to_world.matrix.astype(np.float64)
             # polar decomposition of the upper 3x3 (transform_decompose): S symmetric, Q rotation
             u, sv, vt = np.linalg.svd(m[:3, :3])
@@ -311,21 +320,21 @@ class _Builder:
             tris = np.array([[0, 1, 2], [3, 0, 2], [4, 5, 6], [7, 4, 6], [8, 9, 10], [11, 8, 10], [12, 13, 14],
                              [15, 12, 14], [16, 17, 18], [19, 16, 18], [20, 21, 22], [23, 20, 22]], dtype=np.uint32)
             # Mesh buffers are always float32 (mesh.h:22-28): transform in float32
-            tw = to_world.astype(np.float32)
-            p = np.stack([tw.point_affine(v) for v in verts])
-            n = np.stack([tw.normal(v) for v in nrms])
-            n = (n / np.sqrt(np.sum(n * n, axis=1, dtype=np.float32))[:, None]).astype(np.float32)
+            # cube.cpp:104-107: transformed and normalised in the variant's type, stored as float32
+            p = to_world.point_affine(verts.astype(self.dtype)).astype(np.float32)
+            n = to_world.normal(nrms.astype(self.dtype))
+            n = (n / np.sqrt(np.sum(n * n, axis=1, dtype=self.dtype))[:, None]).astype(np.float32)
             if node.get("flip_normals", False):
                 n = -n
             self.add_mesh(s, p, tris, n, uvs)
         elif t == "mesh":  # in-memory triangle mesh (what obj/ply/serialized loaders produce, src/librender/mesh.cpp)
-            tw = to_world.astype(np.float32)
+            # obj.cpp:172,186: float32 input, transformed in the variant's type, stored as float32
             pos = np.asarray(node["vertex_positions"], dtype=np.float32).reshape(-1, 3)
-            pos = (pos @ tw.matrix[:3, :3].T + tw.matrix[:3, 3]).astype(np.float32)
+            pos = to_world.point_affine(pos.astype(self.dtype)).astype(np.float32)
             nrm = node.get("vertex_normals")
             if nrm is not None:
-                nrm = np.asarray(nrm, dtype=np.float32).reshape(-1, 3) @ tw.inverse_transpose[:3, :3].T
-                nrm = (nrm / np.sqrt(np.sum(nrm * nrm, axis=1))[:, None]).astype(np.float32)
+                nrm = to_world.normal(np.asarray(nrm, dtype=np.float32).reshape(-1, 3).astype(self.dtype))
+                nrm = (nrm / np.sqrt(np.sum(nrm * nrm, axis=1, dtype=self.dtype))[:, None]).astype(np.float32)
             self.add_mesh(s, pos, node["faces"], nrm, node.get("vertex_texcoords"))
         else:
             raise RuntimeError("shape plugin %r is not supported by the B200 volpath" % t)
@@ -346,17 +355,19 @@ class _Builder:
         if "direction" in node:
             if "to_world" in node:
                 raise RuntimeError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!")
-            d = np.asarray(node["direction"], dtype=self.dtype)
-            d = (d / np.sqrt(np.dot(d, d))).astype(self.dtype)
+            d = np.asarray(node["direction"], dtype=np.float32)  # normalize(props.vector3f(..)): single precision
+            d = (d / np.sqrt(np.dot(d, d))).astype(np.float32).astype(self.dtype)
             up, _ = coordinate_system(d, self.dtype)
             tw = Transform.look_at([0, 0, 0], d, up, self.dtype)
         else:
             tw = self.xf(node.get("to_world"))
+        # Endpoint::m_world_transform is an AnimatedTransform: single precision in every variant (transform.h:366)
+        tw = tw.astype(np.float32).astype(self.dtype)
         e.direction[:] = [float(x) for x in tw.vector([0, 0, 1])]
         irr = node.get("irradiance", 1.0)
         if isinstance(irr, dict):
             irr = irr.get("value", 1.0)
-        e.irradiance = float(self.dt(irr))
+        e.irradiance = float(self.prop(irr))
         self.emitters.append(e)
 
     def parse_sensor(self, node):
@@ -400,7 +411,7 @@ class _Builder:
                     raise RuntimeError("sensor target shape must be a rectangle in the B200 volpath")
             else:
                 sn.target_type = abi.TARGET_POINT
-                sn.target_point[:] = [float(dt(x)) for x in tgt]
+                sn.target_point[:] = [float(self.prop(x)) for x in tgt]
 
         if t == "distant":  # distant.cpp:225-290
             sn.type = abi.SENSOR_DISTANT
@@ -410,10 +421,10 @@ class _Builder:
             if "direction" in node:
                 if "to_world" in node:
                     raise RuntimeError("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!")
-                d = np.asarray(node["direction"], dtype=dtp)
-                d = (d / np.sqrt(np.dot(d, d))).astype(dtp)
+                d = np.asarray(node["direction"], dtype=np.float32)  # distant.cpp:253: normalized in single precision
+                d = (d / np.sqrt(np.dot(d, d))).astype(np.float32).astype(dtp)
                 if "orientation" in node:
-                    up = np.cross(d, np.asarray(node["orientation"], dtype=dtp)).astype(dtp)
+                    up = np.cross(d, self.prop3(node["orientation"])).astype(dtp)
                     up = (up / np.sqrt(np.dot(up, up))).astype(dtp)
                 else:
                     _, up = coordinate_system(d, dtp)
@@ -439,8 +450,8 @@ class _Builder:
             if "to_world" not in node and ("direction" in node) != ("origin" in node):
                 raise RuntimeError("If the sensor is specified through origin and direction both values must be set!")
             if "to_world" not in node and "direction" in node:
-                o = np.asarray(node["origin"], dtype=dtp)
-                d = np.asarray(node["direction"], dtype=dtp)
+                o = self.prop3(node["origin"])
+                d = self.prop3(node["direction"])
                 up, _ = coordinate_system(d, dtp)
                 to_world = Transform.look_at(o, o + d, up, dtp)
             if (w, h) != (1, 1):
@@ -464,6 +475,9 @@ class _Builder:
             sn.needs_aperture_sample = 0
         else:
             raise RuntimeError("sensor plugin %r is not supported by the B200 volpath" % t)
+        # distant / radiancemeter keep to_world in Endpoint::m_world_transform (AnimatedTransform, single precision
+        # in every variant, transform.h:366); mdistant / mradiancemeter store ScalarFloat matrices of their own
+        to_world = to_world.astype(np.float32).astype(self.dtype)
         sn.to_world = self.mat(to_world)
         if xfs is not None:
             arr = np.ascontiguousarray(np.stack([x.matrix.T.reshape(-1) for x in xfs]), dtype=np.float64)

@@ -77,15 +77,40 @@ class Transform:
         r = self.matrix @ np.concatenate([p, np.ones(1, dtype=self.dtype)])
         return (r[:3] / r[3]).astype(self.dtype)
 
+    def _fma(self, a, b, c):
+        """enoki::fmadd on the variant's scalar type.  float32: the product is exact in float64 and the sum is
+        rounded once more to float32; float64: numpy has no fused operation, a * b + c is used."""
+        if self.dtype == np.float32:
+            return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(np.float32)
+        return a * b + c
+
     def point_affine(self, p):
+        """transform.h:90-98: result = column 3; result = fmadd(column i, p[i], result) for i = 0, 1, 2.
+        `p` may be one point or an array of points (n, 3)."""
         p = np.asarray(p, dtype=self.dtype)
-        return (self.matrix[:3, :3] @ p + self.matrix[:3, 3]).astype(self.dtype)
+        m = self.matrix
+        r = np.broadcast_to(m[:3, 3], p.shape).astype(self.dtype)
+        for i in range(3):
+            r = self._fma(m[:3, i], p[..., i:i + 1], r)
+        return r.astype(self.dtype)
 
     def vector(self, v):
-        return (self.matrix[:3, :3] @ np.asarray(v, dtype=self.dtype)).astype(self.dtype)
+        """transform.h:116-126: result = column 0 * v[0]; result = fmadd(column i, v[i], result) for i = 1, 2"""
+        v = np.asarray(v, dtype=self.dtype)
+        m = self.matrix
+        r = (m[:3, 0] * v[..., 0:1]).astype(self.dtype)
+        for i in (1, 2):
+            r = self._fma(m[:3, i], v[..., i:i + 1], r)
+        return r.astype(self.dtype)
 
     def normal(self, n):
-        return (self.inverse_transpose[:3, :3] @ np.asarray(n, dtype=self.dtype)).astype(self.dtype)
+        """transform.h:128-138: the same chain with the columns of the inverse transpose"""
+        n = np.asarray(n, dtype=self.dtype)
+        m = self.inverse_transpose
+        r = (m[:3, 0] * n[..., 0:1]).astype(self.dtype)
+        for i in (1, 2):
+            r = self._fma(m[:3, i], n[..., i:i + 1], r)
+        return r.astype(self.dtype)
 
     def colmajor(self):
         """16 doubles, m[c*4+r] (enoki::Matrix column storage)."""

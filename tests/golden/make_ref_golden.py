@@ -1,0 +1,125 @@
+"""Generates tests/golden/ref_golden.npz by running the UNMODIFIED reference (oracle/_ref/refprobe, built from
+/root/reference by oracle/Makefile.ref) on the scenes below.  Run from the repo root, in the container that has
+/root/reference:
+
+    make -f oracle/Makefile.ref -C oracle -j8 && python tests/golden/make_ref_golden.py
+
+Each entry is the raw film storage (X, Y, Z, A, W per pixel) HDRFilm holds after SamplingIntegrator::render
+with ONE thread (the result is thread-count independent: the sampler is seeded per block, integrator.cpp:198).
+Most cases use 1 sample per pixel, so that a pixel is one path and the comparison is per path.
+The CPU tests compare the oracle with these films, the -m gpu tests the CUDA path (tests/test_reference_parity.py)."""
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import scenes  # noqa: E402
+
+
+def _c2_homog(**kw):
+    d = scenes.c2(**kw)
+    d["atm"] = {"type": "homogeneous", "sigma_t": 0.5, "albedo": 0.9, "phase": {"type": "isotropic"}}
+    return d
+
+
+def _c2_sphere(**kw):
+    """C2 with a diffuse sphere floating in the atmosphere (analytic sphere intersection, double precision)."""
+    d = scenes.c2(**kw)
+    d["ball"] = {"type": "sphere", "center": [0.5, -0.25, 0.5], "radius": 0.25,
+                 "bsdf": {"type": "diffuse", "reflectance": 0.75}}
+    return d
+
+
+def _c1_radiancemeter(spp, variant):
+    d = scenes.c1(spp=spp, variant=variant)
+    d["sensor"] = {"type": "radiancemeter", "origin": [0.25, 0.5, 2.0], "direction": [-0.125, -0.25, -1.0],
+                   "sampler": {"type": "independent", "sample_count": spp}, "film": scenes.film(1)}
+    return d
+
+
+def _c3(smooth=False, **kw):
+    """C3 with a ray target that is NOT on the diagonal of the cube's top face: with scenes.c3's target
+    (0.5, 0.5, 1) every camera ray passes exactly through the edge shared by the two triangles of that face and
+    the hit / miss decision is a rounding coin toss in any implementation.
+    smooth=True replaces the 1000:1 cloud / clear-air contrast by smooth low-contrast random fields: next to a
+    cloud edge a position error of one float32 ulp changes the interpolated sigma_t by 1e-3 relative, so the
+    cloud field is ill-conditioned in fp32 and gets a wider per-path tolerance (TOL_OVERRIDE)."""
+    d = scenes.c3(**kw)
+    d["sensor"]["ray_target"] = [0.4, 0.55, 1.0]
+    # The sun is given by its to_world matrix instead of `direction`: directional.cpp:55 normalises `direction`
+    # in single precision with enoki's rsqrt (the SSE estimate + one Newton step, CPU-vendor dependent in the last
+    # ulp); a 1e-8 tilt of the sun is invisible in the plane-parallel cases but not in a 3D field in fp64.
+    T = scenes.T
+    dirn = np.array(d["sun"].pop("direction"), dtype=np.float64)
+    up = np.array([0.0, 1.0, 0.0])
+    d["sun"]["to_world"] = T.look_at([0, 0, 0], dirn, up, np.float32)
+    if smooth:
+        rng = np.random.default_rng(3)
+        n = d["atm"]["sigma_t"]["data"].shape[0]
+        d["atm"]["sigma_t"]["data"] = (5 + 5 * rng.random((n, n, n))).astype(np.float32)
+        d["atm"]["albedo"]["data"] = (0.8 + 0.19 * rng.random((n, n, n))).astype(np.float32)
+    return d
+
+
+# per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
+TOL_OVERRIDE = {
+    "c3_cloud": (1e-3, 0.97),
+    "c3_smooth": (3e-5, 0.97),
+}
+
+CASES = {
+    # name: (builder, variant)
+    "c1": (lambda v: scenes.c1(spp=4096, variant=v), "scalar_mono"),
+    "c1_sun30": (lambda v: scenes.c1(spp=1024, variant=v, sun=(0, 0.5, -1)), "scalar_mono"),
+    "c1_radiancemeter": (lambda v: _c1_radiancemeter(512, v), "scalar_mono"),
+    "c2_paths": (lambda v: scenes.c2(spp=1, variant=v, width=256), "scalar_mono"),
+    "c2_16spp": (lambda v: scenes.c2(spp=16, variant=v, width=64), "scalar_mono"),
+    "c2_tau2": (lambda v: scenes.c2(spp=1, variant=v, width=128, tau=2.0), "scalar_mono"),
+    "c2_nearest": (lambda v: scenes.c2(spp=1, variant=v, width=128, filter_type="nearest"), "scalar_mono"),
+    "c2_mdistant": (lambda v: scenes.c2(spp=1, variant=v, width=128, sensor="mdistant"), "scalar_mono"),
+    "c2_homog_iso": (lambda v: _c2_homog(spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_sphere": (lambda v: _c2_sphere(spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_depth3": (lambda v: scenes.c2(spp=1, variant=v, width=128, max_depth=3, rr_depth=2), "scalar_mono"),
+    "c3_cloud": (lambda v: _c3(spp=1, variant=v, n=16, size=32), "scalar_mono"),
+    "c3_smooth": (lambda v: _c3(smooth=True, spp=1, variant=v, n=16, size=32), "scalar_mono"),
+    "c5_paths": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256), "scalar_mono"),
+    "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
+    "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
+    "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
+    "c3_cloud_f64": (lambda v: _c3(spp=1, variant=v, n=16, size=16), "scalar_mono_double"),
+    "c3_smooth_f64": (lambda v: _c3(smooth=True, spp=1, variant=v, n=16, size=16), "scalar_mono_double"),
+    "c5_paths_f64": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=64), "scalar_mono_double"),
+}
+
+
+def scene_dict(name):
+    """The dictionary both sides load: every number rounded to float32 (what the reference's XML parser and
+    Properties keep, xml.cpp:100-103, properties.h:55)."""
+    from oracle import ref_xml
+    fn, variant = CASES[name]
+    return ref_xml.round_f32(fn(variant)), variant
+
+
+def main():
+    from oracle import ref_xml
+    pkg = scenes.pkg
+    if not ref_xml.available():
+        ref_xml.build()
+    out = {}
+    for name in CASES:
+        d, variant = scene_dict(name)
+        film, sec = ref_xml.render(d, variant, threads=1, write_vol=pkg.scene.write_vol)
+        out[name] = film
+        print("%-18s %-20s %4d x %-4d mean %.7g  (%.3f s)" % (name, variant, film.shape[1], film.shape[0],
+                                                             film[..., 1].sum() / film[..., 4].sum(), sec))
+    np.savez_compressed(os.path.join(HERE, "ref_golden.npz"), **out)
+    print("wrote", len(out), "reference films")
+
+
+if __name__ == "__main__":
+    main()
