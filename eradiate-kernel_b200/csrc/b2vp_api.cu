@@ -212,7 +212,7 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
     if (d->n_faces >= (1ull << 28))
         return fail(B2VP_ERR_UNSUPPORTED, "more than 2^28 triangles (the BVH node reference holds 29 bits)");
     for (uint32_t i = 0; i < d->n_bsdfs; ++i)
-        if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_RPV)
+        if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_BILAMBERTIAN)
             return fail(B2VP_ERR_UNSUPPORTED, "bsdf %u: type %d not supported by the B200 volpath", i, d->bsdfs[i].type);
     for (uint32_t i = 0; i < d->n_phases; ++i)
         if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_HG)

@@ -300,11 +300,11 @@ template <typename F> struct PathCtx {
 
                 /* bsdf->sample(ctx, si, next_1d(), next_2d()) (volpath.cpp:215-216) */
                 F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                 V3<F> bwo;
                 F bs_pdf, bs_eta, bsdf_val;
                 uint32_t sampled_type;
-                bsdf_sample(bsdf, si.wi, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
+                bsdf_sample(bsdf, si.wi, s1, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
 
                 throughput *= bsdf_val;
                 eta *= bs_eta;

@@ -599,11 +599,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 /* no emitter march was started (null BSDF, or nothing to sample): go on in the same visit */
                 if (state == Q_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
-                    F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> bwo;
                     F bs_pdf, bs_eta, bsdf_val;
                     uint32_t sampled_type;
-                    bsdf_sample(bsdf, wi, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
+                    bsdf_sample(bsdf, wi, s1, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_val);
                     throughput *= bsdf_val;
                     s.eta *= bs_eta;
                     Ray<F> r = spawn_ray(sp_, fr.to_world(bwo));

@@ -647,10 +647,20 @@ template <typename F> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2
 
 /* ------------------------------------------------------------------- BSDFs */
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
-    BF_Null = 0x1, BF_DiffuseReflection = 0x2, BF_GlossyReflection = 0x8,
+    BF_Null = 0x1, BF_DiffuseReflection = 0x2, BF_DiffuseTransmission = 0x4, BF_GlossyReflection = 0x8,
     BF_Smooth = 0x2 | 0x4 | 0x8 | 0x10, BF_Delta = 0x1 | 0x20 | 0x40
 };
-VP_D uint32_t bsdf_flags(int type) { return type == 1 ? BF_Null : (type == 0 ? BF_DiffuseReflection : BF_GlossyReflection); }
+VP_D uint32_t bsdf_flags(int type) {
+    if (type == 3) return BF_DiffuseReflection | BF_DiffuseTransmission; /* bilambertian.cpp:55-60 */
+    return type == 1 ? BF_Null : (type == 0 ? BF_DiffuseReflection : BF_GlossyReflection);
+}
+/* BiLambertian lobe weights (src/bsdfs/bilambertian.cpp:80-87): r / (r + t), 1 - that, NaN (r = t = 0) -> 0 */
+template <typename F> VP_D void bilambertian_weights(const DBsdf<F> &b, F &r, F &t, F &rw, F &tw) {
+    r = b.p[0]; t = b.p[1];
+    rw = r / (r + t); tw = (F) 1 - rw;
+    if (rw != rw) rw = 0;
+    if (tw != tw) tw = 0;
+}
 
 /* Frame::sincos_phi (include/mitsuba/core/frame.h:107-118) */
 template <typename F> VP_D void sincos_phi(V3<F> v, F &s, F &c) {
@@ -683,11 +693,26 @@ template <typename F> __device__ __noinline__ F eval_rpv(const DBsdf<F> &b, V3<F
 
 /* BSDF::sample (src/bsdfs/diffuse.cpp:78-102, rpv.cpp:85-105 [weight = f, F8], null.cpp:41-57) */
 template <typename F>
-VP_D void bsdf_sample(const DBsdf<F> &b, V3<F> wi, F s2x, F s2y, V3<F> &wo, F &pdf, F &eta, uint32_t &sampled_type,
-                      F &weight) {
+VP_D void bsdf_sample(const DBsdf<F> &b, V3<F> wi, F s1, F s2x, F s2y, V3<F> &wo, F &pdf, F &eta,
+                      uint32_t &sampled_type, F &weight) {
     wo = mk3<F>(0, 0, 0); pdf = 0; eta = 0; sampled_type = 0; weight = 0;
     if (b.type == 1) {
         wo = -wi; sampled_type = BF_Null; eta = 1; pdf = 1; weight = 1;
+        return;
+    }
+    if (b.type == 3) { /* bilambertian.cpp:63-119 */
+        wo = square_to_cosine_hemisphere(s2x, s2y);
+        F r, t, rw, tw; bilambertian_weights(b, r, t, rw, tw);
+        bool selected_r = s1 < rw;
+        F value = 1;
+        if (selected_r) value *= r / rw; else value *= t / tw;
+        pdf = K<F>::InvPi * wo.z;
+        pdf = selected_r ? pdf * rw : pdf * tw;
+        eta = 1;
+        sampled_type = selected_r ? BF_DiffuseReflection : BF_DiffuseTransmission;
+        if (!(wi.z > 0)) wo.z = -wo.z;   /* the incoming direction comes from "behind" */
+        if (!selected_r) wo.z = -wo.z;   /* transmission */
+        weight = pdf > 0 ? value : (F) 0;
         return;
     }
     bool active = wi.z > 0;
@@ -708,6 +733,10 @@ VP_D void bsdf_sample(const DBsdf<F> &b, V3<F> wi, F s2x, F s2y, V3<F> &wo, F &p
 /* BSDF::eval (diffuse.cpp:104-120, rpv.cpp:143-155, null.cpp:59-62) */
 template <typename F> VP_D F bsdf_eval(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
     if (b.type == 1) return 0;
+    if (b.type == 3) { /* bilambertian.cpp:121-151; sign() is copysign(1, x) */
+        F result = signbit_(wi.z) == signbit_(wo.z) ? b.p[0] : b.p[1];
+        return result * (K<F>::InvPi * abs_(wo.z));
+    }
     bool active = wi.z > 0 && wo.z > 0;
     if (b.type == 0) {
         F value = b.p[0] * K<F>::InvPi * wo.z;
@@ -719,6 +748,11 @@ template <typename F> VP_D F bsdf_eval(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
 /* BSDF::pdf (diffuse.cpp:122-135, rpv.cpp:157-168) */
 template <typename F> VP_D F bsdf_pdf(const DBsdf<F> &b, V3<F> wi, V3<F> wo) {
     if (b.type == 1) return 0;
+    if (b.type == 3) { /* bilambertian.cpp:153-193 */
+        F r, t, rw, tw; bilambertian_weights(b, r, t, rw, tw);
+        F result = K<F>::InvPi * abs_(wo.z);
+        return result * (signbit_(wi.z) == signbit_(wo.z) ? rw : tw);
+    }
     F pdf = K<F>::InvPi * wo.z;
     return (wi.z > 0 && wo.z > 0) ? pdf : (F) 0;
 }

@@ -207,7 +207,7 @@ class _Builder:
         return idx
 
     def bsdf(self, node):
-        """src/bsdfs/diffuse.cpp:70-76, rpv.cpp:66-83, null.cpp:30-39"""
+        """src/bsdfs/diffuse.cpp:70-76, rpv.cpp:66-83, null.cpp:30-39, bilambertian.cpp:50-61"""
         b = abi.Bsdf()
         if node is None:
             node = {"type": "diffuse"}  # shape.cpp: default BSDF
@@ -231,6 +231,10 @@ class _Builder:
             b.p[1] = scalar("k", 0.1)
             b.p[2] = scalar("g", 0.0)
             b.p[3] = scalar("rho_c", b.p[0]) if "rho_c" in node else b.p[0]  # rpv.cpp:72-80
+        elif t == "bilambertian":  # bilambertian.cpp:51-53
+            b.type = abi.BSDF_BILAMBERTIAN
+            b.p[0] = scalar("reflectance", 0.5)
+            b.p[1] = scalar("transmittance", 0.5)
         else:
             raise RuntimeError("BSDF plugin %r is not supported by the B200 volpath" % t)
         self.bsdfs.append(b)
@@ -528,7 +532,7 @@ def load_dict(d, variant="scalar_mono"):
         v.setdefault("id", k)
         if v["type"] in ("homogeneous", "heterogeneous"):
             b.medium(v)
-        elif v["type"] in ("diffuse", "rpv", "null"):
+        elif v["type"] in ("diffuse", "rpv", "null", "bilambertian"):
             b.bsdf(v)
     for k, v in items:
         t = v["type"]
@@ -544,7 +548,7 @@ def load_dict(d, variant="scalar_mono"):
             sensor_node = v
         elif t == "volpath":
             integrator_node = v
-        elif t in ("homogeneous", "heterogeneous", "diffuse", "rpv", "null"):
+        elif t in ("homogeneous", "heterogeneous", "diffuse", "rpv", "null", "bilambertian"):
             pass
         else:
             raise RuntimeError("plugin %r is not supported by the B200 volpath" % t)

@@ -55,7 +55,7 @@ enum {
 enum { B2VP_PREC_F32 = 0 /* scalar_mono */, B2VP_PREC_F64 = 1 /* scalar_mono_double */ };
 
 enum { B2VP_SHAPE_RECTANGLE = 0, B2VP_SHAPE_SPHERE = 1, B2VP_SHAPE_MESH = 2 };
-enum { B2VP_BSDF_DIFFUSE = 0, B2VP_BSDF_NULL = 1, B2VP_BSDF_RPV = 2 };
+enum { B2VP_BSDF_DIFFUSE = 0, B2VP_BSDF_NULL = 1, B2VP_BSDF_RPV = 2, B2VP_BSDF_BILAMBERTIAN = 3 };
 enum { B2VP_MEDIUM_HOMOGENEOUS = 0, B2VP_MEDIUM_HETEROGENEOUS = 1 };
 enum { B2VP_VOLUME_CONST = 0, B2VP_VOLUME_GRID = 1 };
 enum { B2VP_FILTER_NEAREST = 0, B2VP_FILTER_TRILINEAR = 1 };

@@ -160,6 +160,8 @@ struct Heterogeneous { double scale = 1.0; bool has_spectral_extinction = true, 
 struct Diffuse { double reflectance = 0.5; };
 struct Null {};
 struct Rpv { double rho_0 = 0.1, k = 0.1, g = 0.0, rho_c = -1.0; };
+/* src/bsdfs/bilambertian.cpp:50-61 */
+struct Bilambertian { double reflectance = 0.5, transmittance = 0.5; };
 /* src/emitters/directional.cpp:45-73 */
 struct Directional { std::array<double, 3> direction{ 0, 0, 1 }; double irradiance = 1.0; };
 /* src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp */
@@ -196,6 +198,7 @@ public:
     }
     int add_bsdf(const Diffuse &b) { return push_bsdf(B2VP_BSDF_DIFFUSE, (F) b.reflectance, 0, 0, 0); }
     int add_bsdf(const Null &) { return push_bsdf(B2VP_BSDF_NULL, 0, 0, 0, 0); }
+    int add_bsdf(const Bilambertian &b) { return push_bsdf(B2VP_BSDF_BILAMBERTIAN, (F) b.reflectance, (F) b.transmittance, 0, 0); }
     int add_bsdf(const Rpv &b) { return push_bsdf(B2VP_BSDF_RPV, (F) b.rho_0, (F) b.k, (F) b.g, (F) (b.rho_c < 0 ? b.rho_0 : b.rho_c)); }
 
     int add_medium(const Homogeneous &m, const Phase &ph) {

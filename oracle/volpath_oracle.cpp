@@ -789,13 +789,21 @@ template <typename F> inline V3<F> phase_sample(const B2vpPhase &ph, const Mediu
 }
 
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
-    F_Null = 0x1, F_DiffuseReflection = 0x2, F_GlossyReflection = 0x8,
+    F_Null = 0x1, F_DiffuseReflection = 0x2, F_DiffuseTransmission = 0x4, F_GlossyReflection = 0x8,
     F_Smooth = 0x2 | 0x4 | 0x8 | 0x10, F_Delta = 0x1 | 0x20 | 0x40
 };
 template <typename F> struct BSDFSample { V3<F> wo{ 0, 0, 0 }; F pdf = 0, eta = 0; uint32_t sampled_type = 0; };
 
 inline uint32_t bsdf_flags(const B2vpBsdf &b) {
+    if (b.type == B2VP_BSDF_BILAMBERTIAN) return F_DiffuseReflection | F_DiffuseTransmission; /* bilambertian.cpp:55-60 */
     return b.type == B2VP_BSDF_NULL ? F_Null : (b.type == B2VP_BSDF_DIFFUSE ? F_DiffuseReflection : F_GlossyReflection);
+}
+/* BiLambertian lobe weights (src/bsdfs/bilambertian.cpp:80-87): r / (r + t), 1 - that, NaN (r = t = 0) -> 0 */
+template <typename F> inline void bilambertian_weights(const B2vpBsdf &b, F &r, F &t, F &rw, F &tw) {
+    r = (F) b.p[0]; t = (F) b.p[1];
+    rw = r / (r + t); tw = (F) 1 - rw;
+    if (rw != rw) rw = 0;
+    if (tw != tw) tw = 0;
 }
 
 /* Frame::sincos_phi (frame.h:107-118) */
@@ -828,11 +836,27 @@ template <typename F> F eval_rpv(const B2vpBsdf &b, V3<F> wi, V3<F> wo) {
 }
 
 /* BSDF::sample (diffuse.cpp:78-102, rpv.cpp:85-105, null.cpp:41-57) */
-template <typename F> BSDFSample<F> bsdf_sample(const B2vpBsdf &b, V3<F> wi, F s2x, F s2y, F &weight) {
+template <typename F> BSDFSample<F> bsdf_sample(const B2vpBsdf &b, V3<F> wi, F s1, F s2x, F s2y, F &weight) {
     BSDFSample<F> bs;
     weight = 0;
     if (b.type == B2VP_BSDF_NULL) {
         bs.wo = -wi; bs.sampled_type = F_Null; bs.eta = 1; bs.pdf = 1; weight = 1;
+        return bs;
+    }
+    if (b.type == B2VP_BSDF_BILAMBERTIAN) { /* bilambertian.cpp:63-119 */
+        V3<F> wo = square_to_cosine_hemisphere(s2x, s2y);
+        F r, t, rw, tw; bilambertian_weights(b, r, t, rw, tw);
+        bool selected_r = s1 < rw;
+        F value = 1;
+        if (selected_r) value *= r / rw; else value *= t / tw;
+        bs.pdf = Consts<F>::InvPi * wo.z;
+        bs.pdf = selected_r ? bs.pdf * rw : bs.pdf * tw;
+        bs.eta = 1;
+        bs.sampled_type = selected_r ? F_DiffuseReflection : F_DiffuseTransmission;
+        if (!(wi.z > 0)) wo.z = -wo.z;   /* the incoming direction comes from "behind" */
+        if (!selected_r) wo.z = -wo.z;   /* transmission */
+        bs.wo = wo;
+        weight = bs.pdf > 0 ? value : (F) 0;
         return bs;
     }
     F cos_theta_i = wi.z;
@@ -857,6 +881,10 @@ template <typename F> BSDFSample<F> bsdf_sample(const B2vpBsdf &b, V3<F> wi, F s
 /* BSDF::eval (diffuse.cpp:104-120, rpv.cpp:143-155, null.cpp:59-62) */
 template <typename F> F bsdf_eval(const B2vpBsdf &b, V3<F> wi, V3<F> wo) {
     if (b.type == B2VP_BSDF_NULL) return 0;
+    if (b.type == B2VP_BSDF_BILAMBERTIAN) { /* bilambertian.cpp:121-151; sign() is copysign(1, x) */
+        F result = signbit_(wi.z) == signbit_(wo.z) ? (F) b.p[0] : (F) b.p[1];
+        return result * (Consts<F>::InvPi * abs_(wo.z));
+    }
     bool active = wi.z > 0 && wo.z > 0;
     if (b.type == B2VP_BSDF_DIFFUSE) {
         F value = (F) b.p[0] * Consts<F>::InvPi * wo.z;
@@ -868,6 +896,11 @@ template <typename F> F bsdf_eval(const B2vpBsdf &b, V3<F> wi, V3<F> wo) {
 /* BSDF::pdf (diffuse.cpp:122-135, rpv.cpp:157-168) */
 template <typename F> F bsdf_pdf(const B2vpBsdf &b, V3<F> wi, V3<F> wo) {
     if (b.type == B2VP_BSDF_NULL) return 0;
+    if (b.type == B2VP_BSDF_BILAMBERTIAN) { /* bilambertian.cpp:153-193 */
+        F r, t, rw, tw; bilambertian_weights(b, r, t, rw, tw);
+        F result = Consts<F>::InvPi * abs_(wo.z);
+        return result * (signbit_(wi.z) == signbit_(wo.z) ? rw : tw);
+    }
     F pdf = Consts<F>::InvPi * wo.z;
     return (wi.z > 0 && wo.z > 0) ? pdf : (F) 0;
 }
@@ -1254,9 +1287,9 @@ template <typename F> struct Integrator {
                 /* bsdf->sample(ctx, si, next_1d(), next_2d(), ..) (volpath.cpp:215-216):
                    same argument-order caveat as for the phase function */
                 F da = next_1d(active_surface), db = next_1d(active_surface), dc = next_1d(active_surface);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                 F bsdf_val;
-                BSDFSample<F> bs = bsdf_sample(bsdf, si.wi, s2x, s2y, bsdf_val);
+                BSDFSample<F> bs = bsdf_sample(bsdf, si.wi, s1, s2x, s2y, bsdf_val);
 
                 throughput *= bsdf_val;
                 eta *= bs.eta;

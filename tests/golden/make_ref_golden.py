@@ -66,6 +66,8 @@ def _c3(smooth=False, **kw):
     return d
 
 
+_BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # two-sided leaves
+
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
 TOL_OVERRIDE = {
     "c3_cloud": (1e-3, 0.97),
@@ -88,6 +90,9 @@ CASES = {
     "c3_cloud": (lambda v: _c3(spp=1, variant=v, n=16, size=32), "scalar_mono"),
     "c3_smooth": (lambda v: _c3(smooth=True, spp=1, variant=v, n=16, size=32), "scalar_mono"),
     "c5_paths": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256), "scalar_mono"),
+    "c5_bilambertian": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB), "scalar_mono"),
+    "c5_bilambertian_f64": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB),
+                            "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

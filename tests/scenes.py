@@ -122,7 +122,7 @@ def canopy(n_leaves=500, seed=0):
     return v.astype(np.float32), f.astype(np.uint32)
 
 
-def c5(spp=4, variant="scalar_mono", n_leaves=500, n_sensors=64, **integ):
+def c5(spp=4, variant="scalar_mono", n_leaves=500, n_sensors=64, leaf_bsdf=None, **integ):
     """C5: triangle-mesh canopy under a homogeneous Rayleigh slab, lambertian leaves, mradiancemeter array."""
     dt = pkg.scene.VARIANTS[variant][0]
     v, f = canopy(n_leaves)
@@ -140,7 +140,8 @@ def c5(spp=4, variant="scalar_mono", n_leaves=500, n_sensors=64, **integ):
         "atm": {"type": "homogeneous", "sigma_t": 0.3 / 0.8, "albedo": 1.0, "phase": {"type": "rayleigh"}},
         "slab": {"type": "cube", "to_world": T.translate([0, 0, 0.6], dt) @ T.scale([1.5, 1.5, 0.4], dt),
                  "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}},
-        "leaves": {"type": "mesh", "vertex_positions": v, "faces": f, "bsdf": {"type": "diffuse", "reflectance": 0.5}},
+        "leaves": {"type": "mesh", "vertex_positions": v, "faces": f,
+                   "bsdf": leaf_bsdf or {"type": "diffuse", "reflectance": 0.5}},
         "ground": {"type": "rectangle", "to_world": T.scale([1.5, 1.5, 1], dt),
                    "bsdf": {"type": "diffuse", "reflectance": 0.2}},
         "sun": {"type": "directional", "direction": [0.2, 0.1, -1], "irradiance": 1.0},

@@ -18,6 +18,8 @@ CASES = {
     "c2_mdistant": lambda v: scenes.c2(spp=8, variant=v, sensor="mdistant", width=64),
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
+    "c5_bilambertian": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64,
+                                           leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}),
 }
 
 
