@@ -129,6 +129,8 @@ template <typename F> struct DeviceScene {
     DScene<F> g{};
     DevBuf blob, vpos, vnrm, vuv, faces, bvh, bvh_prims, bvh_tris, sensor_xf;
     std::vector<std::unique_ptr<DevBuf>> grids;
+    std::vector<std::unique_ptr<DevBuf>> cells;   /* trilinear cell records of the grids gathered from HBM */
+    size_t cell_bytes = 0;
     std::vector<unsigned char> host_blob;  /* kept for scene_update */
     uint32_t smem_static = 0;              /* blob + staged grids */
     size_t global_grid_bytes = 0;          /* grids gathered from HBM / L2 (not staged in shared memory) */
@@ -345,6 +347,8 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     /* volumes: grids are widened to F at load like the reference (volume_data.h:85-90) */
     std::vector<DVolume<F>> volumes(s->volumes.size());
     ds.grids.clear();
+    ds.cells.clear();
+    ds.cell_bytes = 0;
     for (size_t i = 0; i < volumes.size(); ++i) {
         const B2vpVolume &a = s->volumes[i];
         DVolume<F> &o = volumes[i];
@@ -442,8 +446,29 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
             grid_off += (uint32_t) v.data_bytes;
         } else {
             ds.global_grid_bytes += v.data_bytes;
+            /* A grid gathered from HBM / L2 gets trilinear cell records (vp_types.cuh, DVolume::cells): 8x the
+               memory (2 x 257^3 x 32 B = 1.1 GB for C3, of 180 GB), one 32-byte sector per lookup instead of
+               eight words in four rows.  B2VP_CELLS=0 keeps the plain layout (A/B measurements). */
+            const char *ce = std::getenv("B2VP_CELLS");
+            const bool want_cells = !(ce && !std::strcmp(ce, "0"));
+            const size_t n_cells = (size_t) (v.nx + 1) * (v.ny + 1) * (v.nz + 1), cbytes = n_cells * 8 * sizeof(F);
+            size_t free_b = 0, total_b = 0;
+            cudaMemGetInfo(&free_b, &total_b);
+            if (want_cells && v.filter == B2VP_FILTER_TRILINEAR && v.channels == 1 && v.wrap == B2VP_WRAP_CLAMP &&
+                cbytes < free_b / 4) {
+                ds.cells.emplace_back(new DevBuf());
+                cudaError_t e = ds.cells.back()->alloc(cbytes);
+                if (e != cudaSuccess) return fail(B2VP_ERR_CUDA, "cell-record allocation failed: %s", cudaGetErrorString(e));
+                F *cp = ds.cells.back()->template as<F>();
+                const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) s->sm_count * 16);
+                build_cells_kernel<F><<<blocks, 256>>>(v.data, cp, v.nx, v.ny, v.nz);
+                CU_CHECK(cudaGetLastError());
+                v.cells = cp;
+                ds.cell_bytes += cbytes;
+            }
         }
     }
+    CU_CHECK(cudaDeviceSynchronize());
     g.grid_smem_bytes = grid_off;
 
     ds.host_blob.assign(g.blob_bytes, 0);

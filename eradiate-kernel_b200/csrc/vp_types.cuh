@@ -229,6 +229,11 @@ template <typename F> struct DVolume {
     F w2l[16];
     const F *data;                   /* [((z*ny+y)*nx+x)*channels+c] (volume_data.h:65-95) */
     unsigned long long data_bytes;
+    /* Trilinear cell records (large single-channel clamp-mode grids only, else null): for every cell
+       (cx, cy, cz) in [0, nx] x [0, ny] x [0, nz] the eight corner values d000, d100, d010, d110, d001, d101,
+       d011, d111 of the lookup whose floor index is (cx-1, cy-1, cz-1), contiguous and 8*sizeof(F)-aligned:
+       one lookup reads one 32-byte sector (fp32) instead of eight words from four rows. */
+    const F *cells;
 };
 template <typename F> struct DMedium {
     int type, sigma_t, albedo, phase;

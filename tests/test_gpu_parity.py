@@ -69,6 +69,19 @@ def test_scalar_block_seeding_bit_exact(pkg, oracle, variant):
     compare(pkg, oracle, sc, pkg.abi.SEED_SCALAR_BLOCKS)
 
 
+@pytest.mark.parametrize("cells", ["1", "0"])
+def test_large_grid_layouts(pkg, oracle, cells, monkeypatch):
+    """Grids too large for shared memory are read from HBM either through trilinear cell records (8 corner
+    values per 32-byte record, the default) or through eight plain gathers (B2VP_CELLS=0): same bits."""
+    monkeypatch.setenv("B2VP_CELLS", cells)
+    for variant in ("scalar_mono", "scalar_mono_double"):
+        sc = pkg.load_dict(scenes.c3(spp=2, variant=variant, n=40, size=12), variant)
+        compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
+    d = scenes.c3(spp=2, n=40, size=12)
+    d["atm"]["albedo"] = 0.9   # unpaired: sigma_t grid alone
+    compare(pkg, oracle, pkg.load_dict(d), pkg.abi.SEED_WAVEFRONT)
+
+
 def test_explicit_states(pkg, oracle):
     sc = pkg.load_dict(scenes.c2(spp=4, width=32))
     rng = np.random.default_rng(3)
