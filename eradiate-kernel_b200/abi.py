@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb2vp.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NO_DEVICE, ERR_CANCELLED = range(6)
 PREC_F32, PREC_F64 = 0, 1
@@ -90,7 +90,7 @@ class Sensor(C.Structure):
 class Integrator(C.Structure):
     _fields_ = [
         ("max_depth", c_i32), ("rr_depth", c_i32), ("hide_emitters", c_i32),
-        ("block_size", c_u32), ("samples_per_pass", c_u32), ("arg_order_ltr", c_u32),
+        ("block_size", c_u32), ("samples_per_pass", c_u32), ("arg_order_ltr", c_u32), ("moment", c_u32),
     ]
 
 

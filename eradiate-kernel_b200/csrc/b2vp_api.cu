@@ -534,6 +534,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;
     g.rr_depth = (uint32_t) d.integrator.rr_depth;
     g.hide_emitters = d.integrator.hide_emitters; g.ltr = (int) d.integrator.arg_order_ltr;
+    g.film_ch = d.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS; g.pad_film = 0;
     ds.ready = true;
     return B2VP_OK;
 }
@@ -668,7 +669,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     cudaStream_t stream = (cudaStream_t) a->cuda_stream;
 
     const int W = sp.d.w, H = sp.d.h;
-    const size_t film_n = (size_t) W * H * 5, film_bytes = film_n * sizeof(F);
+    const size_t film_n = (size_t) W * H * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS), film_bytes = film_n * sizeof(F);
     F *d_film;
     if (a->film_on_device) {
         d_film = (F *) film_user;

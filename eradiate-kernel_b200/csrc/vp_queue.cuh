@@ -211,7 +211,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     stage_scene(g, out, smem, sv);
 
     const DSensor<F> &sn = g.sensor;
-    const int W = sn.crop_size[0];
+    const int W = sn.crop_size[0], NCH = g.film_ch;
     F *film = out.film_in_smem ? reinterpret_cast<F *>(smem + out.film_smem_offset) : out.film;
     const uint32_t max_depth = g.max_depth, rr_depth = g.rr_depth;
     const bool ltr = g.ltr != 0;
@@ -702,7 +702,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     tot[TOT_PATHS]++;
                     if (out.out_radiance) out.out_radiance[k * n_samples + j] = value;
                     F alpha = (fl & QF_VALID_RAY) ? (F) 1 : (F) 0;
-                    bool ok = value >= (F) -1e-5f && finite_(value);
+                    bool ok = NCH > 5 || (value >= (F) -1e-5f && finite_(value)); /* no check with AOVs */
                     if (!ok) {
                         tot[TOT_INVALID]++;
                     } else {
@@ -710,11 +710,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
                         if (!(lx < 0 || ly < 0 || lx >= bsx || ly >= bsy)) {
                             int fx = lx + box - sp.ox, fy = ly + boy - sp.oy;
+                            if (NCH > 5) { /* moment.cpp:78-83: the nested integrator's X Y Z (without the ray weight) and squares */
+                                F *q = film + ((size_t) fy * W + fx) * NCH + 5;
+                                const F raw = c.result, raw2 = raw * raw;
+                                film_add(q, raw); film_add(q + 1, raw); film_add(q + 2, raw);
+                                film_add(q + 3, raw2); film_add(q + 4, raw2); film_add(q + 5, raw2);
+                            }
                             if (fx == px - sp.ox && fy == py - sp.oy) {
                                 c.acc0 += value; c.acc3 += alpha; c.acc4 += (F) 1;
                                 fl |= QF_ACC_USED;
                             } else {
-                                F *p = film + ((size_t) fy * W + fx) * 5;
+                                F *p = film + ((size_t) fy * W + fx) * NCH;
                                 film_add(p, value); film_add(p + 1, value); film_add(p + 2, value);
                                 film_add(p + 3, alpha); film_add(p + 4, (F) 1);
                             }
@@ -727,7 +733,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 if ((fl & QF_HAVE_STREAM) && (j >= n_samples || empty)) {
                     /* stream finished: splat its accumulator, write the parity outputs */
                     if (fl & QF_ACC_USED) {
-                        F *p = film + ((size_t) (py - sp.oy) * W + (px - sp.ox)) * 5;
+                        F *p = film + ((size_t) (py - sp.oy) * W + (px - sp.ox)) * NCH;
                         F a0 = c.acc0;
                         film_add(p, a0); film_add(p + 1, a0); film_add(p + 2, a0);
                         film_add(p + 3, c.acc3); film_add(p + 4, c.acc4);
@@ -828,7 +834,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     if (out.film_in_smem) {
         __syncthreads();
         const F *f = reinterpret_cast<const F *>(smem + out.film_smem_offset);
-        uint32_t n = (uint32_t) W * sn.crop_size[1] * 5;
+        uint32_t n = (uint32_t) W * sn.crop_size[1] * NCH;
         for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
             F v = f[i];
             if (v != (F) 0) film_add(out.film + i, v);

@@ -60,7 +60,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     stage_scene(g, out, smem, sv);
 
     const DSensor<F> &sn = g.sensor;
-    const int W = sn.crop_size[0];
+    const int W = sn.crop_size[0], C = g.film_ch;
     F *film = out.film_in_smem ? reinterpret_cast<F *>(smem + out.film_smem_offset) : out.film;
     const uint32_t max_depth = g.max_depth, rr_depth = g.rr_depth;
     const bool ltr = g.ltr != 0;
@@ -399,7 +399,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 tot[TOT_PATHS]++;
                 if (out.out_radiance) out.out_radiance[k * st.n_samples + j] = value;
                 F alpha = valid_ray ? (F) 1 : (F) 0;
-                bool ok = value >= (F) -1e-5f && finite_(value);
+                bool ok = C > 5 || (value >= (F) -1e-5f && finite_(value)); /* no check with AOVs */
                 if (!ok) {
                     tot[TOT_INVALID]++;
                 } else {
@@ -407,11 +407,17 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                     int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
                     if (!(lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy)) {
                         int fx = lx + st.box - sp.ox, fy = ly + st.boy - sp.oy;
+                        if (C > 5) { /* moment.cpp:78-83: the nested integrator's X Y Z (without the ray weight) and squares */
+                            F *q = film + ((size_t) fy * W + fx) * C + 5;
+                            const F raw = result, raw2 = raw * raw;
+                            film_add(q, raw); film_add(q + 1, raw); film_add(q + 2, raw);
+                            film_add(q + 3, raw2); film_add(q + 4, raw2); film_add(q + 5, raw2);
+                        }
                         if (fx == st.px - sp.ox && fy == st.py - sp.oy) {
                             acc0 += value; acc3 += alpha; acc4 += (F) 1;
                             acc_used = true;
                         } else {
-                            F *p = film + ((size_t) fy * W + fx) * 5;
+                            F *p = film + ((size_t) fy * W + fx) * C;
                             film_add(p, value); film_add(p + 1, value); film_add(p + 2, value);
                             film_add(p + 3, alpha); film_add(p + 4, (F) 1);
                         }
@@ -424,7 +430,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 if (have_stream && (j >= st.n_samples || st.empty)) {
                     /* stream finished: splat its accumulator, write the parity outputs */
                     if (acc_used) {
-                        F *p = film + ((size_t) (st.py - sp.oy) * W + (st.px - sp.ox)) * 5;
+                        F *p = film + ((size_t) (st.py - sp.oy) * W + (st.px - sp.ox)) * C;
                         film_add(p, acc0); film_add(p + 1, acc0); film_add(p + 2, acc0);
                         film_add(p + 3, acc3); film_add(p + 4, acc4);
                     }
@@ -488,7 +494,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     if (out.film_in_smem) {
         __syncthreads();
         const F *f = reinterpret_cast<const F *>(smem + out.film_smem_offset);
-        uint32_t n = (uint32_t) W * sn.crop_size[1] * 5;
+        uint32_t n = (uint32_t) W * sn.crop_size[1] * C;
         for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
             F v = f[i];
             if (v != (F) 0) film_add(out.film + i, v);

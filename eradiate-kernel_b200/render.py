@@ -98,10 +98,10 @@ class DeviceScene:
             # film stays resident in HBM: `device_film` is a device pointer to H*W*5 reals (e.g. tensor.data_ptr())
             a.film_on_device, a.clear_film = 1, int(clear)
         elif film is None:
-            film = np.zeros((h, w, 5), dtype=dtype)
+            film = np.zeros((h, w, self.scene.film_channels), dtype=dtype)
             a.clear_film = 1
         else:
-            assert film.dtype == dtype and film.shape == (h, w, 5) and film.flags.c_contiguous
+            assert film.dtype == dtype and film.shape == (h, w, self.scene.film_channels) and film.flags.c_contiguous
             a.clear_film = 0
         tot = abi.Counters()
         a.totals = C.pointer(tot)

@@ -492,9 +492,17 @@ class _Builder:
 
     def parse_integrator(self, node):
         """src/librender/integrator.cpp:23-39,302-315"""
+        outer = node
+        moment = 0
+        if node.get("type", "volpath") == "moment":  # src/integrators/moment.cpp:39-60: one nested volpath
+            nested = [v for v in node.values() if isinstance(v, dict)]
+            if len(nested) != 1 or nested[0].get("type", "volpath") != "volpath":
+                raise RuntimeError("the B200 moment integrator nests exactly one volpath")
+            node, moment = nested[0], 1
         if node.get("type", "volpath") != "volpath":
             raise RuntimeError("integrator plugin %r is not supported by the B200 volpath" % node["type"])
         it = abi.Integrator()
+        it.moment = moment
         it.max_depth = int(node.get("max_depth", -1))
         if it.max_depth < 0 and it.max_depth != -1:
             raise RuntimeError("\"max_depth\" must be set to -1 (infinite) or a value >= 0")
@@ -502,8 +510,9 @@ class _Builder:
         if it.rr_depth <= 0:
             raise RuntimeError("\"rr_depth\" must be set to a value greater than zero!")
         it.hide_emitters = int(bool(node.get("hide_emitters", False)))
-        it.block_size = int(node.get("block_size", 0))
-        it.samples_per_pass = int(node.get("samples_per_pass", 0xffffffff)) & 0xffffffff
+        # block_size / samples_per_pass are read by the SamplingIntegrator that render() runs on: the outer one
+        it.block_size = int(outer.get("block_size", 0))
+        it.samples_per_pass = int(outer.get("samples_per_pass", 0xffffffff)) & 0xffffffff
         it.arg_order_ltr = int(node.get("arg_order_ltr", 0))
         self.integrator = it
 
@@ -514,6 +523,7 @@ class Scene:
     def __init__(self, desc, variant, precision, keep):
         self.desc, self.variant, self.precision, self._keep = desc, variant, precision, keep
         self.film_size = (desc.sensor.crop_size[0], desc.sensor.crop_size[1])
+        self.film_channels = 11 if desc.integrator.moment else 5   # B2VP_FILM_CHANNELS(_MOMENT)
 
 
 def load_dict(d, variant="scalar_mono"):
@@ -546,7 +556,7 @@ def load_dict(d, variant="scalar_mono"):
             if sensor_node is not None:
                 raise RuntimeError("the B200 volpath renders one sensor per scene")
             sensor_node = v
-        elif t == "volpath":
+        elif t in ("volpath", "moment"):
             integrator_node = v
         elif t in ("homogeneous", "heterogeneous", "diffuse", "rpv", "null", "bilambertian"):
             pass

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define B2VP_ABI_VERSION 1u
+#define B2VP_ABI_VERSION 2u
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -191,7 +191,14 @@ typedef struct B2vpIntegrator {
        two sample arguments in compiler-chosen order (volpath.cpp:171,215): 0 =
        right-to-left (GCC, the build SURVEY.md probed), 1 = left-to-right (clang) */
     uint32_t arg_order_ltr;
+    /* 1: the volpath is nested in a `moment` integrator (src/integrators/moment.cpp:39-111): the film has
+       B2VP_FILM_CHANNELS_MOMENT channels per pixel, X Y Z A W followed by the nested integrator's unweighted
+       X Y Z and their squares, and ImageBlock::put skips its validity check (integrator.cpp:113-115) */
+    uint32_t moment;
 } B2vpIntegrator;
+
+#define B2VP_FILM_CHANNELS 5
+#define B2VP_FILM_CHANNELS_MOMENT 11
 
 typedef struct B2vpSceneDesc {
     uint32_t abi_version;

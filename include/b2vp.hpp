@@ -178,7 +178,12 @@ struct Distant {
 /* src/sensors/radiancemeter.cpp:61-104 */
 struct RadianceMeter { std::array<double, 3> origin{ 0, 0, 0 }, direction{ 0, 0, 1 }; int medium = -1; };
 /* src/integrators/volpath.cpp:19-25, src/librender/integrator.cpp:23-39,302-315 */
-struct Volpath { int max_depth = -1, rr_depth = 5; bool hide_emitters = false; uint32_t block_size = 0, samples_per_pass = 0xffffffffu; };
+struct Volpath {
+    int max_depth = -1, rr_depth = 5; bool hide_emitters = false; uint32_t block_size = 0, samples_per_pass = 0xffffffffu;
+    /* true: nested in a `moment` integrator (src/integrators/moment.cpp): the film gets 6 more channels per pixel,
+       the unweighted X Y Z and their squares */
+    bool moment = false;
+};
 
 /* A finished scene: owns the descriptor and every array it points to. */
 struct Scene {
@@ -349,6 +354,7 @@ public:
         B2vpIntegrator &it = sc_->desc.integrator;
         it.max_depth = v.max_depth; it.rr_depth = v.rr_depth; it.hide_emitters = v.hide_emitters;
         it.block_size = v.block_size; it.samples_per_pass = v.samples_per_pass; it.arg_order_ltr = 0;
+        it.moment = v.moment ? 1u : 0u;
         have_integrator_ = true;
     }
 
@@ -424,13 +430,14 @@ private:
     bool have_sensor_ = false, have_integrator_ = false;
 };
 
-/* The film of one render: crop_size x 5 channels (X, Y, Z, A, W), ImageBlock layout (imageblock.cpp). */
+/* The film of one render: crop_size x 5 channels (X, Y, Z, A, W), ImageBlock layout (imageblock.cpp); 11 channels
+   under a moment integrator (+ nested X Y Z and their squares). */
 struct Film {
-    int width = 0, height = 0, precision = B2VP_PREC_F32;
+    int width = 0, height = 0, channels = B2VP_FILM_CHANNELS, precision = B2VP_PREC_F32;
     std::vector<float> f32; std::vector<double> f64;
     B2vpCounters totals{};
     double at(int x, int y, int ch) const {
-        size_t i = ((size_t) y * width + x) * 5 + ch;
+        size_t i = ((size_t) y * width + x) * channels + ch;
         return precision == B2VP_PREC_F32 ? (double) f32[i] : f64[i];
     }
     /* HDRFilm::bitmap for pixel_format=luminance: Y / W (hdrfilm.cpp:251-321) */
@@ -451,7 +458,8 @@ public:
     Film render(int seed_mode = B2VP_SEED_WAVEFRONT, uint64_t first_stream = 0, uint64_t n_streams = 0) {
         Film f;
         f.width = scene_->width(); f.height = scene_->height(); f.precision = scene_->desc.precision;
-        size_t n = (size_t) f.width * f.height * 5;
+        f.channels = scene_->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS;
+        size_t n = (size_t) f.width * f.height * f.channels;
         void *buf;
         if (f.precision == B2VP_PREC_F32) { f.f32.assign(n, 0.f); buf = f.f32.data(); }
         else { f.f64.assign(n, 0.0); buf = f.f64.data(); }

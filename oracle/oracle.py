@@ -74,7 +74,7 @@ def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, e
             raise RuntimeError(lib().b2vp_oracle_last_error().decode())
         count = n_streams if n_streams else n.value - first_stream
         sps = per.value
-    film = np.zeros((h, w, 5), dtype=dtype)
+    film = np.zeros((h, w, scene.film_channels), dtype=dtype)
     a.clear_film = 1
     tot = abi.Counters()
     a.totals = C.pointer(tot)

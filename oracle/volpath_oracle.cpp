@@ -1442,7 +1442,8 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
     if (sp.mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
     if (first + count > sp.n_streams) { g_error = "stream range out of bounds"; return B2VP_ERR_INVALID; }
 
-    const size_t film_n = (size_t) sp.w * sp.h * 5;
+    const int C = d->integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS;
+    const size_t film_n = (size_t) sp.w * sp.h * C;
     if (a->clear_film) std::fill(film, film + film_n, (F) 0);
 
     B2vpCounters tot{};
@@ -1453,7 +1454,7 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
         Stream st = make_stream(sp, a, first + k);
         PCG32 rng; rng.state = st.state; rng.inc = st.inc;
         Counters cnt;
-        F acc[5] = { 0, 0, 0, 0, 0 };
+        F acc[B2VP_FILM_CHANNELS_MOMENT] = { 0 };
         bool acc_used = false;
         for (uint32_t j = 0; j < st.n_samples && !st.empty; ++j) {
             /* render_sample (integrator.cpp:233-288) */
@@ -1472,31 +1473,35 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
             Integrator<F> integ{ scene, rng, cnt, max_depth, (uint32_t) d->integrator.rr_depth,
                                  d->integrator.hide_emitters != 0, d->integrator.arg_order_ltr != 0 };
             bool valid;
-            F value = integ.sample(ray, sn.medium, true, valid);
-            value = ray_weight * value;
+            const F raw_value = integ.sample(ray, sn.medium, true, valid);
+            F value = ray_weight * raw_value;
             tot.n_paths++;
             if (a->out_radiance)
                 ((F *) a->out_radiance)[k * st.n_samples + j] = value;
 
             /* ImageBlock::put, box filter (imageblock.cpp:85-109,162-169) */
-            F aovs[5] = { value, value, value, valid ? (F) 1 : (F) 0, (F) 1 };
+            /* MomentIntegrator::sample (moment.cpp:63-91): the nested integrator's X Y Z without the ray weight,
+               then their squares; with AOVs the block does not check the sample (integrator.cpp:113-115) */
+            F aovs[B2VP_FILM_CHANNELS_MOMENT] = { value, value, value, valid ? (F) 1 : (F) 0, (F) 1,
+                                                  raw_value, raw_value, raw_value,
+                                                  raw_value * raw_value, raw_value * raw_value, raw_value * raw_value };
             bool is_valid = true;
-            for (int c = 0; c < 5; ++c) is_valid = is_valid && aovs[c] >= (F) -1e-5f && std::isfinite(aovs[c]);
+            for (int c = 0; c < 5 && C == 5; ++c) is_valid = is_valid && aovs[c] >= (F) -1e-5f && std::isfinite(aovs[c]);
             if (!is_valid) { tot.n_invalid_samples++; continue; }
             F bx = posx - ((F) st.box + (F) 0.5), by = posy - ((F) st.boy + (F) 0.5);
             int lx = ceil2int(bx - (F) 0.5), ly = ceil2int(by - (F) 0.5);
             if (lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy) continue;
             int fx = lx + st.box - sp.ox, fy = ly + st.boy - sp.oy;
             if (fx == st.px - sp.ox && fy == st.py - sp.oy) {
-                for (int c = 0; c < 5; ++c) acc[c] += aovs[c];
+                for (int c = 0; c < C; ++c) acc[c] += aovs[c];
                 acc_used = true;
             } else { /* sample landed on a neighbour pixel (position sample == 0) */
-                for (int c = 0; c < 5; ++c) film[((size_t) fy * sp.w + fx) * 5 + c] += aovs[c];
+                for (int c = 0; c < C; ++c) film[((size_t) fy * sp.w + fx) * C + c] += aovs[c];
             }
         }
         if (acc_used) {
-            size_t base = ((size_t) (st.py - sp.oy) * sp.w + (st.px - sp.ox)) * 5;
-            for (int c = 0; c < 5; ++c) film[base + c] += acc[c];
+            size_t base = ((size_t) (st.py - sp.oy) * sp.w + (st.px - sp.ox)) * C;
+            for (int c = 0; c < C; ++c) film[base + c] += acc[c];
         }
         if (a->out_state) a->out_state[k] = rng.state;
         if (a->out_counters) {

@@ -66,6 +66,17 @@ def _c3(smooth=False, **kw):
     return d
 
 
+def _moment(d):
+    """Wraps the scene's volpath in a `moment` integrator: 11 film channels."""
+    inner = dict(d["integrator"])
+    outer = {"type": "moment", "nested": inner}
+    for key in ("block_size", "samples_per_pass"):
+        if key in inner:
+            outer[key] = inner.pop(key)
+    d["integrator"] = outer
+    return d
+
+
 _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # SURVEY 8(f) N3: two-sided leaves
 
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
@@ -93,6 +104,9 @@ CASES = {
     "c5_bilambertian": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB), "scalar_mono"),
     "c5_bilambertian_f64": (lambda v: scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB),
                             "scalar_mono_double"),
+    "c2_moment": (lambda v: _moment(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono"),
+    "c2_moment_256spp": (lambda v: _moment(scenes.c2(spp=256, variant=v, width=32)), "scalar_mono"),
+    "c2_moment_f64": (lambda v: _moment(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

@@ -69,6 +69,22 @@ def test_scalar_block_seeding_bit_exact(pkg, oracle, variant):
     compare(pkg, oracle, sc, pkg.abi.SEED_SCALAR_BLOCKS)
 
 
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+def test_moment_integrator(pkg, oracle, variant, kernel):
+    """volpath nested in `moment` (src/integrators/moment.cpp): 11 film channels, no validity check on put."""
+    if kernel in ("q256", "generic") and variant == "scalar_mono_double":
+        pytest.skip("variant covered in fp32")
+    d = scenes.c2(spp=8, variant=variant, width=48)
+    d["integrator"] = {"type": "moment", "nested": d["integrator"]}
+    sc = pkg.load_dict(d, variant)
+    assert sc.film_channels == 11
+    got = compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
+    assert got.film.shape == (1, 48, 11) and (got.film[..., 8] > 0).any()
+    d = scenes.c3(spp=2, variant=variant, n=16, size=72)   # 72 x 72 x 11 film: accumulated in global memory
+    d["integrator"] = {"type": "moment", "nested": d["integrator"]}
+    compare(pkg, oracle, pkg.load_dict(d, variant), pkg.abi.SEED_SCALAR_BLOCKS)
+
+
 @pytest.mark.parametrize("cells", ["1", "0"])
 def test_large_grid_layouts(pkg, oracle, cells, monkeypatch):
     """Grids too large for shared memory are read from HBM either through trilinear cell records (8 corner

@@ -33,8 +33,9 @@ TOL = {"scalar_mono": (1e-5, 0.97), "scalar_mono_double": (1e-12, 0.99)}
 def check_against_reference(name, got, ref, variant):
     tol, min_frac = make_ref_golden.TOL_OVERRIDE.get(name, TOL[variant])
     assert got.shape == ref.shape, name
-    got = got.astype(np.float64).reshape(-1, 5)
-    ref = ref.astype(np.float64).reshape(-1, 5)
+    channels = ref.shape[-1]
+    got = got.astype(np.float64).reshape(-1, channels)
+    ref = ref.astype(np.float64).reshape(-1, channels)
     # sample counts and alpha are exact: same streams, same splats
     assert np.array_equal(got[:, 4], ref[:, 4]), "%s: film weights differ" % name
     assert np.array_equal(got[:, 3], ref[:, 3]), "%s: alpha differs" % name
@@ -59,7 +60,50 @@ def check_against_reference(name, got, ref, variant):
         assert abs(mean_got - mean_ref) <= tol * abs(mean_ref)
     for c in (0, 2):  # X = Y = Z in mono
         assert np.array_equal(got[:, c], got[:, 1])
+    if channels == 11:  # moment integrator: nested X Y Z (no ray weight) and their squares (moment.cpp:78-83)
+        for c in (5, 6, 7, 8, 9, 10):
+            e = np.abs(got[:, c] - ref[:, c]) <= 2 * tol * np.maximum(np.abs(ref[:, c]), 1e-3 * np.abs(ref[:, c]).max())
+            assert e.mean() >= need, "%s: channel %d" % (name, c)
+        assert np.array_equal(got[:, 6], got[:, 5]) and np.array_equal(got[:, 9], got[:, 8])
     return frac
+
+
+def z_test(mean, sample_count, reference, reference_var):
+    """The reference's own test statistic (src/librender/tests/test_renders.py:62-83): two-sided p-value of
+    `mean` (an estimate from `sample_count` samples) against a reference image and its per-pixel variance."""
+    from math import erf, sqrt
+    reference_var = np.maximum(reference_var, 1e-4)
+    z = np.abs(mean - reference) * np.sqrt(sample_count / reference_var)
+    cdf = np.array([(1.0 - erf(-x / sqrt(2.0))) * 0.5 for x in z.ravel()]).reshape(z.shape)
+    return 2.0 * (1.0 - cdf)
+
+
+def moments(film):
+    """bitmap_extract (test_renders.py:55-60) on the raw moment film: per-pixel mean of the nested integrator's Y
+    and its variance m2 - mean^2."""
+    film = film.astype(np.float64)
+    w = film[..., 4]
+    mean, m2 = film[..., 6] / w, film[..., 9] / w
+    return mean, m2 - mean * mean, w
+
+
+def check_z_test(film, ref_film):
+    mean, var, n = moments(film)
+    ref_mean, ref_var, _ = moments(ref_film)
+    p = z_test(mean, n, ref_mean, ref_var)
+    alpha = 1.0 - (1.0 - 0.01) ** (1.0 / p.size)   # Sidak correction, significance level 0.01 (test_renders.py:117-124)
+    assert (p > alpha).all(), "z-test failed on %d of %d pixels" % ((p <= alpha).sum(), p.size)
+    # and the north star's plainer statement: image mean within 3 sigma of the reference estimate
+    sigma = np.sqrt((ref_var / n).sum()) / p.size
+    assert abs(mean.mean() - ref_mean.mean()) <= 3 * np.sqrt(2) * sigma
+
+
+def test_oracle_passes_reference_z_test(pkg, oracle):
+    """Gate (iii) of SURVEY 8(d): an INDEPENDENT estimate (wavefront seeding: other random streams than the
+    reference's scalar seeding) agrees with the reference's moment film under the reference's z-test."""
+    d, variant = make_ref_golden.scene_dict("c2_moment_256spp")
+    r = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT)
+    check_z_test(r.film, REF["c2_moment_256spp"])
 
 
 @pytest.mark.parametrize("name", sorted(make_ref_golden.CASES))
@@ -95,6 +139,15 @@ def test_reference_live(pkg, oracle):
     film, _ = ref_xml.render(d, "scalar_mono", write_vol=pkg.scene.write_vol)
     r = oracle.render(pkg, pkg.load_dict(d), pkg.abi.SEED_SCALAR_BLOCKS)
     check_against_reference("c2_tau01_live", r.film, film, "scalar_mono")
+
+
+@pytest.mark.gpu
+def test_cuda_passes_reference_z_test(pkg):
+    """The CUDA path at 16x the reference's sample count, independent streams, under the reference's z-test."""
+    d, variant = make_ref_golden.scene_dict("c2_moment_256spp")
+    d["sensor"]["sampler"]["sample_count"] = 4096
+    got = pkg.render(pkg.load_dict(d, variant), device=0, seed_mode=pkg.abi.SEED_WAVEFRONT)
+    check_z_test(got.film, REF["c2_moment_256spp"])
 
 
 @pytest.mark.gpu
