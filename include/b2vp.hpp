@@ -201,16 +201,26 @@ public:
     SceneBuilder() : sc_(new Scene()) {
         for (int k = 0; k < 3; ++k) { bmin_[k] = std::numeric_limits<F>::infinity(); bmax_[k] = -bmin_[k]; }
     }
-    int add_bsdf(const Diffuse &b) { return push_bsdf(B2VP_BSDF_DIFFUSE, (F) b.reflectance, 0, 0, 0); }
+    /* A float property as a plugin reads it: Properties keeps floats, 3-vectors and transforms in single precision
+       in every variant (include/mitsuba/core/properties.h:55-56); the plugin widens the value to Float. */
+    static F prop(double v) { return (F) (float) v; }
+    static Vec3<F> prop3(const std::array<double, 3> &v) { return { prop(v[0]), prop(v[1]), prop(v[2]) }; }
+    static Mat4<F> prop_xf(const Mat4<F> &t) { Mat4<F> r; for (int i = 0; i < 16; ++i) r.m[i] = (F) (float) t.m[i]; return r; }
+    /* normalize(props.vector3f(..)): the normalisation itself runs in single precision (distant.cpp:253, directional.cpp:55) */
+    static Vec3<F> prop_dir(const std::array<double, 3> &v) {
+        Vec3<float> d = normalize(Vec3<float>{ (float) v[0], (float) v[1], (float) v[2] });
+        return { (F) d[0], (F) d[1], (F) d[2] };
+    }
+    int add_bsdf(const Diffuse &b) { return push_bsdf(B2VP_BSDF_DIFFUSE, prop(b.reflectance), 0, 0, 0); }
     int add_bsdf(const Null &) { return push_bsdf(B2VP_BSDF_NULL, 0, 0, 0, 0); }
-    int add_bsdf(const Bilambertian &b) { return push_bsdf(B2VP_BSDF_BILAMBERTIAN, (F) b.reflectance, (F) b.transmittance, 0, 0); }
-    int add_bsdf(const Rpv &b) { return push_bsdf(B2VP_BSDF_RPV, (F) b.rho_0, (F) b.k, (F) b.g, (F) (b.rho_c < 0 ? b.rho_0 : b.rho_c)); }
+    int add_bsdf(const Bilambertian &b) { return push_bsdf(B2VP_BSDF_BILAMBERTIAN, prop(b.reflectance), prop(b.transmittance), 0, 0); }
+    int add_bsdf(const Rpv &b) { return push_bsdf(B2VP_BSDF_RPV, prop(b.rho_0), prop(b.k), prop(b.g), prop(b.rho_c < 0 ? b.rho_0 : b.rho_c)); }
 
     int add_medium(const Homogeneous &m, const Phase &ph) {
         B2vpMedium o{};
         o.type = B2VP_MEDIUM_HOMOGENEOUS;
         o.albedo = add_volume(ConstVolume{ m.albedo }); o.sigma_t = add_volume(ConstVolume{ m.sigma_t });
-        return push_medium(o, (F) m.scale, m.has_spectral_extinction, m.sample_emitters, ph);
+        return push_medium(o, prop(m.scale), m.has_spectral_extinction, m.sample_emitters, ph);
     }
     /* sigma_t must be a grid (ConstVolume::max is not implemented in the reference, heterogeneous.cpp:29) */
     int add_medium(const Heterogeneous &m, const GridVolume &sigma_t, const Mat4<F> &sigma_t_to_world, double albedo,
@@ -218,11 +228,11 @@ public:
         B2vpMedium o{};
         o.type = B2VP_MEDIUM_HETEROGENEOUS;
         o.albedo = add_volume(ConstVolume{ albedo }); o.sigma_t = add_volume(sigma_t, sigma_t_to_world);
-        return push_medium(o, (F) m.scale, m.has_spectral_extinction, m.sample_emitters, ph);
+        return push_medium(o, prop(m.scale), m.has_spectral_extinction, m.sample_emitters, ph);
     }
     int add_volume(const ConstVolume &v) {
         B2vpVolume o{};
-        o.type = B2VP_VOLUME_CONST; o.channels = 1; o.value = (double) (F) v.value; o.max_value = o.value;
+        o.type = B2VP_VOLUME_CONST; o.channels = 1; o.value = (double) prop(v.value); o.max_value = o.value;
         finish_volume(o, Mat4<F>());
         return (int) sc_->volumes.size() - 1;
     }
@@ -241,13 +251,14 @@ public:
         else throw Error(B2VP_ERR_INVALID, "Invalid wrap mode \"" + v.wrap_mode + "\"");
         sc_->grids.push_back(v.data);
         o.data = sc_->grids.back().data();
-        o.max_value = v.max_value >= 0 ? (double) (F) v.max_value : (double) *std::max_element(v.data.begin(), v.data.end());
-        finish_volume(o, to_world);
+        o.max_value = v.max_value >= 0 ? (double) prop(v.max_value) : (double) *std::max_element(v.data.begin(), v.data.end());
+        finish_volume(o, prop_xf(to_world));
         return (int) sc_->volumes.size() - 1;
     }
 
     /* src/shapes/rectangle.cpp:75-104 */
-    int add_rectangle(const Mat4<F> &to_world, int bsdf, int interior = -1, int exterior = -1) {
+    int add_rectangle(const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1) {
+        const Mat4<F> to_world = prop_xf(to_world_);
         B2vpShape s{};
         s.type = B2VP_SHAPE_RECTANGLE; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
         Vec3<F> dp_du = to_world.vector({ 2, 0, 0 }), dp_dv = to_world.vector({ 0, 2, 0 });
@@ -296,27 +307,28 @@ public:
         static const float UV[4][2] = { { 0, 1 }, { 1, 1 }, { 1, 0 }, { 0, 0 } };
         static const uint32_t T[12][3] = { { 0, 1, 2 }, { 3, 0, 2 }, { 4, 5, 6 }, { 7, 4, 6 }, { 8, 9, 10 }, { 11, 8, 10 },
             { 12, 13, 14 }, { 15, 12, 14 }, { 16, 17, 18 }, { 19, 16, 18 }, { 20, 21, 22 }, { 23, 20, 22 } };
-        Mat4<float> tw;
-        for (int i = 0; i < 16; ++i) tw.m[i] = (float) to_world.m[i];
+        /* cube.cpp:104-107: transformed and normalised in Float, stored as float32 */
+        const Mat4<F> tw = prop_xf(to_world);
         std::vector<float> p, n, uv;
         std::vector<uint32_t> f;
         for (int v = 0; v < 24; ++v) {
-            Vec3<float> q = tw.point({ V[v][0], V[v][1], V[v][2] });
-            Vec3<float> m = normalize(tw.normal({ N[v / 4][0], N[v / 4][1], N[v / 4][2] }));
-            p.insert(p.end(), q.begin(), q.end()); n.insert(n.end(), m.begin(), m.end());
+            Vec3<F> q = tw.point({ (F) V[v][0], (F) V[v][1], (F) V[v][2] });
+            Vec3<F> m = normalize(tw.normal({ (F) N[v / 4][0], (F) N[v / 4][1], (F) N[v / 4][2] }));
+            for (int k = 0; k < 3; ++k) { p.push_back((float) q[k]); n.push_back((float) m[k]); }
             uv.push_back(UV[v % 4][0]); uv.push_back(UV[v % 4][1]);
         }
         for (auto &t : T) f.insert(f.end(), t, t + 3);
         return add_mesh(p, f, bsdf, interior, exterior, &n, &uv);
     }
     void add_emitter(const Directional &e) {
-        Vec3<F> d = normalize(Vec3<F>{ (F) e.direction[0], (F) e.direction[1], (F) e.direction[2] });
+        Vec3<F> d = prop_dir(e.direction);
         Vec3<F> up, t;
         coordinate_system(d, up, t);
-        Mat4<F> tw = Mat4<F>::look_at({ 0, 0, 0 }, d, up);
+        /* Endpoint::m_world_transform is an AnimatedTransform: single precision in every variant (transform.h:366) */
+        Mat4<F> tw = prop_xf(Mat4<F>::look_at({ 0, 0, 0 }, d, up));
         Vec3<F> z = tw.vector({ 0, 0, 1 });
         B2vpEmitter o{};
-        o.type = B2VP_EMITTER_DIRECTIONAL; o.irradiance = (double) (F) e.irradiance;
+        o.type = B2VP_EMITTER_DIRECTIONAL; o.irradiance = (double) prop(e.irradiance);
         for (int k = 0; k < 3; ++k) o.direction[k] = z[k];
         sc_->emitters.push_back(o);
     }
@@ -325,15 +337,15 @@ public:
         o.type = B2VP_SENSOR_DISTANT; o.flip_directions = sn.flip_directions; o.needs_aperture_sample = 1;
         o.direction_type = (film.width == 1 && film.height == 1) ? B2VP_DIR_SINGLE
                            : film.height == 1 ? B2VP_DIR_SAMPLE_WIDTH : B2VP_DIR_SAMPLE_ALL;
-        Vec3<F> d = normalize(Vec3<F>{ (F) sn.direction[0], (F) sn.direction[1], (F) sn.direction[2] });
+        Vec3<F> d = prop_dir(sn.direction);
         Vec3<F> up, tmp;
         if (sn.has_orientation)
-            up = normalize(cross(d, Vec3<F>{ (F) sn.orientation[0], (F) sn.orientation[1], (F) sn.orientation[2] }));
+            up = normalize(cross(d, prop3(sn.orientation)));
         else
             coordinate_system(d, tmp, up);
-        o.to_world = Mat4<F>::look_at({ 0, 0, 0 }, d, up).pod();
+        o.to_world = prop_xf(Mat4<F>::look_at({ 0, 0, 0 }, d, up)).pod();   /* AnimatedTransform: single precision */
         o.target_type = sn.has_ray_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
-        for (int k = 0; k < 3; ++k) o.target_point[k] = (double) (F) sn.ray_target[k];
+        for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.ray_target[k]);
         o.origin_type = B2VP_ORIGIN_BSPHERE;
         sc_->desc.sensor = o;
         have_sensor_ = true;
@@ -341,10 +353,10 @@ public:
     void set_sensor(const RadianceMeter &sn, const IndependentSampler &sampler) {
         B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
         o.type = B2VP_SENSOR_RADIANCEMETER; o.needs_aperture_sample = 0;
-        Vec3<F> org{ (F) sn.origin[0], (F) sn.origin[1], (F) sn.origin[2] }, d{ (F) sn.direction[0], (F) sn.direction[1], (F) sn.direction[2] };
+        Vec3<F> org = prop3(sn.origin), d = prop3(sn.direction);
         Vec3<F> up, tmp;
         coordinate_system(d, up, tmp);
-        o.to_world = Mat4<F>::look_at(org, { org[0] + d[0], org[1] + d[1], org[2] + d[2] }, up).pod();
+        o.to_world = prop_xf(Mat4<F>::look_at(org, { org[0] + d[0], org[1] + d[1], org[2] + d[2] }, up)).pod();
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
