@@ -1,0 +1,468 @@
+// volpath_b200 -- the B200 volpath as a plugin of the reference itself.
+//
+// This is the host side of the drop-in boundary in the reference's own language and plugin API: a Mitsuba
+// integrator plugin (MTS_EXPORT_PLUGIN, loaded by the reference's PluginManager from `plugins/volpath_b200.so`,
+// src/libcore/plugin.cpp:27-36,94-111) whose Integrator::render (include/mitsuba/render/integrator.h:42) reads
+// the object graph the reference's XML / load_dict loaders built, flattens it into the POD tables of
+// include/b2vp.h and calls the C-ABI (libb2vp.so: hand-written CUDA for sm_100a).  A scene file switches to the
+// GPU path by writing <integrator type="volpath_b200"> instead of <integrator type="volpath">; everything else
+// (sensors, films, samplers, media, shapes, the `mitsuba` driver, film->develop()) stays the reference's.
+//
+// There is no CPU fallback: without a usable device b2vp_scene_create fails and render() throws.
+//
+// describe() reads plugin parameters where they live.  The reference exposes only part of them through
+// accessors / traverse() (INTEGRATION.md section 2 lists which); the rest are private members of the plugin
+// classes (rectangle frame, gridvolume filter / wrap mode, distant-sensor target, ...).  A maintainer adopting
+// this plugin would add accessors; here the class definitions are taken from the reference's own plugin sources
+// with member access opened, and objects are recognised by Class::name() (plugins are dlopen'ed RTLD_LOCAL, so
+// dynamic_cast across plugin boundaries is not available anyway).  Nothing of those sources is instantiated in
+// this library except member offsets.
+//
+// Built by oracle/Makefile.ref (needs the reference's headers, so only where /root/reference exists) into
+// oracle/_ref/plugins/volpath_b200.so, next to the reference's own plugins.
+#include <algorithm>
+#include <array>
+#include <atomic>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#define private public
+#define protected public
+#include <mitsuba/core/fresolver.h>
+#include <mitsuba/core/plugin.h>
+#include <mitsuba/core/properties.h>
+#include <mitsuba/core/transform.h>
+#include <mitsuba/core/warp.h>
+#include <mitsuba/render/bsdf.h>
+#include <mitsuba/render/emitter.h>
+#include <mitsuba/render/film.h>
+#include <mitsuba/render/imageblock.h>
+#include <mitsuba/render/integrator.h>
+#include <mitsuba/render/interaction.h>
+#include <mitsuba/render/medium.h>
+#include <mitsuba/render/mesh.h>
+#include <mitsuba/render/phase.h>
+#include <mitsuba/render/sampler.h>
+#include <mitsuba/render/scene.h>
+#include <mitsuba/render/sensor.h>
+#include <mitsuba/render/shape.h>
+#include <mitsuba/render/texture.h>
+
+// class definitions of the plugins whose parameters describe() reads (no plugin entry points from them)
+#undef MTS_EXPORT_PLUGIN
+#define MTS_EXPORT_PLUGIN(...)
+#include <shapes/rectangle.cpp>
+#include <bsdfs/diffuse.cpp>
+#include <bsdfs/rpv.cpp>
+#include <bsdfs/bilambertian.cpp>
+#include <media/homogeneous.cpp>
+#include <media/heterogeneous.cpp>
+#include <textures/grid3d.cpp>
+#include <phase/hg.cpp>
+#include <emitters/directional.cpp>
+#include <sensors/distant.cpp>
+#define RayTargetType MultiDistantRayTargetType   /* distant.cpp and mdistant.cpp both define this enum */
+#include <sensors/mdistant.cpp>
+#undef RayTargetType
+#include <sensors/mradiancemeter.cpp>
+#undef private
+#undef protected
+#undef MTS_EXPORT_PLUGIN
+#define MTS_EXPORT_PLUGIN(Name, Descr)                                                                       \
+    extern "C" {                                                                                             \
+        MTS_EXPORT const char *plugin_name() { return #Name; }                                               \
+        MTS_EXPORT const char *plugin_descr() { return Descr; }                                              \
+    }                                                                                                        \
+    MTS_INSTANTIATE_CLASS(Name)
+
+#include "b2vp.h"
+
+NAMESPACE_BEGIN(mitsuba)
+
+/* The flattened scene: the descriptor and every array it points to. */
+struct B200SceneTables {
+    B2vpSceneDesc desc{};
+    std::vector<B2vpShape> shapes; std::vector<B2vpBsdf> bsdfs; std::vector<B2vpMedium> media;
+    std::vector<B2vpVolume> volumes; std::vector<B2vpPhase> phases; std::vector<B2vpEmitter> emitters;
+    std::vector<float> vpos, vnrm, vuv; std::vector<uint32_t> faces;
+    std::vector<std::vector<float>> grids;
+    std::vector<double> sensor_xf;
+    std::map<const void *, int> bsdf_ids, medium_ids, shape_ids;
+    void finish() {
+        desc.abi_version = B2VP_ABI_VERSION; desc.struct_size = (uint32_t) sizeof(B2vpSceneDesc);
+        desc.n_shapes = (uint32_t) shapes.size(); desc.shapes = shapes.data();
+        desc.n_bsdfs = (uint32_t) bsdfs.size(); desc.bsdfs = bsdfs.data();
+        desc.n_media = (uint32_t) media.size(); desc.media = media.data();
+        desc.n_volumes = (uint32_t) volumes.size(); desc.volumes = volumes.data();
+        for (size_t i = 0, g = 0; i < volumes.size(); ++i)
+            if (volumes[i].type == B2VP_VOLUME_GRID) volumes[i].data = grids[g++].data();
+        desc.n_phases = (uint32_t) phases.size(); desc.phases = phases.data();
+        desc.n_emitters = (uint32_t) emitters.size(); desc.emitters = emitters.data();
+        desc.n_vertices = (uint32_t) (vpos.size() / 3); desc.n_faces = (uint32_t) (faces.size() / 3);
+        desc.vertex_positions = vpos.data(); desc.vertex_normals = vnrm.data(); desc.vertex_texcoords = vuv.data();
+        desc.faces = faces.data();
+        if (!sensor_xf.empty()) desc.sensor.transforms = sensor_xf.data();
+    }
+};
+
+/* Reads the object graph of a loaded scene (the read-out include/b2vp.h documents per field). */
+template <typename Float, typename Spectrum> struct B200Describe {
+    MTS_IMPORT_TYPES(Scene, Sensor, Shape, Mesh, BSDF, Medium, Volume, PhaseFunction, Emitter, Texture, Film, Sampler)
+    using ScalarTransform = ScalarTransform4f;
+    B200SceneTables &t;
+    explicit B200Describe(B200SceneTables &tables) : t(tables) {}
+
+    static std::string cname(const Object *o) { return o->class_()->name(); }
+    [[noreturn]] static void unsupported(const std::string &what) {
+        Throw("volpath_b200: %s is outside the scope of the B200 volpath (SURVEY.md section 8)", what);
+    }
+    template <typename M> static B2vpMat4 mat(const M &m) { /* column-major, m[c*4+r] */
+        B2vpMat4 o;
+        for (int c = 0; c < 4; ++c) for (int r = 0; r < 4; ++r) o.m[c * 4 + r] = (double) m(r, c);
+        return o;
+    }
+    /* a constant texture / spectrum of a mono variant: its value anywhere (src/spectra/uniform.cpp:40-50) */
+    static double texture_value(const Texture *tex) {
+        SurfaceInteraction3f si = zero<SurfaceInteraction3f>();
+        if (cname(tex) != "UniformSpectrum")
+            unsupported("texture class " + cname(tex) + " (only constant reflectances)");
+        return (double) tex->eval(si, true)[0];
+    }
+
+    int phase(const PhaseFunction *p) {
+        B2vpPhase o{};
+        std::string n = cname(p);
+        if (n == "IsotropicPhaseFunction") o.type = B2VP_PHASE_ISOTROPIC;
+        else if (n == "RayleighPhaseFunction") o.type = B2VP_PHASE_RAYLEIGH;
+        else if (n == "HGPhaseFunction") {
+            o.type = B2VP_PHASE_HG;
+            o.g = (double) static_cast<const HGPhaseFunction<Float, Spectrum> *>(p)->m_g;
+        } else unsupported("phase function " + n);
+        t.phases.push_back(o);
+        return (int) t.phases.size() - 1;
+    }
+
+    int volume(const Volume *v) {
+        B2vpVolume o{};
+        std::string n = cname(v);
+        Interaction3f it = zero<Interaction3f>();
+        if (n == "ConstVolume") {
+            o.type = B2VP_VOLUME_CONST; o.channels = 1;
+            o.value = (double) v->eval(it, true)[0];
+            o.max_value = o.value;
+        } else if (n.rfind("GridVolumeImpl_", 0) == 0) {   /* GridVolumeImpl_<channels>_<raw> (grid3d.cpp:420-440) */
+            /* the members read here do not depend on the Channels / Raw template arguments */
+            using G = GridVolumeImpl<Float, Spectrum, 1, false>;
+            const G *g = static_cast<const G *>(v);
+            o.type = B2VP_VOLUME_GRID;
+            o.channels = (int32_t) g->m_metadata.channel_count;
+            o.res[0] = g->m_metadata.shape.x(); o.res[1] = g->m_metadata.shape.y(); o.res[2] = g->m_metadata.shape.z();
+            o.filter = g->m_filter_type == FilterType::Nearest ? B2VP_FILTER_NEAREST : B2VP_FILTER_TRILINEAR;
+            o.wrap = g->m_wrap_mode == WrapMode::Repeat ? B2VP_WRAP_REPEAT
+                     : g->m_wrap_mode == WrapMode::Mirror ? B2VP_WRAP_MIRROR : B2VP_WRAP_CLAMP;
+            o.max_value = (double) g->m_metadata.max;
+            size_t count = (size_t) o.res[0] * o.res[1] * o.res[2] * o.channels;
+            std::vector<float> data(count);
+            for (size_t i = 0; i < count; ++i) data[i] = (float) g->m_data[i];   /* float32 on disk, widened at load */
+            t.grids.push_back(std::move(data));
+        } else unsupported("volume class " + n);
+        o.world_to_local = mat(v->m_world_to_local.matrix);
+        for (int k = 0; k < 3; ++k) { o.bbox_min[k] = (double) v->m_bbox.min[k]; o.bbox_max[k] = (double) v->m_bbox.max[k]; }
+        t.volumes.push_back(o);
+        return (int) t.volumes.size() - 1;
+    }
+
+    int medium(const Medium *m) {
+        if (!m) return -1;
+        auto it = t.medium_ids.find(m);
+        if (it != t.medium_ids.end()) return it->second;
+        B2vpMedium o{};
+        std::string n = cname(m);
+        const Volume *sigma_t, *albedo;
+        if (n == "HomogeneousMedium") {
+            auto *h = static_cast<const HomogeneousMedium<Float, Spectrum> *>(m);
+            o.type = B2VP_MEDIUM_HOMOGENEOUS; sigma_t = h->m_sigmat.get(); albedo = h->m_albedo.get(); o.scale = (double) h->m_scale;
+        } else if (n == "HeterogeneousMedium") {
+            auto *h = static_cast<const HeterogeneousMedium<Float, Spectrum> *>(m);
+            o.type = B2VP_MEDIUM_HETEROGENEOUS; sigma_t = h->m_sigmat.get(); albedo = h->m_albedo.get(); o.scale = (double) h->m_scale;
+        } else unsupported("medium " + n);
+        o.albedo = volume(albedo);
+        o.sigma_t = volume(sigma_t);
+        o.has_spectral_extinction = m->has_spectral_extinction();
+        o.sample_emitters = m->use_emitter_sampling();
+        o.phase = phase(m->phase_function());
+        t.media.push_back(o);
+        return t.medium_ids[m] = (int) t.media.size() - 1;
+    }
+
+    int bsdf(const BSDF *b) {
+        auto it = t.bsdf_ids.find(b);
+        if (it != t.bsdf_ids.end()) return it->second;
+        B2vpBsdf o{};
+        std::string n = cname(b);
+        if (n == "SmoothDiffuse") {
+            o.type = B2VP_BSDF_DIFFUSE;
+            o.p[0] = texture_value(static_cast<const SmoothDiffuse<Float, Spectrum> *>(b)->m_reflectance.get());
+        } else if (n == "Null") {
+            o.type = B2VP_BSDF_NULL;
+        } else if (n == "RPV") {
+            auto *r = static_cast<const RPV<Float, Spectrum> *>(b);
+            o.type = B2VP_BSDF_RPV;
+            o.p[0] = texture_value(r->m_rho_0.get()); o.p[1] = texture_value(r->m_k.get());
+            o.p[2] = texture_value(r->m_g.get()); o.p[3] = texture_value(r->m_rho_c.get());
+        } else if (n == "BiLambertian") {
+            auto *r = static_cast<const BiLambertian<Float, Spectrum> *>(b);
+            o.type = B2VP_BSDF_BILAMBERTIAN;
+            o.p[0] = texture_value(r->m_reflectance.get()); o.p[1] = texture_value(r->m_transmittance.get());
+        } else unsupported("BSDF " + n);
+        t.bsdfs.push_back(o);
+        return t.bsdf_ids[b] = (int) t.bsdfs.size() - 1;
+    }
+
+    /* scene->shapes(): meshes arrive in world space (cube.cpp:104-107, obj.cpp:172); rectangles keep to_world */
+    int shape(const Shape *s) {
+        B2vpShape o{};
+        std::string n = cname(s);
+        o.bsdf = bsdf(s->bsdf());
+        o.interior_medium = medium(s->interior_medium());
+        o.exterior_medium = medium(s->exterior_medium());
+        if (s->is_emitter() || s->is_sensor()) unsupported("area emitters / shape sensors");
+        if (s->is_mesh()) {
+            const Mesh *m = static_cast<const Mesh *>(s);
+            o.type = B2VP_SHAPE_MESH;
+            const uint32_t nv = (uint32_t) m->vertex_count(), nf = (uint32_t) m->face_count();
+            o.vertex_offset = (uint32_t) (t.vpos.size() / 3); o.vertex_count = nv;
+            o.face_offset = (uint32_t) (t.faces.size() / 3); o.face_count = nf;
+            o.has_vertex_normals = m->has_vertex_normals(); o.has_vertex_texcoords = m->has_vertex_texcoords();
+            const float *p = m->m_vertex_positions_buf.data();
+            t.vpos.insert(t.vpos.end(), p, p + (size_t) nv * 3);
+            if (o.has_vertex_normals) { const float *q = m->m_vertex_normals_buf.data(); t.vnrm.insert(t.vnrm.end(), q, q + (size_t) nv * 3); }
+            else t.vnrm.insert(t.vnrm.end(), (size_t) nv * 3, 0.f);
+            if (o.has_vertex_texcoords) { const float *q = m->m_vertex_texcoords_buf.data(); t.vuv.insert(t.vuv.end(), q, q + (size_t) nv * 2); }
+            else t.vuv.insert(t.vuv.end(), (size_t) nv * 2, 0.f);
+            const uint32_t *f = m->m_faces_buf.data();
+            t.faces.insert(t.faces.end(), f, f + (size_t) nf * 3);
+            ScalarTransform id;
+            o.to_world = mat(id.matrix); o.to_object = mat(id.matrix);
+        } else if (n == "Rectangle") {
+            auto *r = static_cast<const Rectangle<Float, Spectrum> *>(s);
+            o.type = B2VP_SHAPE_RECTANGLE;
+            o.to_world = mat(r->m_to_world.matrix); o.to_object = mat(r->m_to_object.matrix);
+            for (int k = 0; k < 3; ++k) {
+                o.frame_s[k] = (double) r->m_frame.s[k]; o.frame_t[k] = (double) r->m_frame.t[k];
+                o.frame_n[k] = (double) r->m_frame.n[k];
+            }
+            o.inv_surface_area = (double) r->m_inv_surface_area;
+        } else unsupported("shape " + n);
+        t.shapes.push_back(o);
+        return t.shape_ids[s] = (int) t.shapes.size() - 1;
+    }
+
+    void emitter(const Emitter *e) {
+        if (cname(e) != "DirectionalEmitter") unsupported("emitter " + cname(e));
+        auto *d = static_cast<const DirectionalEmitter<Float, Spectrum> *>(e);
+        B2vpEmitter o{};
+        o.type = B2VP_EMITTER_DIRECTIONAL;
+        /* directional.cpp:112: the direction is to_world * (0, 0, 1), to_world in single precision (transform.h:366) */
+        auto trafo = d->m_world_transform->eval(0.f);
+        ScalarVector3f dir = trafo.transform_affine(ScalarVector3f(0.f, 0.f, 1.f));
+        for (int k = 0; k < 3; ++k) o.direction[k] = (double) dir[k];
+        o.irradiance = texture_value(d->m_irradiance.get());
+        t.emitters.push_back(o);
+    }
+
+    void sensor(const Sensor *sn) {
+        B2vpSensor o{};
+        std::string n = cname(sn);
+        const Film *film = sn->film();
+        const Sampler *sampler = sn->m_sampler.get();
+        if (cname(film) != "HDRFilm") unsupported("film " + cname(film));
+        if (cname(sampler) != "IndependentSampler") unsupported("sampler " + cname(sampler));
+        if (film->reconstruction_filter()->radius() > 0.5f + math::RayEpsilon<float>)
+            unsupported("reconstruction filters wider than the box filter");
+        o.film_size[0] = film->size().x(); o.film_size[1] = film->size().y();
+        o.crop_offset[0] = film->crop_offset().x(); o.crop_offset[1] = film->crop_offset().y();
+        o.crop_size[0] = film->crop_size().x(); o.crop_size[1] = film->crop_size().y();
+        o.sample_count = sampler->sample_count();
+        o.sampler_seed = sampler->m_base_seed;
+        o.shutter_open = (double) sn->shutter_open(); o.shutter_open_time = (double) sn->shutter_open_time();
+        o.medium = medium(sn->medium());
+        o.target_shape = o.origin_shape = -1;
+        o.needs_aperture_sample = sn->needs_aperture_sample();
+        auto world = sn->m_world_transform->eval(0.f);   /* AnimatedTransform: single precision */
+        ScalarTransform4f world_s(world);
+        o.to_world = mat(world_s.matrix);
+        auto target_point = [&](const auto &p) { for (int k = 0; k < 3; ++k) o.target_point[k] = (double) p[k]; };
+        if (n.rfind("DistantSensor_", 0) == 0) {
+            /* the members read do not depend on the target / origin template arguments */
+            using D = DistantSensorImpl<Float, Spectrum, RayTargetType::Point, RayOriginType::BoundingSphere>;
+            const D *d = static_cast<const D *>(sn);
+            o.type = B2VP_SENSOR_DISTANT;
+            o.flip_directions = d->m_flip_directions;
+            o.direction_type = d->m_direction_type == RayDirectionType::Single ? B2VP_DIR_SINGLE
+                               : d->m_direction_type == RayDirectionType::SampleWidth ? B2VP_DIR_SAMPLE_WIDTH : B2VP_DIR_SAMPLE_ALL;
+            if (n == "DistantSensor_Point_BoundingSphere") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_ray_target_point); }
+            else if (n == "DistantSensor_None_BoundingSphere") o.target_type = B2VP_TARGET_NONE;
+            else unsupported("distant sensor with shape targets / origins (" + n + ")");
+            o.origin_type = B2VP_ORIGIN_BSPHERE;
+        } else if (n == "RadianceMeter") {
+            o.type = B2VP_SENSOR_RADIANCEMETER;
+        } else if (n.rfind("MultiDistantSensor_", 0) == 0) {
+            using D = MultiDistantSensorImpl<Float, Spectrum, MultiDistantRayTargetType::Point>;
+            const D *d = static_cast<const D *>(sn);
+            o.type = B2VP_SENSOR_MDISTANT;
+            if (n == "MultiDistantSensor_Point") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_target_point); }
+            else if (n == "MultiDistantSensor_NoTarget") o.target_type = B2VP_TARGET_NONE;
+            else unsupported("mdistant sensor with a shape target");
+            o.n_transforms = (int32_t) d->m_sensor_count;
+            for (size_t i = 0; i < d->m_sensor_count * 16; ++i) t.sensor_xf.push_back((double) d->m_transforms[i]);
+        } else if (n == "MultiRadianceMeter") {
+            auto *d = static_cast<const MultiRadianceMeter<Float, Spectrum> *>(sn);
+            o.type = B2VP_SENSOR_MRADIANCEMETER;
+            o.n_transforms = (int32_t) d->m_sensor_count;
+            for (size_t i = 0; i < d->m_sensor_count * 16; ++i) t.sensor_xf.push_back((double) d->m_transforms[i]);
+        } else unsupported("sensor " + n);
+        t.desc.sensor = o;
+    }
+
+    void scene(const Scene *sc, const Sensor *sn) {
+        t.desc.precision = std::is_same_v<ScalarFloat, double> ? B2VP_PREC_F64 : B2VP_PREC_F32;
+        for (auto &s : sc->shapes()) shape(s.get());
+        for (auto &e : sc->emitters()) emitter(e.get());
+        if (sc->environment()) unsupported("environment emitters");
+        sensor(sn);
+        /* Scene::bbox() and the padded bounding sphere of distant.cpp:292-297 / directional.cpp:68-73 */
+        ScalarBoundingBox3f bbox = sc->bbox();
+        auto bs = bbox.bounding_sphere();
+        bs.radius = enoki::max(math::RayEpsilon<Float>, bs.radius * (1.f + math::RayEpsilon<Float>));
+        for (int k = 0; k < 3; ++k) {
+            t.desc.bbox_min[k] = (double) bbox.min[k]; t.desc.bbox_max[k] = (double) bbox.max[k];
+            t.desc.bsphere_center[k] = (double) bs.center[k];
+        }
+        t.desc.bsphere_radius = (double) bs.radius;
+    }
+};
+
+/* The integrator plugin.  Properties are those of `volpath` (src/integrators/volpath.cpp:19-25 over
+   MonteCarloIntegrator / SamplingIntegrator, src/librender/integrator.cpp:23-39,302-315): max_depth, rr_depth,
+   hide_emitters, block_size, samples_per_pass, timeout; plus `device` (CUDA ordinal, default 0). */
+template <typename Float, typename Spectrum>
+class B200VolumetricPathIntegrator final : public MonteCarloIntegrator<Float, Spectrum> {
+public:
+    MTS_IMPORT_BASE(MonteCarloIntegrator, m_max_depth, m_rr_depth, m_hide_emitters, m_stop, m_block_size,
+                    m_samples_per_pass, m_render_timer)
+    MTS_IMPORT_TYPES(Scene, Sensor, Film, ImageBlock, Sampler, Medium)
+
+    B200VolumetricPathIntegrator(const Properties &props) : Base(props) {
+        if constexpr (!is_monochromatic_v<Spectrum> || is_array_v<Float>)
+            Throw("volpath_b200 supports the scalar_mono and scalar_mono_double variants only");
+        m_device = props.int_("device", 0);
+    }
+    ~B200VolumetricPathIntegrator() { release(); }
+
+    /* Integrator::render (integrator.h:42); replaces SamplingIntegrator::render (integrator.cpp:51-179) */
+    bool render(Scene *scene, Sensor *sensor) override {
+        m_stop = false;
+        B200SceneTables tables;
+        describe(scene, sensor, tables);
+        release();
+        check(b2vp_scene_create(&tables.desc, m_device, &m_scene));
+
+        ref<Film> film = sensor->film();
+        std::vector<std::string> channels = { "X", "Y", "Z", "A", "W" };   /* integrator.cpp:67-73 */
+        film->prepare(channels);
+        ScalarVector2i size = film->crop_size();
+        ref<ImageBlock> block = new ImageBlock(size, channels.size(), film->reconstruction_filter(), false);
+        block->set_offset(film->crop_offset());
+        block->clear();
+        if (block->border_size() != 0)
+            Throw("volpath_b200: only the box reconstruction filter is supported");
+
+        m_render_timer.reset();
+        B2vpRenderArgs args{};
+        args.abi_version = B2VP_ABI_VERSION; args.struct_size = (uint32_t) sizeof(args);
+        args.device = m_device;
+        args.precision = tables.desc.precision;
+        args.seed_mode = B2VP_SEED_SCALAR_BLOCKS;      /* the scalar variants' seeding (integrator.cpp:89-130,198) */
+        args.clear_film = 1;
+        args.totals = &m_totals;
+        int rc = b2vp_render(m_scene, &args, block->data().data());   /* host XYZAW buffer, crop_size x 5 */
+        if (rc == B2VP_ERR_CANCELLED) return false;
+        check(rc);
+        film->put(block);                              /* as the reference's wavefront branch, integrator.cpp:155-171 */
+        if (!m_stop)
+            Log(Info, "Processing finished. (took %s; %d paths, %d kernel launches, %.2f ms on the GPU)",
+                util::time_string(m_render_timer.value(), true), (uint64_t) m_totals.n_paths,
+                (uint32_t) m_totals.n_launches, m_totals.gpu_ms);
+        return !m_stop;
+    }
+
+    void cancel() override { m_stop = true; if (m_scene) b2vp_cancel(m_scene); }   /* integrator.h:51 */
+
+    /* the batch boundary is render(): a single-sample entry point does not exist on the GPU path */
+    std::pair<Spectrum, Mask> sample(const Scene *, Sampler *, const RayDifferential3f &, const Medium *, Float *,
+                                     Mask) const override {
+        NotImplementedError("sample");
+    }
+
+    /* object graph -> POD tables of include/b2vp.h */
+    void describe(const Scene *scene, const Sensor *sensor, B200SceneTables &tables) const {
+        B200Describe<Float, Spectrum> d(tables);
+        d.scene(scene, sensor);
+        B2vpIntegrator &it = tables.desc.integrator;
+        it.max_depth = m_max_depth; it.rr_depth = m_rr_depth; it.hide_emitters = m_hide_emitters;
+        it.block_size = m_block_size;
+        it.samples_per_pass = (uint32_t) m_samples_per_pass;
+        it.arg_order_ltr = 0;   /* GCC evaluates the sample arguments right to left (include/b2vp.h) */
+        it.moment = 0;
+        tables.finish();
+    }
+
+    std::string to_string() const override {
+        return tfm::format("B200VolumetricPathIntegrator[\n  max_depth = %i,\n  rr_depth = %i,\n  device = %i\n]",
+                           m_max_depth, m_rr_depth, m_device);
+    }
+    MTS_DECLARE_CLASS()
+private:
+    static void check(int rc) { if (rc != B2VP_OK) Throw("volpath_b200: %s", b2vp_last_error()); }
+    void release() { if (m_scene) b2vp_scene_destroy(m_scene); m_scene = nullptr; }
+    b2vp_scene_t *m_scene = nullptr;
+    B2vpCounters m_totals{};
+    int m_device = 0;
+};
+
+MTS_IMPLEMENT_CLASS_VARIANT(B200VolumetricPathIntegrator, MonteCarloIntegrator)
+MTS_EXPORT_PLUGIN(B200VolumetricPathIntegrator, "B200 volumetric path tracer (CUDA, sm_100a)")
+NAMESPACE_END(mitsuba)
+
+/* Test hook (tests/ only): flattens a loaded scene and hands the descriptor to a callback, so that the CPU test
+   suite can check describe() without a GPU.  `integrator` must be a volpath_b200 instance of the variant. */
+extern "C" MTS_EXPORT int b2vp_plugin_describe(void *scene, void *sensor, void *integrator, int is_double,
+                                               void (*cb)(const B2vpSceneDesc *, void *), void *user) {
+    using namespace mitsuba;
+    B200SceneTables tables;
+    if (is_double) {
+        using F = double; using S = Color<double, 1>;
+        static_cast<B200VolumetricPathIntegrator<F, S> *>((Object *) integrator)
+            ->describe((const Scene<F, S> *) scene, (const Sensor<F, S> *) sensor, tables);
+    } else {
+        using F = float; using S = Color<float, 1>;
+        static_cast<B200VolumetricPathIntegrator<F, S> *>((Object *) integrator)
+            ->describe((const Scene<F, S> *) scene, (const Sensor<F, S> *) sensor, tables);
+    }
+    cb(&tables.desc, user);
+    return 0;
+}

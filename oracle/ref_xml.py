@@ -245,7 +245,7 @@ SHAPES = ("rectangle", "sphere", "cube", "mesh")
 MEDIA = ("homogeneous", "heterogeneous")
 BSDFS = ("diffuse", "rpv", "null", "bilambertian")
 SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter")
-INTEGRATORS = ("volpath", "volpathmis", "moment", "path")
+INTEGRATORS = ("volpath", "volpath_b200", "volpathmis", "moment", "path")
 
 
 def to_xml(scene, workdir, write_vol):
@@ -278,9 +278,25 @@ def to_xml(scene, workdir, write_vol):
     return path
 
 
-def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None, exact_math=False):
-    """Runs the reference on `scene`.  Returns (film[h, w, channels], seconds of the last Integrator::render).
-    exact_math: put oracle_math.h's logf / expf / sincosf / cbrtf in front of glibc (ref_math_preload.cpp)."""
+PLUGIN = os.path.join(REF_DIR, "plugins", "volpath_b200.so")
+ORACLE_LIB = os.path.join(HERE, "libb2vp_oracle.so")
+
+
+def with_plugin(scene):
+    """The same scene with <integrator type="volpath_b200">: the product's plugin inside the reference binary."""
+    d = dict(scene)
+    for k, v in scene.items():
+        if isinstance(v, dict) and v.get("type") == "volpath":
+            d[k] = dict(v, type="volpath_b200")
+    return d
+
+
+def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None, exact_math=False,
+           describe_oracle=False):
+    """Runs the reference binary on `scene`.  Returns (film[h, w, channels], seconds of the last Integrator::render).
+    exact_math: put oracle_math.h's logf / expf / sincosf / cbrtf in front of glibc (ref_math_preload.cpp).
+    describe_oracle (scenes from with_plugin only): do not render on a GPU; run the plugin's describe() and render
+    its descriptor with the CPU oracle (refprobe --describe-oracle)."""
     if not available():
         raise RuntimeError("oracle/_ref/refprobe is not built (run make -f oracle/Makefile.ref where /root/reference exists)")
     tmp = None
@@ -293,8 +309,10 @@ def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, k
         env = dict(os.environ)
         if exact_math:
             env["LD_PRELOAD"] = os.path.join(REF_DIR, "libb2vp_refmath.so")
-        p = subprocess.run([PROBE, variant, xml, out, "-t", str(threads), "-r", str(repeats)],
-                           stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
+        cmd = [PROBE, variant, xml, out, "-t", str(threads), "-r", str(repeats)]
+        if describe_oracle:
+            cmd += ["--describe-oracle", ORACLE_LIB]
+        p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
         if p.returncode != 0:
             raise RuntimeError("refprobe failed (%d): %s" % (p.returncode, p.stderr[-2000:]))
         with open(out, "rb") as f:
