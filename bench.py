@@ -95,6 +95,20 @@ def ref_time_sample(pkg, budget_s, threads):
     return {"paths": n, "seconds": sec, "mpaths_s": n / sec / 1e6, "spp": spp}
 
 
+def plugin_time(pkg, spp):
+    """The drop-in path end to end: the UNMODIFIED reference binary (oracle/_ref/refprobe) loads the workload's XML
+    scene with <integrator type="volpath_b200"> and calls Integrator::render three times; the time of the last call
+    (object graph -> descriptor, scene upload, kernel, film read-back, film->put) is reported.  None where
+    oracle/_ref is not built."""
+    from oracle import ref_xml
+    if not (ref_xml.available() and os.path.exists(ref_xml.PLUGIN)):
+        return None
+    d = ref_xml.with_plugin(ref_xml.round_f32(workload(spp)))
+    _, sec = ref_xml.render(d, "scalar_mono", threads=1, repeats=3, write_vol=pkg.scene.write_vol)
+    return {"value": WIDTH * spp / sec / 1e6, "unit": "Mpaths/s", "ms_per_render": sec * 1e3,
+            "what": "reference binary + volpath_b200 plugin, time of Integrator::render (third call in the process)"}
+
+
 class ClockSampler:
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
@@ -315,6 +329,13 @@ def run_ours(args):
                              "segments_per_s": cb["segments_s"],
                              "one_thread_mpaths_s": cb["pilot_mpaths_s_1thread"]},
         }
+        if not args.profile:
+            try:
+                pl = plugin_time(pkg, args.spp)
+            except RuntimeError as e:   # reported, never fatal for the bench line
+                pl = {"error": str(e)[-300:]}
+            if pl is not None:
+                out["e2e_plugin"] = pl
         if rb is not None:  # the unmodified reference binary is built on this box: it is the baseline, the port is kept beside it
             out["cpu_baseline"] = {"value": rb["mpaths_s"], "unit": "Mpaths/s", "cores": threads, "kind": "reference",
                                    "sample": "the workload at %d spp (%d paths), unmodified reference binary "
