@@ -65,6 +65,7 @@
 #undef MTS_EXPORT_PLUGIN
 #define MTS_EXPORT_PLUGIN(...)
 #include <shapes/rectangle.cpp>
+#include <shapes/sphere.cpp>
 #include <bsdfs/diffuse.cpp>
 #include <bsdfs/rpv.cpp>
 #include <bsdfs/bilambertian.cpp>
@@ -265,6 +266,14 @@ template <typename Float, typename Spectrum> struct B200Describe {
                 o.frame_s[k] = (double) r->m_frame.s[k]; o.frame_t[k] = (double) r->m_frame.t[k];
                 o.frame_n[k] = (double) r->m_frame.n[k];
             }
+            o.inv_surface_area = (double) r->m_inv_surface_area;
+        } else if (n == "Sphere") {
+            auto *r = static_cast<const Sphere<Float, Spectrum> *>(s);
+            o.type = B2VP_SHAPE_SPHERE;
+            o.to_world = mat(r->m_to_world.matrix); o.to_object = mat(r->m_to_object.matrix);
+            for (int k = 0; k < 3; ++k) o.center[k] = (double) r->m_center[k];
+            o.radius = (double) r->m_radius;
+            o.flip_normals = r->m_flip_normals;
             o.inv_surface_area = (double) r->m_inv_surface_area;
         } else unsupported("shape " + n);
         t.shapes.push_back(o);
