@@ -77,6 +77,45 @@ def _moment(d):
     return d
 
 
+def _c2_edit(fn, **kw):
+    d = scenes.c2(**kw)
+    fn(d)
+    return d
+
+
+def _crop(d):
+    d["sensor"]["film"].update({"crop_offset_x": 16, "crop_offset_y": 0, "crop_width": 40, "crop_height": 1})
+
+
+def _seed7(d):
+    d["sensor"]["sampler"]["seed"] = 7
+
+
+def _wrap(mode):
+    def f(d):
+        # the grid covers the lower 40 % of the atmosphere only; above it the lookups wrap
+        T = scenes.T
+        v = d["atm"]["sigma_t"]
+        v["wrap_mode"] = mode
+        v["to_world"] = T.translate([-10, -10, 0], np.float32) @ T.scale([20, 20, 0.4], np.float32)
+        v["data"] = v["data"][:64]
+    return f
+
+
+def _rgb_grid(d):
+    g = d["atm"]["sigma_t"]["data"][:, :, :, None] if d["atm"]["sigma_t"]["data"].ndim == 3 else d["atm"]["sigma_t"]["data"]
+    d["atm"]["sigma_t"]["data"] = np.concatenate([g * 0.5, g, g * 1.5], axis=3).astype(np.float32)
+
+
+def _sensor_in_medium(spp, variant):
+    """radiancemeter inside the homogeneous atmosphere of C1 (sensor->medium())."""
+    d = scenes.c1(spp=spp, variant=variant)
+    d["sensor"] = {"type": "radiancemeter", "origin": [0.125, -0.25, 0.5], "direction": [0.25, 0.125, -1.0],
+                   "medium": {"type": "ref", "id": "atm"},
+                   "sampler": {"type": "independent", "sample_count": spp}, "film": scenes.film(1)}
+    return d
+
+
 _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # SURVEY 8(f) N3: two-sided leaves
 
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
@@ -107,6 +146,19 @@ CASES = {
     "c2_moment": (lambda v: _moment(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono"),
     "c2_moment_256spp": (lambda v: _moment(scenes.c2(spp=256, variant=v, width=32)), "scalar_mono"),
     "c2_moment_f64": (lambda v: _moment(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
+    # edge cases of the render driver and the volume lookups
+    "c2_crop": (lambda v: _c2_edit(_crop, spp=1, variant=v, width=64), "scalar_mono"),
+    "c2_seed7": (lambda v: _c2_edit(_seed7, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_passes": (lambda v: scenes.c2(spp=8, variant=v, width=48, samples_per_pass=2, block_size=16), "scalar_mono"),
+    "c2_maxdepth1": (lambda v: scenes.c2(spp=1, variant=v, width=128, max_depth=1), "scalar_mono"),
+    "c2_rr1": (lambda v: scenes.c2(spp=1, variant=v, width=128, rr_depth=1), "scalar_mono"),
+    "c2_hide_emitters": (lambda v: scenes.c2(spp=1, variant=v, width=64, hide_emitters=True), "scalar_mono"),
+    "c2_notspectral": (lambda v: scenes.c2(spp=1, variant=v, width=128, spectral=False), "scalar_mono"),
+    "c2_repeat": (lambda v: _c2_edit(_wrap("repeat"), spp=1, variant=v, width=128, nz=160), "scalar_mono"),
+    "c2_mirror": (lambda v: _c2_edit(_wrap("mirror"), spp=1, variant=v, width=128, nz=160), "scalar_mono"),
+    "c2_rgb_grid": (lambda v: _c2_edit(_rgb_grid, spp=1, variant=v, width=128, nz=100), "scalar_mono"),
+    "c1_sensor_in_medium": (lambda v: _sensor_in_medium(512, v), "scalar_mono"),
+    "c3_blocks_f64": (lambda v: _c3(spp=2, variant=v, n=16, size=20, block_size=8, samples_per_pass=1), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
