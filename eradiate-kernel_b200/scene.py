@@ -49,6 +49,47 @@ def write_vol(path, data, bbox=(0, 0, 0, 1, 1, 1)):
         f.write(data.tobytes())
 
 
+def read_obj(path, flip_tex_coords=True):
+    """Wavefront OBJ as src/shapes/obj.cpp:140-325 reads it: `v`, `vn`, `vt`, `f`; one output vertex per distinct
+    (v, vt, vn) index triple, numbered in order of first use; polygons as triangle fans.  Returns
+    (positions[n, 3], faces[m, 3], normals[n, 3] or None, texcoords[n, 2] or None), all float32 / uint32,
+    positions and normals still in object space."""
+    vs, vns, vts, tris = [], [], [], []
+    ids, order = {}, []
+    with open(path, "r") as f:
+        for line in f:
+            tok = line.split()
+            if not tok:
+                continue
+            if tok[0] == "v":
+                vs.append([np.float32(x) for x in tok[1:4]])
+            elif tok[0] == "vn":
+                vns.append([np.float32(x) for x in tok[1:4]])
+            elif tok[0] == "vt":
+                u, v = np.float32(tok[1]), np.float32(tok[2])
+                vts.append([u, np.float32(1) - v if flip_tex_coords else v])
+            elif tok[0] == "f":
+                corner = []
+                for item in tok[1:]:
+                    parts = (item.split("/") + ["", ""])[:3]
+                    key = tuple(int(x) if x else 0 for x in parts)
+                    if not 1 <= key[0] <= len(vs):
+                        raise RuntimeError("Error while loading OBJ file %r: reference to invalid vertex %d!" % (path, key[0]))
+                    if key not in ids:
+                        ids[key] = len(order)
+                        order.append(key)
+                    corner.append(ids[key])
+                for k in range(1, len(corner) - 1):
+                    tris.append([corner[0], corner[k], corner[k + 1]])
+    pos = np.array([vs[k[0] - 1] for k in order], dtype=np.float32).reshape(-1, 3)
+    nrm = uv = None
+    if vns:
+        nrm = np.array([vns[k[2] - 1] if k[2] else [0, 0, 0] for k in order], dtype=np.float32).reshape(-1, 3)
+    if vts:
+        uv = np.array([vts[k[1] - 1] if k[1] else [0, 0] for k in order], dtype=np.float32).reshape(-1, 2)
+    return pos, np.array(tris, dtype=np.uint32).reshape(-1, 3), nrm, uv
+
+
 class _Builder:
     def __init__(self, variant):
         if variant not in VARIANTS:
@@ -331,6 +372,19 @@ class _Builder:
             if node.get("flip_normals", False):
                 n = -n
             self.add_mesh(s, p, tris, n, uvs)
+        elif t == "obj":  # src/shapes/obj.cpp
+            pos, faces, nrm, uv = read_obj(node["filename"], bool(node.get("flip_tex_coords", True)))
+            face_normals = bool(node.get("face_normals", False))  # mesh.cpp:30-31: no vertex normals at all
+            if nrm is None and not face_normals:
+                raise RuntimeError("obj: files without normals need face_normals=true (smooth vertex normals, "
+                                   "Mesh::recompute_vertex_normals, are not built in the B200 volpath)")
+            if face_normals:
+                nrm = None
+            pos = to_world.point_affine(pos.astype(self.dtype)).astype(np.float32)
+            if nrm is not None:
+                nrm = to_world.normal(nrm.astype(self.dtype))
+                nrm = (nrm / np.sqrt(np.sum(nrm * nrm, axis=1, dtype=self.dtype))[:, None]).astype(np.float32)
+            self.add_mesh(s, pos, faces, nrm, uv)
         elif t == "mesh":  # in-memory triangle mesh (what obj/ply/serialized loaders produce, src/librender/mesh.cpp)
             # obj.cpp:172,186: float32 input, transformed in the variant's type, stored as float32
             pos = np.asarray(node["vertex_positions"], dtype=np.float32).reshape(-1, 3)
@@ -533,7 +587,7 @@ def load_dict(d, variant="scalar_mono"):
     b = _Builder(variant)
     sensor_node = integrator_node = None
     emitters = []
-    shape_kinds = ("rectangle", "sphere", "cube", "mesh")
+    shape_kinds = ("rectangle", "sphere", "cube", "mesh", "obj")
     # children are visited in key order, as Properties::objects() does (std::map)
     items = [(k, v) for k, v in sorted(d.items()) if isinstance(v, dict)]
     # first pass: named media / bsdfs so that references resolve regardless of order

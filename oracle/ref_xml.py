@@ -150,7 +150,11 @@ class _Writer:
     def shape(self, v, ident):
         t = v["type"]
         out = []
-        if t == "mesh":
+        if t == "obj":
+            out.append('<shape type="obj" id="%s"><string name="filename" value="%s"/>' % (ident, v["filename"]))
+            if "face_normals" in v:
+                out.append('<boolean name="face_normals" value="%s"/>' % ("true" if v["face_normals"] else "false"))
+        elif t == "mesh":
             path = os.path.join(self.dir, "mesh%d.obj" % self.n_files)
             self.n_files += 1
             _write_obj(path, v["vertex_positions"], v["faces"], v.get("vertex_normals"))
@@ -241,7 +245,7 @@ class _Writer:
         return "".join(out)
 
 
-SHAPES = ("rectangle", "sphere", "cube", "mesh")
+SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj")
 MEDIA = ("homogeneous", "heterogeneous")
 BSDFS = ("diffuse", "rpv", "null", "bilambertian")
 SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter")

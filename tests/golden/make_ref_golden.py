@@ -116,6 +116,17 @@ def _sensor_in_medium(spp, variant):
     return d
 
 
+def _c2_obj(face_normals, **kw):
+    """C2 with a small OBJ mesh (tests/golden/data/roof.obj: quads, normals, texcoords, shared vertices) floating in
+    the atmosphere, loaded by the reference's obj plugin on one side and by scene.read_obj on the other."""
+    d = scenes.c2(**kw)
+    T = scenes.T
+    d["roof"] = {"type": "obj", "filename": os.path.join(HERE, "data", "roof.obj"), "face_normals": face_normals,
+                 "to_world": T.translate([0.25, -0.5, 0.125], np.float32) @ T.scale([2.0, 1.5, 1.0], np.float32),
+                 "bsdf": {"type": "diffuse", "reflectance": 0.75}}
+    return d
+
+
 _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # SURVEY 8(f) N3: two-sided leaves
 
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
@@ -159,6 +170,9 @@ CASES = {
     "c2_rgb_grid": (lambda v: _c2_edit(_rgb_grid, spp=1, variant=v, width=128, nz=100), "scalar_mono"),
     "c1_sensor_in_medium": (lambda v: _sensor_in_medium(512, v), "scalar_mono"),
     "c3_blocks_f64": (lambda v: _c3(spp=2, variant=v, n=16, size=20, block_size=8, samples_per_pass=1), "scalar_mono_double"),
+    "c2_obj_normals": (lambda v: _c2_obj(False, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_obj_face_normals": (lambda v: _c2_obj(True, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_obj_normals_f64": (lambda v: _c2_obj(False, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
