@@ -19,6 +19,16 @@ class RenderResult:
         with np.errstate(divide="ignore", invalid="ignore"):
             return np.where(w > 0, self.film[..., 1] / w, 0).astype(self.film.dtype)
 
+    def write_pfm(self, path):
+        """film->develop() for file_format=pfm, pixel_format=luminance, component_format=float32 (the output the
+        reference CLI is driven with): `Pf`, size, `-1` (little endian), then the scanlines
+        bottom to top (Bitmap::write_pfm, src/libcore/bitmap.cpp:2206-2230)."""
+        img = np.ascontiguousarray(self.bitmap(), dtype="<f4")
+        h, w = img.shape
+        with open(path, "wb") as f:
+            f.write(("Pf\n%u %u\n-1\n" % (w, h)).encode())
+            f.write(img[::-1].tobytes())
+
     @property
     def segments(self):
         return self.totals.n_medium_steps + self.totals.n_intersect

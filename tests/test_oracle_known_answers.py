@@ -128,3 +128,18 @@ def test_cube_faces(pkg, oracle):
             d = np.zeros(3); d[axis] = sign
             h = oracle.ray_intersect(sc, o + [0.3, 0.2, 0.1] * (1 - np.abs(d)), d, mint=0.0)
             assert np.isclose(h["t"], 4.0) and np.allclose(h["n"], -d)
+
+
+def test_film_develop_pfm(pkg, tmp_path):
+    """RenderResult.write_pfm: luminance = Y / W, float32, scanlines bottom to top (bitmap.cpp:2206-2230)."""
+    film = np.zeros((2, 3, 5), dtype=np.float32)
+    film[..., 1] = np.arange(6, dtype=np.float32).reshape(2, 3) * 2
+    film[..., 4] = 2
+    film[1, 2, 4] = 0          # a pixel without samples develops to 0
+    r = pkg.RenderResult(film, None)
+    path = tmp_path / "out.pfm"
+    r.write_pfm(str(path))
+    raw = path.read_bytes()
+    assert raw.startswith(b"Pf\n3 2\n-1\n")
+    data = np.frombuffer(raw[len(b"Pf\n3 2\n-1\n"):], dtype="<f4").reshape(2, 3)
+    assert np.array_equal(data, np.array([[3, 4, 0], [0, 1, 2]], dtype=np.float32))
