@@ -41,7 +41,7 @@ template <typename F> std::unique_ptr<b2vp::Scene> scene_c2(uint32_t spp, int wi
     return sb.finish();
 }
 
-static b2vp::Film oracle_render(const b2vp::Scene &s) {
+static b2vp::Film oracle_render(const b2vp::Scene &s, int seed_mode = B2VP_SEED_WAVEFRONT) {
     b2vp::Film f;
     f.width = s.width(); f.height = s.height(); f.precision = s.desc.precision;
     size_t n = (size_t) f.width * f.height * 5;
@@ -49,7 +49,7 @@ static b2vp::Film oracle_render(const b2vp::Scene &s) {
     if (f.precision == B2VP_PREC_F32) { f.f32.assign(n, 0.f); buf = f.f32.data(); } else { f.f64.assign(n, 0.0); buf = f.f64.data(); }
     B2vpRenderArgs a{};
     a.abi_version = B2VP_ABI_VERSION; a.struct_size = sizeof(a); a.precision = f.precision;
-    a.seed_mode = B2VP_SEED_WAVEFRONT; a.clear_film = 1; a.totals = &f.totals;
+    a.seed_mode = seed_mode; a.clear_film = 1; a.totals = &f.totals;
     if (b2vp_oracle_render(&s.desc, &a, buf) != 0) { std::fprintf(stderr, "oracle failed\n"); std::exit(2); }
     return f;
 }
@@ -88,6 +88,20 @@ int main(int argc, char **argv) {
                 return e.code() == B2VP_ERR_NO_DEVICE ? 0 : 1;
             }
         }
+        return 0;
+    }
+    if (mode == "dump") {
+        /* test_host dump <f32|f64> <out.bin>: the C2-shaped scene of scene_c2 (1 sample per pixel, 256 pixels) in
+           the reference's scalar seeding order, rendered by the oracle; tests/test_cpp_host.py compares the film
+           with the one the reference binary renders from the same parameters (tests/golden/ref_golden.npz). */
+        const bool f64 = argc > 2 && std::string(argv[2]) == "f64";
+        auto s = f64 ? scene_c2<double>(1, 256) : scene_c2<float>(1, 256);
+        b2vp::Film f = oracle_render(*s, B2VP_SEED_SCALAR_BLOCKS);
+        FILE *out = std::fopen(argc > 3 ? argv[3] : "film.bin", "wb");
+        if (!out) return 2;
+        if (f64) std::fwrite(f.f64.data(), sizeof(double), f.f64.size(), out);
+        else std::fwrite(f.f32.data(), sizeof(float), f.f32.size(), out);
+        std::fclose(out);
         return 0;
     }
     int bad = 0;

@@ -127,6 +127,29 @@ def _c2_obj(face_normals, **kw):
     return d
 
 
+def _c2_cpp_host(variant):
+    """The scene tests/cpp/test_host.cpp::scene_c2 builds with the C++ host layer (include/b2vp.hpp), as a dictionary."""
+    dt = scenes.pkg.scene.VARIANTS[variant][0]
+    T = scenes.T
+    nz = 200
+    grid = np.array([np.float32(np.exp(-((z + 0.5) / nz) * 100.0 / 8.0)) for z in range(nz)], dtype=np.float32).reshape(nz, 1, 1)
+    return {
+        "type": "scene",
+        "integrator": {"type": "volpath", "max_depth": -1},
+        "atm": {"type": "heterogeneous",
+                "sigma_t": {"type": "gridvolume", "data": grid,
+                            "to_world": T.translate([-10, -10, 0], dt) @ T.scale([20, 20, 1], dt)},
+                "scale": 4.0, "albedo": 1.0, "phase": {"type": "rayleigh"}},
+        "cube": {"type": "cube", "to_world": T.translate([0, 0, 0.45], dt) @ T.scale([10, 10, 0.55], dt),
+                 "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}},
+        "ground": {"type": "rectangle", "to_world": T.scale([10, 10, 1], dt),
+                   "bsdf": {"type": "rpv", "rho_0": 0.1, "k": 0.7, "g": -0.1}},
+        "sun": {"type": "directional", "direction": [0.5, 0, -0.8660254037844386], "irradiance": 1.0},
+        "sensor": {"type": "distant", "direction": [0, 0, 1], "orientation": [1, 0, 0], "ray_target": [0, 0, 0],
+                   "sampler": {"type": "independent", "sample_count": 1}, "film": scenes.film(256)},
+    }
+
+
 _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # SURVEY 8(f) N3: two-sided leaves
 
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
@@ -173,6 +196,8 @@ CASES = {
     "c2_obj_normals": (lambda v: _c2_obj(False, spp=1, variant=v, width=128), "scalar_mono"),
     "c2_obj_face_normals": (lambda v: _c2_obj(True, spp=1, variant=v, width=128), "scalar_mono"),
     "c2_obj_normals_f64": (lambda v: _c2_obj(False, spp=1, variant=v, width=64), "scalar_mono_double"),
+    "c2_cpp_host": (_c2_cpp_host, "scalar_mono"),
+    "c2_cpp_host_f64": (_c2_cpp_host, "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

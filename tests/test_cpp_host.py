@@ -37,3 +37,17 @@ def test_cpp_host_matches_oracle_on_gpu(pkg, oracle):
     out = subprocess.run([exe, "gpu"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count("-> ok") == 4
+
+
+@pytest.mark.parametrize("prec", ["f32", "f64"])
+def test_cpp_host_scene_matches_reference_binary(pkg, oracle, prec, tmp_path):
+    """The scene the C++ host layer builds (SceneBuilder<Float>: derived quantities computed in C++) gives the film
+    the reference binary renders from the same parameters (fixture c2_cpp_host*, tests/golden/make_ref_golden.py)."""
+    import numpy as np
+    from test_reference_parity import REF, check_against_reference
+    exe = build_exe(pkg, oracle)
+    out = tmp_path / "film.bin"
+    subprocess.check_call([exe, "dump", prec, str(out)])
+    name = "c2_cpp_host" + ("_f64" if prec == "f64" else "")
+    film = np.fromfile(str(out), dtype=np.float64 if prec == "f64" else np.float32).reshape(1, 256, 5)
+    check_against_reference(name, film, REF[name], "scalar_mono_double" if prec == "f64" else "scalar_mono")
