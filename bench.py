@@ -103,10 +103,11 @@ def plugin_time(pkg, spp):
     from oracle import ref_xml
     if not (ref_xml.available() and os.path.exists(ref_xml.PLUGIN)):
         return None
-    d = ref_xml.with_plugin(ref_xml.round_f32(workload(spp)))
+    d = ref_xml.with_plugin(ref_xml.round_f32(workload(spp)), seeding="wavefront")
     _, sec = ref_xml.render(d, "scalar_mono", threads=1, repeats=3, write_vol=pkg.scene.write_vol)
     return {"value": WIDTH * spp / sec / 1e6, "unit": "Mpaths/s", "ms_per_render": sec * 1e3,
-            "what": "reference binary + volpath_b200 plugin, time of Integrator::render (third call in the process)"}
+            "what": "reference binary + volpath_b200 plugin (wavefront seeding), time of Integrator::render "
+                    "(third call in the process): object graph -> descriptor, scene upload, kernel, film read-back"}
 
 
 class ClockSampler:

@@ -367,7 +367,15 @@ template <typename Float, typename Spectrum> struct B200Describe {
 
 /* The integrator plugin.  Properties are those of `volpath` (src/integrators/volpath.cpp:19-25 over
    MonteCarloIntegrator / SamplingIntegrator, src/librender/integrator.cpp:23-39,302-315): max_depth, rr_depth,
-   hide_emitters, block_size, samples_per_pass, timeout; plus `device` (CUDA ordinal, default 0). */
+   hide_emitters, block_size, samples_per_pass, timeout; plus
+     device   CUDA ordinal (default 0)
+     seeding  "wavefront" (default): one PCG32 stream per sample, (state, stream) = (tea64(seed, i), tea64(i, seed)),
+              the seeding of the reference's own wavefront variants (sampler.cpp:89-92, integrator.cpp:147-153):
+              every sample is an independent unit of work, which is what fills a GPU.
+              "scalar": the scalar variants' seeding (one stream per pixel, seed = block_id * bs^2 + morton index,
+              all samples of a pixel drawn serially, integrator.cpp:89-130,198): the film then equals the one
+              scalar_mono / scalar_mono_double render on the CPU (to the parity tolerance); parallelism is limited to
+              the number of pixels, so it is for verification, not for speed. */
 template <typename Float, typename Spectrum>
 class B200VolumetricPathIntegrator final : public MonteCarloIntegrator<Float, Spectrum> {
 public:
@@ -379,6 +387,10 @@ public:
         if constexpr (!is_monochromatic_v<Spectrum> || is_array_v<Float>)
             Throw("volpath_b200 supports the scalar_mono and scalar_mono_double variants only");
         m_device = props.int_("device", 0);
+        std::string seeding = props.string("seeding", "wavefront");
+        if (seeding == "wavefront") m_seed_mode = B2VP_SEED_WAVEFRONT;
+        else if (seeding == "scalar") m_seed_mode = B2VP_SEED_SCALAR_BLOCKS;
+        else Throw("volpath_b200: seeding must be \"wavefront\" or \"scalar\"");
     }
     ~B200VolumetricPathIntegrator() { release(); }
 
@@ -405,7 +417,7 @@ public:
         args.abi_version = B2VP_ABI_VERSION; args.struct_size = (uint32_t) sizeof(args);
         args.device = m_device;
         args.precision = tables.desc.precision;
-        args.seed_mode = B2VP_SEED_SCALAR_BLOCKS;      /* the scalar variants' seeding (integrator.cpp:89-130,198) */
+        args.seed_mode = m_seed_mode;
         args.clear_film = 1;
         args.totals = &m_totals;
         int rc = b2vp_render(m_scene, &args, block->data().data());   /* host XYZAW buffer, crop_size x 5 */
@@ -451,6 +463,7 @@ private:
     b2vp_scene_t *m_scene = nullptr;
     B2vpCounters m_totals{};
     int m_device = 0;
+    int m_seed_mode = B2VP_SEED_WAVEFRONT;
 };
 
 MTS_IMPLEMENT_CLASS_VARIANT(B200VolumetricPathIntegrator, MonteCarloIntegrator)

@@ -237,6 +237,8 @@ class _Writer:
         for key in ("max_depth", "rr_depth", "block_size", "samples_per_pass"):
             if key in v:
                 out.append('<integer name="%s" value="%d"/>' % (key, v[key]))
+        if "seeding" in v:
+            out.append('<string name="seeding" value="%s"/>' % v["seeding"])
         if "hide_emitters" in v:
             out.append('<boolean name="hide_emitters" value="%s"/>' % ("true" if v["hide_emitters"] else "false"))
         if "nested" in v:  # moment integrator: one nested integrator
@@ -286,12 +288,14 @@ PLUGIN = os.path.join(REF_DIR, "plugins", "volpath_b200.so")
 ORACLE_LIB = os.path.join(HERE, "libb2vp_oracle.so")
 
 
-def with_plugin(scene):
-    """The same scene with <integrator type="volpath_b200">: the product's plugin inside the reference binary."""
+def with_plugin(scene, seeding="scalar"):
+    """The same scene with <integrator type="volpath_b200">: the product's plugin inside the reference binary.
+    seeding="scalar" asks for the scalar variants' stream order (films comparable sample by sample with the
+    reference's CPU volpath), "wavefront" for the plugin's default."""
     d = dict(scene)
     for k, v in scene.items():
         if isinstance(v, dict) and v.get("type") == "volpath":
-            d[k] = dict(v, type="volpath_b200")
+            d[k] = dict(v, type="volpath_b200", seeding=seeding)
     return d
 
 
