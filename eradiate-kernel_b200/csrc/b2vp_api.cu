@@ -148,6 +148,7 @@ struct b2vp_scene {
     std::vector<B2vpVolume> volumes;
     std::vector<std::vector<float>> volume_data;
     std::vector<B2vpPhase> phases;
+    std::vector<std::vector<double>> phase_values;   /* tabphase tables, copied from the descriptor */
     std::vector<B2vpEmitter> emitters;
     std::vector<float> vpos, vnrm, vuv;
     std::vector<uint32_t> faces;
@@ -174,6 +175,12 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
     s->media.assign(d->media, d->media + d->n_media);
     s->volumes.assign(d->volumes, d->volumes + d->n_volumes);
     s->phases.assign(d->phases, d->phases + d->n_phases);
+    s->phase_values.resize(d->n_phases);
+    for (uint32_t i = 0; i < d->n_phases; ++i)
+        if (d->phases[i].type == B2VP_PHASE_TABULATED && d->phases[i].values) {
+            s->phase_values[i].assign(d->phases[i].values, d->phases[i].values + d->phases[i].n_values);
+            s->phases[i].values = nullptr;
+        }
     s->emitters.assign(d->emitters, d->emitters + d->n_emitters);
     s->volume_data.resize(d->n_volumes);
     for (uint32_t i = 0; i < d->n_volumes; ++i) {
@@ -217,8 +224,11 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_BILAMBERTIAN)
             return fail(B2VP_ERR_UNSUPPORTED, "bsdf %u: type %d not supported by the B200 volpath", i, d->bsdfs[i].type);
     for (uint32_t i = 0; i < d->n_phases; ++i)
-        if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_HG)
+        if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_TABULATED)
             return fail(B2VP_ERR_UNSUPPORTED, "phase %u: type %d not supported by the B200 volpath", i, d->phases[i].type);
+    for (uint32_t i = 0; i < d->n_phases; ++i)
+        if (d->phases[i].type == B2VP_PHASE_TABULATED && s->phase_values[i].size() < 2)
+            return fail(B2VP_ERR_INVALID, "phase %u: ContinuousDistribution: needs at least two entries!", i);
     for (uint32_t i = 0; i < d->n_emitters; ++i)
         if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
             return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
@@ -334,9 +344,36 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         bsdfs[i].type = s->bsdfs[i].type; bsdfs[i].pad = 0;
         cvt(s->bsdfs[i].p, bsdfs[i].p, 4);
     }
+    /* phase functions; tabulated ones get their ContinuousDistribution (distr_1d.h:291-336: running integral in
+       double) appended to the phase table: records first, then pdf[n] + cdf[n - 1] per table */
     std::vector<DPhase<F>> phases(s->phases.size());
+    std::vector<F> phase_tabs;
+    bool have_tabphase = false;
     for (size_t i = 0; i < phases.size(); ++i) {
-        phases[i].type = s->phases[i].type; phases[i].pad = 0; phases[i].g = (F) s->phases[i].g;
+        std::memset(&phases[i], 0, sizeof(DPhase<F>));
+        phases[i].type = s->phases[i].type; phases[i].g = (F) s->phases[i].g;
+        if (s->phases[i].type != B2VP_PHASE_TABULATED) continue;
+        have_tabphase = true;
+        const std::vector<double> &vals = s->phase_values[i];
+        const uint32_t n = (uint32_t) vals.size();
+        DPhase<F> &o = phases[i];
+        o.n = (int) n;
+        o.tab_rel = (int) ((phases.size() - i) * sizeof(DPhase<F>) + phase_tabs.size() * sizeof(F));
+        o.valid_x = o.valid_y = 0xffffffffu;
+        const size_t base = phase_tabs.size();
+        phase_tabs.resize(base + 2 * (size_t) n - 1);
+        for (uint32_t k = 0; k < n; ++k) phase_tabs[base + k] = (F) vals[k];
+        double isz = 2.0 / (n - 1), integ = 0.;
+        for (uint32_t k = 0; k + 1 < n; ++k) {
+            double y0 = (double) phase_tabs[base + k], y1 = (double) phase_tabs[base + k + 1];
+            double value = 0.5 * isz * (y0 + y1);
+            integ += value;
+            phase_tabs[base + n + k] = (F) integ;
+            if (value > 0.) { if (o.valid_x == 0xffffffffu) o.valid_x = k; o.valid_y = k; }
+        }
+        if (o.valid_x == 0xffffffffu) return fail(B2VP_ERR_INVALID, "ContinuousDistribution: no probability mass found!");
+        o.integral = (F) integ; o.normalization = (F) (1. / integ);
+        o.interval_size = (F) isz; o.inv_interval_size = (F) (1. / isz);
     }
     std::vector<DEmitter<F>> emitters(s->emitters.size());
     for (size_t i = 0; i < emitters.size(); ++i) {
@@ -419,6 +456,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         ft |= a.type == B2VP_SHAPE_MESH ? FT_MESH : a.type == B2VP_SHAPE_SPHERE ? FT_SPHERE : FT_RECT;
         if (a.type == B2VP_SHAPE_MESH && (a.has_vertex_normals || a.has_vertex_texcoords)) ft |= FT_MESH_ATTR;
     }
+    if (have_tabphase) ft |= FT_TABPHASE;
     g.features = ft;
 
     /* blob layout */
@@ -429,7 +467,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     g.ofs_bsdfs = place(bsdfs.size() * sizeof(DBsdf<F>));
     g.ofs_media = place(media.size() * sizeof(DMedium<F>));
     g.ofs_volumes = place(volumes.size() * sizeof(DVolume<F>));
-    g.ofs_phases = place(phases.size() * sizeof(DPhase<F>));
+    g.ofs_phases = place(phases.size() * sizeof(DPhase<F>) + phase_tabs.size() * sizeof(F));
     g.ofs_emitters = place(emitters.size() * sizeof(DEmitter<F>));
     g.blob_bytes = align16(off ? off : 16);
     if (g.blob_bytes > 64 * 1024)
@@ -479,6 +517,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     put(g.ofs_media, media.data(), media.size() * sizeof(DMedium<F>));
     put(g.ofs_volumes, volumes.data(), volumes.size() * sizeof(DVolume<F>));
     put(g.ofs_phases, phases.data(), phases.size() * sizeof(DPhase<F>));
+    put(g.ofs_phases + (uint32_t) (phases.size() * sizeof(DPhase<F>)), phase_tabs.data(), phase_tabs.size() * sizeof(F));
     put(g.ofs_emitters, emitters.data(), emitters.size() * sizeof(DEmitter<F>));
     CU_CHECK(ds.blob.upload(ds.host_blob.data(), ds.host_blob.size()));
     g.blob = ds.blob.template as<unsigned char>();

@@ -490,7 +490,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         F ev;
                         DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
                         if (ds.pdf == 0) ev = 0;
-                        F nee_w = throughput * phase_eval(sv.phases[m.phase], -d, ds.d);
+                        F nee_w = throughput * phase_eval<F, FEAT>(sv.phases[m.phase], -d, ds.d);
                         if (ds.pdf != 0) {
                             copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(p, ds.d);
@@ -517,7 +517,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     const DPhase<F> &phase_fn = sv.phases[m.phase];
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                    V3<F> wo = phase_sample(phase_fn, d, s2x, s2y);
+                    V3<F> wo = phase_sample<F, FEAT>(phase_fn, d, s2x, s2y);
                     Ray<F> r = spawn_ray(p, wo);
                     r.mint = 0;
                     st_ray(s.cur, r);

@@ -55,7 +55,8 @@ enum : uint32_t {
     FT_SPHERE = 1u << 10,      /* a sphere is present                                     */
     FT_MESH = 1u << 11,        /* a triangle mesh is present                              */
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
-    FT_ALL = 0x1fffu
+    FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
+    FT_ALL = 0x3fffu
 };
 
 
@@ -669,9 +670,42 @@ template <typename F> VP_D V3<F> square_to_uniform_sphere(F sx, F sy) {
 
 /* ------------------------------------------------------------------- phase */
 /* PhaseFunction::eval (src/phase/rayleigh.cpp:42-45,68-74, hg.cpp:47-50,78-84, isotropic.cpp:41) */
-template <typename F> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo) {
+template <typename F> VP_D const F *phase_table(const DPhase<F> &ph) {
+    return reinterpret_cast<const F *>(reinterpret_cast<const unsigned char *>(&ph) + ph.tab_rel);
+}
+/* ContinuousDistribution::eval_pdf (distr_1d.h:365-380) on [-1, 1]; masked gathers read 0 outside the range */
+template <typename F> VP_D F tab_eval_pdf(const DPhase<F> &ph, F x) {
+    const F *pdf = phase_table(ph);
+    const bool active = x >= (F) -1 && x <= (F) 1;
+    x = (x - (F) -1) * ph.inv_interval_size;
+    long long xi = (long long) x;
+    uint32_t index = (uint32_t) min(max(xi, 0ll), (long long) ph.n - 2);
+    F y0 = active ? pdf[index] : (F) 0, y1 = active ? pdf[index + 1] : (F) 0;
+    F w1 = x - (F) index, w0 = (F) 1 - w1;
+    return fma_(w0, y0, w1 * y1);
+}
+/* ContinuousDistribution::sample (distr_1d.h:416-439) with enoki::binary_search (array_utils.h:150-171) */
+template <typename F> VP_D F tab_sample(const DPhase<F> &ph, F value) {
+    const F *pdf = phase_table(ph), *cdf = pdf + ph.n;
+    value *= ph.integral;
+    uint32_t start = ph.valid_x, end = ph.valid_y;
+    uint32_t iterations = start < end ? (32u - (uint32_t) __clz(end - start)) : 0u;   /* log2i(d) + 1 */
+    for (uint32_t i = 0; i < iterations; ++i) {
+        uint32_t middle = (start + end) >> 1;
+        if (cdf[middle] < value) start = min(middle + 1, end); else end = middle;
+    }
+    const uint32_t index = start;
+    F y0 = pdf[index], y1 = pdf[index + 1], c0 = index > 0 ? cdf[index - 1] : (F) 0;
+    value = (value - c0) * ph.inv_interval_size;
+    F t_linear = (y0 - safe_sqrt_(sqr(y0) + (F) 2 * value * (y1 - y0))) / (y0 - y1), t_const = value / y0;
+    F t = y0 == y1 ? t_const : t_linear;
+    return fma_((F) index + t, ph.interval_size, (F) -1);
+}
+template <typename F, uint32_t FEAT = FT_ALL> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo) {
     if (ph.type == 0) return K<F>::InvFourPi;
     F cos_theta = dot(wo, wi);
+    if ((FEAT & FT_TABPHASE) && ph.type == 3) /* tabphase.cpp:91-99 */
+        return tab_eval_pdf(ph, -cos_theta) * ph.normalization * K<F>::InvTwoPi;
     if (ph.type == 1)
         return ((F) 3 / (F) 16) * K<F>::InvPi * ((F) 1 + sqr(cos_theta));
     F g = ph.g;
@@ -680,11 +714,13 @@ template <typename F> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo)
 }
 /* PhaseFunction::sample (rayleigh.cpp:47-66, hg.cpp:52-76, isotropic.cpp:31-39);
    `d` is the incoming ray direction, the local frame is Frame3f(d) (medium.cpp:42) */
-template <typename F> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2x, F s2y) {
+template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2x, F s2y) {
     if (ph.type == 0)
         return square_to_uniform_sphere(s2x, s2y);
     F cos_theta;
-    if (ph.type == 1) {
+    if ((FEAT & FT_TABPHASE) && ph.type == 3) { /* tabphase.cpp:68-89 */
+        cos_theta = tab_sample(ph, s2x);
+    } else if (ph.type == 1) {
         F z = (F) 2 * ((F) 2 * s2x - (F) 1);
         F tmp = sqrt_(sqr(z) + (F) 1);
         F A = cbrt_(z + tmp), B = cbrt_(z - tmp);

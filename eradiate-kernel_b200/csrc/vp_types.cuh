@@ -46,6 +46,7 @@ template <> struct K<float> {
     static constexpr float Pi = 3.14159265358979323846f;
     static constexpr float InvPi = 0.31830988618379067154f;
     static constexpr float InvFourPi = 0.07957747154594766788f;
+    static constexpr float InvTwoPi = 0.15915494309189533577f;
     static constexpr float Epsilon = 1.1920928955078125e-7f / 2;     /* include/mitsuba/core/math.h:35 */
     static constexpr float RayEpsilon = Epsilon * 1500;              /* math.h:36 */
     static constexpr float ShadowEpsilon = RayEpsilon * 10;          /* math.h:37 */
@@ -54,6 +55,7 @@ template <> struct K<double> {
     static constexpr double Pi = 3.14159265358979323846;
     static constexpr double InvPi = 0.31830988618379067154;
     static constexpr double InvFourPi = 0.07957747154594766788;
+    static constexpr double InvTwoPi = 0.15915494309189533577;
     static constexpr double Epsilon = 2.220446049250313e-16 / 2;
     static constexpr double RayEpsilon = Epsilon * 1500;
     static constexpr double ShadowEpsilon = RayEpsilon * 10;
@@ -219,7 +221,16 @@ template <typename F> struct DShape {
     int has_normals, has_uv;
 };
 template <typename F> struct DBsdf { int type, pad; F p[4]; };
-template <typename F> struct DPhase { int type, pad; F g; };
+/* tabphase: the table (pdf[n] then cdf[n - 1], ContinuousDistribution of distr_1d.h:258-470) lies in the scene blob
+   `tab_rel` bytes after this record, so it is staged in shared memory with the other tables. */
+template <typename F> struct DPhase {
+    int type, n;
+    F g;
+    int tab_rel;
+    uint32_t valid_x, valid_y;
+    int pad;
+    F integral, normalization, interval_size, inv_interval_size;
+};
 template <typename F> struct DEmitter { F dir[3]; F irradiance; };
 template <typename F> struct DVolume {
     int type, filter, wrap, channels;

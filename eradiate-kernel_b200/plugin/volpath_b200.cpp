@@ -73,6 +73,7 @@
 #include <media/heterogeneous.cpp>
 #include <textures/grid3d.cpp>
 #include <phase/hg.cpp>
+#include <phase/tabphase.cpp>
 #include <emitters/directional.cpp>
 #include <sensors/distant.cpp>
 #define RayTargetType MultiDistantRayTargetType   /* distant.cpp and mdistant.cpp both define this enum */
@@ -101,6 +102,7 @@ struct B200SceneTables {
     std::vector<float> vpos, vnrm, vuv; std::vector<uint32_t> faces;
     std::vector<std::vector<float>> grids;
     std::vector<double> sensor_xf;
+    std::vector<std::vector<double>> phase_values;   /* tabphase tables, parallel to `phases` */
     std::map<const void *, int> bsdf_ids, medium_ids, shape_ids;
     void finish() {
         desc.abi_version = B2VP_ABI_VERSION; desc.struct_size = (uint32_t) sizeof(B2vpSceneDesc);
@@ -110,6 +112,10 @@ struct B200SceneTables {
         desc.n_volumes = (uint32_t) volumes.size(); desc.volumes = volumes.data();
         for (size_t i = 0, g = 0; i < volumes.size(); ++i)
             if (volumes[i].type == B2VP_VOLUME_GRID) volumes[i].data = grids[g++].data();
+        for (size_t i = 0; i < phases.size(); ++i)
+            if (phases[i].type == B2VP_PHASE_TABULATED) {
+                phases[i].n_values = (uint32_t) phase_values[i].size(); phases[i].values = phase_values[i].data();
+            }
         desc.n_phases = (uint32_t) phases.size(); desc.phases = phases.data();
         desc.n_emitters = (uint32_t) emitters.size(); desc.emitters = emitters.data();
         desc.n_vertices = (uint32_t) (vpos.size() / 3); desc.n_faces = (uint32_t) (faces.size() / 3);
@@ -145,14 +151,20 @@ template <typename Float, typename Spectrum> struct B200Describe {
 
     int phase(const PhaseFunction *p) {
         B2vpPhase o{};
+        std::vector<double> values;
         std::string n = cname(p);
         if (n == "IsotropicPhaseFunction") o.type = B2VP_PHASE_ISOTROPIC;
         else if (n == "RayleighPhaseFunction") o.type = B2VP_PHASE_RAYLEIGH;
         else if (n == "HGPhaseFunction") {
             o.type = B2VP_PHASE_HG;
             o.g = (double) static_cast<const HGPhaseFunction<Float, Spectrum> *>(p)->m_g;
+        } else if (n == "TabulatedPhaseFunction") {
+            o.type = B2VP_PHASE_TABULATED;   /* the values as the plugin holds them (tabphase.cpp:43-60) */
+            const auto &pdf = static_cast<const TabulatedPhaseFunction<Float, Spectrum> *>(p)->m_distr.m_pdf;
+            for (size_t i = 0; i < pdf.size(); ++i) values.push_back((double) pdf[i]);
         } else unsupported("phase function " + n);
         t.phases.push_back(o);
+        t.phase_values.push_back(std::move(values));
         return (int) t.phases.size() - 1;
     }
 

@@ -218,6 +218,22 @@ class _Builder:
             if not (-1 < g < 1):
                 raise RuntimeError("The asymmetry parameter must lie in the interval (-1, 1)!")
             p.g = float(g)
+        elif t == "tabphase":  # tabphase.cpp:43-66: `values` is a string (or here also a sequence) of samples
+            p.type = abi.PHASE_TABULATED
+            vals = node["values"]
+            if isinstance(vals, str):
+                vals = [float(x) for x in vals.replace(",", " ").split()]
+            vals = np.asarray(vals, dtype=np.float64).astype(self.dtype).astype(np.float64)  # (ScalarFloat) std::stod
+            if len(vals) < 2:
+                raise RuntimeError("ContinuousDistribution: needs at least two entries!")
+            if (vals < 0).any():
+                raise RuntimeError("ContinuousDistribution: entries must be non-negative!")
+            if not ((vals[:-1] + vals[1:]) > 0).any():
+                raise RuntimeError("ContinuousDistribution: no probability mass found!")
+            vals = np.ascontiguousarray(vals)
+            self.keep.append(vals)
+            p.n_values = len(vals)
+            p.values = vals.ctypes.data_as(C.POINTER(C.c_double))
         else:
             raise RuntimeError("phase function %r is not supported by the B200 volpath" % t)
         self.phases.append(p)

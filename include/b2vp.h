@@ -60,7 +60,7 @@ enum { B2VP_MEDIUM_HOMOGENEOUS = 0, B2VP_MEDIUM_HETEROGENEOUS = 1 };
 enum { B2VP_VOLUME_CONST = 0, B2VP_VOLUME_GRID = 1 };
 enum { B2VP_FILTER_NEAREST = 0, B2VP_FILTER_TRILINEAR = 1 };
 enum { B2VP_WRAP_REPEAT = 0, B2VP_WRAP_MIRROR = 1, B2VP_WRAP_CLAMP = 2 };
-enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2 };
+enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2, B2VP_PHASE_TABULATED = 3 };
 enum { B2VP_EMITTER_DIRECTIONAL = 0 };
 enum {
     B2VP_SENSOR_DISTANT        = 0, /* src/sensors/distant.cpp        */
@@ -138,6 +138,12 @@ typedef struct B2vpPhase {
     int32_t type;              /* B2VP_PHASE_*                                 */
     int32_t reserved0;
     double g;                  /* hg asymmetry (hg.cpp:41)                     */
+    /* tabphase (src/phase/tabphase.cpp:43-66): the phase function tabulated at n_values (>= 2) regularly spaced
+       cosines on [-1, 1], not normalised, in the precision the plugin holds them ((ScalarFloat) std::stod(..)).
+       Host pointer; copied by scene_create.                                   */
+    uint32_t n_values;
+    uint32_t reserved1;
+    const double *values;
 } B2vpPhase;
 
 typedef struct B2vpMedium {

@@ -143,6 +143,13 @@ struct Phase {
         if (!(g > -1 && g < 1)) throw Error(B2VP_ERR_INVALID, "The asymmetry parameter must lie in the interval (-1, 1)!");
         Phase p; p.type = B2VP_PHASE_HG; p.g = g; return p;
     }
+    /* src/phase/tabphase.cpp:43-66: the phase function at regularly spaced cosines on [-1, 1] */
+    std::vector<double> values;
+    static Phase tabulated(std::vector<double> v) {
+        if (v.size() < 2) throw Error(B2VP_ERR_INVALID, "ContinuousDistribution: needs at least two entries!");
+        for (double x : v) if (x < 0) throw Error(B2VP_ERR_INVALID, "ContinuousDistribution: entries must be non-negative!");
+        Phase p; p.type = B2VP_PHASE_TABULATED; p.values = std::move(v); return p;
+    }
 };
 /* src/textures/constant3d.cpp:13-55 */
 struct ConstVolume { double value = 1.0; };
@@ -192,6 +199,7 @@ struct Scene {
     std::vector<B2vpVolume> volumes; std::vector<B2vpPhase> phases; std::vector<B2vpEmitter> emitters;
     std::vector<float> vpos, vnrm, vuv; std::vector<uint32_t> faces;
     std::vector<std::vector<float>> grids;
+    std::vector<std::vector<double>> phase_values;   /* tabphase tables, parallel to `phases` */
     int width() const { return desc.sensor.crop_size[0]; }
     int height() const { return desc.sensor.crop_size[1]; }
 };
@@ -382,6 +390,10 @@ public:
         d.n_bsdfs = (uint32_t) s.bsdfs.size(); d.bsdfs = s.bsdfs.data();
         d.n_media = (uint32_t) s.media.size(); d.media = s.media.data();
         d.n_volumes = (uint32_t) s.volumes.size(); d.volumes = s.volumes.data();
+        for (size_t i = 0; i < s.phases.size(); ++i)
+            if (s.phases[i].type == B2VP_PHASE_TABULATED) {
+                s.phases[i].n_values = (uint32_t) s.phase_values[i].size(); s.phases[i].values = s.phase_values[i].data();
+            }
         d.n_phases = (uint32_t) s.phases.size(); d.phases = s.phases.data();
         d.n_emitters = (uint32_t) s.emitters.size(); d.emitters = s.emitters.data();
         d.n_vertices = (uint32_t) (s.vpos.size() / 3); d.n_faces = (uint32_t) (s.faces.size() / 3);
@@ -412,8 +424,11 @@ private:
     }
     int push_medium(B2vpMedium o, F scale, bool spectral, bool sample_emitters, const Phase &ph) {
         B2vpPhase p{};
-        p.type = ph.type; p.g = (double) (F) ph.g;
+        p.type = ph.type; p.g = (double) prop(ph.g);
+        std::vector<double> vals;
+        for (double x : ph.values) vals.push_back((double) (F) x);   /* (ScalarFloat) std::stod(..) */
         sc_->phases.push_back(p);
+        sc_->phase_values.push_back(std::move(vals));
         o.phase = (int) sc_->phases.size() - 1;
         o.scale = scale; o.has_spectral_extinction = spectral; o.sample_emitters = sample_emitters;
         sc_->media.push_back(o);

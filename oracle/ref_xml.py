@@ -116,6 +116,11 @@ class _Writer:
         out = '<phase type="%s">' % v["type"]
         if "g" in v:
             out += '<float name="g" value="%s"/>' % _num(v["g"])
+        if "values" in v:
+            vals = v["values"]
+            if not isinstance(vals, str):
+                vals = ", ".join(repr(float(x)) for x in vals)
+            out += '<string name="values" value="%s"/>' % vals
         return out + "</phase>"
 
     def medium(self, v, ident=None, name=None):

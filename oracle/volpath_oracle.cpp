@@ -195,6 +195,7 @@ template <typename F> struct Consts {
     static constexpr F Pi = (F) 3.14159265358979323846;
     static constexpr F InvPi = (F) 0.31830988618379067154;
     static constexpr F InvFourPi = (F) 0.07957747154594766788;
+    static constexpr F InvTwoPi = (F) 0.15915494309189533577;
     static constexpr F Epsilon = std::numeric_limits<F>::epsilon() / 2;  /* math.h:35 */
     static constexpr F RayEpsilon = Epsilon * 1500;                      /* math.h:36 */
     static constexpr F ShadowEpsilon = RayEpsilon * 10;                  /* math.h:37 */
@@ -315,7 +316,60 @@ template <typename F> struct OMedium {
     int type, sigma_t, albedo, phase; bool spectral, sample_emitters; F scale;
     F max_density; BBox<F> aabb; /* heterogeneous.cpp:29-30 */
 };
+/* ContinuousDistribution<Float> over [-1, 1] (include/mitsuba/core/distr_1d.h:258-470) as tabphase holds it */
+template <typename F> struct TabDistr {
+    std::vector<F> pdf, cdf;
+    F integral = 0, normalization = 0, interval_size = 0, inv_interval_size = 0;
+    uint32_t valid_x = 0, valid_y = 0;
+    /* update(), distr_1d.h:291-336: the running integral is accumulated in double */
+    void build(const double *values, uint32_t n) {
+        pdf.resize(n); cdf.resize(n - 1);
+        for (uint32_t i = 0; i < n; ++i) pdf[i] = (F) values[i];
+        valid_x = valid_y = (uint32_t) -1;
+        double range = 1.0 - (-1.0), isz = range / (n - 1), integ = 0.;
+        for (uint32_t i = 0; i + 1 < n; ++i) {
+            double y0 = (double) pdf[i], y1 = (double) pdf[i + 1];
+            double value = 0.5 * isz * (y0 + y1);
+            integ += value;
+            cdf[i] = (F) integ;
+            if (value > 0.) { if (valid_x == (uint32_t) -1) valid_x = i; valid_y = i; }
+        }
+        integral = (F) integ; normalization = (F) (1. / integ);
+        interval_size = (F) isz; inv_interval_size = (F) (1. / isz);
+    }
+    /* eval_pdf (distr_1d.h:365-380); outside [-1, 1] the gathers are masked: y0 = y1 = 0 */
+    F eval_pdf(F x) const {
+        bool active = x >= (F) -1 && x <= (F) 1;
+        x = (x - (F) -1) * inv_interval_size;
+        /* Index(x): float -> uint32 conversion, clamp to [0, n - 2] */
+        long long xi = (long long) x;
+        uint32_t index = (uint32_t) std::min<long long>(std::max<long long>(xi, 0), (long long) pdf.size() - 2);
+        F y0 = active ? pdf[index] : (F) 0, y1 = active ? pdf[index + 1] : (F) 0;
+        F w1 = x - (F) index, w0 = (F) 1 - w1;
+        return fma_(w0, y0, w1 * y1);
+    }
+    /* sample (distr_1d.h:416-439) with enoki::binary_search (array_utils.h:150-171) */
+    F sample(F value) const {
+        value *= integral;
+        uint32_t start = valid_x, end = valid_y;
+        uint32_t iterations = 0;
+        if (start < end) { uint32_t d = end - start; while (d) { iterations++; d >>= 1; } } /* log2i(d) + 1 */
+        for (uint32_t i = 0; i < iterations; ++i) {
+            uint32_t middle = (start + end) >> 1;
+            bool cond = cdf[middle] < value;
+            if (cond) start = std::min(middle + 1, end); else end = middle;
+        }
+        uint32_t index = start;
+        F y0 = pdf[index], y1 = pdf[index + 1], c0 = index > 0 ? cdf[index - 1] : (F) 0;
+        value = (value - c0) * inv_interval_size;
+        F t_linear = (y0 - safe_sqrt_(sqr(y0) + (F) 2 * value * (y1 - y0))) / (y0 - y1), t_const = value / y0;
+        F t = y0 == y1 ? t_const : t_linear;
+        return fma_((F) index + t, interval_size, (F) -1);
+    }
+};
+
 template <typename F> struct OScene {
+    std::vector<TabDistr<F>> tabs;   /* one per phase function (empty unless tabulated) */
     std::vector<OShape<F>> shapes;
     std::vector<B2vpBsdf> bsdfs;
     std::vector<OMedium<F>> media;
@@ -348,6 +402,12 @@ template <typename F> bool build_scene(const B2vpSceneDesc *d, OScene<F> &s) {
     }
     s.bsdfs.assign(d->bsdfs, d->bsdfs + d->n_bsdfs);
     s.phases.assign(d->phases, d->phases + d->n_phases);
+    s.tabs.resize(d->n_phases);
+    for (uint32_t i = 0; i < d->n_phases; ++i)
+        if (d->phases[i].type == B2VP_PHASE_TABULATED) {
+            if (d->phases[i].n_values < 2 || !d->phases[i].values) { g_error = "tabphase needs at least two values"; return false; }
+            s.tabs[i].build(d->phases[i].values, d->phases[i].n_values);
+        }
     s.emitters.assign(d->emitters, d->emitters + d->n_emitters);
     for (uint32_t i = 0; i < d->n_volumes; ++i) {
         const B2vpVolume &a = d->volumes[i];
@@ -749,7 +809,9 @@ template <typename F> inline V3<F> square_to_uniform_sphere(F sx, F sy) {
 }
 
 /* PhaseFunction::eval (rayleigh.cpp:42-45, hg.cpp:47-50, isotropic.cpp) */
-template <typename F> inline F phase_eval_cos(const B2vpPhase &ph, F cos_theta) {
+template <typename F> inline F phase_eval_cos(const B2vpPhase &ph, const TabDistr<F> &tab, F cos_theta) {
+    if (ph.type == B2VP_PHASE_TABULATED) /* tabphase.cpp:91-99: eval_pdf_normalized(-cos_theta) / (2 pi) */
+        return tab.eval_pdf(-cos_theta) * tab.normalization * Consts<F>::InvTwoPi;
     if (ph.type == B2VP_PHASE_RAYLEIGH)
         return ((F) 3 / (F) 16) * Consts<F>::InvPi * ((F) 1 + sqr(cos_theta));
     if (ph.type == B2VP_PHASE_HG) {
@@ -759,16 +821,20 @@ template <typename F> inline F phase_eval_cos(const B2vpPhase &ph, F cos_theta) 
     }
     return Consts<F>::InvFourPi;
 }
-template <typename F> inline F phase_eval(const B2vpPhase &ph, const MediumInteraction<F> &mi, V3<F> wo) {
+template <typename F>
+inline F phase_eval(const B2vpPhase &ph, const TabDistr<F> &tab, const MediumInteraction<F> &mi, V3<F> wo) {
     if (ph.type == B2VP_PHASE_ISOTROPIC) return Consts<F>::InvFourPi;
-    return phase_eval_cos(ph, dot(wo, mi.wi));
+    return phase_eval_cos(ph, tab, dot(wo, mi.wi));
 }
 /* PhaseFunction::sample (rayleigh.cpp:47-66, hg.cpp:52-76, isotropic.cpp:31-39) */
-template <typename F> inline V3<F> phase_sample(const B2vpPhase &ph, const MediumInteraction<F> &mi, F s2x, F s2y) {
+template <typename F>
+inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const MediumInteraction<F> &mi, F s2x, F s2y) {
     if (ph.type == B2VP_PHASE_ISOTROPIC)
         return square_to_uniform_sphere(s2x, s2y);
     F cos_theta;
-    if (ph.type == B2VP_PHASE_RAYLEIGH) {
+    if (ph.type == B2VP_PHASE_TABULATED) { /* tabphase.cpp:68-89 */
+        cos_theta = tab.sample(s2x);
+    } else if (ph.type == B2VP_PHASE_RAYLEIGH) {
         F z = (F) 2 * ((F) 2 * s2x - (F) 1);
         F tmp = sqrt_(sqr(z) + (F) 1);
         F A = cbrt_(z + tmp), B = cbrt_(z - tmp);
@@ -1245,7 +1311,7 @@ template <typename F> struct Integrator {
                 if (active_e) {
                     DirectionSample<F> ds;
                     F emitted = sample_emitter(mi.p, true, medium, active_e, ds);
-                    F phase_val = phase_eval(phase, mi, ds.d);
+                    F phase_val = phase_eval(phase, scene.tabs[m.phase], mi, ds.d);
                     result += throughput * phase_val * emitted;
                 }
                 /* phase->sample(ctx, mi, next_1d(), next_2d(), ..) (volpath.cpp:171): the
@@ -1255,7 +1321,7 @@ template <typename F> struct Integrator {
                 F da = next_1d(act_medium_scatter), db = next_1d(act_medium_scatter),
                   dc = next_1d(act_medium_scatter);
                 F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> wo = phase_sample(phase, mi, s2x, s2y);
+                V3<F> wo = phase_sample(phase, scene.tabs[m.phase], mi, s2x, s2y);
                 Ray<F> new_ray = spawn_ray(mi.p, wo);
                 new_ray.mint = 0;
                 ray = new_ray;

@@ -150,6 +150,17 @@ def _c2_cpp_host(variant):
     }
 
 
+def _tabphase(values, **kw):
+    """C2 with a tabulated phase function (src/phase/tabphase.cpp; SURVEY 8(f) N3: aerosol layers)."""
+    d = scenes.c2(**kw)
+    d["atm"]["phase"] = {"type": "tabphase", "values": values}
+    return d
+
+
+_MU = np.linspace(-1, 1, 181)
+TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
+TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
+
 _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  # SURVEY 8(f) N3: two-sided leaves
 
 # per-path tolerance overrides (default: tests/test_reference_parity.py TOL): (tolerance, minimum fraction)
@@ -198,6 +209,9 @@ CASES = {
     "c2_obj_normals_f64": (lambda v: _c2_obj(False, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c2_cpp_host": (_c2_cpp_host, "scalar_mono"),
     "c2_cpp_host_f64": (_c2_cpp_host, "scalar_mono_double"),
+    "c2_tabphase": (lambda v: _tabphase(TAB_AEROSOL, spp=1, variant=v, width=256), "scalar_mono"),
+    "c2_tabphase_coarse": (lambda v: _tabphase(TAB_COARSE, spp=1, variant=v, width=256), "scalar_mono"),
+    "c2_tabphase_f64": (lambda v: _tabphase(TAB_AEROSOL, spp=1, variant=v, width=128), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

@@ -18,9 +18,17 @@ CASES = {
     "c2_mdistant": lambda v: scenes.c2(spp=8, variant=v, sensor="mdistant", width=64),
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
+    "c2_tabphase": lambda v: _tabphase(v),
     "c5_bilambertian": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64,
                                            leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}),
 }
+
+
+def _tabphase(variant):
+    import make_ref_golden
+    d = scenes.c2(spp=8, variant=variant, width=64)
+    d["atm"]["phase"] = {"type": "tabphase", "values": make_ref_golden.TAB_AEROSOL}
+    return d
 
 
 def compare(pkg, oracle, sc, mode, **kw):
