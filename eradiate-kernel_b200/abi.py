@@ -15,7 +15,7 @@ OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NO_DEVICE, ERR_CANCELLED = range
 PREC_F32, PREC_F64 = 0, 1
 SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2
 BSDF_DIFFUSE, BSDF_NULL, BSDF_RPV, BSDF_BILAMBERTIAN = 0, 1, 2, 3
-PHASE_TABULATED = 3
+PHASE_TABULATED, PHASE_BLEND = 3, 4
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
 VOLUME_CONST, VOLUME_GRID = 0, 1
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
@@ -62,7 +62,8 @@ class Volume(C.Structure):
 
 class Phase(C.Structure):
     _fields_ = [("type", c_i32), ("reserved0", c_i32), ("g", c_d),
-                ("n_values", c_u32), ("reserved1", c_u32), ("values", C.POINTER(c_d))]
+                ("n_values", c_u32), ("reserved1", c_u32), ("values", C.POINTER(c_d)),
+                ("child", c_i32 * 2), ("weight_volume", c_i32), ("reserved2", c_i32)]
 
 
 class Medium(C.Structure):

@@ -224,11 +224,20 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (d->bsdfs[i].type < 0 || d->bsdfs[i].type > B2VP_BSDF_BILAMBERTIAN)
             return fail(B2VP_ERR_UNSUPPORTED, "bsdf %u: type %d not supported by the B200 volpath", i, d->bsdfs[i].type);
     for (uint32_t i = 0; i < d->n_phases; ++i)
-        if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_TABULATED)
+        if (d->phases[i].type < 0 || d->phases[i].type > B2VP_PHASE_BLEND)
             return fail(B2VP_ERR_UNSUPPORTED, "phase %u: type %d not supported by the B200 volpath", i, d->phases[i].type);
     for (uint32_t i = 0; i < d->n_phases; ++i)
         if (d->phases[i].type == B2VP_PHASE_TABULATED && s->phase_values[i].size() < 2)
             return fail(B2VP_ERR_INVALID, "phase %u: ContinuousDistribution: needs at least two entries!", i);
+    for (uint32_t i = 0; i < d->n_phases; ++i) {
+        const B2vpPhase &p = d->phases[i];
+        if (p.type != B2VP_PHASE_BLEND) continue;
+        for (int k = 0; k < 2; ++k)
+            if (p.child[k] < 0 || p.child[k] >= (int) d->n_phases || d->phases[p.child[k]].type == B2VP_PHASE_BLEND)
+                return fail(B2VP_ERR_INVALID, "phase %u: BlendPhase: Two child phase functions must be specified!", i);
+        if (p.weight_volume < 0 || p.weight_volume >= (int) d->n_volumes)
+            return fail(B2VP_ERR_INVALID, "phase %u: blendphase weight volume out of range", i);
+    }
     for (uint32_t i = 0; i < d->n_emitters; ++i)
         if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
             return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
@@ -348,10 +357,15 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
        double) appended to the phase table: records first, then pdf[n] + cdf[n - 1] per table */
     std::vector<DPhase<F>> phases(s->phases.size());
     std::vector<F> phase_tabs;
-    bool have_tabphase = false;
+    bool have_tabphase = false, have_blendphase = false;
     for (size_t i = 0; i < phases.size(); ++i) {
         std::memset(&phases[i], 0, sizeof(DPhase<F>));
         phases[i].type = s->phases[i].type; phases[i].g = (F) s->phases[i].g;
+        if (s->phases[i].type == B2VP_PHASE_BLEND) {
+            have_blendphase = true;
+            phases[i].child[0] = s->phases[i].child[0]; phases[i].child[1] = s->phases[i].child[1];
+            phases[i].weight_volume = s->phases[i].weight_volume;
+        }
         if (s->phases[i].type != B2VP_PHASE_TABULATED) continue;
         have_tabphase = true;
         const std::vector<double> &vals = s->phase_values[i];
@@ -457,6 +471,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         if (a.type == B2VP_SHAPE_MESH && (a.has_vertex_normals || a.has_vertex_texcoords)) ft |= FT_MESH_ATTR;
     }
     if (have_tabphase) ft |= FT_TABPHASE;
+    if (have_blendphase) ft |= FT_BLENDPHASE;
     g.features = ft;
 
     /* blob layout */

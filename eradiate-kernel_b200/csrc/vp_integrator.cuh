@@ -264,13 +264,13 @@ template <typename F> struct PathCtx {
                 if (sample_emitters) {
                     DirSample<F> ds;
                     F emitted = sample_emitter(mi.p, true, medium, true, ds);
-                    F phase_val = phase_eval(phase, -ray.d, ds.d);
+                    F phase_val = phase_eval_at(sv, phase, mi.p, -ray.d, ds.d);
                     result += throughput * phase_val * emitted;
                 }
                 /* phase->sample(ctx, mi, next_1d(), next_2d()) (volpath.cpp:171) */
                 F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> wo = phase_sample(phase, ray.d, s2x, s2y);
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                V3<F> wo = phase_sample_at(sv, phase, mi.p, ray.d, s1, s2x, s2y);
                 ray = spawn_ray(mi.p, wo);
                 ray.mint = 0;
                 needs_intersection = true;

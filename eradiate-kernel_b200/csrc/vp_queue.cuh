@@ -490,7 +490,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         F ev;
                         DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
                         if (ds.pdf == 0) ev = 0;
-                        F nee_w = throughput * phase_eval<F, FEAT>(sv.phases[m.phase], -d, ds.d);
+                        F nee_w = throughput * phase_eval_at<F, FEAT>(sv, sv.phases[m.phase], p, -d, ds.d);
                         if (ds.pdf != 0) {
                             copy_ctx(c.saved, s.cur);
                             Ray<F> r2 = spawn_ray(p, ds.d);
@@ -516,8 +516,8 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 if (state == Q_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
                     const DPhase<F> &phase_fn = sv.phases[m.phase];
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
-                    F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                    V3<F> wo = phase_sample<F, FEAT>(phase_fn, d, s2x, s2y);
+                    F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> wo = phase_sample_at<F, FEAT>(sv, phase_fn, p, d, s1, s2x, s2y);
                     Ray<F> r = spawn_ray(p, wo);
                     r.mint = 0;
                     st_ray(s.cur, r);

@@ -56,7 +56,8 @@ enum : uint32_t {
     FT_MESH = 1u << 11,        /* a triangle mesh is present                              */
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
-    FT_ALL = 0x3fffu
+    FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
+    FT_ALL = 0x7fffu
 };
 
 
@@ -739,6 +740,23 @@ template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPha
     sincos_((F) 2 * K<F>::Pi * s2y, s, c);
     V3<F> wo = mk3<F>(sin_theta * c, sin_theta * s, cos_theta);
     return make_frame(d).to_world(wo);
+}
+
+/* BlendPhaseFunction (src/phase/blendphase.cpp:68-140, default context): (1 - w) * child[0] + w * child[1] with
+   w = clamp(weight volume at the scattering position, 0, 1); sampling picks child[0] when sample1 > w.
+   Other phase functions pass straight through. */
+template <typename F, uint32_t FEAT = FT_ALL>
+VP_D F phase_eval_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> wi, V3<F> wo) {
+    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_eval<F, FEAT>(ph, wi, wo);
+    F w = min_(max_(volume_eval<F, FT_ALL, true>(sv, sv.volumes[ph.weight_volume], p), (F) 0), (F) 1);
+    return phase_eval<F, FEAT>(sv.phases[ph.child[0]], wi, wo) * ((F) 1 - w) +
+           phase_eval<F, FEAT>(sv.phases[ph.child[1]], wi, wo) * w;
+}
+template <typename F, uint32_t FEAT = FT_ALL>
+VP_D V3<F> phase_sample_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> d, F s1, F s2x, F s2y) {
+    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_sample<F, FEAT>(ph, d, s2x, s2y);
+    F w = min_(max_(volume_eval<F, FT_ALL, true>(sv, sv.volumes[ph.weight_volume], p), (F) 0), (F) 1);
+    return phase_sample<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], d, s2x, s2y);
 }
 
 /* ------------------------------------------------------------------- BSDFs */

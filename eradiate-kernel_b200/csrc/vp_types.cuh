@@ -228,7 +228,8 @@ template <typename F> struct DPhase {
     F g;
     int tab_rel;
     uint32_t valid_x, valid_y;
-    int pad;
+    int weight_volume;               /* blendphase: index into volumes */
+    int child[2];                    /* blendphase: indices of the nested phase functions */
     F integral, normalization, interval_size, inv_interval_size;
 };
 template <typename F> struct DEmitter { F dir[3]; F irradiance; };

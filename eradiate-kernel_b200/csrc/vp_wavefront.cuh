@@ -331,7 +331,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 if (m.sample_emitters) {
                     DirSample<F> ds;
                     bool march = begin_nee(mi.p, true, ds);
-                    nee_w = throughput * phase_eval(sv.phases[m.phase], -ray.d, ds.d);
+                    nee_w = throughput * phase_eval_at(sv, sv.phases[m.phase], mi.p, -ray.d, ds.d);
                     cont = C_SCATTER_B;
                     if (march) { mode = M_NEE; state = L_STEP_A; }
                     else result += nee_w * emitter_val;
@@ -339,8 +339,8 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
             } else if (state == L_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
                 const DPhase<F> &phase_fn = sv.phases[sv.media[medium].phase];
                 F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> wo = phase_sample(phase_fn, ray.d, s2x, s2y);
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                V3<F> wo = phase_sample_at(sv, phase_fn, ray.o, ray.d, s1, s2x, s2y);
                 ray = spawn_ray(ray.o, wo);
                 ray.mint = 0;
                 needs_isect = true;

@@ -74,6 +74,7 @@
 #include <textures/grid3d.cpp>
 #include <phase/hg.cpp>
 #include <phase/tabphase.cpp>
+#include <phase/blendphase.cpp>
 #include <emitters/directional.cpp>
 #include <sensors/distant.cpp>
 #define RayTargetType MultiDistantRayTargetType   /* distant.cpp and mdistant.cpp both define this enum */
@@ -158,6 +159,14 @@ template <typename Float, typename Spectrum> struct B200Describe {
         else if (n == "HGPhaseFunction") {
             o.type = B2VP_PHASE_HG;
             o.g = (double) static_cast<const HGPhaseFunction<Float, Spectrum> *>(p)->m_g;
+        } else if (n == "BlendPhaseFunction") {
+            auto *b = static_cast<const BlendPhaseFunction<Float, Spectrum> *>(p);
+            o.type = B2VP_PHASE_BLEND;
+            for (int k = 0; k < 2; ++k) {
+                if (cname(b->m_nested_phase[k].get()) == "BlendPhaseFunction") unsupported("nested blendphase");
+                o.child[k] = phase(b->m_nested_phase[k].get());
+            }
+            o.weight_volume = volume(b->m_weight.get());
         } else if (n == "TabulatedPhaseFunction") {
             o.type = B2VP_PHASE_TABULATED;   /* the values as the plugin holds them (tabphase.cpp:43-60) */
             const auto &pdf = static_cast<const TabulatedPhaseFunction<Float, Spectrum> *>(p)->m_distr.m_pdf;

@@ -218,6 +218,17 @@ class _Builder:
             if not (-1 < g < 1):
                 raise RuntimeError("The asymmetry parameter must lie in the interval (-1, 1)!")
             p.g = float(g)
+        elif t == "blendphase":  # blendphase.cpp:42-66: two nested phase functions in key order + a weight volume
+            kids = [v for k, v in sorted(node.items()) if isinstance(v, dict) and k != "weight"
+                    and v.get("type") in ("isotropic", "rayleigh", "hg", "tabphase")]
+            if len(kids) != 2:
+                raise RuntimeError("BlendPhase: Two child phase functions must be specified!")
+            if "weight" not in node:
+                raise RuntimeError('Property "weight" has not been specified!')
+            c0, c1 = self.phase(kids[0]), self.phase(kids[1])
+            p.type = abi.PHASE_BLEND
+            p.child[0], p.child[1] = c0, c1
+            p.weight_volume = self.volume(node["weight"], None)
         elif t == "tabphase":  # tabphase.cpp:43-66: `values` is a string (or here also a sequence) of samples
             p.type = abi.PHASE_TABULATED
             vals = node["values"]

@@ -60,7 +60,7 @@ enum { B2VP_MEDIUM_HOMOGENEOUS = 0, B2VP_MEDIUM_HETEROGENEOUS = 1 };
 enum { B2VP_VOLUME_CONST = 0, B2VP_VOLUME_GRID = 1 };
 enum { B2VP_FILTER_NEAREST = 0, B2VP_FILTER_TRILINEAR = 1 };
 enum { B2VP_WRAP_REPEAT = 0, B2VP_WRAP_MIRROR = 1, B2VP_WRAP_CLAMP = 2 };
-enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2, B2VP_PHASE_TABULATED = 3 };
+enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2, B2VP_PHASE_TABULATED = 3, B2VP_PHASE_BLEND = 4 };
 enum { B2VP_EMITTER_DIRECTIONAL = 0 };
 enum {
     B2VP_SENSOR_DISTANT        = 0, /* src/sensors/distant.cpp        */
@@ -144,6 +144,12 @@ typedef struct B2vpPhase {
     uint32_t n_values;
     uint32_t reserved1;
     const double *values;
+    /* blendphase (src/phase/blendphase.cpp:42-140): two nested phase functions (indices into phases, not blends
+       themselves) mixed by a weight volume evaluated at the scattering position, clamped to [0, 1]:
+       (1 - w) * child[0] + w * child[1]; sampling picks child[0] when sample1 > w */
+    int32_t child[2];
+    int32_t weight_volume;     /* index into volumes                           */
+    int32_t reserved2;
 } B2vpPhase;
 
 typedef struct B2vpMedium {

@@ -112,8 +112,8 @@ class _Writer:
         out.append("</volume>")
         return "".join(out)
 
-    def phase(self, v):
-        out = '<phase type="%s">' % v["type"]
+    def phase(self, v, name=None):
+        out = '<phase type="%s"%s>' % (v["type"], ' name="%s"' % name if name else "")
         if "g" in v:
             out += '<float name="g" value="%s"/>' % _num(v["g"])
         if "values" in v:
@@ -121,6 +121,11 @@ class _Writer:
             if not isinstance(vals, str):
                 vals = ", ".join(repr(float(x)) for x in vals)
             out += '<string name="values" value="%s"/>' % vals
+        if v["type"] == "blendphase":   # nested phase functions are named so that they sort like the dictionary keys
+            for k, child in sorted(v.items()):
+                if isinstance(child, dict) and k != "weight":
+                    out += self.phase(child, name=k)
+            out += self.volume("weight", v["weight"])
         return out + "</phase>"
 
     def medium(self, v, ident=None, name=None):

@@ -854,6 +854,28 @@ inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const Med
     return mi.sh_frame.to_world(wo);
 }
 
+/* BlendPhaseFunction (src/phase/blendphase.cpp:68-140, default context): the weight volume is evaluated at the
+   scattering position and clamped to [0, 1] */
+template <typename F> inline F blend_weight(const OScene<F> &s, const B2vpPhase &ph, const MediumInteraction<F> &mi) {
+    return min_(max_(volume_eval(s.volumes[ph.weight_volume], mi.p), (F) 0), (F) 1);
+}
+template <typename F> inline F phase_eval_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, V3<F> wo) {
+    const B2vpPhase &ph = s.phases[idx];
+    if (ph.type != B2VP_PHASE_BLEND) return phase_eval(ph, s.tabs[idx], mi, wo);
+    F weight = blend_weight(s, ph, mi);
+    return phase_eval(s.phases[ph.child[0]], s.tabs[ph.child[0]], mi, wo) * ((F) 1 - weight) +
+           phase_eval(s.phases[ph.child[1]], s.tabs[ph.child[1]], mi, wo) * weight;
+}
+template <typename F>
+inline V3<F> phase_sample_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, F s1, F s2x, F s2y) {
+    const B2vpPhase &ph = s.phases[idx];
+    if (ph.type != B2VP_PHASE_BLEND) return phase_sample(ph, s.tabs[idx], mi, s2x, s2y);
+    F weight = blend_weight(s, ph, mi);
+    /* the rescaled sample1 is passed on, none of the nested phase functions in scope uses it */
+    int c = s1 > weight ? ph.child[0] : ph.child[1];
+    return phase_sample(s.phases[c], s.tabs[c], mi, s2x, s2y);
+}
+
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
     F_Null = 0x1, F_DiffuseReflection = 0x2, F_DiffuseTransmission = 0x4, F_GlossyReflection = 0x8,
     F_Smooth = 0x2 | 0x4 | 0x8 | 0x10, F_Delta = 0x1 | 0x20 | 0x40
@@ -1301,7 +1323,6 @@ template <typename F> struct Integrator {
                 if (not_spectral) throughput *= mi.sigma_s / mi.sigma_t;
 
                 const OMedium<F> &m = scene.media[mi.medium];
-                const B2vpPhase &phase = scene.phases[m.phase];
                 bool sample_emitters = m.sample_emitters;
                 valid_ray = true;
                 specular_chain = specular_chain && !act_medium_scatter;
@@ -1311,7 +1332,7 @@ template <typename F> struct Integrator {
                 if (active_e) {
                     DirectionSample<F> ds;
                     F emitted = sample_emitter(mi.p, true, medium, active_e, ds);
-                    F phase_val = phase_eval(phase, scene.tabs[m.phase], mi, ds.d);
+                    F phase_val = phase_eval_at(scene, m.phase, mi, ds.d);
                     result += throughput * phase_val * emitted;
                 }
                 /* phase->sample(ctx, mi, next_1d(), next_2d(), ..) (volpath.cpp:171): the
@@ -1320,8 +1341,8 @@ template <typename F> struct Integrator {
                    right.  `ltr` selects the clang order; default is GCC's. */
                 F da = next_1d(act_medium_scatter), db = next_1d(act_medium_scatter),
                   dc = next_1d(act_medium_scatter);
-                F s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                V3<F> wo = phase_sample(phase, scene.tabs[m.phase], mi, s2x, s2y);
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                V3<F> wo = phase_sample_at(scene, m.phase, mi, s1, s2x, s2y);
                 Ray<F> new_ray = spawn_ray(mi.p, wo);
                 new_ray.mint = 0;
                 ray = new_ray;

@@ -157,6 +157,23 @@ def _tabphase(values, **kw):
     return d
 
 
+def _blendphase(grid_weight, **kw):
+    """C2 with molecules (rayleigh) and aerosols (tabphase) mixed by `blendphase` (src/phase/blendphase.cpp): the
+    aerosol fraction is a 1D profile (gridvolume) that leaves [0, 1] at both ends (clamped), or a constant."""
+    d = scenes.c2(**kw)
+    T = scenes.T
+    if grid_weight:
+        w = np.clip(np.exp(-np.linspace(0, 1, 50) * 6) * 1.3 - 0.05, -1, 2).astype(np.float32).reshape(50, 1, 1)
+        weight = {"type": "gridvolume", "data": w,
+                  "to_world": T.translate([-10, -10, 0], np.float32) @ T.scale([20, 20, 1], np.float32)}
+        d["atm"]["phase"] = {"type": "blendphase", "a_mol": {"type": "rayleigh"},
+                             "b_aer": {"type": "tabphase", "values": TAB_AEROSOL}, "weight": weight}
+    else:
+        d["atm"]["phase"] = {"type": "blendphase", "p0": {"type": "hg", "g": 0.5}, "p1": {"type": "isotropic"},
+                             "weight": 0.25}
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -212,6 +229,9 @@ CASES = {
     "c2_tabphase": (lambda v: _tabphase(TAB_AEROSOL, spp=1, variant=v, width=256), "scalar_mono"),
     "c2_tabphase_coarse": (lambda v: _tabphase(TAB_COARSE, spp=1, variant=v, width=256), "scalar_mono"),
     "c2_tabphase_f64": (lambda v: _tabphase(TAB_AEROSOL, spp=1, variant=v, width=128), "scalar_mono_double"),
+    "c2_blendphase": (lambda v: _blendphase(True, spp=1, variant=v, width=256), "scalar_mono"),
+    "c2_blendphase_const": (lambda v: _blendphase(False, spp=1, variant=v, width=256), "scalar_mono"),
+    "c2_blendphase_f64": (lambda v: _blendphase(True, spp=1, variant=v, width=128), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

@@ -19,6 +19,8 @@ CASES = {
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
     "c2_tabphase": lambda v: _tabphase(v),
+    "c2_blendphase": lambda v: _blendphase(v, True),
+    "c2_blendphase_const": lambda v: _blendphase(v, False),
     "c5_bilambertian": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64,
                                            leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}),
 }
@@ -29,6 +31,11 @@ def _tabphase(variant):
     d = scenes.c2(spp=8, variant=variant, width=64)
     d["atm"]["phase"] = {"type": "tabphase", "values": make_ref_golden.TAB_AEROSOL}
     return d
+
+
+def _blendphase(variant, grid):
+    import make_ref_golden
+    return make_ref_golden._blendphase(grid, spp=8, variant=variant, width=64)
 
 
 def compare(pkg, oracle, sc, mode, **kw):
