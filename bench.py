@@ -201,6 +201,8 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the B200 volpath has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"   # the version banner goes to stdout, where ONE JSON line is expected
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n_gpus = world
 
