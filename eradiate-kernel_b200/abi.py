@@ -22,7 +22,7 @@ FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_RAYLEIGH, PHASE_HG = 0, 1, 2
 EMITTER_DIRECTIONAL = 0
-SENSOR_DISTANT, SENSOR_MDISTANT, SENSOR_RADIANCEMETER, SENSOR_MRADIANCEMETER = 0, 1, 2, 3
+SENSOR_DISTANT, SENSOR_MDISTANT, SENSOR_RADIANCEMETER, SENSOR_MRADIANCEMETER, SENSOR_DISTANTFLUX = 0, 1, 2, 3, 4
 DIR_SINGLE, DIR_SAMPLE_WIDTH, DIR_SAMPLE_ALL = 0, 1, 2
 TARGET_NONE, TARGET_POINT, TARGET_SHAPE = 0, 1, 2
 ORIGIN_BSPHERE, ORIGIN_SHAPE = 0, 1
@@ -82,7 +82,7 @@ class Sensor(C.Structure):
         ("type", c_i32), ("direction_type", c_i32), ("target_type", c_i32), ("origin_type", c_i32),
         ("target_shape", c_i32), ("origin_shape", c_i32), ("flip_directions", c_i32),
         ("needs_aperture_sample", c_i32), ("medium", c_i32), ("n_transforms", c_i32),
-        ("to_world", Mat4), ("target_point", c_d * 3),
+        ("to_world", Mat4), ("target_point", c_d * 3), ("reference_normal", c_d * 3),
         ("shutter_open", c_d), ("shutter_open_time", c_d),
         ("transforms", C.POINTER(c_d)),
         ("film_size", c_i32 * 2), ("crop_offset", c_i32 * 2), ("crop_size", c_i32 * 2),

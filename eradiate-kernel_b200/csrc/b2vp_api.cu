@@ -242,11 +242,12 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
             return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
     const B2vpSensor &sn = d->sensor;
-    if (sn.type < 0 || sn.type > B2VP_SENSOR_MRADIANCEMETER)
+    if (sn.type < 0 || sn.type > B2VP_SENSOR_DISTANTFLUX)
         return fail(B2VP_ERR_UNSUPPORTED, "sensor type %d not supported by the B200 volpath", sn.type);
-    if (sn.type == B2VP_SENSOR_DISTANT && sn.origin_type == B2VP_ORIGIN_SHAPE)
+    if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_DISTANTFLUX) && sn.origin_type == B2VP_ORIGIN_SHAPE)
         return fail(B2VP_ERR_UNSUPPORTED, "distant sensor with a ray_origin shape is not supported");
-    if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_MDISTANT) && sn.target_type == B2VP_TARGET_SHAPE &&
+    if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_MDISTANT || sn.type == B2VP_SENSOR_DISTANTFLUX) &&
+        sn.target_type == B2VP_TARGET_SHAPE &&
         (sn.target_shape < 0 || sn.target_shape >= (int) d->n_shapes ||
          d->shapes[sn.target_shape].type != B2VP_SHAPE_RECTANGLE))
         return fail(B2VP_ERR_UNSUPPORTED, "sensor ray_target shape must be a rectangle");
@@ -583,6 +584,8 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     o.needs_aperture_sample = sn.needs_aperture_sample; o.medium = sn.medium; o.n_transforms = sn.n_transforms;
     o.has_shutter = sn.shutter_open_time > 0 ? 1 : 0;
     cvt(sn.to_world.m, o.to_world, 16); cvt(sn.target_point, o.target_point, 3);
+    cvt(sn.reference_normal, o.reference_normal, 3);
+    o.n_pixels = sn.film_size[0] * sn.film_size[1]; o.pad_sensor = 0;
     for (int k = 0; k < 2; ++k) { o.crop_offset[k] = sn.crop_offset[k]; o.crop_size[k] = sn.crop_size[k]; }
 
     g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;

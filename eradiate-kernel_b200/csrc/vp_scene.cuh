@@ -960,6 +960,22 @@ template <typename F> VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F f
             ray.o = bs_c + perp * bs_r - ray.d * bs_r;
             weight = 1;
         }
+    } else if (sn.type == 4) { /* distantflux.cpp:184-251 */
+        ray.d = -xf_vector(sn.to_world, square_to_uniform_hemisphere(fx, fy));
+        /* square_to_uniform_hemisphere_pdf is the constant 1 / (2 pi) (warp.h:305-312) */
+        weight = dot(-ray.d, ld3(sn.reference_normal)) / (K<F>::InvTwoPi * (F) sn.n_pixels);
+        V3<F> ray_target = ld3(sn.target_point);
+        if (sn.target_type == 2) {
+            const DShape<F> &sh = sv.shapes[sn.target_shape];
+            ray_target = xf_point_affine(sh.to_world, mk3<F>(ax * (F) 2 - (F) 1, ay * (F) 2 - (F) 1, (F) 0));
+            weight *= (F) 1 / (sh.inv_surface_area * rect_area(sh));
+        } else if (sn.target_type == 0) {
+            F ox, oy;
+            square_to_uniform_disk_concentric(ax, ay, ox, oy);
+            V3<F> perp = xf_vector(sn.to_world, mk3<F>(ox, oy, (F) 0));
+            ray_target = bs_c + perp * bs_r;
+        }
+        ray.o = ray_target - ray.d * (F) 2 * bs_r;
     } else if (sn.type == 2) {
         ray.o = xf_point_affine(sn.to_world, mk3<F>(0, 0, 0));
         ray.d = xf_vector(sn.to_world, mk3<F>(0, 0, 1));

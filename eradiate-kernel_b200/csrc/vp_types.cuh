@@ -260,7 +260,9 @@ template <typename F> struct DSensor {
     int n_transforms, has_shutter;
     F to_world[16];
     F target_point[3];
+    F reference_normal[3];           /* distantflux */
     int crop_offset[2], crop_size[2];
+    int n_pixels, pad_sensor;        /* distantflux: film width * height */
 };
 
 /* 32-byte BVH node over the scene-wide triangle pool.  count == 0: inner node

@@ -80,6 +80,9 @@
 #define RayTargetType MultiDistantRayTargetType   /* distant.cpp and mdistant.cpp both define this enum */
 #include <sensors/mdistant.cpp>
 #undef RayTargetType
+#define RayTargetType DistantFluxRayTargetType
+#include <sensors/distantflux.cpp>
+#undef RayTargetType
 #include <sensors/mradiancemeter.cpp>
 #undef private
 #undef protected
@@ -348,6 +351,16 @@ template <typename Float, typename Spectrum> struct B200Describe {
             else if (n == "DistantSensor_None_BoundingSphere") o.target_type = B2VP_TARGET_NONE;
             else unsupported("distant sensor with shape targets / origins (" + n + ")");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
+        } else if (n.rfind("DistantFluxSensor_", 0) == 0) {
+            using D = DistantFluxSensorImpl<Float, Spectrum, DistantFluxRayTargetType::Point>;
+            const D *d = static_cast<const D *>(sn);
+            o.type = B2VP_SENSOR_DISTANTFLUX;
+            if (n == "DistantFluxSensor_Point") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_target_point); }
+            else if (n == "DistantFluxSensor_NoTarget") o.target_type = B2VP_TARGET_NONE;
+            else unsupported("distantflux sensor with a shape target");
+            if (d->m_origin_shape) unsupported("distantflux sensor with an origin shape");
+            o.origin_type = B2VP_ORIGIN_BSPHERE;
+            for (int k = 0; k < 3; ++k) o.reference_normal[k] = (double) d->m_reference_normal[k];
         } else if (n == "RadianceMeter") {
             o.type = B2VP_SENSOR_RADIANCEMETER;
         } else if (n.rfind("MultiDistantSensor_", 0) == 0) {

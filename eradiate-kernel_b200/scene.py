@@ -519,6 +519,15 @@ class _Builder:
                 raise RuntimeError("distant sensor with a ray_origin shape is not supported by the B200 volpath")
             sn.origin_type = abi.ORIGIN_BSPHERE
             sn.needs_aperture_sample = 1
+        elif t == "distantflux":  # distantflux.cpp:59-176
+            sn.type = abi.SENSOR_DISTANTFLUX
+            target("target")
+            if "origin" in node:
+                raise RuntimeError("distantflux sensor with an origin shape is not supported by the B200 volpath")
+            sn.origin_type = abi.ORIGIN_BSPHERE
+            sn.needs_aperture_sample = 1
+            # m_reference_normal: props.transform("to_world") (single precision, widened) times (0, 0, 1)
+            sn.reference_normal[:] = [float(x) for x in to_world.vector([0, 0, 1])]
         elif t == "mdistant":  # mdistant.cpp:146-207
             sn.type = abi.SENSOR_MDISTANT
             dirs = np.asarray(node["directions"], dtype=np.float32).reshape(-1, 3)  # std::stof
@@ -633,7 +642,7 @@ def load_dict(d, variant="scalar_mono"):
             b.shape(v)
         elif t == "directional":
             emitters.append(v)
-        elif t in ("distant", "mdistant", "radiancemeter", "mradiancemeter"):
+        elif t in ("distant", "mdistant", "radiancemeter", "mradiancemeter", "distantflux"):
             if sensor_node is not None:
                 raise RuntimeError("the B200 volpath renders one sensor per scene")
             sensor_node = v

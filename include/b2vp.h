@@ -66,7 +66,8 @@ enum {
     B2VP_SENSOR_DISTANT        = 0, /* src/sensors/distant.cpp        */
     B2VP_SENSOR_MDISTANT       = 1, /* src/sensors/mdistant.cpp       */
     B2VP_SENSOR_RADIANCEMETER  = 2, /* src/sensors/radiancemeter.cpp  */
-    B2VP_SENSOR_MRADIANCEMETER = 3  /* src/sensors/mradiancemeter.cpp */
+    B2VP_SENSOR_MRADIANCEMETER = 3, /* src/sensors/mradiancemeter.cpp */
+    B2VP_SENSOR_DISTANTFLUX    = 4  /* src/sensors/distantflux.cpp    */
 };
 enum { B2VP_DIR_SINGLE = 0, B2VP_DIR_SAMPLE_WIDTH = 1, B2VP_DIR_SAMPLE_ALL = 2 };
 enum { B2VP_TARGET_NONE = 0, B2VP_TARGET_POINT = 1, B2VP_TARGET_SHAPE = 2 };
@@ -182,6 +183,7 @@ typedef struct B2vpSensor {
     int32_t n_transforms;      /* mdistant / mradiancemeter sensor count       */
     B2vpMat4 to_world;         /* distant / radiancemeter world transform      */
     double target_point[3];
+    double reference_normal[3]; /* distantflux: to_world * (0,0,1) (distantflux.cpp:173-175) */
     double shutter_open, shutter_open_time;
     const double *transforms;  /* n_transforms * 16, column-major              */
     /* film (hdrfilm.cpp / film.cpp) */

@@ -260,7 +260,7 @@ class _Writer:
 SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj")
 MEDIA = ("homogeneous", "heterogeneous")
 BSDFS = ("diffuse", "rpv", "null", "bilambertian")
-SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter")
+SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter", "distantflux")
 INTEGRATORS = ("volpath", "volpath_b200", "volpathmis", "moment", "path")
 
 

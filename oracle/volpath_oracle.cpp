@@ -1080,6 +1080,24 @@ F sensor_sample_ray(const OScene<F> &s, F fx, F fy, F ax, F ay, Ray<F> &ray, boo
             ray.o = s.bs_center + perp * s.bs_radius - ray.d * s.bs_radius;
             weight = 1;
         }
+    } else if (sn.type == B2VP_SENSOR_DISTANTFLUX) { /* distantflux.cpp:184-251 */
+        const M4<F> &trafo = s.sensor_to_world;
+        ray.d = -xf_vector(trafo, square_to_uniform_hemisphere(fx, fy));
+        const F npixels = (F) ((size_t) sn.film_size[0] * (size_t) sn.film_size[1]);
+        /* square_to_uniform_hemisphere_pdf is the constant 1 / (2 pi) (warp.h:305-312, no domain test) */
+        weight = dot(-ray.d, ld3<F>(sn.reference_normal)) / (Consts<F>::InvTwoPi * npixels);
+        V3<F> ray_target = ld3<F>(sn.target_point);
+        if (sn.target_type == B2VP_TARGET_SHAPE) {
+            const OShape<F> &sh = s.shapes[sn.target_shape];
+            ray_target = xf_point_affine(sh.to_world, V3<F>{ ax * (F) 2 - (F) 1, ay * (F) 2 - (F) 1, (F) 0 });
+            weight *= (F) 1 / (sh.inv_surface_area * rect_area(sh));
+        } else if (sn.target_type == B2VP_TARGET_NONE) {
+            F ox, oy; square_to_uniform_disk_concentric(ax, ay, ox, oy);
+            V3<F> perp = xf_vector(trafo, V3<F>{ ox, oy, (F) 0 });
+            ray_target = s.bs_center + perp * s.bs_radius;
+        }
+        if (sn.origin_type == B2VP_ORIGIN_SHAPE) { ok = false; return 0; }
+        ray.o = ray_target - ray.d * (F) 2 * s.bs_radius;
     } else if (sn.type == B2VP_SENSOR_RADIANCEMETER) {
         ray.o = xf_point_affine(s.sensor_to_world, V3<F>{ 0, 0, 0 });
         ray.d = xf_vector(s.sensor_to_world, V3<F>{ 0, 0, 1 });

@@ -174,6 +174,19 @@ def _blendphase(grid_weight, **kw):
     return d
 
 
+def _distantflux(target, **kw):
+    """C2 seen by a `distantflux` sensor (src/sensors/distantflux.cpp): a 16 x 16 film over the
+    hemisphere of a tilted reference normal, with a point target or none (bounding-sphere cross section)."""
+    d = scenes.c2(**kw)
+    T = scenes.T
+    sn = {"type": "distantflux", "to_world": T.look_at([0, 0, 0], [0.125, -0.25, 1.0], [0, 1, 0], np.float32),
+          "sampler": d["sensor"]["sampler"], "film": scenes.film(16, 16)}
+    if target:
+        sn["target"] = [0.25, -0.5, 0.0]
+    d["sensor"] = sn
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -232,6 +245,9 @@ CASES = {
     "c2_blendphase": (lambda v: _blendphase(True, spp=1, variant=v, width=256), "scalar_mono"),
     "c2_blendphase_const": (lambda v: _blendphase(False, spp=1, variant=v, width=256), "scalar_mono"),
     "c2_blendphase_f64": (lambda v: _blendphase(True, spp=1, variant=v, width=128), "scalar_mono_double"),
+    "c2_distantflux": (lambda v: _distantflux(True, spp=1, variant=v), "scalar_mono"),
+    "c2_distantflux_notarget": (lambda v: _distantflux(False, spp=1, variant=v), "scalar_mono"),
+    "c2_distantflux_f64": (lambda v: _distantflux(True, spp=1, variant=v), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
