@@ -473,6 +473,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     }
     if (have_tabphase) ft |= FT_TABPHASE;
     if (have_blendphase) ft |= FT_BLENDPHASE;
+    if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX) ft |= FT_DISTANTFLUX;
     g.features = ft;
 
     /* blob layout */

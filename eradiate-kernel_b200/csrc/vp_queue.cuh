@@ -779,7 +779,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F ax = (posx - (F) sn.crop_offset[0]) / (F) sn.crop_size[0];
                     F ay = (posy - (F) sn.crop_offset[1]) / (F) sn.crop_size[1];
                     Ray<F> ray;
-                    c.ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
+                    c.ray_weight = sensor_sample_ray<F, FEAT>(sv, ax, ay, apx, apy, ray);
                     c.posx = posx; c.posy = posy;
                     s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
                     /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */

@@ -57,7 +57,8 @@ enum : uint32_t {
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
-    FT_ALL = 0x7fffu
+    FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux                             */
+    FT_ALL = 0xffffu
 };
 
 
@@ -904,7 +905,8 @@ template <typename F> VP_D F rect_area(const DShape<F> &sh) { return norm(cross(
 
 /* Sensor::sample_ray_differential (src/sensors/distant.cpp:299-386, mdistant.cpp:216-266,
    radiancemeter.cpp:106-139, mradiancemeter.cpp:134-159); returns the ray weight */
-template <typename F> VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> &ray) {
+template <typename F, uint32_t FEAT = FT_ALL>
+VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> &ray) {
     const DScene<F> &g = *sv.g;
     const DSensor<F> &sn = g.sensor;
     ray.mint = K<F>::RayEpsilon;
@@ -960,7 +962,7 @@ template <typename F> VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F f
             ray.o = bs_c + perp * bs_r - ray.d * bs_r;
             weight = 1;
         }
-    } else if (sn.type == 4) { /* distantflux.cpp:184-251 */
+    } else if ((FEAT & FT_DISTANTFLUX) && sn.type == 4) { /* distantflux.cpp:184-251 */
         ray.d = -xf_vector(sn.to_world, square_to_uniform_hemisphere(fx, fy));
         /* square_to_uniform_hemisphere_pdf is the constant 1 / (2 pi) (warp.h:305-312) */
         weight = dot(-ray.d, ld3(sn.reference_normal)) / (K<F>::InvTwoPi * (F) sn.n_pixels);
