@@ -23,6 +23,7 @@ WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_RAYLEIGH, PHASE_HG = 0, 1, 2
 EMITTER_DIRECTIONAL = 0
 SENSOR_DISTANT, SENSOR_MDISTANT, SENSOR_RADIANCEMETER, SENSOR_MRADIANCEMETER, SENSOR_DISTANTFLUX = 0, 1, 2, 3, 4
+SENSOR_IRRADIANCEMETER = 5
 DIR_SINGLE, DIR_SAMPLE_WIDTH, DIR_SAMPLE_ALL = 0, 1, 2
 TARGET_NONE, TARGET_POINT, TARGET_SHAPE = 0, 1, 2
 ORIGIN_BSPHERE, ORIGIN_SHAPE = 0, 1

@@ -242,7 +242,7 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
             return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
     const B2vpSensor &sn = d->sensor;
-    if (sn.type < 0 || sn.type > B2VP_SENSOR_DISTANTFLUX)
+    if (sn.type < 0 || sn.type > B2VP_SENSOR_IRRADIANCEMETER)
         return fail(B2VP_ERR_UNSUPPORTED, "sensor type %d not supported by the B200 volpath", sn.type);
     if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_DISTANTFLUX) && sn.origin_type == B2VP_ORIGIN_SHAPE)
         return fail(B2VP_ERR_UNSUPPORTED, "distant sensor with a ray_origin shape is not supported");
@@ -251,6 +251,9 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         (sn.target_shape < 0 || sn.target_shape >= (int) d->n_shapes ||
          d->shapes[sn.target_shape].type != B2VP_SHAPE_RECTANGLE))
         return fail(B2VP_ERR_UNSUPPORTED, "sensor ray_target shape must be a rectangle");
+    if (sn.type == B2VP_SENSOR_IRRADIANCEMETER &&
+        (sn.origin_shape < 0 || sn.origin_shape >= (int) d->n_shapes || d->shapes[sn.origin_shape].type != B2VP_SHAPE_RECTANGLE))
+        return fail(B2VP_ERR_UNSUPPORTED, "irradiancemeter: the parent shape must be a rectangle");
     if ((sn.type == B2VP_SENSOR_MDISTANT || sn.type == B2VP_SENSOR_MRADIANCEMETER) &&
         (sn.n_transforms <= 0 || !sn.transforms))
         return fail(B2VP_ERR_INVALID, "multi-sensor without transforms");
@@ -473,7 +476,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     }
     if (have_tabphase) ft |= FT_TABPHASE;
     if (have_blendphase) ft |= FT_BLENDPHASE;
-    if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX) ft |= FT_DISTANTFLUX;
+    if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX || d.sensor.type == B2VP_SENSOR_IRRADIANCEMETER) ft |= FT_DISTANTFLUX;
     g.features = ft;
 
     /* blob layout */
@@ -586,7 +589,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     o.has_shutter = sn.shutter_open_time > 0 ? 1 : 0;
     cvt(sn.to_world.m, o.to_world, 16); cvt(sn.target_point, o.target_point, 3);
     cvt(sn.reference_normal, o.reference_normal, 3);
-    o.n_pixels = sn.film_size[0] * sn.film_size[1]; o.pad_sensor = 0;
+    o.n_pixels = sn.film_size[0] * sn.film_size[1]; o.origin_shape = sn.origin_shape;
     for (int k = 0; k < 2; ++k) { o.crop_offset[k] = sn.crop_offset[k]; o.crop_size[k] = sn.crop_size[k]; }
 
     g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;

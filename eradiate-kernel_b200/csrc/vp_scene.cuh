@@ -57,7 +57,7 @@ enum : uint32_t {
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
-    FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux                             */
+    FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter       */
     FT_ALL = 0xffffu
 };
 
@@ -978,6 +978,12 @@ VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> 
             ray_target = bs_c + perp * bs_r;
         }
         ray.o = ray_target - ray.d * (F) 2 * bs_r;
+    } else if ((FEAT & FT_DISTANTFLUX) && sn.type == 5) { /* irradiancemeter.cpp:88-118 over rectangle.cpp:111-125 */
+        const DShape<F> &sh = sv.shapes[sn.origin_shape];
+        ray.o = xf_point_affine(sh.to_world, mk3<F>(fx * (F) 2 - (F) 1, fy * (F) 2 - (F) 1, (F) 0));
+        V3<F> local = square_to_cosine_hemisphere(ax, ay);
+        ray.d = make_frame(ld3(sh.fn)).to_world(local);
+        weight = K<F>::Pi;
     } else if (sn.type == 2) {
         ray.o = xf_point_affine(sn.to_world, mk3<F>(0, 0, 0));
         ray.d = xf_vector(sn.to_world, mk3<F>(0, 0, 1));

@@ -262,7 +262,7 @@ template <typename F> struct DSensor {
     F target_point[3];
     F reference_normal[3];           /* distantflux */
     int crop_offset[2], crop_size[2];
-    int n_pixels, pad_sensor;        /* distantflux: film width * height */
+    int n_pixels, origin_shape;      /* distantflux: film width * height; irradiancemeter: the parent rectangle */
 };
 
 /* 32-byte BVH node over the scene-wide triangle pool.  count == 0: inner node

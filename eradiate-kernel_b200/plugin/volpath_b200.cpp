@@ -264,7 +264,7 @@ template <typename Float, typename Spectrum> struct B200Describe {
         o.bsdf = bsdf(s->bsdf());
         o.interior_medium = medium(s->interior_medium());
         o.exterior_medium = medium(s->exterior_medium());
-        if (s->is_emitter() || s->is_sensor()) unsupported("area emitters / shape sensors");
+        if (s->is_emitter()) unsupported("area emitters");
         if (s->is_mesh()) {
             const Mesh *m = static_cast<const Mesh *>(s);
             o.type = B2VP_SHAPE_MESH;
@@ -335,9 +335,14 @@ template <typename Float, typename Spectrum> struct B200Describe {
         o.medium = medium(sn->medium());
         o.target_shape = o.origin_shape = -1;
         o.needs_aperture_sample = sn->needs_aperture_sample();
-        auto world = sn->m_world_transform->eval(0.f);   /* AnimatedTransform: single precision */
-        ScalarTransform4f world_s(world);
-        o.to_world = mat(world_s.matrix);
+        if (sn->m_world_transform) {   /* AnimatedTransform: single precision; shape sensors have none of their own */
+            auto world = sn->m_world_transform->eval(0.f);
+            ScalarTransform4f world_s(world);
+            o.to_world = mat(world_s.matrix);
+        } else {
+            ScalarTransform4f id;
+            o.to_world = mat(id.matrix);
+        }
         auto target_point = [&](const auto &p) { for (int k = 0; k < 3; ++k) o.target_point[k] = (double) p[k]; };
         if (n.rfind("DistantSensor_", 0) == 0) {
             /* the members read do not depend on the target / origin template arguments */
@@ -361,6 +366,12 @@ template <typename Float, typename Spectrum> struct B200Describe {
             if (d->m_origin_shape) unsupported("distantflux sensor with an origin shape");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
             for (int k = 0; k < 3; ++k) o.reference_normal[k] = (double) d->m_reference_normal[k];
+        } else if (n == "IrradianceMeter") {   /* attached to a shape (shape.cpp:47-54): a rectangle here */
+            o.type = B2VP_SENSOR_IRRADIANCEMETER;
+            auto it = t.shape_ids.find(sn->shape());
+            if (it == t.shape_ids.end() || t.shapes[it->second].type != B2VP_SHAPE_RECTANGLE)
+                unsupported("an irradiancemeter on a shape other than a rectangle");
+            o.origin_shape = it->second;
         } else if (n == "RadianceMeter") {
             o.type = B2VP_SENSOR_RADIANCEMETER;
         } else if (n.rfind("MultiDistantSensor_", 0) == 0) {

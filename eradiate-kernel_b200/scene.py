@@ -106,6 +106,7 @@ class _Builder:
         self.bbox_min = np.full(3, np.inf, dtype=self.dtype)
         self.bbox_max = np.full(3, -np.inf, dtype=self.dtype)
         self.sensor = None
+        self.shape_sensor = None   # (sensor node, index of its parent shape)
         self.integrator = None
         self.keep = []
 
@@ -339,8 +340,14 @@ class _Builder:
         s.bsdf = self.resolve(node.get("bsdf"), "bsdf", self.bsdf)
         s.interior_medium = self.resolve(node["interior"], "medium", self.medium) if "interior" in node else -1
         s.exterior_medium = self.resolve(node["exterior"], "medium", self.medium) if "exterior" in node else -1
-        if "emitter" in node or "sensor" in node:
-            raise RuntimeError("area emitters / shape sensors are not supported by the B200 volpath")
+        if "emitter" in node:
+            raise RuntimeError("area emitters are not supported by the B200 volpath")
+        if "sensor" in node:  # a sensor attached to the shape (shape.cpp:47-54): irradiancemeter on a rectangle
+            if node["sensor"].get("type") != "irradiancemeter" or t != "rectangle":
+                raise RuntimeError("only an irradiancemeter on a rectangle is supported as a shape sensor")
+            if self.shape_sensor is not None:
+                raise RuntimeError("the B200 volpath renders one sensor per scene")
+            self.shape_sensor = (node["sensor"], len(self.shapes))
         if t == "rectangle":  # src/shapes/rectangle.cpp:75-104
             s.type = abi.SHAPE_RECTANGLE
             if node.get("flip_normals", False):
@@ -519,6 +526,15 @@ class _Builder:
                 raise RuntimeError("distant sensor with a ray_origin shape is not supported by the B200 volpath")
             sn.origin_type = abi.ORIGIN_BSPHERE
             sn.needs_aperture_sample = 1
+        elif t == "irradiancemeter":  # irradiancemeter.cpp:54-80
+            sn.type = abi.SENSOR_IRRADIANCEMETER
+            if "to_world" in node:
+                raise RuntimeError("Found a 'to_world' transformation -- this is not allowed. The irradiance meter "
+                                   "inherits this transformation from its parent shape.")
+            if (w, h) != (1, 1):
+                raise RuntimeError("This sensor only supports films of size 1x1 Pixels!")
+            sn.origin_shape = node["_parent_shape"]
+            sn.needs_aperture_sample = 1
         elif t == "distantflux":  # distantflux.cpp:59-176
             sn.type = abi.SENSOR_DISTANTFLUX
             target("target")
@@ -654,6 +670,10 @@ def load_dict(d, variant="scalar_mono"):
             raise RuntimeError("plugin %r is not supported by the B200 volpath" % t)
     for e in emitters:
         b.emitter(e)
+    if b.shape_sensor is not None:
+        if sensor_node is not None:
+            raise RuntimeError("the B200 volpath renders one sensor per scene")
+        sensor_node = dict(b.shape_sensor[0], _parent_shape=b.shape_sensor[1])
     if sensor_node is None:
         raise RuntimeError("scene has no sensor")
     b.parse_sensor(sensor_node)

@@ -67,7 +67,10 @@ enum {
     B2VP_SENSOR_MDISTANT       = 1, /* src/sensors/mdistant.cpp       */
     B2VP_SENSOR_RADIANCEMETER  = 2, /* src/sensors/radiancemeter.cpp  */
     B2VP_SENSOR_MRADIANCEMETER = 3, /* src/sensors/mradiancemeter.cpp */
-    B2VP_SENSOR_DISTANTFLUX    = 4  /* src/sensors/distantflux.cpp    */
+    B2VP_SENSOR_DISTANTFLUX    = 4, /* src/sensors/distantflux.cpp    */
+    /* src/sensors/irradiancemeter.cpp: a sensor attached to a shape (origin_shape, a rectangle): positions are
+       sampled on it, directions from the cosine hemisphere about its normal, weight pi */
+    B2VP_SENSOR_IRRADIANCEMETER = 5
 };
 enum { B2VP_DIR_SINGLE = 0, B2VP_DIR_SAMPLE_WIDTH = 1, B2VP_DIR_SAMPLE_ALL = 2 };
 enum { B2VP_TARGET_NONE = 0, B2VP_TARGET_POINT = 1, B2VP_TARGET_SHAPE = 2 };

@@ -181,6 +181,8 @@ class _Writer:
             out.append(_xyz("point", "center", v["center"]))
         if "radius" in v:
             out.append('<float name="radius" value="%s"/>' % _num(v["radius"]))
+        if "sensor" in v:
+            out.append(self.sensor(v["sensor"]))
         if "bsdf" in v:
             out.append(self.child("bsdf", v["bsdf"], "bsdf"))
         for key in ("interior", "exterior"):

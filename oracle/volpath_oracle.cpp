@@ -1098,6 +1098,12 @@ F sensor_sample_ray(const OScene<F> &s, F fx, F fy, F ax, F ay, Ray<F> &ray, boo
         }
         if (sn.origin_type == B2VP_ORIGIN_SHAPE) { ok = false; return 0; }
         ray.o = ray_target - ray.d * (F) 2 * s.bs_radius;
+    } else if (sn.type == B2VP_SENSOR_IRRADIANCEMETER) { /* irradiancemeter.cpp:88-118 over rectangle.cpp:111-125 */
+        const OShape<F> &sh = s.shapes[sn.origin_shape];
+        ray.o = xf_point_affine(sh.to_world, V3<F>{ fx * (F) 2 - (F) 1, fy * (F) 2 - (F) 1, (F) 0 });
+        V3<F> local = square_to_cosine_hemisphere(ax, ay);
+        ray.d = make_frame(sh.frame.n).to_world(local);
+        weight = Consts<F>::Pi;
     } else if (sn.type == B2VP_SENSOR_RADIANCEMETER) {
         ray.o = xf_point_affine(s.sensor_to_world, V3<F>{ 0, 0, 0 });
         ray.d = xf_vector(s.sensor_to_world, V3<F>{ 0, 0, 1 });

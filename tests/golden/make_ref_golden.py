@@ -187,6 +187,19 @@ def _distantflux(target, **kw):
     return d
 
 
+def _irradiancemeter(spp, variant):
+    """C2 with an `irradiancemeter` (src/sensors/irradiancemeter.cpp) on a small rectangle floating
+    in the atmosphere, facing up: downwelling irradiance at that level."""
+    d = scenes.c2(spp=spp, variant=variant, width=1)
+    T = scenes.T
+    del d["sensor"]
+    d["plate"] = {"type": "rectangle", "to_world": T.translate([0.5, -0.25, 0.25], np.float32) @ T.scale([0.5, 0.25, 1], np.float32),
+                  "bsdf": {"type": "diffuse", "reflectance": 0.25},
+                  "sensor": {"type": "irradiancemeter", "medium": {"type": "ref", "id": "atm"},
+                             "sampler": {"type": "independent", "sample_count": spp}, "film": scenes.film(1)}}
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -248,6 +261,8 @@ CASES = {
     "c2_distantflux": (lambda v: _distantflux(True, spp=1, variant=v), "scalar_mono"),
     "c2_distantflux_notarget": (lambda v: _distantflux(False, spp=1, variant=v), "scalar_mono"),
     "c2_distantflux_f64": (lambda v: _distantflux(True, spp=1, variant=v), "scalar_mono_double"),
+    "c2_irradiancemeter": (lambda v: _irradiancemeter(256, v), "scalar_mono"),
+    "c2_irradiancemeter_f64": (lambda v: _irradiancemeter(64, v), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

@@ -19,6 +19,7 @@ CASES = {
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
     "c2_tabphase": lambda v: _tabphase(v),
+    "c2_irradiancemeter": lambda v: _irradiancemeter(v),
     "c2_distantflux": lambda v: _distantflux(v, True),
     "c2_distantflux_notarget": lambda v: _distantflux(v, False),
     "c2_blendphase": lambda v: _blendphase(v, True),
@@ -43,6 +44,11 @@ def _blendphase(variant, grid):
 def _distantflux(variant, target):
     import make_ref_golden
     return make_ref_golden._distantflux(target, spp=4, variant=variant)
+
+
+def _irradiancemeter(variant):
+    import make_ref_golden
+    return make_ref_golden._irradiancemeter(2048, variant)
 
 
 def compare(pkg, oracle, sc, mode, **kw):
