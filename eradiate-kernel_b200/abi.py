@@ -94,7 +94,7 @@ class Sensor(C.Structure):
 class Integrator(C.Structure):
     _fields_ = [
         ("max_depth", c_i32), ("rr_depth", c_i32), ("hide_emitters", c_i32),
-        ("block_size", c_u32), ("samples_per_pass", c_u32), ("arg_order_ltr", c_u32), ("moment", c_u32),
+        ("block_size", c_u32), ("samples_per_pass", c_u32), ("arg_order_ltr", c_u32), ("moment", c_u32), ("mis", c_u32),
     ]
 
 

@@ -595,7 +595,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;
     g.rr_depth = (uint32_t) d.integrator.rr_depth;
     g.hide_emitters = d.integrator.hide_emitters; g.ltr = (int) d.integrator.arg_order_ltr;
-    g.film_ch = d.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS; g.pad_film = 0;
+    g.film_ch = d.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS; g.mis = (int) d.integrator.mis;
     ds.ready = true;
     return B2VP_OK;
 }
@@ -799,7 +799,11 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
        records compete with them for it: measured on 2 x 256^3 grids, 2 slots per thread give 90 Mpaths/s,
        3 and more 56. */
     double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
-    if (const char *e = std::getenv("B2VP_KERNEL")) {
+    /* volpathmis runs on the one-thread-per-stream kernel only: its control flow (no direct-light
+       march, path weights as p / f ratios) is not scheduled by the queue kernel yet */
+    const bool mis = s->desc.integrator.mis != 0;
+    if (mis) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
+    if (const char *e = mis ? nullptr : std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(ds.g.features, &preset); threads = 256; }

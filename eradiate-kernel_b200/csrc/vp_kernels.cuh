@@ -179,9 +179,9 @@ volpath_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStr
             Ray<F> ray;
             F ray_weight = sensor_sample_ray(sv, ax, ay, apx, apy, ray);
 
-            PathCtx<F> ctx{ sv, rng, cnt, g.max_depth, g.rr_depth, g.hide_emitters != 0, g.ltr != 0 };
+            PathCtx<F> ctx{ sv, rng, cnt, g.max_depth, g.rr_depth, g.hide_emitters != 0, g.ltr != 0, g.mis != 2 };
             bool valid;
-            const F raw_value = ctx.sample(ray, sn.medium, valid);
+            const F raw_value = g.mis ? ctx.sample_mis(ray, sn.medium, valid) : ctx.sample(ray, sn.medium, valid);
             F value = ray_weight * raw_value;
             tot[TOT_PATHS]++;
             if (out.out_radiance)

@@ -760,6 +760,16 @@ VP_D V3<F> phase_sample_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p,
     return phase_sample<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], d, s2x, s2y);
 }
 
+/* The pdf PhaseFunction::sample returns with the direction (volpathmis.cpp:229): the value of the sampled phase
+   function in that direction; for a blend the pdf of the nested function that was picked, unweighted
+   (blendphase.cpp:97-112).  It enters the path weights only as pdf / pdf. */
+template <typename F, uint32_t FEAT = FT_ALL>
+VP_D F phase_sample_pdf_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> wi, V3<F> wo, F s1) {
+    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_eval<F, FEAT>(ph, wi, wo);
+    F w = min_(max_(volume_eval<F, FT_ALL, true>(sv, sv.volumes[ph.weight_volume], p), (F) 0), (F) 1);
+    return phase_eval<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], wi, wo);
+}
+
 /* ------------------------------------------------------------------- BSDFs */
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
     BF_Null = 0x1, BF_DiffuseReflection = 0x2, BF_DiffuseTransmission = 0x4, BF_GlossyReflection = 0x8,

@@ -298,7 +298,7 @@ template <typename F> struct DScene {
     DSensor<F> sensor;
     uint32_t max_depth, rr_depth;
     int hide_emitters, ltr;
-    int film_ch, pad_film;          /* film channels per pixel: 5, or 11 under a `moment` integrator */
+    int film_ch, mis;               /* film channels per pixel: 5, or 11 under a `moment` integrator; volpathmis */
     /* small tables packed in one blob so a CTA can stage them in shared memory */
     const unsigned char *blob;
     uint32_t blob_bytes;

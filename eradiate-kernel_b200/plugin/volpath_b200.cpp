@@ -436,6 +436,10 @@ public:
         if (seeding == "wavefront") m_seed_mode = B2VP_SEED_WAVEFRONT;
         else if (seeding == "scalar") m_seed_mode = B2VP_SEED_SCALAR_BLOCKS;
         else Throw("volpath_b200: seeding must be \"wavefront\" or \"scalar\"");
+        /* algorithm: "volpath" (default) or "volpathmis" (src/integrators/volpathmis.cpp; use_spectral_mis as there) */
+        std::string algorithm = props.string("algorithm", "volpath");
+        if (algorithm == "volpathmis") m_mis = props.bool_("use_spectral_mis", true) ? 1 : 2;
+        else if (algorithm != "volpath") Throw("volpath_b200: algorithm must be \"volpath\" or \"volpathmis\"");
     }
     ~B200VolumetricPathIntegrator() { release(); }
 
@@ -494,6 +498,7 @@ public:
         it.samples_per_pass = (uint32_t) m_samples_per_pass;
         it.arg_order_ltr = 0;   /* GCC evaluates the sample arguments right to left (include/b2vp.h) */
         it.moment = 0;
+        it.mis = (uint32_t) m_mis;
         tables.finish();
     }
 
@@ -509,6 +514,7 @@ private:
     B2vpCounters m_totals{};
     int m_device = 0;
     int m_seed_mode = B2VP_SEED_WAVEFRONT;
+    int m_mis = 0;
 };
 
 MTS_IMPLEMENT_CLASS_VARIANT(B200VolumetricPathIntegrator, MonteCarloIntegrator)

@@ -602,13 +602,15 @@ class _Builder:
         moment = 0
         if node.get("type", "volpath") == "moment":  # src/integrators/moment.cpp:39-60: one nested volpath
             nested = [v for v in node.values() if isinstance(v, dict)]
-            if len(nested) != 1 or nested[0].get("type", "volpath") != "volpath":
-                raise RuntimeError("the B200 moment integrator nests exactly one volpath")
+            if len(nested) != 1 or nested[0].get("type", "volpath") not in ("volpath", "volpathmis"):
+                raise RuntimeError("the B200 moment integrator nests exactly one volpath / volpathmis")
             node, moment = nested[0], 1
-        if node.get("type", "volpath") != "volpath":
+        if node.get("type", "volpath") not in ("volpath", "volpathmis"):
             raise RuntimeError("integrator plugin %r is not supported by the B200 volpath" % node["type"])
         it = abi.Integrator()
         it.moment = moment
+        if node.get("type") == "volpathmis":  # volpathmis.cpp:35-52: use_spectral_mis selects the implementation
+            it.mis = 1 if node.get("use_spectral_mis", True) else 2
         it.max_depth = int(node.get("max_depth", -1))
         if it.max_depth < 0 and it.max_depth != -1:
             raise RuntimeError("\"max_depth\" must be set to -1 (infinite) or a value >= 0")
@@ -662,7 +664,7 @@ def load_dict(d, variant="scalar_mono"):
             if sensor_node is not None:
                 raise RuntimeError("the B200 volpath renders one sensor per scene")
             sensor_node = v
-        elif t in ("volpath", "moment"):
+        elif t in ("volpath", "volpathmis", "moment"):
             integrator_node = v
         elif t in ("homogeneous", "heterogeneous", "diffuse", "rpv", "null", "bilambertian"):
             pass

@@ -212,6 +212,10 @@ typedef struct B2vpIntegrator {
        B2VP_FILM_CHANNELS_MOMENT channels per pixel, X Y Z A W followed by the nested integrator's unweighted
        X Y Z and their squares, and ImageBlock::put skips its validity check (integrator.cpp:113-115) */
     uint32_t moment;
+    /* 1: the integrator is `volpathmis` (src/integrators/volpathmis.cpp, spectral MIS over channels; one channel in
+       mono) instead of `volpath`: other control flow, other random-number order.  2: volpathmis with
+       use_spectral_mis=false (differs in mono only in when an emitter march stops) */
+    uint32_t mis;
 } B2vpIntegrator;
 
 #define B2VP_FILM_CHANNELS 5

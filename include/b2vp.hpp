@@ -190,6 +190,8 @@ struct Volpath {
     /* true: nested in a `moment` integrator (src/integrators/moment.cpp): the film gets 6 more channels per pixel,
        the unweighted X Y Z and their squares */
     bool moment = false;
+    /* 1: `volpathmis` (src/integrators/volpathmis.cpp) instead of `volpath`; 2: with use_spectral_mis=false */
+    int mis = 0;
 };
 
 /* A finished scene: owns the descriptor and every array it points to. */
@@ -375,6 +377,7 @@ public:
         it.max_depth = v.max_depth; it.rr_depth = v.rr_depth; it.hide_emitters = v.hide_emitters;
         it.block_size = v.block_size; it.samples_per_pass = v.samples_per_pass; it.arg_order_ltr = 0;
         it.moment = v.moment ? 1u : 0u;
+        it.mis = (uint32_t) v.mis;
         have_integrator_ = true;
     }
 

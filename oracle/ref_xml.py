@@ -249,6 +249,10 @@ class _Writer:
         for key in ("max_depth", "rr_depth", "block_size", "samples_per_pass"):
             if key in v:
                 out.append('<integer name="%s" value="%d"/>' % (key, v[key]))
+        if "use_spectral_mis" in v:
+            out.append('<boolean name="use_spectral_mis" value="%s"/>' % ("true" if v["use_spectral_mis"] else "false"))
+        if "algorithm" in v:
+            out.append('<string name="algorithm" value="%s"/>' % v["algorithm"])
         if "seeding" in v:
             out.append('<string name="seeding" value="%s"/>' % v["seeding"])
         if "hide_emitters" in v:
@@ -306,8 +310,8 @@ def with_plugin(scene, seeding="scalar"):
     reference's CPU volpath), "wavefront" for the plugin's default."""
     d = dict(scene)
     for k, v in scene.items():
-        if isinstance(v, dict) and v.get("type") == "volpath":
-            d[k] = dict(v, type="volpath_b200", seeding=seeding)
+        if isinstance(v, dict) and v.get("type") in ("volpath", "volpathmis"):
+            d[k] = dict(v, type="volpath_b200", seeding=seeding, algorithm=v["type"])
     return d
 
 

@@ -876,6 +876,18 @@ inline V3<F> phase_sample_at(const OScene<F> &s, int idx, const MediumInteractio
     return phase_sample(s.phases[c], s.tabs[c], mi, s2x, s2y);
 }
 
+/* The pdf PhaseFunction::sample returns with the direction (volpathmis.cpp:229): the value of the sampled phase
+   function in that direction -- evaluated here through eval() (rayleigh.cpp:62-65, hg.cpp:70-75 evaluate the same
+   formula at the sampled cosine); for a blend it is the pdf of the nested function that was picked, unweighted
+   (blendphase.cpp:97-112).  It enters the path weights only as pdf / pdf. */
+template <typename F>
+inline F phase_sample_pdf_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, V3<F> wo, F s1) {
+    const B2vpPhase &ph = s.phases[idx];
+    if (ph.type != B2VP_PHASE_BLEND) return phase_eval(ph, s.tabs[idx], mi, wo);
+    int c = s1 > blend_weight(s, ph, mi) ? ph.child[0] : ph.child[1];
+    return phase_eval(s.phases[c], s.tabs[c], mi, wo);
+}
+
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
     F_Null = 0x1, F_DiffuseReflection = 0x2, F_DiffuseTransmission = 0x4, F_GlossyReflection = 0x8,
     F_Smooth = 0x2 | 0x4 | 0x8 | 0x10, F_Delta = 0x1 | 0x20 | 0x40
@@ -1129,6 +1141,7 @@ template <typename F> struct Integrator {
     uint32_t max_depth, rr_depth;
     bool hide_emitters;
     bool ltr; /* argument evaluation order of the compiler that built the reference */
+    bool spectral_mis = true; /* volpathmis `use_spectral_mis` (volpathmis.cpp:36) */
 
     F next_1d(bool active) { return rng.next_float(F(), active); }
 
@@ -1276,6 +1289,243 @@ template <typename F> struct Integrator {
                 medium = target_medium(si, ray.d);
         }
         emitted = transmittance * emitter_val;
+    }
+
+    /* ================= VolpathMisIntegratorImpl (src/integrators/volpathmis.cpp), mono ==================
+       WeightMatrix is 1 x 1 in mono.  p_over_f_nee of the main loop is not carried: it is read only when a path
+       hits an emitter (volpathmis.cpp:253-268), and no area / environment emitter is in scope. */
+    static void update_weights(F &p_over_f, F p, F f, bool active) { /* volpathmis.cpp:447-465 */
+        F ratio = p / f;
+        ratio = std::isfinite(ratio) ? ratio : (F) 0;
+        ratio *= p_over_f;
+        if (active) p_over_f = (ratio != ratio) ? (F) 0 : ratio;
+    }
+    static F mis_weight1(F p_over_f) { return p_over_f == 0 ? (F) 0 : (F) 1 / p_over_f; }            /* :467-482 */
+    static F mis_weight2(F a, F b) { F sum = a + b; return sum == 0 ? (F) 0 : (F) 1 / sum; }           /* :485-500 */
+
+    /* volpathmis.cpp:330-444: returns the emitter value; p_over_f_nee / p_over_f_uni through the references */
+    F sample_emitter_mis(V3<F> ref_p, bool is_medium_interaction, int medium, F p_over_f, bool active,
+                         DirectionSample<F> &ds, F &p_over_f_nee, F &p_over_f_uni) {
+        p_over_f_nee = p_over_f; p_over_f_uni = p_over_f;
+        F sx = next_1d(active), sy = next_1d(active);
+        F weight;
+        ds = sample_emitter_direction(scene, sx, sy, weight);
+        F emitter_val = weight * ds.pdf;
+        if (ds.pdf == 0) emitter_val = 0;
+        active = active && ds.pdf != 0;
+        update_weights(p_over_f_nee, ds.pdf, (F) 1, active);
+        if (!active) return emitter_val;
+
+        Ray<F> ray = spawn_ray(ref_p, ds.d);
+        if (is_medium_interaction) ray.mint = 0;
+        F total_dist = 0;
+        SurfaceInteraction<F> si;
+        bool needs_intersection = true;
+        while (active) {
+            F remaining_dist = ds.dist * ((F) 1 - Consts<F>::ShadowEpsilon) - total_dist;
+            ray.maxt = remaining_dist;
+            active = active && remaining_dist > 0;
+            if (!active) break;
+            bool escaped_medium = false;
+            bool active_medium = active && medium >= 0;
+            bool active_surface = active && !active_medium;
+            if (active_medium) {
+                const OMedium<F> &m = scene.media[medium];
+                MediumInteraction<F> mi = sample_interaction(scene, medium, ray, next_1d(active_medium), cnt);
+                if (m.type == B2VP_MEDIUM_HOMOGENEOUS && mi.is_valid()) ray.maxt = min_(mi.t, remaining_dist);
+                if (needs_intersection) si = ray_intersect(scene, ray, cnt);
+                if (si.t < mi.t) mi.t = Consts<F>::Inf;
+                needs_intersection = false;
+                bool is_spectral = m.spectral, not_spectral = !m.spectral;
+                if (is_spectral) {
+                    F t = min_(remaining_dist, min_(mi.t, si.t)) - mi.mint;
+                    F tr = exp_(-t * mi.combined_extinction);
+                    F free_flight_pdf = (si.t < mi.t || mi.t > remaining_dist) ? tr : tr * mi.combined_extinction;
+                    update_weights(p_over_f_nee, free_flight_pdf, tr, true);
+                    update_weights(p_over_f_uni, free_flight_pdf, tr, true);
+                }
+                if (mi.t > remaining_dist && mi.is_valid()) total_dist = ds.dist;
+                if (mi.t > remaining_dist) mi.t = Consts<F>::Inf;
+                escaped_medium = !mi.is_valid();
+                active_medium = mi.is_valid();
+                is_spectral = is_spectral && active_medium;
+                not_spectral = not_spectral && active_medium;
+                if (active_medium) {
+                    total_dist += mi.t;
+                    cnt.n_null++;
+                    ray.o = mi.p; ray.mint = 0;
+                    si.t = si.t - mi.t;
+                    if (is_spectral) {
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n, true);
+                        update_weights(p_over_f_uni, mi.sigma_n / mi.combined_extinction, mi.sigma_n, true);
+                    }
+                    if (not_spectral) {
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n / mi.combined_extinction, true);
+                        update_weights(p_over_f_uni, mi.sigma_n, mi.sigma_n, true);
+                    }
+                }
+            }
+            bool intersect = active_surface && needs_intersection;
+            if (intersect) si = ray_intersect(scene, ray, cnt);
+            active_surface = active_surface || escaped_medium;
+            if (active_surface) total_dist += si.t;
+            active_surface = active_surface && si.is_valid() && active && !active_medium;
+            if (active_surface) {
+                F bsdf_val = bsdf_eval_null_transmission<F>(scene.bsdfs[scene.shapes[si.shape].bsdf]);
+                update_weights(p_over_f_nee, (F) 1, bsdf_val, true);
+                update_weights(p_over_f_uni, (F) 1, bsdf_val, true);
+            }
+            if (active_surface) ray = spawn_ray(si.p, ray.d);
+            ray.maxt = remaining_dist;
+            needs_intersection = needs_intersection || active_surface;
+            if (spectral_mis)
+                active = active && (active_medium || active_surface) && mis_weight1(p_over_f_uni) != 0;
+            else
+                active = active && (active_medium || active_surface) && (p_over_f_uni != 0 || p_over_f_nee != 0);
+            if (active_surface && is_medium_transition(si))
+                medium = target_medium(si, ray.d);
+        }
+        return emitter_val;
+    }
+
+    /* volpathmis.cpp:91-329 */
+    F sample_mis(Ray<F> ray, int initial_medium, bool active, bool &valid_ray_out) {
+        bool valid_ray = false; /* !hide_emitters && environment != nullptr: no environment in scope */
+        F eta = 1, result = 0;
+        int medium = initial_medium;
+        MediumInteraction<F> mi;
+        bool specular_chain = active && !hide_emitters;
+        uint32_t depth = 0;
+        F p_over_f = 1;
+        SurfaceInteraction<F> si;
+        bool needs_intersection = true;
+        for (int bounce = 0;; ++bounce) {
+            /* Russian roulette (122-128); last_event_was_null is never set in this version of the integrator */
+            F mis_throughput = mis_weight1(p_over_f);
+            F q = min_(mis_throughput * sqr(eta), (F) 0.95f);
+            bool perform_rr = active && depth > rr_depth;
+            F rr_sample = next_1d(active);
+            active = active && !(rr_sample >= q && perform_rr);
+            update_weights(p_over_f, q, (F) 1, perform_rr);
+            bool exceeded_max_depth = depth >= max_depth;
+            active = active && !exceeded_max_depth;
+            active = active && mis_weight1(p_over_f) != 0;
+            if (!active) break;
+
+            bool active_medium = active && medium >= 0;
+            bool active_surface = active && !active_medium;
+            bool act_null_scatter = false, act_medium_scatter = false, escaped_medium = false;
+            bool is_spectral = active_medium, not_spectral = false;
+            if (active_medium) {
+                is_spectral = is_spectral && scene.media[medium].spectral;
+                not_spectral = !is_spectral && active_medium;
+            }
+            if (active_medium) {
+                const OMedium<F> &m = scene.media[medium];
+                mi = sample_interaction(scene, medium, ray, next_1d(active_medium), cnt);
+                if (m.type == B2VP_MEDIUM_HOMOGENEOUS && mi.is_valid()) ray.maxt = mi.t;
+                if (needs_intersection) si = ray_intersect(scene, ray, cnt);
+                needs_intersection = false;
+                if (si.t < mi.t) mi.t = Consts<F>::Inf;
+                if (is_spectral) { /* Medium::eval_tr_and_pdf (medium.cpp:77-89) */
+                    F t = min_(mi.t, si.t) - mi.mint;
+                    F tr = exp_(-t * mi.combined_extinction);
+                    F free_flight_pdf = si.t < mi.t ? tr : tr * mi.combined_extinction;
+                    update_weights(p_over_f, free_flight_pdf, tr, true);
+                }
+                escaped_medium = !mi.is_valid();
+                active_medium = mi.is_valid();
+                is_spectral = is_spectral && active_medium;
+                not_spectral = not_spectral && active_medium;
+            }
+            if (active_medium) {
+                const OMedium<F> &m = scene.media[medium];
+                F u = next_1d(active_medium);
+                bool null_scatter = u >= mi.sigma_t / mi.combined_extinction;
+                act_null_scatter = null_scatter && active_medium;
+                act_medium_scatter = !act_null_scatter && active_medium;
+                if (act_medium_scatter) depth += 1;
+                bool sample_emitters = m.sample_emitters;
+                active = active && depth < max_depth;
+                act_medium_scatter = act_medium_scatter && active;
+                specular_chain = specular_chain && !(act_medium_scatter && sample_emitters);
+                if (act_null_scatter) {
+                    cnt.n_null++;
+                    if (is_spectral) update_weights(p_over_f, mi.sigma_n / mi.combined_extinction, mi.sigma_n, true);
+                    if (not_spectral) update_weights(p_over_f, mi.sigma_n, mi.sigma_n, true);
+                    ray.o = mi.p; ray.mint = 0;
+                    si.t = si.t - mi.t;
+                }
+                if (act_medium_scatter) {
+                    cnt.n_real++;
+                    if (is_spectral) update_weights(p_over_f, mi.sigma_t / mi.combined_extinction, mi.sigma_s, true);
+                    if (not_spectral) update_weights(p_over_f, mi.sigma_t, mi.sigma_s, true);
+                    valid_ray = true;
+                    if (sample_emitters) {
+                        DirectionSample<F> ds;
+                        F nee_end, uni_end;
+                        F emitted = sample_emitter_mis(mi.p, true, medium, p_over_f, true, ds, nee_end, uni_end);
+                        F phase_val = phase_eval_at(scene, m.phase, mi, ds.d);
+                        update_weights(nee_end, (F) 1, phase_val, true);
+                        update_weights(uni_end, ds.delta ? (F) 0 : phase_val, phase_val, true);
+                        result += mis_weight2(nee_end, uni_end) * emitted;
+                    }
+                    F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
+                    F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> wo = phase_sample_at(scene, m.phase, mi, s1, s2x, s2y);
+                    /* the pdf phase->sample returns is the phase function value for every phase function in scope */
+                    F phase_pdf = phase_sample_pdf_at(scene, m.phase, mi, wo, s1);
+                    ray = spawn_ray(mi.p, wo);
+                    ray.mint = 0;
+                    needs_intersection = true;
+                    update_weights(p_over_f, phase_pdf, phase_pdf, true);
+                }
+            }
+
+            active_surface = active_surface || escaped_medium;
+            bool intersect = active_surface && needs_intersection;
+            if (intersect) si = ray_intersect(scene, ray, cnt);
+            /* emitter hit (252-268): shapes carry no emitters, no environment */
+            active_surface = active_surface && si.is_valid();
+            if (active_surface) {
+                cnt.n_surface++;
+                const OShape<F> &sh = scene.shapes[si.shape];
+                const B2vpBsdf &bsdf = scene.bsdfs[sh.bsdf];
+                bool active_e = (bsdf_flags(bsdf) & F_Smooth) != 0 && (depth + 1 < max_depth);
+                if (active_e) {
+                    DirectionSample<F> ds;
+                    F nee_end, uni_end;
+                    F emitted = sample_emitter_mis(si.p, false, medium, p_over_f, true, ds, nee_end, uni_end);
+                    V3<F> wo_local = si.sh_frame.to_local(ds.d);
+                    F bsdf_val = bsdf_eval(bsdf, si.wi, wo_local);
+                    F bsdf_pdf = bsdf_pdf_(bsdf, si.wi, wo_local);
+                    update_weights(nee_end, (F) 1, bsdf_val, true);
+                    update_weights(uni_end, ds.delta ? (F) 0 : bsdf_pdf, bsdf_val, true);
+                    result += mis_weight2(nee_end, uni_end) * emitted;
+                }
+                F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
+                F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                F bsdf_weight;
+                BSDFSample<F> bs = bsdf_sample(bsdf, si.wi, s1, s2x, s2y, bsdf_weight);
+                bool invalid_bsdf_sample = bs.pdf == 0;
+                active_surface = active_surface && bs.pdf > 0;
+                if (active_surface) {
+                    eta *= bs.eta;
+                    ray = spawn_ray(si.p, si.sh_frame.to_world(bs.wo));
+                }
+                needs_intersection = needs_intersection || active_surface;
+                bool non_null_bsdf = active_surface && !(bs.sampled_type & F_Null);
+                valid_ray = valid_ray || non_null_bsdf || invalid_bsdf_sample;
+                specular_chain = specular_chain || (non_null_bsdf && (bs.sampled_type & F_Delta) != 0);
+                specular_chain = specular_chain && !(active_surface && (bs.sampled_type & F_Smooth) != 0);
+                if (non_null_bsdf) depth += 1;
+                update_weights(p_over_f, bs.pdf, bsdf_weight * bs.pdf, active_surface);
+                if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
+            }
+            active = active && (active_surface || active_medium);
+        }
+        valid_ray_out = valid_ray;
+        return result;
     }
 
     /* volpath.cpp:38-257 */
@@ -1582,9 +1832,11 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
             if (!ok) { g_error = "sensor configuration not supported (ray_origin shape)"; return B2VP_ERR_UNSUPPORTED; }
 
             Integrator<F> integ{ scene, rng, cnt, max_depth, (uint32_t) d->integrator.rr_depth,
-                                 d->integrator.hide_emitters != 0, d->integrator.arg_order_ltr != 0 };
+                                 d->integrator.hide_emitters != 0, d->integrator.arg_order_ltr != 0,
+                                 d->integrator.mis != 2 };
             bool valid;
-            const F raw_value = integ.sample(ray, sn.medium, true, valid);
+            const F raw_value = d->integrator.mis ? integ.sample_mis(ray, sn.medium, true, valid)
+                                                  : integ.sample(ray, sn.medium, true, valid);
             F value = ray_weight * raw_value;
             tot.n_paths++;
             if (a->out_radiance)

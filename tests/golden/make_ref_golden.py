@@ -200,6 +200,12 @@ def _irradiancemeter(spp, variant):
     return d
 
 
+def _mis(d, **props):
+    """The scene with the `volpathmis` integrator (src/integrators/volpathmis.cpp)."""
+    d["integrator"] = dict(d["integrator"], type="volpathmis", **props)
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -210,6 +216,7 @@ _BILAMB = {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}  #
 TOL_OVERRIDE = {
     "c3_cloud": (1e-3, 0.97),
     "c3_smooth": (3e-5, 0.97),
+    "c3_volpathmis": (3e-5, 0.97),
 }
 
 CASES = {
@@ -263,6 +270,14 @@ CASES = {
     "c2_distantflux_f64": (lambda v: _distantflux(True, spp=1, variant=v), "scalar_mono_double"),
     "c2_irradiancemeter": (lambda v: _irradiancemeter(256, v), "scalar_mono"),
     "c2_irradiancemeter_f64": (lambda v: _irradiancemeter(64, v), "scalar_mono_double"),
+    "c2_volpathmis": (lambda v: _mis(scenes.c2(spp=1, variant=v, width=256)), "scalar_mono"),
+    "c2_volpathmis_notspectral": (lambda v: _mis(scenes.c2(spp=1, variant=v, width=128, spectral=False)), "scalar_mono"),
+    "c2_volpathmis_depth": (lambda v: _mis(scenes.c2(spp=1, variant=v, width=128, max_depth=4, rr_depth=2), use_spectral_mis=False), "scalar_mono"),
+    "c3_volpathmis": (lambda v: _mis(_c3(smooth=True, spp=1, variant=v, n=16, size=16)), "scalar_mono"),
+    "c5_volpathmis": (lambda v: _mis(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB)), "scalar_mono"),
+    "c1_volpathmis_f64": (lambda v: _mis(scenes.c1(spp=1024, variant=v)), "scalar_mono_double"),
+    "c2_volpathmis_f64": (lambda v: _mis(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono_double"),
+    "c3_volpathmis_f64": (lambda v: _mis(_c3(spp=1, variant=v, n=16, size=16)), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

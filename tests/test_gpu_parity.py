@@ -19,6 +19,9 @@ CASES = {
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
     "c2_tabphase": lambda v: _tabphase(v),
+    "c2_volpathmis": lambda v: _mis(scenes.c2(spp=8, variant=v, width=64)),
+    "c3_volpathmis": lambda v: _mis(scenes.c3(spp=2, variant=v, n=16, size=12)),
+    "c5_volpathmis": lambda v: _mis(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64)),
     "c2_irradiancemeter": lambda v: _irradiancemeter(v),
     "c2_distantflux": lambda v: _distantflux(v, True),
     "c2_distantflux_notarget": lambda v: _distantflux(v, False),
@@ -49,6 +52,11 @@ def _distantflux(variant, target):
 def _irradiancemeter(variant):
     import make_ref_golden
     return make_ref_golden._irradiancemeter(2048, variant)
+
+
+def _mis(d):
+    d["integrator"] = dict(d["integrator"], type="volpathmis")
+    return d
 
 
 def compare(pkg, oracle, sc, mode, **kw):
