@@ -436,6 +436,11 @@ public:
         if (seeding == "wavefront") m_seed_mode = B2VP_SEED_WAVEFRONT;
         else if (seeding == "scalar") m_seed_mode = B2VP_SEED_SCALAR_BLOCKS;
         else Throw("volpath_b200: seeding must be \"wavefront\" or \"scalar\"");
+        /* moment=true: the film also gets the channels a `moment` integrator around this one would add
+           (src/integrators/moment.cpp:39-60): nested.X/Y/Z and m2_nested.X/Y/Z, for per-pixel variance estimates.
+           (A `moment` plugin cannot wrap this integrator itself: it calls sample(), and the batch boundary here is
+           render().) */
+        m_moment = props.bool_("moment", false);
         /* algorithm: "volpath" (default) or "volpathmis" (src/integrators/volpathmis.cpp; use_spectral_mis as there) */
         std::string algorithm = props.string("algorithm", "volpath");
         if (algorithm == "volpathmis") m_mis = props.bool_("use_spectral_mis", true) ? 1 : 2;
@@ -453,6 +458,9 @@ public:
 
         ref<Film> film = sensor->film();
         std::vector<std::string> channels = { "X", "Y", "Z", "A", "W" };   /* integrator.cpp:67-73 */
+        if (m_moment)
+            for (const char *name : { "nested.X", "nested.Y", "nested.Z", "m2_nested.X", "m2_nested.Y", "m2_nested.Z" })
+                channels.push_back(name);
         film->prepare(channels);
         ScalarVector2i size = film->crop_size();
         ref<ImageBlock> block = new ImageBlock(size, channels.size(), film->reconstruction_filter(), false);
@@ -497,7 +505,7 @@ public:
         it.block_size = m_block_size;
         it.samples_per_pass = (uint32_t) m_samples_per_pass;
         it.arg_order_ltr = 0;   /* GCC evaluates the sample arguments right to left (include/b2vp.h) */
-        it.moment = 0;
+        it.moment = m_moment ? 1u : 0u;
         it.mis = (uint32_t) m_mis;
         tables.finish();
     }
@@ -515,6 +523,7 @@ private:
     int m_device = 0;
     int m_seed_mode = B2VP_SEED_WAVEFRONT;
     int m_mis = 0;
+    bool m_moment = false;
 };
 
 MTS_IMPLEMENT_CLASS_VARIANT(B200VolumetricPathIntegrator, MonteCarloIntegrator)

@@ -54,7 +54,8 @@ static void oracle_callback(const B2vpSceneDesc *desc, void *user) {
     auto render = (int (*)(const B2vpSceneDesc *, const B2vpRenderArgs *, void *)) dlsym(job->oracle, "b2vp_oracle_render");
     auto last_error = (const char *(*)()) dlsym(job->oracle, "b2vp_oracle_last_error");
     const bool f64 = desc->precision == B2VP_PREC_F64;
-    int32_t hdr[4] = { desc->sensor.crop_size[0], desc->sensor.crop_size[1], B2VP_FILM_CHANNELS, (int32_t) f64 };
+    int32_t hdr[4] = { desc->sensor.crop_size[0], desc->sensor.crop_size[1],
+                       desc->integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS, (int32_t) f64 };
     size_t n = (size_t) hdr[0] * hdr[1] * hdr[2];
     std::vector<unsigned char> film(n * (f64 ? 8 : 4));
     B2vpRenderArgs a{};

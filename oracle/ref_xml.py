@@ -251,6 +251,8 @@ class _Writer:
                 out.append('<integer name="%s" value="%d"/>' % (key, v[key]))
         if "use_spectral_mis" in v:
             out.append('<boolean name="use_spectral_mis" value="%s"/>' % ("true" if v["use_spectral_mis"] else "false"))
+        if v.get("moment") is True:
+            out.append('<boolean name="moment" value="true"/>')
         if "algorithm" in v:
             out.append('<string name="algorithm" value="%s"/>' % v["algorithm"])
         if "seeding" in v:
@@ -312,6 +314,10 @@ def with_plugin(scene, seeding="scalar"):
     for k, v in scene.items():
         if isinstance(v, dict) and v.get("type") in ("volpath", "volpathmis"):
             d[k] = dict(v, type="volpath_b200", seeding=seeding, algorithm=v["type"])
+        elif isinstance(v, dict) and v.get("type") == "moment":   # moment around a volpath -> the plugin's own `moment`
+            inner = [c for c in v.values() if isinstance(c, dict)][0]
+            outer = {kk: vv for kk, vv in v.items() if not isinstance(vv, dict) and kk != "type"}
+            d[k] = dict(inner, type="volpath_b200", seeding=seeding, algorithm=inner["type"], moment=True, **outer)
     return d
 
 

@@ -20,8 +20,9 @@ sys.path.insert(0, os.path.join(HERE, "golden"))
 import make_ref_golden  # noqa: E402
 from test_reference_parity import REF, check_against_reference  # noqa: E402
 
-# fixture scenes with a plain volpath integrator (the moment wrapper calls sample(), which the GPU path does not have)
-PLUGIN_CASES = [n for n in sorted(make_ref_golden.CASES) if "moment" not in n]
+# every fixture scene; a `moment` wrapper becomes the plugin's own moment=true (the wrapper calls sample(), which the
+# GPU path does not have)
+PLUGIN_CASES = sorted(make_ref_golden.CASES)
 
 
 def ref_xml_or_skip():
