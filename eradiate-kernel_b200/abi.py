@@ -16,6 +16,7 @@ PREC_F32, PREC_F64 = 0, 1
 SHAPE_RECTANGLE, SHAPE_SPHERE, SHAPE_MESH = 0, 1, 2
 BSDF_DIFFUSE, BSDF_NULL, BSDF_RPV, BSDF_BILAMBERTIAN = 0, 1, 2, 3
 PHASE_TABULATED, PHASE_BLEND = 3, 4
+EMITTER_CONSTANT = 1
 MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
 VOLUME_CONST, VOLUME_GRID = 0, 1
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1

@@ -239,8 +239,14 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
             return fail(B2VP_ERR_INVALID, "phase %u: blendphase weight volume out of range", i);
     }
     for (uint32_t i = 0; i < d->n_emitters; ++i)
-        if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL)
-            return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` is supported by the B200 volpath", i);
+        if (d->emitters[i].type != B2VP_EMITTER_DIRECTIONAL && d->emitters[i].type != B2VP_EMITTER_CONSTANT)
+            return fail(B2VP_ERR_UNSUPPORTED, "emitter %u: only `directional` and `constant` are supported by the B200 volpath", i);
+    {
+        int n_env = 0;
+        for (uint32_t i = 0; i < d->n_emitters; ++i) n_env += d->emitters[i].type == B2VP_EMITTER_CONSTANT;
+        if (n_env > 1) return fail(B2VP_ERR_INVALID, "Only one environment emitter can be specified per scene.");
+        if (n_env && d->integrator.mis) return fail(B2VP_ERR_UNSUPPORTED, "volpathmis with an environment emitter is not supported");
+    }
     const B2vpSensor &sn = d->sensor;
     if (sn.type < 0 || sn.type > B2VP_SENSOR_IRRADIANCEMETER)
         return fail(B2VP_ERR_UNSUPPORTED, "sensor type %d not supported by the B200 volpath", sn.type);
@@ -397,6 +403,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     for (size_t i = 0; i < emitters.size(); ++i) {
         cvt(s->emitters[i].direction, emitters[i].dir, 3);
         emitters[i].irradiance = (F) s->emitters[i].irradiance;
+        emitters[i].type = s->emitters[i].type; emitters[i].pad[0] = emitters[i].pad[1] = emitters[i].pad[2] = 0;
     }
 
     /* volumes: grids are widened to F at load like the reference (volume_data.h:85-90) */
@@ -596,6 +603,8 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     g.rr_depth = (uint32_t) d.integrator.rr_depth;
     g.hide_emitters = d.integrator.hide_emitters; g.ltr = (int) d.integrator.arg_order_ltr;
     g.film_ch = d.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS; g.mis = (int) d.integrator.mis;
+    g.environment = -1; g.pad_env = 0;
+    for (uint32_t i = 0; i < d.n_emitters; ++i) if (s->emitters[i].type == B2VP_EMITTER_CONSTANT) g.environment = (int) i;
     ds.ready = true;
     return B2VP_OK;
 }
@@ -801,7 +810,10 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
     /* volpathmis runs on the one-thread-per-stream kernel only: its control flow (no direct-light
        march, path weights as p / f ratios) is not scheduled by the queue kernel yet */
-    const bool mis = s->desc.integrator.mis != 0;
+    bool mis = s->desc.integrator.mis != 0;
+    /* an environment emitter (constant.cpp) changes what happens when a ray escapes and makes emitter sampling
+       non-delta (MIS): handled by the one-thread-per-stream kernel, not by the queue kernel yet */
+    for (const B2vpEmitter &e : s->emitters) mis = mis || e.type == B2VP_EMITTER_CONSTANT;
     if (mis) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
     if (const char *e = mis ? nullptr : std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }

@@ -48,9 +48,10 @@ template <typename F> struct PathCtx {
                                              DirSample<F> &ds) {
         F transmittance = 1;
         F sx = next_1d(active);
-        (void) next_1d(active);
+        F sy = next_1d(active);
         F emitter_val;
-        ds = sample_emitter_direction(sv, sx, emitter_val);
+        ds = sv.g->environment >= 0 ? sample_emitter_direction_env(sv, sx, sy, emitter_val)
+                                    : sample_emitter_direction(sv, sx, emitter_val);
         if (ds.pdf == 0) emitter_val = 0;
         active = active && ds.pdf != 0;
         if (!active)
@@ -169,7 +170,14 @@ template <typename F> struct PathCtx {
             needs_intersection = needs_intersection && !intersect;
             active_surface = active_surface || escaped_medium;
 
-            /* si.emitter(scene) (scene.h:244-253): no area emitter, no environment => nullptr */
+            /* si.emitter(scene) (interaction.h:571-596): the environment when nothing was hit (volpath.cpp:429-438;
+               Scene::pdf_emitter_direction, scene.cpp:221-235, over constant.cpp:106-110) */
+            if (sv.g->environment >= 0 && !si.valid() && active_surface) {
+                emitter_val = sv.emitters[sv.g->environment].irradiance;
+                emitter_pdf = K<F>::InvFourPi;
+                if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) sv.g->n_emitters);
+                active = false; active_surface = false; active_medium = false;
+            }
 
             active_surface = active_surface && si.valid() && !active_medium;
             if (active_surface) {
@@ -432,7 +440,7 @@ template <typename F> struct PathCtx {
     /* VolumetricPathIntegrator::sample (volpath.cpp:38-257) */
     __device__ F sample(Ray<F> ray, int initial_medium, bool &valid_ray_out) {
         bool active = true;
-        bool valid_ray = false; /* !hide_emitters && environment: no environment emitter in scope */
+        bool valid_ray = !hide_emitters && sv.g->environment >= 0; /* volpath.cpp:51 */
         F eta = 1, throughput = 1, result = 0;
         int medium = initial_medium;
         MediumHit<F> mi;
@@ -527,7 +535,9 @@ template <typename F> struct PathCtx {
             bool intersect = active_surface && needs_intersection;
             if (intersect) ray_intersect(sv, ray, si, cnt);
 
-            /* emitter hit (volpath.cpp:186-191): shapes carry no emitters, no environment */
+            /* emitter hit (volpath.cpp:186-191): the environment when the ray escaped; shapes carry no emitters */
+            if (active_surface && specular_chain && sv.g->environment >= 0 && !si.valid())
+                result += throughput * sv.emitters[sv.g->environment].irradiance;
 
             active_surface = active_surface && si.valid();
             if (active_surface) {

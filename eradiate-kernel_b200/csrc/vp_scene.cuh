@@ -910,6 +910,40 @@ template <typename F> VP_D DirSample<F> sample_emitter_direction(const SceneView
     return ds;
 }
 
+/* The same with an environment emitter in the scene (ConstantBackgroundEmitter::sample_direction,
+   src/emitters/constant.cpp:81-104): needs the second sample and the rescaling of the first (scene.cpp:190).
+   Used by the one-thread-per-stream kernel, the only one that renders scenes with an environment. */
+template <typename F> VP_D DirSample<F> sample_emitter_direction_env(const SceneView<F> &sv, F sx, F sy, F &spec) {
+    DirSample<F> ds;
+    ds.d = mk3<F>(0, 0, 0); ds.dist = 0; ds.pdf = 0; ds.delta = false;
+    spec = 0;
+    int n = sv.g->n_emitters;
+    if (n == 0) return ds;
+    int index = 0;
+    F emitter_pdf = 1;
+    if (n > 1) {
+        emitter_pdf = (F) 1 / (F) n;
+        uint32_t idx = (uint32_t) (sx * (F) n);
+        index = (int) (idx < (uint32_t) (n - 1) ? idx : (uint32_t) (n - 1));
+        sx = (sx - (F) index * emitter_pdf) * (F) n;
+    }
+    const DEmitter<F> &e = sv.emitters[index];
+    ds.dist = (F) 2 * sv.g->bs_radius;
+    if (e.type == 1) {
+        ds.d = square_to_uniform_sphere(sx, sy);
+        ds.pdf = K<F>::InvFourPi;
+        ds.delta = false;
+        spec = e.irradiance / ds.pdf;
+    } else {
+        ds.d = -ld3(e.dir);
+        ds.pdf = 1;
+        ds.delta = true;
+        spec = e.irradiance;
+    }
+    if (n > 1) { ds.pdf *= emitter_pdf; spec *= rcp_(emitter_pdf); }
+    return ds;
+}
+
 /* ------------------------------------------------------------------ sensors */
 template <typename F> VP_D F rect_area(const DShape<F> &sh) { return norm(cross(ld3(sh.fs), ld3(sh.ft))); }
 

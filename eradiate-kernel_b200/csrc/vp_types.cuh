@@ -232,7 +232,7 @@ template <typename F> struct DPhase {
     int child[2];                    /* blendphase: indices of the nested phase functions */
     F integral, normalization, interval_size, inv_interval_size;
 };
-template <typename F> struct DEmitter { F dir[3]; F irradiance; };
+template <typename F> struct DEmitter { F dir[3]; F irradiance; int type, pad[3]; };   /* type 1: constant (environment), `irradiance` = radiance */
 template <typename F> struct DVolume {
     int type, filter, wrap, channels;
     int nx, ny, nz, smem_offset;     /* smem_offset: byte offset of the staged grid, or -1 */
@@ -299,6 +299,7 @@ template <typename F> struct DScene {
     uint32_t max_depth, rr_depth;
     int hide_emitters, ltr;
     int film_ch, mis;               /* film channels per pixel: 5, or 11 under a `moment` integrator; volpathmis */
+    int environment, pad_env;       /* index of the environment emitter (Scene::environment()) or -1 */
     /* small tables packed in one blob so a CTA can stage them in shared memory */
     const unsigned char *blob;
     uint32_t blob_bytes;

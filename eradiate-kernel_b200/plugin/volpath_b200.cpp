@@ -76,6 +76,7 @@
 #include <phase/tabphase.cpp>
 #include <phase/blendphase.cpp>
 #include <emitters/directional.cpp>
+#include <emitters/constant.cpp>
 #include <sensors/distant.cpp>
 #define RayTargetType MultiDistantRayTargetType   /* distant.cpp and mdistant.cpp both define this enum */
 #include <sensors/mdistant.cpp>
@@ -305,6 +306,13 @@ template <typename Float, typename Spectrum> struct B200Describe {
     }
 
     void emitter(const Emitter *e) {
+        if (cname(e) == "ConstantBackgroundEmitter") { /* the environment (constant.cpp:35-40) */
+            B2vpEmitter o{};
+            o.type = B2VP_EMITTER_CONSTANT;
+            o.irradiance = texture_value(static_cast<const ConstantBackgroundEmitter<Float, Spectrum> *>(e)->m_radiance.get());
+            t.emitters.push_back(o);
+            return;
+        }
         if (cname(e) != "DirectionalEmitter") unsupported("emitter " + cname(e));
         auto *d = static_cast<const DirectionalEmitter<Float, Spectrum> *>(e);
         B2vpEmitter o{};
@@ -396,7 +404,6 @@ template <typename Float, typename Spectrum> struct B200Describe {
         t.desc.precision = std::is_same_v<ScalarFloat, double> ? B2VP_PREC_F64 : B2VP_PREC_F32;
         for (auto &s : sc->shapes()) shape(s.get());
         for (auto &e : sc->emitters()) emitter(e.get());
-        if (sc->environment()) unsupported("environment emitters");
         sensor(sn);
         /* Scene::bbox() and the padded bounding sphere of distant.cpp:292-297 / directional.cpp:68-73 */
         ScalarBoundingBox3f bbox = sc->bbox();

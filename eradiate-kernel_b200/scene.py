@@ -440,6 +440,15 @@ class _Builder:
 
     def emitter(self, node):
         """src/emitters/directional.cpp:45-73"""
+        if node["type"] == "constant":  # src/emitters/constant.cpp:35-40
+            e = abi.Emitter()
+            e.type = abi.EMITTER_CONSTANT
+            rad = node.get("radiance", 1.0)
+            if isinstance(rad, dict):
+                rad = rad.get("value", 1.0)
+            e.irradiance = float(self.prop(rad))
+            self.emitters.append(e)
+            return
         if node["type"] != "directional":
             raise RuntimeError("emitter plugin %r is not supported by the B200 volpath" % node["type"])
         e = abi.Emitter()
@@ -658,7 +667,7 @@ def load_dict(d, variant="scalar_mono"):
             v = dict(v)
             v.setdefault("id", k)
             b.shape(v)
-        elif t == "directional":
+        elif t in ("directional", "constant"):
             emitters.append(v)
         elif t in ("distant", "mdistant", "radiancemeter", "mradiancemeter", "distantflux"):
             if sensor_node is not None:

@@ -61,7 +61,9 @@ enum { B2VP_VOLUME_CONST = 0, B2VP_VOLUME_GRID = 1 };
 enum { B2VP_FILTER_NEAREST = 0, B2VP_FILTER_TRILINEAR = 1 };
 enum { B2VP_WRAP_REPEAT = 0, B2VP_WRAP_MIRROR = 1, B2VP_WRAP_CLAMP = 2 };
 enum { B2VP_PHASE_ISOTROPIC = 0, B2VP_PHASE_RAYLEIGH = 1, B2VP_PHASE_HG = 2, B2VP_PHASE_TABULATED = 3, B2VP_PHASE_BLEND = 4 };
-enum { B2VP_EMITTER_DIRECTIONAL = 0 };
+/* CONSTANT: src/emitters/constant.cpp, the environment emitter (at most one per scene, scene.cpp:40-47):
+   `irradiance` holds its radiance, `direction` is unused */
+enum { B2VP_EMITTER_DIRECTIONAL = 0, B2VP_EMITTER_CONSTANT = 1 };
 enum {
     B2VP_SENSOR_DISTANT        = 0, /* src/sensors/distant.cpp        */
     B2VP_SENSOR_MDISTANT       = 1, /* src/sensors/mdistant.cpp       */

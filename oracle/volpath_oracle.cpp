@@ -370,6 +370,7 @@ template <typename F> struct TabDistr {
 
 template <typename F> struct OScene {
     std::vector<TabDistr<F>> tabs;   /* one per phase function (empty unless tabulated) */
+    int environment = -1;            /* index of the environment emitter (Scene::environment()), or -1 */
     std::vector<OShape<F>> shapes;
     std::vector<B2vpBsdf> bsdfs;
     std::vector<OMedium<F>> media;
@@ -409,6 +410,12 @@ template <typename F> bool build_scene(const B2vpSceneDesc *d, OScene<F> &s) {
             s.tabs[i].build(d->phases[i].values, d->phases[i].n_values);
         }
     s.emitters.assign(d->emitters, d->emitters + d->n_emitters);
+    for (uint32_t i = 0; i < d->n_emitters; ++i)
+        if (d->emitters[i].type == B2VP_EMITTER_CONSTANT) {
+            if (s.environment >= 0) { g_error = "Only one environment emitter can be specified per scene."; return false; }
+            s.environment = (int) i;
+        }
+    if (s.environment >= 0 && d->integrator.mis) { g_error = "volpathmis with an environment emitter is not supported"; return false; }
     for (uint32_t i = 0; i < d->n_volumes; ++i) {
         const B2vpVolume &a = d->volumes[i];
         OVolume<F> o;
@@ -1016,7 +1023,7 @@ template <typename F> struct DirectionSample { V3<F> d{ 0, 0, 0 }; F dist = 0, p
 /* Scene::sample_emitter_direction (scene.cpp:168-218) over
    DirectionalEmitter::sample_direction (directional.cpp:108-135) */
 template <typename F>
-DirectionSample<F> sample_emitter_direction(const OScene<F> &s, F sx, F /*sy*/, F &spec) {
+DirectionSample<F> sample_emitter_direction(const OScene<F> &s, F sx, F sy, F &spec) {
     DirectionSample<F> ds;
     spec = 0;
     size_t n = s.emitters.size();
@@ -1026,11 +1033,20 @@ DirectionSample<F> sample_emitter_direction(const OScene<F> &s, F sx, F /*sy*/, 
     if (n > 1) {
         emitter_pdf = (F) 1 / (F) n;
         index = std::min((size_t) (uint32_t) (sx * (F) n), n - 1);
+        sx = (sx - (F) index * emitter_pdf) * (F) n; /* rescale sample.x() to [0, 1) again (scene.cpp:190) */
     }
     const B2vpEmitter &e = s.emitters[index];
-    V3<F> d = ld3<F>(e.direction);
-    ds.d = -d; ds.dist = (F) 2 * s.bs_radius; ds.pdf = 1; ds.delta = true;
-    spec = (F) e.irradiance;
+    if (e.type == B2VP_EMITTER_CONSTANT) { /* ConstantBackgroundEmitter::sample_direction (constant.cpp:81-104) */
+        ds.d = square_to_uniform_sphere(sx, sy);
+        ds.dist = (F) 2 * s.bs_radius;
+        ds.pdf = Consts<F>::InvFourPi;  /* square_to_uniform_sphere_pdf (warp.h:272-279, no domain test) */
+        ds.delta = false;
+        spec = (F) e.irradiance / ds.pdf;
+    } else {
+        V3<F> d = ld3<F>(e.direction);
+        ds.d = -d; ds.dist = (F) 2 * s.bs_radius; ds.pdf = 1; ds.delta = true;
+        spec = (F) e.irradiance;
+    }
     if (n > 1) { ds.pdf *= emitter_pdf; spec *= rcp_(emitter_pdf); }
     return ds;
 }
@@ -1277,7 +1293,15 @@ template <typename F> struct Integrator {
             needs_intersection = needs_intersection && !intersect;
             active_surface = active_surface || escaped_medium;
 
-            /* si.emitter(scene): no area emitters and no environment in scope => nullptr */
+            /* si.emitter(scene) (interaction.h:571-596): the environment when nothing was hit; no area emitters */
+            bool emitter_hit = scene.environment >= 0 && !si.is_valid() && active_surface;
+            if (emitter_hit) { /* volpath.cpp:429-438 */
+                emitter_val = (F) scene.emitters[scene.environment].irradiance;
+                /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
+                emitter_pdf = Consts<F>::InvFourPi;
+                if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) scene.emitters.size());
+                active = false; active_surface = false; active_medium = false;
+            }
 
             active_surface = active_surface && si.is_valid() && !active_medium;
             if (active_surface)
@@ -1530,7 +1554,7 @@ template <typename F> struct Integrator {
 
     /* volpath.cpp:38-257 */
     F sample(Ray<F> ray, int initial_medium, bool active, bool &valid_ray_out) {
-        bool valid_ray = false; /* !hide_emitters && environment != nullptr: no environment in scope */
+        bool valid_ray = !hide_emitters && scene.environment >= 0; /* volpath.cpp:51 */
         F eta = 1, throughput = 1, result = 0;
         int medium = initial_medium;
         MediumInteraction<F> mi;
@@ -1628,7 +1652,9 @@ template <typename F> struct Integrator {
             bool intersect = active_surface && needs_intersection;
             if (intersect) si = ray_intersect(scene, ray, cnt);
 
-            /* emitter hit (186-191): shapes carry no emitters, no environment */
+            /* emitter hit (186-191): the environment when the ray escaped; shapes carry no emitters */
+            if (active_surface && specular_chain && scene.environment >= 0 && !si.is_valid())
+                result += throughput * (F) scene.emitters[scene.environment].irradiance;
 
             active_surface = active_surface && si.is_valid();
             if (active_surface) {

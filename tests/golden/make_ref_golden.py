@@ -206,6 +206,15 @@ def _mis(d, **props):
     return d
 
 
+def _sky(d, radiance, sun=True):
+    """The scene under a `constant` environment emitter (src/emitters/constant.cpp), with or without
+    the sun: emitter sampling becomes non-delta (MIS with the BSDF), escaping rays see the sky."""
+    d["sky"] = {"type": "constant", "radiance": radiance}
+    if not sun:
+        del d["sun"]
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -278,6 +287,11 @@ CASES = {
     "c1_volpathmis_f64": (lambda v: _mis(scenes.c1(spp=1024, variant=v)), "scalar_mono_double"),
     "c2_volpathmis_f64": (lambda v: _mis(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono_double"),
     "c3_volpathmis_f64": (lambda v: _mis(_c3(spp=1, variant=v, n=16, size=16)), "scalar_mono_double"),
+    "c2_sky": (lambda v: _sky(scenes.c2(spp=1, variant=v, width=256), 0.25), "scalar_mono"),
+    "c2_sky_only": (lambda v: _sky(scenes.c2(spp=1, variant=v, width=256), 1.0, sun=False), "scalar_mono"),
+    "c5_sky": (lambda v: _sky(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB), 0.5), "scalar_mono"),
+    "c2_sky_f64": (lambda v: _sky(scenes.c2(spp=1, variant=v, width=128), 0.25), "scalar_mono_double"),
+    "c3_sky_f64": (lambda v: _sky(_c3(spp=1, variant=v, n=16, size=16), 0.25, sun=False), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

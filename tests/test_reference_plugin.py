@@ -58,7 +58,7 @@ def test_plugin_describe_against_reference_films(pkg, oracle, name):
 def test_plugin_rejects_content_outside_the_scope(pkg):
     ref_xml = ref_xml_or_skip()
     d, variant = make_ref_golden.scene_dict("c2_paths")
-    d["sky"] = {"type": "constant", "radiance": 1.0}   # an environment emitter (not built yet)
+    d["sensor"]["film"]["rfilter"] = {"type": "gaussian"}   # a reconstruction filter wider than a pixel
     with pytest.raises(RuntimeError, match="outside the scope"):
         ref_xml.render(ref_xml.with_plugin(d), variant, write_vol=pkg.scene.write_vol, describe_oracle=True)
 
