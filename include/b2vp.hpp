@@ -171,6 +171,8 @@ struct Rpv { double rho_0 = 0.1, k = 0.1, g = 0.0, rho_c = -1.0; };
 struct Bilambertian { double reflectance = 0.5, transmittance = 0.5; };
 /* src/emitters/directional.cpp:45-73 */
 struct Directional { std::array<double, 3> direction{ 0, 0, 1 }; double irradiance = 1.0; };
+/* src/emitters/constant.cpp:35-40: the environment emitter */
+struct Constant { double radiance = 1.0; };
 /* src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp */
 struct HdrFilm { int width = 768, height = 576; };
 struct IndependentSampler { uint32_t sample_count = 4; uint64_t seed = 0; };
@@ -329,6 +331,11 @@ public:
         }
         for (auto &t : T) f.insert(f.end(), t, t + 3);
         return add_mesh(p, f, bsdf, interior, exterior, &n, &uv);
+    }
+    void add_emitter(const Constant &e) {
+        B2vpEmitter o{};
+        o.type = B2VP_EMITTER_CONSTANT; o.irradiance = (double) prop(e.radiance);
+        sc_->emitters.push_back(o);
     }
     void add_emitter(const Directional &e) {
         Vec3<F> d = prop_dir(e.direction);
