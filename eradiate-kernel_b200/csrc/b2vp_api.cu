@@ -245,7 +245,6 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         int n_env = 0;
         for (uint32_t i = 0; i < d->n_emitters; ++i) n_env += d->emitters[i].type == B2VP_EMITTER_CONSTANT;
         if (n_env > 1) return fail(B2VP_ERR_INVALID, "Only one environment emitter can be specified per scene.");
-        if (n_env && d->integrator.mis) return fail(B2VP_ERR_UNSUPPORTED, "volpathmis with an environment emitter is not supported");
     }
     const B2vpSensor &sn = d->sensor;
     if (sn.type < 0 || sn.type > B2VP_SENSOR_IRRADIANCEMETER)

@@ -193,8 +193,8 @@ template <typename F> struct PathCtx {
     }
 
     /* ================= VolpathMisIntegratorImpl (src/integrators/volpathmis.cpp), mono ==================
-       WeightMatrix is 1 x 1 in mono.  p_over_f_nee of the main loop is not carried: it is read only when a path
-       hits an emitter (volpathmis.cpp:253-268), and no area / environment emitter is in scope. */
+       WeightMatrix is 1 x 1 in mono.  p_over_f_nee of the main loop is read when a path hits an emitter
+       (volpathmis.cpp:253-268): here, when it escapes to the environment emitter. */
     VP_D static void update_weights(F &p_over_f, F p, F f, bool active) { /* volpathmis.cpp:447-465 */
         F ratio = p / f;
         ratio = finite_(ratio) ? ratio : (F) 0;
@@ -209,9 +209,10 @@ template <typename F> struct PathCtx {
                                                  bool active, DirSample<F> &ds, F &p_over_f_nee, F &p_over_f_uni) {
         p_over_f_nee = p_over_f; p_over_f_uni = p_over_f;
         F sx = next_1d(active);
-        (void) next_1d(active);
+        F sy = next_1d(active);
         F weight;
-        ds = sample_emitter_direction(sv, sx, weight);
+        ds = sv.g->environment >= 0 ? sample_emitter_direction_env(sv, sx, sy, weight)
+                                    : sample_emitter_direction(sv, sx, weight);
         F emitter_val = weight * ds.pdf;
         if (ds.pdf == 0) emitter_val = 0;
         active = active && ds.pdf != 0;
@@ -295,14 +296,14 @@ template <typename F> struct PathCtx {
     /* volpathmis.cpp:91-329 */
     VP_D F sample_mis(Ray<F> ray, int initial_medium, bool &valid_ray_out) {
         bool active = true;
-        bool valid_ray = false; /* !hide_emitters && environment != nullptr: no environment in scope */
+        bool valid_ray = !hide_emitters && sv.g->environment >= 0; /* volpathmis.cpp:100 */
         F eta = 1, result = 0;
         int medium = initial_medium;
         MediumHit<F> mi;
         mi.t = inf_<F>();
         bool specular_chain = active && !hide_emitters;
         uint32_t depth = 0;
-        F p_over_f = 1;
+        F p_over_f = 1, p_over_f_nee = 1;
         SurfaceHit<F> si;
         si.t = inf_<F>(); si.shape = -1;
         bool needs_intersection = true;
@@ -339,6 +340,7 @@ template <typename F> struct PathCtx {
                     F tr = exp_(-t * mi.combined);
                     F free_flight_pdf = si.t < mi.t ? tr : tr * mi.combined;
                     update_weights(p_over_f, free_flight_pdf, tr, true);
+                    update_weights(p_over_f_nee, free_flight_pdf, tr, true);
                 }
                 escaped_medium = !mi.valid();
                 active_medium = mi.valid();
@@ -358,8 +360,14 @@ template <typename F> struct PathCtx {
                 specular_chain = specular_chain && !(act_medium_scatter && sample_emitters);
                 if (act_null_scatter) {
                     cnt.n_null++;
-                    if (is_spectral) update_weights(p_over_f, mi.sigma_n / mi.combined, mi.sigma_n, true);
-                    if (not_spectral) update_weights(p_over_f, mi.sigma_n, mi.sigma_n, true);
+                    if (is_spectral) {
+                        update_weights(p_over_f, mi.sigma_n / mi.combined, mi.sigma_n, true);
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n, true);
+                    }
+                    if (not_spectral) {
+                        update_weights(p_over_f, mi.sigma_n, mi.sigma_n, true);
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n / mi.combined, true);
+                    }
                     ray.o = mi.p; ray.mint = 0;
                     si.t = si.t - mi.t;
                 }
@@ -377,6 +385,7 @@ template <typename F> struct PathCtx {
                         update_weights(uni_end, ds.delta ? (F) 0 : phase_val, phase_val, true);
                         result += mis_weight2(nee_end, uni_end) * emitted;
                     }
+                    p_over_f_nee = p_over_f;
                     F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> wo = phase_sample_at(sv, sv.phases[m.phase], mi.p, ray.d, s1, s2x, s2y);
@@ -386,13 +395,24 @@ template <typename F> struct PathCtx {
                     ray.mint = 0;
                     needs_intersection = true;
                     update_weights(p_over_f, phase_pdf, phase_pdf, true);
+                    update_weights(p_over_f_nee, (F) 1, phase_pdf, true);
                 }
             }
 
             active_surface = active_surface || escaped_medium;
             bool intersect = active_surface && needs_intersection;
             if (intersect) ray_intersect(sv, ray, si, cnt);
-            /* emitter hit (252-268): shapes carry no emitters, no environment */
+            /* emitter hit (252-268): the environment when the ray escaped; shapes carry no emitters */
+            if (active_surface && sv.g->environment >= 0 && !si.valid() && !(depth == 0 && hide_emitters)) {
+                bool count_direct = depth == 0 || specular_chain;
+                if (!count_direct) { /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
+                    F emitter_pdf = K<F>::InvFourPi;
+                    if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) sv.g->n_emitters);
+                    update_weights(p_over_f_nee, emitter_pdf, (F) 1, true);
+                }
+                F emitted = sv.emitters[sv.g->environment].irradiance;
+                result += (count_direct ? mis_weight1(p_over_f) : mis_weight2(p_over_f, p_over_f_nee)) * emitted;
+            }
             active_surface = active_surface && si.valid();
             if (active_surface) {
                 cnt.n_surface++;
@@ -428,7 +448,9 @@ template <typename F> struct PathCtx {
                 specular_chain = specular_chain || (non_null_bsdf && (sampled_type & BF_Delta) != 0);
                 specular_chain = specular_chain && !(active_surface && (sampled_type & BF_Smooth) != 0);
                 if (non_null_bsdf) depth += 1;
+                if (non_null_bsdf) p_over_f_nee = p_over_f;
                 update_weights(p_over_f, bs_pdf, bsdf_weight * bs_pdf, active_surface);
+                update_weights(p_over_f_nee, (F) 1, bsdf_weight * bs_pdf, non_null_bsdf);
                 if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
             }
             active = active && (active_surface || active_medium);

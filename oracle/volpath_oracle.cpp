@@ -415,7 +415,7 @@ template <typename F> bool build_scene(const B2vpSceneDesc *d, OScene<F> &s) {
             if (s.environment >= 0) { g_error = "Only one environment emitter can be specified per scene."; return false; }
             s.environment = (int) i;
         }
-    if (s.environment >= 0 && d->integrator.mis) { g_error = "volpathmis with an environment emitter is not supported"; return false; }
+
     for (uint32_t i = 0; i < d->n_volumes; ++i) {
         const B2vpVolume &a = d->volumes[i];
         OVolume<F> o;
@@ -1316,8 +1316,8 @@ template <typename F> struct Integrator {
     }
 
     /* ================= VolpathMisIntegratorImpl (src/integrators/volpathmis.cpp), mono ==================
-       WeightMatrix is 1 x 1 in mono.  p_over_f_nee of the main loop is not carried: it is read only when a path
-       hits an emitter (volpathmis.cpp:253-268), and no area / environment emitter is in scope. */
+       WeightMatrix is 1 x 1 in mono.  p_over_f_nee of the main loop is read when a path hits an emitter
+       (volpathmis.cpp:253-268): here, when it escapes to the environment emitter. */
     static void update_weights(F &p_over_f, F p, F f, bool active) { /* volpathmis.cpp:447-465 */
         F ratio = p / f;
         ratio = std::isfinite(ratio) ? ratio : (F) 0;
@@ -1414,13 +1414,13 @@ template <typename F> struct Integrator {
 
     /* volpathmis.cpp:91-329 */
     F sample_mis(Ray<F> ray, int initial_medium, bool active, bool &valid_ray_out) {
-        bool valid_ray = false; /* !hide_emitters && environment != nullptr: no environment in scope */
+        bool valid_ray = !hide_emitters && scene.environment >= 0; /* volpathmis.cpp:100 */
         F eta = 1, result = 0;
         int medium = initial_medium;
         MediumInteraction<F> mi;
         bool specular_chain = active && !hide_emitters;
         uint32_t depth = 0;
-        F p_over_f = 1;
+        F p_over_f = 1, p_over_f_nee = 1;
         SurfaceInteraction<F> si;
         bool needs_intersection = true;
         for (int bounce = 0;; ++bounce) {
@@ -1456,6 +1456,7 @@ template <typename F> struct Integrator {
                     F tr = exp_(-t * mi.combined_extinction);
                     F free_flight_pdf = si.t < mi.t ? tr : tr * mi.combined_extinction;
                     update_weights(p_over_f, free_flight_pdf, tr, true);
+                    update_weights(p_over_f_nee, free_flight_pdf, tr, true);
                 }
                 escaped_medium = !mi.is_valid();
                 active_medium = mi.is_valid();
@@ -1475,8 +1476,14 @@ template <typename F> struct Integrator {
                 specular_chain = specular_chain && !(act_medium_scatter && sample_emitters);
                 if (act_null_scatter) {
                     cnt.n_null++;
-                    if (is_spectral) update_weights(p_over_f, mi.sigma_n / mi.combined_extinction, mi.sigma_n, true);
-                    if (not_spectral) update_weights(p_over_f, mi.sigma_n, mi.sigma_n, true);
+                    if (is_spectral) {
+                        update_weights(p_over_f, mi.sigma_n / mi.combined_extinction, mi.sigma_n, true);
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n, true);
+                    }
+                    if (not_spectral) {
+                        update_weights(p_over_f, mi.sigma_n, mi.sigma_n, true);
+                        update_weights(p_over_f_nee, (F) 1, mi.sigma_n / mi.combined_extinction, true);
+                    }
                     ray.o = mi.p; ray.mint = 0;
                     si.t = si.t - mi.t;
                 }
@@ -1494,6 +1501,7 @@ template <typename F> struct Integrator {
                         update_weights(uni_end, ds.delta ? (F) 0 : phase_val, phase_val, true);
                         result += mis_weight2(nee_end, uni_end) * emitted;
                     }
+                    p_over_f_nee = p_over_f;
                     F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> wo = phase_sample_at(scene, m.phase, mi, s1, s2x, s2y);
@@ -1503,13 +1511,24 @@ template <typename F> struct Integrator {
                     ray.mint = 0;
                     needs_intersection = true;
                     update_weights(p_over_f, phase_pdf, phase_pdf, true);
+                    update_weights(p_over_f_nee, (F) 1, phase_pdf, true);
                 }
             }
 
             active_surface = active_surface || escaped_medium;
             bool intersect = active_surface && needs_intersection;
             if (intersect) si = ray_intersect(scene, ray, cnt);
-            /* emitter hit (252-268): shapes carry no emitters, no environment */
+            /* emitter hit (252-268): the environment when the ray escaped; shapes carry no emitters */
+            if (active_surface && scene.environment >= 0 && !si.is_valid() && !(depth == 0 && hide_emitters)) {
+                bool count_direct = depth == 0 || specular_chain;
+                if (!count_direct) { /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
+                    F emitter_pdf = Consts<F>::InvFourPi;
+                    if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) scene.emitters.size());
+                    update_weights(p_over_f_nee, emitter_pdf, (F) 1, true);
+                }
+                F emitted = (F) scene.emitters[scene.environment].irradiance;
+                result += (count_direct ? mis_weight1(p_over_f) : mis_weight2(p_over_f, p_over_f_nee)) * emitted;
+            }
             active_surface = active_surface && si.is_valid();
             if (active_surface) {
                 cnt.n_surface++;
@@ -1543,7 +1562,9 @@ template <typename F> struct Integrator {
                 specular_chain = specular_chain || (non_null_bsdf && (bs.sampled_type & F_Delta) != 0);
                 specular_chain = specular_chain && !(active_surface && (bs.sampled_type & F_Smooth) != 0);
                 if (non_null_bsdf) depth += 1;
+                if (non_null_bsdf) p_over_f_nee = p_over_f;
                 update_weights(p_over_f, bs.pdf, bsdf_weight * bs.pdf, active_surface);
+                update_weights(p_over_f_nee, (F) 1, bsdf_weight * bs.pdf, non_null_bsdf);
                 if (active_surface && is_medium_transition(si)) medium = target_medium(si, ray.d);
             }
             active = active && (active_surface || active_medium);

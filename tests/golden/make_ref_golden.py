@@ -292,6 +292,9 @@ CASES = {
     "c5_sky": (lambda v: _sky(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256, leaf_bsdf=_BILAMB), 0.5), "scalar_mono"),
     "c2_sky_f64": (lambda v: _sky(scenes.c2(spp=1, variant=v, width=128), 0.25), "scalar_mono_double"),
     "c3_sky_f64": (lambda v: _sky(_c3(spp=1, variant=v, n=16, size=16), 0.25, sun=False), "scalar_mono_double"),
+    "c2_sky_volpathmis": (lambda v: _mis(_sky(scenes.c2(spp=1, variant=v, width=256), 0.25)), "scalar_mono"),
+    "c5_sky_volpathmis": (lambda v: _mis(_sky(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256), 0.5, sun=False)), "scalar_mono"),
+    "c2_sky_volpathmis_f64": (lambda v: _mis(_sky(scenes.c2(spp=1, variant=v, width=128), 1.0, sun=False)), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

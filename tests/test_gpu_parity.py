@@ -19,6 +19,7 @@ CASES = {
     "c3_small": lambda v: scenes.c3(spp=2, variant=v, n=32, size=16),
     "c5_small": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64),
     "c2_tabphase": lambda v: _tabphase(v),
+    "c2_sky_volpathmis": lambda v: _mis(_sky(scenes.c2(spp=8, variant=v, width=64), 0.25)),
     "c2_sky": lambda v: _sky(scenes.c2(spp=8, variant=v, width=64), 0.25),
     "c5_sky_only": lambda v: _sky(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64), 0.5, sun=False),
     "c2_volpathmis": lambda v: _mis(scenes.c2(spp=8, variant=v, width=64)),
