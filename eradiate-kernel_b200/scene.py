@@ -9,6 +9,7 @@ scalar_mono_double).  Content outside SURVEY.md section 8 raises, like an unknow
 plugin name does in the reference.
 """
 import ctypes as C
+import os
 import struct
 
 import numpy as np
@@ -88,6 +89,100 @@ def read_obj(path, flip_tex_coords=True):
     if vts:
         uv = np.array([vts[k[1] - 1] if k[1] else [0, 0] for k in order], dtype=np.float32).reshape(-1, 2)
     return pos, np.array(tris, dtype=np.uint32).reshape(-1, 3), nrm, uv
+
+
+_PLY_TYPES = {"char": "i1", "int8": "i1", "uchar": "u1", "uint8": "u1", "short": "i2", "int16": "i2",
+              "ushort": "u2", "uint16": "u2", "int": "i4", "int32": "i4", "uint": "u4", "uint32": "u4",
+              "float": "f4", "float32": "f4", "double": "f8", "float64": "f8"}
+
+
+def read_ply(path):
+    """Stanford PLY as src/shapes/ply.cpp:102-380 reads it: ascii or binary (either byte order); element `vertex`
+    with x y z, optional nx ny nz and texture coordinates (u v / texture_u texture_v / s t); element `face` with a
+    `vertex_index(es)` list of exactly three indices per face (anything else is "incompatible contents -- is this a
+    triangle mesh?"); other elements and properties are skipped.  Returns (positions, faces, normals or None,
+    texcoords or None) as float32 / uint32, positions and normals still in object space."""
+    def fail(msg):
+        raise RuntimeError('Error while loading PLY file "%s": %s!' % (os.path.basename(path), msg))
+    with open(path, "rb") as f:
+        raw = f.read()
+    end = raw.find(b"end_header")
+    if not raw.startswith(b"ply") or end < 0:
+        fail("invalid PLY header")
+    nl = raw.index(b"\n", end) + 1
+    fmt, elements = None, []
+    for line in raw[:end].decode("ascii", "replace").splitlines()[1:]:
+        tok = line.split()
+        if not tok or tok[0] in ("comment", "obj_info"):
+            continue
+        if tok[0] == "format":
+            fmt = tok[1]
+        elif tok[0] == "element":
+            elements.append({"name": tok[1], "count": int(tok[2]), "props": []})
+        elif tok[0] == "property":
+            if tok[1] == "list":
+                elements[-1]["props"].append((tok[4], "list", _PLY_TYPES[tok[2]], _PLY_TYPES[tok[3]]))
+            else:
+                elements[-1]["props"].append((tok[2], _PLY_TYPES[tok[1]]))
+    if fmt not in ("ascii", "binary_little_endian", "binary_big_endian"):
+        fail("invalid PLY format")
+    order = ">" if fmt == "binary_big_endian" else "<"
+    pos = faces = nrm = uv = None
+    off = nl
+    words = raw[nl:].split() if fmt == "ascii" else None
+    wi = 0
+    for el in elements:
+        n, props = el["count"], el["props"]
+        has_list = any(p[1] == "list" for p in props)
+        if has_list and not (el["name"] == "face" and len([p for p in props if p[1] == "list"]) == 1):
+            fail("unsupported list property in element '%s'" % el["name"])
+        if has_list:   # every list must hold exactly three entries: then the records are fixed-size
+            fields = []
+            for p in props:
+                if p[1] == "list":
+                    fields += [(p[0] + ".count", p[2]), (p[0], p[3], (3,))]
+                else:
+                    fields.append((p[0], p[1]))
+        else:
+            fields = [(p[0], p[1]) for p in props]
+        if fmt == "ascii":
+            per = sum(int(np.prod(fl[2])) if len(fl) > 2 else 1 for fl in fields)
+            vals = np.array(words[wi:wi + n * per], dtype=np.float64).reshape(n, per) if n else np.zeros((0, per))
+            wi += n * per
+            rec, c = {}, 0
+            for fl in fields:
+                k = int(np.prod(fl[2])) if len(fl) > 2 else 1
+                rec[fl[0]] = vals[:, c] if k == 1 else vals[:, c:c + k]
+                c += k
+        else:
+            dt = np.dtype([(fl[0], order + fl[1]) + ((fl[2],) if len(fl) > 2 else ()) for fl in fields])
+            if off + n * dt.itemsize > len(raw):
+                fail("file is truncated")
+            arr = np.frombuffer(raw, dtype=dt, count=n, offset=off)
+            off += n * dt.itemsize
+            rec = {name: arr[name] for name in dt.names}
+        if el["name"] == "vertex":
+            if not all(k in rec for k in "xyz"):
+                fail("vertex positions not found")
+            pos = np.stack([rec["x"], rec["y"], rec["z"]], axis=1).astype(np.float32)
+            if all(k in rec for k in ("nx", "ny", "nz")):
+                nrm = np.stack([rec["nx"], rec["ny"], rec["nz"]], axis=1).astype(np.float32)
+            for a, b in (("u", "v"), ("texture_u", "texture_v"), ("s", "t")):
+                if a in rec and b in rec:
+                    uv = np.stack([rec[a], rec[b]], axis=1).astype(np.float32)
+                    break
+        elif el["name"] == "face":
+            name = "vertex_index" if "vertex_index" in rec else "vertex_indices" if "vertex_indices" in rec else None
+            if name is None:
+                fail("vertex_index/vertex_indices property not found")
+            if n and not (np.asarray(rec[name + ".count"]) == 3).all():
+                fail("incompatible contents -- is this a triangle mesh?")
+            faces = np.asarray(rec[name]).astype(np.uint32).reshape(-1, 3)
+    if fmt != "ascii" and off != len(raw):
+        fail("invalid file -- trailing content")
+    if pos is None or faces is None:
+        fail("vertex / face element not found")
+    return pos, faces, nrm, uv
 
 
 class _Builder:
@@ -406,11 +501,14 @@ class _Builder:
             if node.get("flip_normals", False):
                 n = -n
             self.add_mesh(s, p, tris, n, uvs)
-        elif t == "obj":  # src/shapes/obj.cpp
-            pos, faces, nrm, uv = read_obj(node["filename"], bool(node.get("flip_tex_coords", True)))
+        elif t in ("obj", "ply"):  # src/shapes/obj.cpp, src/shapes/ply.cpp
+            if t == "obj":
+                pos, faces, nrm, uv = read_obj(node["filename"], bool(node.get("flip_tex_coords", True)))
+            else:
+                pos, faces, nrm, uv = read_ply(node["filename"])
             face_normals = bool(node.get("face_normals", False))  # mesh.cpp:30-31: no vertex normals at all
             if nrm is None and not face_normals:
-                raise RuntimeError("obj: files without normals need face_normals=true (smooth vertex normals, "
+                raise RuntimeError("mesh files without normals need face_normals=true (smooth vertex normals, "
                                    "Mesh::recompute_vertex_normals, are not built in the B200 volpath)")
             if face_normals:
                 nrm = None
@@ -650,7 +748,7 @@ def load_dict(d, variant="scalar_mono"):
     b = _Builder(variant)
     sensor_node = integrator_node = None
     emitters = []
-    shape_kinds = ("rectangle", "sphere", "cube", "mesh", "obj")
+    shape_kinds = ("rectangle", "sphere", "cube", "mesh", "obj", "ply")
     # children are visited in key order, as Properties::objects() does (std::map)
     items = [(k, v) for k, v in sorted(d.items()) if isinstance(v, dict)]
     # first pass: named media / bsdfs so that references resolve regardless of order

@@ -17,6 +17,7 @@
 #include <mitsuba/core/argparser.h>
 #include <mitsuba/core/filesystem.h>
 #include <mitsuba/core/fresolver.h>
+#include <mitsuba/core/jit.h>
 #include <mitsuba/core/logger.h>
 #include <mitsuba/core/thread.h>
 #include <mitsuba/core/timer.h>
@@ -130,6 +131,7 @@ int main(int argc, char **argv) {
         fprintf(stderr, "usage: refprobe <variant> <scene.xml> <out.bin> [-t threads] [-r repeats] [-Dk=v ...]\n");
         return 2;
     }
+    Jit::static_initialization();
     Class::static_initialization();
     Thread::static_initialization();
     Logger::static_initialization();
@@ -178,5 +180,6 @@ int main(int argc, char **argv) {
     Logger::static_shutdown();
     Thread::static_shutdown();
     Class::static_shutdown();
+    Jit::static_shutdown();
     return rc;
 }

@@ -160,8 +160,8 @@ class _Writer:
     def shape(self, v, ident):
         t = v["type"]
         out = []
-        if t == "obj":
-            out.append('<shape type="obj" id="%s"><string name="filename" value="%s"/>' % (ident, v["filename"]))
+        if t in ("obj", "ply"):
+            out.append('<shape type="%s" id="%s"><string name="filename" value="%s"/>' % (t, ident, v["filename"]))
             if "face_normals" in v:
                 out.append('<boolean name="face_normals" value="%s"/>' % ("true" if v["face_normals"] else "false"))
         elif t == "mesh":
@@ -265,7 +265,7 @@ class _Writer:
         return "".join(out)
 
 
-SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj")
+SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj", "ply")
 MEDIA = ("homogeneous", "heterogeneous")
 BSDFS = ("diffuse", "rpv", "null", "bilambertian")
 SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter", "distantflux")

@@ -215,6 +215,17 @@ def _sky(d, radiance, sun=True):
     return d
 
 
+def _c2_ply(name, face_normals, **kw):
+    """C2 with a PLY mesh (tests/golden/data/roof_bin.ply: binary, normals, s/t texcoords; roof_ascii.ply: ascii,
+    positions only), loaded by the reference's ply plugin on one side and by scene.read_ply on the other."""
+    d = scenes.c2(**kw)
+    T = scenes.T
+    d["roof"] = {"type": "ply", "filename": os.path.join(HERE, "data", name), "face_normals": face_normals,
+                 "to_world": T.translate([0.25, -0.5, 0.125], np.float32) @ T.scale([2.0, 1.5, 1.0], np.float32),
+                 "bsdf": {"type": "diffuse", "reflectance": 0.75}}
+    return d
+
+
 _MU = np.linspace(-1, 1, 181)
 TAB_AEROSOL = ((1 - 0.49) / (1 + 0.49 - 1.4 * _MU) ** 1.5 + 0.3 * np.exp(-((_MU + 1) / 0.1) ** 2)).tolist()
 TAB_COARSE = [0.0, 0.0, 1.0, 0.5, 2.0]   # an interval without probability mass, a flat-to-linear mix
@@ -295,6 +306,9 @@ CASES = {
     "c2_sky_volpathmis": (lambda v: _mis(_sky(scenes.c2(spp=1, variant=v, width=256), 0.25)), "scalar_mono"),
     "c5_sky_volpathmis": (lambda v: _mis(_sky(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256), 0.5, sun=False)), "scalar_mono"),
     "c2_sky_volpathmis_f64": (lambda v: _mis(_sky(scenes.c2(spp=1, variant=v, width=128), 1.0, sun=False)), "scalar_mono_double"),
+    "c2_ply_binary": (lambda v: _c2_ply("roof_bin.ply", False, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_ply_ascii": (lambda v: _c2_ply("roof_ascii.ply", True, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_ply_binary_f64": (lambda v: _c2_ply("roof_bin.ply", False, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
