@@ -42,7 +42,8 @@ def config(spp, n_gpus, extra=None):
                      "1x1x1000 (trilinear, exp profile, tau=0.5), rayleigh, rpv, distant %dx1 film, volpath "
                      "max_depth=-1 rr_depth=5, scalar_mono (fp32)" % WIDTH,
          "spp_per_gpu": spp, "paths_per_step": WIDTH * spp * n_gpus, "seeding": "wavefront (sampler.cpp:89-92)",
-         "sharding": "disjoint stream ranges per GPU + one NCCL film reduce" if n_gpus > 1 else "single GPU",
+         "sharding": "interleaved stream blocks (every GPU renders spp of the spp x N samples of every pixel) + one NCCL "
+                     "film reduce" if n_gpus > 1 else "single GPU",
          "l2": "flushed between steps (256 MiB write); the 4 KB grid is staged in shared memory"}
     if extra:
         c.update(extra)
@@ -210,7 +211,9 @@ def run_ours(args):
     spp_total = args.spp * n_gpus
     scene = pkg.load_dict(workload(spp_total))
     per_gpu = WIDTH * args.spp
-    first = rank * per_gpu
+    # every rank renders `spp` of the spp * N samples of EVERY pixel (interleaved blocks, dist.shard_interleaved):
+    # contiguous ranges would give each rank its own pixels, i.e. its own mix of path lengths (10 % imbalance at N=8)
+    shard = pkg.shard_interleaved(spp_total, WIDTH, rank, world) if world > 1 else {"first_stream": 0, "n_streams": per_gpu}
     ds = pkg.DeviceScene(scene, device=local)
     film = torch.zeros((1, WIDTH, 5), dtype=torch.float32, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -222,8 +225,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step():
-        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, first_stream=first, n_streams=per_gpu,
-                      device_film=film.data_ptr(), clear=True, stream=stream)
+        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, device_film=film.data_ptr(), clear=True, stream=stream, **shard)
         if world > 1:
             dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
         return r.totals
@@ -272,7 +274,7 @@ def run_ours(args):
         barrier()
         t0 = time.perf_counter()
         with pkg.DeviceScene(scene, device=local) as ds2:
-            r = ds2.render(seed_mode=abi.SEED_WAVEFRONT, first_stream=first, n_streams=per_gpu, film=host_film * 0)
+            r = ds2.render(seed_mode=abi.SEED_WAVEFRONT, film=host_film * 0, **shard)
             if world > 1:
                 f = torch.from_numpy(r.film).cuda()
                 dist.reduce(f, dst=0, op=dist.ReduceOp.SUM)

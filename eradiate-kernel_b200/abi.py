@@ -132,6 +132,7 @@ class RenderArgs(C.Structure):
         ("abi_version", c_u32), ("struct_size", c_u32), ("precision", c_i32), ("seed_mode", c_i32),
         ("device", c_i32), ("film_on_device", c_i32), ("cuda_stream", C.c_void_p),
         ("first_stream", c_u64), ("n_streams", c_u64),
+        ("interleave_block", c_u64), ("interleave_count", c_u32), ("interleave_index", c_u32),
         ("explicit_state", C.POINTER(c_u64)), ("explicit_inc", C.POINTER(c_u64)),
         ("explicit_pixel", C.POINTER(c_u32)), ("explicit_samples_per_stream", c_u32), ("clear_film", c_u32),
         ("out_state", C.POINTER(c_u64)), ("out_counters", C.POINTER(PathCounters)),

@@ -729,7 +729,16 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     uint64_t first = a->first_stream;
     uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
     if (a->seed_mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
-    if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+    sp.d.il_block = 0; sp.d.il_count = 1; sp.d.il_index = 0;
+    if (a->interleave_block) {
+        if (a->seed_mode == B2VP_SEED_EXPLICIT || !a->n_streams || !a->interleave_count ||
+            a->interleave_index >= a->interleave_count)
+            return fail(B2VP_ERR_INVALID, "invalid interleaved stream range");
+        const uint64_t B = a->interleave_block, kmax = count - 1;
+        const uint64_t last = first + ((kmax / B) * a->interleave_count + a->interleave_index) * B + kmax % B;
+        if (last >= sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+        sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
+    } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
     if (a->seed_mode == B2VP_SEED_EXPLICIT && count &&
         (!a->explicit_state || !a->explicit_inc || !a->explicit_pixel))
         return fail(B2VP_ERR_INVALID, "explicit seeding needs state, inc and pixel arrays");

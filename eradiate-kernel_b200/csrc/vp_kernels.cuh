@@ -159,7 +159,7 @@ volpath_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStr
     for (;;) {
         unsigned long long k = atomicAdd(out.work_counter, 1ull);
         if (k >= sp.count) break;
-        StreamInfo st = make_stream(sp, sp.first + k);
+        StreamInfo st = make_stream(sp, stream_index(sp, k));
         Pcg32 rng;
         rng.state = st.state; rng.inc = st.inc; rng.draws = 0;
         PathCounters cnt;

@@ -312,6 +312,8 @@ template <typename F> struct DScene {
 struct DStreams {
     int mode;
     uint64_t first, count;          /* range rendered by this launch */
+    uint64_t il_block;              /* > 0: interleaved blocks (B2vpRenderArgs::interleave_*) */
+    uint32_t il_count, il_index;
     uint32_t samples_per_stream, spp_pass, n_passes, bs;
     uint32_t n_blocks;
     const SpiralBlockD *blocks;
@@ -320,6 +322,12 @@ struct DStreams {
     const uint64_t *ex_state, *ex_inc;
     const uint32_t *ex_pixel;
 };
+
+/* global stream index of the k-th stream of a launch */
+VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
+    if (sp.il_block == 0) return sp.first + k;
+    return sp.first + ((k / sp.il_block) * sp.il_count + sp.il_index) * sp.il_block + k % sp.il_block;
+}
 
 struct PathCounters { uint32_t draws, medium_steps, n_null, n_real, n_intersect, n_surface; };
 

@@ -449,7 +449,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                     if (k >= sp.count) {
                         state = L_DONE;
                     } else {
-                        st = make_stream(sp, sp.first + k);
+                        st = make_stream(sp, stream_index(sp, k));
                         rng.state = st.state; rng.inc = st.inc; rng.draws = 0;
                         cnt.draws = 0; cnt.medium_steps = 0; cnt.n_null = 0; cnt.n_real = 0;
                         cnt.n_intersect = 0; cnt.n_surface = 0;

@@ -77,7 +77,7 @@ class DeviceScene:
     def cancel(self):
         abi.lib().b2vp_cancel(self._h)
 
-    def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None,
+    def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None, interleave=None,
                want_paths=False, film=None, stream=None, device_film=None, clear=True):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
         `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film)."""
@@ -89,6 +89,8 @@ class DeviceScene:
         a.precision, a.seed_mode, a.device = prec, seed_mode, self.device
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
+        if interleave is not None:   # (block, count, index): B2vpRenderArgs::interleave_*
+            a.interleave_block, a.interleave_count, a.interleave_index = interleave
         keep = []
         if seed_mode == abi.SEED_EXPLICIT:
             st, inc, pix, per = explicit

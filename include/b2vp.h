@@ -291,6 +291,13 @@ typedef struct B2vpRenderArgs {
        across GPUs = disjoint ranges + one film sum-reduce.   */
     uint64_t first_stream;
     uint64_t n_streams;         /* 0 => all remaining                          */
+    /* Interleaved sharding (many small ranges per GPU instead of one, against tail imbalance):
+       with interleave_block = B > 0 the k-th stream of this call, k in [0, n_streams), is the global stream
+       first_stream + ((k / B) * interleave_count + interleave_index) * B + k % B, i.e. the call renders every
+       interleave_count-th block of B streams, starting with block interleave_index.  n_streams must be given.
+       B = samples per pixel and GPU, count = GPUs, index = rank: every GPU renders its share of EVERY pixel. */
+    uint64_t interleave_block;
+    uint32_t interleave_count, interleave_index;
 
     /* B2VP_SEED_EXPLICIT only: per-stream start state, increment and pixel.   */
     const uint64_t *explicit_state;

@@ -44,7 +44,8 @@ def lib():
     return _lib
 
 
-def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, explicit=None, want_paths=False):
+def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, explicit=None, want_paths=False,
+           interleave=None):
     """Same contract as eradiate_kernel_b200.DeviceScene.render, computed by the CPU oracle.
     `pkg` is the loaded product package (for its ctypes struct definitions only)."""
     abi = pkg.abi
@@ -55,6 +56,8 @@ def render(pkg, scene, seed_mode, precision=None, first_stream=0, n_streams=0, e
     a.abi_version, a.struct_size = abi.ABI_VERSION, C.sizeof(abi.RenderArgs)
     a.precision, a.seed_mode = prec, seed_mode
     a.first_stream, a.n_streams = first_stream, n_streams
+    if interleave is not None:
+        a.interleave_block, a.interleave_count, a.interleave_index = interleave
     keep = []
     if seed_mode == abi.SEED_EXPLICIT:
         st, inc, pix, per = explicit

@@ -1848,7 +1848,15 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
     uint64_t first = a->first_stream;
     uint64_t count = a->n_streams ? a->n_streams : sp.n_streams - first;
     if (sp.mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
-    if (first + count > sp.n_streams) { g_error = "stream range out of bounds"; return B2VP_ERR_INVALID; }
+    const uint64_t il_block = a->interleave_block;
+    auto stream_index = [&](uint64_t k) -> uint64_t { /* B2vpRenderArgs::interleave_* */
+        if (!il_block) return first + k;
+        return first + ((k / il_block) * a->interleave_count + a->interleave_index) * il_block + k % il_block;
+    };
+    if (il_block && (!a->n_streams || !a->interleave_count || a->interleave_index >= a->interleave_count ||
+                     sp.mode == B2VP_SEED_EXPLICIT)) { g_error = "invalid interleaved stream range"; return B2VP_ERR_INVALID; }
+    if (count && stream_index(count - 1) >= sp.n_streams) { g_error = "stream range out of bounds"; return B2VP_ERR_INVALID; }
+    if (!il_block && first + count > sp.n_streams) { g_error = "stream range out of bounds"; return B2VP_ERR_INVALID; }
 
     const int C = d->integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS;
     const size_t film_n = (size_t) sp.w * sp.h * C;
@@ -1859,7 +1867,7 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
     uint32_t max_depth = d->integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d->integrator.max_depth;
 
     for (uint64_t k = 0; k < count; ++k) {
-        Stream st = make_stream(sp, a, first + k);
+        Stream st = make_stream(sp, a, stream_index(k));
         PCG32 rng; rng.state = st.state; rng.inc = st.inc;
         Counters cnt;
         F acc[B2VP_FILM_CHANNELS_MOMENT] = { 0 };

@@ -24,6 +24,12 @@ r = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, first_stream=first, n_streams
 film = pkg.reduce_film(r.film.astype(np.float64))
 if rank == 0:
     np.save(os.path.join(%(out)r, "film.npy"), film)
+# the same render sharded by interleaved blocks: every rank renders 3 of the 6 samples of every pixel
+r = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, **pkg.shard_interleaved(6, 8, rank, world))
+assert (r.film[..., 4] == 3).all()
+film = pkg.reduce_film(r.film.astype(np.float64))
+if rank == 0:
+    np.save(os.path.join(%(out)r, "film_interleaved.npy"), film)
 dist.destroy_process_group()
 '''
 
@@ -38,6 +44,9 @@ def test_two_rank_sharded_render_matches_single(pkg, oracle, tmp_path):
     film = np.load(tmp_path / "film.npy")
     sc = pkg.load_dict(scenes.c2(spp=6, width=8, nz=50))
     full = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT)
+    assert np.allclose(film, full.film, rtol=1e-5, atol=1e-7)
+    assert film[..., 4].sum() == 48
+    film = np.load(tmp_path / "film_interleaved.npy")
     assert np.allclose(film, full.film, rtol=1e-5, atol=1e-7)
     assert film[..., 4].sum() == 48
 

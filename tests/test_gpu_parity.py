@@ -172,6 +172,24 @@ def test_stream_ranges_partition(pkg, oracle):
         assert np.allclose(acc.film, full.film, rtol=2e-4, atol=1e-6)
 
 
+def test_interleaved_ranges_partition(pkg, oracle, kernel):
+    """Interleaved sharding (B2vpRenderArgs::interleave_*): three ranks, each a third of every pixel's samples; the
+    films add up to the full render, every rank's paths are bit-exact against the oracle."""
+    sc = pkg.load_dict(scenes.c2(spp=12, width=24))
+    with pkg.DeviceScene(sc) as ds:
+        full = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT)
+        acc = np.zeros_like(full.film)
+        for rank in range(3):
+            kw = pkg.shard_interleaved(12, 24, rank, 3)
+            got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
+            ref = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
+            assert np.array_equal(got.state, ref.state) and np.array_equal(got.radiance, ref.radiance)
+            assert np.array_equal(got.counters, ref.counters)
+            assert (got.film[..., 4] == 4).all()
+            acc += got.film
+        assert np.allclose(acc, full.film, rtol=2e-4, atol=1e-6)
+
+
 def test_scene_update_matches_fresh_scene(pkg, oracle):
     d = scenes.c2(spp=8, width=16)
     sc = pkg.load_dict(d)
