@@ -367,6 +367,12 @@ def main():
     ap.add_argument("--profile", action="store_true", help="kernel-only run for ncu: no e2e leg, no CPU baseline")
     ap.add_argument("--spp", type=int, default=16384, help="samples per pixel per GPU (BASELINE: 2^14)")
     args = ap.parse_args()
+    # ONE JSON line on stdout: native libraries that write to file descriptor 1 themselves (NCCL prints its version
+    # banner there at N>1) are sent to stderr; Python's own stdout keeps the real one
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args)
     else:

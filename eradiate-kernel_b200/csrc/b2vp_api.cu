@@ -709,6 +709,14 @@ constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_A
 template <typename F, int MAXT>
 void (*pick_queue_kernel(uint32_t ft, const char **name))(const DScene<F>, const DStreams, const RenderOut<F>) {
     if (std::getenv("B2VP_GENERIC")) ft = FT_ALL;
+    /* interleaved launches (multi-GPU sharding): the two scene classes the benchmarks shard have an instance with
+       the interleaved stream mapping, everything else goes to the generic instance */
+    if (ft & FT_INTERLEAVE) {
+        if ((ft & ~(PRE_HET | FT_INTERLEAVE)) == 0) { *name = "heterogeneous, interleaved"; return volpath_q_kernel<F, MAXT, PRE_HET | FT_INTERLEAVE>; }
+        if ((ft & ~(PRE_HET_ALB | FT_INTERLEAVE)) == 0) { *name = "heterogeneous+albedo grid, interleaved"; return volpath_q_kernel<F, MAXT, PRE_HET_ALB | FT_INTERLEAVE>; }
+        *name = "generic";
+        return volpath_q_kernel<F, MAXT, FT_ALL>;
+    }
     if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return volpath_q_kernel<F, MAXT, PRE_HOMOG>; }
     if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return volpath_q_kernel<F, MAXT, PRE_HET>; }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return volpath_q_kernel<F, MAXT, PRE_HET_ALB>; }
@@ -808,7 +816,8 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
        (vp_wavefront.cuh), B2VP_KERNEL=mega the one-thread-per-path twin (vp_kernels.cuh): same results. */
     typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
     const char *preset = "";
-    Kern kern = pick_queue_kernel<F, 512>(ds.g.features, &preset);
+    const uint32_t launch_features = ds.g.features | (sp.d.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
+    Kern kern = pick_queue_kernel<F, 512>(launch_features, &preset);
     int threads = 512;
     bool queue_kernel = true;
     /* path slots per thread.  With everything hot on chip the shared memory left sets the pool size (the more
@@ -826,7 +835,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     if (const char *e = mis ? nullptr : std::getenv("B2VP_KERNEL")) {
         if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
         else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
-        else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(ds.g.features, &preset); threads = 256; }
+        else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(launch_features, &preset); threads = 256; }
         else if (!std::strcmp(e, "q384")) { threads = 384; }
 #ifdef B2VP_EXPERIMENT
         else if (!std::strcmp(e, "q768")) { kern = volpath_q_kernel<F, 768, PRE_HET_ALB>; threads = 768; }

@@ -695,7 +695,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 uint32_t j = c.j;
                 int px = 0, py = 0, box = 0, boy = 0, bsx = 0, bsy = 0;
                 bool empty = true;
-                if (fl & QF_HAVE_STREAM) stream_pixel(sp, stream_index(sp, k), px, py, box, boy, bsx, bsy, empty);
+                if (fl & QF_HAVE_STREAM) stream_pixel(sp, stream_index<(FEAT & FT_INTERLEAVE) != 0>(sp, k), px, py, box, boy, bsx, bsy, empty);
                 if (state == Q_PATH_END) {
                     /* render_sample tail (integrator.cpp:267-287) + ImageBlock::put (imageblock.cpp:85-169) */
                     F value = c.ray_weight * c.result;
@@ -754,7 +754,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     if (k >= sp.count) {
                         state = Q_DEAD;
                     } else {
-                        StreamInfo st = make_stream(sp, stream_index(sp, k));
+                        StreamInfo st = make_stream(sp, stream_index<(FEAT & FT_INTERLEAVE) != 0>(sp, k));
                         c.k = k;
                         s.rng_state = st.state; s.rng_inc = st.inc; s.rng_draws = 0;
                         s.c_steps = 0; s.c_null = 0; c.c_real = 0; c.c_isect = 0; c.c_surf = 0;

@@ -58,7 +58,8 @@ enum : uint32_t {
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
     FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter       */
-    FT_ALL = 0xffffu
+    FT_INTERLEAVE = 1u << 16,  /* the launch renders interleaved stream blocks (multi-GPU) */
+    FT_ALL = 0x1ffffu
 };
 
 

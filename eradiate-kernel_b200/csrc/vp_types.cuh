@@ -323,9 +323,10 @@ struct DStreams {
     const uint32_t *ex_pixel;
 };
 
-/* global stream index of the k-th stream of a launch */
-VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
-    if (sp.il_block == 0) return sp.first + k;
+/* global stream index of the k-th stream of a launch; IL = false compiles the interleaved mapping (two 64-bit
+   divisions) out of kernel instances that are never launched with it */
+template <bool IL = true> VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
+    if (!IL || sp.il_block == 0) return sp.first + k;
     return sp.first + ((k / sp.il_block) * sp.il_count + sp.il_index) * sp.il_block + k % sp.il_block;
 }
 
