@@ -11,6 +11,7 @@ plugin name does in the reference.
 import ctypes as C
 import os
 import struct
+import zlib
 
 import numpy as np
 
@@ -48,6 +49,87 @@ def write_vol(path, data, bbox=(0, 0, 0, 1, 1, 1)):
         f.write(struct.pack("<5i", 1, nx, ny, nz, ch))
         f.write(struct.pack("<6f", *bbox))
         f.write(data.tobytes())
+
+
+_SER_HEADER, _SER_NORMALS, _SER_TEXCOORDS, _SER_COLORS, _SER_DOUBLE = 0x041C, 0x0001, 0x0002, 0x0008, 0x2000
+
+
+def read_serialized(path, shape_index=0):
+    """One mesh of a `.serialized` container as src/shapes/serialized.cpp:174-340 reads it.  Little endian; every
+    sub-mesh is [u16 0x041C][u16 version 3|4] followed by a zlib stream of: u32 flags, (v4) a NUL-terminated name,
+    u64 vertex count, u64 face count, positions, [normals], [texcoords], [colours, skipped], u32 face indices;
+    reals are float32 or (flag 0x2000) float64 narrowed to float32.  For shape_index > 0 the offset comes from the
+    dictionary at the end of the file (v4: u64 offsets, v3: u32 offsets, then a u32 count).  Returns (positions,
+    faces, normals or None, texcoords or None), positions and normals still in object space."""
+    def fail(msg):
+        raise RuntimeError('Error while loading serialized file "%s": %s!' % (os.path.basename(path), msg))
+    if not os.path.exists(path):
+        fail("file not found")
+    if shape_index < 0:
+        fail("shape index must be nonnegative!")
+    with open(path, "rb") as f:
+        raw = f.read()
+    fmt, version = struct.unpack_from("<HH", raw, 0)
+    if fmt != _SER_HEADER:
+        fail("encountered an invalid file format!")
+    if version not in (3, 4):
+        fail("encountered an incompatible file version!")
+    start = 0
+    if shape_index != 0:
+        (count,) = struct.unpack_from("<I", raw, len(raw) - 4)
+        if shape_index > count:
+            fail("Unable to unserialize mesh, shape index is out of range! (requested %d out of 0..%d)"
+                 % (shape_index, count - 1))
+        if version == 4:
+            (start,) = struct.unpack_from("<Q", raw, len(raw) - 8 * (count - shape_index) - 4)
+        else:
+            (start,) = struct.unpack_from("<I", raw, len(raw) - 4 * (count - shape_index + 1))
+    try:
+        data = zlib.decompressobj().decompress(raw[start + 4:])
+    except zlib.error as e:
+        fail("inflate(): %s" % e)
+    (flags,) = struct.unpack_from("<I", data, 0)
+    off = 4
+    if version == 4:
+        off = data.index(b"\0", off) + 1
+    n_vert, n_face = struct.unpack_from("<QQ", data, off)
+    off += 16
+    real = "<f8" if flags & _SER_DOUBLE else "<f4"
+
+    def reals(dim):
+        nonlocal off
+        a = np.frombuffer(data, real, n_vert * dim, off).reshape(n_vert, dim)
+        off += a.nbytes
+        return a.astype(np.float32)
+
+    pos = reals(3)
+    nrm = reals(3) if flags & _SER_NORMALS else None
+    uv = reals(2) if flags & _SER_TEXCOORDS else None
+    if flags & _SER_COLORS:
+        reals(3)
+    faces = np.frombuffer(data, "<u4", n_face * 3, off).reshape(n_face, 3).astype(np.uint32)
+    return pos, faces, nrm, uv
+
+
+def write_serialized(path, meshes, version=4, double=False):
+    """Writes meshes = [(name, positions, faces, normals or None, texcoords or None), ...] as one `.serialized`
+    container (the layout read_serialized documents), with the offset dictionary at the end."""
+    offsets, out = [], bytearray()
+    for name, pos, faces, nrm, uv in meshes:
+        offsets.append(len(out))
+        flags = (_SER_DOUBLE if double else 0x1000) | (_SER_NORMALS if nrm is not None else 0) \
+            | (_SER_TEXCOORDS if uv is not None else 0)
+        real = "<f8" if double else "<f4"
+        body = struct.pack("<I", flags) + (name.encode() + b"\0" if version == 4 else b"")
+        body += struct.pack("<QQ", len(pos), len(faces)) + np.asarray(pos, real).tobytes()
+        for a in (nrm, uv):
+            if a is not None:
+                body += np.asarray(a, real).tobytes()
+        body += np.asarray(faces, "<u4").tobytes()
+        out += struct.pack("<HH", _SER_HEADER, version) + zlib.compress(body)
+    out += b"".join(struct.pack("<Q" if version == 4 else "<I", o) for o in offsets) + struct.pack("<I", len(offsets))
+    with open(path, "wb") as f:
+        f.write(bytes(out))
 
 
 def read_obj(path, flip_tex_coords=True):
@@ -501,8 +583,10 @@ class _Builder:
             if node.get("flip_normals", False):
                 n = -n
             self.add_mesh(s, p, tris, n, uvs)
-        elif t in ("obj", "ply"):  # src/shapes/obj.cpp, src/shapes/ply.cpp
-            if t == "obj":
+        elif t in ("obj", "ply", "serialized"):  # src/shapes/obj.cpp, ply.cpp, serialized.cpp
+            if t == "serialized":
+                pos, faces, nrm, uv = read_serialized(node["filename"], int(node.get("shape_index", 0)))
+            elif t == "obj":
                 pos, faces, nrm, uv = read_obj(node["filename"], bool(node.get("flip_tex_coords", True)))
             else:
                 pos, faces, nrm, uv = read_ply(node["filename"])
@@ -748,7 +832,7 @@ def load_dict(d, variant="scalar_mono"):
     b = _Builder(variant)
     sensor_node = integrator_node = None
     emitters = []
-    shape_kinds = ("rectangle", "sphere", "cube", "mesh", "obj", "ply")
+    shape_kinds = ("rectangle", "sphere", "cube", "mesh", "obj", "ply", "serialized")
     # children are visited in key order, as Properties::objects() does (std::map)
     items = [(k, v) for k, v in sorted(d.items()) if isinstance(v, dict)]
     # first pass: named media / bsdfs so that references resolve regardless of order

@@ -160,8 +160,10 @@ class _Writer:
     def shape(self, v, ident):
         t = v["type"]
         out = []
-        if t in ("obj", "ply"):
+        if t in ("obj", "ply", "serialized"):
             out.append('<shape type="%s" id="%s"><string name="filename" value="%s"/>' % (t, ident, v["filename"]))
+            if "shape_index" in v:
+                out.append('<integer name="shape_index" value="%d"/>' % v["shape_index"])
             if "face_normals" in v:
                 out.append('<boolean name="face_normals" value="%s"/>' % ("true" if v["face_normals"] else "false"))
         elif t == "mesh":
@@ -265,7 +267,7 @@ class _Writer:
         return "".join(out)
 
 
-SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj", "ply")
+SHAPES = ("rectangle", "sphere", "cube", "mesh", "obj", "ply", "serialized")
 MEDIA = ("homogeneous", "heterogeneous")
 BSDFS = ("diffuse", "rpv", "null", "bilambertian")
 SENSORS = ("distant", "mdistant", "radiancemeter", "mradiancemeter", "distantflux")
