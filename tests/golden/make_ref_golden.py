@@ -215,14 +215,18 @@ def _sky(d, radiance, sun=True):
     return d
 
 
-def _c2_ply(name, face_normals, **kw):
+def _c2_ply(name, face_normals, kind="ply", shape_index=None, **kw):
     """C2 with a PLY mesh (tests/golden/data/roof_bin.ply: binary, normals, s/t texcoords; roof_ascii.ply: ascii,
     positions only), loaded by the reference's ply plugin on one side and by scene.read_ply on the other."""
     d = scenes.c2(**kw)
     T = scenes.T
-    d["roof"] = {"type": "ply", "filename": os.path.join(HERE, "data", name), "face_normals": face_normals,
+    d["roof"] = {"type": kind, "filename": os.path.join(HERE, "data", name), "face_normals": face_normals,
                  "to_world": T.translate([0.25, -0.5, 0.125], np.float32) @ T.scale([2.0, 1.5, 1.0], np.float32),
                  "bsdf": {"type": "diffuse", "reflectance": 0.75}}
+    if shape_index is not None:
+        # the same mesh as sub-mesh 1 of a `.serialized` container (src/shapes/serialized.cpp; roof.serialized:
+        # version 4, float32, normals + texcoords; roof_v3_f64.serialized: version 3, float64, positions only)
+        d["roof"]["shape_index"] = shape_index
     return d
 
 
@@ -308,6 +312,8 @@ CASES = {
     "c2_sky_volpathmis_f64": (lambda v: _mis(_sky(scenes.c2(spp=1, variant=v, width=128), 1.0, sun=False)), "scalar_mono_double"),
     "c2_ply_binary": (lambda v: _c2_ply("roof_bin.ply", False, spp=1, variant=v, width=128), "scalar_mono"),
     "c2_ply_ascii": (lambda v: _c2_ply("roof_ascii.ply", True, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_serialized": (lambda v: _c2_ply("roof.serialized", False, "serialized", 1, spp=1, variant=v, width=128), "scalar_mono"),
+    "c2_serialized_v3": (lambda v: _c2_ply("roof_v3_f64.serialized", True, "serialized", 1, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c2_ply_binary_f64": (lambda v: _c2_ply("roof_bin.ply", False, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
@@ -331,14 +337,16 @@ def main():
     pkg = scenes.pkg
     if not ref_xml.available():
         ref_xml.build()
-    out = {}
-    for name in CASES:
+    path = os.path.join(HERE, "ref_golden.npz")
+    only = sys.argv[1:]   # names given: render those and keep the other films of the existing file
+    out = dict(np.load(path)) if only else {}
+    for name in (only or CASES):
         d, variant = scene_dict(name)
         film, sec = ref_xml.render(d, variant, threads=1, write_vol=pkg.scene.write_vol)
         out[name] = film
         print("%-18s %-20s %4d x %-4d mean %.7g  (%.3f s)" % (name, variant, film.shape[1], film.shape[0],
                                                              film[..., 1].sum() / film[..., 4].sum(), sec))
-    np.savez_compressed(os.path.join(HERE, "ref_golden.npz"), **out)
+    np.savez_compressed(path, **{k: out[k] for k in CASES})
     print("wrote", len(out), "reference films")
 
 

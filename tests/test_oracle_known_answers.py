@@ -1,5 +1,7 @@
 """Known-answer tests of the reference for sensors and shapes, restated against the oracle (CPU only).
 Each test cites the reference test it follows; the scene dictionaries are the reference's."""
+import os
+
 import numpy as np
 import pytest
 
@@ -143,3 +145,71 @@ def test_film_develop_pfm(pkg, tmp_path):
     assert raw.startswith(b"Pf\n3 2\n-1\n")
     data = np.frombuffer(raw[len(b"Pf\n3 2\n-1\n"):], dtype="<f4").reshape(2, 3)
     assert np.array_equal(data, np.array([[3, 4, 0], [0, 1, 2]], dtype=np.float32))
+
+
+# ---- `.serialized` mesh containers (src/shapes/serialized.cpp) -----------------------------------------
+def _roof(pkg):
+    return pkg.scene.read_ply(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "data", "roof_bin.ply"))
+
+
+@pytest.mark.parametrize("version,double", [(4, False), (4, True), (3, False), (3, True)])
+def test_serialized_round_trip(pkg, tmp_path, version, double):
+    """Every (container version, precision) pair, three sub-meshes, each reached through the offset dictionary."""
+    pos, faces, nrm, uv = _roof(pkg)
+    tri = (np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), np.array([[0, 1, 2]], np.uint32))
+    path = str(tmp_path / "m.serialized")
+    pkg.scene.write_serialized(path, [("a", tri[0], tri[1], None, None), ("roof", pos, faces, nrm, uv),
+                                      ("b", pos, faces, None, uv)], version=version, double=double)
+    p, f, n, t = pkg.scene.read_serialized(path, 1)
+    assert np.array_equal(p, pos) and np.array_equal(f, faces) and np.array_equal(n, nrm) and np.array_equal(t, uv)
+    p, f, n, t = pkg.scene.read_serialized(path, 2)
+    assert np.array_equal(p, pos) and n is None and np.array_equal(t, uv)
+    p, f, n, t = pkg.scene.read_serialized(path)   # shape_index 0: read from the start of the file
+    assert np.array_equal(p, tri[0]) and np.array_equal(f, tri[1]) and n is None and t is None
+    assert p.dtype == np.float32 and f.dtype == np.uint32
+
+
+def test_serialized_errors(pkg, tmp_path):
+    """The reference's failure cases (serialized.cpp:184-221): missing file, bad magic, bad version, bad index."""
+    rd = pkg.scene.read_serialized
+    with pytest.raises(RuntimeError, match="file not found"):
+        rd(str(tmp_path / "absent.serialized"))
+    path = str(tmp_path / "m.serialized")
+    pos, faces, nrm, uv = _roof(pkg)
+    pkg.scene.write_serialized(path, [("roof", pos, faces, nrm, uv)])
+    with pytest.raises(RuntimeError, match="shape index must be nonnegative"):
+        rd(path, -1)
+    with pytest.raises(RuntimeError, match="out of range"):
+        rd(path, 2)
+    raw = bytearray(open(path, "rb").read())
+    bad = str(tmp_path / "bad.serialized")
+    open(bad, "wb").write(bytes([0, 0]) + bytes(raw[2:]))
+    with pytest.raises(RuntimeError, match="invalid file format"):
+        rd(bad)
+    open(bad, "wb").write(bytes(raw[:2]) + bytes([5, 0]) + bytes(raw[4:]))
+    with pytest.raises(RuntimeError, match="incompatible file version"):
+        rd(bad)
+
+
+@pytest.mark.parametrize("features", ["normals", "uv", "normals_uv"])
+def test_serialized_reference_files(pkg, features):
+    """The reference's own test meshes and the values its test asserts (src/librender/tests/test_mesh.py:130-172,
+    test06_load_various_features).  The files live in the reference tree: skipped where that is absent."""
+    path = "/root/reference/resources/data/tests/serialized/rectangle_%s.serialized" % features
+    if not os.path.exists(path):
+        pytest.skip("reference tree not present")
+    pos, faces, nrm, uv = pkg.scene.read_serialized(path)
+    assert faces.shape == (2, 3)
+    assert np.allclose(pos[0], [-2.85, 0.0, -7.6], atol=1e-3)
+    assert np.allclose(pos[2], [2.85, 0.0, 0.599999], atol=1e-3)
+    assert np.allclose(pos[3], [2.85, 0.0, -7.6], atol=1e-3)
+    if "uv" in features:
+        assert np.allclose(uv[0], [0.950589, 1 - 0.988416], atol=1e-3)
+        assert np.allclose(uv[2], [0.025105, 1 - 0.689127], atol=1e-3)
+        assert np.allclose(uv[3], [0.950589, 1 - 0.689127], atol=1e-3)
+    else:
+        assert uv is None
+    if "normals" in features:
+        assert np.allclose(nrm[[0, 2, 3]], [0.0, 1.0, 0.0])
+    else:
+        assert nrm is None
