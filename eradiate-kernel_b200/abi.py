@@ -151,7 +151,7 @@ class ParamPatch(C.Structure):
 
 
 # every symbol include/b2vp.h declares
-EXPORTS = ["b2vp_stream_count", "b2vp_scene_create", "b2vp_scene_update", "b2vp_scene_destroy", "b2vp_render",
+EXPORTS = ["b2vp_stream_count", "b2vp_scene_create", "b2vp_scene_update", "b2vp_scene_update_grid", "b2vp_scene_destroy", "b2vp_render",
            "b2vp_cancel", "b2vp_last_error", "b2vp_abi_version", "b2vp_device_count", "b2vp_measure_fp32_peak"]
 
 _lib = None
@@ -179,6 +179,7 @@ def lib():
     L.b2vp_device_count.restype = C.c_int
     L.b2vp_scene_create.argtypes = [C.POINTER(SceneDesc), c_i32, C.POINTER(C.c_void_p)]
     L.b2vp_scene_update.argtypes = [C.c_void_p, C.POINTER(ParamPatch)]
+    L.b2vp_scene_update_grid.argtypes = [C.c_void_p, c_i32, C.POINTER(C.c_float), c_u64, c_i32]
     L.b2vp_scene_destroy.argtypes = [C.c_void_p]
     L.b2vp_scene_destroy.restype = None
     L.b2vp_render.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]

@@ -737,7 +737,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     uint64_t first = a->first_stream;
     uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
     if (a->seed_mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
-    sp.d.il_block = 0; sp.d.il_count = 1; sp.d.il_index = 0;
+    sp.d.il_block = 0; sp.d.il_count = 1; sp.d.il_index = 0; sp.d.il_shift = -1;
     if (a->interleave_block) {
         if (a->seed_mode == B2VP_SEED_EXPLICIT || !a->n_streams || !a->interleave_count ||
             a->interleave_index >= a->interleave_count)
@@ -746,6 +746,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         const uint64_t last = first + ((kmax / B) * a->interleave_count + a->interleave_index) * B + kmax % B;
         if (last >= sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
         sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
+        if ((B & (B - 1)) == 0) { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
     } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
     if (a->seed_mode == B2VP_SEED_EXPLICIT && count &&
         (!a->explicit_state || !a->explicit_inc || !a->explicit_pixel))
@@ -1032,6 +1033,56 @@ int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch) {
         if (patch->emitter >= 0) emitters[patch->emitter].irradiance = (F) patch->emitter_irradiance;
         if (patch->volume >= 0) volumes[patch->volume].value = (F) patch->volume_value;
         CU_CHECK(cudaMemcpy(ds.blob.p, b, ds.host_blob.size(), cudaMemcpyHostToDevice));
+        return B2VP_OK;
+    };
+    int rc = patch_dev(scene->dev32);
+    if (rc != B2VP_OK) return rc;
+    return patch_dev(scene->dev64);
+}
+
+int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *data, uint64_t n_values, int32_t keep_max) {
+    if (!scene || !data) return fail(B2VP_ERR_INVALID, "null argument");
+    if (volume < 0 || volume >= (int) scene->volumes.size())
+        return fail(B2VP_ERR_INVALID, "volume index out of range");
+    B2vpVolume &hv = scene->volumes[volume];
+    if (hv.type != B2VP_VOLUME_GRID) return fail(B2VP_ERR_INVALID, "grid update targets a constant volume");
+    std::vector<float> &held = scene->volume_data[volume];
+    if (n_values != held.size())   /* grid3d.cpp:373-383 also takes a doubled resolution; this path does not */
+        return fail(B2VP_ERR_UNSUPPORTED, "Unsupported GridVolume data size update: %llu -> %llu",
+                    (unsigned long long) held.size(), (unsigned long long) n_values);
+    held.assign(data, data + n_values);
+    if (!keep_max) {   /* grid3d.cpp:387-390: the maximum follows the data unless max_value was given */
+        float mx = held[0];
+        for (float x : held) mx = x > mx ? x : mx;
+        hv.max_value = mx;
+    }
+    CU_CHECK(cudaSetDevice(scene->device));
+    auto patch_dev = [&](auto &ds) -> int {
+        using F = decltype(ds.g.bs_radius);
+        if (!ds.ready) return B2VP_OK;
+        unsigned char *b = ds.host_blob.data();
+        auto *media = reinterpret_cast<DMedium<F> *>(b + ds.g.ofs_media);
+        auto *volumes = reinterpret_cast<DVolume<F> *>(b + ds.g.ofs_volumes);
+        DVolume<F> &v = volumes[volume];
+        if (sizeof(F) == sizeof(float)) {
+            CU_CHECK(cudaMemcpy((void *) v.data, held.data(), held.size() * sizeof(float), cudaMemcpyHostToDevice));
+        } else {
+            std::vector<F> wide(held.begin(), held.end());
+            CU_CHECK(cudaMemcpy((void *) v.data, wide.data(), wide.size() * sizeof(F), cudaMemcpyHostToDevice));
+        }
+        if (v.cells) {   /* the trilinear cell records are derived from the grid: rebuild them in place */
+            const size_t n_cells = (size_t) (v.nx + 1) * (v.ny + 1) * (v.nz + 1);
+            const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) scene->sm_count * 16);
+            build_cells_kernel<F><<<blocks, 256>>>(v.data, const_cast<F *>(v.cells), v.nx, v.ny, v.nz);
+            CU_CHECK(cudaGetLastError());
+        }
+        v.max_value = (F) hv.max_value;
+        for (size_t i = 0; i < scene->media.size(); ++i) {
+            DMedium<F> &m = media[i];
+            if (m.type == B2VP_MEDIUM_HETEROGENEOUS && m.sigma_t == volume) m.max_density = m.scale * v.max_value;
+        }
+        CU_CHECK(cudaMemcpy(ds.blob.p, b, ds.host_blob.size(), cudaMemcpyHostToDevice));
+        CU_CHECK(cudaDeviceSynchronize());
         return B2VP_OK;
     };
     int rc = patch_dev(scene->dev32);

@@ -314,6 +314,7 @@ struct DStreams {
     uint64_t first, count;          /* range rendered by this launch */
     uint64_t il_block;              /* > 0: interleaved blocks (B2vpRenderArgs::interleave_*) */
     uint32_t il_count, il_index;
+    int il_shift;                   /* log2(il_block) when that is a power of two (shift / mask instead of divisions), else -1 */
     uint32_t samples_per_stream, spp_pass, n_passes, bs;
     uint32_t n_blocks;
     const SpiralBlockD *blocks;
@@ -327,6 +328,8 @@ struct DStreams {
    divisions) out of kernel instances that are never launched with it */
 template <bool IL = true> VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
     if (!IL || sp.il_block == 0) return sp.first + k;
+    if (sp.il_shift >= 0)
+        return sp.first + ((((k >> sp.il_shift) * sp.il_count + sp.il_index) << sp.il_shift) | (k & (sp.il_block - 1)));
     return sp.first + ((k / sp.il_block) * sp.il_count + sp.il_index) * sp.il_block + k % sp.il_block;
 }
 

@@ -74,6 +74,14 @@ class DeviceScene:
         p.volume, p.volume_value = volume, volume_value
         abi.check(abi.lib().b2vp_scene_update(self._h, C.byref(p)))
 
+    def update_grid(self, volume, data, keep_max=False):
+        """New values data[z, y, x(, c)] for grid volume `volume` (index into Scene.volumes) of unchanged resolution:
+        what the reference does through traverse() -> "data" -> GridVolume::parameters_changed
+        (src/textures/grid3d.cpp:366-391).  The grid is overwritten on the device, nothing else is re-uploaded."""
+        arr = np.ascontiguousarray(data, dtype=np.float32).ravel()
+        abi.check(abi.lib().b2vp_scene_update_grid(self._h, int(volume), arr.ctypes.data_as(C.POINTER(C.c_float)),
+                                                   arr.size, int(bool(keep_max))))
+
     def cancel(self):
         abi.lib().b2vp_cancel(self._h)
 

@@ -334,6 +334,13 @@ int b2vp_stream_count(const b2vp_scene_t *scene, int32_t seed_mode,
 
 int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **out);
 int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch);
+/* New values for a grid volume of unchanged resolution (what GridVolume::parameters_changed handles after
+   traverse() hands out "data": src/textures/grid3d.cpp:366-391): the grid is overwritten in HBM, derived layouts
+   are rebuilt on the device, the maximum (and the majorant of every heterogeneous medium using the grid as
+   sigma_t) follows the data unless keep_max is set (the reference's fixed max_value).  n_values must equal
+   res[0]*res[1]*res[2]*channels.                                               */
+int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *data, uint64_t n_values,
+                           int32_t keep_max);
 void b2vp_scene_destroy(b2vp_scene_t *scene);
 
 /* Renders the stream range into `film` (crop_w*crop_h*5 reals, XYZAW

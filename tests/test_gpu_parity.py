@@ -172,20 +172,21 @@ def test_stream_ranges_partition(pkg, oracle):
         assert np.allclose(acc.film, full.film, rtol=2e-4, atol=1e-6)
 
 
-def test_interleaved_ranges_partition(pkg, oracle, kernel):
+@pytest.mark.parametrize("spp", [12, 18])   # blocks of 4 (shift / mask index map) and of 6 (divisions)
+def test_interleaved_ranges_partition(pkg, oracle, kernel, spp):
     """Interleaved sharding (B2vpRenderArgs::interleave_*): three ranks, each a third of every pixel's samples; the
     films add up to the full render, every rank's paths are bit-exact against the oracle."""
-    sc = pkg.load_dict(scenes.c2(spp=12, width=24))
+    sc = pkg.load_dict(scenes.c2(spp=spp, width=24))
     with pkg.DeviceScene(sc) as ds:
         full = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT)
         acc = np.zeros_like(full.film)
         for rank in range(3):
-            kw = pkg.shard_interleaved(12, 24, rank, 3)
+            kw = pkg.shard_interleaved(spp, 24, rank, 3)
             got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
             ref = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
             assert np.array_equal(got.state, ref.state) and np.array_equal(got.radiance, ref.radiance)
             assert np.array_equal(got.counters, ref.counters)
-            assert (got.film[..., 4] == 4).all()
+            assert (got.film[..., 4] == spp // 3).all()
             acc += got.film
         assert np.allclose(acc, full.film, rtol=2e-4, atol=1e-6)
 
@@ -204,6 +205,74 @@ def test_scene_update_matches_fresh_scene(pkg, oracle):
     assert sc2.desc.bsdfs[1].type == pkg.abi.BSDF_RPV
     ref = oracle.render(pkg, sc2, pkg.abi.SEED_WAVEFRONT, want_paths=True)
     assert np.array_equal(got.radiance, ref.radiance) and np.array_equal(got.state, ref.state)
+
+
+def test_grid_update_matches_fresh_scene(pkg, oracle):
+    """b2vp_scene_update_grid (the reference's traverse() -> "data" -> GridVolume::parameters_changed,
+    grid3d.cpp:366-391): new grid values in place == a scene built from those values.  Covers a grid staged in shared
+    memory (C2), a grid read from HBM through cell records with its paired albedo grid (C3, n = 40), both
+    precisions, the majorant following the data, and keep_max."""
+    for variant in ("scalar_mono", "scalar_mono_double"):
+        d = scenes.c2(spp=8, width=16, variant=variant)
+        g0 = np.asarray(d["atm"]["sigma_t"]["data"], np.float32)
+        g1 = (g0[::-1] * np.float32(1.75) + np.float32(0.125)).copy()     # other profile, other maximum
+        sc = pkg.load_dict(d, variant)
+        vol = sc.desc.media[0].sigma_t
+        with pkg.DeviceScene(sc) as ds:
+            ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT)
+            ds.update_grid(vol, g1)
+            got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True)
+            ds.update_grid(vol, g0)                                          # and back: the first film again
+            back = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        d["atm"]["sigma_t"]["data"] = g1
+        ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        assert np.array_equal(got.radiance, ref.radiance) and np.array_equal(got.state, ref.state), variant
+        d["atm"]["sigma_t"]["data"] = g0
+        ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        assert np.array_equal(back.radiance, ref.radiance), variant
+
+        d = scenes.c3(spp=2, variant=variant, n=40, size=12)
+        s0 = np.asarray(d["atm"]["sigma_t"]["data"], np.float32)
+        a0 = np.asarray(d["atm"]["albedo"]["data"], np.float32)
+        s1 = (s0.transpose(2, 1, 0) * np.float32(0.5)).copy()
+        a1 = (np.float32(1) - (np.float32(1) - a0) * np.float32(3)).clip(0, 1).astype(np.float32)
+        sc = pkg.load_dict(d, variant)
+        with pkg.DeviceScene(sc) as ds:
+            ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT)
+            m = sc.desc.media[0]
+            ds.update_grid(m.sigma_t, s1)
+            ds.update_grid(m.albedo, a1)
+            got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        d["atm"]["sigma_t"]["data"], d["atm"]["albedo"]["data"] = s1, a1
+        ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT, want_paths=True)
+        assert np.array_equal(got.radiance, ref.radiance) and np.array_equal(got.state, ref.state), variant
+
+    # keep_max: the majorant of the first grid stays (the reference's fixed max_value)
+    d = scenes.c2(spp=8, width=16)
+    g0 = np.asarray(d["atm"]["sigma_t"]["data"], np.float32)
+    g1 = (g0 * np.float32(0.5)).copy()
+    sc = pkg.load_dict(d)
+    with pkg.DeviceScene(sc) as ds:
+        ds.update_grid(sc.desc.media[0].sigma_t, g1, keep_max=True)
+        got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True)
+    d["atm"]["sigma_t"]["data"] = g1
+    d["atm"]["sigma_t"]["max_value"] = float(g0.max())
+    ref = oracle.render(pkg, pkg.load_dict(d), pkg.abi.SEED_WAVEFRONT, want_paths=True)
+    assert np.array_equal(got.radiance, ref.radiance)
+
+
+def test_grid_update_errors(pkg):
+    d = scenes.c2(spp=1, width=4)
+    sc = pkg.load_dict(d)
+    vol = sc.desc.media[0].sigma_t
+    with pkg.DeviceScene(sc) as ds:
+        g = np.asarray(d["atm"]["sigma_t"]["data"], np.float32)
+        with pytest.raises(pkg.abi.B2vpError, match="Unsupported GridVolume data size update"):
+            ds.update_grid(vol, g[:-1])
+        with pytest.raises(pkg.abi.B2vpError, match="constant volume"):
+            ds.update_grid(1 - vol, g)
+        with pytest.raises(pkg.abi.B2vpError, match="out of range"):
+            ds.update_grid(7, g)
 
 
 def test_cuda_matches_golden_fixtures(pkg):
