@@ -491,6 +491,11 @@ public:
     DeviceScene(const DeviceScene &) = delete;
     DeviceScene &operator=(const DeviceScene &) = delete;
     const Scene &scene() const { return *scene_; }
+    /* traverse() -> "data" -> GridVolume::parameters_changed (src/textures/grid3d.cpp:366-391): new values for a
+       grid of unchanged resolution, written in place on the device */
+    void update_grid(int volume, const std::vector<float> &data, bool keep_max = false) {
+        check(b2vp_scene_update_grid(h_, volume, data.data(), data.size(), keep_max ? 1 : 0));
+    }
     /* Integrator::render: all streams of the seeding mode, or the range [first, first + n) */
     Film render(int seed_mode = B2VP_SEED_WAVEFRONT, uint64_t first_stream = 0, uint64_t n_streams = 0) {
         Film f;
