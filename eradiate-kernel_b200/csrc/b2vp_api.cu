@@ -19,6 +19,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -147,6 +148,7 @@ struct b2vp_scene {
     std::vector<B2vpMedium> media;
     std::vector<B2vpVolume> volumes;
     std::vector<std::vector<float>> volume_data;
+    std::vector<char> volume_pinned;                 /* volume_data[i] is page-locked (b2vp_scene_update_grid) */
     std::vector<B2vpPhase> phases;
     std::vector<std::vector<double>> phase_values;   /* tabphase tables, copied from the descriptor */
     std::vector<B2vpEmitter> emitters;
@@ -984,6 +986,8 @@ void b2vp_scene_destroy(b2vp_scene_t *scene) {
     cudaSetDevice(scene->device);
     if (scene->ev0) cudaEventDestroy(scene->ev0);
     if (scene->ev1) cudaEventDestroy(scene->ev1);
+    for (size_t i = 0; i < scene->volume_pinned.size(); ++i)
+        if (scene->volume_pinned[i]) cudaHostUnregister(scene->volume_data[i].data());
     delete scene;
 }
 
@@ -1050,11 +1054,43 @@ int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *dat
     if (n_values != held.size())   /* grid3d.cpp:373-383 also takes a doubled resolution; this path does not */
         return fail(B2VP_ERR_UNSUPPORTED, "Unsupported GridVolume data size update: %llu -> %llu",
                     (unsigned long long) held.size(), (unsigned long long) n_values);
-    held.assign(data, data + n_values);
-    if (!keep_max) {   /* grid3d.cpp:387-390: the maximum follows the data unless max_value was given */
-        float mx = held[0];
-        for (float x : held) mx = x > mx ? x : mx;
-        hv.max_value = mx;
+    CU_CHECK(cudaSetDevice(scene->device));
+    /* The host copy of the grid (kept for a device instance of the other precision built later) is page-locked at
+       the first update, so that sweeps upload at PCIe rate instead of through the driver's pageable staging; the
+       copy into it and the maximum (grid3d.cpp:387-390: follows the data unless max_value was given) are one
+       pass over the caller's array on a few host threads. */
+    if (scene->volume_pinned.size() != scene->volume_data.size()) scene->volume_pinned.assign(scene->volume_data.size(), 0);
+    if (!scene->volume_pinned[volume] && n_values >= (1u << 18)) {
+        if (cudaHostRegister(held.data(), held.size() * sizeof(float), cudaHostRegisterDefault) == cudaSuccess)
+            scene->volume_pinned[volume] = 1;
+        else
+            cudaGetLastError();   /* stays pageable: slower, not wrong */
+    }
+    {
+        const unsigned hw = std::thread::hardware_concurrency();
+        const size_t n_thr = n_values < (1u << 20) ? 1 : std::min<size_t>(8, hw ? hw : 1);
+        std::vector<float> part(n_thr, data[0]);
+        auto work = [&](size_t t) {
+            const size_t lo = n_values * t / n_thr, hi = n_values * (t + 1) / n_thr;
+            std::memcpy(held.data() + lo, data + lo, (hi - lo) * sizeof(float));
+            float m[8];
+            for (int q = 0; q < 8; ++q) m[q] = data[lo];
+            size_t i = lo;
+            for (; i + 8 <= hi; i += 8)
+                for (int q = 0; q < 8; ++q) m[q] = data[i + q] > m[q] ? data[i + q] : m[q];
+            for (; i < hi; ++i) m[0] = data[i] > m[0] ? data[i] : m[0];
+            for (int q = 1; q < 8; ++q) m[0] = m[q] > m[0] ? m[q] : m[0];
+            part[t] = m[0];
+        };
+        std::vector<std::thread> pool;
+        for (size_t t = 1; t < n_thr; ++t) pool.emplace_back(work, t);
+        work(0);
+        for (auto &th : pool) th.join();
+        if (!keep_max) {
+            float mx = part[0];
+            for (float x : part) mx = x > mx ? x : mx;
+            hv.max_value = mx;
+        }
     }
     CU_CHECK(cudaSetDevice(scene->device));
     auto patch_dev = [&](auto &ds) -> int {
