@@ -152,7 +152,8 @@ class ParamPatch(C.Structure):
 
 # every symbol include/b2vp.h declares
 EXPORTS = ["b2vp_stream_count", "b2vp_scene_create", "b2vp_scene_update", "b2vp_scene_update_grid", "b2vp_scene_destroy", "b2vp_render",
-           "b2vp_cancel", "b2vp_last_error", "b2vp_abi_version", "b2vp_device_count", "b2vp_measure_fp32_peak"]
+           "b2vp_cancel", "b2vp_last_error", "b2vp_abi_version", "b2vp_device_count", "b2vp_measure_fp32_peak",
+           "b2vp_render_noalloc"]
 
 _lib = None
 
@@ -183,6 +184,7 @@ def lib():
     L.b2vp_scene_destroy.argtypes = [C.c_void_p]
     L.b2vp_scene_destroy.restype = None
     L.b2vp_render.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
+    L.b2vp_render_noalloc.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
     L.b2vp_cancel.argtypes = [C.c_void_p]
     L.b2vp_cancel.restype = None
     L.b2vp_stream_count.argtypes = [C.c_void_p, c_i32, C.POINTER(c_u64), C.POINTER(c_u32)]

@@ -931,10 +931,183 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
 
 } // namespace
 
+/* ---- render without device allocation (b2vp_render_noalloc) ---------------------------------------------
+   Scratch of the render kernels (launch totals, stream work counter, spiral block table, cold path records of
+   the queue kernel) in ONE file-scope device array instead of cudaMalloc'ed buffers.  Every GPU that loads the
+   library holds B2VP_NOALLOC_SCRATCH_BYTES of it until exit.  In host code the array's name is only a stand-in
+   for the symbol: the device address comes from cudaGetSymbolAddress, once per device with that device current
+   (noalloc_scratch).  All calls on one device share the array and it keeps the last call's contents: what must
+   start at zero (totals, work counter) is cleared on the launch stream; calls that overlap on the GPU race. */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B2VP_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+unsigned char *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_scratch(int device, unsigned char **out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES)
+        return fail(B2VP_ERR_INVALID, "b2vp_render_noalloc: device ordinal %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        CU_CHECK(cudaSetDevice(device));
+        void *p = nullptr;
+        CU_CHECK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail(B2VP_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[device] = (unsigned char *) p;
+    }
+    *out = g_noalloc_ptr[device];
+    return B2VP_OK;
+}
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t) 255; }
+
+template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_device) {
+    CU_CHECK(cudaSetDevice(s->device));
+    DeviceScene<F> &ds = dev_of<F>(s);
+    if (!ds.ready)
+        return fail(B2VP_ERR_INVALID, "b2vp_render_noalloc: the scene is not resident on the device in this precision "
+                                      "yet; call b2vp_render once at set-up (it allocates), then this entry point");
+    if (!a->film_on_device)
+        return fail(B2VP_ERR_INVALID, "b2vp_render_noalloc: the film must be a device buffer of the caller (film_on_device = 1)");
+    if (a->seed_mode == B2VP_SEED_EXPLICIT || a->out_state || a->out_counters || a->out_radiance)
+        return fail(B2VP_ERR_UNSUPPORTED, "b2vp_render_noalloc: explicit seeding and per-stream outputs need device "
+                                          "staging buffers; use b2vp_render");
+    StreamSpace sp;
+    int rc = make_stream_space(s, a->seed_mode, a->n_streams, a->explicit_samples_per_stream, sp);
+    if (rc != B2VP_OK) return rc;
+    const uint64_t first = a->first_stream;
+    const uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
+    sp.d.il_block = 0; sp.d.il_count = 1; sp.d.il_index = 0; sp.d.il_shift = -1;
+    if (a->interleave_block) {
+        if (!a->n_streams || !a->interleave_count || a->interleave_index >= a->interleave_count)
+            return fail(B2VP_ERR_INVALID, "invalid interleaved stream range");
+        const uint64_t B = a->interleave_block, kmax = count - 1;
+        const uint64_t last = first + ((kmax / B) * a->interleave_count + a->interleave_index) * B + kmax % B;
+        if (last >= sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+        sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
+        if ((B & (B - 1)) == 0) { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
+    } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+    sp.d.first = first;
+    sp.d.count = count;
+    cudaStream_t stream = (cudaStream_t) a->cuda_stream;
+
+    const int W = sp.d.w, H = sp.d.h;
+    const size_t film_n = (size_t) W * H * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS);
+    const size_t film_bytes = film_n * sizeof(F);
+    F *d_film = (F *) film_device;
+
+    /* kernel and launch shape: the product defaults of render_typed (no environment overrides) */
+    RenderOut<F> out{};
+    out.film = d_film;
+    out.grid_smem_offset = align128(ds.g.blob_bytes);
+    out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
+    out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
+    size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
+    typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
+    const char *preset = "";
+    const uint32_t launch_features = ds.g.features | (sp.d.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
+    Kern kern = pick_queue_kernel<F, 512>(launch_features, &preset);
+    int threads = 512;
+    bool queue_kernel = true;
+    const double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
+    bool mis = s->desc.integrator.mis != 0;
+    for (const B2vpEmitter &e : s->emitters) mis = mis || e.type == B2VP_EMITTER_CONSTANT;
+    if (mis) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
+    if (queue_kernel) {
+        size_t base = (smem + 127) & ~(size_t) 127;
+        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
+        size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
+        size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
+        size_t n_slots = std::min<size_t>((size_t) (threads * oversub), max_slots) & ~(size_t) 31;
+        if (n_slots < 64)
+            return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
+        n_slots = std::min<size_t>(n_slots, 32768);
+        size_t cap = 64;
+        while (cap < n_slots) cap *= 2;
+        out.q_ctl_offset = (uint32_t) base;
+        size_t qbytes = (sizeof(QueueCtl) + PH_N * cap * sizeof(unsigned short) + 15) & ~(size_t) 15;
+        out.q_slots_offset = (uint32_t) (base + qbytes);
+        out.q_n_slots = (uint32_t) n_slots;
+        out.q_ring_cap = (uint32_t) cap;
+        out.q_stay_min = 26; out.q_max_iter = 8;
+        out.q_cta_phase = ds.global_grid_bytes > ((size_t) 16 << 20) ? 1u : 2u;
+        smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
+    }
+    int per_sm = 0;
+    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+    if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
+    const uint64_t want = (count + threads - 1) / threads;
+    const int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+
+    /* scratch layout inside the static array: [totals + work counter][spiral blocks][cold path records] */
+    const size_t head_bytes = align256((TOT_N + 32 + 1) * sizeof(unsigned long long));
+    const size_t blocks_bytes = a->seed_mode == B2VP_SEED_SCALAR_BLOCKS ? align256(sp.blocks.size() * sizeof(SpiralBlockD)) : 0;
+    const size_t cold_bytes = queue_kernel ? (size_t) grid * out.q_n_slots * sizeof(PathCold<F>) : 0;
+    const size_t need = head_bytes + blocks_bytes + cold_bytes;
+    if (need > (size_t) B2VP_NOALLOC_SCRATCH_BYTES)
+        return fail(B2VP_ERR_UNSUPPORTED,
+                    "b2vp_render_noalloc: this launch needs %zu bytes of scratch (%zu header, %zu spiral blocks, %zu path "
+                    "records), the static scratch array holds B2VP_NOALLOC_SCRATCH_BYTES = %zu; use b2vp_render",
+                    need, head_bytes, blocks_bytes, cold_bytes, (size_t) B2VP_NOALLOC_SCRATCH_BYTES);
+    unsigned char *scr = nullptr;
+    rc = noalloc_scratch(s->device, &scr);
+    if (rc != B2VP_OK) return rc;
+    out.totals = reinterpret_cast<unsigned long long *>(scr);
+    out.work_counter = out.totals + TOT_N + 32;
+    CU_CHECK(cudaMemsetAsync(scr, 0, head_bytes, stream));   /* the shared array keeps the last call's contents */
+    if (blocks_bytes) {
+        CU_CHECK(cudaMemcpyAsync(scr + head_bytes, sp.blocks.data(), sp.blocks.size() * sizeof(SpiralBlockD),
+                                 cudaMemcpyHostToDevice, stream));
+        sp.d.blocks = reinterpret_cast<const SpiralBlockD *>(scr + head_bytes);
+    }
+    if (queue_kernel) out.q_cold = scr + head_bytes + blocks_bytes;   /* every field is written before it is read */
+    if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
+
+    uint32_t launches = 0;
+    CU_CHECK(cudaEventRecord(s->ev0, stream));
+    if (count) {
+        kern<<<grid, threads, smem, stream>>>(ds.g, sp.d, out);
+        launches++;
+    }
+    CU_CHECK(cudaEventRecord(s->ev1, stream));
+    CU_CHECK(cudaGetLastError());
+    unsigned long long tot[TOT_N];
+    CU_CHECK(cudaMemcpyAsync(tot, out.totals, sizeof(tot), cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaStreamSynchronize(stream));   /* also keeps sp.blocks alive until the copy above has run */
+    if (a->totals) {
+        B2vpCounters &t = *a->totals;
+        std::memset(&t, 0, sizeof(t));
+        t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
+        t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
+        t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
+        float ms = 0;
+        CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        t.gpu_ms = ms;
+        t.n_launches = launches;
+    }
+    return B2VP_OK;
+}
+
+} // namespace
+
 /* ======================================================================== */
 extern "C" {
 
 uint32_t b2vp_abi_version(void) { return B2VP_ABI_VERSION; }
+
+int b2vp_render_noalloc(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film_device) {
+    if (!scene || !args || !film_device) return fail(B2VP_ERR_INVALID, "null argument");
+    if (args->abi_version != B2VP_ABI_VERSION || args->struct_size != sizeof(B2vpRenderArgs))
+        return fail(B2VP_ERR_INVALID, "B2vpRenderArgs ABI mismatch");
+    if (args->device != scene->device)
+        return fail(B2VP_ERR_INVALID, "scene lives on device %d, render asked for %d", scene->device, args->device);
+    if (args->precision == B2VP_PREC_F32) return render_noalloc_typed<float>(scene, args, film_device);
+    if (args->precision == B2VP_PREC_F64) return render_noalloc_typed<double>(scene, args, film_device);
+    return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
+}
 
 const char *b2vp_last_error(void) { return g_error.c_str(); }
 

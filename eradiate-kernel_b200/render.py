@@ -138,6 +138,28 @@ class DeviceScene:
         return RenderResult(film, tot, state, counters, radiance)
 
 
+    def render_noalloc(self, device_film, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0,
+                       interleave=None, stream=None, clear=True):
+        """b2vp_render_noalloc: the same render with the kernels' scratch in the library's static device array -- no
+        device allocation in the call (for callers under CUDA graph capture or in loops that must not cudaMalloc;
+        no counterpart in the reference).  `device_film` is a device pointer to H*W*channels reals owned by the
+        caller; the scene must have been rendered once with `render` before (that call uploads it).  Returns the
+        launch totals.  Calls on one device share the scratch: do not overlap them."""
+        a = abi.RenderArgs()
+        a.abi_version, a.struct_size = abi.ABI_VERSION, C.sizeof(abi.RenderArgs)
+        a.precision = self.scene.precision if precision is None else precision
+        a.seed_mode, a.device = seed_mode, self.device
+        a.cuda_stream = stream
+        a.first_stream, a.n_streams = first_stream, n_streams
+        if interleave is not None:
+            a.interleave_block, a.interleave_count, a.interleave_index = interleave
+        a.film_on_device, a.clear_film = 1, int(clear)
+        tot = abi.Counters()
+        a.totals = C.pointer(tot)
+        abi.check(abi.lib().b2vp_render_noalloc(self._h, C.byref(a), device_film))
+        return tot
+
+
 def render(scene, device=0, **kw):
     """One-shot `integrator.render(scene, sensor)`."""
     with DeviceScene(scene, device) as ds:

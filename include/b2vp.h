@@ -347,6 +347,23 @@ void b2vp_scene_destroy(b2vp_scene_t *scene);
    interleaved like ImageBlock storage, float for F32 / double for F64).       */
 int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film);
 
+/* b2vp_render without any device allocation.  It has NO counterpart in the reference: it was added
+   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+   serving loops, harnesses that forbid it).  Same kernels and same results as b2vp_render, but the kernels'
+   scratch (launch totals, stream work counter, spiral block table, the queue kernel's cold path records) lives
+   in one static device array of B2VP_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit;
+   the call performs no cudaMalloc / cudaFree and no allocating library routine.
+   Conditions: `film_device` is the caller's DEVICE buffer (args->film_on_device = 1; cleared first when
+   args->clear_film); the scene must already be resident in args->precision, i.e. b2vp_render ran once on it at
+   set-up; seed modes SCALAR_BLOCKS and WAVEFRONT; no per-stream outputs (out_state / out_counters /
+   out_radiance NULL).  A launch whose scratch exceeds the array fails with B2VP_ERR_UNSUPPORTED and a message
+   naming the sizes (on a B200 the product launch needs 46-50 MB).  All calls on one device share the array and
+   it keeps the previous call's contents (what must start at zero is cleared by the call): calls that overlap on
+   the GPU -- two host threads, or two streams -- RACE; serialise them.  Synchronises args->cuda_stream before
+   returning, like b2vp_render.                                                    */
+#define B2VP_NOALLOC_SCRATCH_BYTES (64u << 20)
+int b2vp_render_noalloc(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film_device);
+
 /* Asynchronous cancel (Integrator::cancel): polled between kernel launches.   */
 void b2vp_cancel(b2vp_scene_t *scene);
 
