@@ -150,10 +150,19 @@ class ParamPatch(C.Structure):
     ]
 
 
+class SceneInfo(C.Structure):
+    _fields_ = [
+        ("abi_version", c_u32), ("struct_size", c_u32), ("n_triangles", c_u64),
+        ("bvh_nodes", c_u32), ("bvh_leaves", c_u32), ("bvh_max_depth", c_u32),
+        ("bvh_forced_median_splits", c_u32), ("bvh_degenerate_splits", c_u32), ("bvh_stack_capacity", c_u32),
+        ("last_kernel", C.c_char * 96),
+    ]
+
+
 # every symbol include/b2vp.h declares
 EXPORTS = ["b2vp_stream_count", "b2vp_scene_create", "b2vp_scene_update", "b2vp_scene_update_grid", "b2vp_scene_destroy", "b2vp_render",
            "b2vp_cancel", "b2vp_last_error", "b2vp_abi_version", "b2vp_device_count", "b2vp_measure_fp32_peak",
-           "b2vp_render_noalloc"]
+           "b2vp_render_noalloc", "b2vp_scene_info"]
 
 _lib = None
 
@@ -185,6 +194,7 @@ def lib():
     L.b2vp_scene_destroy.restype = None
     L.b2vp_render.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
     L.b2vp_render_noalloc.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
+    L.b2vp_scene_info.argtypes = [C.c_void_p, C.POINTER(SceneInfo)]
     L.b2vp_cancel.argtypes = [C.c_void_p]
     L.b2vp_cancel.restype = None
     L.b2vp_stream_count.argtypes = [C.c_void_p, c_i32, C.POINTER(c_u64), C.POINTER(c_u32)]

@@ -157,6 +157,8 @@ struct b2vp_scene {
     std::vector<double> sensor_xf;
     std::vector<BvhNode> bvh_nodes;
     std::vector<BvhPrim> bvh_prims;
+    BvhStats bvh_stats;
+    std::string last_kernel;                         /* kernel instance launched by the last render (b2vp_scene_info) */
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf;
@@ -294,7 +296,7 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
     return B2VP_OK;
 }
 
-void build_bvh(b2vp_scene *s) {
+int build_bvh(b2vp_scene *s) {
     std::vector<BuildTri> tris;
     for (size_t i = 0; i < s->shapes.size(); ++i) {
         const B2vpShape &a = s->shapes[i];
@@ -320,7 +322,13 @@ void build_bvh(b2vp_scene *s) {
     float pad = (float) (scale * 2e-6);
     int max_leaf = 2;   /* measured: 2-3 triangles per leaf beat 4 and 1 on both the 12-triangle cube and the 1e6-triangle canopy */
     if (const char *e = std::getenv("B2VP_BVH_LEAF")) max_leaf = std::atoi(e);
-    bvh_build(tris, pad, s->bvh_nodes, s->bvh_prims, max_leaf);
+    bvh_build(tris, pad, s->bvh_nodes, s->bvh_prims, max_leaf, &s->bvh_stats);
+    /* the device traversal pushes at most one node per level onto a BVH_STACK_CAPACITY-entry stack; the builder
+       bounds the depth by 24 + log2(n) (index-median splits from level 24 on), n < 2^28 */
+    if (s->bvh_stats.max_depth >= BVH_STACK_CAPACITY)
+        return fail(B2VP_ERR_UNSUPPORTED, "BVH depth %u exceeds the device traversal stack (%u entries)",
+                    s->bvh_stats.max_depth, BVH_STACK_CAPACITY);
+    return B2VP_OK;
 }
 
 } // namespace
@@ -886,6 +894,9 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         out.q_cold = s->q_cold.p;
     }
 
+    s->last_kernel = queue_kernel ? std::string("queue/") + preset + (threads == 512 ? "" : "/" + std::to_string(threads))
+                     : kern == (Kern) volpath_kernel<F> ? "stream (one thread per stream)" : "lanes";
+    s->last_kernel += sizeof(F) == 4 ? " f32" : " f64";
     if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     uint32_t launches = 0;
     CU_CHECK(cudaEventRecord(s->ev0, stream));
@@ -1098,6 +1109,20 @@ extern "C" {
 
 uint32_t b2vp_abi_version(void) { return B2VP_ABI_VERSION; }
 
+int b2vp_scene_info(const b2vp_scene_t *scene, B2vpSceneInfo *info) {
+    if (!scene || !info) return fail(B2VP_ERR_INVALID, "null argument");
+    if (info->abi_version != B2VP_ABI_VERSION || info->struct_size != sizeof(B2vpSceneInfo))
+        return fail(B2VP_ERR_INVALID, "B2vpSceneInfo ABI mismatch");
+    const BvhStats &b = scene->bvh_stats;
+    info->n_triangles = scene->faces.size() / 3;
+    info->bvh_nodes = b.n_nodes; info->bvh_leaves = b.n_leaves; info->bvh_max_depth = b.max_depth;
+    info->bvh_forced_median_splits = b.n_forced_median; info->bvh_degenerate_splits = b.n_degenerate_median;
+    info->bvh_stack_capacity = BVH_STACK_CAPACITY;
+    std::memset(info->last_kernel, 0, sizeof(info->last_kernel));
+    std::strncpy(info->last_kernel, scene->last_kernel.c_str(), sizeof(info->last_kernel) - 1);
+    return B2VP_OK;
+}
+
 int b2vp_render_noalloc(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film_device) {
     if (!scene || !args || !film_device) return fail(B2VP_ERR_INVALID, "null argument");
     if (args->abi_version != B2VP_ABI_VERSION || args->struct_size != sizeof(B2vpRenderArgs))
@@ -1146,7 +1171,8 @@ int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **
     s->smem_optin = (size_t) smem_optin;
     int rc = copy_desc(desc, s.get());
     if (rc != B2VP_OK) return rc;
-    build_bvh(s.get());
+    rc = build_bvh(s.get());
+    if (rc != B2VP_OK) return rc;
     CU_CHECK(cudaSetDevice(device));
     CU_CHECK(cudaEventCreate(&s->ev0));
     CU_CHECK(cudaEventCreate(&s->ev1));

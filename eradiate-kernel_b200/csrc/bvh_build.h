@@ -19,10 +19,23 @@ namespace vp {
 
 struct BuildTri { float bmin[3], bmax[3], c[3]; uint32_t shape, face; };
 
+/* The device traversal (vp_scene.cuh, ray_intersect) pushes at most one node per tree level. */
+constexpr uint32_t BVH_STACK_CAPACITY = 64;
+constexpr uint32_t BVH_FORCE_MEDIAN_DEPTH = 24;
+
+struct BvhStats {
+    uint32_t n_nodes = 0, n_leaves = 0;
+    uint32_t max_depth = 0;              /* depth of the deepest leaf (root = 0) = largest possible stack use */
+    uint32_t n_forced_median = 0;        /* inner nodes split by the index median because depth >= 24 */
+    uint32_t n_degenerate_median = 0;    /* inner nodes split by the index median because SAH found no split */
+};
+
 inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNode> &nodes,
-                      std::vector<BvhPrim> &prims, int max_leaf = 4) {
+                      std::vector<BvhPrim> &prims, int max_leaf = 4, BvhStats *stats = nullptr) {
     nodes.clear();
     prims.clear();
+    BvhStats st;
+    if (stats) *stats = st;
     if (tris.empty()) return;
     const int NB = 16, MAX_LEAF = std::min(std::max(max_leaf, 1), 7);
     nodes.reserve(tris.size());
@@ -45,6 +58,8 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
         for (int a = 0; a < 3; ++a) { n.bmin[a] = bmin[a] - pad; n.bmax[a] = bmax[a] + pad; }
         uint32_t cnt = t.hi - t.lo;
         auto make_leaf = [&]() {
+            st.n_leaves++;
+            st.max_depth = std::max(st.max_depth, t.depth);
             nodes[t.node].child = (uint32_t) prims.size();
             nodes[t.node].count = cnt;
             for (uint32_t i = t.lo; i < t.hi; ++i) prims.push_back(BvhPrim{ tris[i].shape, tris[i].face });
@@ -53,7 +68,7 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
            stack holds 64 entries, one per level: SAH splits may be lopsided, so from depth 24 on the split is the
            index median, which bounds the depth by 24 + log2(n). */
         if (cnt <= (uint32_t) MAX_LEAF) { make_leaf(); continue; }
-        const bool force_median = t.depth >= 24;
+        const bool force_median = t.depth >= BVH_FORCE_MEDIAN_DEPTH;
 
         /* binned SAH over the three axes */
         int best_axis = -1, best_split = -1;
@@ -104,6 +119,7 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
         if (best_axis < 0) {
             /* all centroids coincide, or the tree is getting deep: split by index */
             mid = t.lo + cnt / 2;
+            if (force_median) st.n_forced_median++; else st.n_degenerate_median++;
         } else {
             float ext = cmax[best_axis] - cmin[best_axis], scale = NB / ext, c0 = cmin[best_axis];
             int ax = best_axis, sp = best_split;
@@ -122,6 +138,8 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
         stack.push_back({ child + 1, mid, t.hi, t.depth + 1 });
         stack.push_back({ child, t.lo, mid, t.depth + 1 });
     }
+    st.n_nodes = (uint32_t) nodes.size();
+    if (stats) *stats = st;
 }
 
 } // namespace vp

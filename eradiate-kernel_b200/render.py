@@ -85,6 +85,13 @@ class DeviceScene:
     def cancel(self):
         abi.lib().b2vp_cancel(self._h)
 
+    def info(self):
+        """b2vp_scene_info: BVH figures and the kernel instance the last render launched."""
+        i = abi.SceneInfo()
+        i.abi_version, i.struct_size = abi.ABI_VERSION, C.sizeof(abi.SceneInfo)
+        abi.check(abi.lib().b2vp_scene_info(self._h, C.byref(i)))
+        return i
+
     def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None, interleave=None,
                want_paths=False, film=None, stream=None, device_film=None, clear=True):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).

@@ -364,6 +364,24 @@ int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film);
 #define B2VP_NOALLOC_SCRATCH_BYTES (64u << 20)
 int b2vp_render_noalloc(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film_device);
 
+/* What the library built from the scene and what it ran last: the acceleration structure that stands in for the
+   reference's kd-tree (include/mitsuba/render/kdtree.h:2008-2391; only the traversal RESULT is part of the
+   contract, so the tree's own figures are exposed for tests and logs), and the kernel instance the last
+   b2vp_render on this scene launched -- the reference logs its choices through Log(Info, ...)
+   (src/librender/integrator.cpp:99-104); this is the same information as data.  Fill abi_version / struct_size. */
+typedef struct B2vpSceneInfo {
+    uint32_t abi_version;
+    uint32_t struct_size;
+    uint64_t n_triangles;
+    uint32_t bvh_nodes, bvh_leaves;
+    uint32_t bvh_max_depth;              /* deepest leaf (root = 0): bounds the device traversal stack use */
+    uint32_t bvh_forced_median_splits;   /* splits by index median because the tree was >= 24 levels deep  */
+    uint32_t bvh_degenerate_splits;      /* splits by index median because all centroids coincided         */
+    uint32_t bvh_stack_capacity;         /* entries of the device traversal stack                          */
+    char last_kernel[96];                /* e.g. "queue/heterogeneous f32"; empty before the first render   */
+} B2vpSceneInfo;
+int b2vp_scene_info(const b2vp_scene_t *scene, B2vpSceneInfo *info);
+
 /* Asynchronous cancel (Integrator::cancel): polled between kernel launches.   */
 void b2vp_cancel(b2vp_scene_t *scene);
 

@@ -165,9 +165,9 @@ def test_abi_library_exports(pkg):
     # struct sizes agree with the header as compiled by gcc
     import subprocess
     import tempfile
-    src = ('#include "%s"\n#include <stdio.h>\nint main(){printf("%%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu\\n",'
+    src = ('#include "%s"\n#include <stdio.h>\nint main(){printf("%%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu\\n",'
            'sizeof(B2vpSceneDesc),sizeof(B2vpRenderArgs),sizeof(B2vpShape),sizeof(B2vpSensor),sizeof(B2vpParamPatch),'
-           'sizeof(B2vpVolume),sizeof(B2vpMedium),sizeof(B2vpBsdf),sizeof(B2vpCounters),sizeof(B2vpPathCounters));}'
+           'sizeof(B2vpVolume),sizeof(B2vpMedium),sizeof(B2vpBsdf),sizeof(B2vpCounters),sizeof(B2vpPathCounters),sizeof(B2vpSceneInfo));}'
            % os.path.join(root, "include", "b2vp.h"))
     with tempfile.TemporaryDirectory() as td:
         open(os.path.join(td, "s.c"), "w").write(src)
@@ -175,7 +175,7 @@ def test_abi_library_exports(pkg):
         sizes = [int(x) for x in subprocess.check_output([os.path.join(td, "s")]).split()]
     a = pkg.abi
     assert sizes == [C.sizeof(t) for t in (a.SceneDesc, a.RenderArgs, a.Shape, a.Sensor, a.ParamPatch, a.Volume,
-                                           a.Medium, a.Bsdf, a.Counters, a.PathCounters)]
+                                           a.Medium, a.Bsdf, a.Counters, a.PathCounters, a.SceneInfo)]
 
 
 def test_no_device_fails_loudly(pkg):
