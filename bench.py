@@ -37,14 +37,17 @@ def workload(spp):
     return scenes.c2(spp=spp, width=WIDTH, tau=0.5, nz=1000)
 
 
-def config(spp, n_gpus, extra=None):
+def config(spp, n_gpus, extra=None, math="exact"):
     c = {"workload": "BASELINE configs[1]: 1D plane-parallel heterogeneous atmosphere, gridvolume sigma_t "
                      "1x1x1000 (trilinear, exp profile, tau=0.5), rayleigh, rpv, distant %dx1 film, volpath "
                      "max_depth=-1 rr_depth=5, scalar_mono (fp32)" % WIDTH,
          "spp_per_gpu": spp, "paths_per_step": WIDTH * spp * n_gpus, "seeding": "wavefront (sampler.cpp:89-92)",
          "sharding": "interleaved stream blocks (every GPU renders spp of the spp x N samples of every pixel) + one NCCL "
                      "film reduce" if n_gpus > 1 else "single GPU",
-         "l2": "flushed between steps (256 MiB write); the 4 KB grid is staged in shared memory"}
+         "l2": "flushed between steps (256 MiB write); the 4 KB grid is staged in shared memory",
+         "math": "fast: fp32 tolerance mode (B2VP_MATH_FAST: FMA contraction, hardware lg2/ex2/rcp/rsq; PCG32 exact; "
+                 "gated against the reference films, tests/test_gpu_fastmath.py)" if math == "fast" else
+                 "exact: every fp32 operation in the oracle's IEEE order (bit-exact against the CPU oracle)"}
     if extra:
         c.update(extra)
     return c
@@ -225,7 +228,8 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def step():
-        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, device_film=film.data_ptr(), clear=True, stream=stream, **shard)
+        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, device_film=film.data_ptr(), clear=True, stream=stream,
+                      math=args.math, **shard)
         if world > 1:
             dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
         return r.totals
@@ -274,7 +278,7 @@ def run_ours(args):
         barrier()
         t0 = time.perf_counter()
         with pkg.DeviceScene(scene, device=local) as ds2:
-            r = ds2.render(seed_mode=abi.SEED_WAVEFRONT, film=host_film * 0, **shard)
+            r = ds2.render(seed_mode=abi.SEED_WAVEFRONT, film=host_film * 0, math=args.math, **shard)
             if world > 1:
                 f = torch.from_numpy(r.film).cuda()
                 dist.reduce(f, dst=0, op=dist.ReduceOp.SUM)
@@ -311,7 +315,7 @@ def run_ours(args):
             pass
         roofline = {"bound": "fp32", "achieved": achieved, "peak": fp32.value, "unit": "TFLOP/s",
                     "frac": achieved / fp32.value if fp32.value else None, "traffic": traffic,
-                    "kernel": "vp::volpath_q_kernel<float, 512, FT_HETERO|FT_TRILINEAR|FT_RECT|FT_MESH|FT_MESH_ATTR>", "kernel_ms": k_ms,
+                    "kernel": "vp::volpath_q_kernel [%s]" % ds.info().last_kernel.decode(), "kernel_ms": k_ms,
                     "algorithmic": "%d medium steps x %d flop" % (tot_last.n_medium_steps, FLOP_PER_SEGMENT),
                     "peak_source": "b2vp_measure_fp32_peak (FMA microbenchmark, measured in this run); "
                                    "HBM peak %s GB/s (MEASURED_PEAKS.json) is not the bound here: the grid "
@@ -326,7 +330,7 @@ def run_ours(args):
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "segments_per_s": seg_per_s, "config": config(args.spp, n_gpus),
+            "segments_per_s": seg_per_s, "config": config(args.spp, n_gpus, math=args.math),
             "clocks": clk, "gpu_launches": launches,
             "e2e": {"value": e2e_val, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(host_film.nbytes), "ms_per_step": float(e2e_t.item())},
@@ -366,6 +370,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--profile", action="store_true", help="kernel-only run for ncu: no e2e leg, no CPU baseline")
     ap.add_argument("--spp", type=int, default=16384, help="samples per pixel per GPU (BASELINE: 2^14)")
+    ap.add_argument("--math", default="exact", choices=["exact", "fast"],
+                    help="fp32 mode of the kernels: exact (bit-exact against the oracle) or fast (tolerance mode)")
     args = ap.parse_args()
     # ONE JSON line on stdout: native libraries that write to file descriptor 1 themselves (NCCL prints its version
     # banner there at N>1) are sent to stderr; Python's own stdout keeps the real one

@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb2vp.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NO_DEVICE, ERR_CANCELLED = range(6)
 PREC_F32, PREC_F64 = 0, 1
@@ -29,6 +29,11 @@ DIR_SINGLE, DIR_SAMPLE_WIDTH, DIR_SAMPLE_ALL = 0, 1, 2
 TARGET_NONE, TARGET_POINT, TARGET_SHAPE = 0, 1, 2
 ORIGIN_BSPHERE, ORIGIN_SHAPE = 0, 1
 SEED_SCALAR_BLOCKS, SEED_WAVEFRONT, SEED_EXPLICIT = 0, 1, 2
+MATH_EXACT, MATH_FAST = 0, 1
+KERNEL_AUTO, KERNEL_QUEUE_GENERIC, KERNEL_QUEUE_256, KERNEL_LANES, KERNEL_STREAM = range(5)
+KERNELS = {"auto": KERNEL_AUTO, "queue": KERNEL_AUTO, "generic": KERNEL_QUEUE_GENERIC, "q256": KERNEL_QUEUE_256,
+           "lanes": KERNEL_LANES, "mega": KERNEL_STREAM, "stream": KERNEL_STREAM}
+OPT_NO_CELL_RECORDS, OPT_BVH_LEAF_SHIFT = 1, 8
 
 c_d, c_i32, c_u32, c_u64 = C.c_double, C.c_int32, C.c_uint32, C.c_uint64
 
@@ -101,7 +106,7 @@ class Integrator(C.Structure):
 
 class SceneDesc(C.Structure):
     _fields_ = [
-        ("abi_version", c_u32), ("struct_size", c_u32), ("precision", c_i32), ("reserved0", c_i32),
+        ("abi_version", c_u32), ("struct_size", c_u32), ("precision", c_i32), ("options", c_u32),
         ("n_shapes", c_u32), ("n_bsdfs", c_u32), ("n_media", c_u32), ("n_volumes", c_u32),
         ("n_phases", c_u32), ("n_emitters", c_u32),
         ("shapes", C.POINTER(Shape)), ("bsdfs", C.POINTER(Bsdf)), ("media", C.POINTER(Medium)),
@@ -137,6 +142,7 @@ class RenderArgs(C.Structure):
         ("explicit_pixel", C.POINTER(c_u32)), ("explicit_samples_per_stream", c_u32), ("clear_film", c_u32),
         ("out_state", C.POINTER(c_u64)), ("out_counters", C.POINTER(PathCounters)),
         ("out_radiance", C.c_void_p), ("totals", C.POINTER(Counters)),
+        ("math_mode", c_i32), ("kernel", c_i32), ("tuning", c_u32 * 4), ("debug_flags", c_u32), ("reserved1", c_u32),
     ]
 
 

@@ -6,9 +6,8 @@
  */
 #include "../../include/b2vp.h"
 #include "bvh_build.h"
-#include "vp_kernels.cuh"
-#include "vp_wavefront.cuh"
 #include "vp_queue.cuh"
+#include "vp_launch.h"
 
 #include <cstdlib>
 
@@ -159,6 +158,7 @@ struct b2vp_scene {
     std::vector<BvhPrim> bvh_prims;
     BvhStats bvh_stats;
     std::string last_kernel;                         /* kernel instance launched by the last render (b2vp_scene_info) */
+    bool warned_stream_kernel = false;
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf;
@@ -321,7 +321,7 @@ int build_bvh(b2vp_scene *s) {
     scale += 3.0 * s->desc.bsphere_radius;
     float pad = (float) (scale * 2e-6);
     int max_leaf = 2;   /* measured: 2-3 triangles per leaf beat 4 and 1 on both the 12-triangle cube and the 1e6-triangle canopy */
-    if (const char *e = std::getenv("B2VP_BVH_LEAF")) max_leaf = std::atoi(e);
+    if (const uint32_t v = (s->desc.options >> B2VP_OPT_BVH_LEAF_SHIFT) & 7u) max_leaf = (int) v;
     bvh_build(tris, pad, s->bvh_nodes, s->bvh_prims, max_leaf, &s->bvh_stats);
     /* the device traversal pushes at most one node per level onto a BVH_STACK_CAPACITY-entry stack; the builder
        bounds the depth by 24 + log2(n) (index-median splits from level 24 on), n < 2^28 */
@@ -343,6 +343,7 @@ inline uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
 /* shared-memory budget that still lets two CTAs share an SM */
 constexpr uint32_t SMEM_BUDGET = 100 * 1024;
 constexpr uint32_t FILM_SMEM_MAX = 16 * 1024;
+constexpr size_t BVH_SMEM_MAX = 16 * 1024;     /* BVH nodes + leaf triangles staged with the tables when they fit */
 
 template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     const B2vpSceneDesc &d = s->desc;
@@ -485,15 +486,32 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         if (v.channels != 1) ft |= FT_CH3;
         if (!(v.w2l[3] == 0 && v.w2l[7] == 0 && v.w2l[11] == 0 && v.w2l[15] == 1)) ft |= FT_PROJECTIVE;
     }
+    /* leaf triangles by value, in leaf order (three 16-byte loads per test) */
+    std::vector<BvhTri> soup(s->bvh_prims.size());
+    for (size_t i = 0; i < soup.size(); ++i) {
+        const BvhPrim &pr = s->bvh_prims[i];
+        const B2vpShape &a = s->shapes[pr.shape];
+        const uint32_t *fi = &s->faces[3 * (size_t) (a.face_offset + pr.face)];
+        float *dst[3] = {soup[i].p0, soup[i].p1, soup[i].p2};
+        for (int v = 0; v < 3; ++v)
+            std::memcpy(dst[v], &s->vpos[3 * (size_t) (a.vertex_offset + fi[v])], 3 * sizeof(float));
+        soup[i].shape = pr.shape; soup[i].face = pr.face; soup[i].pad = 0;
+    }
+    /* A small BVH (the 12-triangle cube that bounds the atmosphere in C1-C4: 11 nodes + 12 triangles = 928 bytes) is
+       appended to the table blob, i.e. staged in shared memory by every CTA: Scene::ray_intersect runs ~12 times per
+       path, each traversal is a chain of dependent loads, and the L1 left beside 222 KB of shared memory does not keep
+       even 1 KB resident against the stream of cold path records (ncu: 29 % of all stall samples were
+       long_scoreboard, led by the slab tests of this cube). */
+    const size_t bvh_bytes = s->bvh_nodes.size() * sizeof(BvhNode) + soup.size() * sizeof(BvhTri);
+    const bool bvh_small = !s->bvh_nodes.empty() && bvh_bytes <= BVH_SMEM_MAX;
     for (uint32_t i = 0; i < n_shapes; ++i) {
         const B2vpShape &a = s->shapes[i];
-        ft |= a.type == B2VP_SHAPE_MESH ? FT_MESH : a.type == B2VP_SHAPE_SPHERE ? FT_SPHERE : FT_RECT;
+        ft |= a.type == B2VP_SHAPE_MESH ? (bvh_small ? FT_MESH_SMEM : FT_MESH) : a.type == B2VP_SHAPE_SPHERE ? FT_SPHERE : FT_RECT;
         if (a.type == B2VP_SHAPE_MESH && (a.has_vertex_normals || a.has_vertex_texcoords)) ft |= FT_MESH_ATTR;
     }
     if (have_tabphase) ft |= FT_TABPHASE;
     if (have_blendphase) ft |= FT_BLENDPHASE;
     if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX || d.sensor.type == B2VP_SENSOR_IRRADIANCEMETER) ft |= FT_DISTANTFLUX;
-    g.features = ft;
 
     /* blob layout */
     uint32_t off = 0;
@@ -505,6 +523,12 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     g.ofs_volumes = place(volumes.size() * sizeof(DVolume<F>));
     g.ofs_phases = place(phases.size() * sizeof(DPhase<F>) + phase_tabs.size() * sizeof(F));
     g.ofs_emitters = place(emitters.size() * sizeof(DEmitter<F>));
+    g.bvh_in_blob = bvh_small ? 1u : 0u;
+    g.ofs_bvh = g.ofs_bvh_tris = 0;
+    if (bvh_small) {
+        g.ofs_bvh = place(s->bvh_nodes.size() * sizeof(BvhNode));
+        g.ofs_bvh_tris = place(soup.size() * sizeof(BvhTri));
+    }
     g.blob_bytes = align16(off ? off : 16);
     if (g.blob_bytes > 64 * 1024)
         return fail(B2VP_ERR_UNSUPPORTED, "scene tables (%u bytes) exceed the shared-memory table budget", g.blob_bytes);
@@ -522,9 +546,8 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
             ds.global_grid_bytes += v.data_bytes;
             /* A grid gathered from HBM / L2 gets trilinear cell records (vp_types.cuh, DVolume::cells): 8x the
                memory (2 x 257^3 x 32 B = 1.1 GB for C3, of 180 GB), one 32-byte sector per lookup instead of
-               eight words in four rows.  B2VP_CELLS=0 keeps the plain layout (A/B measurements). */
-            const char *ce = std::getenv("B2VP_CELLS");
-            const bool want_cells = !(ce && !std::strcmp(ce, "0"));
+               eight words in four rows.  B2VP_OPT_NO_CELL_RECORDS keeps the plain layout (A/B measurements). */
+            const bool want_cells = !(d.options & B2VP_OPT_NO_CELL_RECORDS);
             const size_t n_cells = (size_t) (v.nx + 1) * (v.ny + 1) * (v.nz + 1), cbytes = n_cells * 8 * sizeof(F);
             size_t free_b = 0, total_b = 0;
             cudaMemGetInfo(&free_b, &total_b);
@@ -544,6 +567,9 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     }
     CU_CHECK(cudaDeviceSynchronize());
     g.grid_smem_bytes = grid_off;
+    for (size_t i = 0; i < volumes.size(); ++i)
+        if (volumes[i].type == 1) ft |= volumes[i].smem_offset >= 0 ? FT_GRID_SMEM : FT_GRID_GLOBAL;
+    g.features = ft;
 
     ds.host_blob.assign(g.blob_bytes, 0);
     auto put = [&](uint32_t o, const void *p, size_t n) { if (n) std::memcpy(ds.host_blob.data() + o, p, n); };
@@ -555,6 +581,10 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
     put(g.ofs_phases, phases.data(), phases.size() * sizeof(DPhase<F>));
     put(g.ofs_phases + (uint32_t) (phases.size() * sizeof(DPhase<F>)), phase_tabs.data(), phase_tabs.size() * sizeof(F));
     put(g.ofs_emitters, emitters.data(), emitters.size() * sizeof(DEmitter<F>));
+    if (bvh_small) {
+        put(g.ofs_bvh, s->bvh_nodes.data(), s->bvh_nodes.size() * sizeof(BvhNode));
+        put(g.ofs_bvh_tris, soup.data(), soup.size() * sizeof(BvhTri));
+    }
     CU_CHECK(ds.blob.upload(ds.host_blob.data(), ds.host_blob.size()));
     g.blob = ds.blob.template as<unsigned char>();
 
@@ -569,16 +599,6 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
         CU_CHECK(ds.bvh.upload(s->bvh_nodes.data(), s->bvh_nodes.size() * sizeof(BvhNode)));
         CU_CHECK(ds.bvh_prims.upload(s->bvh_prims.data(), s->bvh_prims.size() * sizeof(BvhPrim)));
         g.bvh = ds.bvh.template as<BvhNode>(); g.bvh_prims = ds.bvh_prims.template as<BvhPrim>();
-        std::vector<BvhTri> soup(s->bvh_prims.size());
-        for (size_t i = 0; i < soup.size(); ++i) {
-            const BvhPrim &pr = s->bvh_prims[i];
-            const B2vpShape &a = s->shapes[pr.shape];
-            const uint32_t *fi = &s->faces[3 * (size_t) (a.face_offset + pr.face)];
-            float *dst[3] = {soup[i].p0, soup[i].p1, soup[i].p2};
-            for (int v = 0; v < 3; ++v)
-                std::memcpy(dst[v], &s->vpos[3 * (size_t) (a.vertex_offset + fi[v])], 3 * sizeof(float));
-            soup[i].shape = pr.shape; soup[i].face = pr.face; soup[i].pad = 0;
-        }
         CU_CHECK(ds.bvh_tris.upload(soup.data(), soup.size() * sizeof(BvhTri)));
         g.bvh_tris = ds.bvh_tris.template as<BvhTri>();
     }
@@ -709,41 +729,117 @@ template <> DeviceScene<float> &dev_of<float>(b2vp_scene *s) { return s->dev32; 
 template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64; }
 
 inline uint32_t align128(uint32_t x) { return (x + 127u) & ~127u; }
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t) 255; }
 
-/* queue-kernel instances: the generic one and presets for the common scene classes */
-constexpr uint32_t PRE_FLAT = FT_RECT | FT_MESH | FT_MESH_ATTR;   /* rectangles and meshes, no sphere (double-precision quadratic) */
-constexpr uint32_t PRE_HOMOG = PRE_FLAT | FT_HOMOG;
-constexpr uint32_t PRE_HET = PRE_FLAT | FT_HETERO | FT_TRILINEAR;
-constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO;
+/* ---- launch plan: which kernel, with which shape and shared-memory layout ------------------------------ */
+struct LaunchPlan {
+    const void *kern = nullptr;
+    int threads = 0, grid = 0;
+    size_t smem = 0;
+    bool queue_kernel = false;
+    size_t cold_bytes = 0;          /* queue kernel: grid * q_n_slots cold path records */
+    std::string name;
+};
 
-template <typename F, int MAXT>
-void (*pick_queue_kernel(uint32_t ft, const char **name))(const DScene<F>, const DStreams, const RenderOut<F>) {
-    if (std::getenv("B2VP_GENERIC")) ft = FT_ALL;
-    /* interleaved launches (multi-GPU sharding): the two scene classes the benchmarks shard have an instance with
-       the interleaved stream mapping, everything else goes to the generic instance */
-    if (ft & FT_INTERLEAVE) {
-        if ((ft & ~(PRE_HET | FT_INTERLEAVE)) == 0) { *name = "heterogeneous, interleaved"; return volpath_q_kernel<F, MAXT, PRE_HET | FT_INTERLEAVE>; }
-        if ((ft & ~(PRE_HET_ALB | FT_INTERLEAVE)) == 0) { *name = "heterogeneous+albedo grid, interleaved"; return volpath_q_kernel<F, MAXT, PRE_HET_ALB | FT_INTERLEAVE>; }
-        *name = "generic";
-        return volpath_q_kernel<F, MAXT, FT_ALL>;
+template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, const char **preset);
+template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, const char **preset) {
+    return fast ? vp_launch::queue_f32_fast(ft, preset) : vp_launch::queue_f32(ft, maxt, preset);
+}
+template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, const char **preset) {
+    return vp_launch::queue_f64(ft, maxt, preset);
+}
+template <typename F> const void *stream_entry() { return sizeof(F) == 4 ? vp_launch::stream_f32() : vp_launch::stream_f64(); }
+template <typename F> const void *lanes_entry() { return sizeof(F) == 4 ? vp_launch::lanes_f32() : vp_launch::lanes_f64(); }
+
+/* Fills the shared-memory layout fields of `out` and the plan.  `count` = streams of this launch. */
+template <typename F>
+int plan_launch(b2vp_scene *s, const DeviceScene<F> &ds, const B2vpRenderArgs *a, const DStreams &spd, size_t film_bytes,
+                RenderOut<F> &out, LaunchPlan &pl) {
+    /* shared memory: [tables][grids][film] */
+    out.grid_smem_offset = align128(ds.g.blob_bytes);
+    out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
+    out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
+    size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
+    const bool fast = a->math_mode == B2VP_MATH_FAST;
+    if (a->math_mode != B2VP_MATH_EXACT && !fast) return fail(B2VP_ERR_INVALID, "unknown math_mode %d", a->math_mode);
+    if (fast && sizeof(F) != 4) return fail(B2VP_ERR_INVALID, "B2VP_MATH_FAST is an fp32 mode (precision F32)");
+    /* Kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues (vp_queue.cuh).
+       volpathmis and scenes with an environment emitter (constant.cpp: non-delta emitter sampling,
+       light on escape) are not scheduled by the queue kernel: they run on the one-thread-per-stream kernel, an
+       order of magnitude slower -- said once per scene on stderr and in B2vpSceneInfo::last_kernel. */
+    bool needs_stream = s->desc.integrator.mis != 0;
+    for (const B2vpEmitter &e : s->emitters) needs_stream = needs_stream || e.type == B2VP_EMITTER_CONSTANT;
+    int kernel = a->kernel;
+    if (kernel < B2VP_KERNEL_AUTO || kernel > B2VP_KERNEL_STREAM) return fail(B2VP_ERR_INVALID, "unknown kernel %d", kernel);
+    if (needs_stream) {
+        if (fast) return fail(B2VP_ERR_UNSUPPORTED, "B2VP_MATH_FAST: volpathmis / environment emitters run on the one-thread-per-stream kernel, which has no fast instance");
+        if (kernel == B2VP_KERNEL_AUTO && !s->warned_stream_kernel) {
+            s->warned_stream_kernel = true;
+            std::fprintf(stderr, "[b2vp] warning: %s is rendered by the one-thread-per-stream kernel (about 14x slower than the queue kernel)\n",
+                         s->desc.integrator.mis ? "volpathmis" : "a scene with an environment emitter");
+        }
+        kernel = B2VP_KERNEL_STREAM;
     }
-    if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return volpath_q_kernel<F, MAXT, PRE_HOMOG>; }
-    if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return volpath_q_kernel<F, MAXT, PRE_HET>; }
-    if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return volpath_q_kernel<F, MAXT, PRE_HET_ALB>; }
-    *name = "generic";
-    return volpath_q_kernel<F, MAXT, FT_ALL>;
+    if (fast && (kernel == B2VP_KERNEL_LANES || kernel == B2VP_KERNEL_STREAM || kernel == B2VP_KERNEL_QUEUE_256))
+        return fail(B2VP_ERR_INVALID, "B2VP_MATH_FAST exists for the 512-thread queue kernel only");
+    const uint32_t launch_features = ds.g.features | (spd.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
+    const char *preset = "";
+    pl.queue_kernel = kernel == B2VP_KERNEL_AUTO || kernel == B2VP_KERNEL_QUEUE_GENERIC || kernel == B2VP_KERNEL_QUEUE_256;
+    if (pl.queue_kernel) {
+        pl.threads = kernel == B2VP_KERNEL_QUEUE_256 ? 256 : 512;
+        pl.kern = queue_entry<F>(launch_features | (kernel == B2VP_KERNEL_QUEUE_GENERIC ? vp_launch::FORCE_GENERIC : 0u),
+                                 pl.threads, fast, &preset);
+        pl.name = std::string("queue/") + preset + (pl.threads == 512 ? "" : "/256") + (fast ? " fast" : "");
+    } else if (kernel == B2VP_KERNEL_LANES) {
+        pl.kern = lanes_entry<F>(); pl.threads = 256; pl.name = "lanes";
+    } else {
+        pl.kern = stream_entry<F>(); pl.threads = 256; pl.name = "stream (one thread per stream)";
+    }
+    pl.name += sizeof(F) == 4 ? " f32" : " f64";
+    if (pl.queue_kernel) {
+        /* path slots per thread.  With everything hot on chip the shared memory left sets the pool size (the more
+           paths, the longer a CTA stays in one phase).  When large grids are gathered through L2 the cold path
+           records compete with them for it: measured on 2 x 256^3 grids, 2 slots per thread give 90 Mpaths/s,
+           3 and more 56. */
+        const bool big_grids = ds.global_grid_bytes > ((size_t) 16 << 20);
+        double oversub = big_grids ? 2.0 : 4.0;
+        if (a->tuning[0]) oversub = std::min(8.0, std::max(1.0, a->tuning[0] / 16.0));
+        /* shared memory: [tables][grids][film][queue control + rings][path slots] */
+        size_t base = (smem + 127) & ~(size_t) 127;
+        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
+        size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
+        size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
+        size_t n_slots = std::min<size_t>((size_t) (pl.threads * oversub), max_slots) & ~(size_t) 31;
+        if (n_slots < 64)
+            return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
+        n_slots = std::min<size_t>(n_slots, 32768);
+        size_t cap = 64;
+        while (cap < n_slots) cap *= 2;
+        out.q_ctl_offset = (uint32_t) base;
+        size_t qbytes = (sizeof(QueueCtl) + PH_N * cap * sizeof(unsigned short) + 15) & ~(size_t) 15;
+        out.q_slots_offset = (uint32_t) (base + qbytes);
+        out.q_n_slots = (uint32_t) n_slots;
+        out.q_ring_cap = (uint32_t) cap;
+        out.q_stay_min = a->tuning[1] ? std::min(33u, a->tuning[1]) : 26u;
+        out.q_max_iter = a->tuning[2] ? std::min(1024u, a->tuning[2]) : 8u;
+        /* 2: when the CTA moves on, the ray-making phases are served before STEP (+4 % with everything on chip);
+           1: plain fullest-queue order, better when STEP is bound by gather latency (large grids: 93 vs 84 Mpaths/s) */
+        out.q_cta_phase = a->tuning[3] ? std::min(2u, a->tuning[3] - 1u) : (big_grids ? 1u : 2u);
+        smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
+    }
+    int per_sm = 0;
+    CU_CHECK(cudaFuncSetAttribute(pl.kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pl.kern, pl.threads, smem));
+    if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
+    const uint64_t want = (spd.count + pl.threads - 1) / pl.threads;
+    pl.grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+    pl.smem = smem;
+    pl.cold_bytes = pl.queue_kernel ? (size_t) pl.grid * out.q_n_slots * sizeof(PathCold<F>) : 0;
+    return B2VP_OK;
 }
 
-template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
-    CU_CHECK(cudaSetDevice(s->device));
-    DeviceScene<F> &ds = dev_of<F>(s);
-    if (!ds.ready) {
-        int rc = upload_scene<F>(s, ds);
-        if (rc != B2VP_OK) return rc;
-    }
-    StreamSpace sp;
-    int rc = make_stream_space(s, a->seed_mode, a->n_streams, a->explicit_samples_per_stream, sp);
-    if (rc != B2VP_OK) return rc;
+/* stream range of a launch: [first, first + count) or interleaved blocks (B2vpRenderArgs::interleave_*) */
+int set_stream_range(const B2vpRenderArgs *a, StreamSpace &sp) {
     uint64_t first = a->first_stream;
     uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
     if (a->seed_mode == B2VP_SEED_EXPLICIT) { first = 0; count = a->n_streams; }
@@ -758,15 +854,52 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
         if ((B & (B - 1)) == 0) { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
     } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+    sp.d.first = first;
+    sp.d.count = count;
+    return B2VP_OK;
+}
+
+template <typename F>
+cudaError_t launch_kernel(const LaunchPlan &pl, const DeviceScene<F> &ds, const DStreams &spd, const RenderOut<F> &out,
+                          cudaStream_t stream) {
+    void *kargs[3] = { (void *) &ds.g, (void *) &spd, (void *) &out };
+    return cudaLaunchKernel(pl.kern, dim3((unsigned) pl.grid), dim3((unsigned) pl.threads), kargs, pl.smem, stream);
+}
+
+void fill_totals(B2vpCounters &t, const unsigned long long *tot, float ms, uint32_t launches) {
+    std::memset(&t, 0, sizeof(t));
+    t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
+    t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
+    t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
+    t.gpu_ms = ms;
+    t.n_launches = launches;
+}
+
+template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
+    CU_CHECK(cudaSetDevice(s->device));
+    DeviceScene<F> &ds = dev_of<F>(s);
+    if (!ds.ready) {
+        int rc = upload_scene<F>(s, ds);
+        if (rc != B2VP_OK) return rc;
+    }
+    StreamSpace sp;
+    int rc = make_stream_space(s, a->seed_mode, a->n_streams, a->explicit_samples_per_stream, sp);
+    if (rc != B2VP_OK) return rc;
+    rc = set_stream_range(a, sp);
+    if (rc != B2VP_OK) return rc;
+    const uint64_t count = sp.d.count;
     if (a->seed_mode == B2VP_SEED_EXPLICIT && count &&
         (!a->explicit_state || !a->explicit_inc || !a->explicit_pixel))
         return fail(B2VP_ERR_INVALID, "explicit seeding needs state, inc and pixel arrays");
-    sp.d.first = first;
-    sp.d.count = count;
     cudaStream_t stream = (cudaStream_t) a->cuda_stream;
 
     const int W = sp.d.w, H = sp.d.h;
     const size_t film_n = (size_t) W * H * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS), film_bytes = film_n * sizeof(F);
+    RenderOut<F> out{};
+    LaunchPlan pl;
+    rc = plan_launch<F>(s, ds, a, sp.d, film_bytes, out, pl);
+    if (rc != B2VP_OK) return rc;
+
     F *d_film;
     if (a->film_on_device) {
         d_film = (F *) film_user;
@@ -798,10 +931,9 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         sp.d.ex_pixel = s->ex_pixel.as<uint32_t>();
     }
 
-    RenderOut<F> out{};
     out.film = d_film;
     out.totals = s->totals_buf.as<unsigned long long>();
-    const bool want_qstats = std::getenv("B2VP_QSTATS") != nullptr;
+    const bool want_qstats = (a->debug_flags & 1u) != 0;
     if (want_qstats) out.q_stats = out.totals + TOT_N;
     out.work_counter = s->counter_buf.as<unsigned long long>();
     const uint32_t sps = sp.d.samples_per_stream;
@@ -816,92 +948,18 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         CU_CHECK(cudaMemsetAsync(s->o_radiance.p, 0, count * sps * sizeof(F), stream));
         out.out_radiance = s->o_radiance.as<F>();
     }
-
-    /* shared memory: [tables][grids][film] */
-    out.grid_smem_offset = align128(ds.g.blob_bytes);
-    out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
-    out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
-    size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
-    /* kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues
-       (vp_queue.cuh).  B2VP_KERNEL=lanes selects the register-resident warp-voting wavefront
-       (vp_wavefront.cuh), B2VP_KERNEL=mega the one-thread-per-path twin (vp_kernels.cuh): same results. */
-    typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
-    const char *preset = "";
-    const uint32_t launch_features = ds.g.features | (sp.d.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
-    Kern kern = pick_queue_kernel<F, 512>(launch_features, &preset);
-    int threads = 512;
-    bool queue_kernel = true;
-    /* path slots per thread.  With everything hot on chip the shared memory left sets the pool size (the more
-       paths, the longer a CTA stays in one phase).  When large grids are gathered through L2 the cold path
-       records compete with them for it: measured on 2 x 256^3 grids, 2 slots per thread give 90 Mpaths/s,
-       3 and more 56. */
-    double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
-    /* volpathmis runs on the one-thread-per-stream kernel only: its control flow (no direct-light
-       march, path weights as p / f ratios) is not scheduled by the queue kernel yet */
-    bool mis = s->desc.integrator.mis != 0;
-    /* an environment emitter (constant.cpp) changes what happens when a ray escapes and makes emitter sampling
-       non-delta (MIS): handled by the one-thread-per-stream kernel, not by the queue kernel yet */
-    for (const B2vpEmitter &e : s->emitters) mis = mis || e.type == B2VP_EMITTER_CONSTANT;
-    if (mis) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
-    if (const char *e = mis ? nullptr : std::getenv("B2VP_KERNEL")) {
-        if (!std::strcmp(e, "mega")) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
-        else if (!std::strcmp(e, "lanes")) { kern = volpath_wf_kernel<F, 2>; threads = 256; queue_kernel = false; }
-        else if (!std::strcmp(e, "q256")) { kern = pick_queue_kernel<F, 256>(launch_features, &preset); threads = 256; }
-        else if (!std::strcmp(e, "q384")) { threads = 384; }
-#ifdef B2VP_EXPERIMENT
-        else if (!std::strcmp(e, "q768")) { kern = volpath_q_kernel<F, 768, PRE_HET_ALB>; threads = 768; }
-        else if (!std::strcmp(e, "q1024")) { kern = volpath_q_kernel<F, 1024, PRE_HET_ALB>; threads = 1024; }
-#endif
-    }
-    if (const char *e = std::getenv("B2VP_THREADS")) { int t = std::atoi(e); if (queue_kernel && t >= 32 && t <= threads && t % 32 == 0) threads = t; }
-    if (const char *e = std::getenv("B2VP_OVERSUB")) { double v = std::atof(e); if (v >= 1.0 && v <= 8.0) oversub = v; }
-    int per_sm = 0;
-    if (queue_kernel) {
-        /* shared memory: [tables][grids][film][queue control + stacks][path slots] */
-        size_t base = (smem + 127) & ~(size_t) 127;
-        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
-        size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
-        size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
-        size_t n_slots = std::min<size_t>((size_t) (threads * oversub), max_slots) & ~(size_t) 31;
-        if (n_slots < 64)
-            return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
-        n_slots = std::min<size_t>(n_slots, 32768);
-        size_t cap = 64;
-        while (cap < n_slots) cap *= 2;
-        out.q_ctl_offset = (uint32_t) base;
-        size_t qbytes = (sizeof(QueueCtl) + PH_N * cap * sizeof(unsigned short) + 15) & ~(size_t) 15;
-        out.q_slots_offset = (uint32_t) (base + qbytes);
-        out.q_n_slots = (uint32_t) n_slots;
-        out.q_ring_cap = (uint32_t) cap;
-        out.q_stay_min = 26; out.q_max_iter = 8;
-        /* 2: when the CTA moves on, the ray-making phases are served before STEP (+4 % with everything on chip);
-           1: plain fullest-queue order, better when STEP is bound by gather latency (large grids: 93 vs 84 Mpaths/s) */
-        out.q_cta_phase = ds.global_grid_bytes > ((size_t) 16 << 20) ? 1u : 2u;
-        if (const char *e = std::getenv("B2VP_CTA_PHASE")) out.q_cta_phase = (uint32_t) std::atoi(e);
-        if (const char *e = std::getenv("B2VP_STAY")) { int v = std::atoi(e); if (v >= 1 && v <= 33) out.q_stay_min = (uint32_t) v; }
-        if (const char *e = std::getenv("B2VP_ITER")) { int v = std::atoi(e); if (v >= 1 && v <= 1024) out.q_max_iter = (uint32_t) v; }
-        smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
-    }
-    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-    if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
-    uint64_t want = (count + threads - 1) / threads;
-    int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
-    if (queue_kernel) {
+    if (pl.queue_kernel) {
         /* cold per-path state: one PathCold array per CTA in global memory (L2-resident) */
-        const size_t cold_bytes = (size_t) grid * out.q_n_slots * sizeof(PathCold<F>);
-        if (s->q_cold.bytes < cold_bytes) CU_CHECK(s->q_cold.alloc(cold_bytes));
+        if (s->q_cold.bytes < pl.cold_bytes) CU_CHECK(s->q_cold.alloc(pl.cold_bytes));
         out.q_cold = s->q_cold.p;
     }
+    s->last_kernel = pl.name;
 
-    s->last_kernel = queue_kernel ? std::string("queue/") + preset + (threads == 512 ? "" : "/" + std::to_string(threads))
-                     : kern == (Kern) volpath_kernel<F> ? "stream (one thread per stream)" : "lanes";
-    s->last_kernel += sizeof(F) == 4 ? " f32" : " f64";
     if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     uint32_t launches = 0;
     CU_CHECK(cudaEventRecord(s->ev0, stream));
     if (count) {
-        kern<<<grid, threads, smem, stream>>>(ds.g, sp.d, out);
+        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream));
         launches++;
     }
     CU_CHECK(cudaEventRecord(s->ev1, stream));
@@ -927,15 +985,9 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
                          q[p] ? (double) q[8 + p] / (double) q[p] : 0.0);
     }
     if (a->totals) {
-        B2vpCounters &t = *a->totals;
-        std::memset(&t, 0, sizeof(t));
-        t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
-        t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
-        t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
         float ms = 0;
         CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-        t.gpu_ms = ms;
-        t.n_launches = launches;
+        fill_totals(*a->totals, tot, ms, launches);
     }
     return B2VP_OK;
 }
@@ -972,8 +1024,6 @@ int noalloc_scratch(int device, unsigned char **out) {
     return B2VP_OK;
 }
 
-inline size_t align256(size_t x) { return (x + 255) & ~(size_t) 255; }
-
 template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_device) {
     CU_CHECK(cudaSetDevice(s->device));
     DeviceScene<F> &ds = dev_of<F>(s);
@@ -988,81 +1038,28 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
     StreamSpace sp;
     int rc = make_stream_space(s, a->seed_mode, a->n_streams, a->explicit_samples_per_stream, sp);
     if (rc != B2VP_OK) return rc;
-    const uint64_t first = a->first_stream;
-    const uint64_t count = a->n_streams ? a->n_streams : (first <= sp.n_streams ? sp.n_streams - first : 0);
-    sp.d.il_block = 0; sp.d.il_count = 1; sp.d.il_index = 0; sp.d.il_shift = -1;
-    if (a->interleave_block) {
-        if (!a->n_streams || !a->interleave_count || a->interleave_index >= a->interleave_count)
-            return fail(B2VP_ERR_INVALID, "invalid interleaved stream range");
-        const uint64_t B = a->interleave_block, kmax = count - 1;
-        const uint64_t last = first + ((kmax / B) * a->interleave_count + a->interleave_index) * B + kmax % B;
-        if (last >= sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
-        sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
-        if ((B & (B - 1)) == 0) { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
-    } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
-    sp.d.first = first;
-    sp.d.count = count;
+    rc = set_stream_range(a, sp);
+    if (rc != B2VP_OK) return rc;
+    const uint64_t count = sp.d.count;
     cudaStream_t stream = (cudaStream_t) a->cuda_stream;
-
-    const int W = sp.d.w, H = sp.d.h;
-    const size_t film_n = (size_t) W * H * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS);
+    const size_t film_n = (size_t) sp.d.w * sp.d.h * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS);
     const size_t film_bytes = film_n * sizeof(F);
     F *d_film = (F *) film_device;
-
-    /* kernel and launch shape: the product defaults of render_typed (no environment overrides) */
     RenderOut<F> out{};
     out.film = d_film;
-    out.grid_smem_offset = align128(ds.g.blob_bytes);
-    out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
-    out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
-    size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
-    typedef void (*Kern)(const DScene<F>, const DStreams, const RenderOut<F>);
-    const char *preset = "";
-    const uint32_t launch_features = ds.g.features | (sp.d.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
-    Kern kern = pick_queue_kernel<F, 512>(launch_features, &preset);
-    int threads = 512;
-    bool queue_kernel = true;
-    const double oversub = ds.global_grid_bytes > ((size_t) 16 << 20) ? 2.0 : 4.0;
-    bool mis = s->desc.integrator.mis != 0;
-    for (const B2vpEmitter &e : s->emitters) mis = mis || e.type == B2VP_EMITTER_CONSTANT;
-    if (mis) { kern = volpath_kernel<F>; threads = 256; queue_kernel = false; }
-    if (queue_kernel) {
-        size_t base = (smem + 127) & ~(size_t) 127;
-        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
-        size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
-        size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
-        size_t n_slots = std::min<size_t>((size_t) (threads * oversub), max_slots) & ~(size_t) 31;
-        if (n_slots < 64)
-            return fail(B2VP_ERR_CUDA, "not enough shared memory for the path-slot pool (%zu bytes free)", avail);
-        n_slots = std::min<size_t>(n_slots, 32768);
-        size_t cap = 64;
-        while (cap < n_slots) cap *= 2;
-        out.q_ctl_offset = (uint32_t) base;
-        size_t qbytes = (sizeof(QueueCtl) + PH_N * cap * sizeof(unsigned short) + 15) & ~(size_t) 15;
-        out.q_slots_offset = (uint32_t) (base + qbytes);
-        out.q_n_slots = (uint32_t) n_slots;
-        out.q_ring_cap = (uint32_t) cap;
-        out.q_stay_min = 26; out.q_max_iter = 8;
-        out.q_cta_phase = ds.global_grid_bytes > ((size_t) 16 << 20) ? 1u : 2u;
-        smem = out.q_slots_offset + n_slots * sizeof(PathSlot<F>);
-    }
-    int per_sm = 0;
-    CU_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-    if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
-    const uint64_t want = (count + threads - 1) / threads;
-    const int grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+    LaunchPlan pl;
+    rc = plan_launch<F>(s, ds, a, sp.d, film_bytes, out, pl);
+    if (rc != B2VP_OK) return rc;
 
     /* scratch layout inside the static array: [totals + work counter][spiral blocks][cold path records] */
     const size_t head_bytes = align256((TOT_N + 32 + 1) * sizeof(unsigned long long));
     const size_t blocks_bytes = a->seed_mode == B2VP_SEED_SCALAR_BLOCKS ? align256(sp.blocks.size() * sizeof(SpiralBlockD)) : 0;
-    const size_t cold_bytes = queue_kernel ? (size_t) grid * out.q_n_slots * sizeof(PathCold<F>) : 0;
-    const size_t need = head_bytes + blocks_bytes + cold_bytes;
+    const size_t need = head_bytes + blocks_bytes + pl.cold_bytes;
     if (need > (size_t) B2VP_NOALLOC_SCRATCH_BYTES)
         return fail(B2VP_ERR_UNSUPPORTED,
                     "b2vp_render_noalloc: this launch needs %zu bytes of scratch (%zu header, %zu spiral blocks, %zu path "
                     "records), the static scratch array holds B2VP_NOALLOC_SCRATCH_BYTES = %zu; use b2vp_render",
-                    need, head_bytes, blocks_bytes, cold_bytes, (size_t) B2VP_NOALLOC_SCRATCH_BYTES);
+                    need, head_bytes, blocks_bytes, pl.cold_bytes, (size_t) B2VP_NOALLOC_SCRATCH_BYTES);
     unsigned char *scr = nullptr;
     rc = noalloc_scratch(s->device, &scr);
     if (rc != B2VP_OK) return rc;
@@ -1074,13 +1071,14 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
                                  cudaMemcpyHostToDevice, stream));
         sp.d.blocks = reinterpret_cast<const SpiralBlockD *>(scr + head_bytes);
     }
-    if (queue_kernel) out.q_cold = scr + head_bytes + blocks_bytes;   /* every field is written before it is read */
+    if (pl.queue_kernel) out.q_cold = scr + head_bytes + blocks_bytes;   /* every field is written before it is read */
     if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
+    s->last_kernel = pl.name;
 
     uint32_t launches = 0;
     CU_CHECK(cudaEventRecord(s->ev0, stream));
     if (count) {
-        kern<<<grid, threads, smem, stream>>>(ds.g, sp.d, out);
+        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream));
         launches++;
     }
     CU_CHECK(cudaEventRecord(s->ev1, stream));
@@ -1089,15 +1087,9 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
     CU_CHECK(cudaMemcpyAsync(tot, out.totals, sizeof(tot), cudaMemcpyDeviceToHost, stream));
     CU_CHECK(cudaStreamSynchronize(stream));   /* also keeps sp.blocks alive until the copy above has run */
     if (a->totals) {
-        B2vpCounters &t = *a->totals;
-        std::memset(&t, 0, sizeof(t));
-        t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
-        t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
-        t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
         float ms = 0;
         CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-        t.gpu_ms = ms;
-        t.n_launches = launches;
+        fill_totals(*a->totals, tot, ms, launches);
     }
     return B2VP_OK;
 }

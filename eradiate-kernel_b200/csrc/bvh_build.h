@@ -15,7 +15,7 @@
 
 #include "vp_types.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 struct BuildTri { float bmin[3], bmax[3], c[3]; uint32_t shape, face; };
 
@@ -142,4 +142,4 @@ inline void bvh_build(std::vector<BuildTri> &tris, float pad, std::vector<BvhNod
     if (stats) *stats = st;
 }
 
-} // namespace vp
+} // namespace VP_NS

@@ -10,7 +10,7 @@
 #pragma once
 #include "vp_scene.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 template <typename F> struct PathCtx {
     const SceneView<F> &sv;
@@ -622,4 +622,4 @@ template <typename F> struct PathCtx {
     }
 };
 
-} // namespace vp
+} // namespace VP_NS

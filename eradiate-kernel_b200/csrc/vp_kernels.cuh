@@ -12,7 +12,7 @@
 #pragma once
 #include "vp_integrator.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 enum { SEED_SCALAR_BLOCKS = 0, SEED_WAVEFRONT = 1, SEED_EXPLICIT = 2 };
 enum { TOT_PATHS = 0, TOT_DRAWS, TOT_STEPS, TOT_NULL, TOT_REAL, TOT_ISECT, TOT_SURF, TOT_INVALID, TOT_N };
@@ -111,6 +111,9 @@ VP_D void stage_scene(const DScene<F> &g, const RenderOut<F> &out, unsigned char
     sv.phases = reinterpret_cast<const DPhase<F> *>(smem + g.ofs_phases);
     sv.emitters = reinterpret_cast<const DEmitter<F> *>(smem + g.ofs_emitters);
     sv.grid_smem = smem + out.grid_smem_offset;
+    sv.grid_saddr = smem_addr(sv.grid_smem);
+    sv.bvh_saddr = smem_addr(smem + g.ofs_bvh);
+    sv.tri_saddr = smem_addr(smem + g.ofs_bvh_tris);
 
     if (g.grid_smem_bytes > 0) {
         /* TMA bulk copies global -> shared, completion counted on an mbarrier */
@@ -243,4 +246,4 @@ volpath_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStr
     }
 }
 
-} // namespace vp
+} // namespace VP_NS

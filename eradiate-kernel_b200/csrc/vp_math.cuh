@@ -19,7 +19,17 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
-namespace vp {
+/* The kernel headers are compiled in several translation units (csrc/kern_*.cu).  The exact ones share namespace
+   vp; the tolerance-mode unit (kern_q32_fast.cu: FMA contraction, hardware approximations, VP_FASTMATH = 1)
+   compiles the same text in its own namespace so that the two sets of inline functions never meet at link time. */
+#ifndef VP_NS
+#define VP_NS vp
+#endif
+#ifndef VP_FASTMATH
+#define VP_FASTMATH 0
+#endif
+
+namespace VP_NS {
 
 #define VP_HD __host__ __device__ __forceinline__
 #define VP_D __device__ __forceinline__
@@ -42,9 +52,17 @@ template <> VP_D double real_of<double>(uint64_t u) { return __longlong_as_doubl
 
 VP_D float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 VP_D double fma_(double a, double b, double c) { return __fma_rn(a, b, c); }
+#if VP_FASTMATH
+VP_D float sqrt_(float x) { return sqrtf(x); }   /* -prec-sqrt=false: MUFU.RSQ based */
+#else
 VP_D float sqrt_(float x) { return __fsqrt_rn(x); }
+#endif
 VP_D double sqrt_(double x) { return __dsqrt_rn(x); }
+#if VP_FASTMATH
+VP_D float div_(float a, float b) { return __fdividef(a, b); }
+#else
 VP_D float div_(float a, float b) { return __fdiv_rn(a, b); }
+#endif
 VP_D double div_(double a, double b) { return __ddiv_rn(a, b); }
 VP_D float floor_(float x) { return floorf(x); }
 VP_D double floor_(double x) { return floor(x); }
@@ -85,6 +103,11 @@ template <typename T> VP_D T split2(T x, int &e) {
 }
 
 /* ---------------------------------------------------------------- log --- */
+#if VP_FASTMATH
+/* Tolerance mode: MUFU.LG2 / MUFU.EX2.  __logf has an absolute error of about 2^-21.4 near 1,
+   which on the free-flight distance -log(1 - u) / sigma is 4e-7 mean free paths: the size of fp32 position rounding. */
+VP_D float log_(float x) { return __logf(x); }
+#else
 VP_D float log_(float x) {
     if (!(x >= 0.f)) return Lim<float>::nan();
     if (x == 0.f) return -Lim<float>::inf();
@@ -110,6 +133,7 @@ VP_D float log_(float x) {
     z = fma_(z, -0.5f, m + y);
     return fma_(e, 0.693359375f, z);
 }
+#endif
 
 VP_D double log_(double x) {
     if (!(x >= 0.0)) return Lim<double>::nan();
@@ -159,6 +183,9 @@ VP_D double log_(double x) {
 }
 
 /* ---------------------------------------------------------------- exp --- */
+#if VP_FASTMATH
+VP_D float exp_(float x) { return __expf(x); }
+#else
 VP_D float exp_(float x) {
     if (x > 88.3762588501f) return Lim<float>::inf();
     if (x < -88.3762588501f) return 0.f;
@@ -175,6 +202,7 @@ VP_D float exp_(float x) {
     z = fma_(z, xr * xr, xr + 1.f);
     return scale2(z, (int) n);
 }
+#endif
 
 VP_D double exp_(double x) {
     if (x > 7.0943613930310391424428e2) return Lim<double>::inf();
@@ -198,6 +226,12 @@ VP_D double exp_(double x) {
 }
 
 template <typename T> VP_D T pow_(T x, T y) { return exp_(log_(x) * y); }
+#if VP_FASTMATH
+/* pow (RPV), sincos (azimuths, sensor directions) and cbrt (Rayleigh) run once per scattering or surface event, not per
+   tentative collision: the accurate library versions cost nothing measurable and keep the per-path error down.  Only
+   what the STEP phase evaluates per collision -- log, exp, division, reciprocal, square root -- is approximate. */
+VP_D float pow_(float x, float y) { return powf(x, y); }
+#endif
 
 /* ------------------------------------------------------------- sincos --- */
 template <typename T> struct TrigK;
@@ -239,6 +273,9 @@ template <> struct TrigK<double> {
 };
 
 /* joint sine / cosine, |x| < ~8192 (arguments here are 2*pi*u, pi*u, disk angles) */
+#if VP_FASTMATH
+VP_D void sincos_(float x, float &s_out, float &c_out) { sincosf(x, &s_out, &c_out); }
+#endif
 template <typename T> VP_D void sincos_(T x, T &s_out, T &c_out) {
     using K = TrigK<T>;
     T xa = x < 0 ? -x : x;
@@ -260,6 +297,9 @@ template <typename T> VP_D void sincos_(T x, T &s_out, T &c_out) {
 }
 
 /* --------------------------------------------------------------- cbrt --- */
+#if VP_FASTMATH
+VP_D float cbrt_(float x) { return cbrtf(x); }
+#endif
 template <typename T> VP_D T cbrt_(T x) {
     if (x == 0 || x != x || x == Lim<T>::inf() || x == -Lim<T>::inf())
         return x;
@@ -289,4 +329,4 @@ template <typename T> VP_D T cbrt_(T x) {
 
 template <typename T> VP_D T safe_sqrt_(T x) { return sqrt_(x > 0 ? x : (T) 0); }
 
-} // namespace vp
+} // namespace VP_NS

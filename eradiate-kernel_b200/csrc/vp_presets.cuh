@@ -1,0 +1,41 @@
+/*
+ * vp_presets.cuh -- queue-kernel instances: the generic one and presets for the common scene classes
+ * (see vp_scene.cuh, FT_*: a preset carries no code for features its scenes do not use).
+ */
+#pragma once
+#include "vp_queue.cuh"
+
+namespace VP_NS {
+
+/* rectangles and small meshes (BVH staged in shared memory), no sphere (double-precision quadratic) */
+constexpr uint32_t PRE_FLAT = FT_RECT | FT_MESH_SMEM | FT_MESH_ATTR;
+constexpr uint32_t PRE_HOMOG = PRE_FLAT | FT_HOMOG;                                      /* C1 */
+constexpr uint32_t PRE_HOMOG_BIG = FT_RECT | FT_MESH | FT_MESH_ATTR | FT_HOMOG;          /* C5: BVH in global memory */
+constexpr uint32_t PRE_HET = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_SMEM;         /* C2, C4: grid staged */
+constexpr uint32_t PRE_HET_G = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_GLOBAL;     /* large sigma_t grid, constant albedo */
+constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO | FT_GRID_GLOBAL;   /* C3 */
+
+template <typename F, int MAXT, uint32_t FEAT> const void *q_entry() {
+    return reinterpret_cast<const void *>(&volpath_q_kernel<F, MAXT, FEAT>);
+}
+
+template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool force_generic, const char **name) {
+    if (force_generic) ft = FT_ALL;
+    /* interleaved launches (multi-GPU sharding): the two scene classes the benchmarks shard have an instance with
+       the interleaved stream mapping, everything else goes to the generic instance */
+    if (ft & FT_INTERLEAVE) {
+        if ((ft & ~(PRE_HET | FT_INTERLEAVE)) == 0) { *name = "heterogeneous, interleaved"; return q_entry<F, MAXT, PRE_HET | FT_INTERLEAVE>(); }
+        if ((ft & ~(PRE_HET_ALB | FT_INTERLEAVE)) == 0) { *name = "heterogeneous+albedo grid, interleaved"; return q_entry<F, MAXT, PRE_HET_ALB | FT_INTERLEAVE>(); }
+        *name = "generic";
+        return q_entry<F, MAXT, FT_ALL>();
+    }
+    if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return q_entry<F, MAXT, PRE_HOMOG>(); }
+    if ((ft & ~PRE_HOMOG_BIG) == 0) { *name = "homogeneous, large mesh"; return q_entry<F, MAXT, PRE_HOMOG_BIG>(); }
+    if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return q_entry<F, MAXT, PRE_HET>(); }
+    if ((ft & ~PRE_HET_G) == 0) { *name = "heterogeneous, grid in HBM"; return q_entry<F, MAXT, PRE_HET_G>(); }
+    if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return q_entry<F, MAXT, PRE_HET_ALB>(); }
+    *name = "generic";
+    return q_entry<F, MAXT, FT_ALL>();
+}
+
+} // namespace VP_NS

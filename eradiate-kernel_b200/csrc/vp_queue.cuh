@@ -33,7 +33,7 @@
 #pragma once
 #include "vp_kernels.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 enum QState : int {
     Q_STEP = 0,     /* one tentative-collision step                            */
@@ -80,10 +80,14 @@ template <typename F> struct MarchCtx {
    tentative-collision step reads and writes every iteration; PathCold (global memory, L2-resident, one
    array per CTA) holds what only the rarer phases need.  The smaller the shared-memory slot, the more paths
    a CTA keeps in flight and the fuller its batches. */
+/* PathSlot is 35 words in fp32: an ODD word stride, so that one field of the 32 slots of a batch spreads over the 32
+   shared-memory banks (slot ids within a batch are arbitrary; with the even stride of an 8-byte aligned record one
+   field of 32 slots could reach 16 banks at most -- 61 % of all shared wavefronts were conflict replays in the round-1
+   capture).  That is why the two PCG32 words are stored as 32-bit halves (4-byte alignment). */
 template <typename F> struct PathSlot {
-    unsigned long long rng_state, rng_inc;
+    uint32_t rng_state_lo, rng_state_hi, rng_inc_lo, rng_inc_hi;
     uint32_t rng_draws;
-    uint32_t c_steps, c_null;
+    uint32_t c_steps, c_null, c_isect;
     uint32_t flags;
     MarchCtx<F> cur;
     F eta;
@@ -93,7 +97,7 @@ template <typename F> struct PathSlot {
 template <typename F> struct PathCold {
     unsigned long long k;
     uint32_t j;
-    uint32_t c_real, c_isect, c_surf;
+    uint32_t c_real, c_surf;
     MarchCtx<F> saved;                    /* the main path's context during a march */
     uint32_t prim; F bu, bv;              /* mesh face and barycentrics of the main path's hit */
     F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* its shading frame, completed at the surface event  */
@@ -114,6 +118,15 @@ struct QueueCtl {
 };
 #define Q_EMPTY 0xffffu
 
+template <typename F> VP_D void ld_rng(const PathSlot<F> &s, Pcg32 &rng) {
+    rng.state = ((uint64_t) s.rng_state_hi << 32) | s.rng_state_lo;
+    rng.inc = ((uint64_t) s.rng_inc_hi << 32) | s.rng_inc_lo;
+    rng.draws = s.rng_draws;
+}
+template <typename F> VP_D void st_rng(PathSlot<F> &s, const Pcg32 &rng) {   /* the increment never changes */
+    s.rng_state_lo = (uint32_t) rng.state; s.rng_state_hi = (uint32_t) (rng.state >> 32);
+    s.rng_draws = rng.draws;
+}
 template <typename F> VP_D void ld_ray(const MarchCtx<F> &c, Ray<F> &r) {
     r.o = ld3(c.o); r.d = ld3(c.d); r.d_rcp = ld3(c.d_rcp); r.mint = c.mint; r.maxt = c.maxt;
 }
@@ -150,7 +163,7 @@ VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> 
                             PathCounters &cnt, uint32_t &fl, int &state) {
     SurfaceHit<F> h;
     ray_intersect<F, FEAT, false>(sv, ir, h, cnt);
-    c.c_isect += 1;
+    s.c_isect += 1;
     s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
     if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here: keep what
                          surface_frame() needs to finish it */
@@ -338,7 +351,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             r.o = mi.p; r.d = mi.p; r.d_rcp = mi.p; r.mint = 0; r.maxt = 0;
             rng.state = 0; rng.inc = 1; rng.draws = 0;
             if (mine) {
-                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                ld_rng(s, rng);
                 ld_ray(s.cur, r);
                 med = s.cur.medium;
                 w = s.cur.w;
@@ -456,7 +469,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 else st = Q_MARCH_END;
             }
             if (mine) {
-                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                st_rng(s, rng);
                 s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
                 st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
                 s.cur.w = w;
@@ -474,7 +487,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 uint32_t fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 Pcg32 rng;
-                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                ld_rng(s, rng);
                 const int med = s.cur.medium;
                 const DMedium<F> &m = sv.media[med];
                 const V3<F> d = ld3(s.cur.d);
@@ -530,7 +543,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                     s.cur.w = w;
                 }
-                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                st_rng(s, rng);
                 if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
@@ -540,7 +553,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 uint32_t fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 Pcg32 rng;
-                rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                ld_rng(s, rng);
                 const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
                 const DBsdf<F> &bsdf = sv.bsdfs[sh.bsdf];
                 const V3<F> sp_ = ld3(s.cur.hit_p);
@@ -630,7 +643,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                     s.cur.w = throughput;
                 }
-                s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                st_rng(s, rng);
                 if (do_isect) {
                     if (start_dl) intersect_new_ray<F, FEAT, true>(sv, s, c, ir, isect_main, cnt, fl, state);
                     else intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
@@ -738,15 +751,15 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         film_add(p, a0); film_add(p + 1, a0); film_add(p + 2, a0);
                         film_add(p + 3, c.acc3); film_add(p + 4, c.acc4);
                     }
-                    if (out.out_state) out.out_state[k] = s.rng_state;
+                    if (out.out_state) out.out_state[k] = ((uint64_t) s.rng_state_hi << 32) | s.rng_state_lo;
                     if (out.out_counters) {
                         PathCounters o;
                         o.draws = s.rng_draws; o.medium_steps = s.c_steps; o.n_null = s.c_null; o.n_real = c.c_real;
-                        o.n_intersect = c.c_isect; o.n_surface = c.c_surf;
+                        o.n_intersect = s.c_isect; o.n_surface = c.c_surf;
                         out.out_counters[k] = o;
                     }
                     tot[TOT_DRAWS] += s.rng_draws; tot[TOT_STEPS] += s.c_steps; tot[TOT_NULL] += s.c_null;
-                    tot[TOT_REAL] += c.c_real; tot[TOT_ISECT] += c.c_isect; tot[TOT_SURF] += c.c_surf;
+                    tot[TOT_REAL] += c.c_real; tot[TOT_ISECT] += s.c_isect; tot[TOT_SURF] += c.c_surf;
                     fl &= ~(QF_HAVE_STREAM | QF_ACC_USED);
                 }
                 if (!(fl & QF_HAVE_STREAM)) {
@@ -756,8 +769,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     } else {
                         StreamInfo st = make_stream(sp, stream_index<(FEAT & FT_INTERLEAVE) != 0>(sp, k));
                         c.k = k;
-                        s.rng_state = st.state; s.rng_inc = st.inc; s.rng_draws = 0;
-                        s.c_steps = 0; s.c_null = 0; c.c_real = 0; c.c_isect = 0; c.c_surf = 0;
+                        s.rng_state_lo = (uint32_t) st.state; s.rng_state_hi = (uint32_t) (st.state >> 32);
+                        s.rng_inc_lo = (uint32_t) st.inc; s.rng_inc_hi = (uint32_t) (st.inc >> 32);
+                        s.rng_draws = 0;
+                        s.c_steps = 0; s.c_null = 0; s.c_isect = 0; c.c_real = 0; c.c_surf = 0;
                         c.acc0 = 0; c.acc3 = 0; c.acc4 = 0;
                         j = 0;
                         px = st.px; py = st.py; empty = st.empty;
@@ -769,7 +784,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     /* render_sample prologue (integrator.cpp:233-264); an empty stream (pixel outside its
                        block) is finished on the next visit */
                     Pcg32 rng;
-                    rng.state = s.rng_state; rng.inc = s.rng_inc; rng.draws = s.rng_draws;
+                    ld_rng(s, rng);
                     F posx = (F) (uint32_t) px + rng.next(F(), true);
                     F posy = (F) (uint32_t) py + rng.next(F(), true);
                     F apx = (F) 0.5, apy = (F) 0.5;
@@ -781,7 +796,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     Ray<F> ray;
                     c.ray_weight = sensor_sample_ray<F, FEAT>(sv, ax, ay, apx, apy, ray);
                     c.posx = posx; c.posy = posy;
-                    s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                    st_rng(s, rng);
                     /* VolumetricPathIntegrator::sample prologue (volpath.cpp:45-70) */
                     st_ray(s.cur, ray);
                     s.cur.hit_t = INF; s.cur.hit_shape = -1;
@@ -797,7 +812,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         state = Q_PATH_END;
                     }
                     s.cur.w = w0;
-                    s.rng_state = rng.state; s.rng_inc = rng.inc; s.rng_draws = rng.draws;
+                    st_rng(s, rng);
                     if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, true, cnt, fl, state);
                 }
                 s.flags = (fl & ~QF_STATE) | (uint32_t) state;
@@ -842,4 +857,4 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     }
 }
 
-} // namespace vp
+} // namespace VP_NS

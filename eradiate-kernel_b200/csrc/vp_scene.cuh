@@ -9,7 +9,7 @@
 #pragma once
 #include "vp_types.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 /* Per-thread view of the scene: table pointers resolved to shared memory when
    the CTA staged them there. */
@@ -23,7 +23,20 @@ template <typename F> struct SceneView {
     const DPhase<F> *phases;
     const DEmitter<F> *emitters;
     const unsigned char *grid_smem; /* base of the staged grids */
+    /* 32-bit shared-memory addresses (ld.shared) of what the CTA staged: the grids, and -- for scenes whose meshes
+       are small (the 12-triangle cube of the atmosphere scenes) -- the BVH nodes and leaf triangles, which are part
+       of the table blob then.  Read with explicit ld.shared: a pointer that may be shared OR global is a generic
+       pointer to the compiler, and generic loads cost a trip through the global-memory pipeline. */
+    uint32_t grid_saddr, bvh_saddr, tri_saddr;
 };
+
+VP_D float4 lds_f4(uint32_t a) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+VP_D float lds_real(uint32_t a, float) { float v; asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+VP_D double lds_real(uint32_t a, double) { double v; asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
 
 template <typename F> struct SurfaceHit {
     F t;
@@ -53,14 +66,18 @@ enum : uint32_t {
     FT_PROJECTIVE = 1u << 8,   /* a grid's world_to_local has a non-trivial last row      */
     FT_RECT = 1u << 9,         /* a rectangle is present                                  */
     FT_SPHERE = 1u << 10,      /* a sphere is present                                     */
-    FT_MESH = 1u << 11,        /* a triangle mesh is present                              */
+    FT_MESH = 1u << 11,        /* triangle meshes whose BVH is read from global memory    */
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
     FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter       */
     FT_INTERLEAVE = 1u << 16,  /* the launch renders interleaved stream blocks (multi-GPU) */
-    FT_ALL = 0x1ffffu
+    FT_GRID_SMEM = 1u << 17,   /* some grid is staged in shared memory                    */
+    FT_GRID_GLOBAL = 1u << 18, /* some grid is read from global memory                    */
+    FT_MESH_SMEM = 1u << 19,   /* triangle meshes whose BVH and triangles are staged in shared memory (small meshes) */
+    FT_ALL = 0xfffffu
 };
+constexpr uint32_t FT_ANY_MESH = FT_MESH | FT_MESH_SMEM;
 
 
 /* Rectangle::ray_intersect_preliminary (src/shapes/rectangle.cpp:139-159) */
@@ -110,11 +127,25 @@ template <typename F> VP_D V3<F> load_vertex(const DScene<F> &g, const DShape<F>
     return mk3<F>((F) __ldg(p), (F) __ldg(p + 1), (F) __ldg(p + 2));
 }
 
+/* Where the BVH lives for this kernel instance: staged in shared memory (FT_MESH_SMEM), in global memory (FT_MESH), or
+   decided per scene at run time when the instance is compiled for both (the all-features instance). */
+template <typename F, uint32_t FEAT> struct BvhMem {
+    const float4 *nodes, *tris;
+    uint32_t nodes_s, tris_s;
+    bool smem;
+    VP_D BvhMem(const SceneView<F> &sv)
+        : nodes(reinterpret_cast<const float4 *>(sv.g->bvh)), tris(reinterpret_cast<const float4 *>(sv.g->bvh_tris)),
+          nodes_s(sv.bvh_saddr), tris_s(sv.tri_saddr),
+          smem((FEAT & FT_MESH_SMEM) && (!(FEAT & FT_MESH) || sv.g->bvh_in_blob)) {}
+    /* k-th 16-byte quarter after node i (a node is 32 bytes; two sibling nodes are adjacent) */
+    VP_D float4 node(uint32_t i, int k) const { return smem ? lds_f4(nodes_s + i * 32u + (uint32_t) k * 16u) : __ldg(nodes + 2 * (size_t) i + k); }
+    VP_D float4 tri(uint32_t i, int k) const { return smem ? lds_f4(tris_s + i * 48u + (uint32_t) k * 16u) : __ldg(tris + 3 * (size_t) i + k); }
+};
+
 /* One leaf triangle of the BVH: the three vertex positions (always f32, mesh.h:22-28) and its (shape, face). */
-template <typename F>
-VP_D void load_bvh_tri(const DScene<F> &g, uint32_t i, V3<F> &p0, V3<F> &p1, V3<F> &p2, BvhPrim &pr) {
-    const float4 *t = reinterpret_cast<const float4 *>(g.bvh_tris + i);
-    const float4 a = __ldg(t), b = __ldg(t + 1), c = __ldg(t + 2);
+template <typename F, uint32_t FEAT>
+VP_D void load_bvh_tri(const BvhMem<F, FEAT> &bm, uint32_t i, V3<F> &p0, V3<F> &p1, V3<F> &p2, BvhPrim &pr) {
+    const float4 a = bm.tri(i, 0), b = bm.tri(i, 1), c = bm.tri(i, 2);
     p0 = mk3<F>((F) a.x, (F) a.y, (F) a.z);
     p1 = mk3<F>((F) a.w, (F) b.x, (F) b.y);
     p2 = mk3<F>((F) b.z, (F) b.w, (F) c.x);
@@ -197,7 +228,8 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
        distance, so that it can be skipped once a closer hit is known.  Visiting order does not change the
        answer: the winner is the smallest t, ties going to the later (shape, face), and boxes that touch the
        current maxt are still visited. */
-    if ((FEAT & FT_MESH) && g.n_bvh_nodes > 0) {
+    const BvhMem<F, FEAT> bm(sv);
+    if ((FEAT & FT_ANY_MESH) && g.n_bvh_nodes > 0) {
         uint32_t stack_n[64];
         float stack_t[64];
         int sp = 0;
@@ -223,8 +255,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         uint32_t cur;
         bool have;
         {
-            const float4 *n = reinterpret_cast<const float4 *>(g.bvh);
-            const float4 a = __ldg(n), b = __ldg(n + 1);
+            const float4 a = bm.node(0, 0), b = bm.node(0, 1);
             float tn;
             have = slab(a, b, inflate_max((float) ray.maxt), tn);
             cur = ref_of(a, b);
@@ -232,8 +263,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         while (have) {
             const uint32_t count = cur >> 29, first = cur & 0x1fffffffu;
             if (count == 0) {
-                const float4 *n = reinterpret_cast<const float4 *>(g.bvh + first);
-                const float4 a0 = __ldg(n), b0 = __ldg(n + 1), a1 = __ldg(n + 2), b1 = __ldg(n + 3);
+                const float4 a0 = bm.node(first, 0), b0 = bm.node(first, 1), a1 = bm.node(first, 2), b1 = bm.node(first, 3);
                 const float cur_max = inflate_max((float) ray.maxt);
                 float t0, t1;
                 const bool h0 = slab(a0, b0, cur_max, t0), h1 = slab(a1, b1, cur_max, t1);
@@ -252,7 +282,7 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
                     /* leaf triangles are stored by value in leaf order: three 16-byte loads per test */
                     V3<F> p0, p1, p2;
                     BvhPrim pr;
-                    load_bvh_tri(g, first + k, p0, p1, p2, pr);
+                    load_bvh_tri(bm, first + k, p0, p1, p2, pr);
                     F u, v;
                     F t = triangle_intersect(p0, p1, p2, ray, u, v);
                     if (t != inf_<F>()) {
@@ -304,11 +334,11 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
         }
         if (sh.flip_normals) si.sh.n = -si.sh.n;
         si.n = si.sh.n;
-    } else if (FEAT & FT_MESH) { /* src/librender/mesh.cpp:450-545 */
+    } else if (FEAT & FT_ANY_MESH) { /* src/librender/mesh.cpp:450-545 */
         F b1 = best_u, b2 = best_v, b0 = (F) 1 - b1 - b2;
         V3<F> p0, p1, p2;
         BvhPrim pr;
-        load_bvh_tri(g, best_tri, p0, p1, p2, pr);
+        load_bvh_tri(bm, best_tri, p0, p1, p2, pr);
         V3<F> dp0 = p1 - p0, dp1 = p2 - p0;
         si.p = p0 * b0 + p1 * b1 + p2 * b2;
         si.n = normalize(cross(dp0, dp1));
@@ -360,7 +390,7 @@ __device__ __noinline__ void surface_frame(const SceneView<F> &sv, V3<F> d, Surf
         V3<F> local = xf_point_affine(sh.to_object, si.p);
         dp_du = mk3<F>(-local.y, local.x, (F) 0);
         dp_du = xf_vector(sh.to_world, dp_du) * ((F) 2 * K<F>::Pi);
-    } else if (FEAT & FT_MESH) {
+    } else if (FEAT & FT_ANY_MESH) {
         F b1 = si.bu, b2 = si.bv, b0 = (F) 1 - b1 - b2;
         const uint32_t *fi = g.faces + 3 * (size_t) (sh.fofs + si.prim);
         uint32_t i0 = __ldg(fi), i1 = __ldg(fi + 1), i2 = __ldg(fi + 2);
@@ -456,7 +486,11 @@ VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
     const int nx = v.nx, ny = v.ny, nz = v.nz;
     const int ch = (FEAT & FT_CH3) ? v.channels : 1;
     const int wrap = (FEAT & FT_WRAP) ? v.wrap : 2;
-    const F *data = v.smem_offset >= 0 ? reinterpret_cast<const F *>(sv.grid_smem + v.smem_offset) : v.data;
+    /* a staged grid is read with ld.shared, a grid in HBM with global loads; instances compiled for scenes that have
+       only one kind (FT_GRID_SMEM / FT_GRID_GLOBAL) carry only that path */
+    const bool staged = (FEAT & FT_GRID_SMEM) && (!(FEAT & FT_GRID_GLOBAL) || v.smem_offset >= 0);
+    const uint32_t gs = sv.grid_saddr + (uint32_t) v.smem_offset;
+    auto data = [&](size_t i) -> F { return staged ? lds_real(gs + (uint32_t) i * (uint32_t) sizeof(F), F()) : v.data[i]; };
     F res[3];
     const bool trilinear = (FEAT & FT_TRILINEAR) && (!(FEAT & FT_NEAREST) || v.filter == 1);
     if (trilinear) { /* trilinear, grid3d.cpp:271-341 */
@@ -464,7 +498,7 @@ VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
         int ix = floor2int(p.x), iy = floor2int(p.y), iz = floor2int(p.z);
         F w1x = p.x - (F) ix, w1y = p.y - (F) iy, w1z = p.z - (F) iz;
         F w0x = (F) 1 - w1x, w0y = (F) 1 - w1y, w0z = (F) 1 - w1z;
-        if (v.cells) { /* large grid: one aligned record holds the eight corners (same values, same arithmetic) */
+        if ((FEAT & FT_GRID_GLOBAL) && v.cells) { /* large grid: one aligned record holds the eight corners (same values, same arithmetic) */
             F d[8];
             load_cell(v.cells + cell_index(v, ix, iy, iz), d);
             F v00 = fma_(w0x, d[0], w1x * d[1]), v01 = fma_(w0x, d[4], w1x * d[5]);
@@ -479,10 +513,10 @@ VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
                r01 = ((size_t) z1 * ny + y0) * nx, r11 = ((size_t) z1 * ny + y1) * nx;
 #pragma unroll 1
         for (int c = 0; c < ch; ++c) {
-            F d000 = data[(r00 + x0) * ch + c], d100 = data[(r00 + x1) * ch + c];
-            F d010 = data[(r10 + x0) * ch + c], d110 = data[(r10 + x1) * ch + c];
-            F d001 = data[(r01 + x0) * ch + c], d101 = data[(r01 + x1) * ch + c];
-            F d011 = data[(r11 + x0) * ch + c], d111 = data[(r11 + x1) * ch + c];
+            F d000 = data((r00 + x0) * ch + c), d100 = data((r00 + x1) * ch + c);
+            F d010 = data((r10 + x0) * ch + c), d110 = data((r10 + x1) * ch + c);
+            F d001 = data((r01 + x0) * ch + c), d101 = data((r01 + x1) * ch + c);
+            F d011 = data((r11 + x0) * ch + c), d111 = data((r11 + x1) * ch + c);
             F v00 = fma_(w0x, d000, w1x * d100), v01 = fma_(w0x, d001, w1x * d101);
             F v10 = fma_(w0x, d010, w1x * d110), v11 = fma_(w0x, d011, w1x * d111);
             F v0 = fma_(w0y, v00, w1y * v10), v1 = fma_(w0y, v01, w1y * v11);
@@ -494,7 +528,7 @@ VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
             z = wrap_coord(floor2int(p.z), nz, wrap);
         size_t idx = (((size_t) z * ny + y) * nx + x) * ch;
 #pragma unroll 1
-        for (int c = 0; c < ch; ++c) res[c] = data[idx + c];
+        for (int c = 0; c < ch; ++c) res[c] = data(idx + c);
     }
     if (ch == 1) return res[0];
     /* mitsuba::luminance(Color3f) with float literals (include/mitsuba/core/spectrum.h:247) */
@@ -511,13 +545,16 @@ VP_D void volume_eval_pair(const SceneView<F> &sv, const DVolume<F> &va, const D
     V3<F> p = (FEAT & FT_PROJECTIVE) ? xf_point(va.w2l, p_world) : xf_point_affine(va.w2l, p_world);
     const int nx = va.nx, ny = va.ny, nz = va.nz;
     const int wrap = (FEAT & FT_WRAP) ? va.wrap : 2;
-    const F *da = va.smem_offset >= 0 ? reinterpret_cast<const F *>(sv.grid_smem + va.smem_offset) : va.data;
-    const F *db = vb.smem_offset >= 0 ? reinterpret_cast<const F *>(sv.grid_smem + vb.smem_offset) : vb.data;
+    const bool sa = (FEAT & FT_GRID_SMEM) && (!(FEAT & FT_GRID_GLOBAL) || va.smem_offset >= 0);
+    const bool sb = (FEAT & FT_GRID_SMEM) && (!(FEAT & FT_GRID_GLOBAL) || vb.smem_offset >= 0);
+    const uint32_t ga = sv.grid_saddr + (uint32_t) va.smem_offset, gb = sv.grid_saddr + (uint32_t) vb.smem_offset;
+    auto da = [&](size_t i) -> F { return sa ? lds_real(ga + (uint32_t) i * (uint32_t) sizeof(F), F()) : va.data[i]; };
+    auto db = [&](size_t i) -> F { return sb ? lds_real(gb + (uint32_t) i * (uint32_t) sizeof(F), F()) : vb.data[i]; };
     p = mk3<F>(fma_(p.x, (F) nx, (F) -0.5), fma_(p.y, (F) ny, (F) -0.5), fma_(p.z, (F) nz, (F) -0.5));
     int ix = floor2int(p.x), iy = floor2int(p.y), iz = floor2int(p.z);
     F w1x = p.x - (F) ix, w1y = p.y - (F) iy, w1z = p.z - (F) iz;
     F w0x = (F) 1 - w1x, w0y = (F) 1 - w1y, w0z = (F) 1 - w1z;
-    if (va.cells && vb.cells) { /* both grids have cell records: two sector loads instead of sixteen gathers */
+    if ((FEAT & FT_GRID_GLOBAL) && va.cells && vb.cells) { /* both grids have cell records: two sector loads instead of sixteen gathers */
         F a[8], b[8];
         const size_t ci = cell_index(va, ix, iy, iz);
         load_cell(va.cells + ci, a);
@@ -541,10 +578,10 @@ VP_D void volume_eval_pair(const SceneView<F> &sv, const DVolume<F> &va, const D
     int z0 = wrap_coord(iz, nz, wrap), z1 = wrap_coord(iz + 1, nz, wrap);
     size_t r00 = ((size_t) z0 * ny + y0) * nx, r10 = ((size_t) z0 * ny + y1) * nx,
            r01 = ((size_t) z1 * ny + y0) * nx, r11 = ((size_t) z1 * ny + y1) * nx;
-    F a000 = da[r00 + x0], a100 = da[r00 + x1], a010 = da[r10 + x0], a110 = da[r10 + x1];
-    F a001 = da[r01 + x0], a101 = da[r01 + x1], a011 = da[r11 + x0], a111 = da[r11 + x1];
-    F b000 = db[r00 + x0], b100 = db[r00 + x1], b010 = db[r10 + x0], b110 = db[r10 + x1];
-    F b001 = db[r01 + x0], b101 = db[r01 + x1], b011 = db[r11 + x0], b111 = db[r11 + x1];
+    F a000 = da(r00 + x0), a100 = da(r00 + x1), a010 = da(r10 + x0), a110 = da(r10 + x1);
+    F a001 = da(r01 + x0), a101 = da(r01 + x1), a011 = da(r11 + x0), a111 = da(r11 + x1);
+    F b000 = db(r00 + x0), b100 = db(r00 + x1), b010 = db(r10 + x0), b110 = db(r10 + x1);
+    F b001 = db(r01 + x0), b101 = db(r01 + x1), b011 = db(r11 + x0), b111 = db(r11 + x1);
     {
         F v00 = fma_(w0x, a000, w1x * a100), v01 = fma_(w0x, a001, w1x * a101);
         F v10 = fma_(w0x, a010, w1x * a110), v11 = fma_(w0x, a011, w1x * a111);
@@ -1044,4 +1081,4 @@ VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> 
     return weight;
 }
 
-} // namespace vp
+} // namespace VP_NS

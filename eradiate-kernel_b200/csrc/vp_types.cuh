@@ -8,7 +8,7 @@
 #pragma once
 #include "vp_math.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 /* ------------------------------------------------------------------ vectors */
 template <typename F> struct V3 { F x, y, z; };
@@ -306,6 +306,8 @@ template <typename F> struct DScene {
     uint32_t ofs_shapes, ofs_analytic, ofs_bsdfs, ofs_media, ofs_volumes, ofs_phases, ofs_emitters;
     uint32_t grid_smem_bytes;       /* total bytes of grids staged in shared memory */
     uint32_t features;              /* FT_* bits the scene uses (vp_scene.cuh) */
+    /* small meshes: BVH nodes and leaf triangles are part of the blob (staged in shared memory with the tables) */
+    uint32_t bvh_in_blob, ofs_bvh, ofs_bvh_tris, pad_bvh;
 };
 
 /* stream space (integrator.cpp:51-231, sampler.cpp:83-96, spiral.cpp:8-72) */
@@ -335,4 +337,4 @@ template <bool IL = true> VP_D uint64_t stream_index(const DStreams &sp, uint64_
 
 struct PathCounters { uint32_t draws, medium_steps, n_null, n_real, n_intersect, n_surface; };
 
-} // namespace vp
+} // namespace VP_NS

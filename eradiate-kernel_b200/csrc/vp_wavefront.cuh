@@ -26,7 +26,7 @@
 #pragma once
 #include "vp_kernels.cuh"
 
-namespace vp {
+namespace VP_NS {
 
 enum LaneState : int {
     L_STEP_A = 0,   /* loop top + free-flight sampling                         */
@@ -502,4 +502,4 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
     }
 }
 
-} // namespace vp
+} // namespace VP_NS

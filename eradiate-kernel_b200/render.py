@@ -7,6 +7,24 @@ import numpy as np
 from . import abi
 
 
+# Defaults of DeviceScene.render's `kernel` and `math` arguments.  "auto" + "exact" is the bit-exact product path;
+# the parity tests patch "kernel" to run every test on every device kernel, bench.py asks for math="fast".
+render_defaults = {"kernel": "auto", "math": "exact"}
+
+
+def _set_launch_options(a, kernel, math, tuning, debug):
+    kernel = render_defaults["kernel"] if kernel is None else kernel
+    math = render_defaults["math"] if math is None else math
+    a.kernel = abi.KERNELS[kernel] if isinstance(kernel, str) else int(kernel)
+    a.math_mode = {"exact": abi.MATH_EXACT, "fast": abi.MATH_FAST}[math] if isinstance(math, str) else int(math)
+    if tuning:   # dict: slots_per_thread, stay, iter, cta_phase (B2vpRenderArgs::tuning)
+        a.tuning[0] = int(round(16 * tuning.get("slots_per_thread", 0)))
+        a.tuning[1] = int(tuning.get("stay", 0))
+        a.tuning[2] = int(tuning.get("iter", 0))
+        a.tuning[3] = int(tuning["cta_phase"]) + 1 if "cta_phase" in tuning else 0
+    a.debug_flags = int(debug)
+
+
 class RenderResult:
     def __init__(self, film, totals, state=None, counters=None, radiance=None):
         self.film = film            # (H, W, 5) XYZAW sums, like the hdrfilm storage ImageBlock
@@ -93,9 +111,12 @@ class DeviceScene:
         return i
 
     def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None, interleave=None,
-               want_paths=False, film=None, stream=None, device_film=None, clear=True):
+               want_paths=False, film=None, stream=None, device_film=None, clear=True, kernel=None, math=None,
+               tuning=None, debug=0):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
-        `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film)."""
+        `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film).
+        `kernel`: "auto" | "generic" | "q256" | "lanes" | "mega"; `math`: "exact" (bit-exact against the oracle) |
+        "fast" (fp32 tolerance mode, B2VP_MATH_FAST); `tuning`: queue-kernel scheduler parameters."""
         prec = self.scene.precision if precision is None else precision
         dtype = np.float32 if prec == abi.PREC_F32 else np.float64
         w, h = self.scene.film_size
@@ -104,6 +125,7 @@ class DeviceScene:
         a.precision, a.seed_mode, a.device = prec, seed_mode, self.device
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
+        _set_launch_options(a, kernel, math, tuning, debug)
         if interleave is not None:   # (block, count, index): B2vpRenderArgs::interleave_*
             a.interleave_block, a.interleave_count, a.interleave_index = interleave
         keep = []
@@ -146,7 +168,7 @@ class DeviceScene:
 
 
     def render_noalloc(self, device_film, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0,
-                       interleave=None, stream=None, clear=True):
+                       interleave=None, stream=None, clear=True, kernel=None, math=None, tuning=None):
         """b2vp_render_noalloc: the same render with the kernels' scratch in the library's static device array -- no
         device allocation in the call (for callers under CUDA graph capture or in loops that must not cudaMalloc;
         no counterpart in the reference).  `device_film` is a device pointer to H*W*channels reals owned by the
@@ -158,6 +180,7 @@ class DeviceScene:
         a.seed_mode, a.device = seed_mode, self.device
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
+        _set_launch_options(a, kernel, math, tuning, 0)
         if interleave is not None:
             a.interleave_block, a.interleave_count, a.interleave_index = interleave
         a.film_on_device, a.clear_film = 1, int(clear)

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define B2VP_ABI_VERSION 2u
+#define B2VP_ABI_VERSION 3u
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -89,6 +89,34 @@ enum {
     B2VP_SEED_WAVEFRONT = 1,
     /* parity harness: caller supplies (state, inc) and the pixel per stream */
     B2VP_SEED_EXPLICIT = 2
+};
+
+/* Floating-point mode of the fp32 kernels (B2vpRenderArgs::math_mode).  Integer work -- PCG32 streams, TEA seeding,
+   indices, counters -- is identical in both.
+   EXACT: every operation is the IEEE operation the oracle performs, in its order (no FMA contraction, IEEE division
+          and square root, polynomial log / exp / sincos / cbrt): films, RNG states, counters and per-path radiance
+          are bit-identical to the CPU oracle.  The only mode in fp64.
+   FAST:  the same kernels compiled with FMA contraction, approximate division / square root and the hardware
+          lg2 / ex2 / sin / cos approximations.  Per-path radiance agrees with EXACT within the north star's fp32
+          tolerance (1e-5 relative) on paths that take the same events; a small measured fraction of paths takes a
+          different event sequence, as the reference's own fp32 build does against the oracle.
+          The mode for production renders; validated against the reference's films and z-test. */
+enum { B2VP_MATH_EXACT = 0, B2VP_MATH_FAST = 1 };
+
+/* Which device kernel renders (B2vpRenderArgs::kernel).  All compute the same thing (the same per-path results in
+   EXACT mode); AUTO is the product choice, the rest exist for the parity tests and A/B measurements. */
+enum {
+    B2VP_KERNEL_AUTO = 0,          /* queue kernel, preset instance for the scene class                     */
+    B2VP_KERNEL_QUEUE_GENERIC = 1, /* queue kernel, all-features instance                                    */
+    B2VP_KERNEL_QUEUE_256 = 2,     /* queue kernel with 256-thread CTAs                                      */
+    B2VP_KERNEL_LANES = 3,         /* register-resident warp-voting wavefront (vp_wavefront.cuh)             */
+    B2VP_KERNEL_STREAM = 4         /* one thread per stream: the transliterated reference loop (vp_kernels.cuh) */
+};
+
+/* B2vpSceneDesc::options: device data layout choices (no counterpart in the reference; results are identical) */
+enum {
+    B2VP_OPT_NO_CELL_RECORDS = 1u << 0,   /* large trilinear grids: plain 8-gather lookups instead of cell records */
+    B2VP_OPT_BVH_LEAF_SHIFT = 8           /* bits 8..10: triangles per BVH leaf (0 = default 2)                     */
 };
 
 /* ---- scene description -------------------------------------------------- */
@@ -227,7 +255,7 @@ typedef struct B2vpSceneDesc {
     uint32_t abi_version;
     uint32_t struct_size;
     int32_t precision;         /* B2VP_PREC_* the host computed parameters in  */
-    int32_t reserved0;
+    uint32_t options;          /* B2VP_OPT_* (0 = defaults)                    */
 
     uint32_t n_shapes, n_bsdfs, n_media, n_volumes, n_phases, n_emitters;
     const B2vpShape *shapes;
@@ -313,6 +341,17 @@ typedef struct B2vpRenderArgs {
     B2vpPathCounters *out_counters;
     void *out_radiance;
     B2vpCounters *totals;       /* may be NULL                                 */
+
+    /* ---- ABI 3 ---- */
+    int32_t math_mode;          /* B2VP_MATH_*; FAST needs precision F32 and a queue kernel                    */
+    int32_t kernel;             /* B2VP_KERNEL_*                                                                */
+    /* Scheduler parameters of the queue kernel; 0 = the measured default of each:
+       [0] path slots per thread x 16 (default 64, or 32 when large grids are gathered through L2),
+       [1] STEP keeps its batch while at least this many lanes stay (26), [2] for at most this many steps (8),
+       [3] 1 + CTA phase policy (0 per warp, 1 fullest queue, 2 ray-making phases first).                       */
+    uint32_t tuning[4];
+    uint32_t debug_flags;       /* bit 0: print the queue kernel's scheduler statistics to stderr              */
+    uint32_t reserved1;
 } B2vpRenderArgs;
 
 typedef struct b2vp_scene b2vp_scene_t;

@@ -72,11 +72,11 @@ def _c3_full(variant):
 
 @pytest.mark.parametrize("cells", ["1", "0"])
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
-def test_full_size_c3_parity(pkg, oracle, variant, cells, monkeypatch):
+def test_full_size_c3_parity(pkg, oracle, variant, cells):
     """C3 at full size, trilinear cell records on (the product layout) and off (plain gathers)."""
-    monkeypatch.setenv("B2VP_CELLS", cells)
     abi = pkg.abi
     sc = pkg.load_dict(_c3_full(variant), variant)
+    sc.desc.options = 0 if cells == "1" else abi.OPT_NO_CELL_RECORDS
     with pkg.DeviceScene(sc) as ds:
         n, per = ds.stream_count(abi.SEED_WAVEFRONT)
         assert (n, per) == (512 * 512 * 64, 1)

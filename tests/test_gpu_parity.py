@@ -86,14 +86,11 @@ def compare(pkg, oracle, sc, mode, **kw):
 
 
 @pytest.fixture(params=["queue", "generic", "q256", "lanes", "mega"])
-def kernel(request, monkeypatch):
-    """B2VP_KERNEL selects the device kernel: the queue-based wavefront product kernel (two CTA sizes), the
+def kernel(request, monkeypatch, pkg):
+    """B2vpRenderArgs::kernel selects the device kernel: the queue-based wavefront product kernel (two CTA sizes), the
     register-resident warp-voting wavefront or its one-thread-per-path twin; "generic" forces the product
     kernel's all-features instance instead of the scene-class preset.  All must give identical results."""
-    if request.param == "generic":
-        monkeypatch.setenv("B2VP_GENERIC", "1")
-    else:
-        monkeypatch.setenv("B2VP_KERNEL", request.param)
+    monkeypatch.setitem(pkg.render_defaults, "kernel", request.param)
     return request.param
 
 
@@ -132,16 +129,19 @@ def test_moment_integrator(pkg, oracle, variant, kernel):
 
 
 @pytest.mark.parametrize("cells", ["1", "0"])
-def test_large_grid_layouts(pkg, oracle, cells, monkeypatch):
+def test_large_grid_layouts(pkg, oracle, cells):
     """Grids too large for shared memory are read from HBM either through trilinear cell records (8 corner
-    values per 32-byte record, the default) or through eight plain gathers (B2VP_CELLS=0): same bits."""
-    monkeypatch.setenv("B2VP_CELLS", cells)
+    values per 32-byte record, the default) or through eight plain gathers (B2VP_OPT_NO_CELL_RECORDS): same bits."""
+    options = 0 if cells == "1" else pkg.abi.OPT_NO_CELL_RECORDS
     for variant in ("scalar_mono", "scalar_mono_double"):
         sc = pkg.load_dict(scenes.c3(spp=2, variant=variant, n=40, size=12), variant)
+        sc.desc.options = options
         compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
     d = scenes.c3(spp=2, n=40, size=12)
     d["atm"]["albedo"] = 0.9   # unpaired: sigma_t grid alone
-    compare(pkg, oracle, pkg.load_dict(d), pkg.abi.SEED_WAVEFRONT)
+    sc = pkg.load_dict(d)
+    sc.desc.options = options
+    compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
 
 
 def test_explicit_states(pkg, oracle):
