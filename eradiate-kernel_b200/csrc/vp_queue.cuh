@@ -157,19 +157,24 @@ VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth
 }
 
 /* Scene::ray_intersect for a ray made in this visit, and what follows from the hit without any further draw.
-   START_DL: the ray is intersect2 (volpath.cpp:238-252) and the direct-light march starts from the new hit. */
-template <typename F, uint32_t FEAT, bool START_DL>
+   start_dl: the ray is intersect2 (volpath.cpp:238-252) and the direct-light march starts from the new hit.
+   Called from ONE place in the kernel (after the phase bodies), so that ray_intersect is inlined there once: its
+   Ray / SurfaceHit / counters then live in registers instead of crossing a call boundary through local memory
+   (ncu: what was left of the long_scoreboard stalls after the BVH moved to shared memory). */
+template <typename F, uint32_t FEAT>
 VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> &c, const Ray<F> &ir, bool isect_main,
-                            PathCounters &cnt, uint32_t &fl, int &state) {
+                            bool start_dl, uint32_t &fl, int &state) {
     SurfaceHit<F> h;
-    ray_intersect<F, FEAT, false>(sv, ir, h, cnt);
+    PathCounters cnt;
+    cnt.n_intersect = 0;
+    ray_intersect_impl<F, FEAT, false>(sv, ir, h, cnt);
     s.c_isect += 1;
     s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
     if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here: keep what
                          surface_frame() needs to finish it */
         c.prim = h.prim; c.bu = h.bu; c.bv = h.bv;
     }
-    if (START_DL) {
+    if (start_dl) {
         /* evaluate_direct_light prologue (volpath.cpp:370-383): march along the BSDF ray from the new hit; the
            main path (same ray, new hit, throughput) waits in `saved` */
         copy_ctx(c.saved, s.cur);
@@ -326,6 +331,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
            has happened.  Random numbers are drawn in the reference's order (ray_intersect draws none), and it is
            called exactly when the reference calls it, so the per-path counters agree. */
         Ray<F> ir;                 /* ray to intersect at the end of this visit */
+        uint32_t fl = 0;           /* flag word of the slot (phases other than STEP) */
         bool do_isect = false;
         bool isect_main = false;   /* it is the main path's ray: keep (prim, u, v) for surface_frame() */
         bool start_dl = false;     /* it is intersect2: the direct-light march starts from the new hit */
@@ -484,7 +490,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
         } else if (phase == PH_SCATTER) {
             /* =============================== SCATTER ============================== */
             if (has) {
-                uint32_t fl = s.flags;
+                fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 Pcg32 rng;
                 ld_rng(s, rng);
@@ -544,13 +550,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.w = w;
                 }
                 st_rng(s, rng);
-                if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else if (phase == PH_SURFACE) {
             /* =============================== SURFACE ============================== */
             if (has) {
-                uint32_t fl = s.flags;
+                fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 Pcg32 rng;
                 ld_rng(s, rng);
@@ -644,20 +648,16 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.w = throughput;
                 }
                 st_rng(s, rng);
-                if (do_isect) {
-                    if (start_dl) intersect_new_ray<F, FEAT, true>(sv, s, c, ir, isect_main, cnt, fl, state);
-                    else intersect_new_ray<F, FEAT, false>(sv, s, c, ir, isect_main, cnt, fl, state);
-                }
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else if (phase == PH_MARCH) {
             /* ================================ MARCH =============================== */
+            /* first half: a march crosses a surface; the second half (a march is over) follows the intersection below */
             if (has) {
-                uint32_t fl = s.flags;
+                fl = s.flags;
                 state = (int) (fl & QF_STATE);
-                const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;
-                F w = s.cur.w;
                 if (state == Q_MARCH_SURF) { /* volpath.cpp:329-352, 427-450 */
+                    const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;
+                    F w = s.cur.w;
                     const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
                     /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
                     w *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
@@ -675,33 +675,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                             s.remaining = remaining;
                             cont = remaining > 0;
                         }
+                        /* the new ray is intersected at once (below); outside the medium that settles what the march
+                           does next, often that it is over (the ray left the atmosphere towards the sun) */
                         if (cont) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r; }
                     }
                     st_ray(s.cur, r);
-                    /* the new ray is intersected at once; outside the medium that settles what the march does
-                       next, often that it is over (the ray left the atmosphere towards the sun) */
-                    if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, false, cnt, fl, state);
                 }
-                if (state == Q_MARCH_END) {
-                    /* hand the result back and restore the main path's context */
-                    if (nee) c.result += c.nee_w * (w * c.emitter_val);
-                    /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
-                    copy_ctx(s.cur, c.saved);
-                    const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
-                    if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
-                    else if (cont == QC_SURF_B) state = Q_SURF_B;
-                    else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250); the hit of intersect2 is current */
-                        s.cur.medium = c.medium_next;
-                        state = Q_STEP;
-                    }
-                    fl &= ~(QF_MODE | QF_TOP_DONE);
-                }
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
         } else {
             /* ================================= END ================================ */
             if (has) {
-                uint32_t fl = s.flags;
+                fl = s.flags;
                 state = (int) (fl & QF_STATE);
                 const uint32_t n_samples = sp.samples_per_stream;
                 unsigned long long k = c.k;
@@ -813,10 +797,29 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                     s.cur.w = w0;
                     st_rng(s, rng);
-                    if (do_isect) intersect_new_ray<F, FEAT, false>(sv, s, c, ir, true, cnt, fl, state);
                 }
-                s.flags = (fl & ~QF_STATE) | (uint32_t) state;
             }
+        }
+
+        /* ---------------- the one place where rays are intersected ---------------- */
+        if (phase != PH_STEP) {
+            if (has && do_isect) intersect_new_ray<F, FEAT>(sv, s, c, ir, isect_main, start_dl, fl, state);
+            if (phase == PH_MARCH && has && state == Q_MARCH_END) {
+                /* a march is over: hand the result back and restore the main path's context */
+                const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;
+                if (nee) c.result += c.nee_w * (s.cur.w * c.emitter_val);
+                /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
+                copy_ctx(s.cur, c.saved);
+                const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
+                if (cont == QC_SCATTER_B) state = Q_SCATTER_B;
+                else if (cont == QC_SURF_B) state = Q_SURF_B;
+                else { /* QC_AFTER_DL: medium switch (volpath.cpp:249-250); the hit of intersect2 is current */
+                    s.cur.medium = c.medium_next;
+                    state = Q_STEP;
+                }
+                fl &= ~(QF_MODE | QF_TOP_DONE);
+            }
+            if (has) s.flags = (fl & ~QF_STATE) | (uint32_t) state;
         }
 
         /* ---------------- push every slot onto the queue of its next phase ---------------- */

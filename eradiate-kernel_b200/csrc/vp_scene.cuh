@@ -190,8 +190,7 @@ template <typename F> VP_D void initialize_sh_frame(SurfaceHit<F> &si, V3<F> dp_
    until it actually scatters on the surface); surface_frame() below completes the interaction later from
    (shape, prim, bu, bv). */
 template <typename F, uint32_t FEAT = FT_ALL, bool SHADING = true>
-__device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si,
-                                           PathCounters &cnt) {
+VP_D void ray_intersect_impl(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si, PathCounters &cnt) {
     const DScene<F> &g = *sv.g;
     cnt.n_intersect++;
     si.t = inf_<F>();
@@ -371,6 +370,14 @@ __device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> 
     if (!SHADING) return;
     initialize_sh_frame(si, dp_du);
     si.wi = si.sh.to_local(-ray_in.d);
+}
+
+/* Out-of-line entry for the kernels that intersect from many places (the one-thread-per-stream and lanes twins); the
+   queue kernel inlines ray_intersect_impl at its single call site. */
+template <typename F, uint32_t FEAT = FT_ALL, bool SHADING = true>
+__device__ __noinline__ void ray_intersect(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si,
+                                           PathCounters &cnt) {
+    ray_intersect_impl<F, FEAT, SHADING>(sv, ray_in, si, cnt);
 }
 
 /* The rest of PreliminaryIntersection::compute_surface_interaction (interaction.h:571-596) for a hit found by
