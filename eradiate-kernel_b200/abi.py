@@ -142,7 +142,7 @@ class RenderArgs(C.Structure):
         ("explicit_pixel", C.POINTER(c_u32)), ("explicit_samples_per_stream", c_u32), ("clear_film", c_u32),
         ("out_state", C.POINTER(c_u64)), ("out_counters", C.POINTER(PathCounters)),
         ("out_radiance", C.c_void_p), ("totals", C.POINTER(Counters)),
-        ("math_mode", c_i32), ("kernel", c_i32), ("tuning", c_u32 * 4), ("debug_flags", c_u32), ("reserved1", c_u32),
+        ("math_mode", c_i32), ("kernel", c_i32), ("tuning", c_u32 * 4), ("debug_flags", c_u32), ("majorant_grid", c_u32),
     ]
 
 

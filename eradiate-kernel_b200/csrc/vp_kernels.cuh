@@ -33,6 +33,9 @@ template <typename F> struct RenderOut {
     uint32_t q_stay_min, q_max_iter; /* STEP keeps its batch while >= q_stay_min lanes stay, <= q_max_iter steps */
     unsigned long long *q_stats;    /* optional scheduler statistics (B2VP_QSTATS): pops[8], slots[8], switches, idle polls */
     void *q_cold;                   /* grid * q_n_slots PathCold records */
+    /* majorant grids of the scene's media (floats, staged in shared memory at mg_smem_offset), or null */
+    const float *mg;
+    uint32_t mg_bytes, mg_smem_offset;
 };
 
 struct StreamInfo {
@@ -114,6 +117,13 @@ VP_D void stage_scene(const DScene<F> &g, const RenderOut<F> &out, unsigned char
     sv.grid_saddr = smem_addr(sv.grid_smem);
     sv.bvh_saddr = smem_addr(smem + g.ofs_bvh);
     sv.tri_saddr = smem_addr(smem + g.ofs_bvh_tris);
+    sv.mg_saddr = 0;
+    if (out.mg) {   /* majorant grids: a few KB, plain cooperative copy */
+        float *dstm = reinterpret_cast<float *>(smem + out.mg_smem_offset);
+        for (uint32_t i = threadIdx.x; i < out.mg_bytes / 4; i += blockDim.x) dstm[i] = out.mg[i];
+        sv.mg_saddr = smem_addr(dstm);
+        __syncthreads();
+    }
 
     if (g.grid_smem_bytes > 0) {
         /* TMA bulk copies global -> shared, completion counted on an mbarrier */

@@ -14,6 +14,8 @@ constexpr uint32_t PRE_HOMOG_BIG = FT_RECT | FT_MESH | FT_MESH_ATTR | FT_HOMOG; 
 constexpr uint32_t PRE_HET = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_SMEM;         /* C2, C4: grid staged */
 constexpr uint32_t PRE_HET_G = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_GLOBAL;     /* large sigma_t grid, constant albedo */
 constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_ALBEDO | FT_GRID_GLOBAL;   /* C3 */
+constexpr uint32_t PRE_HET_MG = PRE_HET | FT_MAJORANT_GRID;           /* the same with majorant-grid free flights */
+constexpr uint32_t PRE_HET_ALB_MG = PRE_HET_ALB | FT_MAJORANT_GRID;
 
 template <typename F, int MAXT, uint32_t FEAT> const void *q_entry() {
     return reinterpret_cast<const void *>(&volpath_q_kernel<F, MAXT, FEAT>);
@@ -34,6 +36,8 @@ template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool 
     if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return q_entry<F, MAXT, PRE_HET>(); }
     if ((ft & ~PRE_HET_G) == 0) { *name = "heterogeneous, grid in HBM"; return q_entry<F, MAXT, PRE_HET_G>(); }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return q_entry<F, MAXT, PRE_HET_ALB>(); }
+    if ((ft & ~PRE_HET_MG) == 0) { *name = "heterogeneous, majorant grid"; return q_entry<F, MAXT, PRE_HET_MG>(); }
+    if ((ft & ~PRE_HET_ALB_MG) == 0) { *name = "heterogeneous+albedo grid, majorant grid"; return q_entry<F, MAXT, PRE_HET_ALB_MG>(); }
     *name = "generic";
     return q_entry<F, MAXT, FT_ALL>();
 }

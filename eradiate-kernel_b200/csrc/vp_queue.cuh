@@ -384,11 +384,17 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                here over the full range differs from that only when it lies beyond a valid mi.t, and then it is
                never looked at (a homogeneous medium has no null collisions: the path scatters, a march ends). */
             const bool in_medium = go && med >= 0;
+            bool mg = false;   /* this step samples against the medium's majorant grid (opt-in fast mode) */
             if (in_medium) {
                 const DMedium<F> &m = sv.media[med];
-                sample_interaction<F, FEAT>(sv, m, r, rng.next(F(), true), mi, cnt);
-                if (m.type == 0 && mi.valid())
-                    r.maxt = nee ? min_(mi.t, remaining) : mi.t;
+                mg = (FEAT & FT_MAJORANT_GRID) && sv.mg_saddr != 0 && m.mg_offset >= 0;
+                if (mg) {
+                    sample_interaction_mg<F, FEAT>(sv, m, r, rng.next(F(), true), nee ? min_(hit_t, remaining) : hit_t, mi, cnt);
+                } else {
+                    sample_interaction<F, FEAT>(sv, m, r, rng.next(F(), true), mi, cnt);
+                    if (m.type == 0 && mi.valid())
+                        r.maxt = nee ? min_(mi.t, remaining) : mi.t;
+                }
             }
             __syncwarp();
             /* surface-vs-collision ordering and the transmittance / pdf ratio
@@ -398,7 +404,12 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             if (in_medium) {
                 spectral = sv.media[med].spectral != 0;
                 if (hit_t < mi.t) mi.t = INF;
-                if (spectral) {
+                if (spectral && mg) {
+                    /* tr / pdf of Medium::eval_tr_and_pdf with a piecewise-constant majorant: the transmittance cancels,
+                       1 / mu_cell is left for a collision and 1 when the surface (or the end of the march) comes first */
+                    const bool surface_first = hit_t < mi.t || (nee && mi.t > remaining);
+                    ratio = surface_first ? (F) 1 : (F) 1 / mi.combined;
+                } else if (spectral) {
                     F tt = min_(mi.t, hit_t);
                     if (nee) tt = min_(remaining, tt);
                     F t = tt - mi.mint;

@@ -28,6 +28,7 @@ template <typename F> struct SceneView {
        of the table blob then.  Read with explicit ld.shared: a pointer that may be shared OR global is a generic
        pointer to the compiler, and generic loads cost a trip through the global-memory pipeline. */
     uint32_t grid_saddr, bvh_saddr, tri_saddr;
+    uint32_t mg_saddr;              /* staged majorant grids, 0 when the launch does not use them */
 };
 
 VP_D float4 lds_f4(uint32_t a) {
@@ -75,7 +76,8 @@ enum : uint32_t {
     FT_GRID_SMEM = 1u << 17,   /* some grid is staged in shared memory                    */
     FT_GRID_GLOBAL = 1u << 18, /* some grid is read from global memory                    */
     FT_MESH_SMEM = 1u << 19,   /* triangle meshes whose BVH and triangles are staged in shared memory (small meshes) */
-    FT_ALL = 0xfffffu
+    FT_MAJORANT_GRID = 1u << 20, /* the launch samples free flights against majorant grids (opt-in fast mode) */
+    FT_ALL = 0x1fffffu
 };
 constexpr uint32_t FT_ANY_MESH = FT_MESH | FT_MESH_SMEM;
 
@@ -666,6 +668,100 @@ VP_D void sample_interaction(const SceneView<F> &sv, const DMedium<F> &m, const 
         mi.sigma_s = sigmat * albedo;
     }
     mi.combined = combined;
+}
+
+/* Free-flight sampling against a MAJORANT GRID instead of the medium's one global majorant.
+   Not in the reference (heterogeneous.cpp:29,38 has only the global majorant): an opt-in mode whose
+   tentative collisions are a different -- much sparser -- random sequence with the same distribution of real
+   collisions, so it changes how many random numbers a path draws and is validated statistically, never bit for bit.
+   One uniform variate gives the optical depth tau = -log(1 - u) to the next tentative collision; the ray is walked
+   through the coarse cells (3D-DDA in the volume's local coordinates), accumulating mu_cell * dt until tau is used up.
+   mi.combined is the majorant of the cell the collision falls in: every weight of the integrator that refers to the
+   majorant (null probability sigma_n / mu, ratio-tracking factor, tr / pdf = 1 / mu) uses it unchanged.
+   t_limit: nothing beyond it is looked at by the caller (the closest surface, the remaining distance of a march). */
+template <typename F, uint32_t FEAT>
+VP_D void sample_interaction_mg(const SceneView<F> &sv, const DMedium<F> &m, const Ray<F> &ray, F sample, F t_limit,
+                                MediumHit<F> &mi, PathCounters &cnt) {
+    cnt.medium_steps++;
+    F mint, maxt;
+    bool active = bbox_ray_intersect(m.amin, m.amax, ray, mint, maxt);
+    active = active && (finite_(mint) || finite_(maxt));
+    if (!active) { mint = 0; maxt = inf_<F>(); }
+    mint = max_(ray.mint, mint);
+    maxt = min_(min_(ray.maxt, maxt), t_limit);
+    mi.t = inf_<F>(); mi.mint = mint; mi.p = ray.o;
+    mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = m.max_density;
+    if (!active || !(mint < maxt)) return;
+    const DVolume<F> &vol = sv.volumes[m.sigma_t];
+    const int Rx = m.mg_res[0], Ry = m.mg_res[1], Rz = m.mg_res[2];
+    /* local coordinates scaled to cells: q(t) = qo + t * qd.  Everything per axis lives in scalars (an array indexed
+       by the axis of the next crossing would live in local memory). */
+    const V3<F> ol = xf_point_affine(vol.w2l, ray.o), dl = xf_vector(vol.w2l, ray.d);
+    const F qox = ol.x * (F) Rx, qoy = ol.y * (F) Ry, qoz = ol.z * (F) Rz;
+    const F qdx = dl.x * (F) Rx, qdy = dl.y * (F) Ry, qdz = dl.z * (F) Rz;
+    F t = mint;
+    int cx, cy, cz, sx, sy, sz;
+    F tnx, tny, tnz, tdx, tdy, tdz;
+    auto setup = [&](F qo, F qd, int R, int &c, int &st, F &tn, F &td) {
+        c = (int) floor_(fma_(qd, t, qo));
+        c = c < 0 ? 0 : (c > R - 1 ? R - 1 : c);
+        if (qd > 0) { st = 1; td = (F) 1 / qd; tn = ((F) (c + 1) - qo) * td; }
+        else if (qd < 0) { st = -1; td = (F) -1 / qd; tn = ((F) c - qo) / qd; }
+        else { st = 0; td = inf_<F>(); tn = inf_<F>(); }
+    };
+    setup(qox, qdx, Rx, cx, sx, tnx, tdx);
+    setup(qoy, qdy, Ry, cy, sy, tny, tdy);
+    setup(qoz, qdz, Rz, cz, sz, tnz, tdz);
+    const F tau = -log_((F) 1 - sample);
+    const uint32_t base = sv.mg_saddr + (uint32_t) m.mg_offset * 4u;
+    F acc = 0;
+    /* At most MG_WALK cells per call: the number of cells to the next collision differs wildly between the lanes of a
+       warp (1 .. 3 * 16), and a warp pays for its longest walk.  A walk that is not over after MG_WALK cells returns a
+       VIRTUAL collision at the cell face it has reached: sigma_t = 0 there, so it is a null collision with
+       probability 1 and weight exactly 1, and the caller draws a fresh optical depth from that point on -- which the
+       exponential distribution allows (it has no memory).  Same estimator, bounded work per visit. */
+    constexpr int MG_WALK = 8;
+#pragma unroll 1
+    for (int guard = 0; guard < MG_WALK; ++guard) {
+        const F tn = min_(tnx, min_(tny, tnz));
+        const F t_exit = min_(max_(tn, t), maxt);
+        const F mu = m.scale * (F) lds_real(base + (uint32_t) ((cz * Ry + cy) * Rx + cx) * 4u, float());
+        const F dtau = mu * (t_exit - t);
+        if (acc + dtau >= tau && mu > 0) {   /* the collision falls in this cell */
+            const F tc = t + (tau - acc) / mu;
+            if (tc <= maxt) {
+                mi.t = tc;
+                mi.p = ray.at(tc);
+                mi.combined = mu;
+                F albedo, sigmat;
+                if ((FEAT & FT_GRID_ALBEDO) && (FEAT & FT_TRILINEAR) && m.paired) {
+                    F st;
+                    volume_eval_pair<F, FEAT>(sv, sv.volumes[m.albedo], vol, mi.p, albedo, st);
+                    sigmat = m.scale * st;
+                } else {
+                    albedo = volume_eval<F, FEAT, (FEAT & FT_GRID_ALBEDO) != 0>(sv, sv.volumes[m.albedo], mi.p);
+                    sigmat = m.scale * volume_eval<F, FEAT, true>(sv, vol, mi.p);
+                }
+                mi.sigma_t = sigmat;
+                mi.sigma_n = mu - sigmat;
+                mi.sigma_s = sigmat * albedo;
+            }
+            return;
+        }
+        acc += dtau;
+        t = t_exit;
+        if (!(t < maxt)) return;
+        /* cross into the next cell along the axis whose boundary comes first */
+        if (tnx <= tny && tnx <= tnz) { cx += sx; tnx += tdx; if (cx < 0 || cx >= Rx) return; }
+        else if (tny <= tnz) { cy += sy; tny += tdy; if (cy < 0 || cy >= Ry) return; }
+        else { cz += sz; tnz += tdz; if (cz < 0 || cz >= Rz) return; }
+    }
+    /* virtual collision at the face reached (t < maxt here): null with certainty, weight sigma_n / combined = 1 */
+    mi.t = t;
+    mi.p = ray.at(t);
+    mi.combined = m.max_density;
+    mi.sigma_n = m.max_density;
+    mi.sigma_t = 0; mi.sigma_s = 0;
 }
 
 /* Medium::eval_tr_and_pdf (medium.cpp:77-89) followed by tr / tr_pdf

@@ -253,6 +253,11 @@ template <typename F> struct DMedium {
     int paired, pad0;                /* sigma_t and albedo are single-channel trilinear grids of the same geometry */
     F scale, max_density;            /* heterogeneous.cpp:29 */
     F amin[3], amax[3];              /* heterogeneous.cpp:30 */
+    /* Majorant grid (opt-in fast mode, no counterpart in the reference, which has one global majorant:
+       heterogeneous.cpp:29,38): mg_res cells per axis over the sigma_t volume's unit cube, each holding the maximum
+       of UNSCALED sigma_t over everything a lookup inside the cell can touch; mg_offset = index of the first cell in
+       the staged array, or -1 when the medium has none. */
+    int mg_res[3], mg_offset;
 };
 template <typename F> struct DSensor {
     int type, direction_type, target_type, origin_type;

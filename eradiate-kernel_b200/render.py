@@ -12,7 +12,7 @@ from . import abi
 render_defaults = {"kernel": "auto", "math": "exact"}
 
 
-def _set_launch_options(a, kernel, math, tuning, debug):
+def _set_launch_options(a, kernel, math, tuning, debug, majorant_grid=0):
     kernel = render_defaults["kernel"] if kernel is None else kernel
     math = render_defaults["math"] if math is None else math
     a.kernel = abi.KERNELS[kernel] if isinstance(kernel, str) else int(kernel)
@@ -23,6 +23,7 @@ def _set_launch_options(a, kernel, math, tuning, debug):
         a.tuning[2] = int(tuning.get("iter", 0))
         a.tuning[3] = int(tuning["cta_phase"]) + 1 if "cta_phase" in tuning else 0
     a.debug_flags = int(debug)
+    a.majorant_grid = int(majorant_grid)
 
 
 class RenderResult:
@@ -112,11 +113,13 @@ class DeviceScene:
 
     def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None, interleave=None,
                want_paths=False, film=None, stream=None, device_film=None, clear=True, kernel=None, math=None,
-               tuning=None, debug=0):
+               tuning=None, debug=0, majorant_grid=0):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
         `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film).
         `kernel`: "auto" | "generic" | "q256" | "lanes" | "mega"; `math`: "exact" (bit-exact against the oracle) |
-        "fast" (fp32 tolerance mode, B2VP_MATH_FAST); `tuning`: queue-kernel scheduler parameters."""
+        "fast" (fp32 tolerance mode, B2VP_MATH_FAST); `tuning`: queue-kernel scheduler parameters; `majorant_grid`:
+        non-zero = opt-in free-flight sampling against a grid of local majorants (B2vpRenderArgs::majorant_grid: same
+        estimator, other random sequence -- statistically, not per-path, equal to the reference's global majorant)."""
         prec = self.scene.precision if precision is None else precision
         dtype = np.float32 if prec == abi.PREC_F32 else np.float64
         w, h = self.scene.film_size
@@ -125,7 +128,7 @@ class DeviceScene:
         a.precision, a.seed_mode, a.device = prec, seed_mode, self.device
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
-        _set_launch_options(a, kernel, math, tuning, debug)
+        _set_launch_options(a, kernel, math, tuning, debug, majorant_grid)
         if interleave is not None:   # (block, count, index): B2vpRenderArgs::interleave_*
             a.interleave_block, a.interleave_count, a.interleave_index = interleave
         keep = []
@@ -168,7 +171,7 @@ class DeviceScene:
 
 
     def render_noalloc(self, device_film, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0,
-                       interleave=None, stream=None, clear=True, kernel=None, math=None, tuning=None):
+                       interleave=None, stream=None, clear=True, kernel=None, math=None, tuning=None, majorant_grid=0):
         """b2vp_render_noalloc: the same render with the kernels' scratch in the library's static device array -- no
         device allocation in the call (for callers under CUDA graph capture or in loops that must not cudaMalloc;
         no counterpart in the reference).  `device_film` is a device pointer to H*W*channels reals owned by the
@@ -180,7 +183,7 @@ class DeviceScene:
         a.seed_mode, a.device = seed_mode, self.device
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
-        _set_launch_options(a, kernel, math, tuning, 0)
+        _set_launch_options(a, kernel, math, tuning, 0, majorant_grid)
         if interleave is not None:
             a.interleave_block, a.interleave_count, a.interleave_index = interleave
         a.film_on_device, a.clear_film = 1, int(clear)

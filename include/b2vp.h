@@ -351,7 +351,15 @@ typedef struct B2vpRenderArgs {
        [3] 1 + CTA phase policy (0 per warp, 1 fullest queue, 2 ray-making phases first).                       */
     uint32_t tuning[4];
     uint32_t debug_flags;       /* bit 0: print the queue kernel's scheduler statistics to stderr              */
-    uint32_t reserved1;
+    /* Majorant grid: 0 = the reference's delta / ratio tracking against ONE global majorant scale * max(sigma_t)
+       (src/media/heterogeneous.cpp:29,38) -- the only mode whose random-number consumption, event counters and
+       per-path results match the reference.  Non-zero = opt-in fast mode for heterogeneous media with a clamp-mode
+       single-channel sigma_t grid: free flights are sampled against a coarse grid of LOCAL majorants (1: up to 16
+       cells per axis, more along a lone long axis; n > 1: n cells along the longest axis; at most 4096 cells per
+       medium, staged in shared memory).  The estimator is the same and unbiased; tentative collisions are a sparser
+       random sequence, so paths draw fewer random numbers and the result agrees with the global-majorant film
+       statistically (z-test), not per path.  Queue kernel only; other media in the scene are unaffected.          */
+    uint32_t majorant_grid;
 } B2vpRenderArgs;
 
 typedef struct b2vp_scene b2vp_scene_t;

@@ -11,24 +11,29 @@ import scenes
 abi = pkg.abi
 
 
+RENDER_KW = {}   # e.g. math="fast", majorant_grid=1 (command line: key=value)
+
+
 def run(name, desc, scene_dict, reps=2, extra=None, variant="scalar_mono"):
     t0 = time.perf_counter()
     scene = pkg.load_dict(scene_dict, variant)
     t1 = time.perf_counter()
     with pkg.DeviceScene(scene, device=0) as ds:
         t2 = time.perf_counter()
-        r = ds.render(seed_mode=abi.SEED_WAVEFRONT)       # warm-up (lazy upload, kernel attributes)
+        r = ds.render(seed_mode=abi.SEED_WAVEFRONT, **RENDER_KW)       # warm-up (lazy upload, kernel attributes)
         t3 = time.perf_counter()
         ms = []
         for _ in range(reps):
-            r = ds.render(seed_mode=abi.SEED_WAVEFRONT)
+            r = ds.render(seed_mode=abi.SEED_WAVEFRONT, **RENDER_KW)
             ms.append(r.totals.gpu_ms)
+        kernel = ds.info().last_kernel.decode()
     t = r.totals
     k = min(ms) * 1e-3
-    out = {"config": name, "workload": desc, "paths": t.n_paths, "kernel_ms": min(ms),
+    out = {"config": name, "workload": desc, "mode": RENDER_KW, "kernel": kernel, "paths": t.n_paths, "kernel_ms": min(ms),
            "mpaths_s": t.n_paths / k / 1e6, "segments_per_s": (t.n_medium_steps + t.n_intersect) / k,
            "medium_steps_per_path": t.n_medium_steps / max(t.n_paths, 1),
            "intersections_per_path": t.n_intersect / max(t.n_paths, 1),
+           "real_per_path": t.n_real / max(t.n_paths, 1), "null_per_path": t.n_null / max(t.n_paths, 1),
            "host_load_dict_s": t1 - t0, "scene_create_s": t2 - t1, "first_render_s": t3 - t2,
            "mean_radiance": float(np.mean(r.bitmap()))}
     if extra:
@@ -36,7 +41,10 @@ def run(name, desc, scene_dict, reps=2, extra=None, variant="scalar_mono"):
     print(json.dumps(out), flush=True)
 
 
-which = sys.argv[1:] or ["c1", "c3", "c5"]
+for a in [a for a in sys.argv[1:] if "=" in a]:
+    k, v = a.split("=", 1)
+    RENDER_KW[k] = int(v) if v.isdigit() else v
+which = [a for a in sys.argv[1:] if "=" not in a] or ["c1", "c3", "c5"]
 if "c1" in which:
     run("C1", "homogeneous Rayleigh cube over diffuse rectangle, distant 1x1, 1e6 spp", scenes.c1(spp=1000000))
 if "c3" in which:
@@ -79,5 +87,7 @@ if "c4" in which:
                       "mpaths_s_wall": paths / wall / 1e6, "segments_per_s": segs / (k_ms * 1e-3),
                       "mean_radiance_400nm": float(films[0, :, 1].sum() / films[0, :, 4].sum()),
                       "mean_radiance_1000nm": float(films[-1, :, 1].sum() / films[-1, :, 4].sum())}), flush=True)
+if "c2" in which:
+    run("C2", "1D heterogeneous atmosphere, 256x1, 16384 spp", scenes.c2(spp=16384, width=256))
 if "c2f64" in which:
     run("C2-f64", "C2 in scalar_mono_double, 256x1, 2048 spp", scenes.c2(spp=2048, width=256, variant="scalar_mono_double"), variant="scalar_mono_double")
