@@ -128,7 +128,7 @@ class Counters(C.Structure):
     _fields_ = [
         ("n_paths", c_u64), ("n_rng_draws", c_u64), ("n_medium_steps", c_u64), ("n_null", c_u64),
         ("n_real", c_u64), ("n_intersect", c_u64), ("n_surface", c_u64), ("n_invalid_samples", c_u64),
-        ("gpu_ms", c_d), ("n_launches", c_u32), ("reserved0", c_u32),
+        ("gpu_ms", c_d), ("n_launches", c_u32), ("stopped_early", c_u32),
     ]
 
 
@@ -143,6 +143,7 @@ class RenderArgs(C.Structure):
         ("out_state", C.POINTER(c_u64)), ("out_counters", C.POINTER(PathCounters)),
         ("out_radiance", C.c_void_p), ("totals", C.POINTER(Counters)),
         ("math_mode", c_i32), ("kernel", c_i32), ("tuning", c_u32 * 4), ("debug_flags", c_u32), ("majorant_grid", c_u32),
+        ("timeout_s", c_d), ("devices", C.POINTER(c_i32)), ("n_devices", c_u32), ("reserved2", c_u32),
     ]
 
 
@@ -168,7 +169,7 @@ class SceneInfo(C.Structure):
 # every symbol include/b2vp.h declares
 EXPORTS = ["b2vp_stream_count", "b2vp_scene_create", "b2vp_scene_update", "b2vp_scene_update_grid", "b2vp_scene_destroy", "b2vp_render",
            "b2vp_cancel", "b2vp_last_error", "b2vp_abi_version", "b2vp_device_count", "b2vp_measure_fp32_peak",
-           "b2vp_render_noalloc", "b2vp_scene_info"]
+           "b2vp_render_noalloc", "b2vp_scene_info", "b2vp_shard_streams"]
 
 _lib = None
 
@@ -201,6 +202,7 @@ def lib():
     L.b2vp_render.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
     L.b2vp_render_noalloc.argtypes = [C.c_void_p, C.POINTER(RenderArgs), C.c_void_p]
     L.b2vp_scene_info.argtypes = [C.c_void_p, C.POINTER(SceneInfo)]
+    L.b2vp_shard_streams.argtypes = [c_u64, c_u32, c_u32, C.POINTER(c_u64), C.POINTER(c_u64)]
     L.b2vp_cancel.argtypes = [C.c_void_p]
     L.b2vp_cancel.restype = None
     L.b2vp_stream_count.argtypes = [C.c_void_p, c_i32, C.POINTER(c_u64), C.POINTER(c_u32)]

@@ -10,11 +10,15 @@
 #include "vp_launch.h"
 
 #include <cstdlib>
+#include <dlfcn.h>
+#include <nccl.h>     /* types and prototypes only: the library is loaded with dlopen at the first multi-device render */
 
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -141,6 +145,22 @@ template <typename F> struct DeviceScene {
 
 } // namespace
 
+/* Everything that lives on ONE GPU: the device copies of the scene (one per arithmetic precision, made on first use)
+   and the buffers of a render.  A scene has one context per device it has rendered on; contexts[0] is the device the
+   scene was created for and the root of multi-device renders. */
+struct DeviceCtx {
+    int device = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    DeviceScene<float> dev32;
+    DeviceScene<double> dev64;
+    DevBuf film_buf, totals_buf, counter_buf, blocks_buf, stop_flag;
+    DevBuf ex_state, ex_inc, ex_pixel, o_state, o_counters, o_radiance, q_cold;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_done = nullptr;
+    cudaStream_t ctl_stream = nullptr;    /* raises stop_flag while a render kernel runs on another stream */
+    cudaStream_t work_stream = nullptr;   /* render stream of a non-root device in a multi-device render */
+};
+
 struct b2vp_scene {
     int device = 0;
     B2vpSceneDesc desc{};
@@ -161,13 +181,8 @@ struct b2vp_scene {
     BvhStats bvh_stats;
     std::string last_kernel;                         /* kernel instance launched by the last render (b2vp_scene_info) */
     bool warned_stream_kernel = false;
-    DeviceScene<float> dev32;
-    DeviceScene<double> dev64;
-    DevBuf film_buf, totals_buf, counter_buf, blocks_buf;
-    DevBuf ex_state, ex_inc, ex_pixel, o_state, o_counters, o_radiance, q_cold;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    int sm_count = 0;
-    size_t smem_optin = 0;
+    std::vector<std::unique_ptr<DeviceCtx>> contexts;
+    std::mutex mutex;                                /* guards contexts / last_kernel between the threads of a multi-device render */
     std::atomic<int> cancelled{ 0 };
 };
 
@@ -337,6 +352,38 @@ int build_bvh(b2vp_scene *s) {
 
 namespace {
 
+/* The context of `device`, created on first use (device attributes, events, control stream). */
+int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
+    std::lock_guard<std::mutex> lock(s->mutex);
+    for (auto &c : s->contexts)
+        if (c->device == device) { *out = c.get(); return B2VP_OK; }
+    int n_dev = 0;
+    CU_CHECK(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(B2VP_ERR_INVALID, "device ordinal %d out of range", device);
+    /* single attributes, not cudaGetDeviceProperties: that call costs milliseconds on every scene */
+    int cc_major = 0, cc_minor = 0, sm_count = 0, smem_optin = 0;
+    CU_CHECK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+    CU_CHECK(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, device));
+    CU_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    CU_CHECK(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    if (cc_major != 10)
+        return fail(B2VP_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                    cc_major, cc_minor);
+    std::unique_ptr<DeviceCtx> c(new DeviceCtx());
+    c->device = device; c->sm_count = sm_count; c->smem_optin = (size_t) smem_optin;
+    CU_CHECK(cudaSetDevice(device));
+    CU_CHECK(cudaEventCreate(&c->ev0));
+    CU_CHECK(cudaEventCreate(&c->ev1));
+    CU_CHECK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+    CU_CHECK(cudaStreamCreateWithFlags(&c->ctl_stream, cudaStreamNonBlocking));
+    CU_CHECK(cudaStreamCreateWithFlags(&c->work_stream, cudaStreamNonBlocking));
+    CU_CHECK(c->stop_flag.alloc(256));
+    CU_CHECK(cudaMemset(c->stop_flag.p, 0, 256));
+    *out = c.get();
+    s->contexts.push_back(std::move(c));
+    return B2VP_OK;
+}
+
 /* ---- device upload in precision F ---------------------------------------- */
 template <typename F> void cvt(const double *src, F *dst, int n) { for (int i = 0; i < n; ++i) dst[i] = (F) src[i]; }
 
@@ -347,7 +394,7 @@ constexpr uint32_t SMEM_BUDGET = 100 * 1024;
 constexpr uint32_t FILM_SMEM_MAX = 16 * 1024;
 constexpr size_t BVH_SMEM_MAX = 16 * 1024;     /* BVH nodes + leaf triangles staged with the tables when they fit */
 
-template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
+template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds) {
     const B2vpSceneDesc &d = s->desc;
     DScene<F> &g = ds.g;
     std::memset(&g, 0, sizeof(g));
@@ -561,7 +608,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceScene<F> &ds) {
                 cudaError_t e = ds.cells.back()->alloc(cbytes);
                 if (e != cudaSuccess) return fail(B2VP_ERR_CUDA, "cell-record allocation failed: %s", cudaGetErrorString(e));
                 F *cp = ds.cells.back()->template as<F>();
-                const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) s->sm_count * 16);
+                const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) dc->sm_count * 16);
                 build_cells_kernel<F><<<blocks, 256>>>(v.data, cp, v.nx, v.ny, v.nz);
                 CU_CHECK(cudaGetLastError());
                 v.cells = cp;
@@ -728,12 +775,84 @@ __global__ void fma_peak_kernel(float *sink, int iters, float m) {
     if (r == 123.456f) sink[threadIdx.x] = r;
 }
 
-template <typename F> DeviceScene<F> &dev_of(b2vp_scene *s);
-template <> DeviceScene<float> &dev_of<float>(b2vp_scene *s) { return s->dev32; }
-template <> DeviceScene<double> &dev_of<double>(b2vp_scene *s) { return s->dev64; }
+template <typename F> DeviceScene<F> &dev_of(DeviceCtx *dc);
+template <> DeviceScene<float> &dev_of<float>(DeviceCtx *dc) { return dc->dev32; }
+template <> DeviceScene<double> &dev_of<double>(DeviceCtx *dc) { return dc->dev64; }
 
 inline uint32_t align128(uint32_t x) { return (x + 127u) & ~127u; }
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t) 255; }
+
+/* ---- NCCL, loaded on demand ------------------------------------------------------------------------------
+   Only a multi-device render needs it, and a process may already hold a copy (torch bundles its own libnccl.so.2
+   under the same SONAME): dlopen by SONAME returns whichever is loaded.  Communicators are made once per device set
+   and kept for the life of the process (ncclCommInitAll costs about a second). */
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*Reduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+std::mutex g_nccl_mutex;
+NcclApi g_nccl;
+std::map<std::vector<int>, std::vector<ncclComm_t>> g_nccl_comms;
+
+int nccl_load() {
+    if (g_nccl.lib) return B2VP_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h) return fail(B2VP_ERR_UNSUPPORTED, "multi-device render needs NCCL: dlopen(libnccl.so.2) failed: %s", dlerror());
+    NcclApi a;
+    a.lib = h;
+    a.CommInitAll = (decltype(a.CommInitAll)) dlsym(h, "ncclCommInitAll");
+    a.GroupStart = (decltype(a.GroupStart)) dlsym(h, "ncclGroupStart");
+    a.GroupEnd = (decltype(a.GroupEnd)) dlsym(h, "ncclGroupEnd");
+    a.Reduce = (decltype(a.Reduce)) dlsym(h, "ncclReduce");
+    a.GetErrorString = (decltype(a.GetErrorString)) dlsym(h, "ncclGetErrorString");
+    if (!a.CommInitAll || !a.GroupStart || !a.GroupEnd || !a.Reduce || !a.GetErrorString)
+        return fail(B2VP_ERR_UNSUPPORTED, "libnccl.so.2 lacks an entry point this library needs");
+    g_nccl = a;
+    return B2VP_OK;
+}
+#define NCCL_CHECK(expr)                                                                                          \
+    do {                                                                                                          \
+        ncclResult_t r_ = (expr);                                                                                 \
+        if (r_ != ncclSuccess)                                                                                    \
+            return fail(B2VP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, g_nccl.GetErrorString(r_), __FILE__, __LINE__); \
+    } while (0)
+
+int nccl_comms_for(const std::vector<int> &devices, std::vector<ncclComm_t> **out) {
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
+    int rc = nccl_load();
+    if (rc != B2VP_OK) return rc;
+    auto it = g_nccl_comms.find(devices);
+    if (it == g_nccl_comms.end()) {
+        std::vector<ncclComm_t> comms(devices.size());
+        NCCL_CHECK(g_nccl.CommInitAll(comms.data(), (int) devices.size(), devices.data()));
+        it = g_nccl_comms.emplace(devices, std::move(comms)).first;
+    }
+    *out = &it->second;
+    return B2VP_OK;
+}
+
+/* Interleaved sharding of `count` streams over n devices (b2vp_shard_streams): block = a power of two small enough
+   that every device gets many blocks (balance: pixels differ in cost, every device should see every pixel) and large
+   enough that a block is a few warps' worth of streams. */
+void shard_streams(uint64_t count, uint32_t n, uint32_t index, uint64_t *block, uint64_t *count_i) {
+    uint64_t B = 1024;
+    while (B > 32 && count / B < (uint64_t) n * 8) B >>= 1;
+    const uint64_t n_blocks = (count + B - 1) / B;
+    uint64_t c = 0;
+    if (n && index < n && n_blocks > index) {
+        const uint64_t mine = (n_blocks - index + n - 1) / n;          /* blocks index, index + n, ... */
+        c = mine * B;
+        const uint64_t last_block = index + (mine - 1) * (uint64_t) n;
+        if (last_block == n_blocks - 1 && count % B) c -= B - count % B;   /* the ragged last block is mine */
+    }
+    *block = B;
+    *count_i = c;
+}
 
 /* ---- majorant grids (B2vpRenderArgs::majorant_grid) ---------------------------------------------------------
    Built on first use, per precision instance.  For every heterogeneous medium whose sigma_t is a single-channel
@@ -832,7 +951,7 @@ template <typename F> const void *lanes_entry() { return sizeof(F) == 4 ? vp_lau
 
 /* Fills the shared-memory layout fields of `out` and the plan.  `count` = streams of this launch. */
 template <typename F>
-int plan_launch(b2vp_scene *s, DeviceScene<F> &ds, const B2vpRenderArgs *a, const DStreams &spd, size_t film_bytes,
+int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRenderArgs *a, const DStreams &spd, size_t film_bytes,
                 RenderOut<F> &out, LaunchPlan &pl, bool may_allocate = true) {
     /* shared memory: [tables][grids][film] */
     out.grid_smem_offset = align128(ds.g.blob_bytes);
@@ -861,7 +980,7 @@ int plan_launch(b2vp_scene *s, DeviceScene<F> &ds, const B2vpRenderArgs *a, cons
     }
     if (fast && (kernel == B2VP_KERNEL_LANES || kernel == B2VP_KERNEL_STREAM || kernel == B2VP_KERNEL_QUEUE_256))
         return fail(B2VP_ERR_INVALID, "B2VP_MATH_FAST exists for the 512-thread queue kernel only");
-    uint32_t launch_features = ds.g.features | (spd.il_block ? (uint32_t) FT_INTERLEAVE : 0u);
+    uint32_t launch_features = ds.g.features;
     const char *preset = "";
     pl.queue_kernel = kernel == B2VP_KERNEL_AUTO || kernel == B2VP_KERNEL_QUEUE_GENERIC || kernel == B2VP_KERNEL_QUEUE_256;
     out.mg = nullptr; out.mg_bytes = 0; out.mg_smem_offset = 0;
@@ -902,7 +1021,7 @@ int plan_launch(b2vp_scene *s, DeviceScene<F> &ds, const B2vpRenderArgs *a, cons
         if (a->tuning[0]) oversub = std::min(8.0, std::max(1.0, a->tuning[0] / 16.0));
         /* shared memory: [tables][grids][film][queue control + rings][path slots] */
         size_t base = (smem + 127) & ~(size_t) 127;
-        size_t avail = s->smem_optin > base + 1024 ? s->smem_optin - base - 1024 : 0;
+        size_t avail = dc->smem_optin > base + 1024 ? dc->smem_optin - base - 1024 : 0;
         size_t per_slot = sizeof(PathSlot<F>) + 2 * PH_N * sizeof(unsigned short);
         size_t max_slots = avail > 256 ? (avail - sizeof(QueueCtl) - 64) / per_slot : 0;
         size_t n_slots = std::min<size_t>((size_t) (pl.threads * oversub), max_slots) & ~(size_t) 31;
@@ -928,7 +1047,7 @@ int plan_launch(b2vp_scene *s, DeviceScene<F> &ds, const B2vpRenderArgs *a, cons
     CU_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pl.kern, pl.threads, smem));
     if (per_sm < 1) return fail(B2VP_ERR_CUDA, "kernel does not fit on an SM (smem %zu)", smem);
     const uint64_t want = (spd.count + pl.threads - 1) / pl.threads;
-    pl.grid = (int) std::min<uint64_t>((uint64_t) s->sm_count * per_sm, std::max<uint64_t>(want, 1));
+    pl.grid = (int) std::min<uint64_t>((uint64_t) dc->sm_count * per_sm, std::max<uint64_t>(want, 1));
     pl.smem = smem;
     pl.cold_bytes = pl.queue_kernel ? (size_t) pl.grid * out.q_n_slots * sizeof(PathCold<F>) : 0;
     return B2VP_OK;
@@ -945,10 +1064,11 @@ int set_stream_range(const B2vpRenderArgs *a, StreamSpace &sp) {
             a->interleave_index >= a->interleave_count)
             return fail(B2VP_ERR_INVALID, "invalid interleaved stream range");
         const uint64_t B = a->interleave_block, kmax = count - 1;
+        if (B & (B - 1)) return fail(B2VP_ERR_INVALID, "interleave_block must be a power of two (b2vp_shard_streams gives one)");
         const uint64_t last = first + ((kmax / B) * a->interleave_count + a->interleave_index) * B + kmax % B;
         if (last >= sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
         sp.d.il_block = B; sp.d.il_count = a->interleave_count; sp.d.il_index = a->interleave_index;
-        if ((B & (B - 1)) == 0) { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
+        { int sh = 0; while ((B >> sh) != 1) ++sh; sp.d.il_shift = sh; }
     } else if (first + count > sp.n_streams) return fail(B2VP_ERR_INVALID, "stream range out of bounds");
     sp.d.first = first;
     sp.d.count = count;
@@ -971,11 +1091,39 @@ void fill_totals(B2vpCounters &t, const unsigned long long *tot, float ms, uint3
     t.n_launches = launches;
 }
 
-template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
-    CU_CHECK(cudaSetDevice(s->device));
-    DeviceScene<F> &ds = dev_of<F>(s);
+/* Waits for everything queued on `stream` while watching for b2vp_cancel and the integrator's timeout
+   (should_stop(), include/mitsuba/render/integrator.h:143-146).  Either raises the device stop flag through the
+   context's control stream -- a 4-byte copy that overtakes the running kernel -- after which the kernel hands out no
+   new streams and drains.  *stopped: 0 ran to the end, 1 timeout, 2 cancelled. */
+int wait_for_render(b2vp_scene *s, DeviceCtx *dc, cudaStream_t stream, double timeout_s,
+                    std::chrono::steady_clock::time_point t_start, uint32_t *stopped) {
+    static const int one = 1;
+    *stopped = 0;
+    CU_CHECK(cudaEventRecord(dc->ev_done, stream));
+    for (;;) {
+        cudaError_t e = cudaEventQuery(dc->ev_done);
+        if (e == cudaSuccess) break;
+        if (e != cudaErrorNotReady) return fail(B2VP_ERR_CUDA, "render failed: %s", cudaGetErrorString(e));
+        if (!*stopped) {
+            uint32_t why = 0;
+            if (s->cancelled.load(std::memory_order_relaxed)) why = 2;
+            else if (timeout_s > 0 &&
+                     std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count() > timeout_s) why = 1;
+            if (why) {
+                CU_CHECK(cudaMemcpyAsync(dc->stop_flag.p, &one, sizeof(int), cudaMemcpyHostToDevice, dc->ctl_stream));
+                *stopped = why;
+            }
+        }
+        std::this_thread::yield();
+    }
+    return B2VP_OK;
+}
+
+template <typename F> int render_typed(b2vp_scene *s, DeviceCtx *dc, const B2vpRenderArgs *a, void *film_user) {
+    CU_CHECK(cudaSetDevice(dc->device));
+    DeviceScene<F> &ds = dev_of<F>(dc);
     if (!ds.ready) {
-        int rc = upload_scene<F>(s, ds);
+        int rc = upload_scene<F>(s, dc, ds);
         if (rc != B2VP_OK) return rc;
     }
     StreamSpace sp;
@@ -993,7 +1141,7 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     const size_t film_n = (size_t) W * H * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS), film_bytes = film_n * sizeof(F);
     RenderOut<F> out{};
     LaunchPlan pl;
-    rc = plan_launch<F>(s, ds, a, sp.d, film_bytes, out, pl);
+    rc = plan_launch<F>(s, dc, ds, a, sp.d, film_bytes, out, pl);
     if (rc != B2VP_OK) return rc;
 
     F *d_film;
@@ -1001,68 +1149,75 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
         d_film = (F *) film_user;
         if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
     } else {
-        if (s->film_buf.bytes < film_bytes) CU_CHECK(s->film_buf.alloc(film_bytes));
-        d_film = s->film_buf.as<F>();
+        if (dc->film_buf.bytes < film_bytes) CU_CHECK(dc->film_buf.alloc(film_bytes));
+        d_film = dc->film_buf.as<F>();
         if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
         else CU_CHECK(cudaMemcpyAsync(d_film, film_user, film_bytes, cudaMemcpyHostToDevice, stream));
     }
 
-    if (!s->totals_buf.p) CU_CHECK(s->totals_buf.alloc((TOT_N + 32) * sizeof(unsigned long long)));
-    if (!s->counter_buf.p) CU_CHECK(s->counter_buf.alloc(sizeof(unsigned long long)));
-    CU_CHECK(cudaMemsetAsync(s->totals_buf.p, 0, (TOT_N + 32) * sizeof(unsigned long long), stream));
-    CU_CHECK(cudaMemsetAsync(s->counter_buf.p, 0, sizeof(unsigned long long), stream));
+    if (!dc->totals_buf.p) CU_CHECK(dc->totals_buf.alloc((TOT_N + 32) * sizeof(unsigned long long)));
+    if (!dc->counter_buf.p) CU_CHECK(dc->counter_buf.alloc(sizeof(unsigned long long)));
+    CU_CHECK(cudaMemsetAsync(dc->totals_buf.p, 0, (TOT_N + 32) * sizeof(unsigned long long), stream));
+    CU_CHECK(cudaMemsetAsync(dc->counter_buf.p, 0, sizeof(unsigned long long), stream));
 
     if (a->seed_mode == B2VP_SEED_SCALAR_BLOCKS) {
-        CU_CHECK(s->blocks_buf.upload(sp.blocks.data(), sp.blocks.size() * sizeof(SpiralBlockD)));
-        sp.d.blocks = s->blocks_buf.as<SpiralBlockD>();
+        CU_CHECK(dc->blocks_buf.upload(sp.blocks.data(), sp.blocks.size() * sizeof(SpiralBlockD)));
+        sp.d.blocks = dc->blocks_buf.as<SpiralBlockD>();
     }
     if (a->seed_mode == B2VP_SEED_EXPLICIT && count) {
         for (uint64_t k = 0; k < count; ++k)
             if (a->explicit_pixel[k] >= (uint32_t) (W * H))
                 return fail(B2VP_ERR_INVALID, "explicit_pixel[%llu] outside the film", (unsigned long long) k);
-        CU_CHECK(s->ex_state.upload(a->explicit_state, count * 8));
-        CU_CHECK(s->ex_inc.upload(a->explicit_inc, count * 8));
-        CU_CHECK(s->ex_pixel.upload(a->explicit_pixel, count * 4));
-        sp.d.ex_state = s->ex_state.as<uint64_t>(); sp.d.ex_inc = s->ex_inc.as<uint64_t>();
-        sp.d.ex_pixel = s->ex_pixel.as<uint32_t>();
+        CU_CHECK(dc->ex_state.upload(a->explicit_state, count * 8));
+        CU_CHECK(dc->ex_inc.upload(a->explicit_inc, count * 8));
+        CU_CHECK(dc->ex_pixel.upload(a->explicit_pixel, count * 4));
+        sp.d.ex_state = dc->ex_state.as<uint64_t>(); sp.d.ex_inc = dc->ex_inc.as<uint64_t>();
+        sp.d.ex_pixel = dc->ex_pixel.as<uint32_t>();
     }
 
     out.film = d_film;
-    out.totals = s->totals_buf.as<unsigned long long>();
+    out.totals = dc->totals_buf.as<unsigned long long>();
     const bool want_qstats = (a->debug_flags & 1u) != 0;
     if (want_qstats) out.q_stats = out.totals + TOT_N;
-    out.work_counter = s->counter_buf.as<unsigned long long>();
+    out.work_counter = dc->counter_buf.as<unsigned long long>();
     const uint32_t sps = sp.d.samples_per_stream;
-    if (a->out_state && count) { CU_CHECK(s->o_state.alloc(count * 8)); out.out_state = s->o_state.as<uint64_t>(); }
+    if (a->out_state && count) { CU_CHECK(dc->o_state.alloc(count * 8)); out.out_state = dc->o_state.as<uint64_t>(); }
     if (a->out_counters && count) {
         static_assert(sizeof(PathCounters) == sizeof(B2vpPathCounters), "counter layout");
-        CU_CHECK(s->o_counters.alloc(count * sizeof(PathCounters)));
-        out.out_counters = s->o_counters.as<PathCounters>();
+        CU_CHECK(dc->o_counters.alloc(count * sizeof(PathCounters)));
+        out.out_counters = dc->o_counters.as<PathCounters>();
     }
     if (a->out_radiance && count) {
-        CU_CHECK(s->o_radiance.alloc(count * sps * sizeof(F)));
-        CU_CHECK(cudaMemsetAsync(s->o_radiance.p, 0, count * sps * sizeof(F), stream));
-        out.out_radiance = s->o_radiance.as<F>();
+        CU_CHECK(dc->o_radiance.alloc(count * sps * sizeof(F)));
+        CU_CHECK(cudaMemsetAsync(dc->o_radiance.p, 0, count * sps * sizeof(F), stream));
+        out.out_radiance = dc->o_radiance.as<F>();
     }
     if (pl.queue_kernel) {
         /* cold per-path state: one PathCold array per CTA in global memory (L2-resident) */
-        if (s->q_cold.bytes < pl.cold_bytes) CU_CHECK(s->q_cold.alloc(pl.cold_bytes));
-        out.q_cold = s->q_cold.p;
+        if (dc->q_cold.bytes < pl.cold_bytes) CU_CHECK(dc->q_cold.alloc(pl.cold_bytes));
+        out.q_cold = dc->q_cold.p;
     }
-    s->last_kernel = pl.name;
+    { std::lock_guard<std::mutex> lock(s->mutex); s->last_kernel = pl.name; }
+    out.stop_flag = dc->stop_flag.template as<int>();
+    CU_CHECK(cudaMemsetAsync(dc->stop_flag.p, 0, sizeof(int), stream));
 
-    if (s->cancelled.load()) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     uint32_t launches = 0;
-    CU_CHECK(cudaEventRecord(s->ev0, stream));
+    const auto t_start = std::chrono::steady_clock::now();
+    CU_CHECK(cudaEventRecord(dc->ev0, stream));
     if (count) {
         CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream));
         launches++;
     }
-    CU_CHECK(cudaEventRecord(s->ev1, stream));
+    CU_CHECK(cudaEventRecord(dc->ev1, stream));
     CU_CHECK(cudaGetLastError());
+    /* watch for cancel / timeout while the kernel runs -- BEFORE any read-back is queued: a device-to-host copy into
+       pageable memory blocks the host until the kernel is done */
+    uint32_t stopped = 0;
+    rc = wait_for_render(s, dc, stream, a->timeout_s, t_start, &stopped);
+    if (rc != B2VP_OK) return rc;
 
     unsigned long long tot[TOT_N + 32];
-    CU_CHECK(cudaMemcpyAsync(tot, s->totals_buf.p, sizeof(tot), cudaMemcpyDeviceToHost, stream));
+    CU_CHECK(cudaMemcpyAsync(tot, dc->totals_buf.p, sizeof(tot), cudaMemcpyDeviceToHost, stream));
     if (!a->film_on_device)
         CU_CHECK(cudaMemcpyAsync(film_user, d_film, film_bytes, cudaMemcpyDeviceToHost, stream));
     if (out.out_state) CU_CHECK(cudaMemcpyAsync(a->out_state, out.out_state, count * 8, cudaMemcpyDeviceToHost, stream));
@@ -1082,9 +1237,124 @@ template <typename F> int render_typed(b2vp_scene *s, const B2vpRenderArgs *a, v
     }
     if (a->totals) {
         float ms = 0;
-        CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        CU_CHECK(cudaEventElapsedTime(&ms, dc->ev0, dc->ev1));
         fill_totals(*a->totals, tot, ms, launches);
+        a->totals->stopped_early = stopped;
     }
+    if (stopped == 2)
+        return fail(B2VP_ERR_CANCELLED, "render cancelled (%llu of %llu paths were traced)", (unsigned long long) tot[TOT_PATHS],
+                    (unsigned long long) count * std::max<uint32_t>(sps, 1));
+    return B2VP_OK;
+}
+
+/* ---- multi-device render (B2vpRenderArgs::devices) ---------------------------------------------------------
+   Paths are independent and the only shared state is the film: the stream range is dealt out in
+   interleaved blocks (shard_streams), every device renders its share into a private film from its own host thread
+   (scene replica uploaded on first use), and one ncclReduce(sum) over NVLink merges the films on the root. */
+template <typename F> int render_multi(b2vp_scene *s, const B2vpRenderArgs *a, void *film_user) {
+    const uint32_t n = a->n_devices;
+    if (!a->devices || n > 64) return fail(B2VP_ERR_INVALID, "bad device list");
+    if (a->devices[0] != s->device)
+        return fail(B2VP_ERR_INVALID, "devices[0] must be the scene's device %d (the root of the film reduce)", s->device);
+    for (uint32_t i = 0; i < n; ++i)
+        for (uint32_t j = 0; j < i; ++j)
+            if (a->devices[i] == a->devices[j]) return fail(B2VP_ERR_INVALID, "device %d listed twice", a->devices[i]);
+    if (a->seed_mode == B2VP_SEED_EXPLICIT || a->out_state || a->out_counters || a->out_radiance || a->interleave_block)
+        return fail(B2VP_ERR_UNSUPPORTED, "multi-device render: explicit seeding, per-stream outputs and the caller's own "
+                                          "interleave_* are single-device features");
+    std::vector<DeviceCtx *> ctx(n);
+    std::vector<int> devs(a->devices, a->devices + n);
+    for (uint32_t i = 0; i < n; ++i) {
+        int rc = context_for(s, devs[i], &ctx[i]);
+        if (rc != B2VP_OK) return rc;
+    }
+    StreamSpace sp;
+    int rc = make_stream_space(s, a->seed_mode, 0, 0, sp);
+    if (rc != B2VP_OK) return rc;
+    const uint64_t first = a->first_stream;
+    if (first > sp.n_streams || (a->n_streams && first + a->n_streams > sp.n_streams))
+        return fail(B2VP_ERR_INVALID, "stream range out of bounds");
+    const uint64_t count = a->n_streams ? a->n_streams : sp.n_streams - first;
+    const size_t film_n = (size_t) sp.d.w * sp.d.h * (s->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS);
+    const size_t film_bytes = film_n * sizeof(F);
+
+    /* films: the root's is the caller's device film, or a staging buffer for a host film */
+    std::vector<F *> film(n);
+    std::vector<cudaStream_t> stream(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        CU_CHECK(cudaSetDevice(devs[i]));
+        stream[i] = i == 0 ? (cudaStream_t) a->cuda_stream : ctx[i]->work_stream;
+        if (i == 0 && a->film_on_device) { film[0] = (F *) film_user; continue; }
+        if (ctx[i]->film_buf.bytes < film_bytes) CU_CHECK(ctx[i]->film_buf.alloc(film_bytes));
+        film[i] = ctx[i]->film_buf.template as<F>();
+        if (i == 0 && !a->clear_film)
+            CU_CHECK(cudaMemcpyAsync(film[0], film_user, film_bytes, cudaMemcpyHostToDevice, stream[0]));
+    }
+    std::vector<ncclComm_t> *comms = nullptr;
+    rc = nccl_comms_for(devs, &comms);
+    if (rc != B2VP_OK) return rc;
+
+    std::vector<B2vpCounters> tot(n);
+    std::vector<int> rcs(n, B2VP_OK);
+    std::vector<std::string> errs(n);
+    auto work = [&](uint32_t i) {
+        B2vpRenderArgs ai = *a;
+        uint64_t B = 0, ci = 0;
+        shard_streams(count, n, i, &B, &ci);
+        ai.devices = nullptr; ai.n_devices = 0; ai.device = devs[i];
+        ai.film_on_device = 1;
+        ai.clear_film = i == 0 ? a->clear_film : 1u;
+        ai.first_stream = first; ai.n_streams = ci;
+        ai.interleave_block = B; ai.interleave_count = n; ai.interleave_index = i;
+        ai.totals = &tot[i];
+        ai.cuda_stream = (void *) stream[i];
+        std::memset(&tot[i], 0, sizeof(B2vpCounters));
+        if (ci == 0) {   /* nothing to render here: the film only has to be zero for the reduce */
+            if (cudaSetDevice(devs[i]) != cudaSuccess || (ai.clear_film && cudaMemsetAsync(film[i], 0, film_bytes, stream[i]) != cudaSuccess)) {
+                rcs[i] = B2VP_ERR_CUDA; errs[i] = "clearing the film of an idle device failed";
+            }
+            return;
+        }
+        rcs[i] = render_typed<F>(s, ctx[i], &ai, film[i]);
+        if (rcs[i] != B2VP_OK) errs[i] = g_error;   /* thread-local: carry it to the caller's thread */
+    };
+    std::vector<std::thread> pool;
+    for (uint32_t i = 1; i < n; ++i) pool.emplace_back(work, i);
+    work(0);
+    for (auto &t : pool) t.join();
+    bool cancelled = false;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (rcs[i] == B2VP_ERR_CANCELLED) { cancelled = true; continue; }
+        if (rcs[i] != B2VP_OK) return fail(rcs[i], "device %d: %s", devs[i], errs[i].c_str());
+    }
+
+    /* the single collective of this path: sum the films onto the root, in place */
+    const ncclDataType_t dt = sizeof(F) == 4 ? ncclFloat32 : ncclFloat64;
+    NCCL_CHECK(g_nccl.GroupStart());
+    for (uint32_t i = 0; i < n; ++i) {
+        CU_CHECK(cudaSetDevice(devs[i]));
+        NCCL_CHECK(g_nccl.Reduce(film[i], film[i], film_n, dt, ncclSum, 0, (*comms)[i], stream[i]));
+    }
+    NCCL_CHECK(g_nccl.GroupEnd());
+    for (uint32_t i = n; i-- > 0;) {
+        CU_CHECK(cudaSetDevice(devs[i]));
+        if (i == 0 && !a->film_on_device)
+            CU_CHECK(cudaMemcpyAsync(film_user, film[0], film_bytes, cudaMemcpyDeviceToHost, stream[0]));
+        CU_CHECK(cudaStreamSynchronize(stream[i]));
+    }
+    if (a->totals) {
+        B2vpCounters &t = *a->totals;
+        std::memset(&t, 0, sizeof(t));
+        for (uint32_t i = 0; i < n; ++i) {
+            t.n_paths += tot[i].n_paths; t.n_rng_draws += tot[i].n_rng_draws; t.n_medium_steps += tot[i].n_medium_steps;
+            t.n_null += tot[i].n_null; t.n_real += tot[i].n_real; t.n_intersect += tot[i].n_intersect;
+            t.n_surface += tot[i].n_surface; t.n_invalid_samples += tot[i].n_invalid_samples;
+            t.gpu_ms = std::max(t.gpu_ms, tot[i].gpu_ms);     /* the devices run side by side */
+            t.n_launches += tot[i].n_launches;
+            t.stopped_early = std::max(t.stopped_early, tot[i].stopped_early);
+        }
+    }
+    if (cancelled) return fail(B2VP_ERR_CANCELLED, "render cancelled");
     return B2VP_OK;
 }
 
@@ -1120,9 +1390,9 @@ int noalloc_scratch(int device, unsigned char **out) {
     return B2VP_OK;
 }
 
-template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderArgs *a, void *film_device) {
-    CU_CHECK(cudaSetDevice(s->device));
-    DeviceScene<F> &ds = dev_of<F>(s);
+template <typename F> int render_noalloc_typed(b2vp_scene *s, DeviceCtx *dc, const B2vpRenderArgs *a, void *film_device) {
+    CU_CHECK(cudaSetDevice(dc->device));
+    DeviceScene<F> &ds = dev_of<F>(dc);
     if (!ds.ready)
         return fail(B2VP_ERR_INVALID, "b2vp_render_noalloc: the scene is not resident on the device in this precision "
                                       "yet; call b2vp_render once at set-up (it allocates), then this entry point");
@@ -1144,7 +1414,7 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
     RenderOut<F> out{};
     out.film = d_film;
     LaunchPlan pl;
-    rc = plan_launch<F>(s, ds, a, sp.d, film_bytes, out, pl, false);
+    rc = plan_launch<F>(s, dc, ds, a, sp.d, film_bytes, out, pl, false);
     if (rc != B2VP_OK) return rc;
 
     /* scratch layout inside the static array: [totals + work counter][spiral blocks][cold path records] */
@@ -1157,7 +1427,7 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
                     "records), the static scratch array holds B2VP_NOALLOC_SCRATCH_BYTES = %zu; use b2vp_render",
                     need, head_bytes, blocks_bytes, pl.cold_bytes, (size_t) B2VP_NOALLOC_SCRATCH_BYTES);
     unsigned char *scr = nullptr;
-    rc = noalloc_scratch(s->device, &scr);
+    rc = noalloc_scratch(dc->device, &scr);
     if (rc != B2VP_OK) return rc;
     out.totals = reinterpret_cast<unsigned long long *>(scr);
     out.work_counter = out.totals + TOT_N + 32;
@@ -1169,22 +1439,22 @@ template <typename F> int render_noalloc_typed(b2vp_scene *s, const B2vpRenderAr
     }
     if (pl.queue_kernel) out.q_cold = scr + head_bytes + blocks_bytes;   /* every field is written before it is read */
     if (a->clear_film) CU_CHECK(cudaMemsetAsync(d_film, 0, film_bytes, stream));
-    s->last_kernel = pl.name;
+    { std::lock_guard<std::mutex> lock(s->mutex); s->last_kernel = pl.name; }
 
     uint32_t launches = 0;
-    CU_CHECK(cudaEventRecord(s->ev0, stream));
+    CU_CHECK(cudaEventRecord(dc->ev0, stream));
     if (count) {
         CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream));
         launches++;
     }
-    CU_CHECK(cudaEventRecord(s->ev1, stream));
+    CU_CHECK(cudaEventRecord(dc->ev1, stream));
     CU_CHECK(cudaGetLastError());
     unsigned long long tot[TOT_N];
     CU_CHECK(cudaMemcpyAsync(tot, out.totals, sizeof(tot), cudaMemcpyDeviceToHost, stream));
     CU_CHECK(cudaStreamSynchronize(stream));   /* also keeps sp.blocks alive until the copy above has run */
     if (a->totals) {
         float ms = 0;
-        CU_CHECK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        CU_CHECK(cudaEventElapsedTime(&ms, dc->ev0, dc->ev1));
         fill_totals(*a->totals, tot, ms, launches);
     }
     return B2VP_OK;
@@ -1217,8 +1487,10 @@ int b2vp_render_noalloc(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *f
         return fail(B2VP_ERR_INVALID, "B2vpRenderArgs ABI mismatch");
     if (args->device != scene->device)
         return fail(B2VP_ERR_INVALID, "scene lives on device %d, render asked for %d", scene->device, args->device);
-    if (args->precision == B2VP_PREC_F32) return render_noalloc_typed<float>(scene, args, film_device);
-    if (args->precision == B2VP_PREC_F64) return render_noalloc_typed<double>(scene, args, film_device);
+    if (args->n_devices > 1) return fail(B2VP_ERR_UNSUPPORTED, "b2vp_render_noalloc renders on the scene's device only");
+    DeviceCtx *dc = scene->contexts[0].get();
+    if (args->precision == B2VP_PREC_F32) return render_noalloc_typed<float>(scene, dc, args, film_device);
+    if (args->precision == B2VP_PREC_F64) return render_noalloc_typed<double>(scene, dc, args, film_device);
     return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
 }
 
@@ -1244,35 +1516,30 @@ int b2vp_scene_create(const B2vpSceneDesc *desc, int32_t device, b2vp_scene_t **
                     e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
     }
     if (device < 0 || device >= n) return fail(B2VP_ERR_INVALID, "device ordinal %d out of range", device);
-    /* single attributes, not cudaGetDeviceProperties: that call costs milliseconds on every scene */
-    int cc_major = 0, cc_minor = 0, sm_count = 0, smem_optin = 0;
-    CU_CHECK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
-    CU_CHECK(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, device));
-    CU_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
-    CU_CHECK(cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
-    if (cc_major != 10)
-        return fail(B2VP_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
-                    cc_major, cc_minor);
     std::unique_ptr<b2vp_scene> s(new b2vp_scene());
     s->device = device;
-    s->sm_count = sm_count;
-    s->smem_optin = (size_t) smem_optin;
     int rc = copy_desc(desc, s.get());
     if (rc != B2VP_OK) return rc;
     rc = build_bvh(s.get());
     if (rc != B2VP_OK) return rc;
-    CU_CHECK(cudaSetDevice(device));
-    CU_CHECK(cudaEventCreate(&s->ev0));
-    CU_CHECK(cudaEventCreate(&s->ev1));
+    DeviceCtx *dc = nullptr;
+    rc = context_for(s.get(), device, &dc);   /* contexts[0]: the scene's own device */
+    if (rc != B2VP_OK) return rc;
     *out = s.release();
     return B2VP_OK;
 }
 
 void b2vp_scene_destroy(b2vp_scene_t *scene) {
     if (!scene) return;
+    for (auto &c : scene->contexts) {
+        cudaSetDevice(c->device);
+        if (c->ev0) cudaEventDestroy(c->ev0);
+        if (c->ev1) cudaEventDestroy(c->ev1);
+        if (c->ev_done) cudaEventDestroy(c->ev_done);
+        if (c->ctl_stream) cudaStreamDestroy(c->ctl_stream);
+        if (c->work_stream) cudaStreamDestroy(c->work_stream);
+    }
     cudaSetDevice(scene->device);
-    if (scene->ev0) cudaEventDestroy(scene->ev0);
-    if (scene->ev1) cudaEventDestroy(scene->ev1);
     for (size_t i = 0; i < scene->volume_pinned.size(); ++i)
         if (scene->volume_pinned[i]) cudaHostUnregister(scene->volume_data[i].data());
     delete scene;
@@ -1303,8 +1570,8 @@ int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch) {
             return fail(B2VP_ERR_INVALID, "volume patch targets a grid volume");
         scene->volumes[patch->volume].value = patch->volume_value;
     }
-    /* only the small tables change: rebuild and re-upload the blob, grids and BVH stay resident */
-    CU_CHECK(cudaSetDevice(scene->device));
+    /* only the small tables change: rebuild and re-upload the blob, grids and BVH stay resident (on every device the
+       scene has been rendered on) */
     auto patch_dev = [&](auto &ds) -> int {
         using DS = std::remove_reference_t<decltype(ds)>;
         using F = decltype(ds.g.bs_radius);
@@ -1326,9 +1593,14 @@ int b2vp_scene_update(b2vp_scene_t *scene, const B2vpParamPatch *patch) {
         CU_CHECK(cudaMemcpy(ds.blob.p, b, ds.host_blob.size(), cudaMemcpyHostToDevice));
         return B2VP_OK;
     };
-    int rc = patch_dev(scene->dev32);
-    if (rc != B2VP_OK) return rc;
-    return patch_dev(scene->dev64);
+    for (auto &c : scene->contexts) {
+        CU_CHECK(cudaSetDevice(c->device));
+        int rc = patch_dev(c->dev32);
+        if (rc != B2VP_OK) return rc;
+        rc = patch_dev(c->dev64);
+        if (rc != B2VP_OK) return rc;
+    }
+    return B2VP_OK;
 }
 
 int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *data, uint64_t n_values, int32_t keep_max) {
@@ -1379,7 +1651,7 @@ int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *dat
             hv.max_value = mx;
         }
     }
-    CU_CHECK(cudaSetDevice(scene->device));
+    int cur_sm_count = 0;
     auto patch_dev = [&](auto &ds) -> int {
         using F = decltype(ds.g.bs_radius);
         if (!ds.ready) return B2VP_OK;
@@ -1395,7 +1667,7 @@ int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *dat
         }
         if (v.cells) {   /* the trilinear cell records are derived from the grid: rebuild them in place */
             const size_t n_cells = (size_t) (v.nx + 1) * (v.ny + 1) * (v.nz + 1);
-            const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) scene->sm_count * 16);
+            const int blocks = (int) std::min<size_t>((n_cells + 255) / 256, (size_t) cur_sm_count * 16);
             build_cells_kernel<F><<<blocks, 256>>>(v.data, const_cast<F *>(v.cells), v.nx, v.ny, v.nz);
             CU_CHECK(cudaGetLastError());
         }
@@ -1409,9 +1681,15 @@ int b2vp_scene_update_grid(b2vp_scene_t *scene, int32_t volume, const float *dat
         CU_CHECK(cudaDeviceSynchronize());
         return B2VP_OK;
     };
-    int rc = patch_dev(scene->dev32);
-    if (rc != B2VP_OK) return rc;
-    return patch_dev(scene->dev64);
+    for (auto &c : scene->contexts) {
+        CU_CHECK(cudaSetDevice(c->device));
+        cur_sm_count = c->sm_count;
+        int rc = patch_dev(c->dev32);
+        if (rc != B2VP_OK) return rc;
+        rc = patch_dev(c->dev64);
+        if (rc != B2VP_OK) return rc;
+    }
+    return B2VP_OK;
 }
 
 int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film) {
@@ -1420,9 +1698,26 @@ int b2vp_render(b2vp_scene_t *scene, const B2vpRenderArgs *args, void *film) {
         return fail(B2VP_ERR_INVALID, "B2vpRenderArgs ABI mismatch");
     if (args->device != scene->device)
         return fail(B2VP_ERR_INVALID, "scene lives on device %d, render asked for %d", scene->device, args->device);
-    if (args->precision == B2VP_PREC_F32) return render_typed<float>(scene, args, film);
-    if (args->precision == B2VP_PREC_F64) return render_typed<double>(scene, args, film);
+    /* like m_stop = false at the top of SamplingIntegrator::render (integrator.cpp:59): a cancel only stops the render
+       that is running when it arrives, and the handle stays usable afterwards */
+    scene->cancelled.store(0);
+    if (args->n_devices > 1) {
+        if (args->precision == B2VP_PREC_F32) return render_multi<float>(scene, args, film);
+        if (args->precision == B2VP_PREC_F64) return render_multi<double>(scene, args, film);
+        return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
+    }
+    if (args->n_devices == 1 && args->devices && args->devices[0] != scene->device)
+        return fail(B2VP_ERR_INVALID, "devices[0] must be the scene's device %d", scene->device);
+    DeviceCtx *dc = scene->contexts[0].get();
+    if (args->precision == B2VP_PREC_F32) return render_typed<float>(scene, dc, args, film);
+    if (args->precision == B2VP_PREC_F64) return render_typed<double>(scene, dc, args, film);
     return fail(B2VP_ERR_INVALID, "unknown precision %d", args->precision);
+}
+
+int b2vp_shard_streams(uint64_t count, uint32_t n, uint32_t index, uint64_t *block, uint64_t *count_i) {
+    if (!block || !count_i || n == 0 || index >= n) return fail(B2VP_ERR_INVALID, "bad sharding request");
+    shard_streams(count, n, index, block, count_i);
+    return B2VP_OK;
 }
 
 int b2vp_measure_fp32_peak(int32_t device, double *tflops) {

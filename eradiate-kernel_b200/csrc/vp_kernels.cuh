@@ -36,7 +36,13 @@ template <typename F> struct RenderOut {
     /* majorant grids of the scene's media (floats, staged in shared memory at mg_smem_offset), or null */
     const float *mg;
     uint32_t mg_bytes, mg_smem_offset;
+    /* raised by the host (cancel / timeout) while the kernel runs: no new stream is handed out once it is non-zero */
+    const int *stop_flag;
 };
+
+template <typename F> VP_D bool stop_requested(const RenderOut<F> &out) {
+    return out.stop_flag != nullptr && *reinterpret_cast<const volatile int *>(out.stop_flag) != 0;
+}
 
 struct StreamInfo {
     uint64_t state, inc;
@@ -171,7 +177,7 @@ volpath_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStr
 
     for (;;) {
         unsigned long long k = atomicAdd(out.work_counter, 1ull);
-        if (k >= sp.count) break;
+        if (k >= sp.count || stop_requested(out)) break;
         StreamInfo st = make_stream(sp, stream_index(sp, k));
         Pcg32 rng;
         rng.state = st.state; rng.inc = st.inc; rng.draws = 0;

@@ -23,14 +23,6 @@ template <typename F, int MAXT, uint32_t FEAT> const void *q_entry() {
 
 template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool force_generic, const char **name) {
     if (force_generic) ft = FT_ALL;
-    /* interleaved launches (multi-GPU sharding): the two scene classes the benchmarks shard have an instance with
-       the interleaved stream mapping, everything else goes to the generic instance */
-    if (ft & FT_INTERLEAVE) {
-        if ((ft & ~(PRE_HET | FT_INTERLEAVE)) == 0) { *name = "heterogeneous, interleaved"; return q_entry<F, MAXT, PRE_HET | FT_INTERLEAVE>(); }
-        if ((ft & ~(PRE_HET_ALB | FT_INTERLEAVE)) == 0) { *name = "heterogeneous+albedo grid, interleaved"; return q_entry<F, MAXT, PRE_HET_ALB | FT_INTERLEAVE>(); }
-        *name = "generic";
-        return q_entry<F, MAXT, FT_ALL>();
-    }
     if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return q_entry<F, MAXT, PRE_HOMOG>(); }
     if ((ft & ~PRE_HOMOG_BIG) == 0) { *name = "homogeneous, large mesh"; return q_entry<F, MAXT, PRE_HOMOG_BIG>(); }
     if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return q_entry<F, MAXT, PRE_HET>(); }

@@ -703,7 +703,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 uint32_t j = c.j;
                 int px = 0, py = 0, box = 0, boy = 0, bsx = 0, bsy = 0;
                 bool empty = true;
-                if (fl & QF_HAVE_STREAM) stream_pixel(sp, stream_index<(FEAT & FT_INTERLEAVE) != 0>(sp, k), px, py, box, boy, bsx, bsy, empty);
+                if (fl & QF_HAVE_STREAM) stream_pixel(sp, stream_index(sp, k), px, py, box, boy, bsx, bsy, empty);
                 if (state == Q_PATH_END) {
                     /* render_sample tail (integrator.cpp:267-287) + ImageBlock::put (imageblock.cpp:85-169) */
                     F value = c.ray_weight * c.result;
@@ -759,10 +759,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 }
                 if (!(fl & QF_HAVE_STREAM)) {
                     k = atomicAdd(out.work_counter, 1ull);
-                    if (k >= sp.count) {
+                    if (k >= sp.count || stop_requested(out)) {   /* should_stop() (integrator.h:143-146) */
                         state = Q_DEAD;
                     } else {
-                        StreamInfo st = make_stream(sp, stream_index<(FEAT & FT_INTERLEAVE) != 0>(sp, k));
+                        StreamInfo st = make_stream(sp, stream_index(sp, k));
                         c.k = k;
                         s.rng_state_lo = (uint32_t) st.state; s.rng_state_hi = (uint32_t) (st.state >> 32);
                         s.rng_inc_lo = (uint32_t) st.inc; s.rng_inc_hi = (uint32_t) (st.inc >> 32);

@@ -321,7 +321,7 @@ struct DStreams {
     uint64_t first, count;          /* range rendered by this launch */
     uint64_t il_block;              /* > 0: interleaved blocks (B2vpRenderArgs::interleave_*) */
     uint32_t il_count, il_index;
-    int il_shift;                   /* log2(il_block) when that is a power of two (shift / mask instead of divisions), else -1 */
+    int il_shift;                   /* log2(il_block), or -1: no interleaving */
     uint32_t samples_per_stream, spp_pass, n_passes, bs;
     uint32_t n_blocks;
     const SpiralBlockD *blocks;
@@ -331,13 +331,12 @@ struct DStreams {
     const uint32_t *ex_pixel;
 };
 
-/* global stream index of the k-th stream of a launch; IL = false compiles the interleaved mapping (two 64-bit
-   divisions) out of kernel instances that are never launched with it */
-template <bool IL = true> VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
-    if (!IL || sp.il_block == 0) return sp.first + k;
-    if (sp.il_shift >= 0)
-        return sp.first + ((((k >> sp.il_shift) * sp.il_count + sp.il_index) << sp.il_shift) | (k & (sp.il_block - 1)));
-    return sp.first + ((k / sp.il_block) * sp.il_count + sp.il_index) * sp.il_block + k % sp.il_block;
+/* global stream index of the k-th stream of a launch.  Interleaved sharding (B2vpRenderArgs::interleave_*): blocks are
+   a power of two (il_shift = log2), so the map is a shift, a multiply and a mask -- cheap enough to be part of every
+   kernel instance (round 1 kept it out of the single-GPU instances because the general map needed two 64-bit divisions). */
+VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
+    if (sp.il_shift < 0) return sp.first + k;
+    return sp.first + ((((k >> sp.il_shift) * sp.il_count + sp.il_index) << sp.il_shift) | (k & (sp.il_block - 1)));
 }
 
 struct PathCounters { uint32_t draws, medium_steps, n_null, n_real, n_intersect, n_surface; };

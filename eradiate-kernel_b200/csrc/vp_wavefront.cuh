@@ -446,7 +446,7 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 }
                 if (!have_stream) {
                     k = atomicAdd(out.work_counter, 1ull);
-                    if (k >= sp.count) {
+                    if (k >= sp.count || stop_requested(out)) {
                         state = L_DONE;
                     } else {
                         st = make_stream(sp, stream_index(sp, k));

@@ -113,13 +113,16 @@ class DeviceScene:
 
     def render(self, seed_mode=abi.SEED_WAVEFRONT, precision=None, first_stream=0, n_streams=0, explicit=None, interleave=None,
                want_paths=False, film=None, stream=None, device_film=None, clear=True, kernel=None, math=None,
-               tuning=None, debug=0, majorant_grid=0):
+               tuning=None, debug=0, majorant_grid=0, timeout=0.0, devices=None):
         """Renders a stream range.  `explicit` = (state u64[], inc u64[], pixel u32[], samples_per_stream).
         `film`: optional (H, W, 5) array to accumulate into (otherwise a fresh zeroed film).
         `kernel`: "auto" | "generic" | "q256" | "lanes" | "mega"; `math`: "exact" (bit-exact against the oracle) |
         "fast" (fp32 tolerance mode, B2VP_MATH_FAST); `tuning`: queue-kernel scheduler parameters; `majorant_grid`:
         non-zero = opt-in free-flight sampling against a grid of local majorants (B2vpRenderArgs::majorant_grid: same
-        estimator, other random sequence -- statistically, not per-path, equal to the reference's global majorant)."""
+        estimator, other random sequence -- statistically, not per-path, equal to the reference's global majorant);
+        `timeout`: seconds after which no new streams are started (the integrator's `timeout` property; the result
+        holds the samples taken so far and totals.stopped_early = 1); `devices`: list of CUDA devices for a multi-GPU
+        render inside the library (devices[0] = this scene's device; films merged by one NCCL reduce)."""
         prec = self.scene.precision if precision is None else precision
         dtype = np.float32 if prec == abi.PREC_F32 else np.float64
         w, h = self.scene.film_size
@@ -129,6 +132,10 @@ class DeviceScene:
         a.cuda_stream = stream
         a.first_stream, a.n_streams = first_stream, n_streams
         _set_launch_options(a, kernel, math, tuning, debug, majorant_grid)
+        a.timeout_s = float(timeout)
+        if devices is not None:
+            dev = (C.c_int32 * len(devices))(*devices)
+            a.devices, a.n_devices = dev, len(devices)
         if interleave is not None:   # (block, count, index): B2vpRenderArgs::interleave_*
             a.interleave_block, a.interleave_count, a.interleave_index = interleave
         keep = []
@@ -191,6 +198,14 @@ class DeviceScene:
         a.totals = C.pointer(tot)
         abi.check(abi.lib().b2vp_render_noalloc(self._h, C.byref(a), device_film))
         return tot
+
+
+def shard_streams(count, n, index):
+    """b2vp_shard_streams: (block, count_i) of device `index` of `n` for a render of `count` streams -- the partition a
+    multi-device b2vp_render uses; with first_stream it gives interleave=(block, n, index), n_streams=count_i."""
+    block, ci = C.c_uint64(), C.c_uint64()
+    abi.check(abi.lib().b2vp_shard_streams(int(count), int(n), int(index), C.byref(block), C.byref(ci)))
+    return block.value, ci.value
 
 
 def render(scene, device=0, **kw):

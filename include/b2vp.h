@@ -302,7 +302,7 @@ typedef struct B2vpCounters {
     uint64_t n_invalid_samples; /* dropped by ImageBlock::put (imageblock.cpp:85-109) */
     double gpu_ms;              /* CUDA-event time of the render kernels       */
     uint32_t n_launches;        /* kernels launched by this call               */
-    uint32_t reserved0;
+    uint32_t stopped_early;     /* 1: stopped by timeout_s, 2: by b2vp_cancel; n_paths < requested */
 } B2vpCounters;
 
 typedef struct B2vpRenderArgs {
@@ -360,6 +360,22 @@ typedef struct B2vpRenderArgs {
        random sequence, so paths draw fewer random numbers and the result agrees with the global-majorant film
        statistically (z-test), not per path.  Queue kernel only; other media in the scene are unaffected.          */
     uint32_t majorant_grid;
+    /* Integrator `timeout` property (include/mitsuba/render/integrator.h:143-146, src/librender/integrator.cpp:35,
+       59-65,121): > 0 = stop handing out new streams once this many seconds of rendering have passed; paths in flight
+       finish, the call returns B2VP_OK with the samples taken so far (the film's weight channel counts them, so it
+       stays normalised) and B2vpCounters::stopped_early = 1 -- what SamplingIntegrator::render does when should_stop()
+       turns true.  <= 0: no limit.                                                                                    */
+    double timeout_s;
+    /* Multi-GPU render behind the boundary (no counterpart in the reference, whose render is TBB on one host:
+       src/librender/integrator.cpp:109-139).  n_devices > 1: devices[0] must be the scene's device (the root); the
+       stream range is dealt out in interleaved blocks to the listed devices, each renders into a private film from
+       its own host thread, and ONE NCCL reduce (sum) over NVLink merges the films on the root, from where `film`
+       is filled.  The scene is uploaded to a device the first time it renders there and stays resident;
+       b2vp_scene_update / _update_grid patch every resident copy.  Not combinable with explicit seeding, per-stream
+       outputs or the caller's own interleave_*.  n_devices <= 1 (devices may be NULL): args->device only.            */
+    const int32_t *devices;
+    uint32_t n_devices;
+    uint32_t reserved2;
 } B2vpRenderArgs;
 
 typedef struct b2vp_scene b2vp_scene_t;
@@ -429,7 +445,17 @@ typedef struct B2vpSceneInfo {
 } B2vpSceneInfo;
 int b2vp_scene_info(const b2vp_scene_t *scene, B2vpSceneInfo *info);
 
-/* Asynchronous cancel (Integrator::cancel): polled between kernel launches.   */
+/* How the streams [0, count) of a render are dealt out to n devices: interleaved blocks of `*block` streams (a power
+   of two), device `index` taking blocks index, index + n, ...; `*count_i` = how many streams that is.  Pure host
+   arithmetic (callable without a GPU): the partition b2vp_render uses for args->n_devices > 1, and the values to put
+   into interleave_block / interleave_count / interleave_index when sharding by hand (one process per GPU).          */
+int b2vp_shard_streams(uint64_t count, uint32_t n, uint32_t index, uint64_t *block, uint64_t *count_i);
+
+/* Asynchronous cancel (Integrator::cancel, include/mitsuba/render/integrator.h:44-51): may be called from another
+   thread while b2vp_render runs (it only sets a flag, no CUDA call).  The running render stops handing out new
+   streams -- the persistent kernel polls a device flag where it fetches them -- lets the paths in flight finish and
+   returns B2VP_ERR_CANCELLED; the film holds what was accumulated.  Like the reference's m_stop, the flag is cleared
+   when the next b2vp_render starts: the handle stays usable, and a cancel between renders has no effect.           */
 void b2vp_cancel(b2vp_scene_t *scene);
 
 /* Thread-local message of the last failing call on this thread.               */

@@ -58,3 +58,31 @@ def test_shard_range_partitions(pkg):
             assert r[0][0] == 0 and sum(c for _, c in r) == n
             assert all(r[i][0] + r[i][1] == r[i + 1][0] for i in range(w - 1))
             assert max(c for _, c in r) - min(c for _, c in r) <= 1
+
+
+def test_shard_streams_partitions(pkg):
+    """b2vp_shard_streams (the partition of a multi-device b2vp_render; host arithmetic, no GPU): the interleaved
+    blocks of the n devices are disjoint, cover [0, count) exactly, are balanced to within one block, and the
+    kernel's index map (block a power of two: shift, multiply, mask) lands every local stream in its own block."""
+    for count in (1, 31, 32, 33, 1000, 4096, 65537, 4194304, 16777216 + 5):
+        for n in (1, 2, 3, 4, 8):
+            seen, sizes, total = None, [], 0
+            if count <= 65537:
+                seen = np.zeros(count, dtype=np.int32)
+            for i in range(n):
+                block, ci = pkg.shard_streams(count, n, i)
+                assert block & (block - 1) == 0 and block >= 32
+                sizes.append(ci)
+                total += ci
+                if seen is not None and ci:
+                    k = np.arange(ci, dtype=np.uint64)
+                    sh = int(block).bit_length() - 1
+                    g = (((k >> np.uint64(sh)) * np.uint64(n) + np.uint64(i)) << np.uint64(sh)) | (k & np.uint64(block - 1))
+                    assert g.max() < count
+                    np.add.at(seen, g.astype(np.int64), 1)
+            assert total == count, (count, n, sizes)
+            assert max(sizes) - min(sizes) <= block
+            if seen is not None:
+                assert (seen == 1).all(), (count, n)
+    with __import__("pytest").raises(pkg.B2vpError):
+        pkg.shard_streams(100, 0, 0)

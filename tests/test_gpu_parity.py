@@ -172,23 +172,38 @@ def test_stream_ranges_partition(pkg, oracle):
         assert np.allclose(acc.film, full.film, rtol=2e-4, atol=1e-6)
 
 
-@pytest.mark.parametrize("spp", [12, 18])   # blocks of 4 (shift / mask index map) and of 6 (divisions)
-def test_interleaved_ranges_partition(pkg, oracle, kernel, spp):
-    """Interleaved sharding (B2vpRenderArgs::interleave_*): three ranks, each a third of every pixel's samples; the
-    films add up to the full render, every rank's paths are bit-exact against the oracle."""
+@pytest.mark.parametrize("spp,ranks", [(12, 3), (32, 4)])   # blocks of 4 and of 8 streams (powers of two)
+def test_interleaved_ranges_partition(pkg, oracle, kernel, spp, ranks):
+    """Interleaved sharding (B2vpRenderArgs::interleave_*): each rank a share of every pixel's samples; the films add up
+    to the full render, every rank's paths are bit-exact against the oracle (whose index map is the general one, with
+    divisions; the device's is shift / multiply / mask, which is why blocks must be powers of two)."""
     sc = pkg.load_dict(scenes.c2(spp=spp, width=24))
     with pkg.DeviceScene(sc) as ds:
         full = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT)
         acc = np.zeros_like(full.film)
-        for rank in range(3):
-            kw = pkg.shard_interleaved(spp, 24, rank, 3)
+        for rank in range(ranks):
+            kw = pkg.shard_interleaved(spp, 24, rank, ranks)
             got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
             ref = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, want_paths=True, **kw)
             assert np.array_equal(got.state, ref.state) and np.array_equal(got.radiance, ref.radiance)
             assert np.array_equal(got.counters, ref.counters)
-            assert (got.film[..., 4] == spp // 3).all()
+            assert (got.film[..., 4] == spp // ranks).all()
             acc += got.film
         assert np.allclose(acc, full.film, rtol=2e-4, atol=1e-6)
+        # the partition b2vp_render itself uses for a multi-device render (b2vp_shard_streams), by hand on one device
+        n, _ = ds.stream_count(pkg.abi.SEED_WAVEFRONT)
+        acc = np.zeros_like(full.film)
+        paths = 0
+        for rank in range(3):
+            block, count = pkg.shard_streams(n, 3, rank)
+            got = ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, n_streams=count, interleave=(block, 3, rank), want_paths=True)
+            ref = oracle.render(pkg, sc, pkg.abi.SEED_WAVEFRONT, n_streams=count, interleave=(block, 3, rank), want_paths=True)
+            assert np.array_equal(got.state, ref.state) and np.array_equal(got.counters, ref.counters)
+            acc += got.film
+            paths += got.totals.n_paths
+        assert paths == full.totals.n_paths and np.allclose(acc, full.film, rtol=2e-4, atol=1e-6)
+        with pytest.raises(pkg.B2vpError, match="power of two"):
+            ds.render(seed_mode=pkg.abi.SEED_WAVEFRONT, n_streams=6 * 24, interleave=(6, 3, 0))
 
 
 def test_scene_update_matches_fresh_scene(pkg, oracle):
