@@ -32,6 +32,27 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def host_info():
+    """CPU model, physical cores and hardware threads of the box (for the cpu_baseline record)."""
+    model, cores = "unknown", set()
+    try:
+        phys = core = None
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name") and model == "unknown":
+                model = line.split(":", 1)[1].strip()
+            elif line.startswith("physical id"):
+                phys = line.split(":", 1)[1].strip()
+            elif line.startswith("core id"):
+                core = line.split(":", 1)[1].strip()
+                cores.add((phys, core))
+    except OSError:
+        pass
+    return {"cpu_model": model, "physical_cores": len(cores) or None, "hardware_threads": os.cpu_count()}
+
+
+REF_BLOCK_SIZE = 2   # 256 x 1 film -> 128 image blocks: several per thread, so TBB can balance pixels of different cost
+
+
 def workload(spp):
     import scenes
     return scenes.c2(spp=spp, width=WIDTH, tau=0.5, nz=1000)
@@ -82,13 +103,15 @@ def ref_time_sample(pkg, budget_s, threads):
     `budget_s` seconds.  The time is that of Integrator::render (the reference's "Processing finished (took ..)"
     interval): scene loading and kd-tree build are outside it.  Returns None where the reference is not built."""
     from oracle import ref_xml
-    if not ref_xml.available():
+    build = "release" if ref_xml.available("release") else "parity"
+    if not ref_xml.available(build):
         return None
     import tempfile
     with tempfile.TemporaryDirectory(prefix="b2vp_refbench_") as tmp:
         def run(spp):
             d = ref_xml.round_f32(workload(spp))
-            _, sec = ref_xml.render(d, "scalar_mono", threads=threads, write_vol=pkg.scene.write_vol, keep_dir=tmp)
+            d["integrator"]["block_size"] = REF_BLOCK_SIZE
+            _, sec = ref_xml.render(d, "scalar_mono", threads=threads, write_vol=pkg.scene.write_vol, keep_dir=tmp, build=build)
             return sec
         pilot_spp = 64
         t = max(run(pilot_spp), 1e-4)
@@ -96,7 +119,10 @@ def ref_time_sample(pkg, budget_s, threads):
         spp = 1 << (spp.bit_length() - 1)   # a power of two like the workload's 2^14
         sec = run(spp)
     n = WIDTH * spp
-    return {"paths": n, "seconds": sec, "mpaths_s": n / sec / 1e6, "spp": spp}
+    return {"paths": n, "seconds": sec, "mpaths_s": n / sec / 1e6, "spp": spp,
+            "build": "the reference's Release flags: " + ref_xml.RELEASE_FLAGS if build == "release"
+                     else "parity build: " + ref_xml.PARITY_FLAGS,
+            "block_size": REF_BLOCK_SIZE}
 
 
 def plugin_time(pkg, spp):
@@ -112,6 +138,51 @@ def plugin_time(pkg, spp):
     return {"value": WIDTH * spp / sec / 1e6, "unit": "Mpaths/s", "ms_per_render": sec * 1e3,
             "what": "reference binary + volpath_b200 plugin (wavefront seeding), time of Integrator::render "
                     "(third call in the process): object graph -> descriptor, scene upload, kernel, film read-back"}
+
+
+def other_configs(pkg, math, fp32_peak, hbm_gbs):
+    """BASELINE configs[0], [2], [4] at full size on one GPU, each with the roofline that bounds it:
+    kernel time from CUDA events around the launch (B2vpCounters::gpu_ms), best of two after a warm-up render."""
+    import scenes
+    abi = pkg.abi
+    out = []
+
+    def run(name, what, d):
+        sc = pkg.load_dict(d)
+        with pkg.DeviceScene(sc, device=0) as ds:
+            ds.render(seed_mode=abi.SEED_WAVEFRONT, math=math)
+            best = None
+            for _ in range(2):
+                r = ds.render(seed_mode=abi.SEED_WAVEFRONT, math=math)
+                if best is None or r.totals.gpu_ms < best.totals.gpu_ms:
+                    best = r
+            kernel = ds.info().last_kernel.decode()
+        t, k = best.totals, best.totals.gpu_ms * 1e-3
+        return {"config": name, "workload": what, "kernel": kernel, "paths": t.n_paths, "kernel_ms": t.gpu_ms,
+                "mpaths_s": t.n_paths / k / 1e6, "segments_per_s": (t.n_medium_steps + t.n_intersect) / k}, t, k
+
+    e, t, k = run("C1", "homogeneous Rayleigh cube over a diffuse rectangle, distant 1x1, 10^6 spp", scenes.c1(spp=1000000))
+    ach = t.n_medium_steps * FLOP_PER_SEGMENT / k / 1e12
+    e["roofline"] = {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                     "note": "2.2 ms launch with 7 paths per slot: too short to fill the machine"}
+    out.append(e)
+    e, t, k = run("C3", "cloud field: gridvolume 256^3 sigma_t and albedo, hg g=0.85, distant 512x512, 64 spp",
+                  scenes.c3(spp=64, n=256, size=512))
+    alg = t.n_medium_steps * 32 * 2     # one 32-byte cell record per lookup and field (sigma_t, albedo)
+    e["roofline"] = {"bound": "hbm", "achieved": alg / k / 1e9, "peak": hbm_gbs, "unit": "GB/s",
+                     "frac": alg / k / 1e9 / hbm_gbs if hbm_gbs else None,
+                     "algorithmic": "%d lookups x 32 B x 2 fields" % t.n_medium_steps,
+                     "note": "gather-latency bound at 16 warps per SM, not bandwidth bound (DESIGN.md section 5)"}
+    out.append(e)
+    e, t, k = run("C5", "canopy: 10^6 triangles (BVH), homogeneous Rayleigh slab, diffuse leaves, mradiancemeter 4096, 256 spp",
+                  scenes.c5(spp=256, n_leaves=500000, n_sensors=4096))
+    alg = t.n_bvh_nodes * 32 + t.n_bvh_tris * 48
+    e["roofline"] = {"bound": "hbm", "achieved": alg / k / 1e9, "peak": hbm_gbs, "unit": "GB/s",
+                     "frac": alg / k / 1e9 / hbm_gbs if hbm_gbs else None,
+                     "algorithmic": "%d BVH nodes x 32 B + %d leaf triangles x 48 B (kernel counters)" % (t.n_bvh_nodes, t.n_bvh_tris),
+                     "note": "traversal is latency bound: 31 MB of nodes + 48 MB of leaf triangles sit in the 126 MB L2"}
+    out.append(e)
+    return out
 
 
 class ClockSampler:
@@ -177,8 +248,9 @@ def run_reference(args):
     pilot = oracle.render(pkg, scene, pkg.abi.SEED_WAVEFRONT, first_stream=0, n_streams=8192).totals
     seg = v * 1e6 * (pilot.n_medium_steps + pilot.n_intersect) / pilot.n_paths
     if kind == "reference":
-        sample = ("the workload at %d spp (%d paths) per step, unmodified reference binary (oracle/_ref/refprobe, "
-                  "scalar_mono, TBB %d threads), time of Integrator::render" % (res[0]["spp"], res[0]["paths"], threads))
+        sample = ("the workload at %d spp (%d paths) per step, unmodified reference binary (refprobe, scalar_mono, TBB %d "
+                  "threads, block_size %d = 128 blocks; %s), time of Integrator::render" % (
+                      res[0]["spp"], res[0]["paths"], threads, res[0]["block_size"], res[0]["build"]))
     else:
         sample = "%d of %d streams of the workload per step (64+ chunks spread evenly over the film), %d threads" % (
             res[0]["paths"], WIDTH * args.spp, threads)
@@ -187,7 +259,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / len(res) * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "segments_per_s": seg, "config": config(args.spp, args.gpus),
-        "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": threads, "kind": kind, "sample": sample},
+        "cpu_baseline": dict({"value": v, "unit": "Mpaths/s", "cores": threads, "kind": kind, "sample": sample,
+                              "per_thread_mpaths_s": v / threads}, **host_info()),
         "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -291,6 +364,45 @@ def run_ours(args):
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_val = paths_per_step / (float(e2e_t.item()) * 1e-3) / 1e6
 
+    # ---- the bit-exact mode timed beside the product (fast) mode: same workload, kernel-only
+    exact = None
+    if world == 1 and args.math == "fast" and not args.profile:
+        ms = []
+        for i in range(5):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            r = ds.render(seed_mode=abi.SEED_WAVEFRONT, device_film=film.data_ptr(), clear=True, stream=stream, math="exact", **shard)
+            if i >= 2:
+                ms.append(r.totals.gpu_ms)
+        exact = {"value": per_gpu / (sum(ms) / len(ms) * 1e-3) / 1e6, "unit": "Mpaths/s", "kernel_ms": sum(ms) / len(ms),
+                 "what": "B2VP_MATH_EXACT: every fp32 operation in the oracle's IEEE order; films, PCG32 states and event "
+                         "counters bit-identical to the CPU oracle"}
+
+    # ---- strong scaling: the FIXED single-GPU workload (spp per pixel, not spp x N) split over the N GPUs, one process,
+    # through b2vp_render's device list (host thread per GPU, one NCCL film reduce); rank 0 drives, the others wait
+    strong = None
+    if world > 1 and not args.profile:
+        barrier()
+        if rank == 0:
+            try:
+                sc1 = pkg.load_dict(workload(args.spp))
+                with pkg.DeviceScene(sc1, device=local) as dsm:
+                    devs = [local] + [d for d in range(world) if d != local]
+                    dsm.render(math=args.math, devices=devs)
+                    ts = []
+                    for _ in range(5):
+                        t0 = time.perf_counter()
+                        r = dsm.render(math=args.math, devices=devs)
+                        ts.append(time.perf_counter() - t0)
+                    t1 = min(ts)
+                strong = {"gpus": world, "paths": int(r.totals.n_paths), "wall_ms": t1 * 1e3, "mpaths_s": r.totals.n_paths / t1 / 1e6,
+                          "slowest_kernel_ms": r.totals.gpu_ms,
+                          "what": "the fixed %d-path workload of N=1 split over %d GPUs inside b2vp_render (device list), "
+                                  "wall time of the call incl. the NCCL film reduce and the film read-back" % (r.totals.n_paths, world)}
+            except Exception as e:   # reported, never fatal for the bench line
+                strong = {"error": str(e)[-300:]}
+        barrier()
+
     if rank == 0:
         # ---- roofline of the dominant kernel (the queue kernel, vp_queue.cuh): FP32 issue bound on this workload
         peaks = {}
@@ -306,15 +418,20 @@ def run_ours(args):
         # DRAM traffic of one launch of this kernel on this workload, from the committed `ncu --set full`
         # capture (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); None if the
         # capture is for another spp
-        traffic = None
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-            if int(tr.get("spp", -1)) == args.spp:
-                traffic = tr["dram_bytes_per_launch"]
-        except (OSError, ValueError, KeyError):
-            pass
+        traffic, traffic_source = None, "not measured at N > 1"
+        if world == 1:
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[args.math]
+                if int(tr.get("spp", -1)) == args.spp:
+                    traffic = tr["dram_bytes_per_launch"]
+                    traffic_source = "dram__bytes_read.sum + dram__bytes_write.sum of this kernel on this workload from the " \
+                                     "committed capture %s (N = 1; ncu cannot run inside the timed region)" % tr["capture"]
+            except (OSError, ValueError, KeyError):
+                traffic_source = "no committed capture for this mode"
         roofline = {"bound": "fp32", "achieved": achieved, "peak": fp32.value, "unit": "TFLOP/s",
-                    "frac": achieved / fp32.value if fp32.value else None, "traffic": traffic,
+                    "frac": achieved / fp32.value if fp32.value else None, "traffic": traffic, "traffic_source": traffic_source,
+                    "peak_is": "the FMA peak (2 flop per instruction); the exact mode issues no contracted FMAs, its "
+                               "ceiling is half of it" if args.math == "exact" else "the FMA peak (2 flop per instruction)",
                     "kernel": "vp::volpath_q_kernel [%s]" % ds.info().last_kernel.decode(), "kernel_ms": k_ms,
                     "algorithmic": "%d medium steps x %d flop" % (tot_last.n_medium_steps, FLOP_PER_SEGMENT),
                     "peak_source": "b2vp_measure_fp32_peak (FMA microbenchmark, measured in this run); "
@@ -326,6 +443,12 @@ def run_ours(args):
         host_legs = world == 1 and not args.profile
         cb = cpu_time_sample(pkg, pkg.load_dict(workload(args.spp)), 8.0 if host_legs else 0.2, threads)
         rb = ref_time_sample(pkg, 8.0, threads) if host_legs else None
+        configs = None
+        if host_legs:
+            try:
+                configs = other_configs(pkg, args.math, fp32.value, peaks.get("hbm_gbs"))
+            except Exception as e:   # reported, never fatal for the bench line
+                configs = [{"error": str(e)[-300:]}]
         out = {
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -347,15 +470,24 @@ def run_ours(args):
                 pl = {"error": str(e)[-300:]}
             if pl is not None:
                 out["e2e_plugin"] = pl
+        if exact is not None:
+            out["exact_mode"] = exact
+        if strong is not None:
+            out["strong_scaling"] = strong
+        if configs is not None:
+            out["configs"] = configs
         if not host_legs:
             out["cpu_baseline"]["sample"] += " (a token sample: the CPU legs are timed in the N=1 run)"
         if rb is not None:  # the unmodified reference binary is built on this box: it is the baseline, the port is kept beside it
             out["cpu_baseline"] = {"value": rb["mpaths_s"], "unit": "Mpaths/s", "cores": threads, "kind": "reference",
                                    "sample": "the workload at %d spp (%d paths), unmodified reference binary "
-                                             "(oracle/_ref/refprobe, scalar_mono, TBB %d threads), %.1f s of "
-                                             "Integrator::render" % (rb["spp"], rb["paths"], threads, rb["seconds"]),
+                                             "(refprobe, scalar_mono, TBB %d threads, block_size %d = 128 image blocks), "
+                                             "%.1f s of Integrator::render" % (rb["spp"], rb["paths"], threads,
+                                                                                rb["block_size"], rb["seconds"]),
+                                   "build": rb["build"], "per_thread_mpaths_s": rb["mpaths_s"] / threads,
                                    "port_mpaths_s": cb["mpaths_s"], "port_segments_per_s": cb["segments_s"],
                                    "port_one_thread_mpaths_s": cb["pilot_mpaths_s_1thread"]}
+        out["cpu_baseline"].update(host_info())
         print(json.dumps(out))
     ds.close()
     if world > 1:
@@ -370,8 +502,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--profile", action="store_true", help="kernel-only run for ncu: no e2e leg, no CPU baseline")
     ap.add_argument("--spp", type=int, default=16384, help="samples per pixel per GPU (BASELINE: 2^14)")
-    ap.add_argument("--math", default="exact", choices=["exact", "fast"],
-                    help="fp32 mode of the kernels: exact (bit-exact against the oracle) or fast (tolerance mode)")
+    ap.add_argument("--math", default="fast", choices=["exact", "fast"],
+                    help="fp32 mode of the kernels: fast (the product mode for scalar_mono renders: tolerance mode, gated "
+                         "against the reference's films) or exact (bit-exact against the oracle; timed beside it at N=1)")
     args = ap.parse_args()
     # ONE JSON line on stdout: native libraries that write to file descriptor 1 themselves (NCCL prints its version
     # banner there at N>1) are sent to stderr; Python's own stdout keeps the real one

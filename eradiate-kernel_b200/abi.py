@@ -129,6 +129,7 @@ class Counters(C.Structure):
         ("n_paths", c_u64), ("n_rng_draws", c_u64), ("n_medium_steps", c_u64), ("n_null", c_u64),
         ("n_real", c_u64), ("n_intersect", c_u64), ("n_surface", c_u64), ("n_invalid_samples", c_u64),
         ("gpu_ms", c_d), ("n_launches", c_u32), ("stopped_early", c_u32),
+        ("n_bvh_nodes", c_u64), ("n_bvh_tris", c_u64),
     ]
 
 

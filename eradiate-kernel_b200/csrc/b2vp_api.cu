@@ -1087,6 +1087,7 @@ void fill_totals(B2vpCounters &t, const unsigned long long *tot, float ms, uint3
     t.n_paths = tot[TOT_PATHS]; t.n_rng_draws = tot[TOT_DRAWS]; t.n_medium_steps = tot[TOT_STEPS];
     t.n_null = tot[TOT_NULL]; t.n_real = tot[TOT_REAL]; t.n_intersect = tot[TOT_ISECT];
     t.n_surface = tot[TOT_SURF]; t.n_invalid_samples = tot[TOT_INVALID];
+    t.n_bvh_nodes = tot[TOT_BVH_NODES]; t.n_bvh_tris = tot[TOT_BVH_TRIS];
     t.gpu_ms = ms;
     t.n_launches = launches;
 }
@@ -1349,6 +1350,7 @@ template <typename F> int render_multi(b2vp_scene *s, const B2vpRenderArgs *a, v
             t.n_paths += tot[i].n_paths; t.n_rng_draws += tot[i].n_rng_draws; t.n_medium_steps += tot[i].n_medium_steps;
             t.n_null += tot[i].n_null; t.n_real += tot[i].n_real; t.n_intersect += tot[i].n_intersect;
             t.n_surface += tot[i].n_surface; t.n_invalid_samples += tot[i].n_invalid_samples;
+            t.n_bvh_nodes += tot[i].n_bvh_nodes; t.n_bvh_tris += tot[i].n_bvh_tris;
             t.gpu_ms = std::max(t.gpu_ms, tot[i].gpu_ms);     /* the devices run side by side */
             t.n_launches += tot[i].n_launches;
             t.stopped_early = std::max(t.stopped_early, tot[i].stopped_early);

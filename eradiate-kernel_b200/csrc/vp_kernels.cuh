@@ -15,7 +15,7 @@
 namespace VP_NS {
 
 enum { SEED_SCALAR_BLOCKS = 0, SEED_WAVEFRONT = 1, SEED_EXPLICIT = 2 };
-enum { TOT_PATHS = 0, TOT_DRAWS, TOT_STEPS, TOT_NULL, TOT_REAL, TOT_ISECT, TOT_SURF, TOT_INVALID, TOT_N };
+enum { TOT_PATHS = 0, TOT_DRAWS, TOT_STEPS, TOT_NULL, TOT_REAL, TOT_ISECT, TOT_SURF, TOT_INVALID, TOT_BVH_NODES, TOT_BVH_TRIS, TOT_N };
 
 template <typename F> struct RenderOut {
     F *film;                        /* crop_w * crop_h * 5, XYZAW interleaved */

@@ -163,11 +163,11 @@ VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth
    (ncu: what was left of the long_scoreboard stalls after the BVH moved to shared memory). */
 template <typename F, uint32_t FEAT>
 VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> &c, const Ray<F> &ir, bool isect_main,
-                            bool start_dl, uint32_t &fl, int &state) {
+                            bool start_dl, uint32_t &fl, int &state, BvhWork &work) {
     SurfaceHit<F> h;
     PathCounters cnt;
     cnt.n_intersect = 0;
-    ray_intersect_impl<F, FEAT, false>(sv, ir, h, cnt);
+    ray_intersect_impl<F, FEAT, false>(sv, ir, h, cnt, (FEAT & FT_ANY_MESH) ? &work : nullptr);
     s.c_isect += 1;
     s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
     if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here: keep what
@@ -814,7 +814,12 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
         /* ---------------- the one place where rays are intersected ---------------- */
         if (phase != PH_STEP) {
-            if (has && do_isect) intersect_new_ray<F, FEAT>(sv, s, c, ir, isect_main, start_dl, fl, state);
+            if (has && do_isect) {
+                BvhWork work;
+                work.nodes = 0; work.tris = 0;
+                intersect_new_ray<F, FEAT>(sv, s, c, ir, isect_main, start_dl, fl, state, work);
+                tot[TOT_BVH_NODES] += work.nodes; tot[TOT_BVH_TRIS] += work.tris;
+            }
             if (phase == PH_MARCH && has && state == Q_MARCH_END) {
                 /* a march is over: hand the result back and restore the main path's context */
                 const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;

@@ -192,7 +192,8 @@ template <typename F> VP_D void initialize_sh_frame(SurfaceHit<F> &si, V3<F> dp_
    until it actually scatters on the surface); surface_frame() below completes the interaction later from
    (shape, prim, bu, bv). */
 template <typename F, uint32_t FEAT = FT_ALL, bool SHADING = true>
-VP_D void ray_intersect_impl(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si, PathCounters &cnt) {
+VP_D void ray_intersect_impl(const SceneView<F> &sv, const Ray<F> &ray_in, SurfaceHit<F> &si, PathCounters &cnt,
+                             BvhWork *work = nullptr) {
     const DScene<F> &g = *sv.g;
     cnt.n_intersect++;
     si.t = inf_<F>();
@@ -265,6 +266,7 @@ VP_D void ray_intersect_impl(const SceneView<F> &sv, const Ray<F> &ray_in, Surfa
             const uint32_t count = cur >> 29, first = cur & 0x1fffffffu;
             if (count == 0) {
                 const float4 a0 = bm.node(first, 0), b0 = bm.node(first, 1), a1 = bm.node(first, 2), b1 = bm.node(first, 3);
+                if (work) work->nodes += 2;
                 const float cur_max = inflate_max((float) ray.maxt);
                 float t0, t1;
                 const bool h0 = slab(a0, b0, cur_max, t0), h1 = slab(a1, b1, cur_max, t1);
@@ -284,6 +286,7 @@ VP_D void ray_intersect_impl(const SceneView<F> &sv, const Ray<F> &ray_in, Surfa
                     V3<F> p0, p1, p2;
                     BvhPrim pr;
                     load_bvh_tri(bm, first + k, p0, p1, p2, pr);
+                    if (work) work->tris += 1;
                     F u, v;
                     F t = triangle_intersect(p0, p1, p2, ray, u, v);
                     if (t != inf_<F>()) {

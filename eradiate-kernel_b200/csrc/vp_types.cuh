@@ -340,5 +340,7 @@ VP_D uint64_t stream_index(const DStreams &sp, uint64_t k) {
 }
 
 struct PathCounters { uint32_t draws, medium_steps, n_null, n_real, n_intersect, n_surface; };
+/* BVH work of one ray_intersect call (launch totals only: the memory roofline of the mesh configuration) */
+struct BvhWork { uint32_t nodes, tris; };
 
 } // namespace VP_NS

@@ -303,6 +303,9 @@ typedef struct B2vpCounters {
     double gpu_ms;              /* CUDA-event time of the render kernels       */
     uint32_t n_launches;        /* kernels launched by this call               */
     uint32_t stopped_early;     /* 1: stopped by timeout_s, 2: by b2vp_cancel; n_paths < requested */
+    /* BVH work of the launch (queue kernel): nodes whose box was tested (32 B each) and leaf triangles tested (48 B
+       each) -- the algorithmic bytes of the mesh configuration's memory roofline           */
+    uint64_t n_bvh_nodes, n_bvh_tris;
 } B2vpCounters;
 
 typedef struct B2vpRenderArgs {

@@ -16,11 +16,15 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(HERE, "_ref")
 PROBE = os.path.join(REF_DIR, "refprobe")
+# the timing build (Makefile.ref `release`): the reference's Release flags; never used for parity
+RELEASE_PROBE = os.path.join(REF_DIR, "release", "refprobe")
+RELEASE_FLAGS = "-O3 -march=x86-64-v3 -ffp-contract=fast -fno-math-errno (grid3d.cpp at -O1)"
+PARITY_FLAGS = "-O3 -march=x86-64-v3 -ffp-contract=off (grid3d.cpp at -O1)"
 REFERENCE_SRC = "/root/reference"
 
 
-def available():
-    return os.path.exists(PROBE)
+def available(build="parity"):
+    return os.path.exists(RELEASE_PROBE if build == "release" else PROBE)
 
 
 def build():
@@ -28,6 +32,7 @@ def build():
     if not os.path.isdir(REFERENCE_SRC):
         return False
     subprocess.check_call(["make", "-s", "-f", "Makefile.ref", "-C", HERE, "-j", str(os.cpu_count() or 4)])
+    subprocess.check_call(["make", "-s", "-f", "Makefile.ref", "-C", HERE, "-j", str(os.cpu_count() or 4), "release"])
     return True
 
 
@@ -324,12 +329,13 @@ def with_plugin(scene, seeding="scalar"):
 
 
 def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None, exact_math=False,
-           describe_oracle=False):
+           describe_oracle=False, build="parity"):
     """Runs the reference binary on `scene`.  Returns (film[h, w, channels], seconds of the last Integrator::render).
     exact_math: put oracle_math.h's logf / expf / sincosf / cbrtf in front of glibc (ref_math_preload.cpp).
     describe_oracle (scenes from with_plugin only): do not render on a GPU; run the plugin's describe() and render
     its descriptor with the CPU oracle (refprobe --describe-oracle)."""
-    if not available():
+    probe = RELEASE_PROBE if build == "release" else PROBE
+    if not available(build):
         raise RuntimeError("oracle/_ref/refprobe is not built (run make -f oracle/Makefile.ref where /root/reference exists)")
     tmp = None
     if keep_dir is None:
@@ -341,7 +347,7 @@ def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, k
         env = dict(os.environ)
         if exact_math:
             env["LD_PRELOAD"] = os.path.join(REF_DIR, "libb2vp_refmath.so")
-        cmd = [PROBE, variant, xml, out, "-t", str(threads), "-r", str(repeats)]
+        cmd = [probe, variant, xml, out, "-t", str(threads), "-r", str(repeats)]
         if describe_oracle:
             cmd += ["--describe-oracle", ORACLE_LIB]
         p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
