@@ -958,7 +958,7 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
     out.film_smem_offset = align128(out.grid_smem_offset + ds.g.grid_smem_bytes);
     out.film_in_smem = film_bytes <= FILM_SMEM_MAX ? 1u : 0u;
     size_t smem = out.film_smem_offset + (out.film_in_smem ? film_bytes : 0);
-    const bool fast = a->math_mode == B2VP_MATH_FAST;
+    bool fast = a->math_mode == B2VP_MATH_FAST;
     if (a->math_mode != B2VP_MATH_EXACT && !fast) return fail(B2VP_ERR_INVALID, "unknown math_mode %d", a->math_mode);
     if (fast && sizeof(F) != 4) return fail(B2VP_ERR_INVALID, "B2VP_MATH_FAST is an fp32 mode (precision F32)");
     /* Kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues (vp_queue.cuh).
@@ -970,7 +970,11 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
     int kernel = a->kernel;
     if (kernel < B2VP_KERNEL_AUTO || kernel > B2VP_KERNEL_STREAM) return fail(B2VP_ERR_INVALID, "unknown kernel %d", kernel);
     if (needs_stream) {
-        if (fast) return fail(B2VP_ERR_UNSUPPORTED, "B2VP_MATH_FAST: volpathmis / environment emitters run on the one-thread-per-stream kernel, which has no fast instance");
+        /* FAST is a tolerance, and the exact arithmetic meets it: with the kernel left to the library, such a scene is
+           simply rendered exactly (the one-time note below says by which kernel) */
+        if (fast && kernel != B2VP_KERNEL_AUTO)
+            return fail(B2VP_ERR_UNSUPPORTED, "B2VP_MATH_FAST: volpathmis / environment emitters run on the one-thread-per-stream kernel, which has no fast instance");
+        fast = false;
         if (kernel == B2VP_KERNEL_AUTO && !s->warned_stream_kernel) {
             s->warned_stream_kernel = true;
             std::fprintf(stderr, "[b2vp] warning: %s is rendered by the one-thread-per-stream kernel (about 14x slower than the queue kernel)\n",

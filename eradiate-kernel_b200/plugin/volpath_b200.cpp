@@ -109,6 +109,26 @@ struct B200SceneTables {
     std::vector<double> sensor_xf;
     std::vector<std::vector<double>> phase_values;   /* tabphase tables, parallel to `phases` */
     std::map<const void *, int> bsdf_ids, medium_ids, shape_ids;
+    /* Fingerprint of everything the device scene is built from.  Taken BEFORE finish() fills the pointer fields, so
+       it depends on content only; render() keeps the resident device scene while it is unchanged. */
+    uint64_t fingerprint() const {
+        uint64_t h = 0xcbf29ce484222325ull;
+        auto mix = [&h](const void *p, size_t n) {
+            const unsigned char *b = (const unsigned char *) p;
+            size_t i = 0;
+            for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h = (h ^ w) * 0x100000001b3ull; h ^= h >> 29; }
+            for (; i < n; ++i) h = (h ^ b[i]) * 0x100000001b3ull;
+            h = (h ^ (uint64_t) n) * 0x100000001b3ull;
+        };
+        auto vec = [&mix](const auto &v) { mix(v.data(), v.size() * sizeof(v[0])); };
+        mix(&desc, sizeof(desc));
+        vec(shapes); vec(bsdfs); vec(media); vec(volumes); vec(phases); vec(emitters);
+        vec(vpos); vec(vnrm); vec(vuv); vec(faces); vec(sensor_xf);
+        for (const auto &g : grids) vec(g);
+        for (const auto &t : phase_values) vec(t);
+        return h;
+    }
+    uint64_t hash = 0;
     void finish() {
         desc.abi_version = B2VP_ABI_VERSION; desc.struct_size = (uint32_t) sizeof(B2vpSceneDesc);
         desc.n_shapes = (uint32_t) shapes.size(); desc.shapes = shapes.data();
@@ -432,7 +452,7 @@ template <typename Float, typename Spectrum>
 class B200VolumetricPathIntegrator final : public MonteCarloIntegrator<Float, Spectrum> {
 public:
     MTS_IMPORT_BASE(MonteCarloIntegrator, m_max_depth, m_rr_depth, m_hide_emitters, m_stop, m_block_size,
-                    m_samples_per_pass, m_render_timer)
+                    m_samples_per_pass, m_render_timer, m_timeout)
     MTS_IMPORT_TYPES(Scene, Sensor, Film, ImageBlock, Sampler, Medium)
 
     B200VolumetricPathIntegrator(const Properties &props) : Base(props) {
@@ -452,6 +472,22 @@ public:
         std::string algorithm = props.string("algorithm", "volpath");
         if (algorithm == "volpathmis") m_mis = props.bool_("use_spectral_mis", true) ? 1 : 2;
         else if (algorithm != "volpath") Throw("volpath_b200: algorithm must be \"volpath\" or \"volpathmis\"");
+        /* math: "fast" (default in scalar_mono: the fp32 tolerance mode, B2VP_MATH_FAST) or "exact" (every fp32
+           operation in the oracle's order; the only mode in scalar_mono_double) */
+        std::string math = props.string("math", std::is_same_v<scalar_t<Float>, double> ? "exact" : "fast");
+        if (math == "fast") m_math = B2VP_MATH_FAST;
+        else if (math == "exact") m_math = B2VP_MATH_EXACT;
+        else Throw("volpath_b200: math must be \"fast\" or \"exact\"");
+        if (m_math == B2VP_MATH_FAST && (std::is_same_v<scalar_t<Float>, double> || m_mis))
+            m_math = B2VP_MATH_EXACT;   /* no fast instance in double precision / for volpathmis */
+        /* majorant_grid: 0 (default) = the reference's global majorant; see B2vpRenderArgs::majorant_grid */
+        m_majorant_grid = (uint32_t) props.int_("majorant_grid", 0);
+        /* n_devices: render on this many GPUs (device, then the others in ascending order), one NCCL film reduce */
+        int n_dev = props.int_("n_devices", 1);
+        if (n_dev < 1 || (n_dev > 1 && n_dev > b2vp_device_count())) Throw("volpath_b200: n_devices = %d, %d CUDA devices present", n_dev, b2vp_device_count());
+        m_devices.push_back(m_device);
+        for (int d = 0; (int) m_devices.size() < n_dev; ++d)
+            if (d != m_device) m_devices.push_back(d);
     }
     ~B200VolumetricPathIntegrator() { release(); }
 
@@ -460,8 +496,18 @@ public:
         m_stop = false;
         B200SceneTables tables;
         describe(scene, sensor, tables);
-        release();
-        check(b2vp_scene_create(&tables.desc, m_device, &m_scene));
+        {
+            /* The device scene (grids, BVH, tables in HBM) stays resident between render() calls while the flattened
+               scene is unchanged -- the object graph is re-read every time (cheap, host only), so any edit through
+               traverse() / parameters_changed, a new sensor or other integrator properties is seen without the
+               plugin having to be told. */
+            std::lock_guard<std::mutex> lock(m_mutex);
+            if (!m_scene || tables.hash != m_scene_hash) {
+                release_locked();
+                check(b2vp_scene_create(&tables.desc, m_device, &m_scene));
+                m_scene_hash = tables.hash;
+            }
+        }
 
         ref<Film> film = sensor->film();
         std::vector<std::string> channels = { "X", "Y", "Z", "A", "W" };   /* integrator.cpp:67-73 */
@@ -484,6 +530,10 @@ public:
         args.seed_mode = m_seed_mode;
         args.clear_film = 1;
         args.totals = &m_totals;
+        args.math_mode = m_math;
+        args.majorant_grid = m_majorant_grid;
+        args.timeout_s = (double) m_timeout;           /* integrator.h:143-146: <= 0 = none */
+        if (m_devices.size() > 1) { args.devices = m_devices.data(); args.n_devices = (uint32_t) m_devices.size(); }
         int rc = b2vp_render(m_scene, &args, block->data().data());   /* host XYZAW buffer, crop_size x 5 */
         if (rc == B2VP_ERR_CANCELLED) return false;
         check(rc);
@@ -495,7 +545,12 @@ public:
         return !m_stop;
     }
 
-    void cancel() override { m_stop = true; if (m_scene) b2vp_cancel(m_scene); }   /* integrator.h:51 */
+    /* integrator.h:44-51: may come from another thread while render() runs; m_scene is only replaced under the lock */
+    void cancel() override {
+        m_stop = true;
+        std::lock_guard<std::mutex> lock(m_mutex);
+        if (m_scene) b2vp_cancel(m_scene);
+    }
 
     /* the batch boundary is render(): a single-sample entry point does not exist on the GPU path */
     std::pair<Spectrum, Mask> sample(const Scene *, Sampler *, const RayDifferential3f &, const Medium *, Float *,
@@ -514,6 +569,7 @@ public:
         it.arg_order_ltr = 0;   /* GCC evaluates the sample arguments right to left (include/b2vp.h) */
         it.moment = m_moment ? 1u : 0u;
         it.mis = (uint32_t) m_mis;
+        tables.hash = tables.fingerprint();
         tables.finish();
     }
 
@@ -524,8 +580,14 @@ public:
     MTS_DECLARE_CLASS()
 private:
     static void check(int rc) { if (rc != B2VP_OK) Throw("volpath_b200: %s", b2vp_last_error()); }
-    void release() { if (m_scene) b2vp_scene_destroy(m_scene); m_scene = nullptr; }
+    void release_locked() { if (m_scene) b2vp_scene_destroy(m_scene); m_scene = nullptr; }
+    void release() { std::lock_guard<std::mutex> lock(m_mutex); release_locked(); }
+    std::mutex m_mutex;
     b2vp_scene_t *m_scene = nullptr;
+    uint64_t m_scene_hash = 0;
+    int m_math = B2VP_MATH_EXACT;
+    uint32_t m_majorant_grid = 0;
+    std::vector<int32_t> m_devices;
     B2vpCounters m_totals{};
     int m_device = 0;
     int m_seed_mode = B2VP_SEED_WAVEFRONT;

@@ -85,7 +85,7 @@ int run(Object *parsed, const char *out_path, int repeats, const char *oracle_pa
         Throw("No integrator specified for scene");
     if (oracle_path) {
         if (std::string(integrator->class_()->name()) != "B200VolumetricPathIntegrator")
-            Throw("--describe-oracle needs <integrator type=\"volpath_b200\">");
+            Throw("--describe-oracle needs <integrator type=\"volpath_b200\"> (or type=\"volpath\" with --plugin-root)");
         fs::path plug = util::library_path().parent_path() / "plugins" / "volpath_b200.so";
         void *h = dlopen(plug.native().c_str(), RTLD_LAZY | RTLD_LOCAL);   /* already loaded: same handle */
         void *orc = dlopen(oracle_path, RTLD_NOW | RTLD_LOCAL);
@@ -140,7 +140,7 @@ int main(int argc, char **argv) {
     try {
         std::string mode = argv[1];
         int threads = 1, repeats = 1;
-        const char *oracle_path = nullptr;
+        const char *oracle_path = nullptr, *plugin_root = nullptr;
         xml::ParameterList params;
         for (int i = 4; i < argc; ++i) {
             if (!strcmp(argv[i], "-t") && i + 1 < argc)
@@ -149,6 +149,8 @@ int main(int argc, char **argv) {
                 repeats = atoi(argv[++i]);
             else if (!strcmp(argv[i], "--describe-oracle") && i + 1 < argc)
                 oracle_path = argv[++i];
+            else if (!strcmp(argv[i], "--plugin-root") && i + 1 < argc)   /* a directory searched BEFORE the reference's own */
+                plugin_root = argv[++i];
             else if (!strncmp(argv[i], "-D", 2)) {
                 std::string kv = argv[i] + 2;
                 auto sep = kv.find('=');
@@ -161,6 +163,8 @@ int main(int argc, char **argv) {
         ref<Thread> thread = Thread::thread();
         ref<FileResolver> fr = thread->file_resolver();
         fs::path base = util::library_path().parent_path();   // plugins/ lives next to libmitsuba-core.so
+        if (plugin_root)   /* <root>/plugins/volpath.so shadows the stock volpath.so (plugin.cpp:94-105 resolves in order) */
+            fr->prepend(fs::path(plugin_root));
         if (!fr->contains(base))
             fr->append(base);
         fs::path scene_dir = fs::path(argv[2]).parent_path();

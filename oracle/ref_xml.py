@@ -264,6 +264,13 @@ class _Writer:
             out.append('<string name="algorithm" value="%s"/>' % v["algorithm"])
         if "seeding" in v:
             out.append('<string name="seeding" value="%s"/>' % v["seeding"])
+        if "math" in v:
+            out.append('<string name="math" value="%s"/>' % v["math"])
+        for key in ("majorant_grid", "n_devices", "device"):
+            if key in v:
+                out.append('<integer name="%s" value="%d"/>' % (key, v[key]))
+        if "timeout" in v:
+            out.append('<float name="timeout" value="%r"/>' % float(v["timeout"]))
         if "hide_emitters" in v:
             out.append('<boolean name="hide_emitters" value="%s"/>' % ("true" if v["hide_emitters"] else "false"))
         if "nested" in v:  # moment integrator: one nested integrator
@@ -313,23 +320,24 @@ PLUGIN = os.path.join(REF_DIR, "plugins", "volpath_b200.so")
 ORACLE_LIB = os.path.join(HERE, "libb2vp_oracle.so")
 
 
-def with_plugin(scene, seeding="scalar"):
+def with_plugin(scene, seeding="scalar", type_name="volpath_b200", **props):
     """The same scene with <integrator type="volpath_b200">: the product's plugin inside the reference binary.
     seeding="scalar" asks for the scalar variants' stream order (films comparable sample by sample with the
-    reference's CPU volpath), "wavefront" for the plugin's default."""
+    reference's CPU volpath), "wavefront" for the plugin's default.  type_name="volpath" + render(plugin_root=True):
+    the plugin under the reference's own name.  props: math, majorant_grid, n_devices, timeout."""
     d = dict(scene)
     for k, v in scene.items():
         if isinstance(v, dict) and v.get("type") in ("volpath", "volpathmis"):
-            d[k] = dict(v, type="volpath_b200", seeding=seeding, algorithm=v["type"])
+            d[k] = dict(v, type=type_name, seeding=seeding, algorithm=v["type"], **props)
         elif isinstance(v, dict) and v.get("type") == "moment":   # moment around a volpath -> the plugin's own `moment`
             inner = [c for c in v.values() if isinstance(c, dict)][0]
             outer = {kk: vv for kk, vv in v.items() if not isinstance(vv, dict) and kk != "type"}
-            d[k] = dict(inner, type="volpath_b200", seeding=seeding, algorithm=inner["type"], moment=True, **outer)
+            d[k] = dict(inner, type=type_name, seeding=seeding, algorithm=inner["type"], moment=True, **dict(outer, **props))
     return d
 
 
 def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None, exact_math=False,
-           describe_oracle=False, build="parity"):
+           describe_oracle=False, build="parity", plugin_root=False, record=False):
     """Runs the reference binary on `scene`.  Returns (film[h, w, channels], seconds of the last Integrator::render).
     exact_math: put oracle_math.h's logf / expf / sincosf / cbrtf in front of glibc (ref_math_preload.cpp).
     describe_oracle (scenes from with_plugin only): do not render on a GPU; run the plugin's describe() and render
@@ -345,11 +353,16 @@ def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, k
         xml = to_xml(scene, keep_dir, write_vol)
         out = os.path.join(keep_dir, "film.bin")
         env = dict(os.environ)
+        rec_path = os.path.join(keep_dir, "records.bin")
+        if record:   # the scene's sampler must be {"type": "recording"} (oracle/ref_recording_sampler.cpp)
+            env["B2VP_RECORD_PATH"] = rec_path
         if exact_math:
             env["LD_PRELOAD"] = os.path.join(REF_DIR, "libb2vp_refmath.so")
         cmd = [probe, variant, xml, out, "-t", str(threads), "-r", str(repeats)]
         if describe_oracle:
             cmd += ["--describe-oracle", ORACLE_LIB]
+        if plugin_root:   # <integrator type="volpath"> resolves to the product's plugin (oracle/_ref/b200/plugins/volpath.so)
+            cmd += ["--plugin-root", os.path.join(REF_DIR, "b200")]
         p = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
         if p.returncode != 0:
             raise RuntimeError("refprobe failed (%d): %s" % (p.returncode, p.stderr[-2000:]))
@@ -358,6 +371,10 @@ def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, k
         w, h, c, is_double = struct.unpack_from("<4i", raw, 0)
         seconds, = struct.unpack_from("<d", raw, 16)
         film = np.frombuffer(raw, dtype="<f8" if is_double else "<f4", offset=24).reshape(h, w, c).copy()
+        if record:
+            # (seed value, sample index within the seed, PCG32 state after the sample, draws since the seed) per advance()
+            rec = np.fromfile(rec_path, dtype="<u8").reshape(-1, 4)
+            return film, seconds, rec
         return film, seconds
     finally:
         if tmp is not None:

@@ -99,12 +99,9 @@ def test_fast_matches_reference_films(pkg, name):
     """The films of the unmodified reference binary, same checker and tolerances as for the exact kernel."""
     d, variant = make_ref_golden.scene_dict(name)
     sc = pkg.load_dict(d, variant)
-    try:
-        got = pkg.render(sc, device=0, seed_mode=pkg.abi.SEED_SCALAR_BLOCKS, math="fast")
-    except pkg.B2vpError as e:
-        if e.code == pkg.abi.ERR_UNSUPPORTED:
-            pytest.skip("rendered by the one-thread-per-stream kernel (no fast instance)")
-        raise
+    # (volpathmis / environment-emitter scenes have no fast instance: with the kernel left to the library they are
+    # rendered exactly, which meets the tolerance trivially)
+    got = pkg.render(sc, device=0, seed_mode=pkg.abi.SEED_SCALAR_BLOCKS, math="fast")
     frac = trp.check_against_reference(name, got.film, trp.REF[name], variant)
     print("\nFAST vs reference film %-28s %.4f of the pixels within tolerance" % (name, frac))
 

@@ -68,6 +68,64 @@ def test_plugin_rejects_content_outside_the_scope(pkg):
 def test_reference_binary_renders_on_the_gpu_through_the_plugin(pkg, name):
     ref_xml = ref_xml_or_skip()
     d, variant = make_ref_golden.scene_dict(name)
-    film, seconds = ref_xml.render(ref_xml.with_plugin(d), variant, write_vol=pkg.scene.write_vol)
+    film, seconds = ref_xml.render(ref_xml.with_plugin(d, math="exact"), variant, write_vol=pkg.scene.write_vol)
     check_against_reference(name, film, REF[name], variant)
     assert seconds > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", [n for n in PLUGIN_CASES if make_ref_golden.scene_dict(n)[1] == "scalar_mono"])
+def test_plugin_default_mode_against_reference_films(pkg, name):
+    """The plugin's default in scalar_mono is the fp32 tolerance mode (math = "fast"): same films, same checker."""
+    ref_xml = ref_xml_or_skip()
+    d, variant = make_ref_golden.scene_dict(name)
+    film, _ = ref_xml.render(ref_xml.with_plugin(d), variant, write_vol=pkg.scene.write_vol)
+    check_against_reference(name, film, REF[name], variant)
+
+
+@pytest.mark.gpu
+def test_drop_in_by_name_and_resident_scene(pkg):
+    """<integrator type="volpath"> resolves to the product when its plugin directory is ahead of the reference's
+    (plugin.cpp:94-105): the scene carries a property only the product knows (`seeding`; the stock volpath rejects
+    unknown properties), and without the directory the very same scene fails.  Three Integrator::render calls in one
+    process reuse the resident device scene and give the film of one."""
+    ref_xml = ref_xml_or_skip()
+    if not os.path.exists(os.path.join(ref_xml.REF_DIR, "b200", "plugins", "volpath.so")):
+        pytest.skip("oracle/_ref/b200/plugins/volpath.so is not built")
+    name = "c2_paths"
+    d, variant = make_ref_golden.scene_dict(name)
+    scene = ref_xml.with_plugin(d, type_name="volpath", math="exact")
+    film, _ = ref_xml.render(scene, variant, write_vol=pkg.scene.write_vol, plugin_root=True)
+    check_against_reference(name, film, REF[name], variant)
+    with pytest.raises(RuntimeError):
+        ref_xml.render(scene, variant, write_vol=pkg.scene.write_vol)          # the stock volpath: unknown property
+    again, seconds = ref_xml.render(scene, variant, write_vol=pkg.scene.write_vol, plugin_root=True, repeats=3)
+    assert np.array_equal(again, film)
+    # a stock scene (no extra property at all) renders too, with the plugin's defaults (wavefront seeding, fast math):
+    # an independent estimate of the same image
+    import scenes
+    d2 = ref_xml.round_f32(scenes.c2(spp=512, width=64))
+    stock, _ = ref_xml.render(d2, "scalar_mono", write_vol=pkg.scene.write_vol, plugin_root=True)
+    cpu, _ = ref_xml.render(d2, "scalar_mono", threads=8, write_vol=pkg.scene.write_vol)      # the reference's own volpath
+    assert np.array_equal(stock[..., 4], cpu[..., 4])
+    m_stock, m_cpu = stock[..., 1].sum() / stock[..., 4].sum(), cpu[..., 1].sum() / cpu[..., 4].sum()
+    assert abs(m_stock - m_cpu) < 0.03 * m_cpu, (m_stock, m_cpu)
+
+
+@pytest.mark.gpu
+def test_plugin_timeout_and_modes(pkg):
+    """The integrator's `timeout` property and the majorant-grid mode through the reference's own XML."""
+    import scenes
+    ref_xml = ref_xml_or_skip()
+    d = ref_xml.round_f32(scenes.c2(spp=1 << 18, width=256))
+    # two Integrator::render calls; the time is that of the second (CUDA is up, the scene is resident on the device)
+    film, seconds = ref_xml.render(ref_xml.with_plugin(d, seeding="wavefront", timeout=0.05), "scalar_mono",
+                                   write_vol=pkg.scene.write_vol, repeats=2)
+    total = 256 * (1 << 18)
+    assert 0 < film[..., 4].sum() < total and seconds < 0.4
+    d = ref_xml.round_f32(scenes.c2(spp=256, width=64))
+    a, _ = ref_xml.render(ref_xml.with_plugin(d, seeding="wavefront"), "scalar_mono", write_vol=pkg.scene.write_vol)
+    b, _ = ref_xml.render(ref_xml.with_plugin(d, seeding="wavefront", majorant_grid=1), "scalar_mono", write_vol=pkg.scene.write_vol)
+    assert np.array_equal(a[..., 4], b[..., 4])
+    ma, mb = a[..., 1].sum() / a[..., 4].sum(), b[..., 1].sum() / b[..., 4].sum()
+    assert abs(ma - mb) < 0.02 * ma
