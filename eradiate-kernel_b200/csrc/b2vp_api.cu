@@ -180,7 +180,6 @@ struct b2vp_scene {
     std::vector<BvhPrim> bvh_prims;
     BvhStats bvh_stats;
     std::string last_kernel;                         /* kernel instance launched by the last render (b2vp_scene_info) */
-    bool warned_stream_kernel = false;
     std::vector<std::unique_ptr<DeviceCtx>> contexts;
     std::mutex mutex;                                /* guards contexts / last_kernel between the threads of a multi-device render */
     std::atomic<int> cancelled{ 0 };
@@ -939,12 +938,15 @@ struct LaunchPlan {
     std::string name;
 };
 
-template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, const char **preset);
-template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, const char **preset) {
+template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset);
+template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset) {
+    if (env) return fast ? vp_launch::queue_f32_fast_env(mis, preset) : vp_launch::queue_f32_env(mis, preset);
+    if (mis) return fast ? vp_launch::queue_f32_fast_mis(ft, preset) : vp_launch::queue_f32_mis(ft, preset);
     return fast ? vp_launch::queue_f32_fast(ft, preset) : vp_launch::queue_f32(ft, maxt, preset);
 }
-template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, const char **preset) {
-    return vp_launch::queue_f64(ft, maxt, preset);
+template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, bool mis, bool env, const char **preset) {
+    if (env) return vp_launch::queue_f64_env(mis, preset);
+    return mis ? vp_launch::queue_f64_mis(ft, preset) : vp_launch::queue_f64(ft, maxt, preset);
 }
 template <typename F> const void *stream_entry() { return sizeof(F) == 4 ? vp_launch::stream_f32() : vp_launch::stream_f64(); }
 template <typename F> const void *lanes_entry() { return sizeof(F) == 4 ? vp_launch::lanes_f32() : vp_launch::lanes_f64(); }
@@ -961,25 +963,22 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
     bool fast = a->math_mode == B2VP_MATH_FAST;
     if (a->math_mode != B2VP_MATH_EXACT && !fast) return fail(B2VP_ERR_INVALID, "unknown math_mode %d", a->math_mode);
     if (fast && sizeof(F) != 4) return fail(B2VP_ERR_INVALID, "B2VP_MATH_FAST is an fp32 mode (precision F32)");
-    /* Kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues (vp_queue.cuh).
-       volpathmis and scenes with an environment emitter (constant.cpp: non-delta emitter sampling,
-       light on escape) are not scheduled by the queue kernel: they run on the one-thread-per-stream kernel, an
-       order of magnitude slower -- said once per scene on stderr and in B2vpSceneInfo::last_kernel. */
-    bool needs_stream = s->desc.integrator.mis != 0;
-    for (const B2vpEmitter &e : s->emitters) needs_stream = needs_stream || e.type == B2VP_EMITTER_CONSTANT;
+    /* Kernel selection.  Product: the CTA-resident wavefront with shared-memory phase queues (vp_queue.cuh), for
+       volpath and -- as other bodies of the same phases -- volpathmis (FT_MIS) and scenes with an
+       environment emitter (FT_ENV; constant.cpp: non-delta emitter sampling, light on escape).  Those two exist as
+       512-thread instances only: when another kernel is asked for (tests, comparisons) they run on the
+       one-thread-per-stream kernel, an order of magnitude slower; B2vpSceneInfo::last_kernel says which. */
+    const bool mis = s->desc.integrator.mis != 0;
+    bool env = false;
+    for (const B2vpEmitter &e : s->emitters) env = env || e.type == B2VP_EMITTER_CONSTANT;
     int kernel = a->kernel;
     if (kernel < B2VP_KERNEL_AUTO || kernel > B2VP_KERNEL_STREAM) return fail(B2VP_ERR_INVALID, "unknown kernel %d", kernel);
+    const bool needs_stream = (mis || env) && kernel != B2VP_KERNEL_AUTO && kernel != B2VP_KERNEL_QUEUE_GENERIC;
+    if ((mis || env) && a->majorant_grid)
+        return fail(B2VP_ERR_UNSUPPORTED, "majorant_grid is a mode of volpath without an environment emitter, not of volpathmis");
     if (needs_stream) {
-        /* FAST is a tolerance, and the exact arithmetic meets it: with the kernel left to the library, such a scene is
-           simply rendered exactly (the one-time note below says by which kernel) */
-        if (fast && kernel != B2VP_KERNEL_AUTO)
-            return fail(B2VP_ERR_UNSUPPORTED, "B2VP_MATH_FAST: volpathmis / environment emitters run on the one-thread-per-stream kernel, which has no fast instance");
-        fast = false;
-        if (kernel == B2VP_KERNEL_AUTO && !s->warned_stream_kernel) {
-            s->warned_stream_kernel = true;
-            std::fprintf(stderr, "[b2vp] warning: %s is rendered by the one-thread-per-stream kernel (about 14x slower than the queue kernel)\n",
-                         s->desc.integrator.mis ? "volpathmis" : "a scene with an environment emitter");
-        }
+        if (fast)
+            return fail(B2VP_ERR_UNSUPPORTED, "B2VP_MATH_FAST: volpathmis / environment-emitter scenes have fast instances of the 512-thread queue kernel only");
         kernel = B2VP_KERNEL_STREAM;
     }
     if (fast && (kernel == B2VP_KERNEL_LANES || kernel == B2VP_KERNEL_STREAM || kernel == B2VP_KERNEL_QUEUE_256))
@@ -1007,7 +1006,7 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
     if (pl.queue_kernel) {
         pl.threads = kernel == B2VP_KERNEL_QUEUE_256 ? 256 : 512;
         pl.kern = queue_entry<F>(launch_features | (kernel == B2VP_KERNEL_QUEUE_GENERIC ? vp_launch::FORCE_GENERIC : 0u),
-                                 pl.threads, fast, &preset);
+                                 pl.threads, fast, mis, env, &preset);
         pl.name = std::string("queue/") + preset + (pl.threads == 512 ? "" : "/256") + (fast ? " fast" : "");
     } else if (kernel == B2VP_KERNEL_LANES) {
         pl.kern = lanes_entry<F>(); pl.threads = 256; pl.name = "lanes";

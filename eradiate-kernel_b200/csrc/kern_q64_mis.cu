@@ -1,0 +1,10 @@
+/* kern_q64_mis.cu -- the queue kernel running volpathmis (FT_MIS), fp64 instances. */
+#include "vp_presets.cuh"
+#include "vp_launch.h"
+
+namespace vp_launch {
+const void *queue_f64_mis(uint32_t features, const char **preset) {
+    const bool generic = (features & 0x80000000u) != 0;
+    return vp::pick_queue_kernel_mis<double>(features & ~0x80000000u, generic, preset);
+}
+} // namespace vp_launch

@@ -21,6 +21,14 @@ const void *queue_f64(uint32_t features, int max_threads, const char **preset);
 /* Tolerance-mode fp32 instances (kern_q32_fast.cu): same kernel text, PCG32 exact, floating point with FMA
    contraction and hardware approximations.  512 threads only. */
 const void *queue_f32_fast(uint32_t features, const char **preset);
+/* The same kernel running volpathmis' state machine (FT_MIS; kern_q*_mis.cu).  512 threads only. */
+const void *queue_f32_mis(uint32_t features, const char **preset);
+const void *queue_f64_mis(uint32_t features, const char **preset);
+const void *queue_f32_fast_mis(uint32_t features, const char **preset);
+/* ... and for scenes with an environment emitter (FT_ENV; kern_q*_env.cu): all-features instances, 512 threads */
+const void *queue_f32_env(bool mis, const char **preset);
+const void *queue_f64_env(bool mis, const char **preset);
+const void *queue_f32_fast_env(bool mis, const char **preset);
 /* The one-thread-per-stream twin (vp_kernels.cuh) and the register-resident warp-voting wavefront (vp_wavefront.cuh) */
 const void *stream_f32();
 const void *stream_f64();

@@ -34,4 +34,21 @@ template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool 
     return q_entry<F, MAXT, FT_ALL>();
 }
 
+/* volpathmis instances (FT_MIS): 512 threads only, in their own translation units (kern_q*_mis.cu) */
+template <typename F> const void *pick_queue_kernel_mis(uint32_t ft, bool force_generic, const char **name) {
+    if (force_generic) ft = FT_ALL;
+    if ((ft & ~PRE_HOMOG) == 0) { *name = "volpathmis, homogeneous"; return q_entry<F, 512, PRE_HOMOG | FT_MIS>(); }
+    if ((ft & ~PRE_HET) == 0) { *name = "volpathmis, heterogeneous"; return q_entry<F, 512, PRE_HET | FT_MIS>(); }
+    if ((ft & ~PRE_HET_ALB) == 0) { *name = "volpathmis, heterogeneous+albedo grid"; return q_entry<F, 512, PRE_HET_ALB | FT_MIS>(); }
+    *name = "volpathmis, generic";
+    return q_entry<F, 512, FT_ALL | FT_MIS>();
+}
+
+/* scenes with an environment emitter (FT_ENV): the all-features instance of either integrator */
+template <typename F> const void *pick_queue_kernel_env(bool mis, const char **name) {
+    if (mis) { *name = "volpathmis, environment, generic"; return q_entry<F, 512, FT_ALL | FT_ENV | FT_MIS>(); }
+    *name = "environment, generic";
+    return q_entry<F, 512, FT_ALL | FT_ENV>();
+}
+
 } // namespace VP_NS

@@ -61,7 +61,9 @@ enum : uint32_t {
     QF_STATE = 0xfu, QF_MODE_SHIFT = 4, QF_MODE = 0x3u << 4, QF_CONT_SHIFT = 6, QF_CONT = 0x7u << 6,
     QF_TOP_DONE = 1u << 10,  /* the part of this loop iteration that precedes the step (roulette / remaining
                                 distance, intersection) was done where the ray was made */
-    QF_VALID_RAY = 1u << 11, QF_HAVE_STREAM = 1u << 13,
+    QF_VALID_RAY = 1u << 11,
+    QF_SPEC_CHAIN = 1u << 12, /* `specular_chain` (volpath.cpp:53, volpathmis.cpp:104): kept only with an environment */
+    QF_HAVE_STREAM = 1u << 13,
     QF_ACC_USED = 1u << 14
 };
 
@@ -92,14 +94,19 @@ template <typename F> struct PathSlot {
     MarchCtx<F> cur;
     F eta;
     uint32_t depth;
-    F total_dist, ds_dist, remaining;
+    /* emitter march: distance covered, distance to the emitter.  (The remaining distance of the current march
+       iteration is not stored: whoever makes or continues a march ray stores it as the ray's maxt.) */
+    F total_dist, ds_dist;
+    F w2;   /* volpathmis: the second weight of the current context -- p_over_f_uni of an emitter march (volpathmis.cpp:330-444) */
 };
 template <typename F> struct PathCold {
     unsigned long long k;
     uint32_t j;
     uint32_t c_real, c_surf;
     MarchCtx<F> saved;                    /* the main path's context during a march */
-    uint32_t prim; F bu, bv;              /* mesh face and barycentrics of the main path's hit */
+    uint32_t prim; F bu, bv;              /* mesh face and barycentrics of the main path's hit (dead once the surface
+                                             frame is complete; volpathmis keeps the caller's pdf of an emitter march in
+                                             `bu` and its phase / BSDF value in `nee_w` while the march runs) */
     F wi[3], sh_s[3], sh_t[3], sh_n[3];   /* its shading frame, completed at the surface event  */
     F result;
     int medium_next;
@@ -156,6 +163,62 @@ VP_D bool loop_top_rr(Pcg32 &rng, F &w, F eta, uint32_t depth, uint32_t rr_depth
     return active && depth < max_depth;
 }
 
+/* ---- volpathmis (src/integrators/volpathmis.cpp), mono: the 1 x 1 weight "matrices" are scalars.  A path carries
+   p_over_f (pdf over contribution) where volpath carries a throughput; every event multiplies a ratio into it. */
+template <typename F> VP_D void mis_update(F &p_over_f, F p, F f) {   /* update_weights, volpathmis.cpp:447-465 */
+    F ratio = p / f;
+    ratio = finite_(ratio) ? ratio : (F) 0;
+    ratio *= p_over_f;
+    p_over_f = (ratio != ratio) ? (F) 0 : ratio;
+}
+template <typename F> VP_D F mis_w1(F p_over_f) { return p_over_f == 0 ? (F) 0 : (F) 1 / p_over_f; }          /* :467-482 */
+template <typename F> VP_D F mis_w2(F a, F b) { F sum = a + b; return sum == 0 ? (F) 0 : (F) 1 / sum; }       /* :485-500 */
+/* Top of the main loop (volpathmis.cpp:122-133).  False: the path ends. */
+template <typename F>
+VP_D bool mis_loop_top(Pcg32 &rng, F &p_over_f, F eta, uint32_t depth, uint32_t rr_depth, uint32_t max_depth) {
+    const F q = min_(mis_w1(p_over_f) * sqr(eta), (F) 0.95f);
+    const bool perform_rr = depth > rr_depth;
+    const F rr_sample = rng.next(F(), true);
+    bool active = !(rr_sample >= q && perform_rr);
+    if (perform_rr) mis_update(p_over_f, q, (F) 1);
+    active = active && depth < max_depth;
+    return active && mis_w1(p_over_f) != 0;
+}
+
+/* Scene::sample_emitter_direction as the integrators call it: returns the sample and the emitter VALUE the caller
+   works with -- the importance weight for volpath (volpath.cpp:266-269), weight * pdf for volpathmis
+   (volpathmis.cpp:341-343); 0 when the pdf is 0. */
+template <typename F, uint32_t FEAT>
+VP_D DirSample<F> queue_sample_emitter(const SceneView<F> &sv, Pcg32 &rng, F &ev) {
+    const F sx = rng.next(F(), true), sy = rng.next(F(), true);
+    DirSample<F> ds = (FEAT & FT_ENV) ? sample_emitter_direction_env(sv, sx, sy, ev) : sample_emitter_direction(sv, sx, ev);
+    if (FEAT & FT_MIS) ev = ev * ds.pdf;
+    if (ds.pdf == 0) ev = 0;
+    return ds;
+}
+/* Scene::pdf_emitter_direction for the environment (scene.cpp:221-235 over constant.cpp:106-110) */
+template <typename F> VP_D F env_pdf(const SceneView<F> &sv) {
+    F pdf = K<F>::InvFourPi;
+    if (sv.g->n_emitters > 1) pdf = pdf * ((F) 1 / (F) sv.g->n_emitters);
+    return pdf;
+}
+/* The main path's ray left the scene: the environment is the emitter it "hits" (volpath.cpp:186-191,
+   volpathmis.cpp:252-268).  w = throughput (volpath) or p_over_f (volpathmis), w_nee = p_over_f_nee. */
+template <typename F, uint32_t FEAT>
+VP_D void env_escape_main(const SceneView<F> &sv, PathCold<F> &c, uint32_t fl, F w, F w_nee, uint32_t depth) {
+    const DScene<F> &g = *sv.g;
+    if (g.environment < 0) return;
+    const F emitted = sv.emitters[g.environment].irradiance;
+    if (FEAT & FT_MIS) {
+        if (depth == 0 && g.hide_emitters) return;
+        const bool count_direct = depth == 0 || (fl & QF_SPEC_CHAIN);
+        if (!count_direct) mis_update(w_nee, env_pdf(sv), (F) 1);
+        c.result += (count_direct ? mis_w1(w) : mis_w2(w, w_nee)) * emitted;
+    } else if (fl & QF_SPEC_CHAIN) {
+        c.result += w * emitted;
+    }
+}
+
 /* Scene::ray_intersect for a ray made in this visit, and what follows from the hit without any further draw.
    start_dl: the ray is intersect2 (volpath.cpp:238-252) and the direct-light march starts from the new hit.
    Called from ONE place in the kernel (after the phase bodies), so that ray_intersect is inlined there once: its
@@ -190,9 +253,13 @@ VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> 
         const bool valid = h.t != inf_<F>();
         if (mode == QM_MAIN) {
             state = valid ? Q_SURFACE : Q_PATH_END;
+            if ((FEAT & FT_ENV) && !valid) env_escape_main<F, FEAT>(sv, c, fl, s.cur.w, s.w2, s.depth);
         } else {
             if (mode == QM_NEE) s.total_dist += h.t;
             state = valid ? Q_MARCH_SURF : Q_MARCH_END;
+            /* the direct-light march reached the environment (volpath.cpp:429-438) */
+            if ((FEAT & FT_ENV) && mode == QM_DL && !valid && sv.g->environment >= 0)
+                c.emitter_val = sv.emitters[sv.g->environment].irradiance;
         }
         fl &= ~QF_TOP_DONE;
     }
@@ -233,6 +300,8 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     F *film = out.film_in_smem ? reinterpret_cast<F *>(smem + out.film_smem_offset) : out.film;
     const uint32_t max_depth = g.max_depth, rr_depth = g.rr_depth;
     const bool ltr = g.ltr != 0;
+    constexpr bool MIS = (FEAT & FT_MIS) != 0;   /* this instance runs volpathmis' state machine */
+    constexpr bool ENV = (FEAT & FT_ENV) != 0;   /* ... for scenes with an environment emitter */
     const F INF = inf_<F>();
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -352,6 +421,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             Ray<F> r;
             int med = -1;
             F w = 0, hit_t = INF, remaining = 0;
+            F w2 = 0;          /* volpathmis: p_over_f_uni of an emitter march */
             MediumHit<F> mi;
             mi.t = INF; mi.mint = 0; mi.p = mk3<F>(0, 0, 0); mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
             r.o = mi.p; r.d = mi.p; r.d_rcp = mi.p; r.mint = 0; r.maxt = 0;
@@ -362,18 +432,20 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 med = s.cur.medium;
                 w = s.cur.w;
                 hit_t = s.cur.hit_t;
+                if (MIS && (nee || ENV)) w2 = s.w2;   /* main mode: p_over_f_nee, read where a path meets the environment */
             }
             bool go = mine;
             if (go) {
                 if (fl & QF_TOP_DONE) {
-                    if (nee) remaining = s.remaining;
+                    if (nee) remaining = r.maxt;   /* stored by the visit that made or continued the march ray */
                 } else if (main_mode) {
-                    /* termination / Russian roulette (volpath.cpp:72-87) */
-                    if (!loop_top_rr(rng, w, s.eta, s.depth, rr_depth, max_depth)) { st = Q_PATH_END; go = false; }
+                    /* termination / Russian roulette (volpath.cpp:72-87; volpathmis.cpp:122-133) */
+                    const bool on = MIS ? mis_loop_top(rng, w, s.eta, s.depth, rr_depth, max_depth)
+                                        : loop_top_rr(rng, w, s.eta, s.depth, rr_depth, max_depth);
+                    if (!on) { st = Q_PATH_END; go = false; }
                 } else if (nee) {
                     remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
                     r.maxt = remaining;
-                    s.remaining = remaining;
                     if (!(remaining > 0)) { st = Q_MARCH_END; go = false; }
                 }
                 fl &= ~QF_TOP_DONE;
@@ -401,6 +473,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                (Medium::eval_tr_and_pdf, medium.cpp:77-89; volpath.cpp:113-117,300-311,402-404) */
             bool spectral = false;
             F ratio = 1;
+            F ff_p = 1, ff_f = 1;   /* volpathmis: free-flight pdf and transmittance, applied as update_weights(.., p, f) */
             if (in_medium) {
                 spectral = sv.media[med].spectral != 0;
                 if (hit_t < mi.t) mi.t = INF;
@@ -409,6 +482,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                        1 / mu_cell is left for a collision and 1 when the surface (or the end of the march) comes first */
                     const bool surface_first = hit_t < mi.t || (nee && mi.t > remaining);
                     ratio = surface_first ? (F) 1 : (F) 1 / mi.combined;
+                    ff_p = surface_first ? (F) 1 : mi.combined;
                 } else if (spectral) {
                     F tt = min_(mi.t, hit_t);
                     if (nee) tt = min_(remaining, tt);
@@ -416,11 +490,78 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F tr = exp_(-t * mi.combined);
                     bool surface_first = hit_t < mi.t || (nee && mi.t > remaining);
                     F pdf = surface_first ? tr : tr * mi.combined;
-                    ratio = pdf > 0 ? tr / pdf : (F) 0;
+                    if (MIS) { ff_p = pdf; ff_f = tr; }
+                    else ratio = pdf > 0 ? tr / pdf : (F) 0;
                 }
             }
             __syncwarp();
-            if (go && main_mode) {
+            if (MIS && go && main_mode) {
+                /* volpathmis.cpp:135-250: free-flight weights, null / real decision */
+                bool act_null = false, act_real = false, escaped = false;
+                uint32_t depth = s.depth;
+                if (in_medium) {
+                    if (spectral) mis_update(w, ff_p, ff_f);
+                    if (ENV && spectral) mis_update(w2, ff_p, ff_f);
+                    escaped = !mi.valid();
+                    const bool active_medium = mi.valid();
+                    F u = rng.next(F(), active_medium);
+                    bool null_scatter = u >= mi.sigma_t / mi.combined;
+                    act_null = null_scatter && active_medium;
+                    act_real = !act_null && active_medium;
+                    if (act_real) { depth += 1; s.depth = depth; }
+                }
+                const bool real_beyond_depth = act_real && !(depth < max_depth);
+                act_real = act_real && depth < max_depth;
+                if (act_null) {
+                    cnt.n_null++;
+                    if (spectral) mis_update(w, mi.sigma_n / mi.combined, mi.sigma_n);
+                    else mis_update(w, mi.sigma_n, mi.sigma_n);
+                    if (ENV) {
+                        if (spectral) mis_update(w2, (F) 1, mi.sigma_n);
+                        else mis_update(w2, (F) 1, mi.sigma_n / mi.combined);
+                    }
+                    r.o = mi.p;
+                    r.mint = 0;
+                    hit_t = hit_t - mi.t;
+                } else if (act_real) {
+                    if (spectral) mis_update(w, mi.sigma_t / mi.combined, mi.sigma_s);
+                    else mis_update(w, mi.sigma_t, mi.sigma_s);
+                    r.o = mi.p;
+                    st = Q_SCATTER;
+                } else if (!real_beyond_depth && (!in_medium || escaped) && hit_t != INF) {
+                    st = Q_SURFACE;
+                } else {
+                    st = Q_PATH_END;
+                    if (ENV && (!in_medium || escaped) && hit_t == INF) env_escape_main<F, FEAT>(sv, c, fl, w, w2, depth);
+                }
+            } else if (MIS && go) {
+                /* sample_emitter of volpathmis (volpathmis.cpp:362-442): two weights along the march */
+                bool escaped = false, active_medium = false;
+                F total_dist = s.total_dist;
+                if (in_medium) {
+                    if (spectral) { mis_update(w, ff_p, ff_f); mis_update(w2, ff_p, ff_f); }
+                    if (mi.t > remaining && mi.valid()) total_dist = s.ds_dist;
+                    if (mi.t > remaining) mi.t = INF;
+                    escaped = !mi.valid();
+                    active_medium = mi.valid();
+                    if (active_medium) {
+                        total_dist += mi.t;
+                        cnt.n_null++;
+                        r.o = mi.p;
+                        r.mint = 0;
+                        hit_t = hit_t - mi.t;
+                        if (spectral) { mis_update(w, (F) 1, mi.sigma_n); mis_update(w2, mi.sigma_n / mi.combined, mi.sigma_n); }
+                        else { mis_update(w, (F) 1, mi.sigma_n / mi.combined); mis_update(w2, mi.sigma_n, mi.sigma_n); }
+                    }
+                }
+                bool active_surface = !in_medium || escaped;
+                if (active_surface) total_dist += hit_t;
+                active_surface = active_surface && hit_t != INF && !active_medium;
+                r.maxt = remaining; s.total_dist = total_dist;
+                if (active_surface) st = Q_MARCH_SURF;
+                else if (active_medium && (g.mis != 2 ? mis_w1(w2) != 0 : (w2 != 0 || w != 0))) st = Q_STEP;
+                else st = Q_MARCH_END;
+            } else if (go && main_mode) {
                 bool act_null = false, act_real = false, escaped = false;
                 uint32_t depth = s.depth;
                 if (in_medium) {
@@ -452,6 +593,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     st = Q_SURFACE;
                 } else {
                     st = Q_PATH_END;
+                    if (ENV && (!in_medium || escaped) && hit_t == INF) env_escape_main<F, FEAT>(sv, c, fl, w, w, depth);
                 }
             } else if (go) {
                 /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
@@ -483,13 +625,19 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                    end of the march are rare: they run as their own phase, in full batches */
                 if (active_surface) st = Q_MARCH_SURF;
                 else if (active_medium && w != 0) st = Q_STEP;
-                else st = Q_MARCH_END;
+                else {
+                    st = Q_MARCH_END;
+                    /* the direct-light march reached the environment (volpath.cpp:429-438) */
+                    if (ENV && !nee && !active_medium && hit_t == INF && g.environment >= 0)
+                        c.emitter_val = sv.emitters[g.environment].irradiance;
+                }
             }
             if (mine) {
                 st_rng(s, rng);
                 s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
                 st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
                 s.cur.w = w;
+                if (MIS && (nee || ENV)) s.w2 = w2;
                 s.cur.hit_t = hit_t;
                 s.flags = (fl & ~QF_STATE) | (uint32_t) st;
                 state = st;
@@ -509,17 +657,73 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 const DMedium<F> &m = sv.media[med];
                 const V3<F> d = ld3(s.cur.d);
                 const V3<F> p = ld3(s.cur.o); /* the scattering position (STEP left it as the ray origin) */
-                if (state == Q_SCATTER) { /* volpath.cpp:146-168 */
+                if (MIS && state == Q_SCATTER) { /* volpathmis.cpp:201-218, sample_emitter prologue :330-349 */
+                    c.c_real += 1;
+                    fl |= QF_VALID_RAY;
+                    state = Q_SCATTER_B;
+                    if (ENV && m.sample_emitters) fl &= ~QF_SPEC_CHAIN;   /* volpathmis.cpp:171 */
+                    if (m.sample_emitters) {
+                        F ev;
+                        DirSample<F> ds = queue_sample_emitter<F, FEAT>(sv, rng, ev);
+                        F nee = s.cur.w, uni = s.cur.w;
+                        if (ds.pdf != 0) mis_update(nee, ds.pdf, (F) 1);
+                        /* what the caller applies to the march's two weights when it is over (volpathmis.cpp:211-216) */
+                        const F phase_val = phase_eval_at<F, FEAT>(sv, sv.phases[m.phase], p, -d, ds.d);
+                        const F phase_p = ds.delta ? (F) 0 : phase_val;
+                        if (ds.pdf != 0) {
+                            copy_ctx(c.saved, s.cur);
+                            Ray<F> r2 = spawn_ray(p, ds.d);
+                            r2.mint = 0;
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = phase_val; c.bu = phase_p;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SCATTER_B << QF_CONT_SHIFT);
+                            const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
+                            r2.maxt = remaining;
+                            st_ray(s.cur, r2);
+                            s.cur.hit_t = INF; s.cur.hit_shape = -1;
+                            s.cur.w = nee; s.w2 = uni;
+                            if (remaining > 0) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r2; }
+                            else state = Q_MARCH_END;
+                        } else {
+                            mis_update(nee, (F) 1, phase_val);
+                            mis_update(uni, phase_p, phase_val);
+                            c.result += mis_w2(nee, uni) * ev;
+                        }
+                    }
+                }
+                if (MIS && state == Q_SCATTER_B) { /* phase function sampling (volpathmis.cpp:220-236) */
+                    const DPhase<F> &phase_fn = sv.phases[m.phase];
+                    F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
+                    F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> wo = phase_sample_at<F, FEAT>(sv, phase_fn, p, d, s1, s2x, s2y);
+                    const F phase_pdf = phase_sample_pdf_at<F, FEAT>(sv, phase_fn, p, -d, wo, s1);
+                    Ray<F> r = spawn_ray(p, wo);
+                    r.mint = 0;
+                    st_ray(s.cur, r);
+                    F w = s.cur.w;
+                    if (ENV) {   /* p_over_f_nee restarts from the scattering event (volpathmis.cpp:219, 234) */
+                        F w_nee = w;
+                        mis_update(w_nee, (F) 1, phase_pdf);
+                        s.w2 = w_nee;
+                    }
+                    mis_update(w, phase_pdf, phase_pdf);
+                    /* top of the next loop iteration */
+                    if (mis_loop_top(rng, w, s.eta, s.depth, rr_depth, max_depth)) {
+                        state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = r;
+                    } else {
+                        state = Q_PATH_END;
+                    }
+                    s.cur.w = w;
+                }
+                if (!MIS && state == Q_SCATTER) { /* volpath.cpp:146-168 */
                     c.c_real += 1;
                     const F throughput = s.cur.w;
                     fl |= QF_VALID_RAY;
                     state = Q_SCATTER_B;
+                    if (ENV) fl = m.sample_emitters ? (fl & ~QF_SPEC_CHAIN) : (fl | QF_SPEC_CHAIN);   /* volpath.cpp:158-159 */
                     if (m.sample_emitters) { /* sample_emitter prologue (volpath.cpp:261-283) */
-                        F sx = rng.next(F(), true);
-                        (void) rng.next(F(), true);
                         F ev;
-                        DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
-                        if (ds.pdf == 0) ev = 0;
+                        DirSample<F> ds = queue_sample_emitter<F, FEAT>(sv, rng, ev);
                         F nee_w = throughput * phase_eval_at<F, FEAT>(sv, sv.phases[m.phase], p, -d, ds.d);
                         if (ds.pdf != 0) {
                             copy_ctx(c.saved, s.cur);
@@ -531,7 +735,6 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                             /* top of the march's first iteration (volpath.cpp:285-291) */
                             const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
                             r2.maxt = remaining;
-                            s.remaining = remaining;
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
@@ -543,7 +746,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                 }
                 /* no emitter march was started: sample the phase function in the same visit */
-                if (state == Q_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
+                if (!MIS && state == Q_SCATTER_B) { /* phase function sampling (volpath.cpp:170-176) */
                     const DPhase<F> &phase_fn = sv.phases[m.phase];
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
@@ -588,16 +791,81 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 }
                 F throughput = s.cur.w;
                 uint32_t depth = s.depth;
-                if (state == Q_SURFACE) { /* volpath.cpp:192-212 */
+                if (MIS && state == Q_SURFACE) { /* volpathmis.cpp:270-290 */
+                    c.c_surf += 1;
+                    const bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
+                    state = Q_SURF_B;
+                    if (active_e) {
+                        F ev;
+                        DirSample<F> ds = queue_sample_emitter<F, FEAT>(sv, rng, ev);
+                        F nee = throughput, uni = throughput;   /* p_over_f */
+                        if (ds.pdf != 0) mis_update(nee, ds.pdf, (F) 1);
+                        const V3<F> wo = fr.to_local(ds.d);
+                        const F bsdf_val = bsdf_eval(bsdf, wi, wo);
+                        const F bsdf_p = ds.delta ? (F) 0 : bsdf_pdf(bsdf, wi, wo);
+                        if (ds.pdf != 0) {
+                            copy_ctx(c.saved, s.cur);
+                            Ray<F> r2 = spawn_ray(sp_, ds.d);
+                            s.total_dist = 0; s.ds_dist = ds.dist; c.emitter_val = ev; c.nee_w = bsdf_val; c.bu = bsdf_p;
+                            fl = (fl & ~(QF_MODE | QF_CONT)) | ((uint32_t) QM_NEE << QF_MODE_SHIFT) |
+                                 ((uint32_t) QC_SURF_B << QF_CONT_SHIFT);
+                            const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
+                            r2.maxt = remaining;
+                            st_ray(s.cur, r2);
+                            s.cur.hit_t = INF; s.cur.hit_shape = -1;
+                            s.cur.w = nee; s.w2 = uni;
+                            if (remaining > 0) { state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; ir = r2; }
+                            else state = Q_MARCH_END;
+                        } else {
+                            mis_update(nee, (F) 1, bsdf_val);
+                            mis_update(uni, bsdf_p, bsdf_val);
+                            c.result += mis_w2(nee, uni) * ev;
+                        }
+                    }
+                }
+                if (MIS && state == Q_SURF_B) { /* BSDF sampling (volpathmis.cpp:292-322) */
+                    F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
+                    F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
+                    V3<F> bwo;
+                    F bs_pdf, bs_eta, bsdf_weight;
+                    uint32_t sampled_type;
+                    bsdf_sample(bsdf, wi, s1, s2x, s2y, bwo, bs_pdf, bs_eta, sampled_type, bsdf_weight);
+                    const bool invalid_sample = bs_pdf == 0;
+                    const bool alive = bs_pdf > 0;
+                    const bool non_null = alive && !(sampled_type & BF_Null);
+                    if (non_null || invalid_sample) fl |= QF_VALID_RAY;
+                    if (ENV) {   /* volpathmis.cpp:311-312 */
+                        if (non_null && (sampled_type & BF_Delta)) fl |= QF_SPEC_CHAIN;
+                        if (alive && (sampled_type & BF_Smooth)) fl &= ~QF_SPEC_CHAIN;
+                    }
+                    state = Q_PATH_END;
+                    if (alive) {
+                        s.eta *= bs_eta;
+                        Ray<F> r = spawn_ray(sp_, fr.to_world(bwo));
+                        st_ray(s.cur, r);
+                        if (non_null) { depth += 1; s.depth = depth; }
+                        if (ENV) {   /* p_over_f_nee (volpathmis.cpp:314-317); a null BSDF leaves it as it is */
+                            F w_nee = non_null ? throughput : s.w2;
+                            if (non_null) mis_update(w_nee, (F) 1, bsdf_weight * bs_pdf);
+                            s.w2 = w_nee;
+                        }
+                        mis_update(throughput, bs_pdf, bsdf_weight * bs_pdf);
+                        if (sh.interior >= 0 || sh.exterior >= 0)
+                            s.cur.medium = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
+                        /* top of the next loop iteration */
+                        if (mis_loop_top(rng, throughput, s.eta, depth, rr_depth, max_depth)) {
+                            state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = r;
+                        }
+                    }
+                    s.cur.w = throughput;
+                }
+                if (!MIS && state == Q_SURFACE) { /* volpath.cpp:192-212 */
                     c.c_surf += 1;
                     bool active_e = (bsdf_flags(bsdf.type) & BF_Smooth) != 0 && (depth + 1 < max_depth);
                     state = Q_SURF_B;
                     if (active_e) { /* sample_emitter prologue (volpath.cpp:261-283) */
-                        F sx = rng.next(F(), true);
-                        (void) rng.next(F(), true);
                         F ev;
-                        DirSample<F> ds = sample_emitter_direction(sv, sx, ev);
-                        if (ds.pdf == 0) ev = 0;
+                        DirSample<F> ds = queue_sample_emitter<F, FEAT>(sv, rng, ev);
                         V3<F> wo = fr.to_local(ds.d);
                         F bsdf_val = bsdf_eval(bsdf, wi, wo);
                         F bpdf = bsdf_pdf(bsdf, wi, wo);
@@ -613,7 +881,6 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                                  ((uint32_t) QC_SURF_B << QF_CONT_SHIFT);
                             const F remaining = ds.dist * ((F) 1 - K<F>::ShadowEpsilon) - (F) 0;
                             r2.maxt = remaining;
-                            s.remaining = remaining;
                             st_ray(s.cur, r2);
                             s.cur.hit_t = INF; s.cur.hit_shape = -1;
                             s.cur.w = 1;
@@ -625,7 +892,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                 }
                 /* no emitter march was started (null BSDF, or nothing to sample): go on in the same visit */
-                if (state == Q_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
+                if (!MIS && state == Q_SURF_B) { /* BSDF sampling (volpath.cpp:214-241) */
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
                     V3<F> bwo;
@@ -638,6 +905,10 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     st_ray(s.cur, r);
                     bool non_null = !(sampled_type & BF_Null);
                     if (non_null) { depth += 1; s.depth = depth; fl |= QF_VALID_RAY; }
+                    if (ENV) {   /* volpath.cpp:228-229 */
+                        if (non_null && (sampled_type & BF_Delta)) fl |= QF_SPEC_CHAIN;
+                        if (sampled_type & BF_Smooth) fl &= ~QF_SPEC_CHAIN;
+                    }
                     bool add_emitter = !(sampled_type & BF_Delta) && throughput != 0 && (depth < max_depth);
                     /* medium switch (volpath.cpp:249-250), applied after the direct-light march */
                     const int medium = s.cur.medium;
@@ -645,6 +916,11 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                                                 ? (dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior) : medium;
                     if (add_emitter) { /* intersect2: the new hit replaces si (volpath.cpp:238-252) */
                         c.medium_next = medium_next;
+                        if (ENV) {   /* mis_weight(bs.pdf, emitter_pdf) for the emitter the march can reach (volpath.cpp:244) */
+                            F pa = bs_pdf, pb = env_pdf(sv);
+                            pa *= pa; pb *= pb;
+                            c.nee_w = pa > 0 ? pa / (pa + pb) : (F) 0;
+                        }
                         do_isect = true; isect_main = true; start_dl = true; ir = r;
                         state = Q_STEP;
                     } else {
@@ -671,19 +947,29 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     F w = s.cur.w;
                     const DShape<F> &sh = sv.shapes[s.cur.hit_shape];
                     /* eval_null_transmission: 1 for `null`, 0 otherwise (null.cpp:69-72, bsdf.cpp:11-14) */
-                    w *= sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
+                    const F null_tr = sv.bsdfs[sh.bsdf].type == 1 ? (F) 1 : (F) 0;
+                    bool on;
+                    if (MIS) {   /* volpathmis.cpp:415-440: both weights; the march goes on while they say so */
+                        F w2 = s.w2;
+                        mis_update(w, (F) 1, null_tr);
+                        mis_update(w2, (F) 1, null_tr);
+                        s.w2 = w2;
+                        on = g.mis != 2 ? mis_w1(w2) != 0 : (w2 != 0 || w != 0);
+                    } else {
+                        w *= null_tr;
+                        on = w != 0;
+                    }
                     Ray<F> r = spawn_ray(ld3(s.cur.hit_p), ld3(s.cur.d));
                     if (sh.interior >= 0 || sh.exterior >= 0)
                         s.cur.medium = dot(r.d, ld3(s.cur.hit_n)) > 0 ? sh.exterior : sh.interior;
                     s.cur.w = w;
                     state = Q_MARCH_END;
-                    if (w != 0) {
+                    if (on) {
                         /* top of the march's next iteration */
                         bool cont = true;
                         if (nee) {
                             const F remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
                             r.maxt = remaining;
-                            s.remaining = remaining;
                             cont = remaining > 0;
                         }
                         /* the new ray is intersected at once (below); outside the medium that settles what the march
@@ -798,10 +1084,16 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     s.cur.medium = sn.medium;
                     s.cur.w = 1;
                     c.result = 0; s.eta = 1; s.depth = 0;
-                    fl &= ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_TOP_DONE);
+                    fl &= ~(QF_MODE | QF_CONT | QF_VALID_RAY | QF_TOP_DONE | QF_SPEC_CHAIN);
+                    if (ENV) {   /* volpath.cpp:51-53, volpathmis.cpp:100-104 */
+                        if (!g.hide_emitters) fl |= QF_SPEC_CHAIN;
+                        if (!g.hide_emitters && g.environment >= 0) fl |= QF_VALID_RAY;
+                        if (MIS) s.w2 = 1;
+                    }
                     /* top of the first loop iteration */
                     F w0 = 1;
-                    if (loop_top_rr(rng, w0, (F) 1, 0u, rr_depth, max_depth)) {
+                    if (MIS ? mis_loop_top(rng, w0, (F) 1, 0u, rr_depth, max_depth)
+                            : loop_top_rr(rng, w0, (F) 1, 0u, rr_depth, max_depth)) {
                         state = Q_STEP; fl |= QF_TOP_DONE; do_isect = true; isect_main = true; ir = ray;
                     } else {
                         state = Q_PATH_END;
@@ -823,8 +1115,15 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             if (phase == PH_MARCH && has && state == Q_MARCH_END) {
                 /* a march is over: hand the result back and restore the main path's context */
                 const bool nee = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT) == QM_NEE;
-                if (nee) c.result += c.nee_w * (s.cur.w * c.emitter_val);
-                /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added */
+                if (MIS) {   /* the caller's half of the emitter sample (volpathmis.cpp:211-216, 282-289) */
+                    F nee_end = s.cur.w, uni_end = s.w2;
+                    mis_update(nee_end, (F) 1, c.nee_w);
+                    mis_update(uni_end, c.bu, c.nee_w);
+                    c.result += mis_w2(nee_end, uni_end) * c.emitter_val;
+                } else if (nee) c.result += c.nee_w * (s.cur.w * c.emitter_val);
+                /* QM_DL: emitter_val = 0 and emitter_pdf = 0 for delta emitters: nothing is added.  With an environment
+                   the march may have reached it: emitter_val is then its radiance (0 otherwise: adds nothing) */
+                else if (ENV && c.emitter_val != 0) c.result += c.nee_w * c.saved.w * (s.cur.w * c.emitter_val);
                 copy_ctx(s.cur, c.saved);
                 const int cont = (int) ((fl & QF_CONT) >> QF_CONT_SHIFT);
                 if (cont == QC_SCATTER_B) state = Q_SCATTER_B;

@@ -77,7 +77,14 @@ enum : uint32_t {
     FT_GRID_GLOBAL = 1u << 18, /* some grid is read from global memory                    */
     FT_MESH_SMEM = 1u << 19,   /* triangle meshes whose BVH and triangles are staged in shared memory (small meshes) */
     FT_MAJORANT_GRID = 1u << 20, /* the launch samples free flights against majorant grids (opt-in fast mode) */
-    FT_ALL = 0x1fffffu
+    FT_ALL = 0x1fffffu,
+    /* the integrator is volpathmis (src/integrators/volpathmis.cpp) instead of volpath: not a scene feature but another
+       state machine in the same phases, so it is outside FT_ALL -- an instance is compiled for one or the other */
+    FT_MIS = 1u << 21,
+    /* the scene has an environment emitter (src/emitters/constant.cpp): non-delta emitter sampling with both samples,
+       radiance where a ray escapes, the specular-chain flag.  Like FT_MIS it selects other phase bodies: outside
+       FT_ALL, own instances */
+    FT_ENV = 1u << 22
 };
 constexpr uint32_t FT_ANY_MESH = FT_MESH | FT_MESH_SMEM;
 

@@ -336,10 +336,9 @@ def with_plugin(scene, seeding="scalar", type_name="volpath_b200", **props):
     return d
 
 
-def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None, exact_math=False,
+def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, keep_dir=None,
            describe_oracle=False, build="parity", plugin_root=False, record=False):
     """Runs the reference binary on `scene`.  Returns (film[h, w, channels], seconds of the last Integrator::render).
-    exact_math: put oracle_math.h's logf / expf / sincosf / cbrtf in front of glibc (ref_math_preload.cpp).
     describe_oracle (scenes from with_plugin only): do not render on a GPU; run the plugin's describe() and render
     its descriptor with the CPU oracle (refprobe --describe-oracle)."""
     probe = RELEASE_PROBE if build == "release" else PROBE
@@ -356,8 +355,6 @@ def render(scene, variant="scalar_mono", threads=1, repeats=1, write_vol=None, k
         rec_path = os.path.join(keep_dir, "records.bin")
         if record:   # the scene's sampler must be {"type": "recording"} (oracle/ref_recording_sampler.cpp)
             env["B2VP_RECORD_PATH"] = rec_path
-        if exact_math:
-            env["LD_PRELOAD"] = os.path.join(REF_DIR, "libb2vp_refmath.so")
         cmd = [probe, variant, xml, out, "-t", str(threads), "-r", str(repeats)]
         if describe_oracle:
             cmd += ["--describe-oracle", ORACLE_LIB]

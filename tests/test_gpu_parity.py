@@ -25,6 +25,34 @@ CASES = {
     "c2_volpathmis": lambda v: _mis(scenes.c2(spp=8, variant=v, width=64)),
     "c3_volpathmis": lambda v: _mis(scenes.c3(spp=2, variant=v, n=16, size=12)),
     "c5_volpathmis": lambda v: _mis(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64)),
+    # volpathmis on the queue kernel: the other implementation (use_spectral_mis = false, volpathmis.cpp:35-52), media
+    # without spectral free-flight weights, a blend phase (its pdf enters the weights as pdf / pdf), a depth limit
+    "c2_volpathmis_nospectralmis": lambda v: _mis(scenes.c2(spp=8, variant=v, width=64), use_spectral_mis=False),
+    "c2_volpathmis_notspectral": lambda v: _mis(scenes.c2(spp=8, variant=v, width=64, spectral=False)),
+    "c3_volpathmis_nospectralmis": lambda v: _mis(scenes.c3(spp=2, variant=v, n=16, size=12), use_spectral_mis=False),
+    "c2_volpathmis_blendphase": lambda v: _mis(_blendphase(v, True)),
+    "c1_volpathmis_depth3": lambda v: _mis(scenes.c1(spp=2048, variant=v, max_depth=3, rr_depth=2)),
+    # two suns: the emitter pdf is 1/2, volpathmis works with weight * pdf (volpathmis.cpp:341-343)
+    "c2_two_suns": lambda v: _two_suns(scenes.c2(spp=8, variant=v, width=64)),
+    "c2_two_suns_volpathmis": lambda v: _mis(_two_suns(scenes.c2(spp=8, variant=v, width=64))),
+    "c5_two_suns_volpathmis": lambda v: _mis(_two_suns(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64))),
+    # environment emitter on the queue kernel (FT_ENV): with and without a sun, hidden, both integrators, surfaces
+    "c2_sky_hidden": lambda v: _hide(_sky(scenes.c2(spp=8, variant=v, width=64), 0.25)),
+    "c2_sky_hidden_volpathmis": lambda v: _mis(_hide(_sky(scenes.c2(spp=8, variant=v, width=64), 0.25))),
+    "c2_sky_only_volpathmis": lambda v: _mis(_sky(scenes.c2(spp=8, variant=v, width=64), 0.5, sun=False)),
+    "c1_sky_depth3": lambda v: _sky(scenes.c1(spp=2048, variant=v, max_depth=3, rr_depth=2), 0.25),
+    "c3_sky": lambda v: _sky(scenes.c3(spp=2, variant=v, n=16, size=12), 0.25),
+    "c3_sky_volpathmis": lambda v: _mis(_sky(scenes.c3(spp=2, variant=v, n=16, size=12), 0.25)),
+    "c5_sky": lambda v: _sky(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64), 0.5),
+    "c5_sky_volpathmis": lambda v: _mis(_sky(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64), 0.5)),
+    "c5_sky_only_volpathmis_nospectralmis": lambda v: _mis(_sky(scenes.c5(spp=4, variant=v, n_leaves=200, n_sensors=64), 0.5,
+                                                                sun=False), use_spectral_mis=False),
+    "c5_sky_two_suns_bilambertian": lambda v: _two_suns(_sky(scenes.c5(
+        spp=8, variant=v, n_leaves=400, n_sensors=64,
+        leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}), 0.5)),
+    "c5_volpathmis_bilambertian": lambda v: _mis(scenes.c5(
+        spp=8, variant=v, n_leaves=400, n_sensors=64,
+        leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25})),
     "c2_irradiancemeter": lambda v: _irradiancemeter(v),
     "c2_distantflux": lambda v: _distantflux(v, True),
     "c2_distantflux_notarget": lambda v: _distantflux(v, False),
@@ -64,8 +92,18 @@ def _sky(d, radiance, sun=True):
     return d
 
 
-def _mis(d):
-    d["integrator"] = dict(d["integrator"], type="volpathmis")
+def _two_suns(d):
+    d["sun2"] = {"type": "directional", "direction": [-0.4, 0.1, -1], "irradiance": 0.5}
+    return d
+
+
+def _hide(d):
+    d["integrator"] = dict(d["integrator"], hide_emitters=True)
+    return d
+
+
+def _mis(d, **props):
+    d["integrator"] = dict(d["integrator"], type="volpathmis", **props)
     return d
 
 
@@ -101,6 +139,31 @@ def test_wavefront_seeding_bit_exact(pkg, oracle, case, variant, kernel):
         pytest.skip("variant covered in fp32")
     sc = pkg.load_dict(CASES[case](variant), variant)
     compare(pkg, oracle, sc, pkg.abi.SEED_WAVEFRONT)
+
+
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+def test_volpathmis_runs_on_the_queue_kernel(pkg, oracle, variant):
+    """volpathmis is a set of phase bodies of the product kernel (FT_MIS instances), not a job for the slow
+    one-thread-per-stream kernel: B2vpSceneInfo::last_kernel says which instance a launch took."""
+    abi = pkg.abi
+    for make, preset in ((lambda: scenes.c1(spp=256, variant=variant), "homogeneous"),
+                         (lambda: scenes.c2(spp=4, variant=variant, width=32), "heterogeneous"),
+                         (lambda: scenes.c3(spp=1, variant=variant, n=48, size=8), "heterogeneous+albedo grid"),
+                         (lambda: _sky(scenes.c2(spp=4, variant=variant, width=32), 0.25), "environment, generic"),
+                         (lambda: scenes.c5(spp=2, variant=variant, n_leaves=100, n_sensors=16), "generic")):   # BVH in HBM
+        sc = pkg.load_dict(_mis(make()), variant)
+        with pkg.DeviceScene(sc) as ds:
+            ds.render(seed_mode=abi.SEED_WAVEFRONT)
+            assert ds.info().last_kernel.decode().startswith("queue/volpathmis, " + preset), ds.info().last_kernel.decode()
+            ds.render(seed_mode=abi.SEED_WAVEFRONT, kernel="generic")
+            assert "generic" in ds.info().last_kernel.decode()
+            ds.render(seed_mode=abi.SEED_WAVEFRONT, kernel="mega")
+            assert ds.info().last_kernel.decode().startswith("stream")
+            with pytest.raises(pkg.B2vpError, match="volpathmis"):
+                ds.render(seed_mode=abi.SEED_WAVEFRONT, majorant_grid=1)
+            if variant == "scalar_mono":
+                ds.render(seed_mode=abi.SEED_WAVEFRONT, math="fast")
+                assert ds.info().last_kernel.decode().endswith("fast f32")
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
