@@ -152,6 +152,7 @@ struct DeviceCtx {
     int device = 0;
     int sm_count = 0;
     size_t smem_optin = 0;
+    size_t l2_window_max = 0;   /* largest access-policy window (0: no persisting L2 on this device) */
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf, stop_flag;
@@ -371,6 +372,15 @@ int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
     std::unique_ptr<DeviceCtx> c(new DeviceCtx());
     c->device = device; c->sm_count = sm_count; c->smem_optin = (size_t) smem_optin;
     CU_CHECK(cudaSetDevice(device));
+    {
+        int l2_persist_max = 0, window_max = 0;
+        CU_CHECK(cudaDeviceGetAttribute(&l2_persist_max, cudaDevAttrMaxPersistingL2CacheSize, device));
+        CU_CHECK(cudaDeviceGetAttribute(&window_max, cudaDevAttrMaxAccessPolicyWindowSize, device));
+        if (l2_persist_max > 0 && window_max > 0 &&
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t) l2_persist_max) == cudaSuccess)
+            c->l2_window_max = (size_t) window_max;
+        (void) cudaGetLastError();
+    }
     CU_CHECK(cudaEventCreate(&c->ev0));
     CU_CHECK(cudaEventCreate(&c->ev1));
     CU_CHECK(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
@@ -1080,9 +1090,24 @@ int set_stream_range(const B2vpRenderArgs *a, StreamSpace &sp) {
 
 template <typename F>
 cudaError_t launch_kernel(const LaunchPlan &pl, const DeviceScene<F> &ds, const DStreams &spd, const RenderOut<F> &out,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, const DeviceCtx *dc = nullptr, bool pin_cold = false) {
     void *kargs[3] = { (void *) &ds.g, (void *) &spd, (void *) &out };
-    return cudaLaunchKernel(pl.kern, dim3((unsigned) pl.grid), dim3((unsigned) pl.threads), kargs, pl.smem, stream);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) pl.grid); cfg.blockDim = dim3((unsigned) pl.threads);
+    cfg.dynamicSmemBytes = pl.smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (pin_cold && dc && dc->l2_window_max && out.q_cold && pl.cold_bytes) {
+        /* the cold path records are read and written by every phase but STEP for the whole launch: ask L2 to keep
+           them (persisting lines) rather than cycle them through HBM */
+        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[0].val.accessPolicyWindow.base_ptr = out.q_cold;
+        attr[0].val.accessPolicyWindow.num_bytes = std::min(pl.cold_bytes, dc->l2_window_max);
+        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelExC(&cfg, pl.kern, kargs);
 }
 
 void fill_totals(B2vpCounters &t, const unsigned long long *tot, float ms, uint32_t launches) {
@@ -1209,7 +1234,7 @@ template <typename F> int render_typed(b2vp_scene *s, DeviceCtx *dc, const B2vpR
     const auto t_start = std::chrono::steady_clock::now();
     CU_CHECK(cudaEventRecord(dc->ev0, stream));
     if (count) {
-        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream));
+        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream, dc, (a->debug_flags & 2u) == 0));
         launches++;
     }
     CU_CHECK(cudaEventRecord(dc->ev1, stream));

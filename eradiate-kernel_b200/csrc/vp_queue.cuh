@@ -230,7 +230,9 @@ VP_D void intersect_new_ray(const SceneView<F> &sv, PathSlot<F> &s, PathCold<F> 
     SurfaceHit<F> h;
     PathCounters cnt;
     cnt.n_intersect = 0;
-    ray_intersect_impl<F, FEAT, false>(sv, ir, h, cnt, (FEAT & FT_ANY_MESH) ? &work : nullptr);
+    /* BVH work is counted for meshes whose BVH lives in HBM (its memory roofline, bench.py); the few-triangle
+       meshes staged in shared memory are not worth the registers: counting them cost the C2 instance 8 % */
+    ray_intersect_impl<F, FEAT, false>(sv, ir, h, cnt, (FEAT & FT_MESH) ? &work : nullptr);
     s.c_isect += 1;
     s.cur.hit_t = h.t; st3(s.cur.hit_p, h.p); st3(s.cur.hit_n, h.n); s.cur.hit_shape = h.shape;
     if (isect_main) { /* the main path will want the whole SurfaceInteraction if it scatters here: keep what
@@ -309,6 +311,8 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
     PathSlot<F> *S = reinterpret_cast<PathSlot<F> *>(smem + out.q_slots_offset);
     PathCold<F> *C = reinterpret_cast<PathCold<F> *>(out.q_cold) + (size_t) blockIdx.x * out.q_n_slots;
+    __builtin_assume(__isGlobal(C));   /* LDG / STG instead of generic loads and stores */
+    __builtin_assume(__isGlobal(out.film)); __builtin_assume(__isGlobal(out.totals));
     QueueCtl *ctl = reinterpret_cast<QueueCtl *>(smem + out.q_ctl_offset);
     unsigned short *Q = reinterpret_cast<unsigned short *>(ctl + 1); /* [PH_N][cap] rings of slot ids */
     const int P = (int) out.q_n_slots;
@@ -329,9 +333,16 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
     }
     __syncthreads();
 
-    unsigned long long tot[TOT_N];
+    /* Per-thread launch totals.  The BVH work counters are kept apart and exist only in the instances that count
+       them: as elements 8 and 9 of this array they cost the C2 instance 8 % (221 against 240 Mpaths/s; A/B over four
+       builds on one box, profiles/r2_history.md).  Tried instead: shared-memory totals fed by atomics when a stream
+       ends -- with wavefront seeding a stream is one path, and six contended 64-bit shared atomics per path cost
+       more (196). */
+    constexpr int TOT_Q = TOT_BVH_NODES;
+    unsigned long long tot[TOT_Q];
 #pragma unroll
-    for (int i = 0; i < TOT_N; ++i) tot[i] = 0;
+    for (int i = 0; i < TOT_Q; ++i) tot[i] = 0;
+    unsigned long long bvh_nodes = 0, bvh_tris = 0;   /* FT_MESH instances only (dead code elsewhere) */
 
     int last_phase = PH_END;
     for (;;) {
@@ -1110,7 +1121,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 BvhWork work;
                 work.nodes = 0; work.tris = 0;
                 intersect_new_ray<F, FEAT>(sv, s, c, ir, isect_main, start_dl, fl, state, work);
-                tot[TOT_BVH_NODES] += work.nodes; tot[TOT_BVH_TRIS] += work.tris;
+                if (FEAT & FT_MESH) { bvh_nodes += work.nodes; bvh_tris += work.tris; }
             }
             if (phase == PH_MARCH && has && state == Q_MARCH_END) {
                 /* a march is over: hand the result back and restore the main path's context */
@@ -1159,10 +1170,14 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
 
     /* totals: warp reduce, one atomic per warp and counter */
 #pragma unroll
-    for (int i = 0; i < TOT_N; ++i) {
+    for (int i = 0; i < TOT_Q; ++i) {
         unsigned long long v = tot[i];
         for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(FULL, v, o);
         if (lane == 0 && v) atomicAdd(out.totals + i, v);
+    }
+    if (FEAT & FT_MESH) {
+        if (bvh_nodes) atomicAdd(out.totals + TOT_BVH_NODES, bvh_nodes);
+        if (bvh_tris) atomicAdd(out.totals + TOT_BVH_TRIS, bvh_tris);
     }
     if (out.film_in_smem) {
         __syncthreads();
