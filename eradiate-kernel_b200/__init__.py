@@ -3,9 +3,9 @@ reference's load_dict / render entry points over the C-ABI of include/b2vp.h."""
 from . import abi
 from .abi import B2vpError
 from .dist import reduce_film, shard_interleaved, shard_range
-from .render import DeviceScene, RenderResult, render, render_defaults, shard_streams
+from .render import DeviceScene, RenderResult, read_exr, render, render_defaults, shard_streams
 from .scene import Scene, load_dict, read_vol, write_vol
 from .transform import Transform
 
-__all__ = ["abi", "B2vpError", "DeviceScene", "RenderResult", "render", "render_defaults", "shard_streams", "Scene", "load_dict", "read_vol", "write_vol",
+__all__ = ["abi", "B2vpError", "DeviceScene", "RenderResult", "render", "render_defaults", "shard_streams", "read_exr", "Scene", "load_dict", "read_vol", "write_vol",
            "Transform", "shard_range", "shard_interleaved", "reduce_film"]

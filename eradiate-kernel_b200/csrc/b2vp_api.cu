@@ -153,6 +153,7 @@ struct DeviceCtx {
     int sm_count = 0;
     size_t smem_optin = 0;
     size_t l2_window_max = 0;   /* largest access-policy window (0: no persisting L2 on this device) */
+    size_t l2_persist_bytes = 0; /* the persisting L2 carve-out this library set (cudaLimitPersistingL2CacheSize) */
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf, stop_flag;
@@ -378,7 +379,7 @@ int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
         CU_CHECK(cudaDeviceGetAttribute(&window_max, cudaDevAttrMaxAccessPolicyWindowSize, device));
         if (l2_persist_max > 0 && window_max > 0 &&
             cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t) l2_persist_max) == cudaSuccess)
-            c->l2_window_max = (size_t) window_max;
+            { c->l2_window_max = (size_t) window_max; c->l2_persist_bytes = (size_t) l2_persist_max; }
         (void) cudaGetLastError();
     }
     CU_CHECK(cudaEventCreate(&c->ev0));
@@ -1101,8 +1102,10 @@ cudaError_t launch_kernel(const LaunchPlan &pl, const DeviceScene<F> &ds, const 
            them (persisting lines) rather than cycle them through HBM */
         attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
         attr[0].val.accessPolicyWindow.base_ptr = out.q_cold;
-        attr[0].val.accessPolicyWindow.num_bytes = std::min(pl.cold_bytes, dc->l2_window_max);
-        attr[0].val.accessPolicyWindow.hitRatio = 1.0f;
+        const size_t window = std::min(pl.cold_bytes, dc->l2_window_max);
+        attr[0].val.accessPolicyWindow.num_bytes = window;
+        /* a window larger than the persisting carve-out thrashes inside it: mark only the share that fits */
+        attr[0].val.accessPolicyWindow.hitRatio = (float) std::min(1.0, (double) dc->l2_persist_bytes / (double) window);
         attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
         attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
         cfg.attrs = attr; cfg.numAttrs = 1;

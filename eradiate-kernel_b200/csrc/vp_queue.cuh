@@ -421,21 +421,22 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             /* ================================ STEP ================================ */
             /* A warp keeps its batch for several steps while most of its lanes stay in this phase (null
                collisions come in runs): the pop / push cost is paid once per run, not once per step. */
+            /* The lanes that stay keep their path in REGISTERS from one step to the next: the slot is read once when the
+               batch is taken and written once when a lane leaves the phase (or the warp gives the batch back) -- not
+               once per step (slot ids within a batch are arbitrary, so every slot access is a ~3-way bank conflict). */
             bool mine = has;
-            for (int it = 1;; ++it) {
-            cnt.medium_steps = 0; cnt.n_null = 0;
             uint32_t fl = mine ? s.flags : (uint32_t) Q_DEAD;
             int st = (int) (fl & QF_STATE);
             const int mode = (int) ((fl & QF_MODE) >> QF_MODE_SHIFT);
-            const bool main_mode = mode == QM_MAIN, nee = mode == QM_NEE;
+            const bool main_mode = mode == QM_MAIN, nee = mode == QM_NEE;   /* a path does not change mode inside STEP */
             Pcg32 rng;
             Ray<F> r;
             int med = -1;
-            F w = 0, hit_t = INF, remaining = 0;
+            F w = 0, hit_t = INF;
             F w2 = 0;          /* volpathmis: p_over_f_uni of an emitter march */
-            MediumHit<F> mi;
-            mi.t = INF; mi.mint = 0; mi.p = mk3<F>(0, 0, 0); mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
-            r.o = mi.p; r.d = mi.p; r.d_rcp = mi.p; r.mint = 0; r.maxt = 0;
+            F total_dist = 0;  /* emitter march: distance covered */
+            uint32_t acc_steps = 0, acc_null = 0;
+            r.o = mk3<F>(0, 0, 0); r.d = r.o; r.d_rcp = r.o; r.mint = 0; r.maxt = 0;
             rng.state = 0; rng.inc = 1; rng.draws = 0;
             if (mine) {
                 ld_rng(s, rng);
@@ -444,7 +445,13 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 w = s.cur.w;
                 hit_t = s.cur.hit_t;
                 if (MIS && (nee || ENV)) w2 = s.w2;   /* main mode: p_over_f_nee, read where a path meets the environment */
+                if (nee) total_dist = s.total_dist;
             }
+            for (int it = 1;; ++it) {
+            cnt.medium_steps = 0; cnt.n_null = 0;
+            F remaining = 0;
+            MediumHit<F> mi;
+            mi.t = INF; mi.mint = 0; mi.p = mk3<F>(0, 0, 0); mi.sigma_s = 0; mi.sigma_n = 0; mi.sigma_t = 0; mi.combined = 0;
             bool go = mine;
             if (go) {
                 if (fl & QF_TOP_DONE) {
@@ -455,7 +462,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                                         : loop_top_rr(rng, w, s.eta, s.depth, rr_depth, max_depth);
                     if (!on) { st = Q_PATH_END; go = false; }
                 } else if (nee) {
-                    remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - s.total_dist;
+                    remaining = s.ds_dist * ((F) 1 - K<F>::ShadowEpsilon) - total_dist;
                     r.maxt = remaining;
                     if (!(remaining > 0)) { st = Q_MARCH_END; go = false; }
                 }
@@ -548,7 +555,6 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             } else if (MIS && go) {
                 /* sample_emitter of volpathmis (volpathmis.cpp:362-442): two weights along the march */
                 bool escaped = false, active_medium = false;
-                F total_dist = s.total_dist;
                 if (in_medium) {
                     if (spectral) { mis_update(w, ff_p, ff_f); mis_update(w2, ff_p, ff_f); }
                     if (mi.t > remaining && mi.valid()) total_dist = s.ds_dist;
@@ -568,7 +574,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 bool active_surface = !in_medium || escaped;
                 if (active_surface) total_dist += hit_t;
                 active_surface = active_surface && hit_t != INF && !active_medium;
-                r.maxt = remaining; s.total_dist = total_dist;
+                r.maxt = remaining;
                 if (active_surface) st = Q_MARCH_SURF;
                 else if (active_medium && (g.mis != 2 ? mis_w1(w2) != 0 : (w2 != 0 || w != 0))) st = Q_STEP;
                 else st = Q_MARCH_END;
@@ -609,7 +615,6 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             } else if (go) {
                 /* sample_emitter (volpath.cpp:285-365) / evaluate_direct_light (volpath.cpp:384-463) */
                 bool escaped = false, active_medium = false;
-                F total_dist = nee ? s.total_dist : (F) 0;
                 if (in_medium) {
                     if (spectral) w *= ratio;
                     if (nee) {
@@ -631,7 +636,7 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 bool active_surface = !in_medium || escaped;
                 if (nee && active_surface) total_dist += hit_t;
                 active_surface = active_surface && hit_t != INF && !active_medium;
-                if (nee) { r.maxt = remaining; s.total_dist = total_dist; }
+                if (nee) r.maxt = remaining;
                 /* a surface on the march (null.cpp:69-72 lets it through, anything else blocks it) and the
                    end of the march are rare: they run as their own phase, in full batches */
                 if (active_surface) st = Q_MARCH_SURF;
@@ -643,19 +648,23 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                         c.emitter_val = sv.emitters[g.environment].irradiance;
                 }
             }
-            if (mine) {
+            acc_steps += cnt.medium_steps; acc_null += cnt.n_null;
+            const bool staying = mine && st == Q_STEP;
+            const int stay = __popc(__ballot_sync(FULL, staying));
+            const bool give_back = stay < (int) out.q_stay_min || it >= (int) out.q_max_iter;
+            if (mine && (!staying || give_back)) {   /* this lane's path leaves the warp: back into its slot */
                 st_rng(s, rng);
-                s.c_steps += cnt.medium_steps; s.c_null += cnt.n_null;
+                s.c_steps += acc_steps; s.c_null += acc_null;
                 st3(s.cur.o, r.o); s.cur.mint = r.mint; s.cur.maxt = r.maxt;
                 s.cur.w = w;
                 if (MIS && (nee || ENV)) s.w2 = w2;
+                if (nee) s.total_dist = total_dist;
                 s.cur.hit_t = hit_t;
                 s.flags = (fl & ~QF_STATE) | (uint32_t) st;
                 state = st;
             }
-            mine = mine && st == Q_STEP;
-            const int stay = __popc(__ballot_sync(FULL, mine));
-            if (stay < (int) out.q_stay_min || it >= (int) out.q_max_iter) break;
+            mine = staying;
+            if (give_back) break;
             }
         } else if (phase == PH_SCATTER) {
             /* =============================== SCATTER ============================== */

@@ -20,6 +20,9 @@
 //
 // Built by oracle/Makefile.ref (needs the reference's headers, so only where /root/reference exists) into
 // oracle/_ref/plugins/volpath_b200.so, next to the reference's own plugins.
+#ifndef B2VP_DEFAULT_ALGORITHM
+#define B2VP_DEFAULT_ALGORITHM "volpath"
+#endif
 #include <algorithm>
 #include <array>
 #include <atomic>
@@ -469,7 +472,8 @@ public:
            render().) */
         m_moment = props.bool_("moment", false);
         /* algorithm: "volpath" (default) or "volpathmis" (src/integrators/volpathmis.cpp; use_spectral_mis as there) */
-        std::string algorithm = props.string("algorithm", "volpath");
+        /* B2VP_DEFAULT_ALGORITHM: the same source is also built as the drop-in `volpathmis.so` (oracle/Makefile.ref) */
+        std::string algorithm = props.string("algorithm", B2VP_DEFAULT_ALGORITHM);
         if (algorithm == "volpathmis") m_mis = props.bool_("use_spectral_mis", true) ? 1 : 2;
         else if (algorithm != "volpath") Throw("volpath_b200: algorithm must be \"volpath\" or \"volpathmis\"");
         /* math: "fast" (default in scalar_mono: the fp32 tolerance mode, B2VP_MATH_FAST) or "exact" (every fp32
@@ -478,8 +482,8 @@ public:
         if (math == "fast") m_math = B2VP_MATH_FAST;
         else if (math == "exact") m_math = B2VP_MATH_EXACT;
         else Throw("volpath_b200: math must be \"fast\" or \"exact\"");
-        if (m_math == B2VP_MATH_FAST && (std::is_same_v<scalar_t<Float>, double> || m_mis))
-            m_math = B2VP_MATH_EXACT;   /* no fast instance in double precision / for volpathmis */
+        if (m_math == B2VP_MATH_FAST && std::is_same_v<scalar_t<Float>, double>)
+            m_math = B2VP_MATH_EXACT;   /* no fast instance in double precision */
         /* majorant_grid: 0 (default) = the reference's global majorant; see B2vpRenderArgs::majorant_grid */
         m_majorant_grid = (uint32_t) props.int_("majorant_grid", 0);
         /* n_devices: render on this many GPUs (device, then the others in ascending order), one NCCL film reduce */

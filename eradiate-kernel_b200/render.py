@@ -48,6 +48,48 @@ class RenderResult:
             f.write(("Pf\n%u %u\n-1\n" % (w, h)).encode())
             f.write(img[::-1].tobytes())
 
+    def write_exr(self, path, component_format="float16", pixel_format="luminance"):
+        """film->develop() for file_format=openexr (the hdrfilm default, src/films/hdrfilm.cpp:251-343 ->
+        Bitmap::write_openexr, src/libcore/bitmap.cpp): a scan-line OpenEXR 2 file, channels in alphabetical order,
+        increasing y, data and display window = the crop window.  pixel_format "luminance" writes the one channel `Y`
+        (= Y / W, what mono variants develop), "xyzaw" the raw accumulation buffer (channels A, W, X, Y, Z) as
+        `develop(raw=true)` would keep it.  component_format float16 (hdrfilm's default) | float32.  Written without
+        compression (the reference's default is PIZ; compression is a container detail, the pixels are the same) by
+        this file alone: no OpenEXR library is needed."""
+        import struct
+        ctype, dtype = {"float16": (1, "<f2"), "float32": (2, "<f4")}[component_format]
+        if pixel_format == "luminance":
+            planes = {"Y": self.bitmap()}
+        elif pixel_format == "xyzaw":
+            planes = {n: self.film[..., i] for i, n in enumerate("XYZAW")}
+        else:
+            raise ValueError("pixel_format must be 'luminance' or 'xyzaw'")
+        names = sorted(planes)
+        h, w = planes[names[0]].shape
+        rows = np.stack([np.ascontiguousarray(planes[n], dtype=dtype) for n in names], axis=1)   # (h, channels, w)
+
+        def attr(name, typ, payload):
+            return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(payload)) + payload
+        chlist = b"".join(n.encode() + b"\0" + struct.pack("<iB3xii", ctype, 0, 1, 1) for n in names) + b"\0"
+        box = struct.pack("<4i", 0, 0, w - 1, h - 1)
+        header = (struct.pack("<II", 20000630, 2)
+                  + attr("channels", "chlist", chlist)
+                  + attr("compression", "compression", b"\0")
+                  + attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box)
+                  + attr("lineOrder", "lineOrder", b"\0")
+                  + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0))
+                  + attr("screenWindowCenter", "v2f", struct.pack("<2f", 0.0, 0.0))
+                  + attr("screenWindowWidth", "float", struct.pack("<f", 1.0))
+                  + b"\0")
+        row_bytes = rows.shape[1] * w * rows.dtype.itemsize
+        first = len(header) + 8 * h
+        with open(path, "wb") as f:
+            f.write(header)
+            f.write(np.arange(h, dtype="<u8").__mul__(row_bytes + 8).__add__(first).tobytes())   # scan-line offset table
+            for y in range(h):
+                f.write(struct.pack("<ii", y, row_bytes))
+                f.write(rows[y].tobytes())
+
     @property
     def segments(self):
         return self.totals.n_medium_steps + self.totals.n_intersect
@@ -198,6 +240,41 @@ class DeviceScene:
         a.totals = C.pointer(tot)
         abi.check(abi.lib().b2vp_render_noalloc(self._h, C.byref(a), device_film))
         return tot
+
+
+def read_exr(path):
+    """Reads back what RenderResult.write_exr writes (scan lines, no compression, HALF / FLOAT channels):
+    {channel name: (h, w) array}.  For tests and for callers without an OpenEXR library."""
+    import struct
+    b = open(path, "rb").read()
+    magic, version = struct.unpack_from("<II", b, 0)
+    if magic != 20000630 or (version & 0xff) != 2 or version & 0x200:
+        raise ValueError("not a scan-line OpenEXR 2 file")
+    pos, attrs = 8, {}
+    while b[pos] != 0:
+        e = b.index(b"\0", pos); name = b[pos:e].decode(); pos = e + 1
+        e = b.index(b"\0", pos); typ = b[pos:e].decode(); pos = e + 1
+        (n,) = struct.unpack_from("<i", b, pos); pos += 4
+        attrs[name] = (typ, b[pos:pos + n]); pos += n
+    pos += 1
+    if attrs["compression"][1] != b"\0":
+        raise ValueError("compressed OpenEXR files are not supported by this reader")
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    ch, c, p = [], attrs["channels"][1], 0
+    while c[p] != 0:
+        e = c.index(b"\0", p); name = c[p:e].decode(); p = e + 1
+        (ctype,) = struct.unpack_from("<i", c, p); p += 16
+        ch.append((name, {1: "<f2", 2: "<f4", 0: "<u4"}[ctype]))
+    offsets = np.frombuffer(b, dtype="<u8", count=h, offset=pos)
+    out = {name: np.zeros((h, w), dtype=dt) for name, dt in ch}
+    for off in offsets:
+        y, size = struct.unpack_from("<ii", b, int(off))
+        q = int(off) + 8
+        for name, dt in ch:
+            out[name][y - y0] = np.frombuffer(b, dtype=dt, count=w, offset=q)
+            q += w * np.dtype(dt).itemsize
+    return out
 
 
 def shard_streams(count, n, index):

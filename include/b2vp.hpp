@@ -26,8 +26,12 @@
 #include <algorithm>
 #include <array>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <fstream>
 #include <limits>
+#include <map>
+#include <sstream>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -160,6 +164,9 @@ struct GridVolume {
     std::string filter_type = "trilinear", wrap_mode = "clamp";
     double max_value = -1;   /* < 0: the maximum of the data (grid3d.cpp:157-160) */
 };
+/* A version-3 float32 `.vol` file (src/textures/volume_data.h:42-102) as a GridVolume.  `bbox` (if given) receives the
+   file's bounding box: min xyz, max xyz (what `use_grid_bbox` applies, grid3d.cpp:152-155). */
+inline GridVolume read_vol(const std::string &path, std::array<float, 6> *bbox = nullptr);
 /* src/media/homogeneous.cpp:21-54 / heterogeneous.cpp:21-54, src/librender/medium.cpp:12-30 */
 struct Homogeneous { double sigma_t = 1.0, albedo = 0.75, scale = 1.0; bool has_spectral_extinction = true, sample_emitters = true; };
 struct Heterogeneous { double scale = 1.0; bool has_spectral_extinction = true, sample_emitters = true; };
@@ -186,6 +193,22 @@ struct Distant {
 };
 /* src/sensors/radiancemeter.cpp:61-104 */
 struct RadianceMeter { std::array<double, 3> origin{ 0, 0, 0 }, direction{ 0, 0, 1 }; int medium = -1; };
+/* src/shapes/sphere.cpp:95-160: `center`, `radius`, `flip_normals` (+ a to_world given to add_sphere) */
+struct Sphere { std::array<double, 3> center{ 0, 0, 0 }; double radius = 1.0; bool flip_normals = false; };
+/* src/sensors/mdistant.cpp:146-207: one direction per film column (film size [n, 1]), optional target point */
+struct MDistant {
+    std::vector<std::array<double, 3>> directions;
+    bool has_target = false; std::array<double, 3> target{ 0, 0, 0 };
+    int medium = -1;
+};
+/* src/sensors/mradiancemeter.cpp:75-131: one (origin, direction) pair per film column */
+struct MRadianceMeter { std::vector<std::array<double, 3>> origins, directions; int medium = -1; };
+/* A triangle mesh as the reference's loaders leave it in memory (src/librender/mesh.cpp): object-space positions,
+   optional vertex normals and texture coordinates */
+struct MeshData { std::vector<float> positions, normals, texcoords; std::vector<uint32_t> faces; };
+/* Wavefront OBJ as src/shapes/obj.cpp:140-325 reads it: v / vn / vt / f, one output vertex per distinct (v, vt, vn)
+   index triple in order of first use, polygons as triangle fans, v flipped to 1 - v unless flip_tex_coords = false */
+inline MeshData load_obj(const std::string &path, bool flip_tex_coords = true);
 /* src/integrators/volpath.cpp:19-25, src/librender/integrator.cpp:23-39,302-315 */
 struct Volpath {
     int max_depth = -1, rr_depth = 5; bool hide_emitters = false; uint32_t block_size = 0, samples_per_pass = 0xffffffffu;
@@ -204,6 +227,7 @@ struct Scene {
     std::vector<float> vpos, vnrm, vuv; std::vector<uint32_t> faces;
     std::vector<std::vector<float>> grids;
     std::vector<std::vector<double>> phase_values;   /* tabphase tables, parallel to `phases` */
+    std::vector<double> sensor_transforms;           /* mdistant / mradiancemeter: 16 doubles per film column */
     int width() const { return desc.sensor.crop_size[0]; }
     int height() const { return desc.sensor.crop_size[1]; }
 };
@@ -309,6 +333,62 @@ public:
         sc_->shapes.push_back(s);
         return (int) sc_->shapes.size() - 1;
     }
+    /* A loaded mesh (load_obj, or the caller's own loader) under `to_world`: positions by the fmadd chain of
+       Transform::transform_affine in Float, normals by the inverse transpose and renormalised, both rounded to
+       float32 like the reference's mesh buffers (obj.cpp:172-190) */
+    int add_mesh(const MeshData &m, const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1) {
+        const Mat4<F> tw = prop_xf(to_world_);
+        std::vector<float> p(m.positions.size()), n(m.normals.size());
+        for (size_t v = 0; v + 2 < m.positions.size(); v += 3) {
+            Vec3<F> q = tw.point({ (F) m.positions[v], (F) m.positions[v + 1], (F) m.positions[v + 2] });
+            for (int k = 0; k < 3; ++k) p[v + k] = (float) q[k];
+        }
+        for (size_t v = 0; v + 2 < m.normals.size(); v += 3) {
+            Vec3<F> q = normalize(tw.normal({ (F) m.normals[v], (F) m.normals[v + 1], (F) m.normals[v + 2] }));
+            for (int k = 0; k < 3; ++k) n[v + k] = (float) q[k];
+        }
+        return add_mesh(p, m.faces, bsdf, interior, exterior, m.normals.empty() ? nullptr : &n,
+                        m.texcoords.empty() ? nullptr : &m.texcoords);
+    }
+    /* src/shapes/sphere.cpp:95-160.  to_world * translate(center) * scale(radius) must be a similarity (rotation,
+       uniform scale, translation): the reference takes the radius from a polar decomposition and warns otherwise;
+       here anything else is refused */
+    int add_sphere(const Sphere &sp, const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1) {
+        const Vec3<F> c0 = prop3(sp.center);
+        const F r0 = prop(sp.radius);
+        Mat4<F> m = prop_xf(to_world_) * Mat4<F>::translate(c0[0], c0[1], c0[2]) * Mat4<F>::scale(r0, r0, r0);
+        Vec3<F> col[3];
+        for (int c = 0; c < 3; ++c) col[c] = { m(0, c), m(1, c), m(2, c) };
+        const bool diagonal = m(0, 1) == 0 && m(0, 2) == 0 && m(1, 0) == 0 && m(1, 2) == 0 && m(2, 0) == 0 && m(2, 1) == 0;
+        F radius = diagonal ? m(0, 0) : std::sqrt(dot(col[0], col[0]));
+        const F tol = (F) 1e-4 * std::fabs(radius);
+        for (int c = 0; c < 3; ++c) {
+            if (std::fabs(std::sqrt(dot(col[c], col[c])) - std::fabs(radius)) > tol ||
+                std::fabs(dot(col[c], col[(c + 1) % 3])) > tol * std::fabs(radius))
+                throw Error(B2VP_ERR_UNSUPPORTED, "sphere: 'to_world' transform shouldn't contain any scale along individual axes");
+        }
+        const Vec3<F> cr = cross(col[0], col[1]);
+        if (!diagonal && dot(cr, col[2]) < 0) radius = -radius;   /* a reflection: det(Q) > 0 puts the sign into the scale */
+        bool flip = sp.flip_normals;
+        if (radius <= 0) { radius = std::fabs(radius); flip = !flip; }
+        if (radius == 0) throw Error(B2VP_ERR_INVALID, "sphere: radius must be non-zero");
+        B2vpShape s{};
+        s.type = B2VP_SHAPE_SPHERE; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
+        Mat4<F> tw;   /* rotation * radius + centre */
+        const F sign = (diagonal ? m(0, 0) : (dot(cr, col[2]) < 0 ? (F) -1 : (F) 1)) < 0 ? (F) -1 : (F) 1;
+        for (int c = 0; c < 3; ++c)
+            for (int r = 0; r < 3; ++r) tw(r, c) = diagonal ? (r == c ? radius : (F) 0) : sign * col[c][r];
+        const Vec3<F> center = { m(0, 3), m(1, 3), m(2, 3) };
+        for (int k = 0; k < 3; ++k) { tw(k, 3) = center[k]; s.center[k] = (double) center[k]; }
+        s.radius = (double) radius; s.flip_normals = flip ? 1 : 0;
+        const F pi = (F) 3.14159265358979323846;
+        s.inv_surface_area = (double) ((F) 1 / ((F) 4 * pi * radius * radius));
+        s.to_world = tw.pod(); s.to_object = tw.inverse().pod();
+        expand({ center[0] - radius, center[1] - radius, center[2] - radius });
+        expand({ center[0] + radius, center[1] + radius, center[2] + radius });
+        sc_->shapes.push_back(s);
+        return (int) sc_->shapes.size() - 1;
+    }
     /* src/shapes/cube.cpp:54-116: 24 vertices, 12 triangles, face normals and texcoords; transformed in f32 */
     int add_cube(const Mat4<F> &to_world, int bsdf, int interior = -1, int exterior = -1) {
         static const float V[24][3] = { { 1, -1, -1 }, { 1, -1, 1 }, { -1, -1, 1 }, { -1, -1, -1 }, { 1, 1, -1 }, { -1, 1, -1 },
@@ -377,6 +457,46 @@ public:
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
+    /* src/sensors/mdistant.cpp:146-207: a look-at matrix per direction, ScalarFloat matrices of the plugin's own */
+    void set_sensor(const MDistant &sn, const IndependentSampler &sampler) {
+        const int n = (int) sn.directions.size();
+        if (n == 0) throw Error(B2VP_ERR_INVALID, "mdistant: no directions");
+        B2vpSensor o = base_sensor(HdrFilm{ n, 1 }, sampler, sn.medium);
+        o.type = B2VP_SENSOR_MDISTANT; o.needs_aperture_sample = 1;
+        o.target_type = sn.has_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
+        for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.target[k]);
+        o.origin_type = B2VP_ORIGIN_BSPHERE;
+        sc_->sensor_transforms.clear();
+        for (const auto &dir : sn.directions) {
+            const Vec3<F> d = prop3(dir);   /* std::stof values widened; not normalised by the plugin */
+            Vec3<F> tmp, up;
+            coordinate_system(d, tmp, up);
+            const B2vpMat4 t = Mat4<F>::look_at({ 0, 0, 0 }, d, up).pod();
+            sc_->sensor_transforms.insert(sc_->sensor_transforms.end(), t.m, t.m + 16);
+        }
+        o.n_transforms = n;
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
+    /* src/sensors/mradiancemeter.cpp:75-131 */
+    void set_sensor(const MRadianceMeter &sn, const IndependentSampler &sampler) {
+        const int n = (int) sn.directions.size();
+        if (n == 0 || sn.origins.size() != sn.directions.size())
+            throw Error(B2VP_ERR_INVALID, "Invalid specification! Number of parameters for origins and directions are not equal.");
+        B2vpSensor o = base_sensor(HdrFilm{ n, 1 }, sampler, sn.medium);
+        o.type = B2VP_SENSOR_MRADIANCEMETER; o.needs_aperture_sample = 0;
+        sc_->sensor_transforms.clear();
+        for (int i = 0; i < n; ++i) {
+            const Vec3<F> org = prop3(sn.origins[i]), d = prop3(sn.directions[i]);
+            Vec3<F> up, tmp;
+            coordinate_system(d, up, tmp);
+            const B2vpMat4 t = Mat4<F>::look_at(org, { org[0] + d[0], org[1] + d[1], org[2] + d[2] }, up).pod();
+            sc_->sensor_transforms.insert(sc_->sensor_transforms.end(), t.m, t.m + 16);
+        }
+        o.n_transforms = n;
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
     void set_integrator(const Volpath &v) {
         if (v.max_depth < -1) throw Error(B2VP_ERR_INVALID, "\"max_depth\" must be set to -1 (infinite) or a value >= 0");
         if (v.rr_depth <= 0) throw Error(B2VP_ERR_INVALID, "\"rr_depth\" must be set to a value greater than zero!");
@@ -406,6 +526,7 @@ public:
             }
         d.n_phases = (uint32_t) s.phases.size(); d.phases = s.phases.data();
         d.n_emitters = (uint32_t) s.emitters.size(); d.emitters = s.emitters.data();
+        if (d.sensor.n_transforms) d.sensor.transforms = s.sensor_transforms.data();
         d.n_vertices = (uint32_t) (s.vpos.size() / 3); d.n_faces = (uint32_t) (s.faces.size() / 3);
         if (d.n_vertices) {
             d.vertex_positions = s.vpos.data(); d.vertex_normals = s.vnrm.data();
@@ -479,6 +600,65 @@ struct Film {
     }
     /* HDRFilm::bitmap for pixel_format=luminance: Y / W (hdrfilm.cpp:251-321) */
     double luminance(int x, int y) const { double w = at(x, y, 4); return w > 0 ? at(x, y, 1) / w : 0.0; }
+    /* film->develop() for file_format=pfm, pixel_format=luminance (Bitmap::write_pfm, src/libcore/bitmap.cpp:2206-2230):
+       `Pf`, size, `-1` (little endian), scan lines bottom to top */
+    void write_pfm(const std::string &path) const {
+        std::ofstream f(path, std::ios::binary);
+        if (!f) throw Error(B2VP_ERR_INVALID, "cannot write " + path);
+        f << "Pf\n" << width << " " << height << "\n-1\n";
+        std::vector<float> row((size_t) width);
+        for (int y = height - 1; y >= 0; --y) {
+            for (int x = 0; x < width; ++x) row[(size_t) x] = (float) luminance(x, y);
+            f.write(reinterpret_cast<const char *>(row.data()), (std::streamsize) (row.size() * sizeof(float)));
+        }
+    }
+    /* film->develop() for file_format=openexr, pixel_format=luminance, component_format=float32 (hdrfilm.cpp:251-343):
+       a scan-line OpenEXR 2 file with the one channel `Y`, uncompressed, written without the OpenEXR library */
+    void write_exr(const std::string &path) const {
+        std::string h;
+        auto put32 = [&h](int32_t v) { h.append(reinterpret_cast<const char *>(&v), 4); };
+        auto putf = [&h](float v) { h.append(reinterpret_cast<const char *>(&v), 4); };
+        auto attr = [&](const char *name, const char *type, const std::string &payload) {
+            h.append(name); h.push_back('\0'); h.append(type); h.push_back('\0');
+            put32((int32_t) payload.size()); h.append(payload);
+        };
+        put32(20000630); put32(2);
+        { std::string c("Y"); c.push_back('\0'); int32_t v[4] = { 2 /* FLOAT */, 0, 1, 1 };
+          c.append(reinterpret_cast<const char *>(v), 16); c.push_back('\0'); attr("channels", "chlist", c); }
+        attr("compression", "compression", std::string(1, '\0'));
+        { int32_t b[4] = { 0, 0, width - 1, height - 1 }; std::string w(reinterpret_cast<const char *>(b), 16);
+          attr("dataWindow", "box2i", w); attr("displayWindow", "box2i", w); }
+        attr("lineOrder", "lineOrder", std::string(1, '\0'));
+        { std::string one; float v = 1.0f; one.append(reinterpret_cast<const char *>(&v), 4);
+          attr("pixelAspectRatio", "float", one);
+          std::string z(8, '\0'); attr("screenWindowCenter", "v2f", z);
+          attr("screenWindowWidth", "float", one); }
+        (void) putf;
+        h.push_back('\0');
+        std::ofstream f(path, std::ios::binary);
+        if (!f) throw Error(B2VP_ERR_INVALID, "cannot write " + path);
+        f.write(h.data(), (std::streamsize) h.size());
+        const uint64_t row_bytes = (uint64_t) width * 4, first = h.size() + 8ull * (uint64_t) height;
+        for (int y = 0; y < height; ++y) { uint64_t o = first + (uint64_t) y * (row_bytes + 8); f.write(reinterpret_cast<const char *>(&o), 8); }
+        std::vector<float> row((size_t) width);
+        for (int y = 0; y < height; ++y) {
+            int32_t head[2] = { y, (int32_t) row_bytes };
+            f.write(reinterpret_cast<const char *>(head), 8);
+            for (int x = 0; x < width; ++x) row[(size_t) x] = (float) luminance(x, y);
+            f.write(reinterpret_cast<const char *>(row.data()), (std::streamsize) row_bytes);
+        }
+    }
+};
+
+/* What Integrator::render is given besides the scene: the stream range, and the knobs of B2vpRenderArgs that the
+   reference reads from integrator properties (`timeout`) or has no counterpart for (math mode, devices, majorant grid) */
+struct RenderOptions {
+    int seed_mode = B2VP_SEED_WAVEFRONT;
+    uint64_t first_stream = 0, n_streams = 0;
+    int math = B2VP_MATH_EXACT;        /* B2VP_MATH_FAST: the fp32 tolerance mode */
+    uint32_t majorant_grid = 0;        /* opt-in local majorants (statistically, not per path, the reference's estimator) */
+    double timeout_s = 0;              /* integrator.h:143-146: <= 0 = none */
+    std::vector<int32_t> devices;      /* empty: the scene's device; else devices[0] must be it (multi-GPU render) */
 };
 
 /* A scene resident on one CUDA device: b2vp_scene_create .. b2vp_scene_destroy. */
@@ -498,6 +678,20 @@ public:
     }
     /* Integrator::render: all streams of the seeding mode, or the range [first, first + n) */
     Film render(int seed_mode = B2VP_SEED_WAVEFRONT, uint64_t first_stream = 0, uint64_t n_streams = 0) {
+        RenderOptions o;
+        o.seed_mode = seed_mode; o.first_stream = first_stream; o.n_streams = n_streams;
+        return render(o);
+    }
+    /* kd-tree statistics of the reference's log, here the BVH's; and which kernel instance the last render launched */
+    B2vpSceneInfo info() const {
+        B2vpSceneInfo i{};
+        i.abi_version = B2VP_ABI_VERSION; i.struct_size = (uint32_t) sizeof(i);
+        check(b2vp_scene_info(h_, &i));
+        return i;
+    }
+    Film render(const RenderOptions &opt) {
+        const int seed_mode = opt.seed_mode;
+        const uint64_t first_stream = opt.first_stream, n_streams = opt.n_streams;
         Film f;
         f.width = scene_->width(); f.height = scene_->height(); f.precision = scene_->desc.precision;
         f.channels = scene_->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS;
@@ -509,6 +703,8 @@ public:
         a.abi_version = B2VP_ABI_VERSION; a.struct_size = (uint32_t) sizeof(a);
         a.precision = f.precision; a.seed_mode = seed_mode; a.device = device_;
         a.first_stream = first_stream; a.n_streams = n_streams; a.clear_film = 1; a.totals = &f.totals;
+        a.math_mode = opt.math; a.majorant_grid = opt.majorant_grid; a.timeout_s = opt.timeout_s;
+        if (!opt.devices.empty()) { a.devices = opt.devices.data(); a.n_devices = (uint32_t) opt.devices.size(); }
         check(b2vp_render(h_, &a, buf));
         return f;
     }
@@ -518,5 +714,85 @@ private:
     int device_ = 0;
     b2vp_scene_t *h_ = nullptr;
 };
+
+inline GridVolume read_vol(const std::string &path, std::array<float, 6> *bbox) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw Error(B2VP_ERR_INVALID, path + ": file does not exist!");
+    char head[48];
+    f.read(head, 48);
+    if (!f || std::memcmp(head, "VOL", 3) != 0 || head[3] != 3) throw Error(B2VP_ERR_INVALID, path + ": not a version-3 VOL file");
+    int32_t v[5];
+    std::memcpy(v, head + 4, 20);
+    if (v[0] != 1) throw Error(B2VP_ERR_UNSUPPORTED, path + ": only float32 volumes are supported");
+    GridVolume g;
+    g.nx = v[1]; g.ny = v[2]; g.nz = v[3]; g.channels = v[4];
+    if ((int64_t) g.nx * g.ny * g.nz < 8)
+        throw Error(B2VP_ERR_INVALID, path + ": invalid grid dimensions (must have at least one value at each corner)");
+    if (bbox) std::memcpy(bbox->data(), head + 24, 24);
+    g.data.resize((size_t) g.nx * g.ny * g.nz * g.channels);
+    f.read(reinterpret_cast<char *>(g.data.data()), (std::streamsize) (g.data.size() * sizeof(float)));
+    if (!f) throw Error(B2VP_ERR_INVALID, path + ": file is truncated");
+    return g;
+}
+
+inline MeshData load_obj(const std::string &path, bool flip_tex_coords) {
+    std::ifstream f(path);
+    if (!f) throw Error(B2VP_ERR_INVALID, path + ": file does not exist!");
+    std::vector<std::array<float, 3>> vs, vns;
+    std::vector<std::array<float, 2>> vts;
+    std::map<std::array<int, 3>, uint32_t> ids;
+    std::vector<std::array<int, 3>> order;
+    MeshData m;
+    std::string line, tok;
+    while (std::getline(f, line)) {
+        std::istringstream in(line);
+        if (!(in >> tok)) continue;
+        if (tok == "v" || tok == "vn") {
+            std::string a, b, c;
+            in >> a >> b >> c;
+            (tok == "v" ? vs : vns).push_back({ std::stof(a), std::stof(b), std::stof(c) });   /* the reference parses with stof */
+        } else if (tok == "vt") {
+            std::string a, b;
+            in >> a >> b;
+            const float u = std::stof(a), v = std::stof(b);
+            vts.push_back({ u, flip_tex_coords ? 1.0f - v : v });
+        } else if (tok == "f") {
+            std::vector<uint32_t> corner;
+            std::string item;
+            while (in >> item) {
+                std::array<int, 3> key{ 0, 0, 0 };
+                size_t p0 = 0;
+                for (int k = 0; k < 3 && p0 <= item.size(); ++k) {
+                    size_t p1 = item.find('/', p0);
+                    std::string part = item.substr(p0, p1 == std::string::npos ? std::string::npos : p1 - p0);
+                    if (!part.empty()) key[k] = std::stoi(part);
+                    if (p1 == std::string::npos) break;
+                    p0 = p1 + 1;
+                }
+                if (key[0] < 1 || key[0] > (int) vs.size())
+                    throw Error(B2VP_ERR_INVALID, "Error while loading OBJ file \"" + path + "\": reference to invalid vertex " + std::to_string(key[0]) + "!");
+                auto it = ids.find(key);
+                if (it == ids.end()) { it = ids.emplace(key, (uint32_t) order.size()).first; order.push_back(key); }
+                corner.push_back(it->second);
+            }
+            for (size_t k = 1; k + 1 < corner.size(); ++k) { m.faces.push_back(corner[0]); m.faces.push_back(corner[k]); m.faces.push_back(corner[k + 1]); }
+        }
+    }
+    for (const auto &k : order) {
+        const auto &p = vs[(size_t) k[0] - 1];
+        m.positions.insert(m.positions.end(), p.begin(), p.end());
+        if (!vns.empty()) {
+            std::array<float, 3> n{ 0, 0, 0 };
+            if (k[2] >= 1 && k[2] <= (int) vns.size()) n = vns[(size_t) k[2] - 1];
+            m.normals.insert(m.normals.end(), n.begin(), n.end());
+        }
+        if (!vts.empty()) {
+            std::array<float, 2> t{ 0, 0 };
+            if (k[1] >= 1 && k[1] <= (int) vts.size()) t = vts[(size_t) k[1] - 1];
+            m.texcoords.insert(m.texcoords.end(), t.begin(), t.end());
+        }
+    }
+    return m;
+}
 
 } // namespace b2vp

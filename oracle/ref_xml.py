@@ -328,7 +328,9 @@ def with_plugin(scene, seeding="scalar", type_name="volpath_b200", **props):
     d = dict(scene)
     for k, v in scene.items():
         if isinstance(v, dict) and v.get("type") in ("volpath", "volpathmis"):
-            d[k] = dict(v, type=type_name, seeding=seeding, algorithm=v["type"], **props)
+            # under the integrator's own name (the drop-in .so of that name) the algorithm is the plugin's default
+            alg = {} if type_name == v["type"] else {"algorithm": v["type"]}
+            d[k] = dict(v, type=type_name, seeding=seeding, **alg, **props)
         elif isinstance(v, dict) and v.get("type") == "moment":   # moment around a volpath -> the plugin's own `moment`
             inner = [c for c in v.values() if isinstance(c, dict)][0]
             outer = {kk: vv for kk, vv in v.items() if not isinstance(vv, dict) and kk != "type"}

@@ -41,6 +41,43 @@ template <typename F> std::unique_ptr<b2vp::Scene> scene_c2(uint32_t spp, int wi
     return sb.finish();
 }
 
+/* A scene through the loaders and plugins the builder gained in round 2: a `.vol` grid, an OBJ mesh under a
+   transform, an analytic sphere, and an mdistant / mradiancemeter sensor.  tests/test_cpp_host.py builds the same
+   scene with the Python host (`load_dict`) and compares the films. */
+template <typename F> std::unique_ptr<b2vp::Scene> scene_ext(const std::string &dir, const std::string &sensor, uint32_t spp) {
+    using M = b2vp::Mat4<F>;
+    b2vp::SceneBuilder<F> sb;
+    std::array<float, 6> bbox;
+    b2vp::GridVolume g = b2vp::read_vol(dir + "/col.vol", &bbox);
+    if (g.nx != 1 || g.ny != 1 || g.nz != 64 || bbox[5] != 1.0f) throw b2vp::Error(B2VP_ERR_INVALID, "unexpected col.vol");
+    M box = M::translate(-10, -10, 0) * M::scale(20, 20, 1);
+    int atm = sb.add_medium(b2vp::Heterogeneous{ 4.0 }, g, box, 1.0, b2vp::Phase::rayleigh());
+    sb.add_cube(M::translate(0, 0, (F) 0.45) * M::scale(10, 10, (F) 0.55), sb.add_bsdf(b2vp::Null{}), atm);
+    sb.add_rectangle(M::scale(10, 10, 1), sb.add_bsdf(b2vp::Rpv{ 0.1, 0.7, -0.1 }));
+    sb.add_sphere(b2vp::Sphere{ { 0.5, -0.25, 0.5 }, 0.25 }, M(), sb.add_bsdf(b2vp::Diffuse{ 0.75 }));
+    sb.add_mesh(b2vp::load_obj(dir + "/roof.obj"), M::translate((F) 0.25, (F) -0.5, (F) 0.125) * M::scale(2, (F) 1.5, 1),
+                sb.add_bsdf(b2vp::Diffuse{ 0.75 }));
+    sb.add_emitter(b2vp::Directional{ { 0.5, 0, -0.8660254037844386 }, 1.0 });
+    const int n = 8;
+    if (sensor == "mdistant") {
+        b2vp::MDistant sn;
+        for (int i = 0; i < n; ++i) {
+            const double th = (i + 0.5) / n * 3.14159265358979323846;
+            sn.directions.push_back({ -std::cos(th), 0.0, -std::sin(th) });
+        }
+        sn.has_target = true;
+        sb.set_sensor(sn, b2vp::IndependentSampler{ spp, 0 });
+    } else {
+        b2vp::MRadianceMeter sn;
+        for (int i = 0; i < n; ++i) {
+            sn.origins.push_back({ -1.0 + 0.25 * i, 0.125 * i - 0.5, 2.0 });
+            sn.directions.push_back({ 0.0625 * i, -0.03125 * i, -1.0 });
+        }
+        sb.set_sensor(sn, b2vp::IndependentSampler{ spp, 0 });
+    }
+    return sb.finish();
+}
+
 static b2vp::Film oracle_render(const b2vp::Scene &s, int seed_mode = B2VP_SEED_WAVEFRONT) {
     b2vp::Film f;
     f.width = s.width(); f.height = s.height(); f.precision = s.desc.precision;
@@ -104,7 +141,45 @@ int main(int argc, char **argv) {
         std::fclose(out);
         return 0;
     }
+    if (mode == "ext") {
+        /* test_host ext <dir> <f32|f64> <mdistant|mradiancemeter> <out.bin>: oracle film of scene_ext, plus
+           <dir>/film.pfm and <dir>/film.exr developed by the C++ host */
+        const std::string dir = argv[2], sensor = argv[4];
+        const bool f64 = std::string(argv[3]) == "f64";
+        auto s = f64 ? scene_ext<double>(dir, sensor, 64) : scene_ext<float>(dir, sensor, 64);
+        b2vp::Film f = oracle_render(*s);
+        FILE *out = std::fopen(argv[5], "wb");
+        if (!out) return 2;
+        if (f64) std::fwrite(f.f64.data(), sizeof(double), f.f64.size(), out);
+        else std::fwrite(f.f32.data(), sizeof(float), f.f32.size(), out);
+        std::fclose(out);
+        f.write_pfm(dir + "/film.pfm");
+        f.write_exr(dir + "/film.exr");
+        return 0;
+    }
     int bad = 0;
+    if (argc > 2) {   /* gpu <dir>: the round-2 plugins and loaders on the device, both sensors, both precisions */
+        const std::string dir = argv[2];
+        for (const char *sensor : { "mdistant", "mradiancemeter" }) {
+            { auto s = scene_ext<float>(dir, sensor, 256); b2vp::Film ref = oracle_render(*s); b2vp::DeviceScene dev(std::move(s));
+              bad += compare((std::string("ext ") + sensor + " f32").c_str(), dev.render(), ref); }
+            { auto s = scene_ext<double>(dir, sensor, 64); b2vp::Film ref = oracle_render(*s); b2vp::DeviceScene dev(std::move(s));
+              bad += compare((std::string("ext ") + sensor + " f64").c_str(), dev.render(), ref); }
+        }
+        /* render options: the tolerance mode stays within 1 % of the exact film mean; BVH info is filled */
+        auto s = scene_ext<float>(dir, "mdistant", 1024);
+        b2vp::DeviceScene dev(std::move(s));
+        b2vp::Film exact = dev.render();
+        b2vp::RenderOptions opt; opt.math = B2VP_MATH_FAST;
+        b2vp::Film fast = dev.render(opt);
+        double me = 0, mf = 0;
+        for (int x = 0; x < exact.width; ++x) { me += exact.luminance(x, 0); mf += fast.luminance(x, 0); }
+        const B2vpSceneInfo info = dev.info();
+        const bool ok = std::fabs(me - mf) < 0.01 * me && fast.totals.n_paths == exact.totals.n_paths && info.bvh_nodes > 0;
+        std::printf("render options: exact mean %.6f fast mean %.6f, last kernel '%s', %u BVH nodes -> %s\n", me / exact.width,
+                    mf / exact.width, info.last_kernel, (unsigned) info.bvh_nodes, ok ? "ok" : "MISMATCH");
+        bad += !ok;
+    }
     { auto s = scene_c1<float>(4096); b2vp::Film ref = oracle_render(*s); b2vp::DeviceScene dev(std::move(s)); bad += compare("C1 f32", dev.render(), ref); }
     { auto s = scene_c1<double>(2048); b2vp::Film ref = oracle_render(*s); b2vp::DeviceScene dev(std::move(s)); bad += compare("C1 f64", dev.render(), ref); }
     { auto s = scene_c2<float>(256, 16); b2vp::Film ref = oracle_render(*s); b2vp::DeviceScene dev(std::move(s)); bad += compare("C2 f32", dev.render(), ref); }

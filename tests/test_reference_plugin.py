@@ -113,6 +113,22 @@ def test_drop_in_by_name_and_resident_scene(pkg):
 
 
 @pytest.mark.gpu
+def test_drop_in_volpathmis_by_name(pkg):
+    """<integrator type="volpathmis"> untouched: the product's `volpathmis.so` (same source, `algorithm` defaulting to
+    volpathmis) renders the reference's volpathmis fixtures on the queue kernel; `use_spectral_mis` is honoured."""
+    ref_xml = ref_xml_or_skip()
+    if not os.path.exists(os.path.join(ref_xml.REF_DIR, "b200", "plugins", "volpathmis.so")):
+        pytest.skip("oracle/_ref/b200/plugins/volpathmis.so is not built")
+    names = [n for n in sorted(make_ref_golden.CASES) if "volpathmis" in n]
+    assert names
+    for name in names:
+        d, variant = make_ref_golden.scene_dict(name)
+        scene = ref_xml.with_plugin(d, type_name="volpathmis", math="exact")
+        film, _ = ref_xml.render(scene, variant, write_vol=pkg.scene.write_vol, plugin_root=True)
+        check_against_reference(name, film, REF[name], variant)
+
+
+@pytest.mark.gpu
 def test_plugin_timeout_and_modes(pkg):
     """The integrator's `timeout` property and the majorant-grid mode through the reference's own XML."""
     import scenes
