@@ -9,3 +9,10 @@ from .transform import Transform
 
 __all__ = ["abi", "B2vpError", "DeviceScene", "RenderResult", "render", "render_defaults", "shard_streams", "read_exr", "Scene", "load_dict", "read_vol", "write_vol",
            "Transform", "shard_range", "shard_interleaved", "reduce_film"]
+
+
+def ext():
+    """The pybind11 front end (`_b2vp`: load_dict / DeviceScene.render in C++ over include/b2vp.hpp), built by
+    __graft_entry__.build() next to libb2vp.so.  Imported on demand: the ctypes host needs no compiled module."""
+    import importlib
+    return importlib.import_module("._b2vp", __name__)

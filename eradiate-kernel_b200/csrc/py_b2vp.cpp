@@ -1,0 +1,347 @@
+/*
+ * py_b2vp.cpp -- pybind11 module `_b2vp`: `load_dict` and `render` in C++ over include/b2vp.hpp.
+ *
+ * The reference's Python front end is a pybind11 module: `mitsuba.core.xml.load_dict` turns nested dictionaries into
+ * plugin instances (src/libcore/python/xml_v.cpp:100-240) and `Integrator.render(scene, sensor)` releases the GIL,
+ * routes SIGINT to `Integrator::cancel` and calls the C++ render (src/librender/python/integrator_v.cpp:124-153).
+ * This module is the same pair for the B200 path: `load_dict` walks the dictionary in C++ and drives the
+ * `SceneBuilder` of b2vp.hpp (so it covers the plugin types that header covers; the ctypes host in scene.py covers
+ * the rest: ply / serialized meshes, blendphase, distantflux, irradiancemeter, crop windows), `DeviceScene.render`
+ * calls `b2vp_render` with the GIL released and Ctrl-C wired to `b2vp_cancel`.  Built by __graft_entry__.build()
+ * with g++ against the installed pybind11 3; no CUDA in this file.
+ */
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <atomic>
+#include <csignal>
+#include <functional>
+#include <map>
+
+#include "b2vp.hpp"
+
+namespace py = pybind11;
+using namespace pybind11::literals;
+
+namespace {
+
+[[noreturn]] void unsupported(const std::string &kind, const std::string &type) {
+    throw std::runtime_error(kind + " plugin \"" + type + "\" is not supported by the C++ host of the B200 volpath "
+                             "(include/b2vp.hpp); the ctypes host (load_dict of the package) may cover it");
+}
+
+std::string type_of(const py::dict &d) {
+    if (!d.contains("type")) throw std::runtime_error("load_dict: missing key 'type'");
+    return py::cast<std::string>(d["type"]);
+}
+template <typename T> T get(const py::dict &d, const char *key, T def) {
+    return d.contains(key) ? py::cast<T>(d[key]) : def;
+}
+std::array<double, 3> vec3(const py::handle &h) {
+    auto v = py::cast<std::vector<double>>(h);
+    if (v.size() != 3) throw std::runtime_error("load_dict: expected a 3-vector");
+    return { v[0], v[1], v[2] };
+}
+
+template <typename F> struct Loader {
+    b2vp::SceneBuilder<F> sb;
+    std::map<std::string, int> media;
+
+    /* a Transform of the package (attribute `matrix`) or anything numpy turns into a 4 x 4 array */
+    b2vp::Mat4<F> xf(const py::dict &d, const char *key = "to_world") {
+        b2vp::Mat4<F> m;
+        if (!d.contains(key)) return m;
+        py::object o = d[key];
+        if (py::hasattr(o, "matrix")) o = o.attr("matrix");
+        auto a = py::array_t<double, py::array::c_style | py::array::forcecast>::ensure(o);
+        if (!a || a.ndim() != 2 || a.shape(0) != 4 || a.shape(1) != 4) throw std::runtime_error("load_dict: to_world must be 4 x 4");
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m(r, c) = (F) a.at(r, c);
+        return m;
+    }
+    b2vp::Phase phase(const py::dict &d) {
+        const std::string t = type_of(d);
+        if (t == "isotropic") return b2vp::Phase::isotropic();
+        if (t == "rayleigh") return b2vp::Phase::rayleigh();
+        if (t == "hg") return b2vp::Phase::hg(get<double>(d, "g", 0.8));
+        if (t == "tabphase") return b2vp::Phase::tabulated(py::cast<std::vector<double>>(d["values"]));
+        unsupported("phase function", t);
+    }
+    b2vp::GridVolume grid(const py::dict &d) {
+        b2vp::GridVolume g;
+        if (d.contains("filename")) {
+            g = b2vp::read_vol(py::cast<std::string>(d["filename"]));
+        } else {   /* in-memory data[z, y, x(, c)] */
+            auto a = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(d["data"]);
+            if (!a || (a.ndim() != 3 && a.ndim() != 4)) throw std::runtime_error("gridvolume: data must be [z, y, x] or [z, y, x, c]");
+            g.nz = (int) a.shape(0); g.ny = (int) a.shape(1); g.nx = (int) a.shape(2); g.channels = a.ndim() == 4 ? (int) a.shape(3) : 1;
+            g.data.assign(a.data(), a.data() + a.size());
+        }
+        g.filter_type = get<std::string>(d, "filter_type", "trilinear");
+        g.wrap_mode = get<std::string>(d, "wrap_mode", "clamp");
+        if (d.contains("max_value")) g.max_value = py::cast<double>(d["max_value"]);
+        if (get<bool>(d, "use_grid_bbox", false) || get<bool>(d, "raw", false))
+            throw std::runtime_error("gridvolume: use_grid_bbox / raw are not supported by the C++ host");
+        return g;
+    }
+    void medium(const std::string &id, const py::dict &d) {
+        const std::string t = type_of(d);
+        if (!d.contains("phase")) throw std::runtime_error("medium \"" + id + "\": no phase function");
+        const b2vp::Phase ph = phase(py::cast<py::dict>(d["phase"]));
+        const bool spectral = get<bool>(d, "has_spectral_extinction", true), se = get<bool>(d, "sample_emitters", true);
+        const double scale = get<double>(d, "scale", 1.0);
+        if (t == "homogeneous") {
+            media[id] = sb.add_medium(b2vp::Homogeneous{ get<double>(d, "sigma_t", 1.0), get<double>(d, "albedo", 0.75), scale, spectral, se }, ph);
+        } else if (t == "heterogeneous") {
+            if (!py::isinstance<py::dict>(d["sigma_t"])) throw std::runtime_error("heterogeneous: sigma_t must be a gridvolume");
+            const py::dict st = py::cast<py::dict>(d["sigma_t"]);
+            if (type_of(st) != "gridvolume") unsupported("volume", type_of(st));
+            const b2vp::Heterogeneous h{ scale, spectral, se };
+            if (d.contains("albedo") && py::isinstance<py::dict>(d["albedo"])) {
+                const py::dict al = py::cast<py::dict>(d["albedo"]);
+                if (type_of(al) == "gridvolume")
+                    media[id] = sb.add_medium(h, grid(st), xf(st), grid(al), xf(al), ph);
+                else if (type_of(al) == "constvolume")
+                    media[id] = sb.add_medium(h, grid(st), xf(st), get<double>(al, "value", 1.0), ph);
+                else unsupported("volume", type_of(al));
+            } else {
+                media[id] = sb.add_medium(h, grid(st), xf(st), get<double>(d, "albedo", 0.75), ph);
+            }
+        } else unsupported("medium", t);
+    }
+    int medium_ref(const py::dict &d, const char *key) {
+        if (!d.contains(key)) return -1;
+        const py::dict r = py::cast<py::dict>(d[key]);
+        if (type_of(r) != "ref") throw std::runtime_error("load_dict: nested media are not supported by the C++ host; use {\"type\": \"ref\", \"id\": ...}");
+        const std::string id = py::cast<std::string>(r["id"]);
+        auto it = media.find(id);
+        if (it == media.end()) throw std::runtime_error("load_dict: reference to unknown medium \"" + id + "\"");
+        return it->second;
+    }
+    int bsdf(const py::dict &shape) {
+        if (!shape.contains("bsdf")) return sb.add_bsdf(b2vp::Diffuse{});   /* the reference's default BSDF */
+        const py::dict d = py::cast<py::dict>(shape["bsdf"]);
+        const std::string t = type_of(d);
+        if (t == "diffuse") return sb.add_bsdf(b2vp::Diffuse{ get<double>(d, "reflectance", 0.5) });
+        if (t == "null") return sb.add_bsdf(b2vp::Null{});
+        if (t == "rpv") return sb.add_bsdf(b2vp::Rpv{ get<double>(d, "rho_0", 0.1), get<double>(d, "k", 0.1), get<double>(d, "g", 0.0), get<double>(d, "rho_c", -1.0) });
+        if (t == "bilambertian") return sb.add_bsdf(b2vp::Bilambertian{ get<double>(d, "reflectance", 0.5), get<double>(d, "transmittance", 0.5) });
+        unsupported("BSDF", t);
+    }
+    bool shape(const py::dict &d) {
+        const std::string t = type_of(d);
+        if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj") return false;
+        const int b = bsdf(d), in = medium_ref(d, "interior"), ex = medium_ref(d, "exterior");
+        if (t == "cube") sb.add_cube(xf(d), b, in, ex);
+        else if (t == "rectangle") sb.add_rectangle(xf(d), b, in, ex);
+        else if (t == "sphere") {
+            b2vp::Sphere s;
+            if (d.contains("center")) s.center = vec3(d["center"]);
+            s.radius = get<double>(d, "radius", 1.0); s.flip_normals = get<bool>(d, "flip_normals", false);
+            sb.add_sphere(s, xf(d), b, in, ex);
+        } else {
+            if (get<bool>(d, "face_normals", false)) throw std::runtime_error("obj: face_normals is not supported by the C++ host");
+            sb.add_mesh(b2vp::load_obj(py::cast<std::string>(d["filename"]), get<bool>(d, "flip_tex_coords", true)), xf(d), b, in, ex);
+        }
+        return true;
+    }
+    void sensor(const py::dict &d) {
+        const std::string t = type_of(d);
+        b2vp::IndependentSampler smp;
+        if (d.contains("sampler")) {
+            const py::dict s = py::cast<py::dict>(d["sampler"]);
+            if (type_of(s) != "independent") unsupported("sampler", type_of(s));
+            smp.sample_count = get<uint32_t>(s, "sample_count", 4); smp.seed = get<uint64_t>(s, "seed", 0);
+        }
+        b2vp::HdrFilm film;
+        if (d.contains("film")) {
+            const py::dict f = py::cast<py::dict>(d["film"]);
+            if (type_of(f) != "hdrfilm") unsupported("film", type_of(f));
+            film.width = get<int>(f, "width", 768); film.height = get<int>(f, "height", 576);
+            if (f.contains("rfilter") && type_of(py::cast<py::dict>(f["rfilter"])) != "box")
+                unsupported("reconstruction filter", type_of(py::cast<py::dict>(f["rfilter"])));
+            if (f.contains("crop_width") || f.contains("crop_offset_x")) throw std::runtime_error("hdrfilm: crop windows are not supported by the C++ host");
+        }
+        const int med = medium_ref(d, "medium");
+        if (t == "distant") {
+            b2vp::Distant s;
+            if (d.contains("direction")) s.direction = vec3(d["direction"]);
+            if (d.contains("orientation")) { s.has_orientation = true; s.orientation = vec3(d["orientation"]); }
+            if (d.contains("ray_target")) {
+                if (py::isinstance<py::dict>(d["ray_target"])) throw std::runtime_error("distant: a shape as ray_target is not supported by the C++ host");
+                s.has_ray_target = true; s.ray_target = vec3(d["ray_target"]);
+            }
+            s.flip_directions = get<bool>(d, "flip_directions", false); s.medium = med;
+            sb.set_sensor(s, film, smp);
+        } else if (t == "radiancemeter") {
+            b2vp::RadianceMeter s;
+            s.origin = vec3(d["origin"]); s.direction = vec3(d["direction"]); s.medium = med;
+            sb.set_sensor(s, smp);
+        } else if (t == "mdistant" || t == "mradiancemeter") {
+            auto triples = [](const py::handle &h) {
+                auto v = py::cast<std::vector<double>>(h);
+                if (v.size() % 3) throw std::runtime_error("load_dict: directions / origins must come in triples");
+                std::vector<std::array<double, 3>> o;
+                for (size_t i = 0; i < v.size(); i += 3) o.push_back({ v[i], v[i + 1], v[i + 2] });
+                return o;
+            };
+            const auto dirs = triples(d["directions"]);
+            if (d.contains("film") && (film.width != (int) dirs.size() || film.height != 1))
+                throw std::runtime_error("Film size must be [sensor_count, 1]. Expected [" + std::to_string(dirs.size()) + ", 1], got [" +
+                                         std::to_string(film.width) + ", " + std::to_string(film.height) + "]");
+            if (t == "mdistant") {
+                b2vp::MDistant s;
+                s.directions = dirs; s.medium = med;
+                if (d.contains("target")) { s.has_target = true; s.target = vec3(d["target"]); }
+                sb.set_sensor(s, smp);
+            } else {
+                b2vp::MRadianceMeter s;
+                s.directions = dirs; s.origins = triples(d["origins"]); s.medium = med;
+                sb.set_sensor(s, smp);
+            }
+        } else unsupported("sensor", t);
+    }
+    void integrator(py::dict d) {
+        b2vp::Volpath v;
+        if (type_of(d) == "moment") {
+            v.moment = true;
+            for (auto kv : d)
+                if (py::isinstance<py::dict>(kv.second)) { d = py::cast<py::dict>(kv.second); break; }
+        }
+        const std::string t = type_of(d);
+        if (t == "volpathmis") v.mis = get<bool>(d, "use_spectral_mis", true) ? 1 : 2;
+        else if (t != "volpath") unsupported("integrator", t);
+        v.max_depth = get<int>(d, "max_depth", -1); v.rr_depth = get<int>(d, "rr_depth", 5);
+        v.hide_emitters = get<bool>(d, "hide_emitters", false);
+        v.block_size = get<uint32_t>(d, "block_size", 0);
+        if (d.contains("samples_per_pass")) v.samples_per_pass = py::cast<uint32_t>(d["samples_per_pass"]);
+        sb.set_integrator(v);
+    }
+
+    std::unique_ptr<b2vp::Scene> load(const py::dict &root) {
+        if (get<std::string>(root, "type", "scene") != "scene") throw std::runtime_error("load_dict: the top-level dictionary must be a scene");
+        /* children are visited in KEY order, as Properties::objects() hands them to the Scene constructor (a
+           std::map; src/libcore/properties.cpp): the order of shapes and emitters is part of the result (ties between
+           coincident hits go to the later shape, emitters are picked by index).  Media first: shapes and sensors
+           refer to them by id. */
+        std::map<std::string, py::dict> items;
+        for (auto kv : root)
+            if (py::isinstance<py::dict>(kv.second)) items.emplace(py::cast<std::string>(kv.first), py::cast<py::dict>(kv.second));
+        for (auto &kv : items) {
+            const std::string t = type_of(kv.second);
+            if (t == "homogeneous" || t == "heterogeneous") medium(kv.first, kv.second);
+        }
+        for (auto &kv : items) {
+            const py::dict &d = kv.second;
+            const std::string t = type_of(d);
+            if (t == "homogeneous" || t == "heterogeneous") continue;
+            if (shape(d)) continue;
+            if (t == "directional") {
+                b2vp::Directional e;
+                if (d.contains("to_world")) throw std::runtime_error("directional: give `direction` (to_world is not supported by the C++ host)");
+                if (d.contains("direction")) e.direction = vec3(d["direction"]);
+                e.irradiance = get<double>(d, "irradiance", 1.0);
+                sb.add_emitter(e);
+            } else if (t == "constant") sb.add_emitter(b2vp::Constant{ get<double>(d, "radiance", 1.0) });
+            else if (t == "volpath" || t == "volpathmis" || t == "moment") integrator(d);
+            else if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") sensor(d);
+            else unsupported("scene", t);
+        }
+        return sb.finish();
+    }
+};
+
+/* integrator_v.cpp:124-153: while a render runs, SIGINT cancels it instead of killing the interpreter */
+std::function<void()> g_sigint_handler;
+void (*g_sigint_prev)(int) = nullptr;
+
+struct PyScene {
+    std::unique_ptr<b2vp::Scene> scene;
+    std::string variant;
+};
+
+struct PyDeviceScene {
+    std::unique_ptr<b2vp::DeviceScene> dev;
+    int channels = B2VP_FILM_CHANNELS;
+    bool f64 = false;
+
+    py::tuple render(const std::string &seeding, const std::string &math, const std::vector<int32_t> &devices, double timeout,
+                     uint32_t majorant_grid, uint64_t first_stream, uint64_t n_streams) {
+        b2vp::RenderOptions opt;
+        if (seeding == "wavefront") opt.seed_mode = B2VP_SEED_WAVEFRONT;
+        else if (seeding == "scalar") opt.seed_mode = B2VP_SEED_SCALAR_BLOCKS;
+        else throw std::runtime_error("seeding must be \"wavefront\" or \"scalar\"");
+        if (math == "fast") opt.math = B2VP_MATH_FAST;
+        else if (math != "exact") throw std::runtime_error("math must be \"exact\" or \"fast\"");
+        opt.devices = devices; opt.timeout_s = timeout; opt.majorant_grid = majorant_grid;
+        opt.first_stream = first_stream; opt.n_streams = n_streams;
+        b2vp::Film film;
+        {
+            py::gil_scoped_release release;
+            b2vp::DeviceScene *d = dev.get();
+            g_sigint_handler = [d]() { d->cancel(); };
+            g_sigint_prev = std::signal(SIGINT, [](int) {
+                if (g_sigint_handler) { g_sigint_handler(); g_sigint_handler = std::function<void()>(); }
+            });
+            try {
+                film = dev->render(opt);
+            } catch (...) {
+                std::signal(SIGINT, g_sigint_prev);
+                g_sigint_handler = std::function<void()>();
+                throw;
+            }
+            std::signal(SIGINT, g_sigint_prev);
+            g_sigint_handler = std::function<void()>();
+        }
+        py::object arr;
+        const std::vector<py::ssize_t> shape{ film.height, film.width, film.channels };
+        if (film.precision == B2VP_PREC_F32) { py::array_t<float> a(shape); std::memcpy(a.mutable_data(), film.f32.data(), film.f32.size() * 4); arr = a; }
+        else { py::array_t<double> a(shape); std::memcpy(a.mutable_data(), film.f64.data(), film.f64.size() * 8); arr = a; }
+        const B2vpCounters &t = film.totals;
+        py::dict tot("n_paths"_a = t.n_paths, "n_rng_draws"_a = t.n_rng_draws, "n_medium_steps"_a = t.n_medium_steps,
+                     "n_null"_a = t.n_null, "n_real"_a = t.n_real, "n_intersect"_a = t.n_intersect, "n_surface"_a = t.n_surface,
+                     "n_invalid_samples"_a = t.n_invalid_samples, "gpu_ms"_a = t.gpu_ms, "n_launches"_a = t.n_launches,
+                     "stopped_early"_a = t.stopped_early);
+        return py::make_tuple(arr, tot);
+    }
+};
+
+} // namespace
+
+PYBIND11_MODULE(_b2vp, m) {
+    m.doc() = "pybind11 front end of the B200 volpath: load_dict / render over include/b2vp.hpp (libb2vp.so)";
+    m.attr("abi_version") = b2vp_abi_version();
+    py::register_exception<b2vp::Error>(m, "B2vpError", PyExc_RuntimeError);
+
+    py::class_<PyScene>(m, "Scene", "A loaded scene (B2vpSceneDesc + the arrays it points to)")
+        .def_property_readonly("variant", [](const PyScene &s) { return s.variant; })
+        .def_property_readonly("film_size", [](const PyScene &s) { return py::make_tuple(s.scene->width(), s.scene->height()); })
+        .def_property_readonly("desc_address", [](const PyScene &s) { return (uintptr_t) &s.scene->desc; },
+                               "address of the B2vpSceneDesc (for ctypes callers; valid while this object lives)");
+
+    m.def("load_dict", [](const py::dict &d, const std::string &variant) {
+        PyScene s;
+        s.variant = variant;
+        if (variant == "scalar_mono") s.scene = Loader<float>().load(d);
+        else if (variant == "scalar_mono_double") s.scene = Loader<double>().load(d);
+        else throw std::runtime_error("variant must be scalar_mono or scalar_mono_double");
+        return s;
+    }, "dict"_a, "variant"_a = "scalar_mono",
+    "mitsuba.core.xml.load_dict for the plugin types of include/b2vp.hpp (src/libcore/python/xml_v.cpp:100-240)");
+
+    py::class_<PyDeviceScene>(m, "DeviceScene", "A scene resident on a CUDA device (b2vp_scene_create .. b2vp_scene_destroy)")
+        .def(py::init([](PyScene &s, int device) {
+            if (!s.scene) throw std::runtime_error("this Scene was already moved onto a device");
+            PyDeviceScene d;
+            d.channels = s.scene->desc.integrator.moment ? B2VP_FILM_CHANNELS_MOMENT : B2VP_FILM_CHANNELS;
+            d.f64 = s.scene->desc.precision == B2VP_PREC_F64;
+            d.dev.reset(new b2vp::DeviceScene(std::move(s.scene), device));
+            return d;
+        }), "scene"_a, "device"_a = 0)
+        .def("render", &PyDeviceScene::render, "seeding"_a = "wavefront", "math"_a = "exact", "devices"_a = std::vector<int32_t>(),
+             "timeout"_a = 0.0, "majorant_grid"_a = 0u, "first_stream"_a = 0ull, "n_streams"_a = 0ull,
+             "Integrator.render (src/librender/python/integrator_v.cpp:124-153): GIL released, Ctrl-C cancels the render. "
+             "Returns (film[h, w, channels], totals).")
+        .def("cancel", [](PyDeviceScene &d) { d.dev->cancel(); }, "Integrator.cancel")
+        .def("last_kernel", [](PyDeviceScene &d) { return std::string(d.dev->info().last_kernel); });
+}

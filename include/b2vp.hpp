@@ -266,6 +266,14 @@ public:
         o.albedo = add_volume(ConstVolume{ albedo }); o.sigma_t = add_volume(sigma_t, sigma_t_to_world);
         return push_medium(o, prop(m.scale), m.has_spectral_extinction, m.sample_emitters, ph);
     }
+    /* the same with an albedo grid (C3: sigma_t and albedo fields of one cloud scene) */
+    int add_medium(const Heterogeneous &m, const GridVolume &sigma_t, const Mat4<F> &sigma_t_to_world, const GridVolume &albedo,
+                   const Mat4<F> &albedo_to_world, const Phase &ph) {
+        B2vpMedium o{};
+        o.type = B2VP_MEDIUM_HETEROGENEOUS;
+        o.albedo = add_volume(albedo, albedo_to_world); o.sigma_t = add_volume(sigma_t, sigma_t_to_world);
+        return push_medium(o, prop(m.scale), m.has_spectral_extinction, m.sample_emitters, ph);
+    }
     int add_volume(const ConstVolume &v) {
         B2vpVolume o{};
         o.type = B2VP_VOLUME_CONST; o.channels = 1; o.value = (double) prop(v.value); o.max_value = o.value;

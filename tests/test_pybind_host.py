@@ -1,0 +1,99 @@
+"""The pybind11 front end (`_b2vp`, csrc/py_b2vp.cpp): `load_dict` in C++ over include/b2vp.hpp and `render` with the
+GIL released -- the pair the reference's Python module offers (src/libcore/python/xml_v.cpp:100-240,
+src/librender/python/integrator_v.cpp:124-153).  Its scenes must be the ctypes host's scenes (which are pinned on the
+reference binary): same films through the oracle on the CPU, same films and counters from the device."""
+import numpy as np
+import pytest
+
+import scenes
+from test_cpp_host import ext_dict, ext_files
+
+
+def _ext(pkg):
+    try:
+        return pkg.ext()
+    except ImportError as e:
+        pytest.skip("pybind11 module not built: %s" % e)
+
+
+def _cases(pkg, tmp_path):
+    ext_files(pkg, tmp_path)
+    return {
+        "c1": lambda v: scenes.c1(spp=64, variant=v),
+        "c2": lambda v: scenes.c2(spp=4, variant=v, width=16),
+        "c2_mdistant_mis": lambda v: dict(scenes.c2(spp=4, variant=v, width=16, sensor="mdistant"),
+                                          integrator={"type": "volpathmis", "max_depth": -1, "use_spectral_mis": False}),
+        "c3": lambda v: scenes.c3(spp=1, variant=v, n=8, size=6),
+        "ext_mdistant": lambda v: ext_dict(pkg, tmp_path, v, "mdistant", 16),
+        "ext_mradiancemeter": lambda v: ext_dict(pkg, tmp_path, v, "mradiancemeter", 16),
+        "c2_sky_moment": lambda v: dict(scenes.c2(spp=4, variant=v, width=16), sky={"type": "constant", "radiance": 0.25},
+                                        integrator={"type": "moment", "nested": {"type": "volpath", "max_depth": -1}}),
+    }
+
+
+def _as_host_scene(pkg, s):
+    """A Scene of the pybind11 module seen through the ctypes structs (for the oracle, which takes a B2vpSceneDesc)."""
+    desc = pkg.abi.SceneDesc.from_address(s.desc_address)
+    return pkg.scene.Scene(desc, s.variant, desc.precision, [s])
+
+
+NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment"]
+
+
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+@pytest.mark.parametrize("name", NAMES)
+def test_pybind_load_dict_is_the_ctypes_load_dict(pkg, oracle, name, variant, tmp_path):
+    ext = _ext(pkg)
+    d = _cases(pkg, tmp_path)[name](variant)
+    s = ext.load_dict(d, variant)
+    ours = oracle.render(pkg, _as_host_scene(pkg, s), pkg.abi.SEED_WAVEFRONT)
+    ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT)
+    assert s.film_size == ref.film.shape[1::-1]
+    assert np.array_equal(ours.film[..., 3:5], ref.film[..., 3:5])
+    assert ours.totals.n_rng_draws == ref.totals.n_rng_draws and ours.totals.n_intersect == ref.totals.n_intersect
+    tol = 1e-12 if variant == "scalar_mono_double" else 1e-5
+    assert np.allclose(ours.film, ref.film, rtol=tol, atol=0)
+
+
+def test_pybind_rejects_what_the_cpp_host_does_not_cover(pkg, tmp_path):
+    ext = _ext(pkg)
+    d = scenes.c2(spp=1, width=4)
+    d["sensor"]["film"]["rfilter"] = {"type": "gaussian"}
+    with pytest.raises(RuntimeError, match="gaussian"):
+        ext.load_dict(d)
+    d = scenes.c2(spp=1, width=4)
+    d["atm"]["phase"] = {"type": "blendphase"}
+    with pytest.raises(RuntimeError, match="blendphase"):
+        ext.load_dict(d)
+    with pytest.raises(RuntimeError, match="variant"):
+        ext.load_dict(scenes.c1(spp=1), "scalar_rgb")
+
+
+def test_pybind_fails_loudly_without_a_device(pkg):
+    ext = _ext(pkg)
+    if pkg.abi.lib().b2vp_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(RuntimeError, match="CUDA|device"):
+        ext.DeviceScene(ext.load_dict(scenes.c1(spp=1)), 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+@pytest.mark.parametrize("name", NAMES)
+def test_pybind_render_on_the_device(pkg, oracle, name, variant, tmp_path):
+    ext = _ext(pkg)
+    d = _cases(pkg, tmp_path)[name](variant)
+    ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT)
+    ds = ext.DeviceScene(ext.load_dict(d, variant), 0)
+    film, tot = ds.render()
+    assert ds.last_kernel().startswith("queue/")
+    for k in ("n_paths", "n_rng_draws", "n_medium_steps", "n_null", "n_real", "n_intersect", "n_surface"):
+        assert tot[k] == getattr(ref.totals, k), k
+    tol = 2e-4 if variant == "scalar_mono" else 1e-12
+    assert film.shape == ref.film.shape and np.allclose(film, ref.film, rtol=tol, atol=tol * 1e-2)
+    if variant == "scalar_mono":
+        fast, tot2 = ds.render(math="fast")
+        assert tot2["n_paths"] == tot["n_paths"] and ds.last_kernel().endswith("fast f32")
+        assert abs(fast[..., 1].sum() - film[..., 1].sum()) < 0.05 * film[..., 1].sum()
+    with pytest.raises(RuntimeError):
+        ds.render(math="sloppy")
