@@ -43,7 +43,10 @@ def run(name, desc, scene_dict, reps=2, extra=None, variant="scalar_mono"):
 
 for a in [a for a in sys.argv[1:] if "=" in a]:
     k, v = a.split("=", 1)
-    RENDER_KW[k] = int(v) if v.isdigit() else v
+    if k in ("stay", "iter", "cta_phase", "slots_per_thread"):   # queue-kernel scheduler parameters (B2vpRenderArgs::tuning)
+        RENDER_KW.setdefault("tuning", {})[k] = float(v) if k == "slots_per_thread" else int(v)
+    else:
+        RENDER_KW[k] = int(v) if v.isdigit() else v
 which = [a for a in sys.argv[1:] if "=" not in a] or ["c1", "c3", "c5"]
 if "c1" in which:
     run("C1", "homogeneous Rayleigh cube over diffuse rectangle, distant 1x1, 1e6 spp", scenes.c1(spp=1000000))
