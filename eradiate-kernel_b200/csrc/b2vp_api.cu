@@ -1049,7 +1049,9 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
         out.q_slots_offset = (uint32_t) (base + qbytes);
         out.q_n_slots = (uint32_t) n_slots;
         out.q_ring_cap = (uint32_t) cap;
-        out.q_stay_min = a->tuning[1] ? std::min(33u, a->tuning[1]) : 26u;
+        /* a warp keeps its STEP batch while at least this many lanes stay (sweep after STEP went register-resident:
+           16-24 equal within 0.5 % in fast mode, 24 best in exact mode, 26 costs 2.5 %; profiles/r2_history.md) */
+        out.q_stay_min = a->tuning[1] ? std::min(33u, a->tuning[1]) : 24u;
         out.q_max_iter = a->tuning[2] ? std::min(1024u, a->tuning[2]) : 8u;
         /* 2: when the CTA moves on, the ray-making phases are served before STEP (+4 % with everything on chip);
            1: plain fullest-queue order, better when STEP is bound by gather latency (large grids: 93 vs 84 Mpaths/s) */
