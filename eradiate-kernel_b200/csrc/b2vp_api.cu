@@ -153,7 +153,8 @@ struct DeviceCtx {
     int sm_count = 0;
     size_t smem_optin = 0;
     size_t l2_window_max = 0;   /* largest access-policy window (0: no persisting L2 on this device) */
-    size_t l2_persist_bytes = 0; /* the persisting L2 carve-out this library set (cudaLimitPersistingL2CacheSize) */
+    size_t l2_persist_max = 0;   /* largest persisting L2 carve-out the device allows */
+    size_t l2_persist_bytes = 0; /* the carve-out this library has set (cudaLimitPersistingL2CacheSize); 0 = none yet */
     DeviceScene<float> dev32;
     DeviceScene<double> dev64;
     DevBuf film_buf, totals_buf, counter_buf, blocks_buf, stop_flag;
@@ -377,9 +378,7 @@ int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
         int l2_persist_max = 0, window_max = 0;
         CU_CHECK(cudaDeviceGetAttribute(&l2_persist_max, cudaDevAttrMaxPersistingL2CacheSize, device));
         CU_CHECK(cudaDeviceGetAttribute(&window_max, cudaDevAttrMaxAccessPolicyWindowSize, device));
-        if (l2_persist_max > 0 && window_max > 0 &&
-            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t) l2_persist_max) == cudaSuccess)
-            { c->l2_window_max = (size_t) window_max; c->l2_persist_bytes = (size_t) l2_persist_max; }
+        if (l2_persist_max > 0 && window_max > 0) { c->l2_window_max = (size_t) window_max; c->l2_persist_max = (size_t) l2_persist_max; }
         (void) cudaGetLastError();
     }
     CU_CHECK(cudaEventCreate(&c->ev0));
@@ -1093,15 +1092,25 @@ int set_stream_range(const B2vpRenderArgs *a, StreamSpace &sp) {
 
 template <typename F>
 cudaError_t launch_kernel(const LaunchPlan &pl, const DeviceScene<F> &ds, const DStreams &spd, const RenderOut<F> &out,
-                          cudaStream_t stream, const DeviceCtx *dc = nullptr, bool pin_cold = false) {
+                          cudaStream_t stream, DeviceCtx *dc = nullptr, bool pin_cold = false) {
     void *kargs[3] = { (void *) &ds.g, (void *) &spd, (void *) &out };
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) pl.grid); cfg.blockDim = dim3((unsigned) pl.threads);
     cfg.dynamicSmemBytes = pl.smem; cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     if (pin_cold && dc && dc->l2_window_max && out.q_cold && pl.cold_bytes) {
-        /* the cold path records are read and written by every phase but STEP for the whole launch: ask L2 to keep
-           them (persisting lines) rather than cycle them through HBM */
+        if (!dc->l2_persist_bytes) {   /* the carve-out takes capacity from everything else: set it only when it is used */
+            const size_t want = std::min(dc->l2_persist_max, (pl.cold_bytes + ((size_t) 1 << 20)) & ~(((size_t) 1 << 20) - 1));
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) dc->l2_persist_bytes = want;
+            (void) cudaGetLastError();
+        }
+        if (!dc->l2_persist_bytes) pin_cold = false;
+    }
+    if (pin_cold && dc && dc->l2_window_max && out.q_cold && pl.cold_bytes) {
+        /* EXPERIMENT (debug_flags bit 1), off by default: a persisting L2 window over the cold path records.  Measured
+           (profiles/r2_history.md): no change in kernel time on C2 or C3, and the carve-out it needs takes capacity
+           from everything else -- DRAM writes per C2 launch 0.40 GB without it, 1.08 GB with a 41 MB carve-out,
+           5.3 GB with the device maximum of 79 MB */
         attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
         attr[0].val.accessPolicyWindow.base_ptr = out.q_cold;
         const size_t window = std::min(pl.cold_bytes, dc->l2_window_max);
@@ -1239,7 +1248,7 @@ template <typename F> int render_typed(b2vp_scene *s, DeviceCtx *dc, const B2vpR
     const auto t_start = std::chrono::steady_clock::now();
     CU_CHECK(cudaEventRecord(dc->ev0, stream));
     if (count) {
-        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream, dc, (a->debug_flags & 2u) == 0));
+        CU_CHECK(launch_kernel<F>(pl, ds, sp.d, out, stream, dc, (a->debug_flags & 2u) != 0));
         launches++;
     }
     CU_CHECK(cudaEventRecord(dc->ev1, stream));

@@ -525,9 +525,19 @@ VP_D F volume_eval(const SceneView<F> &sv, const DVolume<F> &v, V3<F> p_world) {
             F v0 = fma_(w0y, v00, w1y * v10), v1 = fma_(w0y, v01, w1y * v11);
             return fma_(w0z, v0, w1z * v1);
         }
+        int z0 = wrap_coord(iz, nz, wrap), z1 = wrap_coord(iz + 1, nz, wrap);
+        if (nx == 1 && ny == 1 && ch == 1) {
+            /* a 1 x 1 x N column (the plane-parallel atmospheres of C2 / C4): every wrap mode maps both x and both y
+               indices to 0, so four of the eight corners are data[z0] and four data[z1].  Two loads instead of eight;
+               the interpolation is evaluated on the same operands in the same order, so the bits are the same (the
+               x- and y-lerps of equal values are NOT skipped: w0 * a + w1 * a need not round to a). */
+            const F a = data((size_t) z0), b = data((size_t) z1);
+            const F v00 = fma_(w0x, a, w1x * a), v01 = fma_(w0x, b, w1x * b);
+            const F v0 = fma_(w0y, v00, w1y * v00), v1 = fma_(w0y, v01, w1y * v01);
+            return fma_(w0z, v0, w1z * v1);
+        }
         int x0 = wrap_coord(ix, nx, wrap), x1 = wrap_coord(ix + 1, nx, wrap);
         int y0 = wrap_coord(iy, ny, wrap), y1 = wrap_coord(iy + 1, ny, wrap);
-        int z0 = wrap_coord(iz, nz, wrap), z1 = wrap_coord(iz + 1, nz, wrap);
         size_t r00 = ((size_t) z0 * ny + y0) * nx, r10 = ((size_t) z0 * ny + y1) * nx,
                r01 = ((size_t) z1 * ny + y0) * nx, r11 = ((size_t) z1 * ny + y1) * nx;
 #pragma unroll 1

@@ -353,8 +353,8 @@ typedef struct B2vpRenderArgs {
        [1] STEP keeps its batch while at least this many lanes stay (26), [2] for at most this many steps (8),
        [3] 1 + CTA phase policy (0 per warp, 1 fullest queue, 2 ray-making phases first).                       */
     uint32_t tuning[4];
-    uint32_t debug_flags;       /* bit 0: print the queue kernel's scheduler statistics to stderr; bit 1: do NOT
-                                   ask L2 to keep the queue kernel's cold path records (persisting access window) */
+    uint32_t debug_flags;       /* bit 0: print the queue kernel's scheduler statistics to stderr; bit 1: experiment,
+                                   a persisting L2 access window over the queue kernel's cold path records (no gain) */
     /* Majorant grid: 0 = the reference's delta / ratio tracking against ONE global majorant scale * max(sigma_t)
        (src/media/heterogeneous.cpp:29,38) -- the only mode whose random-number consumption, event counters and
        per-path results match the reference.  Non-zero = opt-in fast mode for heterogeneous media with a clamp-mode
