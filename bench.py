@@ -281,6 +281,9 @@ def run_ours(args):
         if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"   # the version banner goes to stdout, where ONE JSON line is expected
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # a CPU-side group for the one wait that must not touch the GPUs (strong scaling below): a rank that waits in
+        # an NCCL barrier keeps a spinning kernel on its GPU, and the render kernel is one persistent CTA per SM
+        host_group = dist.new_group(backend="gloo")
     n_gpus = world
 
     # weak scaling: every GPU renders `spp` samples per pixel; the global stream space has spp * N
@@ -401,6 +404,7 @@ def run_ours(args):
                                   "wall time of the call incl. the NCCL film reduce and the film read-back" % (r.totals.n_paths, world)}
             except Exception as e:   # reported, never fatal for the bench line
                 strong = {"error": str(e)[-300:]}
+        dist.barrier(group=host_group)   # the other ranks wait here on the CPU, their GPUs idle for rank 0
         barrier()
 
     if rank == 0:
