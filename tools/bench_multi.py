@@ -80,5 +80,6 @@ if "c4" in which:
                       "math": MATH, "gpus": N, "paths": n_paths, "wall_s": wall, "sum_of_slowest_kernel_ms": k_ms,
                       "mpaths_s_wall": n_paths / wall / 1e6, "segments_per_s_wall": segs / wall,
                       "per_wavelength_ms": wall / n_wl * 1e3,
-                      "films_complete": bool((films[:, :, 4].astype(np.float64).sum(axis=1) == spp * WIDTH).all()),
+                      "film_weight_deficit_per_wavelength": float(spp * WIDTH - films[:, :, 4].astype(np.float64).sum(axis=1).max()),
+                      "films_complete": bool(n_paths == n_wl * spp * WIDTH and (np.abs(films[:, :, 4].astype(np.float64).sum(axis=1) - spp * WIDTH) <= 1e-6 * spp * WIDTH).all()),
                       "mean_radiance_400nm": float(mean[0]), "mean_radiance_1000nm": float(mean[-1])}), flush=True)
