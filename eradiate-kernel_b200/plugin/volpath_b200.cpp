@@ -33,6 +33,9 @@
 #include <fstream>
 #include <functional>
 #include <iostream>
+#include <cstdio>
+#include <cstdlib>
+#include <unistd.h>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -47,6 +50,7 @@
 #include <mitsuba/core/fresolver.h>
 #include <mitsuba/core/plugin.h>
 #include <mitsuba/core/properties.h>
+#include <mitsuba/core/rfilter.h>
 #include <mitsuba/core/transform.h>
 #include <mitsuba/core/warp.h>
 #include <mitsuba/render/bsdf.h>
@@ -423,6 +427,125 @@ template <typename Float, typename Spectrum> struct B200Describe {
         t.desc.sensor = o;
     }
 
+    /* ---- load-time self-check ------------------------------------------------------------------------------
+       describe() reads private members of classes that live in OTHER shared objects (the reference's plugins), through
+       class definitions compiled into this one.  That is only right while both sides were compiled from the same
+       sources with the same flags; a drift would be silent memory corruption.  So before the first render, canary
+       objects of every such class are created through the reference's own PluginManager with known parameters and read
+       back through the very code paths describe() uses: any disagreement throws, naming the class.  (A plugin that is
+       not installed is skipped: scenes cannot contain it either.) */
+    template <typename T> static ref<T> canary(const Properties &props) {
+        try {
+            ref<T> o = PluginManager::instance()->create_object<T>(props);
+            /* wrapper plugins (distant, mdistant, gridvolume, ...) stand for the object expand() returns, as in the
+               XML loader (src/libcore/xml.cpp) */
+            std::vector<ref<Object>> ex = o->expand();
+            if (!ex.empty()) o = static_cast<T *>(ex[0].get());
+            return o;
+        } catch (const std::exception &) {
+            return nullptr;
+        }
+    }
+    static void expect(bool ok, const char *what) {
+        if (!ok)
+            Throw("volpath_b200: self-check failed for %s: this plugin and the reference's plugins were not built from "
+                  "the same sources / flags (class layouts differ); refusing to read scene objects", what);
+    }
+    static bool near(double a, double b) { return std::fabs(a - b) <= 1e-6 * (1.0 + std::fabs(b)); }
+    static void self_check() {
+        B200SceneTables scratch;
+        B200Describe d(scratch);
+        const bool trace_on = std::getenv("B2VP_SELFCHECK_TRACE") != nullptr;   /* diagnostics: which canary is being read */
+        auto trace = [trace_on, &scratch](const char *name) {
+            if (trace_on) std::fprintf(stderr, "[volpath_b200 self-check] %s\n", name);
+            /* the tables remember objects by address, and a canary may be allocated where the previous one was freed */
+            scratch.bsdf_ids.clear(); scratch.medium_ids.clear(); scratch.shape_ids.clear();
+        };
+        { trace("hg"); Properties p("hg"); p.set_float("g", 0.3125f);
+          if (auto o = canary<PhaseFunction>(p)) { int i = d.phase(o.get()); expect(scratch.phases[i].type == B2VP_PHASE_HG && near(scratch.phases[i].g, 0.3125), "HGPhaseFunction"); } }
+        { trace("tabphase"); Properties p("tabphase"); p.set_string("values", "0.5, 1.0, 2.0");
+          if (auto o = canary<PhaseFunction>(p)) { int i = d.phase(o.get()); const auto &v = scratch.phase_values[i];
+              expect(v.size() == 3 && near(v[0], 0.5) && near(v[1], 1.0) && near(v[2], 2.0), "TabulatedPhaseFunction"); } }
+        { trace("diffuse"); Properties p("diffuse"); p.set_float("reflectance", 0.375f);
+          if (auto o = canary<BSDF>(p)) { int i = d.bsdf(o.get()); expect(scratch.bsdfs[i].type == B2VP_BSDF_DIFFUSE && near(scratch.bsdfs[i].p[0], 0.375), "SmoothDiffuse"); } }
+        { trace("rpv"); Properties p("rpv"); p.set_float("rho_0", 0.125f); p.set_float("k", 0.75f); p.set_float("g", -0.25f); p.set_float("rho_c", 0.0625f);
+          if (auto o = canary<BSDF>(p)) { int i = d.bsdf(o.get()); const auto &b = scratch.bsdfs[i];
+              expect(b.type == B2VP_BSDF_RPV && near(b.p[0], 0.125) && near(b.p[1], 0.75) && near(b.p[2], -0.25) && near(b.p[3], 0.0625), "RPV"); } }
+        { trace("bilambertian"); Properties p("bilambertian"); p.set_float("reflectance", 0.375f); p.set_float("transmittance", 0.25f);
+          if (auto o = canary<BSDF>(p)) { int i = d.bsdf(o.get()); const auto &b = scratch.bsdfs[i];
+              expect(b.type == B2VP_BSDF_BILAMBERTIAN && near(b.p[0], 0.375) && near(b.p[1], 0.25), "BiLambertian"); } }
+        { trace("rectangle"); Properties p("rectangle");
+          p.set_transform("to_world", ScalarTransform4f::translate(ScalarVector3f(1.f, 2.f, 3.f)) * ScalarTransform4f::scale(ScalarVector3f(2.f, 4.f, 1.f)));
+          if (auto o = canary<Shape>(p)) { int i = d.shape(o.get()); const auto &r = scratch.shapes[i];
+              expect(r.type == B2VP_SHAPE_RECTANGLE && near(r.to_world.m[12], 1.0) && near(r.to_world.m[13], 2.0) && near(r.to_world.m[14], 3.0) &&
+                     near(r.frame_s[0], 4.0) && near(r.frame_t[1], 8.0) && near(r.frame_n[2], 1.0) && near(r.inv_surface_area, 1.0 / 32.0), "Rectangle"); } }
+        { trace("sphere"); Properties p("sphere"); p.set_array3f("center", Properties::Array3f(1.f, 2.f, 3.f)); p.set_float("radius", 0.5f);
+          if (auto o = canary<Shape>(p)) { int i = d.shape(o.get()); const auto &r = scratch.shapes[i];
+              expect(r.type == B2VP_SHAPE_SPHERE && near(r.center[0], 1.0) && near(r.center[1], 2.0) && near(r.center[2], 3.0) && near(r.radius, 0.5) &&
+                     r.flip_normals == 0 && near(r.inv_surface_area, 1.0 / (4.0 * 3.14159265358979323846 * 0.25)), "Sphere"); } }
+        { Properties ph("isotropic");
+          auto pf = canary<PhaseFunction>(ph);
+          trace("homogeneous"); Properties p("homogeneous"); p.set_float("sigma_t", 0.625f); p.set_float("albedo", 0.875f); p.set_float("scale", 2.f);
+          if (pf) p.set_object("phase", pf.get());
+          if (auto o = canary<Medium>(p)) { int i = d.medium(o.get()); const auto &m = scratch.media[i];
+              expect(m.type == B2VP_MEDIUM_HOMOGENEOUS && near(m.scale, 2.0) && near(scratch.volumes[m.sigma_t].value, 0.625) &&
+                     near(scratch.volumes[m.albedo].value, 0.875) && scratch.phases[m.phase].type == B2VP_PHASE_ISOTROPIC, "HomogeneousMedium"); } }
+        { trace("directional"); Properties p("directional"); p.set_array3f("direction", Properties::Array3f(0.f, 0.f, -1.f)); p.set_float("irradiance", 1.5f);
+          if (auto o = canary<Emitter>(p)) { d.emitter(o.get()); const auto &e = scratch.emitters.back();
+              expect(e.type == B2VP_EMITTER_DIRECTIONAL && near(e.direction[0], 0.0) && near(e.direction[1], 0.0) && near(e.direction[2], -1.0) && near(e.irradiance, 1.5), "DirectionalEmitter"); } }
+        { trace("constant"); Properties p("constant"); p.set_float("radiance", 0.25f);
+          if (auto o = canary<Emitter>(p)) { d.emitter(o.get()); const auto &e = scratch.emitters.back();
+              expect(e.type == B2VP_EMITTER_CONSTANT && near(e.irradiance, 0.25), "ConstantBackgroundEmitter"); } }
+        { trace("gridvolume");   /* a 2 x 2 x 2 version-3 .vol file (volume_data.h:42-102) with the values 1 .. 8 */
+          char path[] = "/tmp/b2vp_canary_XXXXXX";
+          const int fd = mkstemp(path);
+          if (fd >= 0) {
+              unsigned char head[48] = { 'V', 'O', 'L', 3 };
+              const int32_t meta[5] = { 1, 2, 2, 2, 1 };
+              const float box[6] = { 0, 0, 0, 1, 1, 1 }, vals[8] = { 1, 2, 3, 4, 5, 6, 7, 8 };
+              std::memcpy(head + 4, meta, 20); std::memcpy(head + 24, box, 24);
+              const bool written = write(fd, head, 48) == 48 && write(fd, vals, 32) == 32;
+              close(fd);
+              Properties p("gridvolume"); p.set_string("filename", path); p.set_string("filter_type", "nearest"); p.set_string("wrap_mode", "mirror");
+              if (written) if (auto o = canary<Volume>(p)) { int i = d.volume(o.get()); const auto &v = scratch.volumes[i];
+                  expect(v.type == B2VP_VOLUME_GRID && v.channels == 1 && v.res[0] == 2 && v.res[1] == 2 && v.res[2] == 2 && v.filter == B2VP_FILTER_NEAREST &&
+                         v.wrap == B2VP_WRAP_MIRROR && near(v.max_value, 8.0) && scratch.grids.back().size() == 8 && scratch.grids.back()[0] == 1.f &&
+                         scratch.grids.back()[7] == 8.f && near(v.bbox_max[2], 1.0), "GridVolumeImpl"); }
+              unlink(path);
+          } }
+        /* sensors: film and sampler children, then the members of the sensor classes themselves */
+        auto film_of = [&trace](int w, int h) {
+            trace("box"); Properties rf("box"); auto filter = canary<mitsuba::ReconstructionFilter<Float, Spectrum>>(rf);
+            trace("hdrfilm"); Properties p("hdrfilm"); p.set_int("width", w); p.set_int("height", h);
+            if (filter) p.set_object("rfilter", filter.get());
+            return canary<Film>(p);
+        };
+        auto sampler_of = [&trace]() { trace("independent"); Properties p("independent"); p.set_int("sample_count", 7); p.set_int("seed", 11); return canary<Sampler>(p); };
+        { auto film = film_of(3, 1); auto smp = sampler_of();
+          trace("distant"); Properties p("distant"); p.set_array3f("direction", Properties::Array3f(0.f, 0.f, 1.f)); p.set_array3f("ray_target", Properties::Array3f(0.5f, -0.25f, 0.125f));
+          if (film && smp) { p.set_object("film", film.get()); p.set_object("sampler", smp.get());
+              if (auto o = canary<Sensor>(p)) { d.sensor(o.get()); const auto &sn = scratch.desc.sensor;
+                  expect(sn.type == B2VP_SENSOR_DISTANT && sn.direction_type == B2VP_DIR_SAMPLE_WIDTH && sn.target_type == B2VP_TARGET_POINT &&
+                         near(sn.target_point[0], 0.5) && near(sn.target_point[1], -0.25) && near(sn.target_point[2], 0.125) &&
+                         sn.film_size[0] == 3 && sn.film_size[1] == 1 && sn.sample_count == 7 && sn.sampler_seed == 11 && sn.flip_directions == 0,
+                         "DistantSensor / HDRFilm / IndependentSampler"); } } }
+        { auto film = film_of(2, 1); auto smp = sampler_of();
+          trace("mdistant"); Properties p("mdistant"); p.set_string("directions", "0, 0, -1, 1, 0, -1"); p.set_array3f("target", Properties::Array3f(0.5f, -0.25f, 0.125f));
+          if (film && smp) { p.set_object("film", film.get()); p.set_object("sampler", smp.get());
+              scratch.sensor_xf.clear();
+              if (auto o = canary<Sensor>(p)) { d.sensor(o.get()); const auto &sn = scratch.desc.sensor;
+                  expect(sn.type == B2VP_SENSOR_MDISTANT && sn.n_transforms == 2 && scratch.sensor_xf.size() == 32 && sn.target_type == B2VP_TARGET_POINT &&
+                         near(sn.target_point[0], 0.5) && near(scratch.sensor_xf[10], -1.0) /* first look-at: z axis = (0, 0, -1) */, "MultiDistantSensor"); } } }
+        { auto film = film_of(2, 1); auto smp = sampler_of();
+          trace("mradiancemeter"); Properties p("mradiancemeter"); p.set_string("origins", "1, 2, 3, 4, 5, 6"); p.set_string("directions", "0, 0, -1, 0, 0, 1");
+          if (film && smp) { p.set_object("film", film.get()); p.set_object("sampler", smp.get());
+              scratch.sensor_xf.clear();
+              if (auto o = canary<Sensor>(p)) { d.sensor(o.get()); const auto &sn = scratch.desc.sensor;
+                  expect(sn.type == B2VP_SENSOR_MRADIANCEMETER && sn.n_transforms == 2 && scratch.sensor_xf.size() == 32 &&
+                         near(scratch.sensor_xf[12], 1.0) && near(scratch.sensor_xf[13], 2.0) && near(scratch.sensor_xf[14], 3.0) &&
+                         near(scratch.sensor_xf[16 + 12], 4.0) && near(scratch.sensor_xf[16 + 14], 6.0), "MultiRadianceMeter"); } } }
+    }
+
     void scene(const Scene *sc, const Sensor *sn) {
         t.desc.precision = std::is_same_v<ScalarFloat, double> ? B2VP_PREC_F64 : B2VP_PREC_F32;
         for (auto &s : sc->shapes()) shape(s.get());
@@ -564,6 +687,8 @@ public:
 
     /* object graph -> POD tables of include/b2vp.h */
     void describe(const Scene *scene, const Sensor *sensor, B200SceneTables &tables) const {
+        static std::once_flag checked;   /* per variant (this is a class template): canaries before any real object */
+        std::call_once(checked, [] { B200Describe<Float, Spectrum>::self_check(); });
         B200Describe<Float, Spectrum> d(tables);
         d.scene(scene, sensor);
         B2vpIntegrator &it = tables.desc.integrator;

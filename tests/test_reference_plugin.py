@@ -55,6 +55,26 @@ def test_plugin_describe_against_reference_films(pkg, oracle, name):
         assert np.array_equal(r.film, film), name
 
 
+def test_plugin_self_check_reads_canaries_of_every_opened_class(pkg, tmp_path):
+    """describe() reads private members of classes that live in the reference's own plugin objects; before the first
+    render it creates canary objects of every such class through the reference's PluginManager and reads them back
+    through the same code (volpath_b200.cpp: B200Describe::self_check) -- a layout drift between the two builds
+    throws instead of corrupting memory.  Here: the check runs in both variants, visits every class, and passes."""
+    import subprocess
+    ref_xml = ref_xml_or_skip()
+    d, _ = make_ref_golden.scene_dict("c2_paths")
+    xml = ref_xml.to_xml(ref_xml.with_plugin(d), str(tmp_path), pkg.scene.write_vol)
+    for variant in ("scalar_mono", "scalar_mono_double"):
+        p = subprocess.run([ref_xml.PROBE, variant, xml, str(tmp_path / "film.bin"), "-t", "1", "--describe-oracle", ref_xml.ORACLE_LIB],
+                           capture_output=True, text=True, env=dict(os.environ, B2VP_SELFCHECK_TRACE="1"))
+        assert p.returncode == 0, p.stderr[-500:]
+        seen = [l.split("] ", 1)[1].strip() for l in p.stderr.splitlines() if "[volpath_b200 self-check]" in l]
+        for name in ("hg", "tabphase", "diffuse", "rpv", "bilambertian", "rectangle", "sphere", "homogeneous", "directional",
+                     "constant", "gridvolume", "hdrfilm", "independent", "distant", "mdistant", "mradiancemeter"):
+            assert name in seen, (variant, name, seen)
+        assert "self-check failed" not in p.stderr
+
+
 def test_plugin_rejects_content_outside_the_scope(pkg):
     ref_xml = ref_xml_or_skip()
     d, variant = make_ref_golden.scene_dict("c2_paths")
