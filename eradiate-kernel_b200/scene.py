@@ -669,6 +669,21 @@ class _Builder:
         sn.film_size[:] = [w, h]
         sn.crop_offset[:] = [int(film.get("crop_offset_x", 0)), int(film.get("crop_offset_y", 0))]
         sn.crop_size[:] = [int(film.get("crop_width", w)), int(film.get("crop_height", h))]
+        # Film::set_crop_window (src/librender/film.cpp:54-63): the crop size does not adjust itself to the offset
+        for k, full in enumerate((w, h)):
+            if sn.crop_offset[k] < 0 or sn.crop_size[k] <= 0 or sn.crop_offset[k] + sn.crop_size[k] > full:
+                raise RuntimeError("Invalid crop window specification!\noffset %s + crop size %s vs full size %s" % (
+                    list(sn.crop_offset), list(sn.crop_size), [w, h]))
+        # HDRFilm (src/films/hdrfilm.cpp:100-155): the develop() parameters are validated at construction
+        if film.get("file_format", "openexr") not in ("openexr", "exr", "rgbe", "pfm"):
+            raise RuntimeError("The \"file_format\" parameter must either be equal to \"openexr\", \"pfm\", or \"rgbe\","
+                               " found %s instead." % film["file_format"])
+        if film.get("pixel_format", "luminance") not in ("luminance", "luminance_alpha", "rgb", "rgba", "xyz", "xyza"):
+            raise RuntimeError("The \"pixel_format\" parameter must either be equal to \"luminance\", \"luminance_alpha\", "
+                               "\"rgb\", \"rgba\",  \"xyz\" or \"xyza\". Found %s." % film["pixel_format"])
+        if film.get("component_format", "float16") not in ("float16", "float32", "uint32"):
+            raise RuntimeError("The \"component_format\" parameter must either be equal to \"float16\", \"float32\", or "
+                               "\"uint32\". Found %s instead." % film["component_format"])
         sampler = node.get("sampler", {"type": "independent", "sample_count": 4})
         if sampler.get("type", "independent") != "independent":
             raise RuntimeError("sampler plugin %r is not supported by the B200 volpath" % sampler["type"])

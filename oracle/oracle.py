@@ -139,3 +139,46 @@ def ray_intersect(scene, o, d, mint=-1.0, maxt=-1.0):
         raise RuntimeError("oracle error %d" % rc)
     return {"t": None if t.value < 0 else t.value, "p": np.array(p[:]), "n": np.array(n[:]),
             "wi": np.array(wi[:]), "shape": shape.value}
+
+
+def _vec(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a, a.ctypes.data_as(C.c_void_p)
+
+
+def phase_samples(pkg, phase, wi, samples):
+    """n samples of a phase function (abi.Phase) for incident direction wi: (wo[n, 3], value[n]) -- the value of the
+    phase function in each sampled direction, which is also its pdf (phase functions are normalised)."""
+    samples, sp = _vec(samples)
+    n = len(samples)
+    wi, wp = _vec(wi)
+    wo, value = np.zeros((n, 3)), np.zeros(n)
+    lib().b2vp_oracle_probe_phase(C.byref(phase), wp, C.c_int(n), sp, wo.ctypes.data_as(C.c_void_p), value.ctypes.data_as(C.c_void_p))
+    return wo, value
+
+
+def phase_eval(pkg, phase, wi, wo):
+    f = lib().b2vp_oracle_probe_phase_eval
+    f.restype = C.c_double
+    wi, wp = _vec(wi)
+    wo, op = _vec(wo)
+    return f(C.byref(phase), wp, op)
+
+
+def bsdf_samples(pkg, bsdf, wi, samples):
+    """n samples of a BSDF (abi.Bsdf) in the local frame: (wo[n, 3], value[n], pdf[n], weight[n])."""
+    samples, sp = _vec(samples)
+    n = len(samples)
+    wi, wp = _vec(wi)
+    wo, value, pdf, weight = np.zeros((n, 3)), np.zeros(n), np.zeros(n), np.zeros(n)
+    lib().b2vp_oracle_probe_bsdf(C.byref(bsdf), wp, C.c_int(n), sp, *[a.ctypes.data_as(C.c_void_p) for a in (wo, value, pdf, weight)])
+    return wo, value, pdf, weight
+
+
+def bsdf_eval(pkg, bsdf, wi, wo):
+    wo, op = _vec(wo)
+    wi, wp = _vec(wi)
+    n = len(wo)
+    value, pdf = np.zeros(n), np.zeros(n)
+    lib().b2vp_oracle_probe_bsdf_eval(C.byref(bsdf), wp, C.c_int(n), op, value.ctypes.data_as(C.c_void_p), pdf.ctypes.data_as(C.c_void_p))
+    return value, pdf

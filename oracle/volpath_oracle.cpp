@@ -2042,6 +2042,50 @@ double b2vp_oracle_rpv_eval(double rho_0, double k, double g, double rho_c, cons
     return bsdf_eval<double>(b, V3<double>{ wi[0], wi[1], wi[2] }, V3<double>{ wo[0], wo[1], wo[2] });
 }
 
+/* Probes for the statistical tests of the reference (src/phase/tests/test_*.py, src/bsdfs/tests/test_*.py):
+   n samples of a phase function / BSDF for the incident direction wi, with the value and pdf of each sampled direction.
+   samples: n x 3 (sample1, sample2.x, sample2.y); wo: n x 3; value / pdf / weight: n. */
+void b2vp_oracle_probe_phase(const B2vpPhase *ph, const double *wi, int n, const double *samples, double *wo, double *value) {
+    TabDistr<double> tab;
+    if (ph->type == B2VP_PHASE_TABULATED) tab.build(ph->values, ph->n_values);
+    MediumInteraction<double> mi;
+    mi.wi = V3<double>{ wi[0], wi[1], wi[2] };
+    mi.sh_frame = make_frame(-mi.wi);   /* the frame sample_interaction gives a collision: around the ray direction = -wi (medium.cpp:60-62) */
+    for (int i = 0; i < n; ++i) {
+        V3<double> w = phase_sample(*ph, tab, mi, samples[3 * i + 1], samples[3 * i + 2]);
+        wo[3 * i] = w.x; wo[3 * i + 1] = w.y; wo[3 * i + 2] = w.z;
+        value[i] = phase_eval(*ph, tab, mi, w);
+    }
+}
+double b2vp_oracle_probe_phase_eval(const B2vpPhase *ph, const double *wi, const double *wo) {
+    TabDistr<double> tab;
+    if (ph->type == B2VP_PHASE_TABULATED) tab.build(ph->values, ph->n_values);
+    MediumInteraction<double> mi;
+    mi.wi = V3<double>{ wi[0], wi[1], wi[2] };
+    mi.sh_frame = make_frame(-mi.wi);
+    return phase_eval(*ph, tab, mi, V3<double>{ wo[0], wo[1], wo[2] });
+}
+void b2vp_oracle_probe_bsdf(const B2vpBsdf *b, const double *wi, int n, const double *samples, double *wo, double *value,
+                            double *pdf, double *weight) {
+    const V3<double> w_i{ wi[0], wi[1], wi[2] };
+    for (int i = 0; i < n; ++i) {
+        double wgt;
+        BSDFSample<double> bs = bsdf_sample<double>(*b, w_i, samples[3 * i], samples[3 * i + 1], samples[3 * i + 2], wgt);
+        wo[3 * i] = bs.wo.x; wo[3 * i + 1] = bs.wo.y; wo[3 * i + 2] = bs.wo.z;
+        value[i] = bsdf_eval<double>(*b, w_i, bs.wo);
+        pdf[i] = bsdf_pdf<double>(*b, w_i, bs.wo);
+        weight[i] = wgt;
+    }
+}
+void b2vp_oracle_probe_bsdf_eval(const B2vpBsdf *b, const double *wi, int n, const double *wo, double *value, double *pdf) {
+    const V3<double> w_i{ wi[0], wi[1], wi[2] };
+    for (int i = 0; i < n; ++i) {
+        const V3<double> w{ wo[3 * i], wo[3 * i + 1], wo[3 * i + 2] };
+        value[i] = bsdf_eval<double>(*b, w_i, w);
+        pdf[i] = bsdf_pdf<double>(*b, w_i, w);
+    }
+}
+
 int b2vp_oracle_probe_sensor_ray(const B2vpSceneDesc *desc, int precision, double fx, double fy, double ax, double ay,
                                  double *o, double *d, double *weight) {
     return precision == B2VP_PREC_F32 ? probe_sensor_ray_t<float>(desc, fx, fy, ax, ay, o, d, weight)

@@ -65,3 +65,29 @@ def test_pfm(pkg, tmp_path):
     assert raw.startswith(b"Pf\n5 3\n-1\n")
     data = np.frombuffer(raw[len(b"Pf\n5 3\n-1\n"):], dtype="<f4").reshape(3, 5)
     assert np.array_equal(data[::-1], r.bitmap())                  # PFM stores the bottom scan line first
+
+
+def _film_scene(pkg, **film):
+    import scenes
+    d = scenes.c1(spp=1)
+    d["sensor"]["film"] = dict({"type": "hdrfilm", "width": 32, "height": 21, "rfilter": {"type": "box"}}, **film)
+    return pkg.load_dict(d)
+
+
+def test_hdrfilm_crops_and_parameters(pkg):
+    """src/films/tests/test_hdrfilm.py:7-33 (construction errors) and :35-74 (crop windows), through load_dict"""
+    sn = _film_scene(pkg, crop_width=11, crop_height=5, crop_offset_x=2, crop_offset_y=3).desc.sensor
+    assert list(sn.film_size) == [32, 21] and list(sn.crop_size) == [11, 5] and list(sn.crop_offset) == [2, 3]
+    # the crop size does not adjust itself: an offset alone pushes the window out of bounds
+    with pytest.raises(RuntimeError, match="Invalid crop window"):
+        _film_scene(pkg, crop_offset_x=30, crop_offset_y=20)
+    sn = _film_scene(pkg, crop_offset_x=30, crop_offset_y=20, crop_width=2, crop_height=1).desc.sensor
+    assert list(sn.film_size) == [32, 21] and list(sn.crop_size) == [2, 1] and list(sn.crop_offset) == [30, 20]
+    with pytest.raises(RuntimeError, match="component_format"):
+        _film_scene(pkg, component_format="uint8")
+    with pytest.raises(RuntimeError, match="pixel_format"):
+        _film_scene(pkg, pixel_format="brga")
+    with pytest.raises(RuntimeError, match="file_format"):
+        _film_scene(pkg, file_format="png")
+    with pytest.raises(RuntimeError, match="box"):
+        _film_scene(pkg, rfilter={"type": "gaussian", "stddev": 18.5})   # wider filters: out of scope, refused by name
