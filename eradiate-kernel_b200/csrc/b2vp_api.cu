@@ -355,6 +355,8 @@ int build_bvh(b2vp_scene *s) {
 namespace {
 
 /* The context of `device`, created on first use (device attributes, events, control stream). */
+int noalloc_scratch(int device, unsigned char **out);   /* defined with b2vp_render_noalloc below */
+
 int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
     std::lock_guard<std::mutex> lock(s->mutex);
     for (auto &c : s->contexts)
@@ -388,6 +390,14 @@ int context_for(b2vp_scene *s, int device, DeviceCtx **out) {
     CU_CHECK(cudaStreamCreateWithFlags(&c->work_stream, cudaStreamNonBlocking));
     CU_CHECK(c->stop_flag.alloc(256));
     CU_CHECK(cudaMemset(c->stop_flag.p, 0, 256));
+    /* The static scratch array of b2vp_render_noalloc is part of this library's device image; with CUDA's lazy module
+       loading it would be instantiated (64 MiB) by the first call that asks for its address.  Ask here, at set-up, so
+       that b2vp_render_noalloc itself never makes the driver allocate (tests/test_zz_no_alloc.py). */
+    {
+        unsigned char *scratch = nullptr;
+        int rc = noalloc_scratch(device, &scratch);
+        if (rc != B2VP_OK) return rc;
+    }
     *out = c.get();
     s->contexts.push_back(std::move(c));
     return B2VP_OK;
@@ -948,15 +958,17 @@ struct LaunchPlan {
     std::string name;
 };
 
-template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset);
-template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset) {
+template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset, int *threads);
+template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset, int *threads) {
+    *threads = maxt;
     if (env) return fast ? vp_launch::queue_f32_fast_env(mis, preset) : vp_launch::queue_f32_env(mis, preset);
     if (mis) return fast ? vp_launch::queue_f32_fast_mis(ft, preset) : vp_launch::queue_f32_mis(ft, preset);
-    return fast ? vp_launch::queue_f32_fast(ft, preset) : vp_launch::queue_f32(ft, maxt, preset);
+    return fast ? vp_launch::queue_f32_fast(ft, preset, threads) : vp_launch::queue_f32(ft, maxt, preset, threads);
 }
-template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, bool mis, bool env, const char **preset) {
+template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, bool mis, bool env, const char **preset, int *threads) {
+    *threads = maxt;
     if (env) return vp_launch::queue_f64_env(mis, preset);
-    return mis ? vp_launch::queue_f64_mis(ft, preset) : vp_launch::queue_f64(ft, maxt, preset);
+    return mis ? vp_launch::queue_f64_mis(ft, preset) : vp_launch::queue_f64(ft, maxt, preset, threads);
 }
 template <typename F> const void *stream_entry() { return sizeof(F) == 4 ? vp_launch::stream_f32() : vp_launch::stream_f64(); }
 template <typename F> const void *lanes_entry() { return sizeof(F) == 4 ? vp_launch::lanes_f32() : vp_launch::lanes_f64(); }
@@ -1016,8 +1028,8 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
     if (pl.queue_kernel) {
         pl.threads = kernel == B2VP_KERNEL_QUEUE_256 ? 256 : 512;
         pl.kern = queue_entry<F>(launch_features | (kernel == B2VP_KERNEL_QUEUE_GENERIC ? vp_launch::FORCE_GENERIC : 0u),
-                                 pl.threads, fast, mis, env, &preset);
-        pl.name = std::string("queue/") + preset + (pl.threads == 512 ? "" : "/256") + (fast ? " fast" : "");
+                                 pl.threads, fast, mis, env, &preset, &pl.threads);
+        pl.name = std::string("queue/") + preset + (kernel == B2VP_KERNEL_QUEUE_256 ? "/256" : "") + (fast ? " fast" : "");
     } else if (kernel == B2VP_KERNEL_LANES) {
         pl.kern = lanes_entry<F>(); pl.threads = 256; pl.name = "lanes";
     } else {

@@ -10,9 +10,9 @@
 #include "vp_launch.h"
 
 namespace vp_launch {
-const void *queue_f32_fast(uint32_t features, const char **preset) {
+const void *queue_f32_fast(uint32_t features, const char **preset, int *threads) {
     const bool generic = (features & 0x80000000u) != 0;
     features &= ~0x80000000u;
-    return vp_fast::pick_queue_kernel<float, 512>(features, generic, preset);
+    return vp_fast::pick_queue_kernel<float, 512>(features, generic, preset, threads);
 }
 } // namespace vp_launch

@@ -15,12 +15,13 @@ namespace vp_launch {
 constexpr uint32_t FORCE_GENERIC = 0x80000000u;
 
 /* The queue kernel (vp_queue.cuh) for a scene-feature set: the smallest preset instance that covers `features`,
-   else the all-features instance.  max_threads: 512 (product) or 256.  `*preset` names the instance. */
-const void *queue_f32(uint32_t features, int max_threads, const char **preset);
-const void *queue_f64(uint32_t features, int max_threads, const char **preset);
+   else the all-features instance.  max_threads: 512 (product) or 256.  `*preset` names the instance, `*threads` is
+   the CTA size to launch it with (max_threads, except for presets that are built for another size). */
+const void *queue_f32(uint32_t features, int max_threads, const char **preset, int *threads);
+const void *queue_f64(uint32_t features, int max_threads, const char **preset, int *threads);
 /* Tolerance-mode fp32 instances (kern_q32_fast.cu): same kernel text, PCG32 exact, floating point with FMA
    contraction and hardware approximations.  512 threads only. */
-const void *queue_f32_fast(uint32_t features, const char **preset);
+const void *queue_f32_fast(uint32_t features, const char **preset, int *threads);
 /* The same kernel running volpathmis' state machine (FT_MIS; kern_q*_mis.cu).  512 threads only. */
 const void *queue_f32_mis(uint32_t features, const char **preset);
 const void *queue_f64_mis(uint32_t features, const char **preset);

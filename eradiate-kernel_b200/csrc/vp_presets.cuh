@@ -21,10 +21,21 @@ template <typename F, int MAXT, uint32_t FEAT> const void *q_entry() {
     return reinterpret_cast<const void *>(&volpath_q_kernel<F, MAXT, FEAT>);
 }
 
-template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool force_generic, const char **name) {
+/* CTA size of the large-mesh preset in fp32.  BVH traversal through L2 is a chain of dependent loads; with the BVH out
+   of shared memory the kernel is bound by that latency, and more warps hide more of it than the registers they give
+   up cost: C5 123 Mpaths/s at 512 threads (116 registers), 142 at 640 (96), **157 at 768 (80, 30-130 bytes of spills)**,
+   155 at 1024 (64).  Every other preset loses with more threads (C2 335 -> 316 at 640, C3 176 -> 142). */
+constexpr int BIG_MESH_THREADS = 768;
+
+template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool force_generic, const char **name, int *threads) {
+    *threads = MAXT;
     if (force_generic) ft = FT_ALL;
     if ((ft & ~PRE_HOMOG) == 0) { *name = "homogeneous"; return q_entry<F, MAXT, PRE_HOMOG>(); }
-    if ((ft & ~PRE_HOMOG_BIG) == 0) { *name = "homogeneous, large mesh"; return q_entry<F, MAXT, PRE_HOMOG_BIG>(); }
+    if ((ft & ~PRE_HOMOG_BIG) == 0) {
+        *name = "homogeneous, large mesh";
+        if constexpr (sizeof(F) == 4 && MAXT == 512) { *threads = BIG_MESH_THREADS; return q_entry<F, BIG_MESH_THREADS, PRE_HOMOG_BIG>(); }
+        else return q_entry<F, MAXT, PRE_HOMOG_BIG>();
+    }
     if ((ft & ~PRE_HET) == 0) { *name = "heterogeneous"; return q_entry<F, MAXT, PRE_HET>(); }
     if ((ft & ~PRE_HET_G) == 0) { *name = "heterogeneous, grid in HBM"; return q_entry<F, MAXT, PRE_HET_G>(); }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return q_entry<F, MAXT, PRE_HET_ALB>(); }
