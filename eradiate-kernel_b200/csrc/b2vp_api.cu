@@ -962,13 +962,13 @@ template <typename F> const void *queue_entry(uint32_t ft, int maxt, bool fast, 
 template <> const void *queue_entry<float>(uint32_t ft, int maxt, bool fast, bool mis, bool env, const char **preset, int *threads) {
     *threads = maxt;
     if (env) return fast ? vp_launch::queue_f32_fast_env(mis, preset) : vp_launch::queue_f32_env(mis, preset);
-    if (mis) return fast ? vp_launch::queue_f32_fast_mis(ft, preset) : vp_launch::queue_f32_mis(ft, preset);
+    if (mis) return fast ? vp_launch::queue_f32_fast_mis(ft, preset, threads) : vp_launch::queue_f32_mis(ft, preset, threads);
     return fast ? vp_launch::queue_f32_fast(ft, preset, threads) : vp_launch::queue_f32(ft, maxt, preset, threads);
 }
 template <> const void *queue_entry<double>(uint32_t ft, int maxt, bool, bool mis, bool env, const char **preset, int *threads) {
     *threads = maxt;
     if (env) return vp_launch::queue_f64_env(mis, preset);
-    return mis ? vp_launch::queue_f64_mis(ft, preset) : vp_launch::queue_f64(ft, maxt, preset, threads);
+    return mis ? vp_launch::queue_f64_mis(ft, preset, threads) : vp_launch::queue_f64(ft, maxt, preset, threads);
 }
 template <typename F> const void *stream_entry() { return sizeof(F) == 4 ? vp_launch::stream_f32() : vp_launch::stream_f64(); }
 template <typename F> const void *lanes_entry() { return sizeof(F) == 4 ? vp_launch::lanes_f32() : vp_launch::lanes_f64(); }

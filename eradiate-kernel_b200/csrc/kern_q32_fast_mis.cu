@@ -5,8 +5,8 @@
 #include "vp_launch.h"
 
 namespace vp_launch {
-const void *queue_f32_fast_mis(uint32_t features, const char **preset) {
+const void *queue_f32_fast_mis(uint32_t features, const char **preset, int *threads) {
     const bool generic = (features & 0x80000000u) != 0;
-    return vp_fast::pick_queue_kernel_mis<float>(features & ~0x80000000u, generic, preset);
+    return vp_fast::pick_queue_kernel_mis<float>(features & ~0x80000000u, generic, preset, threads);
 }
 } // namespace vp_launch

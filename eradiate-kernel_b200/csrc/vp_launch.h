@@ -23,9 +23,9 @@ const void *queue_f64(uint32_t features, int max_threads, const char **preset, i
    contraction and hardware approximations.  512 threads only. */
 const void *queue_f32_fast(uint32_t features, const char **preset, int *threads);
 /* The same kernel running volpathmis' state machine (FT_MIS; kern_q*_mis.cu).  512 threads only. */
-const void *queue_f32_mis(uint32_t features, const char **preset);
-const void *queue_f64_mis(uint32_t features, const char **preset);
-const void *queue_f32_fast_mis(uint32_t features, const char **preset);
+const void *queue_f32_mis(uint32_t features, const char **preset, int *threads);
+const void *queue_f64_mis(uint32_t features, const char **preset, int *threads);
+const void *queue_f32_fast_mis(uint32_t features, const char **preset, int *threads);
 /* ... and for scenes with an environment emitter (FT_ENV; kern_q*_env.cu): all-features instances, 512 threads */
 const void *queue_f32_env(bool mis, const char **preset);
 const void *queue_f64_env(bool mis, const char **preset);

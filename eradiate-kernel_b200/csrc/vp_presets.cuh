@@ -46,9 +46,16 @@ template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool 
 }
 
 /* volpathmis instances (FT_MIS): 512 threads only, in their own translation units (kern_q*_mis.cu) */
-template <typename F> const void *pick_queue_kernel_mis(uint32_t ft, bool force_generic, const char **name) {
+template <typename F> const void *pick_queue_kernel_mis(uint32_t ft, bool force_generic, const char **name, int *threads) {
+    *threads = 512;
     if (force_generic) ft = FT_ALL;
     if ((ft & ~PRE_HOMOG) == 0) { *name = "volpathmis, homogeneous"; return q_entry<F, 512, PRE_HOMOG | FT_MIS>(); }
+    if constexpr (sizeof(F) == 4) {   /* C5 under volpathmis: the larger CTA of the large-mesh preset */
+        if ((ft & ~PRE_HOMOG_BIG) == 0) {
+            *name = "volpathmis, homogeneous, large mesh"; *threads = BIG_MESH_THREADS;
+            return q_entry<F, BIG_MESH_THREADS, PRE_HOMOG_BIG | FT_MIS>();
+        }
+    }
     if ((ft & ~PRE_HET) == 0) { *name = "volpathmis, heterogeneous"; return q_entry<F, 512, PRE_HET | FT_MIS>(); }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "volpathmis, heterogeneous+albedo grid"; return q_entry<F, 512, PRE_HET_ALB | FT_MIS>(); }
     *name = "volpathmis, generic";

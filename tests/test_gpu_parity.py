@@ -150,7 +150,8 @@ def test_volpathmis_runs_on_the_queue_kernel(pkg, oracle, variant):
                          (lambda: scenes.c2(spp=4, variant=variant, width=32), "heterogeneous"),
                          (lambda: scenes.c3(spp=1, variant=variant, n=48, size=8), "heterogeneous+albedo grid"),
                          (lambda: _sky(scenes.c2(spp=4, variant=variant, width=32), 0.25), "environment, generic"),
-                         (lambda: scenes.c5(spp=2, variant=variant, n_leaves=100, n_sensors=16), "generic")):   # BVH in HBM
+                         (lambda: scenes.c5(spp=2, variant=variant, n_leaves=100, n_sensors=16),   # BVH in HBM
+                          "homogeneous, large mesh" if variant == "scalar_mono" else "generic")):
         sc = pkg.load_dict(_mis(make()), variant)
         with pkg.DeviceScene(sc) as ds:
             ds.render(seed_mode=abi.SEED_WAVEFRONT)
