@@ -1,4 +1,5 @@
-"""Where the end-to-end time of one render goes (scene upload / render call / teardown). GPU box only."""
+"""Where the end-to-end step of bench.py spends its time: b2vp_scene_create (descriptor -> device), the first render on a
+fresh device scene, the film read-back.  One GPU; wall-clock microseconds, best of 20."""
 import os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -6,19 +7,18 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import __graft_entry__ as ge
 pkg = ge.build()
 import scenes
-from bench import workload
 abi = pkg.abi
-spp = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
-scene = pkg.load_dict(workload(spp))
-for it in range(4):
+sc = pkg.load_dict(scenes.c2(spp=16384, width=256))
+pkg.render(sc, math="fast")   # CUDA up, kernels loaded
+t_create, t_render, t_destroy = [], [], []
+for _ in range(20):
     t0 = time.perf_counter()
-    ds = pkg.DeviceScene(scene, device=0)
+    ds = pkg.DeviceScene(sc, 0)
     t1 = time.perf_counter()
-    r = ds.render(seed_mode=abi.SEED_WAVEFRONT)
+    r = ds.render(math="fast")
     t2 = time.perf_counter()
-    r2 = ds.render(seed_mode=abi.SEED_WAVEFRONT)
-    t3 = time.perf_counter()
     ds.close()
-    t4 = time.perf_counter()
-    print("iter %d: create %.2f ms, first render %.2f ms (kernel %.2f), second render %.2f ms (kernel %.2f), destroy %.2f ms"
-          % (it, (t1 - t0) * 1e3, (t2 - t1) * 1e3, r.totals.gpu_ms, (t3 - t2) * 1e3, r2.totals.gpu_ms, (t4 - t3) * 1e3))
+    t3 = time.perf_counter()
+    t_create.append(t1 - t0); t_render.append(t2 - t1); t_destroy.append(t3 - t2)
+print("scene_create %.0f us, render (incl. lazy upload, kernel %.0f us, read-back) %.0f us, destroy %.0f us" % (
+    min(t_create) * 1e6, r.totals.gpu_ms * 1e3, min(t_render) * 1e6, min(t_destroy) * 1e6))
