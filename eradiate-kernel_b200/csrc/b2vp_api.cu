@@ -1043,6 +1043,10 @@ int plan_launch(b2vp_scene *s, DeviceCtx *dc, DeviceScene<F> &ds, const B2vpRend
            3 and more 56. */
         const bool big_grids = ds.global_grid_bytes > ((size_t) 16 << 20);
         double oversub = big_grids ? 2.0 : 4.0;
+        /* the large-mesh preset (768-thread CTAs): its BVH is read through L1 / L2, and every KB of shared memory the
+           pool does not take is L1 -- C5 fast 153.7 Mpaths/s with the pool that fills shared memory (1.8 slots per
+           thread), 165 at 1.5, **172 at 1.0-1.25** */
+        if (pl.threads > 512) oversub = 1.125;
         if (a->tuning[0]) oversub = std::min(8.0, std::max(1.0, a->tuning[0] / 16.0));
         /* shared memory: [tables][grids][film][queue control + rings][path slots] */
         size_t base = (smem + 127) & ~(size_t) 127;
