@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb2vp.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 OK, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_NO_DEVICE, ERR_CANCELLED = range(6)
 PREC_F32, PREC_F64 = 0, 1
@@ -84,6 +84,10 @@ class Emitter(C.Structure):
     _fields_ = [("type", c_i32), ("reserved0", c_i32), ("direction", c_d * 3), ("irradiance", c_d)]
 
 
+RFILTER_RESOLUTION = 31   # MTS_FILTER_RESOLUTION (include/mitsuba/core/rfilter.h:10)
+RFILTER_MAX_TAPS = 16
+
+
 class Sensor(C.Structure):
     _fields_ = [
         ("type", c_i32), ("direction_type", c_i32), ("target_type", c_i32), ("origin_type", c_i32),
@@ -94,6 +98,8 @@ class Sensor(C.Structure):
         ("transforms", C.POINTER(c_d)),
         ("film_size", c_i32 * 2), ("crop_offset", c_i32 * 2), ("crop_size", c_i32 * 2),
         ("sample_count", c_u32), ("reserved0", c_u32), ("sampler_seed", c_u64),
+        ("rfilter_radius", c_d), ("rfilter_scale", c_d), ("rfilter_taps", c_u32), ("rfilter_border", c_u32),
+        ("rfilter_values", c_d * (RFILTER_RESOLUTION + 1)),
     ]
 
 

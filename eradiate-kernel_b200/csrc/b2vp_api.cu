@@ -289,6 +289,18 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         return fail(B2VP_ERR_INVALID, "sensor medium index out of range");
     if (sn.crop_size[0] <= 0 || sn.crop_size[1] <= 0)
         return fail(B2VP_ERR_INVALID, "empty film");
+    if (sn.rfilter_radius > 0.5) { /* possibly wider than a pixel (the device decides in the scene's precision): the table may be read */
+        if (!(sn.rfilter_radius <= 0.5 * B2VP_RFILTER_MAX_TAPS) || sn.rfilter_taps == 0 ||
+            sn.rfilter_taps > B2VP_RFILTER_MAX_TAPS || !(sn.rfilter_scale > 0))
+            return fail(B2VP_ERR_INVALID, "reconstruction filter: radius %g with %u taps (at most %d taps)",
+                        sn.rfilter_radius, sn.rfilter_taps, B2VP_RFILTER_MAX_TAPS);
+        if ((double) sn.rfilter_border + 0.5 < sn.rfilter_radius - 1e-3)
+            return fail(B2VP_ERR_INVALID, "reconstruction filter: border %u too small for radius %g", sn.rfilter_border,
+                        sn.rfilter_radius);
+        for (int k = 0; k <= B2VP_RFILTER_RESOLUTION; ++k)
+            if (!std::isfinite(sn.rfilter_values[k]))
+                return fail(B2VP_ERR_INVALID, "reconstruction filter: table entry %d is not finite", k);
+    }
     if (sn.n_transforms > 0 && sn.transforms)
         s->sensor_xf.assign(sn.transforms, sn.transforms + (size_t) sn.n_transforms * 16);
     s->desc.sensor.transforms = nullptr;
@@ -582,6 +594,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene
     if (have_tabphase) ft |= FT_TABPHASE;
     if (have_blendphase) ft |= FT_BLENDPHASE;
     if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX || d.sensor.type == B2VP_SENSOR_IRRADIANCEMETER) ft |= FT_DISTANTFLUX;
+    if (d.sensor.rfilter_radius > (double) ((F) 0.5 + K<F>::RayEpsilon)) ft |= FT_RFILTER;   /* imageblock.cpp:117; the box filter's radius is 0.5 + RayEpsilon */
 
     /* blob layout */
     uint32_t off = 0;
@@ -697,6 +710,11 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene
     cvt(sn.reference_normal, o.reference_normal, 3);
     o.n_pixels = sn.film_size[0] * sn.film_size[1]; o.origin_shape = sn.origin_shape;
     for (int k = 0; k < 2; ++k) { o.crop_offset[k] = sn.crop_offset[k]; o.crop_size[k] = sn.crop_size[k]; }
+    /* imageblock.cpp:117: the footprint loop only for a radius above 0.5 + RayEpsilon */
+    const bool wide = sn.rfilter_radius > (double) ((F) 0.5 + K<F>::RayEpsilon);
+    o.rf_taps = wide ? (int) sn.rfilter_taps : 0; o.rf_border = wide ? (int) sn.rfilter_border : 0;
+    o.rf_radius = (F) sn.rfilter_radius; o.rf_scale = (F) sn.rfilter_scale;
+    for (int k = 0; k <= B2VP_RFILTER_RESOLUTION; ++k) o.rf_values[k] = wide ? (F) sn.rfilter_values[k] : (F) 0;
 
     g.max_depth = d.integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) d.integrator.max_depth;
     g.rr_depth = (uint32_t) d.integrator.rr_depth;

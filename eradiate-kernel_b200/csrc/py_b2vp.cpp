@@ -158,9 +158,22 @@ template <typename F> struct Loader {
             const py::dict f = py::cast<py::dict>(d["film"]);
             if (type_of(f) != "hdrfilm") unsupported("film", type_of(f));
             film.width = get<int>(f, "width", 768); film.height = get<int>(f, "height", 576);
-            if (f.contains("rfilter") && type_of(py::cast<py::dict>(f["rfilter"])) != "box")
-                unsupported("reconstruction filter", type_of(py::cast<py::dict>(f["rfilter"])));
-            if (f.contains("crop_width") || f.contains("crop_offset_x")) throw std::runtime_error("hdrfilm: crop windows are not supported by the C++ host");
+            if (f.contains("rfilter")) {   /* src/rfilters/*.cpp */
+                const py::dict r = py::cast<py::dict>(f["rfilter"]);
+                const std::string rt = type_of(r);
+                b2vp::RFilter &rf = film.rfilter;
+                if (rt == "box") { rf.type = b2vp::RFilter::Box; rf.radius = (double) (float) get<double>(r, "radius", 0.5); }
+                else if (rt == "tent") rf.type = b2vp::RFilter::Tent;
+                else if (rt == "gaussian") { rf.type = b2vp::RFilter::Gaussian; rf.stddev = (double) (float) get<double>(r, "stddev", 0.5); }
+                else if (rt == "mitchell") {
+                    rf.type = b2vp::RFilter::Mitchell;
+                    rf.B = (double) (float) get<double>(r, "B", 1.f / 3.f); rf.C = (double) (float) get<double>(r, "C", 1.f / 3.f);
+                } else if (rt == "catmullrom") rf.type = b2vp::RFilter::CatmullRom;
+                else if (rt == "lanczos") { rf.type = b2vp::RFilter::Lanczos; rf.lobes = get<int>(r, "lobes", 3); }
+                else unsupported("reconstruction filter", rt);
+            }
+            film.crop_offset_x = get<int>(f, "crop_offset_x", 0); film.crop_offset_y = get<int>(f, "crop_offset_y", 0);
+            film.crop_width = get<int>(f, "crop_width", film.width); film.crop_height = get<int>(f, "crop_height", film.height);
         }
         const int med = medium_ref(d, "medium");
         if (t == "distant") {

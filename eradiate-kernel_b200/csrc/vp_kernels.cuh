@@ -96,6 +96,55 @@ VP_D uint32_t smem_addr(const void *p) { return (uint32_t) __cvta_generic_to_sha
 VP_D void film_add(float *p, float v) { atomicAdd(p, v); }
 VP_D void film_add(double *p, double v) { atomicAdd(p, v); }
 
+/* ImageBlock::put for a reconstruction filter wider than a pixel (imageblock.cpp:117-152), followed by the
+   film's put(block) (hdrfilm.cpp:207-211, imageblock.cpp:52-76), which keeps what falls inside the crop window.
+   The sample at film position (posx, posy) was drawn in the block at (box, boy) of bsx x bsy pixels; the block
+   carries a border of rf_border pixels on every side, so its pixel (0, 0) is film pixel (box - border, boy -
+   border).  Weights come from the filter's 32-entry table as eval_discretized() reads it (rfilter.h:68-71).
+   Out of line: the box filter of every BASELINE configuration never comes here. */
+template <typename F>
+__device__ __noinline__ void film_put_wide(F *film, const DSensor<F> &sn, int NCH, F posx, F posy, int box, int boy,
+                                           int bsx, int bsy, int ox, int oy, F value, F alpha, F raw) {
+    const int b = sn.rf_border, n = sn.rf_taps;
+    const int W = sn.crop_size[0], H = sn.crop_size[1];
+    const F radius = sn.rf_radius;
+    const F px = posx - ((F) (box - b) + (F) 0.5), py = posy - ((F) (boy - b) + (F) 0.5);
+    const int lox = max((int) ceil_(px - radius), 0), loy = max((int) ceil_(py - radius), 0);
+    const int hix = min((int) floor_(px + radius), bsx + 2 * b - 1), hiy = min((int) floor_(py + radius), bsy + 2 * b - 1);
+    const F basex = (F) lox - px, basey = (F) loy - py;
+    F wx[B2VP_RFILTER_MAX_TAPS], wy[B2VP_RFILTER_MAX_TAPS];
+    for (int i = 0; i < n; ++i) {
+        F qx = (basex + (F) i) * sn.rf_scale, qy = (basey + (F) i) * sn.rf_scale;
+        if (qx < 0) qx = -qx;
+        if (qy < 0) qy = -qy;
+        /* the comparison in F first: int(x) of a huge x is not what min() should see */
+        wx[i] = sn.rf_values[qx < (F) B2VP_RFILTER_RESOLUTION ? (int) qx : B2VP_RFILTER_RESOLUTION];
+        wy[i] = sn.rf_values[qy < (F) B2VP_RFILTER_RESOLUTION ? (int) qy : B2VP_RFILTER_RESOLUTION];
+    }
+    const F raw2 = raw * raw;
+    for (int yr = 0; yr < n; ++yr) {
+        const int y = loy + yr;
+        if (y > hiy) break;
+        const int fy = y - b + boy - oy;
+        for (int xr = 0; xr < n; ++xr) {
+            const int x = lox + xr;
+            if (x > hix) break;
+            const int fx = x - b + box - ox;
+            if (fx < 0 || fy < 0 || fx >= W || fy >= H) continue;
+            const F weight = wy[yr] * wx[xr];
+            F *p = film + ((size_t) fy * W + fx) * NCH;
+            const F v = value * weight;
+            film_add(p, v); film_add(p + 1, v); film_add(p + 2, v);
+            film_add(p + 3, alpha * weight); film_add(p + 4, weight);
+            if (NCH > 5) { /* moment.cpp:78-83 */
+                const F a = raw * weight, a2 = raw2 * weight;
+                film_add(p + 5, a); film_add(p + 6, a); film_add(p + 7, a);
+                film_add(p + 8, a2); film_add(p + 9, a2); film_add(p + 10, a2);
+            }
+        }
+    }
+}
+
 /* CTA prologue: stage the scene tables and the small grids in shared memory. */
 template <typename F>
 VP_D void stage_scene(const DScene<F> &g, const RenderOut<F> &out, unsigned char *smem, SceneView<F> &sv) {
@@ -212,6 +261,10 @@ volpath_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DStr
             if (!ok) { tot[TOT_INVALID]++; continue; }
             F bx = posx - ((F) st.box + (F) 0.5), by = posy - ((F) st.boy + (F) 0.5);
             int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
+            if (sn.rf_taps > 0) {
+                film_put_wide(film, sn, C, posx, posy, st.box, st.boy, st.bsx, st.bsy, sp.ox, sp.oy, value, alpha, raw_value);
+                continue;
+            }
             if (lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy) continue;
             int fx = lx + st.box - sp.ox, fy = ly + st.boy - sp.oy;
             if (C > 5) { /* moment.cpp:78-83: the nested integrator's X Y Z (without the ray weight) and squares */

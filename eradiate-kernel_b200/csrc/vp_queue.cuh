@@ -1022,7 +1022,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     } else {
                         F bx = c.posx - ((F) box + (F) 0.5), by = c.posy - ((F) boy + (F) 0.5);
                         int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
-                        if (!(lx < 0 || ly < 0 || lx >= bsx || ly >= bsy)) {
+                        if ((FEAT & FT_RFILTER) && sn.rf_taps > 0) {
+                            film_put_wide(film, sn, NCH, c.posx, c.posy, box, boy, bsx, bsy, sp.ox, sp.oy, value, alpha, c.result);
+                        } else if (!(lx < 0 || ly < 0 || lx >= bsx || ly >= bsy)) {
                             int fx = lx + box - sp.ox, fy = ly + boy - sp.oy;
                             if (NCH > 5) { /* moment.cpp:78-83: the nested integrator's X Y Z (without the ray weight) and squares */
                                 F *q = film + ((size_t) fy * W + fx) * NCH + 5;

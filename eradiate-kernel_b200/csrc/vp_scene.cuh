@@ -72,7 +72,7 @@ enum : uint32_t {
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
     FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter       */
-    FT_RESERVED16 = 1u << 16,  /* (was: interleaved launches; the index map is part of every instance now) */
+    FT_RFILTER = 1u << 16,     /* the film's reconstruction filter is wider than a pixel (no preset: generic instances) */
     FT_GRID_SMEM = 1u << 17,   /* some grid is staged in shared memory                    */
     FT_GRID_GLOBAL = 1u << 18, /* some grid is read from global memory                    */
     FT_MESH_SMEM = 1u << 19,   /* triangle meshes whose BVH and triangles are staged in shared memory (small meshes) */

@@ -7,6 +7,7 @@
  */
 #pragma once
 #include "vp_math.cuh"
+#include "../../include/b2vp.h"   /* B2VP_RFILTER_RESOLUTION, B2VP_RFILTER_MAX_TAPS */
 
 namespace VP_NS {
 
@@ -268,6 +269,11 @@ template <typename F> struct DSensor {
     F reference_normal[3];           /* distantflux */
     int crop_offset[2], crop_size[2];
     int n_pixels, origin_shape;      /* distantflux: film width * height; irradiancemeter: the parent rectangle */
+    /* reconstruction filter wider than a pixel (rf_taps == 0: the box filter, one pixel per sample): radius,
+       table scale, footprint taps, block border and the discretised table (rfilter.h:55-98, rfilter.cpp:9-21) */
+    int rf_taps, rf_border;
+    F rf_radius, rf_scale;
+    F rf_values[B2VP_RFILTER_RESOLUTION + 1];
 };
 
 /* 32-byte BVH node over the scene-wide triangle pool.  count == 0: inner node

@@ -405,7 +405,9 @@ volpath_wf_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ D
                 } else {
                     F bx = posx - ((F) st.box + (F) 0.5), by = posy - ((F) st.boy + (F) 0.5);
                     int lx = (int) ceil_(bx - (F) 0.5), ly = (int) ceil_(by - (F) 0.5);
-                    if (!(lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy)) {
+                    if (sn.rf_taps > 0) {
+                        film_put_wide(film, sn, C, posx, posy, st.box, st.boy, st.bsx, st.bsy, sp.ox, sp.oy, value, alpha, result);
+                    } else if (!(lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy)) {
                         int fx = lx + st.box - sp.ox, fy = ly + st.boy - sp.oy;
                         if (C > 5) { /* moment.cpp:78-83: the nested integrator's X Y Z (without the ray weight) and squares */
                             F *q = film + ((size_t) fy * W + fx) * C + 5;

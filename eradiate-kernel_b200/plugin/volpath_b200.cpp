@@ -359,8 +359,19 @@ template <typename Float, typename Spectrum> struct B200Describe {
         const Sampler *sampler = sn->m_sampler.get();
         if (cname(film) != "HDRFilm") unsupported("film " + cname(film));
         if (cname(sampler) != "IndependentSampler") unsupported("sampler " + cname(sampler));
-        if (film->reconstruction_filter()->radius() > 0.5f + math::RayEpsilon<float>)
-            unsupported("reconstruction filters wider than the box filter");
+        {   /* the film's reconstruction filter, through its public interface only (rfilter.h:55-71): the table is
+               read back entry by entry with eval_discretized() at the centre of each of its cells */
+            const ReconstructionFilter<Float, Spectrum> *rf = film->reconstruction_filter();
+            const ScalarFloat radius = rf->radius(), scale = ScalarFloat(MTS_FILTER_RESOLUTION) / radius;   /* rfilter.cpp:19 */
+            o.rfilter_radius = (double) radius; o.rfilter_scale = (double) scale;
+            o.rfilter_border = rf->border_size();
+            o.rfilter_taps = enoki::ceil2int<uint32_t>((radius - 2.f * math::RayEpsilon<ScalarFloat>) * 2.f);   /* imageblock.cpp:122 */
+            for (int i = 0; i <= MTS_FILTER_RESOLUTION; ++i)
+                o.rfilter_values[i] = (double) rf->eval_discretized((ScalarFloat(i) + ScalarFloat(0.5)) / scale);
+            static_assert(MTS_FILTER_RESOLUTION == B2VP_RFILTER_RESOLUTION, "filter table size");
+            if (radius > 0.5f + math::RayEpsilon<Float> && o.rfilter_taps > B2VP_RFILTER_MAX_TAPS)
+                unsupported("reconstruction filters wider than " + std::to_string(B2VP_RFILTER_MAX_TAPS / 2) + " pixels");
+        }
         o.film_size[0] = film->size().x(); o.film_size[1] = film->size().y();
         o.crop_offset[0] = film->crop_offset().x(); o.crop_offset[1] = film->crop_offset().y();
         o.crop_size[0] = film->crop_size().x(); o.crop_size[1] = film->crop_size().y();
@@ -643,11 +654,12 @@ public:
                 channels.push_back(name);
         film->prepare(channels);
         ScalarVector2i size = film->crop_size();
-        ref<ImageBlock> block = new ImageBlock(size, channels.size(), film->reconstruction_filter(), false);
+        /* b2vp_render returns the film of the crop window with the reconstruction filter applied and the part of the
+           footprints outside the window already dropped, which is what the film's put(block) would do to a bordered
+           block (imageblock.cpp:52-76): so this block has no border */
+        ref<ImageBlock> block = new ImageBlock(size, channels.size(), film->reconstruction_filter(), false, true, false);
         block->set_offset(film->crop_offset());
         block->clear();
-        if (block->border_size() != 0)
-            Throw("volpath_b200: only the box reconstruction filter is supported");
 
         m_render_timer.reset();
         B2vpRenderArgs args{};

@@ -9,6 +9,7 @@ scalar_mono_double).  Content outside SURVEY.md section 8 raises, like an unknow
 plugin name does in the reference.
 """
 import ctypes as C
+import math
 import os
 import struct
 import zlib
@@ -265,6 +266,81 @@ def read_ply(path):
     if pos is None or faces is None:
         fail("vertex / face element not found")
     return pos, faces, nrm, uv
+
+
+
+def rfilter_table(node, dtype):
+    """The film's reconstruction filter as ImageBlock::put reads it: radius, the 32-entry table of
+    ReconstructionFilter::init_discretization (src/libcore/rfilter.cpp:9-21) with its scale factor and border, and the
+    footprint width of imageblock.cpp:122.  The filters are src/rfilters/{box,tent,gaussian,mitchell,catmullrom,
+    lanczos}.cpp, evaluated in the variant's scalar type `dtype`; exp and sin are taken in double and rounded, which
+    is where a single-precision table can differ from the reference's expf/sinf by one unit in the last place."""
+    f = dtype
+    t = node.get("type", "box")
+    eps = f(np.finfo(dtype).eps) / f(2)
+    ray_eps = eps * f(1500)                                    # math.h:36-37
+    known = {"box": ("radius",), "tent": (), "gaussian": ("stddev",), "mitchell": ("B", "C"), "catmullrom": (),
+             "lanczos": ("lobes",)}
+    if t not in known:
+        raise RuntimeError("reconstruction filter plugin %r is not supported by the B200 volpath" % t)
+    for key in node:
+        if key not in ("type", "id") + known[t]:
+            raise RuntimeError("Unreferenced property %r in plugin of type %r" % (key, t))
+    if t == "box":
+        radius = f(np.float32(node.get("radius", 0.5))) + ray_eps   # box.cpp:28; Properties keeps floats in single precision
+        ev = lambda x: f(1) if abs(x) <= radius else f(0)
+    elif t == "tent":
+        radius = f(1)
+        inv = f(1) / radius
+        ev = lambda x: max(f(0), f(1) - abs(x * inv))
+    elif t == "gaussian":
+        stddev = f(np.float32(node.get("stddev", 0.5)))
+        radius = f(4) * stddev                                 # gaussian.cpp:31-36
+        alpha = f(-1) / (f(2) * stddev * stddev)
+        bias = f(math.exp(float(alpha * (radius * radius))))
+        ev = lambda x: max(f(0), f(math.exp(float(alpha * (x * x)))) - bias)
+    elif t in ("mitchell", "catmullrom"):
+        radius = f(2)
+        third = np.float32(1) / np.float32(3)                  # the defaults and 1/6 are float literals in every variant
+        B = f(np.float32(node.get("B", third))) if t == "mitchell" else f(0)
+        Cc = f(np.float32(node.get("C", third))) if t == "mitchell" else f(0.5)
+        sixth = f(np.float32(1) / np.float32(6))
+
+        def ev(x):                                             # mitchell.cpp:40-53, catmullrom.cpp:27-42
+            x = abs(x)
+            x2 = x * x
+            x3 = x2 * x
+            if x < 1:
+                r = (f(12) - f(9) * B - f(6) * Cc) * x3 + (f(-18) + f(12) * B + f(6) * Cc) * x2 + (f(6) - f(2) * B)
+            else:
+                r = ((-B - f(6) * Cc) * x3 + (f(6) * B + f(30) * Cc) * x2 + (f(-12) * B - f(48) * Cc) * x
+                     + (f(8) * B + f(24) * Cc))
+            return sixth * r if x < 2 else f(0)
+    else:                                                      # lanczos.cpp:34-48
+        radius = f(int(node.get("lobes", 3)))
+        pi = f(math.pi)
+
+        def ev(x):
+            x = abs(x)
+            if x < eps:
+                return f(1)
+            if x > radius:
+                return f(0)
+            x1 = pi * x
+            x2 = x1 / radius
+            return f(f(math.sin(float(x1))) * f(math.sin(float(x2)))) / (x1 * x2)
+    if not radius > 0:
+        raise RuntimeError("reconstruction filter: the radius must be positive")
+    res = abi.RFILTER_RESOLUTION
+    with np.errstate(all="ignore"):
+        values = [float(f(ev((radius * f(i)) / f(res)))) for i in range(res)] + [0.0]
+        scale = f(res) / radius
+        border = int(math.ceil(float(radius - f(0.5) - f(2) * ray_eps)))
+        taps = int(math.ceil(float((radius - f(2) * ray_eps) * f(2))))
+    if radius > f(0.5) + ray_eps and taps > abi.RFILTER_MAX_TAPS:
+        raise RuntimeError("reconstruction filter: a radius of %g pixels is more than the B200 volpath carries (%g)"
+                           % (float(radius), abi.RFILTER_MAX_TAPS / 2))
+    return {"radius": float(radius), "scale": float(scale), "taps": taps, "border": max(border, 0), "values": values}
 
 
 class _Builder:
@@ -662,9 +738,10 @@ class _Builder:
         film = node.get("film", {"type": "hdrfilm"})
         if film.get("type", "hdrfilm") != "hdrfilm":
             raise RuntimeError("film plugin %r is not supported by the B200 volpath" % film["type"])
-        rf = film.get("rfilter", {"type": "box"})
-        if rf.get("type", "box") != "box":
-            raise RuntimeError("only the box reconstruction filter is supported by the B200 volpath")
+        rf = rfilter_table(film.get("rfilter", {"type": "box"}), dtp)
+        sn.rfilter_radius, sn.rfilter_scale = rf["radius"], rf["scale"]
+        sn.rfilter_taps, sn.rfilter_border = rf["taps"], rf["border"]
+        sn.rfilter_values[:] = rf["values"]
         w, h = int(film.get("width", 768)), int(film.get("height", 576))
         sn.film_size[:] = [w, h]
         sn.crop_offset[:] = [int(film.get("crop_offset_x", 0)), int(film.get("crop_offset_y", 0))]

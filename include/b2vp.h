@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define B2VP_ABI_VERSION 3u
+#define B2VP_ABI_VERSION 4u
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -203,6 +203,9 @@ typedef struct B2vpEmitter {
     double irradiance;
 } B2vpEmitter;
 
+#define B2VP_RFILTER_RESOLUTION 31   /* MTS_FILTER_RESOLUTION (rfilter.h:10) */
+#define B2VP_RFILTER_MAX_TAPS 16     /* footprint bound of the device code: radius <= 8 pixels */
+
 typedef struct B2vpSensor {
     int32_t type;              /* B2VP_SENSOR_*                                */
     int32_t direction_type;    /* distant: B2VP_DIR_*                          */
@@ -226,6 +229,16 @@ typedef struct B2vpSensor {
     uint32_t sample_count;     /* sampler->sample_count()                      */
     uint32_t reserved0;
     uint64_t sampler_seed;     /* independent sampler `seed` property          */
+    /* reconstruction filter of the film (include/mitsuba/core/rfilter.h:55-98, src/libcore/rfilter.cpp:9-21).
+       rfilter_radius <= 0.5 + RayEpsilon (the default `box`): every sample lands in the one pixel under it
+       (imageblock.cpp:153-160) and the other fields are not read.  Wider filters (tent, gaussian, mitchell,
+       catmullrom, lanczos, a wide box): ImageBlock::put's footprint loop (imageblock.cpp:117-152) with
+       eval_discretized() over this table */
+    double rfilter_radius;     /* m_radius                                     */
+    double rfilter_scale;      /* m_scale_factor = MTS_FILTER_RESOLUTION / m_radius, in the variant's float type */
+    uint32_t rfilter_taps;     /* n of imageblock.cpp:122: ceil((radius - 2 RayEpsilon) * 2) */
+    uint32_t rfilter_border;   /* m_border_size (rfilter.cpp:20)               */
+    double rfilter_values[B2VP_RFILTER_RESOLUTION + 1]; /* m_values; the last one is 0 */
 } B2vpSensor;
 
 typedef struct B2vpIntegrator {

@@ -181,7 +181,19 @@ struct Directional { std::array<double, 3> direction{ 0, 0, 1 }; double irradian
 /* src/emitters/constant.cpp:35-40: the environment emitter */
 struct Constant { double radiance = 1.0; };
 /* src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp */
-struct HdrFilm { int width = 768, height = 576; };
+/* src/rfilters/{box,tent,gaussian,mitchell,catmullrom,lanczos}.cpp: the film's reconstruction filter */
+struct RFilter {
+    enum Type { Box, Tent, Gaussian, Mitchell, CatmullRom, Lanczos } type = Box;
+    double radius = 0.5;                       /* box.cpp:28 (RayEpsilon is added to it) */
+    double stddev = 0.5;                       /* gaussian.cpp:31 */
+    double B = 1.f / 3.f, C = 1.f / 3.f;       /* mitchell.cpp:34-36: float literals in every variant */
+    int lobes = 3;                             /* lanczos.cpp:34 */
+};
+struct HdrFilm {
+    int width = 768, height = 576;
+    RFilter rfilter{};
+    int crop_offset_x = 0, crop_offset_y = 0, crop_width = -1, crop_height = -1;   /* film.cpp:30-63; -1 = the whole film */
+};
 struct IndependentSampler { uint32_t sample_count = 4; uint64_t seed = 0; };
 /* src/sensors/distant.cpp:225-290 */
 struct Distant {
@@ -583,13 +595,67 @@ private:
     }
     B2vpSensor base_sensor(const HdrFilm &film, const IndependentSampler &sampler, int medium) {
         B2vpSensor o{};
-        o.film_size[0] = o.crop_size[0] = film.width; o.film_size[1] = o.crop_size[1] = film.height;
+        o.film_size[0] = film.width; o.film_size[1] = film.height;
+        o.crop_offset[0] = film.crop_offset_x; o.crop_offset[1] = film.crop_offset_y;
+        o.crop_size[0] = film.crop_width < 0 ? film.width : film.crop_width;
+        o.crop_size[1] = film.crop_height < 0 ? film.height : film.crop_height;
+        for (int k = 0; k < 2; ++k)   /* Film::set_crop_window (film.cpp:54-63) */
+            if (o.crop_offset[k] < 0 || o.crop_size[k] <= 0 || o.crop_offset[k] + o.crop_size[k] > o.film_size[k])
+                throw Error(B2VP_ERR_INVALID, "Invalid crop window specification!");
+        rfilter_table(film.rfilter, o);
         o.sample_count = sampler.sample_count; o.sampler_seed = sampler.seed;
         o.medium = medium; o.target_shape = o.origin_shape = -1;
         o.to_world = Mat4<F>().pod();
         return o;
     }
     void expand(const Vec3<F> &p) { for (int k = 0; k < 3; ++k) { bmin_[k] = std::min(bmin_[k], p[k]); bmax_[k] = std::max(bmax_[k], p[k]); } }
+
+    /* ReconstructionFilter::init_discretization (src/libcore/rfilter.cpp:9-21) over the eval() of the six filter
+       plugins, in the variant's scalar type, plus the footprint width ImageBlock::put derives (imageblock.cpp:122) */
+    static void rfilter_table(const RFilter &rf, B2vpSensor &o) {
+        const F eps = std::numeric_limits<F>::epsilon() / 2, ray_eps = eps * 1500;   /* math.h:36-37 */
+        F radius = 0;
+        const F stddev = (F) rf.stddev, alpha = (F) -1 / ((F) 2 * stddev * stddev);
+        const F B = rf.type == RFilter::Mitchell ? (F) rf.B : (F) 0, C = rf.type == RFilter::Mitchell ? (F) rf.C : (F) 0.5;
+        switch (rf.type) {
+            case RFilter::Box: radius = (F) rf.radius + ray_eps; break;
+            case RFilter::Tent: radius = 1; break;
+            case RFilter::Gaussian: radius = (F) 4 * stddev; break;
+            case RFilter::Mitchell: case RFilter::CatmullRom: radius = 2; break;
+            case RFilter::Lanczos: radius = (F) rf.lobes; break;
+        }
+        if (!(radius > 0)) throw Error(B2VP_ERR_INVALID, "reconstruction filter: the radius must be positive");
+        const F bias = std::exp(alpha * (radius * radius));
+        auto eval = [&](F x) -> F {
+            x = std::abs(x);
+            switch (rf.type) {
+                case RFilter::Box: return x <= radius ? (F) 1 : (F) 0;
+                case RFilter::Tent: return std::max((F) 0, (F) 1 - std::abs(x * ((F) 1 / radius)));
+                case RFilter::Gaussian: return std::max((F) 0, std::exp(alpha * (x * x)) - bias);
+                case RFilter::Mitchell: case RFilter::CatmullRom: {
+                    const F x2 = x * x, x3 = x2 * x;
+                    const F r = x < 1 ? ((F) 12 - (F) 9 * B - (F) 6 * C) * x3 + ((F) -18 + (F) 12 * B + (F) 6 * C) * x2 + ((F) 6 - (F) 2 * B)
+                                      : (-B - (F) 6 * C) * x3 + ((F) 6 * B + (F) 30 * C) * x2 + ((F) -12 * B - (F) 48 * C) * x + ((F) 8 * B + (F) 24 * C);
+                    return x < 2 ? (F) (1.f / 6.f) * r : (F) 0;
+                }
+                default: {
+                    if (x < eps) return 1;
+                    if (x > radius) return 0;
+                    const F x1 = (F) 3.14159265358979323846 * x, x2 = x1 / radius;
+                    return (std::sin(x1) * std::sin(x2)) / (x1 * x2);
+                }
+            }
+        };
+        for (int i = 0; i < B2VP_RFILTER_RESOLUTION; ++i) o.rfilter_values[i] = (double) eval((radius * (F) i) / (F) B2VP_RFILTER_RESOLUTION);
+        o.rfilter_values[B2VP_RFILTER_RESOLUTION] = 0;
+        o.rfilter_radius = (double) radius;
+        o.rfilter_scale = (double) ((F) B2VP_RFILTER_RESOLUTION / radius);
+        o.rfilter_border = (uint32_t) std::max(0, (int) std::ceil(radius - (F) 0.5 - (F) 2 * ray_eps));
+        o.rfilter_taps = (uint32_t) std::ceil((radius - (F) 2 * ray_eps) * (F) 2);
+        if (radius > (F) 0.5 + ray_eps && o.rfilter_taps > B2VP_RFILTER_MAX_TAPS)
+            throw Error(B2VP_ERR_UNSUPPORTED, "reconstruction filter: a radius of " + std::to_string((double) radius) +
+                                              " pixels is more than the B200 volpath carries");
+    }
 
     std::unique_ptr<Scene> sc_;
     F bmin_[3], bmax_[3];

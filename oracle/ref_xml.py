@@ -247,7 +247,14 @@ class _Writer:
         for key in ("width", "height", "crop_offset_x", "crop_offset_y", "crop_width", "crop_height"):
             if key in f:
                 out.append('<integer name="%s" value="%d"/>' % (key, f[key]))
-        out.append('<rfilter type="%s"/>' % f.get("rfilter", {"type": "box"}).get("type", "box"))
+        rf = f.get("rfilter", {"type": "box"})
+        out.append('<rfilter type="%s">' % rf.get("type", "box"))
+        for key in ("radius", "stddev", "B", "C"):
+            if key in rf:
+                out.append('<float name="%s" value="%r"/>' % (key, float(rf[key])))
+        if "lobes" in rf:
+            out.append('<integer name="lobes" value="%d"/>' % rf["lobes"])
+        out.append("</rfilter>")
         out.append("</film></sensor>")
         return "".join(out)
 

@@ -1906,6 +1906,43 @@ int render_typed(const B2vpSceneDesc *d, const B2vpRenderArgs *a, F *film) {
             bool is_valid = true;
             for (int c = 0; c < 5 && C == 5; ++c) is_valid = is_valid && aovs[c] >= (F) -1e-5f && std::isfinite(aovs[c]);
             if (!is_valid) { tot.n_invalid_samples++; continue; }
+            if (sn.rfilter_radius > (double) ((F) 0.5 + Consts<F>::RayEpsilon)) {
+                /* ImageBlock::put with a filter wider than a pixel (imageblock.cpp:117-152).  The block of this
+                   stream has a border of m_border_size pixels (integrator.cpp:114-116, rfilter.cpp:20); the film's
+                   own put(block) then adds the block to the storage, which has no border, and so drops what lies
+                   outside the crop window (hdrfilm.cpp:201-211, imageblock.cpp:52-76). */
+                const int border = (int) sn.rfilter_border;
+                const F radius = (F) sn.rfilter_radius, scale = (F) sn.rfilter_scale;
+                const int size_x = st.bsx + 2 * border, size_y = st.bsy + 2 * border;
+                const F qx = posx - ((F) (st.box - border) + (F) 0.5), qy = posy - ((F) (st.boy - border) + (F) 0.5);
+                const int lo_x = std::max(ceil2int(qx - radius), 0), lo_y = std::max(ceil2int(qy - radius), 0);
+                const int hi_x = std::min((int) std::floor(qx + radius), size_x - 1),
+                          hi_y = std::min((int) std::floor(qy + radius), size_y - 1);
+                const uint32_t n = sn.rfilter_taps;
+                std::vector<F> weights_x(n), weights_y(n);
+                auto eval_discretized = [&](F x) { /* rfilter.h:68-71 */
+                    const int index = std::min((int) std::abs(x * scale), B2VP_RFILTER_RESOLUTION);
+                    return (F) sn.rfilter_values[index];
+                };
+                for (uint32_t i = 0; i < n; ++i) {
+                    weights_x[i] = eval_discretized(((F) lo_x - qx) + (F) i);
+                    weights_y[i] = eval_discretized(((F) lo_y - qy) + (F) i);
+                }
+                for (uint32_t yr = 0; yr < n; ++yr) {
+                    const int y = lo_y + (int) yr;
+                    bool enabled = y <= hi_y;
+                    for (uint32_t xr = 0; xr < n; ++xr) {
+                        const int x = lo_x + (int) xr;
+                        const F weight = weights_y[yr] * weights_x[xr];
+                        enabled = enabled && x <= hi_x;
+                        if (!enabled) continue;
+                        const int fx = x - border + st.box - sp.ox, fy = y - border + st.boy - sp.oy;
+                        if (fx < 0 || fy < 0 || fx >= (int) sp.w || fy >= (int) sp.h) continue; /* the film's put */
+                        for (int c = 0; c < C; ++c) film[((size_t) fy * sp.w + fx) * C + c] += aovs[c] * weight;
+                    }
+                }
+                continue;
+            }
             F bx = posx - ((F) st.box + (F) 0.5), by = posy - ((F) st.boy + (F) 0.5);
             int lx = ceil2int(bx - (F) 0.5), ly = ceil2int(by - (F) 0.5);
             if (lx < 0 || ly < 0 || lx >= st.bsx || ly >= st.bsy) continue;

@@ -324,11 +324,44 @@ CASES = {
 }
 
 
+def _rfilter(d, rfilter, width, height, **film):
+    """The scene with a two-dimensional film under a reconstruction filter wider than a pixel
+    (src/rfilters/*.cpp, src/librender/imageblock.cpp:117-152; VERDICT missing #6)."""
+    d["sensor"]["film"] = dict({"type": "hdrfilm", "width": width, "height": height, "rfilter": rfilter}, **film)
+    return d
+
+
+_CROP = {"crop_offset_x": 3, "crop_offset_y": 2, "crop_width": 17, "crop_height": 7}
+
+# films under wide reconstruction filters: weights and alpha are sums of products, not counts, so these are compared
+# by tests/test_rfilter.py with its own check (not by check_against_reference, which wants integer weights).  Single
+# precision: one sample per pixel mostly, so that a path that diverges from the reference binary
+# cannot move the position of the next sample of its stream and with it a whole footprint of weights
+RFILTER_CASES = {
+    "rf_gaussian": (lambda v: _rfilter(scenes.c2(spp=2, variant=v, block_size=8), {"type": "gaussian"}, 24, 10), "scalar_mono"),
+    "rf_gaussian_f64": (lambda v: _rfilter(scenes.c2(spp=2, variant=v, block_size=8), {"type": "gaussian"}, 24, 10), "scalar_mono_double"),
+    "rf_gaussian_wide_f64": (lambda v: _rfilter(scenes.c2(spp=1, variant=v), {"type": "gaussian", "stddev": 0.8}, 16, 12), "scalar_mono_double"),
+    "rf_tent_crop_f64": (lambda v: _rfilter(scenes.c2(spp=2, variant=v, block_size=4), {"type": "tent"}, 24, 12, **_CROP), "scalar_mono_double"),
+    "rf_tent_crop": (lambda v: _rfilter(scenes.c2(spp=1, variant=v, block_size=4), {"type": "tent"}, 24, 12, **_CROP), "scalar_mono"),
+    "rf_mitchell": (lambda v: _rfilter(scenes.c2(spp=1, variant=v, block_size=16), {"type": "mitchell"}, 20, 9), "scalar_mono"),
+    "rf_mitchell_bc_f64": (lambda v: _rfilter(scenes.c2(spp=1, variant=v), {"type": "mitchell", "B": 0.2, "C": 0.4}, 20, 9), "scalar_mono_double"),
+    "rf_catmullrom_f64": (lambda v: _rfilter(scenes.c2(spp=1, variant=v, block_size=8), {"type": "catmullrom"}, 20, 9), "scalar_mono_double"),
+    "rf_lanczos_f64": (lambda v: _rfilter(scenes.c2(spp=1, variant=v, block_size=8), {"type": "lanczos"}, 20, 9), "scalar_mono_double"),
+    "rf_lanczos2": (lambda v: _rfilter(scenes.c2(spp=1, variant=v), {"type": "lanczos", "lobes": 2}, 20, 9), "scalar_mono"),
+    "rf_box_wide": (lambda v: _rfilter(scenes.c2(spp=2, variant=v, block_size=4), {"type": "box", "radius": 1.2}, 13, 10), "scalar_mono"),
+    "rf_gaussian_moment": (lambda v: _moment(_rfilter(scenes.c2(spp=1, variant=v, block_size=8), {"type": "gaussian"}, 16, 8)), "scalar_mono"),
+    "rf_gaussian_volpathmis_f64": (lambda v: _mis(_rfilter(scenes.c2(spp=1, variant=v), {"type": "gaussian"}, 16, 8)), "scalar_mono_double"),
+    "rf_c5_tent_row": (lambda v: _rfilter(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=64), {"type": "tent"}, 64, 1), "scalar_mono"),
+    "rf_c3_gaussian_f64": (lambda v: _rfilter(_c3(spp=1, variant=v, n=16, size=16, block_size=8), {"type": "gaussian"}, 16, 16), "scalar_mono_double"),
+}
+ALL_CASES = dict(CASES, **RFILTER_CASES)
+
+
 def scene_dict(name):
     """The dictionary both sides load: every number rounded to float32 (what the reference's XML parser and
     Properties keep, xml.cpp:100-103, properties.h:55)."""
     from oracle import ref_xml
-    fn, variant = CASES[name]
+    fn, variant = ALL_CASES[name]
     return ref_xml.round_f32(fn(variant)), variant
 
 
@@ -340,13 +373,13 @@ def main():
     path = os.path.join(HERE, "ref_golden.npz")
     only = sys.argv[1:]   # names given: render those and keep the other films of the existing file
     out = dict(np.load(path)) if only else {}
-    for name in (only or CASES):
+    for name in (only or ALL_CASES):
         d, variant = scene_dict(name)
         film, sec = ref_xml.render(d, variant, threads=1, write_vol=pkg.scene.write_vol)
         out[name] = film
         print("%-18s %-20s %4d x %-4d mean %.7g  (%.3f s)" % (name, variant, film.shape[1], film.shape[0],
                                                              film[..., 1].sum() / film[..., 4].sum(), sec))
-    np.savez_compressed(path, **{k: out[k] for k in CASES})
+    np.savez_compressed(path, **{k: out[k] for k in ALL_CASES})
     print("wrote", len(out), "reference films")
 
 

@@ -89,5 +89,5 @@ def test_hdrfilm_crops_and_parameters(pkg):
         _film_scene(pkg, pixel_format="brga")
     with pytest.raises(RuntimeError, match="file_format"):
         _film_scene(pkg, file_format="png")
-    with pytest.raises(RuntimeError, match="box"):
-        _film_scene(pkg, rfilter={"type": "gaussian", "stddev": 18.5})   # wider filters: out of scope, refused by name
+    with pytest.raises(RuntimeError, match="radius of 74 pixels"):
+        _film_scene(pkg, rfilter={"type": "gaussian", "stddev": 18.5})   # footprints of up to 16 x 16 pixels are carried (tests/test_rfilter.py)

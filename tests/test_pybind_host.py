@@ -28,7 +28,18 @@ def _cases(pkg, tmp_path):
         "ext_mradiancemeter": lambda v: ext_dict(pkg, tmp_path, v, "mradiancemeter", 16),
         "c2_sky_moment": lambda v: dict(scenes.c2(spp=4, variant=v, width=16), sky={"type": "constant", "radiance": 0.25},
                                         integrator={"type": "moment", "nested": {"type": "volpath", "max_depth": -1}}),
+        # reconstruction filters wider than a pixel and a crop window (include/b2vp.hpp: RFilter, HdrFilm)
+        "c2_tent_crop": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "tent"}, crop_offset_x=2, crop_offset_y=1,
+                                        crop_width=9, crop_height=5),
+        "c2_gaussian": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "gaussian", "stddev": 0.7}),
+        "c2_mitchell": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "mitchell", "B": 0.25, "C": 0.5}),
+        "c2_lanczos": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "lanczos", "lobes": 2}),
     }
+
+
+def _film(d, rfilter, **crop):
+    d["sensor"]["film"] = dict({"type": "hdrfilm", "width": 12, "height": 7, "rfilter": rfilter}, **crop)
+    return d
 
 
 def _as_host_scene(pkg, s):
@@ -37,7 +48,8 @@ def _as_host_scene(pkg, s):
     return pkg.scene.Scene(desc, s.variant, desc.precision, [s])
 
 
-NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment"]
+NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment",
+         "c2_tent_crop", "c2_gaussian", "c2_mitchell", "c2_lanczos"]
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
@@ -49,7 +61,12 @@ def test_pybind_load_dict_is_the_ctypes_load_dict(pkg, oracle, name, variant, tm
     ours = oracle.render(pkg, _as_host_scene(pkg, s), pkg.abi.SEED_WAVEFRONT)
     ref = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_WAVEFRONT)
     assert s.film_size == ref.film.shape[1::-1]
-    assert np.array_equal(ours.film[..., 3:5], ref.film[..., 3:5])
+    if name == "c2_lanczos" and variant == "scalar_mono":
+        # the one table that goes through sinf: libm's here, a rounded double sine in the Python host (one unit in the
+        # last place apart on a few entries; the reference binary's film accepts both, tests/test_rfilter.py)
+        assert np.allclose(ours.film[..., 3:5], ref.film[..., 3:5], rtol=1e-6, atol=0)
+    else:
+        assert np.array_equal(ours.film[..., 3:5], ref.film[..., 3:5])
     assert ours.totals.n_rng_draws == ref.totals.n_rng_draws and ours.totals.n_intersect == ref.totals.n_intersect
     tol = 1e-12 if variant == "scalar_mono_double" else 1e-5
     assert np.allclose(ours.film, ref.film, rtol=tol, atol=0)
@@ -58,8 +75,8 @@ def test_pybind_load_dict_is_the_ctypes_load_dict(pkg, oracle, name, variant, tm
 def test_pybind_rejects_what_the_cpp_host_does_not_cover(pkg, tmp_path):
     ext = _ext(pkg)
     d = scenes.c2(spp=1, width=4)
-    d["sensor"]["film"]["rfilter"] = {"type": "gaussian"}
-    with pytest.raises(RuntimeError, match="gaussian"):
+    d["sensor"]["film"]["rfilter"] = {"type": "sinc"}
+    with pytest.raises(RuntimeError, match="sinc"):
         ext.load_dict(d)
     d = scenes.c2(spp=1, width=4)
     d["atm"]["phase"] = {"type": "blendphase"}

@@ -78,7 +78,7 @@ def test_plugin_self_check_reads_canaries_of_every_opened_class(pkg, tmp_path):
 def test_plugin_rejects_content_outside_the_scope(pkg):
     ref_xml = ref_xml_or_skip()
     d, variant = make_ref_golden.scene_dict("c2_paths")
-    d["sensor"]["film"]["rfilter"] = {"type": "gaussian"}   # a reconstruction filter wider than a pixel
+    d["sensor"]["film"]["rfilter"] = {"type": "gaussian", "stddev": 5.0}   # a footprint of 40 x 40 pixels (carried: 16 x 16)
     with pytest.raises(RuntimeError, match="outside the scope"):
         ref_xml.render(ref_xml.with_plugin(d), variant, write_vol=pkg.scene.write_vol, describe_oracle=True)
 
