@@ -50,7 +50,7 @@ class Shape(C.Structure):
         ("inv_surface_area", c_d), ("center", c_d * 3), ("radius", c_d),
         ("flip_normals", c_i32),
         ("vertex_offset", c_u32), ("vertex_count", c_u32), ("face_offset", c_u32), ("face_count", c_u32),
-        ("has_vertex_normals", c_i32), ("has_vertex_texcoords", c_i32), ("reserved0", c_i32),
+        ("has_vertex_normals", c_i32), ("has_vertex_texcoords", c_i32), ("sample_only", c_i32),
     ]
 
 

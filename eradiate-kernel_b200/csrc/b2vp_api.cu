@@ -236,6 +236,8 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (a.bsdf < 0 || a.bsdf >= (int) d->n_bsdfs || a.interior_medium >= (int) d->n_media ||
             a.exterior_medium >= (int) d->n_media)
             return fail(B2VP_ERR_INVALID, "shape %u: bsdf/medium index out of range", i);
+        if (a.sample_only && (a.type != B2VP_SHAPE_RECTANGLE || d->sensor.target_type != B2VP_TARGET_SHAPE || d->sensor.target_shape != (int) i))
+            return fail(B2VP_ERR_INVALID, "shape %u: sample_only is for the rectangle the sensor targets", i);
         if (a.type == B2VP_SHAPE_MESH &&
             ((uint64_t) a.vertex_offset + a.vertex_count > d->n_vertices ||
              (uint64_t) a.face_offset + a.face_count > d->n_faces))
@@ -446,7 +448,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene
         o.radius = (F) a.radius; o.flip_normals = a.flip_normals;
         o.vofs = a.vertex_offset; o.fofs = a.face_offset; o.fcount = a.face_count;
         o.has_normals = a.has_vertex_normals; o.has_uv = a.has_vertex_texcoords;
-        if (a.type != B2VP_SHAPE_MESH) analytic.push_back((int) i);
+        if (a.type != B2VP_SHAPE_MESH && !a.sample_only) analytic.push_back((int) i);   /* a sensor's own target shape is sampled, never hit */
     }
     std::vector<DBsdf<F>> bsdfs(s->bsdfs.size());
     for (size_t i = 0; i < bsdfs.size(); ++i) {
@@ -588,6 +590,7 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene
     const bool bvh_small = !s->bvh_nodes.empty() && bvh_bytes <= BVH_SMEM_MAX;
     for (uint32_t i = 0; i < n_shapes; ++i) {
         const B2vpShape &a = s->shapes[i];
+        if (a.sample_only) continue;   /* not intersected: no intersection code needed for it */
         ft |= a.type == B2VP_SHAPE_MESH ? (bvh_small ? FT_MESH_SMEM : FT_MESH) : a.type == B2VP_SHAPE_SPHERE ? FT_SPHERE : FT_RECT;
         if (a.type == B2VP_SHAPE_MESH && (a.has_vertex_normals || a.has_vertex_texcoords)) ft |= FT_MESH_ATTR;
     }

@@ -390,6 +390,18 @@ template <typename Float, typename Spectrum> struct B200Describe {
             o.to_world = mat(id.matrix);
         }
         auto target_point = [&](const auto &p) { for (int k = 0; k < 3; ++k) o.target_point[k] = (double) p[k]; };
+        /* a shape as target: area sampling of the shape (distant.cpp:345-354); the device samples rectangles */
+        auto target_shape = [&](const Shape *shape) {
+            auto it = t.shape_ids.find(shape);
+            int index;
+            if (it != t.shape_ids.end()) index = it->second;
+            else {   /* a shape nested in the sensor is not a child of the scene (scene.cpp:23-40): sampled, never hit */
+                index = this->shape(shape);
+                t.shapes[index].sample_only = 1;
+            }
+            if (t.shapes[index].type != B2VP_SHAPE_RECTANGLE) unsupported("a sensor target shape other than a rectangle");
+            o.target_type = B2VP_TARGET_SHAPE; o.target_shape = index;
+        };
         if (n.rfind("DistantSensor_", 0) == 0) {
             /* the members read do not depend on the target / origin template arguments */
             using D = DistantSensorImpl<Float, Spectrum, RayTargetType::Point, RayOriginType::BoundingSphere>;
@@ -400,7 +412,8 @@ template <typename Float, typename Spectrum> struct B200Describe {
                                : d->m_direction_type == RayDirectionType::SampleWidth ? B2VP_DIR_SAMPLE_WIDTH : B2VP_DIR_SAMPLE_ALL;
             if (n == "DistantSensor_Point_BoundingSphere") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_ray_target_point); }
             else if (n == "DistantSensor_None_BoundingSphere") o.target_type = B2VP_TARGET_NONE;
-            else unsupported("distant sensor with shape targets / origins (" + n + ")");
+            else if (n == "DistantSensor_Shape_BoundingSphere") target_shape(d->m_ray_target_shape.get());
+            else unsupported("distant sensor with a ray_origin shape (" + n + ")");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
         } else if (n.rfind("DistantFluxSensor_", 0) == 0) {
             using D = DistantFluxSensorImpl<Float, Spectrum, DistantFluxRayTargetType::Point>;
@@ -408,7 +421,8 @@ template <typename Float, typename Spectrum> struct B200Describe {
             o.type = B2VP_SENSOR_DISTANTFLUX;
             if (n == "DistantFluxSensor_Point") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_target_point); }
             else if (n == "DistantFluxSensor_NoTarget") o.target_type = B2VP_TARGET_NONE;
-            else unsupported("distantflux sensor with a shape target");
+            else if (n == "DistantFluxSensor_Shape") target_shape(d->m_target_shape.get());
+            else unsupported("distantflux sensor " + n);
             if (d->m_origin_shape) unsupported("distantflux sensor with an origin shape");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
             for (int k = 0; k < 3; ++k) o.reference_normal[k] = (double) d->m_reference_normal[k];
@@ -426,7 +440,8 @@ template <typename Float, typename Spectrum> struct B200Describe {
             o.type = B2VP_SENSOR_MDISTANT;
             if (n == "MultiDistantSensor_Point") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_target_point); }
             else if (n == "MultiDistantSensor_NoTarget") o.target_type = B2VP_TARGET_NONE;
-            else unsupported("mdistant sensor with a shape target");
+            else if (n == "MultiDistantSensor_Shape") target_shape(d->m_target_shape.get());
+            else unsupported("mdistant sensor " + n);
             o.n_transforms = (int32_t) d->m_sensor_count;
             for (size_t i = 0; i < d->m_sensor_count * 16; ++i) t.sensor_xf.push_back((double) d->m_transforms[i]);
         } else if (n == "MultiRadianceMeter") {

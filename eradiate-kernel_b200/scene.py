@@ -781,7 +781,15 @@ class _Builder:
                 sn.target_type = abi.TARGET_NONE
             elif isinstance(tgt, dict):
                 sn.target_type = abi.TARGET_SHAPE
-                sn.target_shape = self.resolve(tgt, "shape", self.shape)
+                if tgt.get("type") == "ref":
+                    sn.target_shape = self.resolve(tgt, "shape", self.shape)
+                else:
+                    # a shape of the sensor's own (distant.cpp:270-277): sampled, but not a child of the scene -- it is
+                    # never intersected and does not enlarge the scene's bounding box
+                    box = (self.bbox_min.copy(), self.bbox_max.copy())
+                    sn.target_shape = self.shape(tgt)
+                    self.bbox_min, self.bbox_max = box
+                    self.shapes[sn.target_shape].sample_only = 1
                 if self.shapes[sn.target_shape].type != abi.SHAPE_RECTANGLE:
                     raise RuntimeError("sensor target shape must be a rectangle in the B200 volpath")
             else:

@@ -142,7 +142,9 @@ typedef struct B2vpShape {
     uint32_t vertex_offset, vertex_count;
     uint32_t face_offset, face_count;
     int32_t has_vertex_normals, has_vertex_texcoords;
-    int32_t reserved0;
+    /* 1: not a shape of the scene but a sensor's own target shape (a <shape name="ray_target"> nested in the sensor,
+       distant.cpp:270-277): sampled by the sensor, never intersected, outside the scene's bounding box.  Rectangles only */
+    int32_t sample_only;
 } B2vpShape;
 
 typedef struct B2vpBsdf {

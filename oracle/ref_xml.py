@@ -220,7 +220,10 @@ class _Writer:
                 out.append(_xyz("point", key, v[key]))
         for key in ("ray_target", "target"):
             if key in v:
-                if isinstance(v[key], dict):
+                if isinstance(v[key], dict) and v[key].get("type") != "ref":   # a shape of the sensor's own, not in the scene
+                    self.n_files += 1
+                    out.append(self.shape(v[key], "target%d" % self.n_files).replace("<shape ", '<shape name="%s" ' % key, 1))
+                elif isinstance(v[key], dict):
                     out.append('<ref name="%s" id="%s"/>' % (key, v[key]["id"]))
                 else:
                     out.append(_xyz("point", key, v[key]))

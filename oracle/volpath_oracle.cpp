@@ -303,6 +303,7 @@ template <typename F> struct OShape {
     V3<F> translation;   /* to_world.translation() */
     F inv_surface_area;
     V3<F> center; F radius; bool flip_normals;
+    bool sample_only = false;   /* B2vpShape::sample_only */
     uint32_t vofs, vcount, fofs, fcount; bool has_normals, has_uv;
 };
 template <typename F> struct OVolume {
@@ -392,6 +393,7 @@ template <typename F> bool build_scene(const B2vpSceneDesc *d, OScene<F> &s) {
         const B2vpShape &a = d->shapes[i];
         OShape<F> o;
         o.type = a.type; o.bsdf = a.bsdf; o.interior = a.interior_medium; o.exterior = a.exterior_medium;
+        o.sample_only = a.sample_only != 0;
         o.to_world = load_mat<F>(a.to_world); o.to_object = load_mat<F>(a.to_object);
         o.frame.s = ld3<F>(a.frame_s); o.frame.t = ld3<F>(a.frame_t); o.frame.n = ld3<F>(a.frame_n);
         o.translation = { o.to_world.c(3, 0), o.to_world.c(3, 1), o.to_world.c(3, 2) };
@@ -576,6 +578,7 @@ SurfaceInteraction<F> ray_intersect(const OScene<F> &s, const Ray<F> &ray_in, Co
     int best_shape = -1; uint32_t best_prim = 0; F best_u = 0, best_v = 0;
     for (size_t i = 0; i < s.shapes.size(); ++i) {
         const OShape<F> &sh = s.shapes[i];
+        if (sh.sample_only) continue;   /* a sensor's own target shape is not a child of the scene (scene.cpp:23-40) */
         if (sh.type == B2VP_SHAPE_RECTANGLE) {
             F t = rectangle_intersect(sh, ray);
             if (t != Consts<F>::Inf) { best_shape = (int) i; ray.maxt = t; }

@@ -187,6 +187,23 @@ def _distantflux(target, **kw):
     return d
 
 
+def _target_shape(d, key="ray_target", shape="ground"):
+    """The sensor targets a rectangle of the scene instead of a point: area sampling of the shape with the aperture
+    sample, weight 1 / (pdf * area) (distant.cpp:345-354, mdistant.cpp:247-252, distantflux.cpp:228-233)."""
+    d["sensor"][key] = {"type": "ref", "id": shape}
+    return d
+
+
+def _nested_target(d, key="ray_target"):
+    """The target is a rectangle of the sensor's own, nested in the sensor: sampled like any target shape, but not a
+    child of the scene -- rays pass through it (it floats inside the atmosphere, tilted) and the scene's bounding
+    sphere, which places the ray origins, does not know it."""
+    T = scenes.T
+    d["sensor"][key] = {"type": "rectangle", "to_world": T.translate([0.5, -0.25, 0.3], np.float32) @
+                        T.rotate([1, 0, 0], 20.0, np.float32) @ T.scale([2.0, 1.5, 1], np.float32)}
+    return d
+
+
 def _irradiancemeter(spp, variant):
     """C2 with an `irradiancemeter` (src/sensors/irradiancemeter.cpp) on a small rectangle floating
     in the atmosphere, facing up: downwelling irradiance at that level."""
@@ -315,6 +332,18 @@ CASES = {
     "c2_serialized": (lambda v: _c2_ply("roof.serialized", False, "serialized", 1, spp=1, variant=v, width=128), "scalar_mono"),
     "c2_serialized_v3": (lambda v: _c2_ply("roof_v3_f64.serialized", True, "serialized", 1, spp=1, variant=v, width=64), "scalar_mono_double"),
     "c2_ply_binary_f64": (lambda v: _c2_ply("roof_bin.ply", False, spp=1, variant=v, width=64), "scalar_mono_double"),
+    # sensors that target a shape (the rectangle on the ground of C2, the null rectangle above the cloud of C3)
+    "c2_target_shape": (lambda v: _target_shape(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono"),
+    "c2_target_shape_f64": (lambda v: _target_shape(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
+    "c3_target_shape_f64": (lambda v: _target_shape(_c3(spp=1, variant=v, n=16, size=16), shape="top"), "scalar_mono_double"),
+    "c2_mdistant_target_shape": (lambda v: _target_shape(scenes.c2(spp=1, variant=v, width=128, sensor="mdistant"), "target"), "scalar_mono"),
+    "c2_mdistant_target_shape_f64": (lambda v: _target_shape(scenes.c2(spp=1, variant=v, width=64, sensor="mdistant"), "target"), "scalar_mono_double"),
+    "c2_distantflux_target_shape": (lambda v: _target_shape(_distantflux(False, spp=1, variant=v), "target"), "scalar_mono"),
+    "c2_distantflux_target_shape_f64": (lambda v: _target_shape(_distantflux(False, spp=1, variant=v), "target"), "scalar_mono_double"),
+    "c2_nested_target": (lambda v: _nested_target(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono"),
+    "c2_nested_target_f64": (lambda v: _nested_target(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
+    "c2_mdistant_nested_target_f64": (lambda v: _nested_target(scenes.c2(spp=1, variant=v, width=64, sensor="mdistant"), "target"), "scalar_mono_double"),
+    "c2_distantflux_nested_target": (lambda v: _nested_target(_distantflux(False, spp=1, variant=v), "target"), "scalar_mono"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

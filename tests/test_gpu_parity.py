@@ -60,7 +60,18 @@ CASES = {
     "c2_blendphase_const": lambda v: _blendphase(v, False),
     "c5_bilambertian": lambda v: scenes.c5(spp=8, variant=v, n_leaves=400, n_sensors=64,
                                            leaf_bsdf={"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.25}),
+    # sensors that target a shape: a rectangle of the scene, or one nested in the sensor (sampled, never intersected)
+    "c2_target_shape": lambda v: _golden()._target_shape(scenes.c2(spp=8, variant=v, width=64)),
+    "c3_target_shape": lambda v: _golden()._target_shape(scenes.c3(spp=2, variant=v, n=16, size=12), shape="top"),
+    "c2_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=8, variant=v, width=64)),
+    "c2_mdistant_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=8, variant=v, width=64, sensor="mdistant"), "target"),
+    "c2_distantflux_target_shape": lambda v: _golden()._target_shape(_distantflux(v, False), "target"),
 }
+
+
+def _golden():
+    import make_ref_golden
+    return make_ref_golden
 
 
 def _tabphase(variant):

