@@ -236,8 +236,10 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
         if (a.bsdf < 0 || a.bsdf >= (int) d->n_bsdfs || a.interior_medium >= (int) d->n_media ||
             a.exterior_medium >= (int) d->n_media)
             return fail(B2VP_ERR_INVALID, "shape %u: bsdf/medium index out of range", i);
-        if (a.sample_only && (a.type != B2VP_SHAPE_RECTANGLE || d->sensor.target_type != B2VP_TARGET_SHAPE || d->sensor.target_shape != (int) i))
-            return fail(B2VP_ERR_INVALID, "shape %u: sample_only is for the rectangle the sensor targets", i);
+        const bool is_target = d->sensor.target_type == B2VP_TARGET_SHAPE && d->sensor.target_shape == (int) i;
+        const bool is_origin = d->sensor.origin_type == B2VP_ORIGIN_SHAPE && d->sensor.origin_shape == (int) i;
+        if (a.sample_only && (a.type != B2VP_SHAPE_RECTANGLE || !(is_target || is_origin)))
+            return fail(B2VP_ERR_INVALID, "shape %u: sample_only is for the rectangle the sensor targets or starts its rays on", i);
         if (a.type == B2VP_SHAPE_MESH &&
             ((uint64_t) a.vertex_offset + a.vertex_count > d->n_vertices ||
              (uint64_t) a.face_offset + a.face_count > d->n_faces))
@@ -274,8 +276,12 @@ int copy_desc(const B2vpSceneDesc *d, b2vp_scene *s) {
     const B2vpSensor &sn = d->sensor;
     if (sn.type < 0 || sn.type > B2VP_SENSOR_IRRADIANCEMETER)
         return fail(B2VP_ERR_UNSUPPORTED, "sensor type %d not supported by the B200 volpath", sn.type);
-    if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_DISTANTFLUX) && sn.origin_type == B2VP_ORIGIN_SHAPE)
-        return fail(B2VP_ERR_UNSUPPORTED, "distant sensor with a ray_origin shape is not supported");
+    if (sn.origin_type == B2VP_ORIGIN_SHAPE) {   /* distant.cpp:281-290, distantflux.cpp:171-180 */
+        if (sn.type != B2VP_SENSOR_DISTANT && sn.type != B2VP_SENSOR_DISTANTFLUX)
+            return fail(B2VP_ERR_INVALID, "only distant and distantflux sensors take their ray origins from a shape");
+        if (sn.origin_shape < 0 || sn.origin_shape >= (int) d->n_shapes || d->shapes[sn.origin_shape].type != B2VP_SHAPE_RECTANGLE)
+            return fail(B2VP_ERR_UNSUPPORTED, "sensor ray_origin shape must be a rectangle");
+    }
     if ((sn.type == B2VP_SENSOR_DISTANT || sn.type == B2VP_SENSOR_MDISTANT || sn.type == B2VP_SENSOR_DISTANTFLUX) &&
         sn.target_type == B2VP_TARGET_SHAPE &&
         (sn.target_shape < 0 || sn.target_shape >= (int) d->n_shapes ||
@@ -596,7 +602,8 @@ template <typename F> int upload_scene(b2vp_scene *s, DeviceCtx *dc, DeviceScene
     }
     if (have_tabphase) ft |= FT_TABPHASE;
     if (have_blendphase) ft |= FT_BLENDPHASE;
-    if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX || d.sensor.type == B2VP_SENSOR_IRRADIANCEMETER) ft |= FT_DISTANTFLUX;
+    if (d.sensor.type == B2VP_SENSOR_DISTANTFLUX || d.sensor.type == B2VP_SENSOR_IRRADIANCEMETER ||
+        d.sensor.origin_type == B2VP_ORIGIN_SHAPE) ft |= FT_DISTANTFLUX;
     if (d.sensor.rfilter_radius > (double) ((F) 0.5 + K<F>::RayEpsilon)) ft |= FT_RFILTER;   /* imageblock.cpp:117; the box filter's radius is 0.5 + RayEpsilon */
 
     /* blob layout */

@@ -71,7 +71,7 @@ enum : uint32_t {
     FT_MESH_ATTR = 1u << 12,   /* some mesh has vertex normals or texture coordinates     */
     FT_TABPHASE = 1u << 13,    /* a tabulated phase function is present                   */
     FT_BLENDPHASE = 1u << 14,  /* a blended phase function (weight volume) is present     */
-    FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter       */
+    FT_DISTANTFLUX = 1u << 15, /* the sensor is a distantflux or an irradiancemeter, or takes its ray origins from a shape */
     FT_RFILTER = 1u << 16,     /* the film's reconstruction filter is wider than a pixel (no preset: generic instances) */
     FT_GRID_SMEM = 1u << 17,   /* some grid is staged in shared memory                    */
     FT_GRID_GLOBAL = 1u << 18, /* some grid is read from global memory                    */
@@ -97,6 +97,20 @@ template <typename F> VP_D F rectangle_intersect(const DShape<F> &sh, const Ray<
     F lx = fma_(d.x, t, o.x), ly = fma_(d.y, t, o.y);
     bool active = t >= r.mint && t <= r.maxt && abs_(lx) <= (F) 1 && abs_(ly) <= (F) 1;
     return active ? t : inf_<F>();
+}
+
+/* The ray origin on a `ray_origin` / `origin` rectangle (distant.cpp:366-375, distantflux.cpp:245-252): the target
+   projected onto the shape along -d by Shape::ray_intersect(.., Minimal), i.e. ray_intersect_preliminary above and the
+   re-projected hit point of rectangle.cpp:194-197, for the ray Ray3f(target, -d, time) with mint = RayEpsilon.  On a
+   miss pi.t is inf, the origin is not finite and the caller zeroes the ray weight. */
+template <typename F> VP_D V3<F> origin_on_shape(const DShape<F> &sh, V3<F> target, V3<F> d, bool &valid) {
+    Ray<F> tmp = make_ray(target, -d, K<F>::RayEpsilon, inf_<F>());
+    const F t = rectangle_intersect(sh, tmp);
+    valid = t != inf_<F>();
+    V3<F> p = tmp.at(t);
+    V3<F> fn = ld3(sh.fn);
+    F dist = dot(ld3(sh.translation) - p, fn);
+    return fmadd3(fn, dist, p);
 }
 
 /* math::solve_quadratic (include/mitsuba/core/math.h) in double */
@@ -1144,7 +1158,11 @@ VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> 
             weight = (F) 1;
             weight /= dot(-ray.d, mk3<F>(0, 0, 1));
         }
-        if (sn.target_type == 0)
+        if ((FEAT & FT_DISTANTFLUX) && sn.origin_type == 1) {
+            bool valid;
+            ray.o = origin_on_shape(sv.shapes[sn.origin_shape], ray_target, ray.d, valid);
+            if (!valid) weight = 0;
+        } else if (sn.target_type == 0)
             ray.o = ray_target - ray.d * bs_r;
         else
             ray.o = ray_target - ray.d * (F) 2 * bs_r;
@@ -1182,7 +1200,12 @@ VP_D F sensor_sample_ray(const SceneView<F> &sv, F fx, F fy, F ax, F ay, Ray<F> 
             V3<F> perp = xf_vector(sn.to_world, mk3<F>(ox, oy, (F) 0));
             ray_target = bs_c + perp * bs_r;
         }
-        ray.o = ray_target - ray.d * (F) 2 * bs_r;
+        if (sn.origin_type == 1) {
+            bool valid;
+            ray.o = origin_on_shape(sv.shapes[sn.origin_shape], ray_target, ray.d, valid);
+            if (!valid) weight = 0;
+        } else
+            ray.o = ray_target - ray.d * (F) 2 * bs_r;
     } else if ((FEAT & FT_DISTANTFLUX) && sn.type == 5) { /* irradiancemeter.cpp:88-118 over rectangle.cpp:111-125 */
         const DShape<F> &sh = sv.shapes[sn.origin_shape];
         ray.o = xf_point_affine(sh.to_world, mk3<F>(fx * (F) 2 - (F) 1, fy * (F) 2 - (F) 1, (F) 0));

@@ -390,18 +390,23 @@ template <typename Float, typename Spectrum> struct B200Describe {
             o.to_world = mat(id.matrix);
         }
         auto target_point = [&](const auto &p) { for (int k = 0; k < 3; ++k) o.target_point[k] = (double) p[k]; };
-        /* a shape as target: area sampling of the shape (distant.cpp:345-354); the device samples rectangles */
-        auto target_shape = [&](const Shape *shape) {
+        /* a shape given to the sensor: one of the scene's, or a shape nested in the sensor, which is not a child of the
+           scene (scene.cpp:23-40): used by the sensor, never hit by a path.  The device handles rectangles */
+        auto own_shape = [&](const Shape *shape, const char *role) {
             auto it = t.shape_ids.find(shape);
             int index;
             if (it != t.shape_ids.end()) index = it->second;
-            else {   /* a shape nested in the sensor is not a child of the scene (scene.cpp:23-40): sampled, never hit */
+            else {
                 index = this->shape(shape);
                 t.shapes[index].sample_only = 1;
             }
-            if (t.shapes[index].type != B2VP_SHAPE_RECTANGLE) unsupported("a sensor target shape other than a rectangle");
-            o.target_type = B2VP_TARGET_SHAPE; o.target_shape = index;
+            if (t.shapes[index].type != B2VP_SHAPE_RECTANGLE) unsupported(std::string("a sensor ") + role + " shape other than a rectangle");
+            return index;
         };
+        /* a shape as target: area sampling of the shape (distant.cpp:345-354) */
+        auto target_shape = [&](const Shape *shape) { o.target_type = B2VP_TARGET_SHAPE; o.target_shape = own_shape(shape, "target"); };
+        /* a shape as ray origin: the target projected onto it along the ray (distant.cpp:366-375) */
+        auto origin_shape = [&](const Shape *shape) { o.origin_type = B2VP_ORIGIN_SHAPE; o.origin_shape = own_shape(shape, "origin"); };
         if (n.rfind("DistantSensor_", 0) == 0) {
             /* the members read do not depend on the target / origin template arguments */
             using D = DistantSensorImpl<Float, Spectrum, RayTargetType::Point, RayOriginType::BoundingSphere>;
@@ -410,11 +415,13 @@ template <typename Float, typename Spectrum> struct B200Describe {
             o.flip_directions = d->m_flip_directions;
             o.direction_type = d->m_direction_type == RayDirectionType::Single ? B2VP_DIR_SINGLE
                                : d->m_direction_type == RayDirectionType::SampleWidth ? B2VP_DIR_SAMPLE_WIDTH : B2VP_DIR_SAMPLE_ALL;
-            if (n == "DistantSensor_Point_BoundingSphere") { o.target_type = B2VP_TARGET_POINT; target_point(d->m_ray_target_point); }
-            else if (n == "DistantSensor_None_BoundingSphere") o.target_type = B2VP_TARGET_NONE;
-            else if (n == "DistantSensor_Shape_BoundingSphere") target_shape(d->m_ray_target_shape.get());
-            else unsupported("distant sensor with a ray_origin shape (" + n + ")");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
+            if (n.rfind("DistantSensor_Point_", 0) == 0) { o.target_type = B2VP_TARGET_POINT; target_point(d->m_ray_target_point); }
+            else if (n.rfind("DistantSensor_None_", 0) == 0) o.target_type = B2VP_TARGET_NONE;
+            else if (n.rfind("DistantSensor_Shape_", 0) == 0) target_shape(d->m_ray_target_shape.get());
+            else unsupported("distant sensor " + n);
+            if (n.size() > 6 && n.compare(n.size() - 6, 6, "_Shape") == 0) origin_shape(d->m_ray_origin_shape.get());
+            else if (n.size() < 15 || n.compare(n.size() - 15, 15, "_BoundingSphere") != 0) unsupported("distant sensor " + n);
         } else if (n.rfind("DistantFluxSensor_", 0) == 0) {
             using D = DistantFluxSensorImpl<Float, Spectrum, DistantFluxRayTargetType::Point>;
             const D *d = static_cast<const D *>(sn);
@@ -423,8 +430,8 @@ template <typename Float, typename Spectrum> struct B200Describe {
             else if (n == "DistantFluxSensor_NoTarget") o.target_type = B2VP_TARGET_NONE;
             else if (n == "DistantFluxSensor_Shape") target_shape(d->m_target_shape.get());
             else unsupported("distantflux sensor " + n);
-            if (d->m_origin_shape) unsupported("distantflux sensor with an origin shape");
             o.origin_type = B2VP_ORIGIN_BSPHERE;
+            if (d->m_origin_shape) origin_shape(d->m_origin_shape.get());
             for (int k = 0; k < 3; ++k) o.reference_normal[k] = (double) d->m_reference_normal[k];
         } else if (n == "IrradianceMeter") {   /* attached to a shape (shape.cpp:47-54): a rectangle here */
             o.type = B2VP_SENSOR_IRRADIANCEMETER;

@@ -775,21 +775,36 @@ class _Builder:
         to_world = self.xf(node.get("to_world"))
         xfs = None
 
+        def own_shape(sub):
+            """A shape given to the sensor: a reference to a shape of the scene, or a shape of the sensor's own
+            (distant.cpp:270-290) -- used by the sensor, but not a child of the scene: never intersected by paths and
+            not part of the scene's bounding box."""
+            if sub.get("type") == "ref":
+                return self.resolve(sub, "shape", self.shape)
+            box = (self.bbox_min.copy(), self.bbox_max.copy())
+            idx = self.shape(sub)
+            self.bbox_min, self.bbox_max = box
+            self.shapes[idx].sample_only = 1
+            return idx
+
+        def origin(key):   # distant.cpp:281-290 `ray_origin`, distantflux.cpp:171-180 `origin`
+            if key not in node:
+                sn.origin_type = abi.ORIGIN_BSPHERE
+                return
+            if not isinstance(node[key], dict):
+                raise RuntimeError("Invalid parameter %s, must be a Shape." % key)
+            sn.origin_type = abi.ORIGIN_SHAPE
+            sn.origin_shape = own_shape(node[key])
+            if self.shapes[sn.origin_shape].type != abi.SHAPE_RECTANGLE:
+                raise RuntimeError("sensor origin shape must be a rectangle in the B200 volpath")
+
         def target(key):
             tgt = node.get(key)
             if tgt is None:
                 sn.target_type = abi.TARGET_NONE
             elif isinstance(tgt, dict):
                 sn.target_type = abi.TARGET_SHAPE
-                if tgt.get("type") == "ref":
-                    sn.target_shape = self.resolve(tgt, "shape", self.shape)
-                else:
-                    # a shape of the sensor's own (distant.cpp:270-277): sampled, but not a child of the scene -- it is
-                    # never intersected and does not enlarge the scene's bounding box
-                    box = (self.bbox_min.copy(), self.bbox_max.copy())
-                    sn.target_shape = self.shape(tgt)
-                    self.bbox_min, self.bbox_max = box
-                    self.shapes[sn.target_shape].sample_only = 1
+                sn.target_shape = own_shape(tgt)
                 if self.shapes[sn.target_shape].type != abi.SHAPE_RECTANGLE:
                     raise RuntimeError("sensor target shape must be a rectangle in the B200 volpath")
             else:
@@ -813,9 +828,7 @@ class _Builder:
                     _, up = coordinate_system(d, dtp)
                 to_world = Transform.look_at([0, 0, 0], d, up, dtp)
             target("ray_target")
-            if "ray_origin" in node:
-                raise RuntimeError("distant sensor with a ray_origin shape is not supported by the B200 volpath")
-            sn.origin_type = abi.ORIGIN_BSPHERE
+            origin("ray_origin")
             sn.needs_aperture_sample = 1
         elif t == "irradiancemeter":  # irradiancemeter.cpp:54-80
             sn.type = abi.SENSOR_IRRADIANCEMETER
@@ -829,9 +842,7 @@ class _Builder:
         elif t == "distantflux":  # distantflux.cpp:59-176
             sn.type = abi.SENSOR_DISTANTFLUX
             target("target")
-            if "origin" in node:
-                raise RuntimeError("distantflux sensor with an origin shape is not supported by the B200 volpath")
-            sn.origin_type = abi.ORIGIN_BSPHERE
+            origin("origin")
             sn.needs_aperture_sample = 1
             # m_reference_normal: props.transform("to_world") (single precision, widened) times (0, 0, 1)
             sn.reference_normal[:] = [float(x) for x in to_world.vector([0, 0, 1])]

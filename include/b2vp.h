@@ -142,8 +142,9 @@ typedef struct B2vpShape {
     uint32_t vertex_offset, vertex_count;
     uint32_t face_offset, face_count;
     int32_t has_vertex_normals, has_vertex_texcoords;
-    /* 1: not a shape of the scene but a sensor's own target shape (a <shape name="ray_target"> nested in the sensor,
-       distant.cpp:270-277): sampled by the sensor, never intersected, outside the scene's bounding box.  Rectangles only */
+    /* 1: not a shape of the scene but a sensor's own target or origin shape (a <shape name="ray_target"> or
+       <shape name="ray_origin"> nested in the sensor, distant.cpp:270-290): used by the sensor, never intersected by
+       paths, outside the scene's bounding box.  Rectangles only */
     int32_t sample_only;
 } B2vpShape;
 
@@ -214,7 +215,7 @@ typedef struct B2vpSensor {
     int32_t target_type;       /* distant/mdistant: B2VP_TARGET_*              */
     int32_t origin_type;       /* distant: B2VP_ORIGIN_*                       */
     int32_t target_shape;      /* shape index (rectangle) when TARGET_SHAPE    */
-    int32_t origin_shape;      /* shape index when ORIGIN_SHAPE                */
+    int32_t origin_shape;      /* shape index (rectangle) when ORIGIN_SHAPE; irradiancemeter: its parent rectangle */
     int32_t flip_directions;   /* distant.cpp:229                              */
     int32_t needs_aperture_sample; /* sensor.h:79                             */
     int32_t medium;            /* sensor->medium(): index or -1                */

@@ -216,10 +216,10 @@ class _Writer:
             if key in v:
                 out.append(_xyz("vector", key, v[key]))
         for key in ("origin",):
-            if key in v:
+            if key in v and not isinstance(v[key], dict):
                 out.append(_xyz("point", key, v[key]))
-        for key in ("ray_target", "target"):
-            if key in v:
+        for key in ("ray_target", "target", "ray_origin", "origin"):
+            if key in v and (isinstance(v[key], dict) or key in ("ray_target", "target")):
                 if isinstance(v[key], dict) and v[key].get("type") != "ref":   # a shape of the sensor's own, not in the scene
                     self.n_files += 1
                     out.append(self.shape(v[key], "target%d" % self.n_files).replace("<shape ", '<shape name="%s" ' % key, 1))

@@ -1058,6 +1058,21 @@ template <typename F> inline F rect_area(const OShape<F> &sh) { return norm(cros
 
 /* Sensor::sample_ray (distant.cpp:299-386, mdistant.cpp:216-266,
    radiancemeter.cpp:106-139, mradiancemeter.cpp:134-159); returns the weight */
+/* The ray origin on a `ray_origin` / `origin` shape (distant.cpp:366-375, distantflux.cpp:245-252): the target is
+   projected onto the shape along -d with Shape::ray_intersect(.., Minimal) -- for a rectangle ray_intersect_preliminary
+   (rectangle.cpp:139-159) and the re-projected hit point of compute_surface_interaction (rectangle.cpp:194-197).  The
+   temporary ray is Ray3f(o, d, time): mint = RayEpsilon, maxt = inf (ray.h:33-34,44-47).  A miss leaves pi.t = inf, so
+   the origin is not finite, and the caller zeroes the ray weight (`ray_weight && active`). */
+template <typename F>
+V3<F> origin_on_shape(const OShape<F> &sh, const V3<F> &target, const V3<F> &d, bool &valid) {
+    Ray<F> tmp = make_ray(target, -d, Consts<F>::RayEpsilon, Consts<F>::Inf);
+    const F t = rectangle_intersect(sh, tmp);
+    valid = t != Consts<F>::Inf;
+    V3<F> p = tmp.at(t);
+    F dist = dot(sh.translation - p, sh.frame.n);
+    return fmadd3(sh.frame.n, dist, p);
+}
+
 template <typename F>
 F sensor_sample_ray(const OScene<F> &s, F fx, F fy, F ax, F ay, Ray<F> &ray, bool &ok) {
     const B2vpSensor &sn = s.sensor;
@@ -1088,8 +1103,11 @@ F sensor_sample_ray(const OScene<F> &s, F fx, F fy, F ax, F ay, Ray<F> &ray, boo
             weight = (F) 1;
             weight /= dot(-ray.d, V3<F>{ 0, 0, 1 });
         }
-        if (sn.origin_type == B2VP_ORIGIN_SHAPE) { ok = false; return 0; }
-        if (sn.target_type == B2VP_TARGET_NONE)
+        if (sn.origin_type == B2VP_ORIGIN_SHAPE) {
+            bool valid;
+            ray.o = origin_on_shape(s.shapes[sn.origin_shape], ray_target, ray.d, valid);
+            if (!valid) weight = 0;
+        } else if (sn.target_type == B2VP_TARGET_NONE)
             ray.o = ray_target - ray.d * s.bs_radius;
         else
             ray.o = ray_target - ray.d * (F) 2 * s.bs_radius;
@@ -1127,8 +1145,12 @@ F sensor_sample_ray(const OScene<F> &s, F fx, F fy, F ax, F ay, Ray<F> &ray, boo
             V3<F> perp = xf_vector(trafo, V3<F>{ ox, oy, (F) 0 });
             ray_target = s.bs_center + perp * s.bs_radius;
         }
-        if (sn.origin_type == B2VP_ORIGIN_SHAPE) { ok = false; return 0; }
-        ray.o = ray_target - ray.d * (F) 2 * s.bs_radius;
+        if (sn.origin_type == B2VP_ORIGIN_SHAPE) {
+            bool valid;
+            ray.o = origin_on_shape(s.shapes[sn.origin_shape], ray_target, ray.d, valid);
+            if (!valid) weight = 0;
+        } else
+            ray.o = ray_target - ray.d * (F) 2 * s.bs_radius;
     } else if (sn.type == B2VP_SENSOR_IRRADIANCEMETER) { /* irradiancemeter.cpp:88-118 over rectangle.cpp:111-125 */
         const OShape<F> &sh = s.shapes[sn.origin_shape];
         ray.o = xf_point_affine(sh.to_world, V3<F>{ fx * (F) 2 - (F) 1, fy * (F) 2 - (F) 1, (F) 0 });

@@ -204,6 +204,18 @@ def _nested_target(d, key="ray_target"):
     return d
 
 
+def _origin_shape(d, key="ray_origin", half=15.0, height=1.2, sweep=False):
+    """Ray origins on a rectangle of the sensor's own above the atmosphere instead of on the scene's bounding sphere
+    (distant.cpp:281-290,366-375; distantflux.cpp:171-180,245-252): the target is projected onto it along the ray.
+    `sweep`: no fixed direction, the film's columns sweep the directions of the XZ half plane -- with a small rectangle
+    the slanted ones miss it, their ray weight is zero and the sample counts with alpha 0."""
+    T = scenes.T
+    d["sensor"][key] = {"type": "rectangle", "to_world": T.translate([0.25, -0.5, height], np.float32) @ T.scale([half, half, 1], np.float32)}
+    if sweep:
+        del d["sensor"]["direction"], d["sensor"]["orientation"]
+    return d
+
+
 def _irradiancemeter(spp, variant):
     """C2 with an `irradiancemeter` (src/sensors/irradiancemeter.cpp) on a small rectangle floating
     in the atmosphere, facing up: downwelling irradiance at that level."""
@@ -344,6 +356,14 @@ CASES = {
     "c2_nested_target_f64": (lambda v: _nested_target(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
     "c2_mdistant_nested_target_f64": (lambda v: _nested_target(scenes.c2(spp=1, variant=v, width=64, sensor="mdistant"), "target"), "scalar_mono_double"),
     "c2_distantflux_nested_target": (lambda v: _nested_target(_distantflux(False, spp=1, variant=v), "target"), "scalar_mono"),
+    # ray origins on a shape
+    "c2_origin_shape": (lambda v: _origin_shape(scenes.c2(spp=1, variant=v, width=128)), "scalar_mono"),
+    "c2_origin_shape_f64": (lambda v: _origin_shape(_target_shape(scenes.c2(spp=2, variant=v, width=64))), "scalar_mono_double"),
+    "c2_origin_shape_miss": (lambda v: _origin_shape(scenes.c2(spp=1, variant=v, width=128), half=1.0, sweep=True), "scalar_mono"),
+    "c2_origin_shape_miss_f64": (lambda v: _origin_shape(scenes.c2(spp=2, variant=v, width=64), half=1.0, sweep=True), "scalar_mono_double"),
+    "c3_origin_ref_f64": (lambda v: _target_shape(_c3(spp=1, variant=v, n=16, size=16), "ray_origin", "top"), "scalar_mono_double"),
+    "c2_distantflux_origin": (lambda v: _origin_shape(_distantflux(True, spp=1, variant=v), "origin", half=2.0), "scalar_mono"),
+    "c2_distantflux_origin_f64": (lambda v: _origin_shape(_distantflux(False, spp=1, variant=v), "origin", half=4.0), "scalar_mono_double"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),

@@ -66,6 +66,12 @@ CASES = {
     "c2_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=8, variant=v, width=64)),
     "c2_mdistant_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=8, variant=v, width=64, sensor="mdistant"), "target"),
     "c2_distantflux_target_shape": lambda v: _golden()._target_shape(_distantflux(v, False), "target"),
+    # ray origins on a shape (distant.cpp:366-375): all rays start on it; a small one that slanted rays miss (weight 0);
+    # a null rectangle of the scene itself; distantflux
+    "c2_origin_shape": lambda v: _golden()._origin_shape(scenes.c2(spp=8, variant=v, width=64)),
+    "c2_origin_shape_miss": lambda v: _golden()._origin_shape(scenes.c2(spp=8, variant=v, width=64), half=1.0, sweep=True),
+    "c3_origin_ref": lambda v: _golden()._target_shape(scenes.c3(spp=2, variant=v, n=16, size=12), "ray_origin", "top"),
+    "c2_distantflux_origin": lambda v: _golden()._origin_shape(_distantflux(v, True), "origin", half=2.0),
 }
 
 
