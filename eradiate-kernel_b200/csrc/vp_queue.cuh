@@ -1001,6 +1001,9 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
             }
         } else {
             /* ================================= END ================================ */
+            /* the accumulator of a finished stream, splatted after the per-lane work by the whole warp together */
+            int splat_pix = -1;
+            F splat0 = 0, splat3 = 0, splat4 = 0;
             if (has) {
                 fl = s.flags;
                 state = (int) (fl & QF_STATE);
@@ -1049,10 +1052,8 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                 if ((fl & QF_HAVE_STREAM) && (j >= n_samples || empty)) {
                     /* stream finished: splat its accumulator, write the parity outputs */
                     if (fl & QF_ACC_USED) {
-                        F *p = film + ((size_t) (py - sp.oy) * W + (px - sp.ox)) * NCH;
-                        F a0 = c.acc0;
-                        film_add(p, a0); film_add(p + 1, a0); film_add(p + 2, a0);
-                        film_add(p + 3, c.acc3); film_add(p + 4, c.acc4);
+                        splat_pix = (py - sp.oy) * W + (px - sp.ox);
+                        splat0 = c.acc0; splat3 = c.acc3; splat4 = c.acc4;
                     }
                     if (out.out_state) out.out_state[k] = ((uint64_t) s.rng_state_hi << 32) | s.rng_state_lo;
                     if (out.out_counters) {
@@ -1122,6 +1123,32 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     }
                     s.cur.w = w0;
                     st_rng(s, rng);
+                }
+            }
+            /* Warp-aggregated film accumulation (north star (5)).  In wavefront seeding consecutive streams share a
+               pixel, so the lanes of a batch that finish together mostly splat onto ONE pixel: 32 x 5 atomics on the
+               same five addresses.  When every finishing lane of the warp has the same pixel the accumulators are
+               summed by a butterfly and one lane adds five numbers; otherwise each lane adds its own. */
+            const unsigned splat_mask = __ballot_sync(FULL, splat_pix >= 0);
+            if (splat_mask) {
+                const int first = __ffs(splat_mask) - 1;
+                const int pix0 = __shfl_sync(FULL, splat_pix, first);
+                if (__all_sync(FULL, splat_pix < 0 || splat_pix == pix0)) {
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        splat0 += __shfl_xor_sync(FULL, splat0, o);
+                        splat3 += __shfl_xor_sync(FULL, splat3, o);
+                        splat4 += __shfl_xor_sync(FULL, splat4, o);
+                    }
+                    if (lane == first) {
+                        F *p = film + (size_t) pix0 * NCH;
+                        film_add(p, splat0); film_add(p + 1, splat0); film_add(p + 2, splat0);
+                        film_add(p + 3, splat3); film_add(p + 4, splat4);
+                    }
+                } else if (splat_pix >= 0) {
+                    F *p = film + (size_t) splat_pix * NCH;
+                    film_add(p, splat0); film_add(p + 1, splat0); film_add(p + 2, splat0);
+                    film_add(p + 3, splat3); film_add(p + 4, splat4);
                 }
             }
         }
