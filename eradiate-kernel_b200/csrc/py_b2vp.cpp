@@ -128,12 +128,25 @@ template <typename F> struct Loader {
         if (t == "bilambertian") return sb.add_bsdf(b2vp::Bilambertian{ get<double>(d, "reflectance", 0.5), get<double>(d, "transmittance", 0.5) });
         unsupported("BSDF", t);
     }
-    bool shape(const py::dict &d) {
+    std::map<std::string, int> shapes;   /* id (or key) -> shape index, for sensors that refer to a shape */
+    /* a shape given to a sensor (distant.cpp:270-290): a reference to a rectangle of the scene, or a rectangle of the
+       sensor's own, which is used by the sensor only (sample_only) */
+    int sensor_shape(const py::dict &d, const char *key) {
+        const py::dict r = py::cast<py::dict>(d[key]);
+        if (type_of(r) == "ref") {
+            auto it = shapes.find(py::cast<std::string>(r["id"]));
+            if (it == shapes.end()) throw std::runtime_error(std::string("load_dict: ") + key + " refers to an unknown shape (rectangles only)");
+            return it->second;
+        }
+        if (type_of(r) != "rectangle") throw std::runtime_error("sensor target shape must be a rectangle in the B200 volpath");
+        return sb.add_rectangle(xf(r), bsdf(r), medium_ref(r, "interior"), medium_ref(r, "exterior"), true);
+    }
+    bool shape(const std::string &key, const py::dict &d) {
         const std::string t = type_of(d);
         if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj") return false;
         const int b = bsdf(d), in = medium_ref(d, "interior"), ex = medium_ref(d, "exterior");
         if (t == "cube") sb.add_cube(xf(d), b, in, ex);
-        else if (t == "rectangle") sb.add_rectangle(xf(d), b, in, ex);
+        else if (t == "rectangle") shapes[get<std::string>(d, "id", key)] = sb.add_rectangle(xf(d), b, in, ex);
         else if (t == "sphere") {
             b2vp::Sphere s;
             if (d.contains("center")) s.center = vec3(d["center"]);
@@ -181,9 +194,10 @@ template <typename F> struct Loader {
             if (d.contains("direction")) s.direction = vec3(d["direction"]);
             if (d.contains("orientation")) { s.has_orientation = true; s.orientation = vec3(d["orientation"]); }
             if (d.contains("ray_target")) {
-                if (py::isinstance<py::dict>(d["ray_target"])) throw std::runtime_error("distant: a shape as ray_target is not supported by the C++ host");
-                s.has_ray_target = true; s.ray_target = vec3(d["ray_target"]);
+                if (py::isinstance<py::dict>(d["ray_target"])) s.ray_target_shape = sensor_shape(d, "ray_target");
+                else { s.has_ray_target = true; s.ray_target = vec3(d["ray_target"]); }
             }
+            if (d.contains("ray_origin")) s.ray_origin_shape = sensor_shape(d, "ray_origin");
             s.flip_directions = get<bool>(d, "flip_directions", false); s.medium = med;
             sb.set_sensor(s, film, smp);
         } else if (t == "radiancemeter") {
@@ -205,7 +219,10 @@ template <typename F> struct Loader {
             if (t == "mdistant") {
                 b2vp::MDistant s;
                 s.directions = dirs; s.medium = med;
-                if (d.contains("target")) { s.has_target = true; s.target = vec3(d["target"]); }
+                if (d.contains("target")) {
+                    if (py::isinstance<py::dict>(d["target"])) s.target_shape = sensor_shape(d, "target");
+                    else { s.has_target = true; s.target = vec3(d["target"]); }
+                }
                 sb.set_sensor(s, smp);
             } else {
                 b2vp::MRadianceMeter s;
@@ -248,7 +265,7 @@ template <typename F> struct Loader {
             const py::dict &d = kv.second;
             const std::string t = type_of(d);
             if (t == "homogeneous" || t == "heterogeneous") continue;
-            if (shape(d)) continue;
+            if (shape(kv.first, d)) continue;
             if (t == "directional") {
                 b2vp::Directional e;
                 if (d.contains("to_world")) throw std::runtime_error("directional: give `direction` (to_world is not supported by the C++ host)");
@@ -257,8 +274,13 @@ template <typename F> struct Loader {
                 sb.add_emitter(e);
             } else if (t == "constant") sb.add_emitter(b2vp::Constant{ get<double>(d, "radiance", 1.0) });
             else if (t == "volpath" || t == "volpathmis" || t == "moment") integrator(d);
-            else if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") sensor(d);
+            else if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") continue;   /* below */
             else unsupported("scene", t);
+        }
+        /* the sensor last: it may refer to a shape whose key sorts after its own */
+        for (auto &kv : items) {
+            const std::string t = type_of(kv.second);
+            if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") sensor(kv.second);
         }
         return sb.finish();
     }

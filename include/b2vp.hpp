@@ -202,6 +202,9 @@ struct Distant {
     bool has_ray_target = false; std::array<double, 3> ray_target{ 0, 0, 0 };
     bool flip_directions = false;
     int medium = -1;
+    /* a rectangle as ray_target / ray_origin (distant.cpp:270-290): the index add_rectangle returned -- for a shape of
+       the sensor's own, one added with sample_only = true.  -1: the point target above / the bounding sphere */
+    int ray_target_shape = -1, ray_origin_shape = -1;
 };
 /* src/sensors/radiancemeter.cpp:61-104 */
 struct RadianceMeter { std::array<double, 3> origin{ 0, 0, 0 }, direction{ 0, 0, 1 }; int medium = -1; };
@@ -212,6 +215,7 @@ struct MDistant {
     std::vector<std::array<double, 3>> directions;
     bool has_target = false; std::array<double, 3> target{ 0, 0, 0 };
     int medium = -1;
+    int target_shape = -1;   /* a rectangle as target (mdistant.cpp:193-200), see Distant::ray_target_shape */
 };
 /* src/sensors/mradiancemeter.cpp:75-131: one (origin, direction) pair per film column */
 struct MRadianceMeter { std::vector<std::array<double, 3>> origins, directions; int medium = -1; };
@@ -313,7 +317,9 @@ public:
     }
 
     /* src/shapes/rectangle.cpp:75-104 */
-    int add_rectangle(const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1) {
+    /* sample_only: a rectangle of a sensor's own (its ray_target / ray_origin), not a child of the scene: never
+       intersected by paths and outside the scene's bounding box (B2vpShape::sample_only) */
+    int add_rectangle(const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1, bool sample_only = false) {
         const Mat4<F> to_world = prop_xf(to_world_);
         B2vpShape s{};
         s.type = B2VP_SHAPE_RECTANGLE; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
@@ -324,7 +330,9 @@ public:
         for (int k = 0; k < 3; ++k) { s.frame_s[k] = dp_du[k]; s.frame_t[k] = dp_dv[k]; s.frame_n[k] = n[k]; }
         s.inv_surface_area = (double) ((F) 1 / area);
         const F corners[4][3] = { { -1, -1, 0 }, { 1, -1, 0 }, { 1, 1, 0 }, { -1, 1, 0 } };
-        for (auto &c : corners) expand(to_world.point({ c[0], c[1], c[2] }));
+        if (!sample_only)
+            for (auto &c : corners) expand(to_world.point({ c[0], c[1], c[2] }));
+        s.sample_only = sample_only ? 1 : 0;
         s.to_world = to_world.pod(); s.to_object = to_world.inverse().pod();
         sc_->shapes.push_back(s);
         return (int) sc_->shapes.size() - 1;
@@ -463,7 +471,9 @@ public:
         o.to_world = prop_xf(Mat4<F>::look_at({ 0, 0, 0 }, d, up)).pod();   /* AnimatedTransform: single precision */
         o.target_type = sn.has_ray_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
         for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.ray_target[k]);
+        if (sn.ray_target_shape >= 0) { o.target_type = B2VP_TARGET_SHAPE; o.target_shape = rectangle_index(sn.ray_target_shape); }
         o.origin_type = B2VP_ORIGIN_BSPHERE;
+        if (sn.ray_origin_shape >= 0) { o.origin_type = B2VP_ORIGIN_SHAPE; o.origin_shape = rectangle_index(sn.ray_origin_shape); }
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
@@ -485,6 +495,7 @@ public:
         o.type = B2VP_SENSOR_MDISTANT; o.needs_aperture_sample = 1;
         o.target_type = sn.has_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
         for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.target[k]);
+        if (sn.target_shape >= 0) { o.target_type = B2VP_TARGET_SHAPE; o.target_shape = rectangle_index(sn.target_shape); }
         o.origin_type = B2VP_ORIGIN_BSPHERE;
         sc_->sensor_transforms.clear();
         for (const auto &dir : sn.directions) {
@@ -592,6 +603,11 @@ private:
         Vec3<F> a = to_world.point({ 0, 0, 0 }), b = to_world.point({ 1, 1, 1 });
         for (int k = 0; k < 3; ++k) { o.bbox_min[k] = std::min(a[k], b[k]); o.bbox_max[k] = std::max(a[k], b[k]); }
         sc_->volumes.push_back(o);
+    }
+    int rectangle_index(int shape) const {
+        if (shape >= (int) sc_->shapes.size() || sc_->shapes[(size_t) shape].type != B2VP_SHAPE_RECTANGLE)
+            throw Error(B2VP_ERR_UNSUPPORTED, "sensor target / origin shape must be a rectangle");
+        return shape;
     }
     B2vpSensor base_sensor(const HdrFilm &film, const IndependentSampler &sampler, int medium) {
         B2vpSensor o{};

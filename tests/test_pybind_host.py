@@ -34,7 +34,19 @@ def _cases(pkg, tmp_path):
         "c2_gaussian": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "gaussian", "stddev": 0.7}),
         "c2_mitchell": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "mitchell", "B": 0.25, "C": 0.5}),
         "c2_lanczos": lambda v: _film(scenes.c2(spp=2, variant=v), {"type": "lanczos", "lobes": 2}),
+        # sensors that use a shape: a rectangle of the scene as target, one of the sensor's own as target and as origin
+        "c2_target_ref": lambda v: _golden()._target_shape(scenes.c2(spp=4, variant=v, width=16)),
+        "c2_nested_target_origin": lambda v: _golden()._origin_shape(_golden()._nested_target(scenes.c2(spp=4, variant=v, width=16))),
+        "c2_mdistant_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=4, variant=v, width=16, sensor="mdistant"), "target"),
+        "c3_origin_ref": lambda v: _golden()._target_shape(scenes.c3(spp=1, variant=v, n=8, size=6), "ray_origin", "top"),
     }
+
+
+def _golden():
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_ref_golden
+    return make_ref_golden
 
 
 def _film(d, rfilter, **crop):
@@ -49,7 +61,8 @@ def _as_host_scene(pkg, s):
 
 
 NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment",
-         "c2_tent_crop", "c2_gaussian", "c2_mitchell", "c2_lanczos"]
+         "c2_tent_crop", "c2_gaussian", "c2_mitchell", "c2_lanczos",
+         "c2_target_ref", "c2_nested_target_origin", "c2_mdistant_nested_target", "c3_origin_ref"]
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
