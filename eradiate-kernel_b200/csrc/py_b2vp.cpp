@@ -65,6 +65,29 @@ template <typename F> struct Loader {
         if (t == "rayleigh") return b2vp::Phase::rayleigh();
         if (t == "hg") return b2vp::Phase::hg(get<double>(d, "g", 0.8));
         if (t == "tabphase") return b2vp::Phase::tabulated(py::cast<std::vector<double>>(d["values"]));
+        if (t == "blendphase") {   /* blendphase.cpp:42-66: the two nested phase functions in key order + `weight` */
+            std::map<std::string, py::dict> kids;
+            for (auto kv : d) {
+                const std::string k = py::cast<std::string>(kv.first);
+                if (k != "weight" && py::isinstance<py::dict>(kv.second)) kids.emplace(k, py::cast<py::dict>(kv.second));
+            }
+            if (kids.size() != 2) throw std::runtime_error("BlendPhase: Two child phase functions must be specified!");
+            if (!d.contains("weight")) throw std::runtime_error("Property \"weight\" has not been specified!");
+            auto it = kids.begin();
+            const b2vp::Phase a = phase(it->second), b = phase((++it)->second);
+            if (!py::isinstance<py::dict>(d["weight"])) return b2vp::Phase::blend(a, b, py::cast<double>(d["weight"]));
+            const py::dict w = py::cast<py::dict>(d["weight"]);
+            if (type_of(w) == "constvolume") return b2vp::Phase::blend(a, b, get<double>(w, "value", 1.0));
+            if (type_of(w) != "gridvolume") unsupported("volume", type_of(w));
+            b2vp::Phase p = b2vp::Phase::blend(a, b, 0.0);
+            const b2vp::GridVolume g = grid(w);
+            if (g.channels != 1) throw std::runtime_error("blendphase: the weight grid must have one channel");
+            p.weight_grid = g.data; p.weight_res[0] = g.nx; p.weight_res[1] = g.ny; p.weight_res[2] = g.nz;
+            p.weight_filter = g.filter_type; p.weight_wrap = g.wrap_mode;
+            const b2vp::Mat4<F> tw = xf(w);
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) p.weight_to_world[(size_t) (r * 4 + c)] = (double) tw(r, c);
+            return p;
+        }
         unsupported("phase function", t);
     }
     b2vp::GridVolume grid(const py::dict &d) {
@@ -129,6 +152,7 @@ template <typename F> struct Loader {
         unsupported("BSDF", t);
     }
     std::map<std::string, int> shapes;   /* id (or key) -> shape index, for sensors that refer to a shape */
+    py::dict shape_sensor; int shape_sensor_index = -1; bool have_shape_sensor = false;
     /* a shape given to a sensor (distant.cpp:270-290): a reference to a rectangle of the scene, or a rectangle of the
        sensor's own, which is used by the sensor only (sample_only) */
     int sensor_shape(const py::dict &d, const char *key) {
@@ -146,7 +170,15 @@ template <typename F> struct Loader {
         if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj") return false;
         const int b = bsdf(d), in = medium_ref(d, "interior"), ex = medium_ref(d, "exterior");
         if (t == "cube") sb.add_cube(xf(d), b, in, ex);
-        else if (t == "rectangle") shapes[get<std::string>(d, "id", key)] = sb.add_rectangle(xf(d), b, in, ex);
+        else if (t == "rectangle") {
+            const int index = sb.add_rectangle(xf(d), b, in, ex);
+            shapes[get<std::string>(d, "id", key)] = index;
+            if (d.contains("sensor")) {   /* a sensor attached to the shape (shape.cpp:47-54): the irradiancemeter */
+                if (have_shape_sensor) throw std::runtime_error("the B200 volpath renders one sensor per scene");
+                shape_sensor = py::cast<py::dict>(d["sensor"]); shape_sensor_index = index; have_shape_sensor = true;
+                if (type_of(shape_sensor) != "irradiancemeter") throw std::runtime_error("only an irradiancemeter on a rectangle is supported as a shape sensor");
+            }
+        }
         else if (t == "sphere") {
             b2vp::Sphere s;
             if (d.contains("center")) s.center = vec3(d["center"]);
@@ -200,6 +232,24 @@ template <typename F> struct Loader {
             if (d.contains("ray_origin")) s.ray_origin_shape = sensor_shape(d, "ray_origin");
             s.flip_directions = get<bool>(d, "flip_directions", false); s.medium = med;
             sb.set_sensor(s, film, smp);
+        } else if (t == "distantflux") {   /* distantflux.cpp:140-182 */
+            b2vp::DistantFlux s;
+            const b2vp::Mat4<F> tw = xf(d);
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) s.to_world[(size_t) (r * 4 + c)] = (double) tw(r, c);
+            if (d.contains("target")) {
+                if (py::isinstance<py::dict>(d["target"])) s.target_shape = sensor_shape(d, "target");
+                else { s.has_target = true; s.target = vec3(d["target"]); }
+            }
+            if (d.contains("origin")) s.origin_shape = sensor_shape(d, "origin");
+            s.medium = med;
+            sb.set_sensor(s, film, smp);
+        } else if (t == "irradiancemeter") {   /* irradiancemeter.cpp:54-80 */
+            if (d.contains("to_world"))
+                throw std::runtime_error("Found a 'to_world' transformation -- this is not allowed. The irradiance meter inherits this transformation from its parent shape.");
+            if (d.contains("film") && (film.width != 1 || film.height != 1)) throw std::runtime_error("This sensor only supports films of size 1x1 Pixels!");
+            b2vp::IrradianceMeter s;
+            s.shape = shape_sensor_index; s.medium = med;
+            sb.set_sensor(s, smp);
         } else if (t == "radiancemeter") {
             b2vp::RadianceMeter s;
             s.origin = vec3(d["origin"]); s.direction = vec3(d["direction"]); s.medium = med;
@@ -274,14 +324,15 @@ template <typename F> struct Loader {
                 sb.add_emitter(e);
             } else if (t == "constant") sb.add_emitter(b2vp::Constant{ get<double>(d, "radiance", 1.0) });
             else if (t == "volpath" || t == "volpathmis" || t == "moment") integrator(d);
-            else if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") continue;   /* below */
+            else if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter" || t == "distantflux") continue;   /* below */
             else unsupported("scene", t);
         }
         /* the sensor last: it may refer to a shape whose key sorts after its own */
         for (auto &kv : items) {
             const std::string t = type_of(kv.second);
-            if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter") sensor(kv.second);
+            if (t == "distant" || t == "radiancemeter" || t == "mdistant" || t == "mradiancemeter" || t == "distantflux") sensor(kv.second);
         }
+        if (have_shape_sensor) sensor(shape_sensor);
         return sb.finish();
     }
 };

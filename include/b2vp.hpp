@@ -154,6 +154,19 @@ struct Phase {
         for (double x : v) if (x < 0) throw Error(B2VP_ERR_INVALID, "ContinuousDistribution: entries must be non-negative!");
         Phase p; p.type = B2VP_PHASE_TABULATED; p.values = std::move(v); return p;
     }
+    /* src/phase/blendphase.cpp:42-140: (1 - w) a + w b with the weight volume w evaluated where the path scatters.
+       The weight is a constant (`weight_value`) or a grid (`weight_grid`: data[((z ny + y) nx + x)], resolution,
+       filter / wrap mode and a row-major 4 x 4 to_world, the members of GridVolume below) */
+    std::vector<Phase> children;
+    double weight_value = 0.5;
+    std::vector<float> weight_grid; int weight_res[3] = { 0, 0, 0 };
+    std::string weight_filter = "trilinear", weight_wrap = "clamp";
+    std::array<double, 16> weight_to_world{ 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+    static Phase blend(const Phase &a, const Phase &b, double weight) {
+        if (a.type == B2VP_PHASE_BLEND || b.type == B2VP_PHASE_BLEND)
+            throw Error(B2VP_ERR_UNSUPPORTED, "blendphase: nested blends are not supported by the B200 volpath");
+        Phase p; p.type = B2VP_PHASE_BLEND; p.children = { a, b }; p.weight_value = weight; return p;
+    }
 };
 /* src/textures/constant3d.cpp:13-55 */
 struct ConstVolume { double value = 1.0; };
@@ -206,6 +219,16 @@ struct Distant {
        the sensor's own, one added with sample_only = true.  -1: the point target above / the bounding sphere */
     int ray_target_shape = -1, ray_origin_shape = -1;
 };
+/* src/sensors/distantflux.cpp:140-182: a film over the hemisphere around to_world * (0, 0, 1); target point, target
+   rectangle (an index add_rectangle returned) or none; rays start on the bounding sphere or on an origin rectangle */
+struct DistantFlux {
+    std::array<double, 16> to_world{ 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };   /* row-major */
+    bool has_target = false; std::array<double, 3> target{ 0, 0, 0 };
+    int target_shape = -1, origin_shape = -1;
+    int medium = -1;
+};
+/* src/sensors/irradiancemeter.cpp:54-80: attached to a rectangle of the scene (`shape` = the index add_rectangle returned) */
+struct IrradianceMeter { int shape = -1; int medium = -1; };
 /* src/sensors/radiancemeter.cpp:61-104 */
 struct RadianceMeter { std::array<double, 3> origin{ 0, 0, 0 }, direction{ 0, 0, 1 }; int medium = -1; };
 /* src/shapes/sphere.cpp:95-160: `center`, `radius`, `flip_normals` (+ a to_world given to add_sphere) */
@@ -477,6 +500,31 @@ public:
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
+    void set_sensor(const DistantFlux &sn, const HdrFilm &film, const IndependentSampler &sampler) {
+        B2vpSensor o = base_sensor(film, sampler, sn.medium);
+        o.type = B2VP_SENSOR_DISTANTFLUX; o.needs_aperture_sample = 1;
+        Mat4<F> tw;
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) tw(r, c) = (F) sn.to_world[(size_t) (r * 4 + c)];
+        tw = prop_xf(tw);                           /* AnimatedTransform / props.transform(): single precision */
+        o.to_world = tw.pod();
+        const Vec3<F> n = tw.vector({ 0, 0, 1 });   /* m_reference_normal (distantflux.cpp:173-175) */
+        for (int k = 0; k < 3; ++k) o.reference_normal[k] = (double) n[k];
+        o.target_type = sn.has_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
+        for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.target[k]);
+        if (sn.target_shape >= 0) { o.target_type = B2VP_TARGET_SHAPE; o.target_shape = rectangle_index(sn.target_shape); }
+        o.origin_type = B2VP_ORIGIN_BSPHERE;
+        if (sn.origin_shape >= 0) { o.origin_type = B2VP_ORIGIN_SHAPE; o.origin_shape = rectangle_index(sn.origin_shape); }
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
+    void set_sensor(const IrradianceMeter &sn, const IndependentSampler &sampler) {
+        B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
+        o.type = B2VP_SENSOR_IRRADIANCEMETER; o.needs_aperture_sample = 1;
+        if (sn.shape < 0) throw Error(B2VP_ERR_INVALID, "irradiancemeter: no parent shape");
+        o.origin_shape = rectangle_index(sn.shape);
+        sc_->desc.sensor = o;
+        have_sensor_ = true;
+    }
     void set_sensor(const RadianceMeter &sn, const IndependentSampler &sampler) {
         B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
         o.type = B2VP_SENSOR_RADIANCEMETER; o.needs_aperture_sample = 0;
@@ -584,14 +632,30 @@ private:
         sc_->bsdfs.push_back(b);
         return (int) sc_->bsdfs.size() - 1;
     }
-    int push_medium(B2vpMedium o, F scale, bool spectral, bool sample_emitters, const Phase &ph) {
+    int push_phase(const Phase &ph) {
         B2vpPhase p{};
         p.type = ph.type; p.g = (double) prop(ph.g);
+        if (ph.type == B2VP_PHASE_BLEND) {
+            if (ph.children.size() != 2) throw Error(B2VP_ERR_INVALID, "BlendPhase: Two child phase functions must be specified!");
+            p.child[0] = push_phase(ph.children[0]); p.child[1] = push_phase(ph.children[1]);
+            if (ph.weight_grid.empty()) p.weight_volume = add_volume(ConstVolume{ ph.weight_value });
+            else {
+                GridVolume g;
+                g.data = ph.weight_grid; g.nx = ph.weight_res[0]; g.ny = ph.weight_res[1]; g.nz = ph.weight_res[2];
+                g.filter_type = ph.weight_filter; g.wrap_mode = ph.weight_wrap;
+                Mat4<F> tw;
+                for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) tw(r, c) = (F) ph.weight_to_world[(size_t) (r * 4 + c)];
+                p.weight_volume = add_volume(g, tw);
+            }
+        }
         std::vector<double> vals;
         for (double x : ph.values) vals.push_back((double) (F) x);   /* (ScalarFloat) std::stod(..) */
         sc_->phases.push_back(p);
         sc_->phase_values.push_back(std::move(vals));
-        o.phase = (int) sc_->phases.size() - 1;
+        return (int) sc_->phases.size() - 1;
+    }
+    int push_medium(B2vpMedium o, F scale, bool spectral, bool sample_emitters, const Phase &ph) {
+        o.phase = push_phase(ph);
         o.scale = scale; o.has_spectral_extinction = spectral; o.sample_emitters = sample_emitters;
         sc_->media.push_back(o);
         return (int) sc_->media.size() - 1;

@@ -39,6 +39,12 @@ def _cases(pkg, tmp_path):
         "c2_nested_target_origin": lambda v: _golden()._origin_shape(_golden()._nested_target(scenes.c2(spp=4, variant=v, width=16))),
         "c2_mdistant_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=4, variant=v, width=16, sensor="mdistant"), "target"),
         "c3_origin_ref": lambda v: _golden()._target_shape(scenes.c3(spp=1, variant=v, n=8, size=6), "ray_origin", "top"),
+        # blendphase (grid and constant weight), distantflux (with an origin rectangle), irradiancemeter
+        "c2_blendphase": lambda v: _golden()._blendphase(True, spp=4, variant=v, width=16),
+        "c2_blendphase_const": lambda v: _golden()._blendphase(False, spp=4, variant=v, width=16),
+        "c2_distantflux": lambda v: _golden()._distantflux(True, spp=1, variant=v),
+        "c2_distantflux_origin": lambda v: _golden()._origin_shape(_golden()._distantflux(False, spp=1, variant=v), "origin", half=4.0),
+        "c2_irradiancemeter": lambda v: _golden()._irradiancemeter(64, v),
     }
 
 
@@ -62,7 +68,8 @@ def _as_host_scene(pkg, s):
 
 NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment",
          "c2_tent_crop", "c2_gaussian", "c2_mitchell", "c2_lanczos",
-         "c2_target_ref", "c2_nested_target_origin", "c2_mdistant_nested_target", "c3_origin_ref"]
+         "c2_target_ref", "c2_nested_target_origin", "c2_mdistant_nested_target", "c3_origin_ref",
+         "c2_blendphase", "c2_blendphase_const", "c2_distantflux", "c2_distantflux_origin", "c2_irradiancemeter"]
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
@@ -93,7 +100,10 @@ def test_pybind_rejects_what_the_cpp_host_does_not_cover(pkg, tmp_path):
         ext.load_dict(d)
     d = scenes.c2(spp=1, width=4)
     d["atm"]["phase"] = {"type": "blendphase"}
-    with pytest.raises(RuntimeError, match="blendphase"):
+    with pytest.raises(RuntimeError, match="Two child phase functions"):
+        ext.load_dict(d)
+    d["atm"]["phase"] = {"type": "microflake"}
+    with pytest.raises(RuntimeError, match="microflake"):
         ext.load_dict(d)
     with pytest.raises(RuntimeError, match="variant"):
         ext.load_dict(scenes.c1(spp=1), "scalar_rgb")
