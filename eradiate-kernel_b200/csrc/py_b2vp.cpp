@@ -19,6 +19,7 @@
 #include <functional>
 #include <map>
 
+#define B2VP_WITH_ZLIB 1   /* the .serialized reader (zlib) */
 #include "b2vp.hpp"
 
 namespace py = pybind11;
@@ -167,7 +168,7 @@ template <typename F> struct Loader {
     }
     bool shape(const std::string &key, const py::dict &d) {
         const std::string t = type_of(d);
-        if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj") return false;
+        if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj" && t != "ply" && t != "serialized") return false;
         const int b = bsdf(d), in = medium_ref(d, "interior"), ex = medium_ref(d, "exterior");
         if (t == "cube") sb.add_cube(xf(d), b, in, ex);
         else if (t == "rectangle") {
@@ -184,9 +185,16 @@ template <typename F> struct Loader {
             if (d.contains("center")) s.center = vec3(d["center"]);
             s.radius = get<double>(d, "radius", 1.0); s.flip_normals = get<bool>(d, "flip_normals", false);
             sb.add_sphere(s, xf(d), b, in, ex);
-        } else {
-            if (get<bool>(d, "face_normals", false)) throw std::runtime_error("obj: face_normals is not supported by the C++ host");
-            sb.add_mesh(b2vp::load_obj(py::cast<std::string>(d["filename"]), get<bool>(d, "flip_tex_coords", true)), xf(d), b, in, ex);
+        } else {   /* src/shapes/obj.cpp, ply.cpp, serialized.cpp */
+            const std::string file = py::cast<std::string>(d["filename"]);
+            b2vp::MeshData m = t == "obj" ? b2vp::load_obj(file, get<bool>(d, "flip_tex_coords", true))
+                               : t == "ply" ? b2vp::load_ply(file) : b2vp::load_serialized(file, get<int>(d, "shape_index", 0));
+            const bool face_normals = get<bool>(d, "face_normals", false);   /* mesh.cpp:30-31: no vertex normals at all */
+            if (m.normals.empty() && !face_normals)
+                throw std::runtime_error("mesh files without normals need face_normals=true (smooth vertex normals, "
+                                         "Mesh::recompute_vertex_normals, are not built in the B200 volpath)");
+            if (face_normals) m.normals.clear();
+            sb.add_mesh(m, xf(d), b, in, ex);
         }
         return true;
     }

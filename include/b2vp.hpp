@@ -25,6 +25,9 @@
 
 #include <algorithm>
 #include <array>
+#ifdef B2VP_WITH_ZLIB
+#include <zlib.h>
+#endif
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -248,6 +251,17 @@ struct MeshData { std::vector<float> positions, normals, texcoords; std::vector<
 /* Wavefront OBJ as src/shapes/obj.cpp:140-325 reads it: v / vn / vt / f, one output vertex per distinct (v, vt, vn)
    index triple in order of first use, polygons as triangle fans, v flipped to 1 - v unless flip_tex_coords = false */
 inline MeshData load_obj(const std::string &path, bool flip_tex_coords = true);
+/* Stanford PLY as src/shapes/ply.cpp:102-380 reads it: ascii or binary of either byte order; element `vertex` with
+   x y z, optional nx ny nz and texture coordinates (u v / texture_u texture_v / s t); element `face` with one
+   vertex_index(es) list of exactly three indices per face; other elements and scalar properties are skipped */
+inline MeshData load_ply(const std::string &path);
+#ifdef B2VP_WITH_ZLIB
+/* One mesh of a `.serialized` container (src/shapes/serialized.cpp:174-340): [u16 0x041C][u16 version 3 | 4], a zlib
+   stream of flags, (v4) name, vertex and face counts, positions, [normals], [texcoords], [colours], u32 indices; reals
+   float32 or (flag 0x2000) float64; for shape_index > 0 the offset dictionary at the end of the file.  Needs zlib:
+   compile with -DB2VP_WITH_ZLIB and link -lz */
+inline MeshData load_serialized(const std::string &path, int shape_index = 0);
+#endif
 /* src/integrators/volpath.cpp:19-25, src/librender/integrator.cpp:23-39,302-315 */
 struct Volpath {
     int max_depth = -1, rr_depth = 5; bool hide_emitters = false; uint32_t block_size = 0, samples_per_pass = 0xffffffffu;
@@ -948,5 +962,175 @@ inline MeshData load_obj(const std::string &path, bool flip_tex_coords) {
     }
     return m;
 }
+
+namespace detail {
+inline std::string read_file(const std::string &path, const std::string &what) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw Error(B2VP_ERR_INVALID, "Error while loading " + what + " file \"" + path + "\": file not found!");
+    std::ostringstream ss;
+    ss << f.rdbuf();
+    return ss.str();
+}
+/* a scalar of the given PLY type at p (byte order `big`), as double; returns its size */
+inline size_t ply_scalar(const std::string &type, const unsigned char *p, bool big, double &out) {
+    auto load = [&](size_t n, unsigned char *dst) { for (size_t i = 0; i < n; ++i) dst[i] = p[big ? n - 1 - i : i]; };
+    if (type == "char" || type == "int8") { out = (double) (int8_t) p[0]; return 1; }
+    if (type == "uchar" || type == "uint8") { out = (double) p[0]; return 1; }
+    if (type == "short" || type == "int16") { int16_t v; load(2, (unsigned char *) &v); out = v; return 2; }
+    if (type == "ushort" || type == "uint16") { uint16_t v; load(2, (unsigned char *) &v); out = v; return 2; }
+    if (type == "int" || type == "int32") { int32_t v; load(4, (unsigned char *) &v); out = v; return 4; }
+    if (type == "uint" || type == "uint32") { uint32_t v; load(4, (unsigned char *) &v); out = v; return 4; }
+    if (type == "float" || type == "float32") { float v; load(4, (unsigned char *) &v); out = v; return 4; }
+    if (type == "double" || type == "float64") { double v; load(8, (unsigned char *) &v); out = v; return 8; }
+    throw Error(B2VP_ERR_INVALID, "PLY: unknown property type " + type);
+}
+} // namespace detail
+
+inline MeshData load_ply(const std::string &path) {
+    const std::string raw = detail::read_file(path, "PLY");
+    auto fail = [&](const std::string &msg) -> void { throw Error(B2VP_ERR_INVALID, "Error while loading PLY file \"" + path + "\": " + msg + "!"); };
+    const size_t end = raw.find("end_header");
+    if (raw.compare(0, 3, "ply") != 0 || end == std::string::npos) fail("invalid PLY header");
+    const size_t body = raw.find('\n', end) + 1;
+    struct Prop { std::string name, type, count_type; bool list = false; };
+    struct Element { std::string name; size_t count = 0; std::vector<Prop> props; };
+    std::vector<Element> elements;
+    std::string format;
+    {
+        std::istringstream header(raw.substr(0, end));
+        std::string line;
+        std::getline(header, line);   /* "ply" */
+        while (std::getline(header, line)) {
+            std::istringstream in(line);
+            std::string tok;
+            if (!(in >> tok) || tok == "comment" || tok == "obj_info") continue;
+            if (tok == "format") in >> format;
+            else if (tok == "element") { Element e; in >> e.name >> e.count; elements.push_back(e); }
+            else if (tok == "property" && !elements.empty()) {
+                Prop p; std::string t;
+                in >> t;
+                if (t == "list") { p.list = true; in >> p.count_type >> p.type >> p.name; }
+                else { p.type = t; in >> p.name; }
+                elements.back().props.push_back(p);
+            }
+        }
+    }
+    if (format != "ascii" && format != "binary_little_endian" && format != "binary_big_endian") fail("invalid PLY format");
+    const bool ascii = format == "ascii", big = format == "binary_big_endian";
+    std::istringstream words(ascii ? raw.substr(body) : std::string());
+    size_t off = body;
+    auto next = [&](const std::string &type) -> double {
+        double v = 0;
+        if (ascii) { if (!(words >> v)) fail("file is truncated"); return v; }
+        unsigned char buf[8] = { 0 };   /* a copy, so that a truncated file is never read past its end */
+        const size_t left = off < raw.size() ? raw.size() - off : 0;
+        std::memcpy(buf, raw.data() + std::min(off, raw.size()), std::min<size_t>(8, left));
+        const size_t n = detail::ply_scalar(type, buf, big, v);
+        if (n > left) fail("file is truncated");
+        off += n;
+        return v;
+    };
+    MeshData m;
+    bool have_vertex = false, have_face = false;
+    for (const Element &el : elements) {
+        std::map<std::string, int> col;
+        int n_lists = 0;
+        for (size_t i = 0; i < el.props.size(); ++i) { col[el.props[i].name] = (int) i; n_lists += el.props[i].list; }
+        if (n_lists && !(el.name == "face" && n_lists == 1)) fail("unsupported list property in element '" + el.name + "'");
+        const bool vertex = el.name == "vertex", face = el.name == "face";
+        int cx = -1, cy = -1, cz = -1, cnx = -1, cny = -1, cnz = -1, cu = -1, cv = -1;
+        auto find = [&](const char *k) { auto it = col.find(k); return it == col.end() ? -1 : it->second; };
+        if (vertex) {
+            cx = find("x"); cy = find("y"); cz = find("z");
+            if (cx < 0 || cy < 0 || cz < 0) fail("vertex positions not found");
+            cnx = find("nx"); cny = find("ny"); cnz = find("nz");
+            if (cnx < 0 || cny < 0 || cnz < 0) cnx = cny = cnz = -1;
+            const char *names[3][2] = { { "u", "v" }, { "texture_u", "texture_v" }, { "s", "t" } };
+            for (auto &pr : names) if (find(pr[0]) >= 0 && find(pr[1]) >= 0) { cu = find(pr[0]); cv = find(pr[1]); break; }
+        }
+        if (face && find("vertex_index") < 0 && find("vertex_indices") < 0) fail("vertex_index/vertex_indices property not found");
+        std::vector<double> rec(el.props.size());
+        for (size_t r = 0; r < el.count; ++r) {
+            for (size_t i = 0; i < el.props.size(); ++i) {
+                const Prop &p = el.props[i];
+                if (!p.list) { rec[i] = next(p.type); continue; }
+                const int cnt = (int) next(p.count_type);
+                if (cnt != 3) fail("incompatible contents -- is this a triangle mesh?");
+                for (int k = 0; k < 3; ++k) m.faces.push_back((uint32_t) next(p.type));
+            }
+            if (vertex) {
+                for (int c : { cx, cy, cz }) m.positions.push_back((float) rec[(size_t) c]);
+                if (cnx >= 0) for (int c : { cnx, cny, cnz }) m.normals.push_back((float) rec[(size_t) c]);
+                if (cu >= 0) for (int c : { cu, cv }) m.texcoords.push_back((float) rec[(size_t) c]);
+            }
+        }
+        have_vertex |= vertex; have_face |= face;
+        if (!face && !vertex) continue;
+    }
+    if (!ascii && off != raw.size()) fail("invalid file -- trailing content");
+    if (!have_vertex || !have_face) fail("vertex / face element not found");
+    return m;
+}
+
+#ifdef B2VP_WITH_ZLIB
+inline MeshData load_serialized(const std::string &path, int shape_index) {
+    auto fail = [&](const std::string &msg) -> void { throw Error(B2VP_ERR_INVALID, "Error while loading serialized file \"" + path + "\": " + msg + "!"); };
+    if (shape_index < 0) fail("shape index must be nonnegative");
+    const std::string raw = detail::read_file(path, "serialized");
+    auto rd = [&](size_t at, size_t n, void *dst) { if (at + n > raw.size()) fail("file is truncated"); std::memcpy(dst, raw.data() + at, n); };
+    uint16_t fmt = 0, version = 0;
+    rd(0, 2, &fmt); rd(2, 2, &version);
+    if (fmt != 0x041C) fail("encountered an invalid file format");
+    if (version != 3 && version != 4) fail("encountered an incompatible file version");
+    size_t start = 0;
+    if (shape_index != 0) {   /* the offset dictionary at the end of the file (serialized.cpp:215-246) */
+        uint32_t count = 0;
+        rd(raw.size() - 4, 4, &count);
+        if ((uint32_t) shape_index > count)
+            fail("Unable to unserialize mesh, shape index is out of range! (requested " + std::to_string(shape_index) + " out of 0.." + std::to_string((int) count - 1) + ")");
+        if (version == 4) { uint64_t o; rd(raw.size() - 8 * (size_t) (count - (uint32_t) shape_index) - 4, 8, &o); start = (size_t) o; }
+        else { uint32_t o; rd(raw.size() - 4 * (size_t) (count - (uint32_t) shape_index + 1), 4, &o); start = o; }
+    }
+    if (start + 4 > raw.size()) fail("file is truncated");
+    std::string data;
+    {
+        z_stream zs{};
+        if (inflateInit(&zs) != Z_OK) fail("inflateInit()");
+        zs.next_in = (Bytef *) (raw.data() + start + 4); zs.avail_in = (uInt) (raw.size() - start - 4);
+        std::vector<char> buf(1 << 16);
+        int rc = Z_OK;
+        while (rc == Z_OK) {
+            zs.next_out = (Bytef *) buf.data(); zs.avail_out = (uInt) buf.size();
+            rc = inflate(&zs, Z_NO_FLUSH);
+            data.append(buf.data(), buf.size() - zs.avail_out);
+        }
+        inflateEnd(&zs);
+        if (rc != Z_STREAM_END) fail("inflate(): stream error");
+    }
+    size_t off = 0;
+    auto take = [&](size_t n, void *dst) { if (off + n > data.size()) fail("stream is truncated"); std::memcpy(dst, data.data() + off, n); off += n; };
+    uint32_t flags = 0;
+    take(4, &flags);
+    if (version == 4) { const size_t z = data.find('\0', off); if (z == std::string::npos) fail("stream is truncated"); off = z + 1; }
+    uint64_t n_vert = 0, n_face = 0;
+    take(8, &n_vert); take(8, &n_face);
+    const bool dbl = (flags & 0x2000u) != 0;
+    auto reals = [&](size_t dim, std::vector<float> *out) {
+        for (uint64_t i = 0; i < n_vert * dim; ++i) {
+            float v;
+            if (dbl) { double d; take(8, &d); v = (float) d; } else take(4, &v);
+            if (out) out->push_back(v);
+        }
+    };
+    MeshData m;
+    reals(3, &m.positions);
+    if (flags & 0x0001u) reals(3, &m.normals);
+    if (flags & 0x0002u) reals(2, &m.texcoords);
+    if (flags & 0x0008u) reals(3, nullptr);
+    m.faces.resize((size_t) n_face * 3);
+    take(m.faces.size() * 4, m.faces.data());
+    return m;
+}
+#endif
 
 } // namespace b2vp

@@ -45,6 +45,13 @@ def _cases(pkg, tmp_path):
         "c2_distantflux": lambda v: _golden()._distantflux(True, spp=1, variant=v),
         "c2_distantflux_origin": lambda v: _golden()._origin_shape(_golden()._distantflux(False, spp=1, variant=v), "origin", half=4.0),
         "c2_irradiancemeter": lambda v: _golden()._irradiancemeter(64, v),
+        # mesh files: PLY (binary with normals and texcoords; ascii with face normals), `.serialized` (v4 float32 with
+        # normals, sub-mesh 1; v3 float64, positions only), OBJ with face normals
+        "c2_ply_binary": lambda v: _golden()._c2_ply("roof_bin.ply", False, spp=2, variant=v, width=16),
+        "c2_ply_ascii": lambda v: _golden()._c2_ply("roof_ascii.ply", True, spp=2, variant=v, width=16),
+        "c2_serialized": lambda v: _golden()._c2_ply("roof.serialized", False, "serialized", 1, spp=2, variant=v, width=16),
+        "c2_serialized_v3": lambda v: _golden()._c2_ply("roof_v3_f64.serialized", True, "serialized", 1, spp=2, variant=v, width=16),
+        "c2_obj_face_normals": lambda v: _golden()._c2_obj(True, spp=2, variant=v, width=16),
     }
 
 
@@ -69,7 +76,8 @@ def _as_host_scene(pkg, s):
 NAMES = ["c1", "c2", "c2_mdistant_mis", "c3", "ext_mdistant", "ext_mradiancemeter", "c2_sky_moment",
          "c2_tent_crop", "c2_gaussian", "c2_mitchell", "c2_lanczos",
          "c2_target_ref", "c2_nested_target_origin", "c2_mdistant_nested_target", "c3_origin_ref",
-         "c2_blendphase", "c2_blendphase_const", "c2_distantflux", "c2_distantflux_origin", "c2_irradiancemeter"]
+         "c2_blendphase", "c2_blendphase_const", "c2_distantflux", "c2_distantflux_origin", "c2_irradiancemeter",
+         "c2_ply_binary", "c2_ply_ascii", "c2_serialized", "c2_serialized_v3", "c2_obj_face_normals"]
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
