@@ -38,7 +38,7 @@ def _cases(pkg, tmp_path):
         "c2_target_ref": lambda v: _golden()._target_shape(scenes.c2(spp=4, variant=v, width=16)),
         "c2_nested_target_origin": lambda v: _golden()._origin_shape(_golden()._nested_target(scenes.c2(spp=4, variant=v, width=16))),
         "c2_mdistant_nested_target": lambda v: _golden()._nested_target(scenes.c2(spp=4, variant=v, width=16, sensor="mdistant"), "target"),
-        "c3_origin_ref": lambda v: _golden()._target_shape(scenes.c3(spp=1, variant=v, n=8, size=6), "ray_origin", "top"),
+        "c3_origin_ref": lambda v: _golden()._target_shape(scenes.c3(spp=8, variant=v, n=8, size=6), "ray_origin", "top"),
         # blendphase (grid and constant weight), distantflux (with an origin rectangle), irradiancemeter
         "c2_blendphase": lambda v: _golden()._blendphase(True, spp=4, variant=v, width=16),
         "c2_blendphase_const": lambda v: _golden()._blendphase(False, spp=4, variant=v, width=16),
