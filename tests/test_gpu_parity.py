@@ -185,6 +185,26 @@ def test_volpathmis_runs_on_the_queue_kernel(pkg, oracle, variant):
 
 
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+def test_aerosol_and_flux_scenes_take_their_preset(pkg, oracle, variant):
+    """Atmospheres with particles (tabphase, blendphase with a grid or constant weight) and the flux sensors have a
+    preset of their own (PRE_HET_AER, both integrators) instead of the all-features instance: same bits, 1.4x faster."""
+    abi = pkg.abi
+    for make in (lambda: _tabphase(variant), lambda: _blendphase(variant, True), lambda: _blendphase(variant, False),
+                 lambda: _distantflux(variant, True), lambda: _irradiancemeter(variant)):
+        for integ, name in (("volpath", "queue/heterogeneous, aerosols"), ("volpathmis", "queue/volpathmis, heterogeneous, aerosols")):
+            d = make()
+            d["integrator"] = dict(d["integrator"], type=integ)
+            sc = pkg.load_dict(d, variant)
+            with pkg.DeviceScene(sc) as ds:
+                got = ds.render(seed_mode=abi.SEED_WAVEFRONT, want_paths=True)
+                assert ds.info().last_kernel.decode().startswith(name), ds.info().last_kernel.decode()
+                generic = ds.render(seed_mode=abi.SEED_WAVEFRONT, want_paths=True, kernel="generic")
+                assert "generic" in ds.info().last_kernel.decode()
+            assert np.array_equal(got.state, generic.state) and np.array_equal(got.counters, generic.counters)
+            assert np.array_equal(got.radiance.view(np.uint8), generic.radiance.view(np.uint8))
+
+
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
 def test_scalar_block_seeding_bit_exact(pkg, oracle, variant):
     """Reference scalar-mode seeding: one stream per pixel, spp drawn serially (integrator.cpp:197-208)."""
     sc = pkg.load_dict(scenes.c2(spp=32, variant=variant, width=48, block_size=16), variant)
