@@ -19,6 +19,9 @@ constexpr uint32_t PRE_HET_ALB = PRE_FLAT | FT_HETERO | FT_TRILINEAR | FT_GRID_A
    including `distantflux` / `irradiancemeter` / rays starting on a shape.  The generic instance renders these at
    157-208 Mpaths/s where the plain-Rayleigh preset does 252-338 (tools/bench_aerosol.py) */
 constexpr uint32_t PRE_HET_AER = PRE_HET | FT_TABPHASE | FT_BLENDPHASE | FT_DISTANTFLUX;   /* + the flux / irradiance sensors */
+/* a large mesh (BVH in HBM: a canopy) under a heterogeneous atmosphere with or without particles: Eradiate's
+   surface-atmosphere scenes (RAMI4ATM-like) */
+constexpr uint32_t PRE_HET_BIG = (PRE_HET_AER & ~FT_MESH_SMEM) | FT_MESH;
 constexpr uint32_t PRE_HET_MG = PRE_HET | FT_MAJORANT_GRID;           /* the same with majorant-grid free flights */
 constexpr uint32_t PRE_HET_ALB_MG = PRE_HET_ALB | FT_MAJORANT_GRID;
 
@@ -45,6 +48,13 @@ template <typename F, int MAXT> const void *pick_queue_kernel(uint32_t ft, bool 
     if constexpr (MAXT == 512) {
         if ((ft & ~PRE_HET_AER) == 0) { *name = "heterogeneous, aerosols"; return q_entry<F, MAXT, PRE_HET_AER>(); }
     }
+    if constexpr (MAXT == 512) {
+        if ((ft & ~PRE_HET_BIG) == 0) {
+            *name = "heterogeneous, large mesh";
+            if constexpr (sizeof(F) == 4) { *threads = BIG_MESH_THREADS; return q_entry<F, BIG_MESH_THREADS, PRE_HET_BIG>(); }
+            else return q_entry<F, MAXT, PRE_HET_BIG>();
+        }
+    }
     if ((ft & ~PRE_HET_G) == 0) { *name = "heterogeneous, grid in HBM"; return q_entry<F, MAXT, PRE_HET_G>(); }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "heterogeneous+albedo grid"; return q_entry<F, MAXT, PRE_HET_ALB>(); }
     if ((ft & ~PRE_HET_MG) == 0) { *name = "heterogeneous, majorant grid"; return q_entry<F, MAXT, PRE_HET_MG>(); }
@@ -66,6 +76,11 @@ template <typename F> const void *pick_queue_kernel_mis(uint32_t ft, bool force_
     }
     if ((ft & ~PRE_HET) == 0) { *name = "volpathmis, heterogeneous"; return q_entry<F, 512, PRE_HET | FT_MIS>(); }
     if ((ft & ~PRE_HET_AER) == 0) { *name = "volpathmis, heterogeneous, aerosols"; return q_entry<F, 512, PRE_HET_AER | FT_MIS>(); }
+    if ((ft & ~PRE_HET_BIG) == 0) {
+        *name = "volpathmis, heterogeneous, large mesh";
+        if constexpr (sizeof(F) == 4) { *threads = BIG_MESH_THREADS; return q_entry<F, BIG_MESH_THREADS, PRE_HET_BIG | FT_MIS>(); }
+        else return q_entry<F, 512, PRE_HET_BIG | FT_MIS>();
+    }
     if ((ft & ~PRE_HET_ALB) == 0) { *name = "volpathmis, heterogeneous+albedo grid"; return q_entry<F, 512, PRE_HET_ALB | FT_MIS>(); }
     *name = "volpathmis, generic";
     return q_entry<F, 512, FT_ALL | FT_MIS>();

@@ -204,6 +204,45 @@ def test_aerosol_and_flux_scenes_take_their_preset(pkg, oracle, variant):
             assert np.array_equal(got.radiance.view(np.uint8), generic.radiance.view(np.uint8))
 
 
+def _canopy_under_atmosphere(variant, aerosols):
+    """The C5 canopy under a heterogeneous 1D atmosphere (the C2 column over the slab), optionally with an aerosol layer
+    mixed in by a blendphase: the shape of Eradiate's surface-atmosphere scenes."""
+    import make_ref_golden
+    T = scenes.T
+    d = scenes.c5(spp=4, variant=variant, n_leaves=150, n_sensors=16)
+    grid = scenes.sigma_t_1d(64)
+    tw = T.translate([-1.5, -1.5, 0.2], np.float32) @ T.scale([3.0, 3.0, 0.8], np.float32)
+    d["atm"] = {"type": "heterogeneous", "sigma_t": {"type": "gridvolume", "data": grid, "to_world": tw},
+                "scale": 0.3 / float(grid.mean()) / 0.8, "albedo": 1.0, "phase": {"type": "rayleigh"}}
+    if aerosols:
+        w = np.clip(np.linspace(1.0, -0.5, 16), 0, 1).astype(np.float32).reshape(16, 1, 1)
+        d["atm"]["phase"] = {"type": "blendphase", "a_molecules": {"type": "rayleigh"},
+                             "b_aerosols": {"type": "tabphase", "values": make_ref_golden.TAB_AEROSOL},
+                             "weight": {"type": "gridvolume", "data": w, "to_world": tw}}
+    return d
+
+
+@pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
+@pytest.mark.parametrize("aerosols", [False, True])
+def test_canopy_under_a_heterogeneous_atmosphere(pkg, oracle, variant, aerosols):
+    """Preset PRE_HET_BIG (a mesh whose BVH is read from HBM under a heterogeneous atmosphere with or without
+    particles; 768-thread CTAs in fp32): the oracle's bits, the generic instance's bits, both integrators."""
+    abi = pkg.abi
+    for integ in ("volpath", "volpathmis"):
+        d = _canopy_under_atmosphere(variant, aerosols)
+        d["integrator"] = dict(d["integrator"], type=integ)
+        sc = pkg.load_dict(d, variant)
+        ref = oracle.render(pkg, sc, abi.SEED_WAVEFRONT, want_paths=True)
+        with pkg.DeviceScene(sc) as ds:
+            got = ds.render(seed_mode=abi.SEED_WAVEFRONT, want_paths=True)
+            name = ds.info().last_kernel.decode()
+            assert "heterogeneous, large mesh" in name or "heterogeneous, aerosols" in name, name
+            generic = ds.render(seed_mode=abi.SEED_WAVEFRONT, want_paths=True, kernel="generic")
+        for other in (generic, ref):
+            assert np.array_equal(got.state, other.state) and np.array_equal(got.counters, other.counters)
+            assert np.array_equal(got.radiance.view(np.uint8), other.radiance.view(np.uint8))
+
+
 @pytest.mark.parametrize("variant", ["scalar_mono", "scalar_mono_double"])
 def test_scalar_block_seeding_bit_exact(pkg, oracle, variant):
     """Reference scalar-mode seeding: one stream per pixel, spp drawn serially (integrator.cpp:197-208)."""

@@ -7,6 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import __graft_entry__ as ge
 pkg = ge.build()
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 import scenes
 abi = pkg.abi
 
@@ -62,6 +63,25 @@ if "c3" in which:
 if "c5" in which:
     run("C5", "canopy 1e6 triangles (BVH), homogeneous Rayleigh slab, diffuse leaves, mradiancemeter 4096, 256 spp",
         scenes.c5(spp=256, n_leaves=500000, n_sensors=4096))
+if "c5atm" in which or "c5aer" in which:
+    # what a RAMI4ATM-like Eradiate scene looks like: the C5 canopy under a HETEROGENEOUS 1D atmosphere (the C2 sigma_t
+    # column over the slab), Rayleigh only ("c5atm") or with an aerosol layer mixed in by a blendphase ("c5aer")
+    import make_ref_golden as _g
+    for tag in [t for t in ("c5atm", "c5aer") if t in which]:
+        d = scenes.c5(spp=256, n_leaves=500000, n_sensors=4096)
+        T = scenes.T
+        grid = scenes.sigma_t_1d(1000)
+        d["atm"] = {"type": "heterogeneous",
+                    "sigma_t": {"type": "gridvolume", "data": grid,
+                                "to_world": T.translate([-1.5, -1.5, 0.2], np.float32) @ T.scale([3.0, 3.0, 0.8], np.float32)},
+                    "scale": 0.3 / float(grid.mean()) / 0.8, "albedo": 1.0, "phase": {"type": "rayleigh"}}
+        if tag == "c5aer":
+            w = np.clip(np.linspace(1.0, -0.5, 64), 0, 1).astype(np.float32).reshape(64, 1, 1)
+            d["atm"]["phase"] = {"type": "blendphase", "a_molecules": {"type": "rayleigh"},
+                                 "b_aerosols": {"type": "tabphase", "values": _g.TAB_AEROSOL},
+                                 "weight": {"type": "gridvolume", "data": w, "to_world": d["atm"]["sigma_t"]["to_world"]}}
+        run(tag.upper(), "C5 canopy (1e6 triangles) under a heterogeneous 1D atmosphere%s, mradiancemeter 4096, 256 spp"
+            % (" with an aerosol layer" if tag == "c5aer" else ""), d)
 if "c4" in which:
     # mono spectral sweep: 64 wavelengths x the C2 atmosphere; per wavelength only scalars change (Rayleigh
     # extinction ~ lambda^-4, RPV rho_0(lambda)), applied with b2vp_scene_update -- no re-upload, no rebuild.
