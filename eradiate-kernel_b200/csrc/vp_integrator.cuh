@@ -175,7 +175,7 @@ template <typename F> struct PathCtx {
             if (sv.g->environment >= 0 && !si.valid() && active_surface) {
                 emitter_val = sv.emitters[sv.g->environment].irradiance;
                 emitter_pdf = K<F>::InvFourPi;
-                if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) sv.g->n_emitters);
+                if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * (F) (1.f / (float) sv.g->n_emitters);   /* scene.cpp:233 */
                 active = false; active_surface = false; active_medium = false;
             }
 
@@ -407,7 +407,7 @@ template <typename F> struct PathCtx {
                 bool count_direct = depth == 0 || specular_chain;
                 if (!count_direct) { /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
                     F emitter_pdf = K<F>::InvFourPi;
-                    if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) sv.g->n_emitters);
+                    if (sv.g->n_emitters > 1) emitter_pdf = emitter_pdf * (F) (1.f / (float) sv.g->n_emitters);   /* scene.cpp:233 */
                     update_weights(p_over_f_nee, emitter_pdf, (F) 1, true);
                 }
                 F emitted = sv.emitters[sv.g->environment].irradiance;

@@ -199,7 +199,7 @@ VP_D DirSample<F> queue_sample_emitter(const SceneView<F> &sv, Pcg32 &rng, F &ev
 /* Scene::pdf_emitter_direction for the environment (scene.cpp:221-235 over constant.cpp:106-110) */
 template <typename F> VP_D F env_pdf(const SceneView<F> &sv) {
     F pdf = K<F>::InvFourPi;
-    if (sv.g->n_emitters > 1) pdf = pdf * ((F) 1 / (F) sv.g->n_emitters);
+    if (sv.g->n_emitters > 1) pdf = pdf * (F) (1.f / (float) sv.g->n_emitters);   /* scene.cpp:233: a float quotient in every variant */
     return pdf;
 }
 /* The main path's ray left the scene: the environment is the emitter it "hits" (volpath.cpp:186-191,

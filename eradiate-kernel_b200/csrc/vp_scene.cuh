@@ -1071,7 +1071,7 @@ template <typename F> VP_D DirSample<F> sample_emitter_direction(const SceneView
     int index = 0;
     F emitter_pdf = 1;
     if (n > 1) {
-        emitter_pdf = (F) 1 / (F) n;
+        emitter_pdf = (F) (1.f / (float) n);   /* scene.cpp:183: `1.f / m_emitters.size()`, a float quotient in every variant */
         uint32_t idx = (uint32_t) (sx * (F) n);
         index = (int) (idx < (uint32_t) (n - 1) ? idx : (uint32_t) (n - 1));
     }
@@ -1097,7 +1097,7 @@ template <typename F> VP_D DirSample<F> sample_emitter_direction_env(const Scene
     int index = 0;
     F emitter_pdf = 1;
     if (n > 1) {
-        emitter_pdf = (F) 1 / (F) n;
+        emitter_pdf = (F) (1.f / (float) n);   /* scene.cpp:183: `1.f / m_emitters.size()`, a float quotient in every variant */
         uint32_t idx = (uint32_t) (sx * (F) n);
         index = (int) (idx < (uint32_t) (n - 1) ? idx : (uint32_t) (n - 1));
         sx = (sx - (F) index * emitter_pdf) * (F) n;

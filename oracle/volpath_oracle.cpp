@@ -1034,7 +1034,7 @@ DirectionSample<F> sample_emitter_direction(const OScene<F> &s, F sx, F sy, F &s
     size_t index = 0;
     F emitter_pdf = 1;
     if (n > 1) {
-        emitter_pdf = (F) 1 / (F) n;
+        emitter_pdf = (F) (1.f / (float) n);   /* `ScalarFloat emitter_pdf = 1.f / m_emitters.size()` (scene.cpp:183): a float quotient in every variant */
         index = std::min((size_t) (uint32_t) (sx * (F) n), n - 1);
         sx = (sx - (F) index * emitter_pdf) * (F) n; /* rescale sample.x() to [0, 1) again (scene.cpp:190) */
     }
@@ -1324,7 +1324,7 @@ template <typename F> struct Integrator {
                 emitter_val = (F) scene.emitters[scene.environment].irradiance;
                 /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
                 emitter_pdf = Consts<F>::InvFourPi;
-                if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) scene.emitters.size());
+                if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * (F) (1.f / (float) scene.emitters.size());   /* scene.cpp:233: (1.f / m_emitters.size()) */
                 active = false; active_surface = false; active_medium = false;
             }
 
@@ -1548,7 +1548,7 @@ template <typename F> struct Integrator {
                 bool count_direct = depth == 0 || specular_chain;
                 if (!count_direct) { /* Scene::pdf_emitter_direction (scene.cpp:221-235) over constant.cpp:106-110 */
                     F emitter_pdf = Consts<F>::InvFourPi;
-                    if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * ((F) 1 / (F) scene.emitters.size());
+                    if (scene.emitters.size() > 1) emitter_pdf = emitter_pdf * (F) (1.f / (float) scene.emitters.size());   /* scene.cpp:233: (1.f / m_emitters.size()) */
                     update_weights(p_over_f_nee, emitter_pdf, (F) 1, true);
                 }
                 F emitted = (F) scene.emitters[scene.environment].irradiance;

@@ -216,6 +216,12 @@ def _origin_shape(d, key="ray_origin", half=15.0, height=1.2, sweep=False):
     return d
 
 
+def _three_emitters(d):
+    d["sun2"] = {"type": "directional", "direction": [-0.4, 0.1, -1], "irradiance": 0.5}
+    d["sky"] = {"type": "constant", "radiance": 0.2}
+    return d
+
+
 def _irradiancemeter(spp, variant):
     """C2 with an `irradiancemeter` (src/sensors/irradiancemeter.cpp) on a small rectangle floating
     in the atmosphere, facing up: downwelling irradiance at that level."""
@@ -364,6 +370,11 @@ CASES = {
     "c3_origin_ref_f64": (lambda v: _target_shape(_c3(spp=1, variant=v, n=16, size=16), "ray_origin", "top"), "scalar_mono_double"),
     "c2_distantflux_origin": (lambda v: _origin_shape(_distantflux(True, spp=1, variant=v), "origin", half=2.0), "scalar_mono"),
     "c2_distantflux_origin_f64": (lambda v: _origin_shape(_distantflux(False, spp=1, variant=v), "origin", half=4.0), "scalar_mono_double"),
+    # three emitters: `ScalarFloat emitter_pdf = 1.f / m_emitters.size()` (scene.cpp:183,233) is a FLOAT quotient in
+    # every variant -- (double) (1.f / 3) in scalar_mono_double, 3e-8 away from 1 / 3 (found by the random-scene test)
+    "c2_three_emitters_f64": (lambda v: _three_emitters(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
+    "c2_three_emitters_volpathmis_f64": (lambda v: _mis(_three_emitters(scenes.c2(spp=2, variant=v, width=64))), "scalar_mono_double"),
+    "c5_three_emitters": (lambda v: _three_emitters(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256)), "scalar_mono"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
