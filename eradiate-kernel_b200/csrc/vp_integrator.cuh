@@ -388,9 +388,8 @@ template <typename F> struct PathCtx {
                     p_over_f_nee = p_over_f;
                     F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                    V3<F> wo = phase_sample_at(sv, sv.phases[m.phase], mi.p, ray.d, s1, s2x, s2y);
-                    /* the pdf phase->sample returns is the phase function value for every phase function in scope */
-                    F phase_pdf = phase_sample_pdf_at(sv, sv.phases[m.phase], mi.p, -ray.d, wo, s1);
+                    F phase_pdf;   /* what phase->sample returns with the direction (volpathmis.cpp:229) */
+                    V3<F> wo = phase_sample_at(sv, sv.phases[m.phase], mi.p, ray.d, s1, s2x, s2y, &phase_pdf);
                     ray = spawn_ray(mi.p, wo);
                     ray.mint = 0;
                     needs_intersection = true;

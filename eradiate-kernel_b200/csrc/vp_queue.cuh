@@ -715,8 +715,8 @@ volpath_q_kernel(const __grid_constant__ DScene<F> g, const __grid_constant__ DS
                     const DPhase<F> &phase_fn = sv.phases[m.phase];
                     F da = rng.next(F(), true), db = rng.next(F(), true), dc = rng.next(F(), true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                    V3<F> wo = phase_sample_at<F, FEAT>(sv, phase_fn, p, d, s1, s2x, s2y);
-                    const F phase_pdf = phase_sample_pdf_at<F, FEAT>(sv, phase_fn, p, -d, wo, s1);
+                    F phase_pdf;   /* what phase->sample returns with the direction (volpathmis.cpp:229) */
+                    V3<F> wo = phase_sample_at<F, FEAT>(sv, phase_fn, p, d, s1, s2x, s2y, &phase_pdf);
                     Ray<F> r = spawn_ray(p, wo);
                     r.mint = 0;
                     st_ray(s.cur, r);

@@ -878,9 +878,9 @@ template <typename F> VP_D F tab_sample(const DPhase<F> &ph, F value) {
     F t = y0 == y1 ? t_const : t_linear;
     return fma_((F) index + t, ph.interval_size, (F) -1);
 }
-template <typename F, uint32_t FEAT = FT_ALL> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo) {
+/* the phase function as a function of the cosine its eval() computes, dot(wo, wi) (isotropic: a constant) */
+template <typename F, uint32_t FEAT = FT_ALL> VP_D F phase_eval_cos(const DPhase<F> &ph, F cos_theta) {
     if (ph.type == 0) return K<F>::InvFourPi;
-    F cos_theta = dot(wo, wi);
     if ((FEAT & FT_TABPHASE) && ph.type == 3) /* tabphase.cpp:91-99 */
         return tab_eval_pdf(ph, -cos_theta) * ph.normalization * K<F>::InvTwoPi;
     if (ph.type == 1)
@@ -889,11 +889,20 @@ template <typename F, uint32_t FEAT = FT_ALL> VP_D F phase_eval(const DPhase<F> 
     F temp = (F) 1 + g * g + (F) 2 * g * cos_theta;
     return K<F>::InvFourPi * ((F) 1 - g * g) / (temp * sqrt_(temp));
 }
+template <typename F, uint32_t FEAT = FT_ALL> VP_D F phase_eval(const DPhase<F> &ph, V3<F> wi, V3<F> wo) {
+    if (ph.type == 0) return K<F>::InvFourPi;
+    return phase_eval_cos<F, FEAT>(ph, dot(wo, wi));
+}
 /* PhaseFunction::sample (rayleigh.cpp:47-66, hg.cpp:52-76, isotropic.cpp:31-39);
-   `d` is the incoming ray direction, the local frame is Frame3f(d) (medium.cpp:42) */
-template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2x, F s2y) {
-    if (ph.type == 0)
+   `d` is the incoming ray direction, the local frame is Frame3f(d) (medium.cpp:42).  `pdf` (volpathmis only): what
+   sample() returns with the direction -- the phase function at the LOCAL sampled cosine, eval_*(-cos_theta)
+   (rayleigh.cpp:63, hg.cpp:73, tabphase.cpp:79-80), not eval(wo): for a ray direction that is not exactly of unit
+   length (a sensor frame rounded to single precision) dot(to_world(wo), wi) is another number */
+template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPhase<F> &ph, V3<F> d, F s2x, F s2y, F *pdf = nullptr) {
+    if (ph.type == 0) {
+        if (pdf) *pdf = K<F>::InvFourPi;
         return square_to_uniform_sphere(s2x, s2y);
+    }
     F cos_theta;
     if ((FEAT & FT_TABPHASE) && ph.type == 3) { /* tabphase.cpp:68-89 */
         cos_theta = tab_sample(ph, s2x);
@@ -915,6 +924,7 @@ template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPha
     F s, c;
     sincos_((F) 2 * K<F>::Pi * s2y, s, c);
     V3<F> wo = mk3<F>(sin_theta * c, sin_theta * s, cos_theta);
+    if (pdf) *pdf = phase_eval_cos<F, FEAT>(ph, -cos_theta);
     return make_frame(d).to_world(wo);
 }
 
@@ -929,20 +939,11 @@ VP_D F phase_eval_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F>
            phase_eval<F, FEAT>(sv.phases[ph.child[1]], wi, wo) * w;
 }
 template <typename F, uint32_t FEAT = FT_ALL>
-VP_D V3<F> phase_sample_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> d, F s1, F s2x, F s2y) {
-    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_sample<F, FEAT>(ph, d, s2x, s2y);
+VP_D V3<F> phase_sample_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> d, F s1, F s2x, F s2y, F *pdf = nullptr) {
+    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_sample<F, FEAT>(ph, d, s2x, s2y, pdf);
     F w = min_(max_(volume_eval<F, FT_ALL, true>(sv, sv.volumes[ph.weight_volume], p), (F) 0), (F) 1);
-    return phase_sample<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], d, s2x, s2y);
-}
-
-/* The pdf PhaseFunction::sample returns with the direction (volpathmis.cpp:229): the value of the sampled phase
-   function in that direction; for a blend the pdf of the nested function that was picked, unweighted
-   (blendphase.cpp:97-112).  It enters the path weights only as pdf / pdf. */
-template <typename F, uint32_t FEAT = FT_ALL>
-VP_D F phase_sample_pdf_at(const SceneView<F> &sv, const DPhase<F> &ph, V3<F> p, V3<F> wi, V3<F> wo, F s1) {
-    if (!(FEAT & FT_BLENDPHASE) || ph.type != 4) return phase_eval<F, FEAT>(ph, wi, wo);
-    F w = min_(max_(volume_eval<F, FT_ALL, true>(sv, sv.volumes[ph.weight_volume], p), (F) 0), (F) 1);
-    return phase_eval<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], wi, wo);
+    /* the pdf of a blend is that of the nested function that was picked, unweighted (blendphase.cpp:97-112) */
+    return phase_sample<F, FEAT>(sv.phases[s1 > w ? ph.child[0] : ph.child[1]], d, s2x, s2y, pdf);
 }
 
 /* ------------------------------------------------------------------- BSDFs */

@@ -838,9 +838,12 @@ inline F phase_eval(const B2vpPhase &ph, const TabDistr<F> &tab, const MediumInt
 }
 /* PhaseFunction::sample (rayleigh.cpp:47-66, hg.cpp:52-76, isotropic.cpp:31-39) */
 template <typename F>
-inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const MediumInteraction<F> &mi, F s2x, F s2y) {
-    if (ph.type == B2VP_PHASE_ISOTROPIC)
+inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const MediumInteraction<F> &mi, F s2x, F s2y,
+                          F *pdf = nullptr) {
+    if (ph.type == B2VP_PHASE_ISOTROPIC) {
+        if (pdf) *pdf = Consts<F>::InvFourPi;   /* square_to_uniform_sphere_pdf (isotropic.cpp:37) */
         return square_to_uniform_sphere(s2x, s2y);
+    }
     F cos_theta;
     if (ph.type == B2VP_PHASE_TABULATED) { /* tabphase.cpp:68-89 */
         cos_theta = tab.sample(s2x);
@@ -861,6 +864,10 @@ inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const Med
     F sin_theta = safe_sqrt_((F) 1 - cos_theta * cos_theta);
     auto sc = sincos_((F) 2 * Consts<F>::Pi * s2y);
     V3<F> wo = { sin_theta * sc.second, sin_theta * sc.first, cos_theta };
+    /* the pdf returned with the sample is the phase function at the LOCAL sampled cosine, eval_*(-cos_theta)
+       (rayleigh.cpp:63, hg.cpp:73, tabphase.cpp:79-80) -- not eval(wo): with a ray direction that is not exactly of
+       unit length (a sensor frame rounded to single precision) dot(to_world(wo), wi) is another number */
+    if (pdf) *pdf = phase_eval_cos(ph, tab, -cos_theta);
     return mi.sh_frame.to_world(wo);
 }
 
@@ -877,25 +884,15 @@ template <typename F> inline F phase_eval_at(const OScene<F> &s, int idx, const 
            phase_eval(s.phases[ph.child[1]], s.tabs[ph.child[1]], mi, wo) * weight;
 }
 template <typename F>
-inline V3<F> phase_sample_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, F s1, F s2x, F s2y) {
+inline V3<F> phase_sample_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, F s1, F s2x, F s2y,
+                             F *pdf = nullptr) {
     const B2vpPhase &ph = s.phases[idx];
-    if (ph.type != B2VP_PHASE_BLEND) return phase_sample(ph, s.tabs[idx], mi, s2x, s2y);
+    if (ph.type != B2VP_PHASE_BLEND) return phase_sample(ph, s.tabs[idx], mi, s2x, s2y, pdf);
     F weight = blend_weight(s, ph, mi);
-    /* the rescaled sample1 is passed on, none of the nested phase functions in scope uses it */
+    /* the rescaled sample1 is passed on, none of the nested phase functions in scope uses it; the pdf is that of the
+       nested function that was picked, unweighted (blendphase.cpp:97-112) */
     int c = s1 > weight ? ph.child[0] : ph.child[1];
-    return phase_sample(s.phases[c], s.tabs[c], mi, s2x, s2y);
-}
-
-/* The pdf PhaseFunction::sample returns with the direction (volpathmis.cpp:229): the value of the sampled phase
-   function in that direction -- evaluated here through eval() (rayleigh.cpp:62-65, hg.cpp:70-75 evaluate the same
-   formula at the sampled cosine); for a blend it is the pdf of the nested function that was picked, unweighted
-   (blendphase.cpp:97-112).  It enters the path weights only as pdf / pdf. */
-template <typename F>
-inline F phase_sample_pdf_at(const OScene<F> &s, int idx, const MediumInteraction<F> &mi, V3<F> wo, F s1) {
-    const B2vpPhase &ph = s.phases[idx];
-    if (ph.type != B2VP_PHASE_BLEND) return phase_eval(ph, s.tabs[idx], mi, wo);
-    int c = s1 > blend_weight(s, ph, mi) ? ph.child[0] : ph.child[1];
-    return phase_eval(s.phases[c], s.tabs[c], mi, wo);
+    return phase_sample(s.phases[c], s.tabs[c], mi, s2x, s2y, pdf);
 }
 
 enum : uint32_t { /* BSDFFlags (include/mitsuba/render/bsdf.h:44-123) */
@@ -1529,9 +1526,8 @@ template <typename F> struct Integrator {
                     p_over_f_nee = p_over_f;
                     F da = next_1d(true), db = next_1d(true), dc = next_1d(true);
                     F s1 = ltr ? da : dc, s2x = ltr ? db : da, s2y = ltr ? dc : db;
-                    V3<F> wo = phase_sample_at(scene, m.phase, mi, s1, s2x, s2y);
-                    /* the pdf phase->sample returns is the phase function value for every phase function in scope */
-                    F phase_pdf = phase_sample_pdf_at(scene, m.phase, mi, wo, s1);
+                    F phase_pdf;   /* what phase->sample returns with the direction (volpathmis.cpp:229) */
+                    V3<F> wo = phase_sample_at(scene, m.phase, mi, s1, s2x, s2y, &phase_pdf);
                     ray = spawn_ray(mi.p, wo);
                     ray.mint = 0;
                     needs_intersection = true;

@@ -60,14 +60,15 @@ def test_plugin_describe_against_reference_films(pkg, oracle, name):
             assert np.array_equal(r.film, film), name
 
 
-@pytest.mark.parametrize("seed", range(64))
+@pytest.mark.parametrize("seed", range(96))
 def test_random_scenes_against_the_reference(pkg, oracle, seed):
     """The random scenes of tests/test_gpu_fuzz.py (products of every scoped plugin that no named fixture writes
     down), rendered by the reference's own integrators and, from the same XML through the plugin's describe(), by the
     oracle: scalar_mono_double, the reference's block seeding.  This is the test that found `emitter_pdf = 1.f /
-    m_emitters.size()` (a float quotient in the double variant, scene.cpp:183) and the reference's refusal of grids with
-    fewer than 8 values.  Tolerance 1e-8 of the channel's maximum, not 1e-12: one random scene (volpathmis under an
-    environment emitter, a distant sensor sampling directions through a rotated frame) is 3e-9 off, cause unknown."""
+    m_emitters.size()` (a float quotient in the double variant, scene.cpp:183), the pdf phase->sample() returns (the
+    phase function at the LOCAL sampled cosine, which is not eval(wo) once a ray direction comes out of a sensor frame
+    rounded to single precision: 3e-9 under volpathmis with an environment emitter) and the reference's refusal of
+    grids with fewer than 8 values."""
     import test_gpu_fuzz
     ref_xml = ref_xml_or_skip()
     variant = "scalar_mono_double"
@@ -77,7 +78,7 @@ def test_random_scenes_against_the_reference(pkg, oracle, seed):
     assert got.shape == want.shape
     for c in range(want.shape[-1]):
         scale = max(np.abs(want[..., c]).max(), 1e-30)
-        assert np.abs(got[..., c] - want[..., c]).max() <= 1e-8 * scale, "channel %d" % c
+        assert np.abs(got[..., c] - want[..., c]).max() <= 1e-11 * scale, "channel %d" % c
 
 
 def test_plugin_self_check_reads_canaries_of_every_opened_class(pkg, tmp_path):
