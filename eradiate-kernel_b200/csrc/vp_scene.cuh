@@ -924,7 +924,10 @@ template <typename F, uint32_t FEAT = FT_ALL> VP_D V3<F> phase_sample(const DPha
     F s, c;
     sincos_((F) 2 * K<F>::Pi * s2y, s, c);
     V3<F> wo = mk3<F>(sin_theta * c, sin_theta * s, cos_theta);
-    if (pdf) *pdf = phase_eval_cos<F, FEAT>(ph, -cos_theta);
+    /* tabphase: sample() returns eval_pdf_normalized(-cos_theta) (tabphase.cpp:79) where eval() of the same direction,
+       whose dot(wo, wi) is -cos_theta, reads eval_pdf_normalized(+cos_theta) (tabphase.cpp:94-96): the reference's
+       sampled pdf is the table at the mirrored cosine.  Mirrored here, not corrected */
+    if (pdf) *pdf = phase_eval_cos<F, FEAT>(ph, ((FEAT & FT_TABPHASE) && ph.type == 3) ? cos_theta : -cos_theta);
     return make_frame(d).to_world(wo);
 }
 

@@ -867,7 +867,10 @@ inline V3<F> phase_sample(const B2vpPhase &ph, const TabDistr<F> &tab, const Med
     /* the pdf returned with the sample is the phase function at the LOCAL sampled cosine, eval_*(-cos_theta)
        (rayleigh.cpp:63, hg.cpp:73, tabphase.cpp:79-80) -- not eval(wo): with a ray direction that is not exactly of
        unit length (a sensor frame rounded to single precision) dot(to_world(wo), wi) is another number */
-    if (pdf) *pdf = phase_eval_cos(ph, tab, -cos_theta);
+    /* tabphase: sample() returns m_distr.eval_pdf_normalized(-cos_theta) (tabphase.cpp:79) where eval() of the same
+       direction, whose dot(wo, wi) is -cos_theta, looks up eval_pdf_normalized(+cos_theta) (tabphase.cpp:94-96): the
+       reference's sampled pdf is the table read at the mirrored cosine.  Mirrored here, not corrected */
+    if (pdf) *pdf = phase_eval_cos(ph, tab, ph.type == B2VP_PHASE_TABULATED ? cos_theta : -cos_theta);
     return mi.sh_frame.to_world(wo);
 }
 

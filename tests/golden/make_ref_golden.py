@@ -375,6 +375,10 @@ CASES = {
     "c2_three_emitters_f64": (lambda v: _three_emitters(scenes.c2(spp=2, variant=v, width=64)), "scalar_mono_double"),
     "c2_three_emitters_volpathmis_f64": (lambda v: _mis(_three_emitters(scenes.c2(spp=2, variant=v, width=64))), "scalar_mono_double"),
     "c5_three_emitters": (lambda v: _three_emitters(scenes.c5(spp=1, variant=v, n_leaves=200, n_sensors=256)), "scalar_mono"),
+    # volpathmis carries the pdf phase->sample() returns into the MIS weight of the next non-delta emitter hit; for
+    # tabphase that pdf is the table read at the MIRRORED cosine (tabphase.cpp:79 against :94-96)
+    "c2_tabphase_sky_volpathmis_f64": (lambda v: _mis(_sky(_tabphase(TAB_AEROSOL, spp=2, variant=v, width=64), 0.25)), "scalar_mono_double"),
+    "c2_tabphase_sky_volpathmis": (lambda v: _mis(_sky(_tabphase(TAB_AEROSOL, spp=1, variant=v, width=128), 0.25, sun=False)), "scalar_mono"),
     "c1_f64": (lambda v: scenes.c1(spp=1024, variant=v), "scalar_mono_double"),
     "c2_paths_f64": (lambda v: scenes.c2(spp=1, variant=v, width=128), "scalar_mono_double"),
     "c2_sphere_f64": (lambda v: _c2_sphere(spp=1, variant=v, width=64), "scalar_mono_double"),
