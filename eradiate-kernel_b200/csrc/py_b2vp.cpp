@@ -291,6 +291,7 @@ template <typename F> struct Loader {
     }
     void integrator(py::dict d) {
         b2vp::Volpath v;
+        const py::dict outer = d;   /* block_size / samples_per_pass: of the integrator render() runs on (integrator.cpp:51-110) */
         if (type_of(d) == "moment") {
             v.moment = true;
             for (auto kv : d)
@@ -301,8 +302,8 @@ template <typename F> struct Loader {
         else if (t != "volpath") unsupported("integrator", t);
         v.max_depth = get<int>(d, "max_depth", -1); v.rr_depth = get<int>(d, "rr_depth", 5);
         v.hide_emitters = get<bool>(d, "hide_emitters", false);
-        v.block_size = get<uint32_t>(d, "block_size", 0);
-        if (d.contains("samples_per_pass")) v.samples_per_pass = py::cast<uint32_t>(d["samples_per_pass"]);
+        v.block_size = get<uint32_t>(outer, "block_size", 0);
+        if (outer.contains("samples_per_pass")) v.samples_per_pass = py::cast<uint32_t>(outer["samples_per_pass"]);
         sb.set_integrator(v);
     }
 

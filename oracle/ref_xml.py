@@ -344,6 +344,9 @@ def with_plugin(scene, seeding="scalar", type_name="volpath_b200", **props):
         elif isinstance(v, dict) and v.get("type") == "moment":   # moment around a volpath -> the plugin's own `moment`
             inner = [c for c in v.values() if isinstance(c, dict)][0]
             outer = {kk: vv for kk, vv in v.items() if not isinstance(vv, dict) and kk != "type"}
+            # block_size / samples_per_pass belong to the integrator render() runs on, the outer one; what the nested
+            # integrator says about them is never read (integrator.cpp:51-110)
+            inner = {kk: vv for kk, vv in inner.items() if kk not in ("block_size", "samples_per_pass")}
             d[k] = dict(inner, type=type_name, seeding=seeding, algorithm=inner["type"], moment=True, **dict(outer, **props))
     return d
 

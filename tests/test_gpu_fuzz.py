@@ -25,6 +25,8 @@ def random_scene(seed, variant):
     if integ["type"] == "volpathmis":
         integ["use_spectral_mis"] = bool(pick(True, False))
     if pick(False, False, True):
+        integ["block_size"] = int(pick(2, 4))
+    if pick(False, False, True):
         integ = {"type": "moment", "nested": integ}
     d["integrator"] = integ
     # ---- phase function
@@ -42,10 +44,14 @@ def random_scene(seed, variant):
             return {"type": "blendphase", "a": phase(1), "b": phase(1), "weight": w}
         return {"type": kind}
     # ---- medium
-    kind = pick("homogeneous", "heterogeneous", "heterogeneous", "cloud")
     tw = T.translate([-2, -2, 0], dt) @ T.scale([4, 4, 1], dt)
+    kind = pick("homogeneous", "heterogeneous", "heterogeneous", "cloud")
     if kind == "homogeneous":
-        d["atm"] = {"type": "homogeneous", "sigma_t": float(pick(0.5, 2.0)), "albedo": float(pick(1.0, 0.8)), "phase": phase()}
+        # (no gridvolume here: the reference evaluates a homogeneous medium's sigma_t at mi.p BEFORE it is set,
+        # medium.cpp:55 -- with a grid the result depends on what the stack held)
+        sigma_t = pick(0.5, 2.0, {"type": "constvolume", "value": 1.5})
+        d["atm"] = {"type": "homogeneous", "sigma_t": sigma_t if isinstance(sigma_t, dict) else float(sigma_t),
+                    "albedo": pick(1.0, 0.8, {"type": "constvolume", "value": 0.7}), "phase": phase()}
     elif kind == "heterogeneous":
         grid = np.exp(-np.linspace(0, 4, 24)).astype(np.float32).reshape(24, 1, 1)
         d["atm"] = {"type": "heterogeneous",
@@ -57,7 +63,8 @@ def random_scene(seed, variant):
         n = 6
         d["atm"] = {"type": "heterogeneous",
                     "sigma_t": {"type": "gridvolume", "data": rng.uniform(0, 3, (n, n, n)).astype(np.float32), "to_world": tw},
-                    "albedo": {"type": "gridvolume", "data": rng.uniform(0.5, 1, (n, n, n)).astype(np.float32), "to_world": tw},
+                    "albedo": {"type": "gridvolume", "to_world": tw,
+                               "data": rng.uniform(0.5, 1, (n, n, n) + ((3,) if pick(False, True) else ())).astype(np.float32)},
                     "phase": phase()}
     d["box"] = {"type": "cube", "to_world": T.translate([0, 0, 0.5], dt) @ T.scale([2, 2, 0.5], dt),
                 "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}}
@@ -66,7 +73,8 @@ def random_scene(seed, variant):
                 {"type": "bilambertian", "reflectance": 0.4, "transmittance": 0.2})
     d["ground"] = {"type": "rectangle", "to_world": T.translate([0, 0, -0.01], dt) @ T.scale([2.5, 2.5, 1], dt), "bsdf": bsdf}
     if pick(False, True):
-        d["ball"] = {"type": "sphere", "center": [0.3, -0.2, 0.4], "radius": 0.25, "bsdf": {"type": "diffuse", "reflectance": 0.6}}
+        d["ball"] = {"type": "sphere", "center": [0.3, -0.2, 0.4], "radius": 0.25, "flip_normals": bool(pick(False, True)),
+                     "bsdf": {"type": "diffuse", "reflectance": 0.6}}
     if pick(False, True):
         v, f = scenes.canopy(int(pick(6, 40)))
         d["leaves"] = {"type": "mesh", "vertex_positions": v, "faces": f,
@@ -84,18 +92,21 @@ def random_scene(seed, variant):
     spp = int(pick(1, 2, 4))
     w, h = pick((8, 1), (6, 5), (1, 1), (7, 3))
     film = {"type": "hdrfilm", "width": w, "height": h,
-            "rfilter": pick({"type": "box"}, {"type": "box"}, {"type": "gaussian"}, {"type": "tent"}, {"type": "mitchell"})}
+            "rfilter": pick({"type": "box"}, {"type": "box"}, {"type": "gaussian"}, {"type": "tent"}, {"type": "mitchell"},
+                            {"type": "catmullrom"}, {"type": "lanczos", "lobes": 2}, {"type": "box", "radius": 1.1})}
     if w >= 6 and pick(False, True):
         film.update(crop_offset_x=1, crop_offset_y=0, crop_width=w - 2, crop_height=h)
     own = {"type": "rectangle", "to_world": T.translate([0.1, 0.2, pick(0.0, 0.6)], dt) @ T.scale([1.2, 0.8, 1], dt)}
     origin = {"type": "rectangle", "to_world": T.translate([0, 0, 1.3], dt) @ T.scale([pick(9.0, 1.5), 9.0, 1], dt)}
     sampler = {"type": "independent", "sample_count": spp, "seed": int(pick(0, 5))}
-    kind = pick("distant", "distant", "mdistant", "distantflux", "radiancemeter", "mradiancemeter")
+    kind = pick("distant", "distant", "mdistant", "distantflux", "radiancemeter", "mradiancemeter", "irradiancemeter")
     target = pick(None, [0.1, -0.2, 0.0], {"type": "ref", "id": "ground"}, own)
     if kind == "distant":
         sn = {"type": "distant", "film": film}
         if pick(False, True):
             sn.update(direction=[0.1, 0.2, 1.0])
+        if pick(False, False, True):
+            sn["flip_directions"] = True
         if target is not None:
             sn["ray_target"] = target
         if pick(False, False, True):
@@ -121,15 +132,24 @@ def random_scene(seed, variant):
               "film": {"type": "hdrfilm", "width": 1, "height": 1, "rfilter": {"type": "box"}}}
         if sn["origin"][2] < 1:
             sn["medium"] = {"type": "ref", "id": "atm"}
+    elif kind == "irradiancemeter":   # on a small plate floating in (or above) the medium, facing up or down
+        sn = {"type": "irradiancemeter", "film": {"type": "hdrfilm", "width": 1, "height": 1, "rfilter": {"type": "box"}}}
+        z = pick(0.4, 1.2)
+        if z < 1:
+            sn["medium"] = {"type": "ref", "id": "atm"}
+        d["plate"] = {"type": "rectangle", "flip_normals": bool(pick(False, True)),
+                      "to_world": T.translate([0.4, -0.3, z], dt) @ T.scale([0.3, 0.2, 1], dt),
+                      "bsdf": {"type": "diffuse", "reflectance": 0.25}}
     else:
         n = 4
         sn = {"type": "mradiancemeter", "origins": [0.1 * i for i in range(3 * n)][:3 * n],
               "directions": [0.1, 0.0, -1.0] * n, "film": {"type": "hdrfilm", "width": n, "height": 1, "rfilter": {"type": "box"}}}
         sn["origins"] = np.stack([np.linspace(-1, 1, n), np.zeros(n), np.full(n, 2.0)], 1).reshape(-1).tolist()
     sn["sampler"] = sampler
-    d["sensor"] = sn
-    d["integrator_block"] = None
-    del d["integrator_block"]
+    if kind == "irradiancemeter":
+        d["plate"]["sensor"] = sn
+    else:
+        d["sensor"] = sn
     return d
 
 
