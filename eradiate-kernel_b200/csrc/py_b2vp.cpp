@@ -78,7 +78,7 @@ template <typename F> struct Loader {
             const b2vp::Phase a = phase(it->second), b = phase((++it)->second);
             if (!py::isinstance<py::dict>(d["weight"])) return b2vp::Phase::blend(a, b, py::cast<double>(d["weight"]));
             const py::dict w = py::cast<py::dict>(d["weight"]);
-            if (type_of(w) == "constvolume") return b2vp::Phase::blend(a, b, get<double>(w, "value", 1.0));
+            if (type_of(w) == "constvolume") return b2vp::Phase::blend(a, b, get<double>(w, "color", 1.0));   /* constant3d.cpp:14 */
             if (type_of(w) != "gridvolume") unsupported("volume", type_of(w));
             b2vp::Phase p = b2vp::Phase::blend(a, b, 0.0);
             const b2vp::GridVolume g = grid(w);
@@ -114,8 +114,15 @@ template <typename F> struct Loader {
         const b2vp::Phase ph = phase(py::cast<py::dict>(d["phase"]));
         const bool spectral = get<bool>(d, "has_spectral_extinction", true), se = get<bool>(d, "sample_emitters", true);
         const double scale = get<double>(d, "scale", 1.0);
+        /* props.volume(): a number, or a `constvolume` (its `color`, constant3d.cpp:14); grids are for heterogeneous media */
+        auto constant = [&](const char *key, double fallback) -> double {
+            if (!d.contains(key) || !py::isinstance<py::dict>(d[key])) return get<double>(d, key, fallback);
+            const py::dict v = py::cast<py::dict>(d[key]);
+            if (type_of(v) != "constvolume") unsupported("volume of a homogeneous medium", type_of(v));
+            return get<double>(v, "color", 1.0);
+        };
         if (t == "homogeneous") {
-            media[id] = sb.add_medium(b2vp::Homogeneous{ get<double>(d, "sigma_t", 1.0), get<double>(d, "albedo", 0.75), scale, spectral, se }, ph);
+            media[id] = sb.add_medium(b2vp::Homogeneous{ constant("sigma_t", 1.0), constant("albedo", 0.75), scale, spectral, se }, ph);
         } else if (t == "heterogeneous") {
             if (!py::isinstance<py::dict>(d["sigma_t"])) throw std::runtime_error("heterogeneous: sigma_t must be a gridvolume");
             const py::dict st = py::cast<py::dict>(d["sigma_t"]);
@@ -126,7 +133,7 @@ template <typename F> struct Loader {
                 if (type_of(al) == "gridvolume")
                     media[id] = sb.add_medium(h, grid(st), xf(st), grid(al), xf(al), ph);
                 else if (type_of(al) == "constvolume")
-                    media[id] = sb.add_medium(h, grid(st), xf(st), get<double>(al, "value", 1.0), ph);
+                    media[id] = sb.add_medium(h, grid(st), xf(st), get<double>(al, "color", 1.0), ph);   /* constant3d.cpp:14 */
                 else unsupported("volume", type_of(al));
             } else {
                 media[id] = sb.add_medium(h, grid(st), xf(st), get<double>(d, "albedo", 0.75), ph);

@@ -406,14 +406,19 @@ class _Builder:
         if node is None:
             node = default
         if isinstance(node, (int, float)):
-            node = {"type": "constvolume", "value": float(node)}
+            node = {"type": "constvolume", "color": float(node)}
         t = node["type"]
         to_world = self.xf(node.get("to_world"))
         w2l = to_world.inverse()
         arr = None
         if t == "constvolume":
             v.type = abi.VOLUME_CONST
-            v.value = float(self.prop(node.get("value", 1.0)))
+            if "value" in node:   # the plugin's property is `color` (constant3d.cpp:14); the reference rejects others
+                raise RuntimeError('Unreferenced property "value" in plugin of type "constvolume" (the property is "color")')
+            color = node.get("color", 1.0)
+            if isinstance(color, dict):
+                color = color.get("value", 1.0)   # a nested `uniform` spectrum
+            v.value = float(self.prop(color))
             v.max_value = v.value
             v.channels = 1
         elif t == "gridvolume":

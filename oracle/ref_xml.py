@@ -111,7 +111,7 @@ class _Writer:
             if "max_value" in v:
                 out.append('<float name="max_value" value="%s"/>' % _num(v["max_value"]))
         else:
-            out.append('<float name="value" value="%s"/>' % _num(v.get("value", 1.0)))
+            out.append('<float name="color" value="%s"/>' % _num(v.get("color", 1.0)))   # constant3d.cpp:14
         if "to_world" in v:
             out.append(_matrix(v["to_world"]))
         out.append("</volume>")

@@ -49,9 +49,9 @@ def random_scene(seed, variant):
     if kind == "homogeneous":
         # (no gridvolume here: the reference evaluates a homogeneous medium's sigma_t at mi.p BEFORE it is set,
         # medium.cpp:55 -- with a grid the result depends on what the stack held)
-        sigma_t = pick(0.5, 2.0, {"type": "constvolume", "value": 1.5})
+        sigma_t = pick(0.5, 2.0, {"type": "constvolume", "color": 1.5})
         d["atm"] = {"type": "homogeneous", "sigma_t": sigma_t if isinstance(sigma_t, dict) else float(sigma_t),
-                    "albedo": pick(1.0, 0.8, {"type": "constvolume", "value": 0.7}), "phase": phase()}
+                    "albedo": pick(1.0, 0.8, {"type": "constvolume", "color": 0.7}), "phase": phase()}
     elif kind == "heterogeneous":
         grid = np.exp(-np.linspace(0, 4, 24)).astype(np.float32).reshape(24, 1, 1)
         d["atm"] = {"type": "heterogeneous",
