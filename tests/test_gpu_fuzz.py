@@ -28,6 +28,7 @@ def random_scene(seed, variant):
         integ["block_size"] = int(pick(2, 4))
     if pick(False, False, True):
         integ = {"type": "moment", "nested": integ}
+    passes = bool(pick(False, False, True))
     d["integrator"] = integ
     # ---- phase function
     def phase(depth=0):
@@ -55,9 +56,10 @@ def random_scene(seed, variant):
     elif kind == "heterogeneous":
         grid = np.exp(-np.linspace(0, 4, 24)).astype(np.float32).reshape(24, 1, 1)
         d["atm"] = {"type": "heterogeneous",
-                    "sigma_t": {"type": "gridvolume", "data": grid, "to_world": tw, "filter_type": pick("trilinear", "nearest"),
-                                "wrap_mode": pick("clamp", "clamp", "repeat", "mirror")},
-                    "scale": float(pick(2.0, 6.0)), "albedo": float(pick(1.0, 0.9)), "phase": phase(),
+                    "sigma_t": dict({"type": "gridvolume", "data": grid, "to_world": tw, "filter_type": pick("trilinear", "nearest"),
+                                     "wrap_mode": pick("clamp", "clamp", "repeat", "mirror")},
+                                    **pick({}, {}, {"max_value": 1.5})),   # a majorant above the data: other free flights
+                    "scale": float(pick(2.0, 6.0)), "albedo": pick(1.0, 0.9, {"type": "constvolume", "color": 0.85}), "phase": phase(),
                     "has_spectral_extinction": bool(pick(True, True, False))}
     else:
         n = 6
@@ -70,6 +72,7 @@ def random_scene(seed, variant):
                 "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}}
     # ---- surfaces
     bsdf = pick({"type": "diffuse", "reflectance": 0.3}, {"type": "rpv", "rho_0": 0.1, "k": 0.7, "g": -0.1},
+                {"type": "rpv", "rho_0": 0.2, "k": 0.9, "g": 0.1, "rho_c": 0.05},
                 {"type": "bilambertian", "reflectance": 0.4, "transmittance": 0.2})
     d["ground"] = {"type": "rectangle", "to_world": T.translate([0, 0, -0.01], dt) @ T.scale([2.5, 2.5, 1], dt), "bsdf": bsdf}
     if pick(False, True):
@@ -81,6 +84,9 @@ def random_scene(seed, variant):
                        "bsdf": pick({"type": "diffuse", "reflectance": 0.5}, {"type": "bilambertian", "reflectance": 0.5, "transmittance": 0.3})}
     # ---- emitters
     d["sun"] = {"type": "directional", "direction": [0.2, pick(0.0, 0.4), -1], "irradiance": 1.0}
+    if pick(False, False, True):   # the same kind of sun through to_world (directional.cpp:50-60)
+        d["sun"] = {"type": "directional", "irradiance": 1.5,
+                    "to_world": T.look_at([0, 0, 0], [0.3, -0.1, -1.0], [0, 1, 0], np.float32)}
     if pick(False, False, True):
         d["sun2"] = {"type": "directional", "direction": [-0.5, 0.1, -1], "irradiance": 0.5}
     if pick(False, False, True):
@@ -90,6 +96,8 @@ def random_scene(seed, variant):
             d.pop("sun2", None)
     # ---- sensor and film
     spp = int(pick(1, 2, 4))
+    if passes and spp > 1:
+        d["integrator"]["samples_per_pass"] = spp // 2
     w, h = pick((8, 1), (6, 5), (1, 1), (7, 3))
     film = {"type": "hdrfilm", "width": w, "height": h,
             "rfilter": pick({"type": "box"}, {"type": "box"}, {"type": "gaussian"}, {"type": "tent"}, {"type": "mitchell"},
@@ -103,8 +111,13 @@ def random_scene(seed, variant):
     target = pick(None, [0.1, -0.2, 0.0], {"type": "ref", "id": "ground"}, own)
     if kind == "distant":
         sn = {"type": "distant", "film": film}
-        if pick(False, True):
+        how = pick("none", "direction", "direction+orientation", "to_world")
+        if how.startswith("direction"):
             sn.update(direction=[0.1, 0.2, 1.0])
+        if how == "direction+orientation":
+            sn.update(orientation=[1.0, 0.5, 0.0])
+        if how == "to_world":
+            sn.update(to_world=T.look_at([0, 0, 0], [0.2, -0.1, 1.0], [0, 1, 0], np.float32))
         if pick(False, False, True):
             sn["flip_directions"] = True
         if target is not None:
