@@ -3,10 +3,14 @@
 window and reconstruction filter, integrator and its limits, seeding mode) and rendered by the CUDA path and by the
 oracle; PCG32 end states, event counters and per-path radiance must agree bit for bit, films to summation order.
 The named parity cases cover each feature on its own; this covers the products nobody wrote down."""
+import os
+
 import numpy as np
 import pytest
 
 import scenes
+
+DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "data")
 
 pytestmark = pytest.mark.gpu
 
@@ -64,7 +68,8 @@ def random_scene(seed, variant):
     else:
         n = 6
         d["atm"] = {"type": "heterogeneous",
-                    "sigma_t": {"type": "gridvolume", "data": rng.uniform(0, 3, (n, n, n)).astype(np.float32), "to_world": tw},
+                    "sigma_t": dict({"type": "gridvolume", "data": rng.uniform(0, 3, (n, n, n)).astype(np.float32), "to_world": tw},
+                                    **pick({}, {}, {"use_grid_bbox": True, "bbox": (0.0, 0.0, 0.0, 1.0, 1.0, 0.5)})),
                     "albedo": {"type": "gridvolume", "to_world": tw,
                                "data": rng.uniform(0.5, 1, (n, n, n) + ((3,) if pick(False, True) else ())).astype(np.float32)},
                     "phase": phase()}
@@ -75,9 +80,21 @@ def random_scene(seed, variant):
                 {"type": "rpv", "rho_0": 0.2, "k": 0.9, "g": 0.1, "rho_c": 0.05},
                 {"type": "bilambertian", "reflectance": 0.4, "transmittance": 0.2})
     d["ground"] = {"type": "rectangle", "to_world": T.translate([0, 0, -0.01], dt) @ T.scale([2.5, 2.5, 1], dt), "bsdf": bsdf}
+    if pick(False, False, False, True):   # a ground that faces down: one-sided BSDFs reflect nothing (rectangle.cpp:80-83)
+        d["ground"]["flip_normals"] = True
+    if pick(False, False, True):   # a mesh file under a transform, with its own normals or face normals
+        name, kind = pick(("roof.obj", "obj"), ("roof_bin.ply", "ply"), ("roof.serialized", "serialized"))
+        d["roof"] = {"type": kind, "filename": os.path.join(DATA, name), "face_normals": bool(pick(False, True)),
+                     "to_world": T.translate([0.25, -0.5, 0.3], dt) @ T.scale([1.0, 0.75, 1.0], dt),
+                     "bsdf": {"type": "diffuse", "reflectance": 0.75}}
+        if kind == "serialized":
+            d["roof"]["shape_index"] = 1
     if pick(False, True):
         d["ball"] = {"type": "sphere", "center": [0.3, -0.2, 0.4], "radius": 0.25, "flip_normals": bool(pick(False, True)),
                      "bsdf": {"type": "diffuse", "reflectance": 0.6}}
+        if pick(False, True):   # placed by to_world instead (a similarity: sphere.cpp:100-117)
+            d["ball"] = {"type": "sphere", "to_world": T.translate([-0.4, 0.3, 0.5], dt) @ T.scale(0.2, dt),
+                         "bsdf": {"type": "diffuse", "reflectance": 0.6}}
     if pick(False, True):
         v, f = scenes.canopy(int(pick(6, 40)))
         d["leaves"] = {"type": "mesh", "vertex_positions": v, "faces": f,
