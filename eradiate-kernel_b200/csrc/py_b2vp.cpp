@@ -171,15 +171,15 @@ template <typename F> struct Loader {
             return it->second;
         }
         if (type_of(r) != "rectangle") throw std::runtime_error("sensor target shape must be a rectangle in the B200 volpath");
-        return sb.add_rectangle(xf(r), bsdf(r), medium_ref(r, "interior"), medium_ref(r, "exterior"), true);
+        return sb.add_rectangle(xf(r), bsdf(r), medium_ref(r, "interior"), medium_ref(r, "exterior"), true, get<bool>(r, "flip_normals", false));
     }
     bool shape(const std::string &key, const py::dict &d) {
         const std::string t = type_of(d);
-        if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj" && t != "ply" && t != "serialized") return false;
+        if (t != "cube" && t != "rectangle" && t != "sphere" && t != "obj" && t != "ply" && t != "serialized" && t != "mesh") return false;
         const int b = bsdf(d), in = medium_ref(d, "interior"), ex = medium_ref(d, "exterior");
         if (t == "cube") sb.add_cube(xf(d), b, in, ex);
         else if (t == "rectangle") {
-            const int index = sb.add_rectangle(xf(d), b, in, ex);
+            const int index = sb.add_rectangle(xf(d), b, in, ex, false, get<bool>(d, "flip_normals", false));
             shapes[get<std::string>(d, "id", key)] = index;
             if (d.contains("sensor")) {   /* a sensor attached to the shape (shape.cpp:47-54): the irradiancemeter */
                 if (have_shape_sensor) throw std::runtime_error("the B200 volpath renders one sensor per scene");
@@ -192,6 +192,22 @@ template <typename F> struct Loader {
             if (d.contains("center")) s.center = vec3(d["center"]);
             s.radius = get<double>(d, "radius", 1.0); s.flip_normals = get<bool>(d, "flip_normals", false);
             sb.add_sphere(s, xf(d), b, in, ex);
+        } else if (t == "mesh") {   /* an in-memory triangle mesh: what the file loaders produce (src/librender/mesh.cpp) */
+            b2vp::MeshData m;
+            auto p = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(d["vertex_positions"]);
+            auto f = py::array_t<uint32_t, py::array::c_style | py::array::forcecast>::ensure(d["faces"]);
+            if (!p || !f || p.size() % 3 || f.size() % 3) throw std::runtime_error("mesh: vertex_positions / faces must be (n, 3) arrays");
+            m.positions.assign(p.data(), p.data() + p.size());
+            m.faces.assign(f.data(), f.data() + f.size());
+            if (d.contains("vertex_normals")) {
+                auto n = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(d["vertex_normals"]);
+                if (n) m.normals.assign(n.data(), n.data() + n.size());
+            }
+            if (d.contains("vertex_texcoords")) {
+                auto uv = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(d["vertex_texcoords"]);
+                if (uv) m.texcoords.assign(uv.data(), uv.data() + uv.size());
+            }
+            sb.add_mesh(m, xf(d), b, in, ex);
         } else {   /* src/shapes/obj.cpp, ply.cpp, serialized.cpp */
             const std::string file = py::cast<std::string>(d["filename"]);
             b2vp::MeshData m = t == "obj" ? b2vp::load_obj(file, get<bool>(d, "flip_tex_coords", true))
@@ -240,6 +256,12 @@ template <typename F> struct Loader {
             b2vp::Distant s;
             if (d.contains("direction")) s.direction = vec3(d["direction"]);
             if (d.contains("orientation")) { s.has_orientation = true; s.orientation = vec3(d["orientation"]); }
+            if (d.contains("to_world")) {
+                if (d.contains("direction")) throw std::runtime_error("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!");
+                const b2vp::Mat4<F> tw = xf(d);
+                s.has_to_world = true;
+                for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) s.to_world[(size_t) (r * 4 + c)] = (double) tw(r, c);
+            }
             if (d.contains("ray_target")) {
                 if (py::isinstance<py::dict>(d["ray_target"])) s.ray_target_shape = sensor_shape(d, "ray_target");
                 else { s.has_ray_target = true; s.ray_target = vec3(d["ray_target"]); }
@@ -264,11 +286,11 @@ template <typename F> struct Loader {
             if (d.contains("film") && (film.width != 1 || film.height != 1)) throw std::runtime_error("This sensor only supports films of size 1x1 Pixels!");
             b2vp::IrradianceMeter s;
             s.shape = shape_sensor_index; s.medium = med;
-            sb.set_sensor(s, smp);
+            sb.set_sensor(s, smp, d.contains("film") ? &film : nullptr);
         } else if (t == "radiancemeter") {
             b2vp::RadianceMeter s;
             s.origin = vec3(d["origin"]); s.direction = vec3(d["direction"]); s.medium = med;
-            sb.set_sensor(s, smp);
+            sb.set_sensor(s, smp, d.contains("film") ? &film : nullptr);
         } else if (t == "mdistant" || t == "mradiancemeter") {
             auto triples = [](const py::handle &h) {
                 auto v = py::cast<std::vector<double>>(h);
@@ -288,11 +310,11 @@ template <typename F> struct Loader {
                     if (py::isinstance<py::dict>(d["target"])) s.target_shape = sensor_shape(d, "target");
                     else { s.has_target = true; s.target = vec3(d["target"]); }
                 }
-                sb.set_sensor(s, smp);
+                sb.set_sensor(s, smp, d.contains("film") ? &film : nullptr);
             } else {
                 b2vp::MRadianceMeter s;
                 s.directions = dirs; s.origins = triples(d["origins"]); s.medium = med;
-                sb.set_sensor(s, smp);
+                sb.set_sensor(s, smp, d.contains("film") ? &film : nullptr);
             }
         } else unsupported("sensor", t);
     }
@@ -334,7 +356,12 @@ template <typename F> struct Loader {
             if (shape(kv.first, d)) continue;
             if (t == "directional") {
                 b2vp::Directional e;
-                if (d.contains("to_world")) throw std::runtime_error("directional: give `direction` (to_world is not supported by the C++ host)");
+                if (d.contains("to_world")) {
+                    if (d.contains("direction")) throw std::runtime_error("Only one of the parameters 'direction' and 'to_world' can be specified at the same time!");
+                    const b2vp::Mat4<F> tw = xf(d);
+                    e.has_to_world = true;
+                    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) e.to_world[(size_t) (r * 4 + c)] = (double) tw(r, c);
+                }
                 if (d.contains("direction")) e.direction = vec3(d["direction"]);
                 e.irradiance = get<double>(d, "irradiance", 1.0);
                 sb.add_emitter(e);

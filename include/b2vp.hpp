@@ -128,9 +128,16 @@ template <typename F> struct Mat4 {
         for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) o(r, c) = (F) a[r][4 + c];
         return o;
     }
-    /* normals transform with the inverse transpose */
+    /* The inverse as a Transform4f read from Properties carries it: single precision in every variant
+       (properties.h:55-56 -- matrix AND inverse transpose are float members, widened afterwards) */
+    Mat4 inverse_f32() const {
+        Mat4 o = inverse();
+        for (int i = 0; i < 16; ++i) o.m[i] = (F) (float) o.m[i];
+        return o;
+    }
+    /* normals transform with the inverse transpose (of a transform that came through Properties: inverse_f32) */
     Vec3<F> normal(const Vec3<F> &n) const {
-        Mat4 it = inverse();
+        Mat4 it = inverse_f32();
         return { it(0, 0) * n[0] + it(1, 0) * n[1] + it(2, 0) * n[2], it(0, 1) * n[0] + it(1, 1) * n[1] + it(2, 1) * n[2],
                  it(0, 2) * n[0] + it(1, 2) * n[1] + it(2, 2) * n[2] };
     }
@@ -193,7 +200,11 @@ struct Rpv { double rho_0 = 0.1, k = 0.1, g = 0.0, rho_c = -1.0; };
 /* src/bsdfs/bilambertian.cpp:50-61 */
 struct Bilambertian { double reflectance = 0.5, transmittance = 0.5; };
 /* src/emitters/directional.cpp:45-73 */
-struct Directional { std::array<double, 3> direction{ 0, 0, 1 }; double irradiance = 1.0; };
+struct Directional {
+    std::array<double, 3> direction{ 0, 0, 1 }; double irradiance = 1.0;
+    /* instead of `direction` (directional.cpp:50-60): the emitter's to_world, row-major; the light travels along its z axis */
+    bool has_to_world = false; std::array<double, 16> to_world{ 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+};
 /* src/emitters/constant.cpp:35-40: the environment emitter */
 struct Constant { double radiance = 1.0; };
 /* src/films/hdrfilm.cpp:100-183, src/samplers/independent.cpp */
@@ -221,6 +232,8 @@ struct Distant {
     /* a rectangle as ray_target / ray_origin (distant.cpp:270-290): the index add_rectangle returned -- for a shape of
        the sensor's own, one added with sample_only = true.  -1: the point target above / the bounding sphere */
     int ray_target_shape = -1, ray_origin_shape = -1;
+    /* instead of `direction` / `orientation` (distant.cpp:246-262): the sensor's to_world, row-major */
+    bool has_to_world = false; std::array<double, 16> to_world{ 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
 };
 /* src/sensors/distantflux.cpp:140-182: a film over the hemisphere around to_world * (0, 0, 1); target point, target
    rectangle (an index add_rectangle returned) or none; rays start on the bounding sphere or on an origin rectangle */
@@ -356,8 +369,10 @@ public:
     /* src/shapes/rectangle.cpp:75-104 */
     /* sample_only: a rectangle of a sensor's own (its ray_target / ray_origin), not a child of the scene: never
        intersected by paths and outside the scene's bounding box (B2vpShape::sample_only) */
-    int add_rectangle(const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1, bool sample_only = false) {
-        const Mat4<F> to_world = prop_xf(to_world_);
+    int add_rectangle(const Mat4<F> &to_world_, int bsdf, int interior = -1, int exterior = -1, bool sample_only = false,
+                      bool flip_normals = false) {
+        /* flip_normals: to_world * scale(1, 1, -1) (rectangle.cpp:80-83) */
+        const Mat4<F> to_world = flip_normals ? prop_xf(to_world_) * Mat4<F>::scale(1, 1, -1) : prop_xf(to_world_);
         B2vpShape s{};
         s.type = B2VP_SHAPE_RECTANGLE; s.bsdf = bsdf; s.interior_medium = interior; s.exterior_medium = exterior;
         Vec3<F> dp_du = to_world.vector({ 2, 0, 0 }), dp_dv = to_world.vector({ 0, 2, 0 });
@@ -370,7 +385,7 @@ public:
         if (!sample_only)
             for (auto &c : corners) expand(to_world.point({ c[0], c[1], c[2] }));
         s.sample_only = sample_only ? 1 : 0;
-        s.to_world = to_world.pod(); s.to_object = to_world.inverse().pod();
+        s.to_world = to_world.pod(); s.to_object = to_world.inverse_f32().pod();
         sc_->shapes.push_back(s);
         return (int) sc_->shapes.size() - 1;
     }
@@ -448,7 +463,7 @@ public:
         s.radius = (double) radius; s.flip_normals = flip ? 1 : 0;
         const F pi = (F) 3.14159265358979323846;
         s.inv_surface_area = (double) ((F) 1 / ((F) 4 * pi * radius * radius));
-        s.to_world = tw.pod(); s.to_object = tw.inverse().pod();
+        s.to_world = tw.pod(); s.to_object = tw.inverse_f32().pod();
         expand({ center[0] - radius, center[1] - radius, center[2] - radius });
         expand({ center[0] + radius, center[1] + radius, center[2] + radius });
         sc_->shapes.push_back(s);
@@ -488,6 +503,10 @@ public:
         coordinate_system(d, up, t);
         /* Endpoint::m_world_transform is an AnimatedTransform: single precision in every variant (transform.h:366) */
         Mat4<F> tw = prop_xf(Mat4<F>::look_at({ 0, 0, 0 }, d, up));
+        if (e.has_to_world) {
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) tw(r, c) = (F) e.to_world[(size_t) (r * 4 + c)];
+            tw = prop_xf(tw);
+        }
         Vec3<F> z = tw.vector({ 0, 0, 1 });
         B2vpEmitter o{};
         o.type = B2VP_EMITTER_DIRECTIONAL; o.irradiance = (double) prop(e.irradiance);
@@ -506,6 +525,11 @@ public:
         else
             coordinate_system(d, tmp, up);
         o.to_world = prop_xf(Mat4<F>::look_at({ 0, 0, 0 }, d, up)).pod();   /* AnimatedTransform: single precision */
+        if (sn.has_to_world) {
+            Mat4<F> tw;
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) tw(r, c) = (F) sn.to_world[(size_t) (r * 4 + c)];
+            o.to_world = prop_xf(tw).pod();
+        }
         o.target_type = sn.has_ray_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
         for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.ray_target[k]);
         if (sn.ray_target_shape >= 0) { o.target_type = B2VP_TARGET_SHAPE; o.target_shape = rectangle_index(sn.ray_target_shape); }
@@ -531,16 +555,16 @@ public:
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
-    void set_sensor(const IrradianceMeter &sn, const IndependentSampler &sampler) {
-        B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
+    void set_sensor(const IrradianceMeter &sn, const IndependentSampler &sampler, const HdrFilm *film = nullptr) {
+        B2vpSensor o = base_sensor(fixed_film(film, 1), sampler, sn.medium);
         o.type = B2VP_SENSOR_IRRADIANCEMETER; o.needs_aperture_sample = 1;
         if (sn.shape < 0) throw Error(B2VP_ERR_INVALID, "irradiancemeter: no parent shape");
         o.origin_shape = rectangle_index(sn.shape);
         sc_->desc.sensor = o;
         have_sensor_ = true;
     }
-    void set_sensor(const RadianceMeter &sn, const IndependentSampler &sampler) {
-        B2vpSensor o = base_sensor(HdrFilm{ 1, 1 }, sampler, sn.medium);
+    void set_sensor(const RadianceMeter &sn, const IndependentSampler &sampler, const HdrFilm *film = nullptr) {
+        B2vpSensor o = base_sensor(fixed_film(film, 1), sampler, sn.medium);
         o.type = B2VP_SENSOR_RADIANCEMETER; o.needs_aperture_sample = 0;
         Vec3<F> org = prop3(sn.origin), d = prop3(sn.direction);
         Vec3<F> up, tmp;
@@ -550,10 +574,10 @@ public:
         have_sensor_ = true;
     }
     /* src/sensors/mdistant.cpp:146-207: a look-at matrix per direction, ScalarFloat matrices of the plugin's own */
-    void set_sensor(const MDistant &sn, const IndependentSampler &sampler) {
+    void set_sensor(const MDistant &sn, const IndependentSampler &sampler, const HdrFilm *film = nullptr) {
         const int n = (int) sn.directions.size();
         if (n == 0) throw Error(B2VP_ERR_INVALID, "mdistant: no directions");
-        B2vpSensor o = base_sensor(HdrFilm{ n, 1 }, sampler, sn.medium);
+        B2vpSensor o = base_sensor(fixed_film(film, n), sampler, sn.medium);
         o.type = B2VP_SENSOR_MDISTANT; o.needs_aperture_sample = 1;
         o.target_type = sn.has_target ? B2VP_TARGET_POINT : B2VP_TARGET_NONE;
         for (int k = 0; k < 3; ++k) o.target_point[k] = (double) prop(sn.target[k]);
@@ -572,11 +596,11 @@ public:
         have_sensor_ = true;
     }
     /* src/sensors/mradiancemeter.cpp:75-131 */
-    void set_sensor(const MRadianceMeter &sn, const IndependentSampler &sampler) {
+    void set_sensor(const MRadianceMeter &sn, const IndependentSampler &sampler, const HdrFilm *film = nullptr) {
         const int n = (int) sn.directions.size();
         if (n == 0 || sn.origins.size() != sn.directions.size())
             throw Error(B2VP_ERR_INVALID, "Invalid specification! Number of parameters for origins and directions are not equal.");
-        B2vpSensor o = base_sensor(HdrFilm{ n, 1 }, sampler, sn.medium);
+        B2vpSensor o = base_sensor(fixed_film(film, n), sampler, sn.medium);
         o.type = B2VP_SENSOR_MRADIANCEMETER; o.needs_aperture_sample = 0;
         sc_->sensor_transforms.clear();
         for (int i = 0; i < n; ++i) {
@@ -676,11 +700,20 @@ private:
     }
     /* Volume base class: world_to_local = to_world^-1, bbox = image of the unit cube (texture.h:265-272) */
     void finish_volume(B2vpVolume &o, const Mat4<F> &to_world) {
-        Mat4<F> w2l = to_world.inverse();
+        Mat4<F> w2l = to_world.inverse_f32();
         o.world_to_local = w2l.pod();
         Vec3<F> a = to_world.point({ 0, 0, 0 }), b = to_world.point({ 1, 1, 1 });
         for (int k = 0; k < 3; ++k) { o.bbox_min[k] = std::min(a[k], b[k]); o.bbox_max[k] = std::max(a[k], b[k]); }
         sc_->volumes.push_back(o);
+    }
+    /* sensors whose film size is given by the sensor ([n, 1]): the caller's film, if any, brings its reconstruction
+       filter and crop window; its size must be the sensor's (mdistant.cpp:178-183, radiancemeter.cpp:94-95) */
+    static HdrFilm fixed_film(const HdrFilm *film, int n) {
+        if (!film) return HdrFilm{ n, 1 };
+        if (film->width != n || film->height != 1)
+            throw Error(B2VP_ERR_INVALID, "Film size must be [" + std::to_string(n) + ", 1], got [" + std::to_string(film->width) + ", " +
+                                          std::to_string(film->height) + "]");
+        return *film;
     }
     int rectangle_index(int shape) const {
         if (shape >= (int) sc_->shapes.size() || sc_->shapes[(size_t) shape].type != B2VP_SHAPE_RECTANGLE)
