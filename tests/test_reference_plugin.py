@@ -135,6 +135,24 @@ def test_plugin_rejects_content_outside_the_scope(pkg):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(32))
+def test_random_scenes_on_the_gpu_through_the_plugin(pkg, seed):
+    """The whole drop-in chain on products nobody wrote down: the reference binary loads a random scene, its own
+    integrator renders it on the host, and the same process image with the plugin renders it on the B200 (exact
+    arithmetic, the reference's block seeding): the same film to summation order, scalar_mono_double."""
+    import test_gpu_fuzz
+    ref_xml = ref_xml_or_skip()
+    variant = "scalar_mono_double"
+    d = ref_xml.round_f32(test_gpu_fuzz.random_scene(seed, variant))
+    want, _ = ref_xml.render(d, variant, write_vol=pkg.scene.write_vol)
+    got, _ = ref_xml.render(ref_xml.with_plugin(d, seeding="scalar", math="exact"), variant, write_vol=pkg.scene.write_vol)
+    assert got.shape == want.shape
+    for c in range(want.shape[-1]):
+        scale = max(np.abs(want[..., c]).max(), 1e-30)
+        assert np.abs(got[..., c] - want[..., c]).max() <= 1e-11 * scale, "channel %d" % c
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", PLUGIN_CASES)
 def test_reference_binary_renders_on_the_gpu_through_the_plugin(pkg, name):
     ref_xml = ref_xml_or_skip()
