@@ -40,7 +40,7 @@ def random_scene(seed, variant):
         if kind == "hg":
             return {"type": "hg", "g": float(pick(0.85, -0.3, 0.0))}
         if kind == "tabphase":
-            return {"type": "tabphase", "values": TAB}
+            return {"type": "tabphase", "values": pick(TAB, [float(x) for x in rng.uniform(0.1, 2.0, int(pick(2, 5, 17)))])}
         if kind == "blendphase":
             w = pick(0.3, "grid")
             if w == "grid":
@@ -59,6 +59,8 @@ def random_scene(seed, variant):
                     "albedo": pick(1.0, 0.8, {"type": "constvolume", "color": 0.7}), "phase": phase()}
     elif kind == "heterogeneous":
         grid = np.exp(-np.linspace(0, 4, 24)).astype(np.float32).reshape(24, 1, 1)
+        if pick(False, False, False, True):   # a 3-channel grid read in a mono variant (grid3d.cpp:163-185)
+            grid = np.repeat(grid[..., None], 3, axis=3) * np.array([1.0, 0.8, 1.2], np.float32)
         d["atm"] = {"type": "heterogeneous",
                     "sigma_t": dict({"type": "gridvolume", "data": grid, "to_world": tw, "filter_type": pick("trilinear", "nearest"),
                                      "wrap_mode": pick("clamp", "clamp", "repeat", "mirror")},
@@ -73,6 +75,10 @@ def random_scene(seed, variant):
                     "albedo": {"type": "gridvolume", "to_world": tw,
                                "data": rng.uniform(0.5, 1, (n, n, n) + ((3,) if pick(False, True) else ())).astype(np.float32)},
                     "phase": phase()}
+    if pick(False, False, False, True):
+        d["atm"]["sample_emitters"] = False          # medium.cpp:29: no emitter sampling at scattering events in this medium
+    if kind == "homogeneous" and pick(False, True):
+        d["atm"]["scale"] = 1.5                      # homogeneous.cpp:27
     d["box"] = {"type": "cube", "to_world": T.translate([0, 0, 0.5], dt) @ T.scale([2, 2, 0.5], dt),
                 "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}}
     # ---- surfaces
