@@ -94,7 +94,9 @@ template <typename F> struct Loader {
     b2vp::GridVolume grid(const py::dict &d) {
         b2vp::GridVolume g;
         if (d.contains("filename")) {
-            g = b2vp::read_vol(py::cast<std::string>(d["filename"]));
+            std::array<float, 6> file_bbox{ 0, 0, 0, 1, 1, 1 };
+            g = b2vp::read_vol(py::cast<std::string>(d["filename"]), &file_bbox);
+            g.bbox = file_bbox;
         } else {   /* in-memory data[z, y, x(, c)] */
             auto a = py::array_t<float, py::array::c_style | py::array::forcecast>::ensure(d["data"]);
             if (!a || (a.ndim() != 3 && a.ndim() != 4)) throw std::runtime_error("gridvolume: data must be [z, y, x] or [z, y, x, c]");
@@ -104,8 +106,13 @@ template <typename F> struct Loader {
         g.filter_type = get<std::string>(d, "filter_type", "trilinear");
         g.wrap_mode = get<std::string>(d, "wrap_mode", "clamp");
         if (d.contains("max_value")) g.max_value = py::cast<double>(d["max_value"]);
-        if (get<bool>(d, "use_grid_bbox", false) || get<bool>(d, "raw", false))
-            throw std::runtime_error("gridvolume: use_grid_bbox / raw are not supported by the C++ host");
+        if (get<bool>(d, "raw", false)) throw std::runtime_error("gridvolume raw=true is not supported in mono variants");
+        g.use_grid_bbox = get<bool>(d, "use_grid_bbox", false);
+        if (!d.contains("filename") && d.contains("bbox")) {   /* in-memory data: the bounding box a file would carry */
+            const auto bb = py::cast<std::vector<float>>(d["bbox"]);
+            if (bb.size() != 6) throw std::runtime_error("gridvolume: bbox must be (min xyz, max xyz)");
+            for (size_t i = 0; i < 6; ++i) g.bbox[i] = bb[i];
+        }
         return g;
     }
     void medium(const std::string &id, const py::dict &d) {

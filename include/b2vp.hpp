@@ -186,6 +186,9 @@ struct GridVolume {
     int nx = 0, ny = 0, nz = 0, channels = 1;
     std::string filter_type = "trilinear", wrap_mode = "clamp";
     double max_value = -1;   /* < 0: the maximum of the data (grid3d.cpp:157-160) */
+    /* use_grid_bbox (grid3d.cpp:152-155): the file's bounding box (min xyz, max xyz; read_vol returns it) is mapped onto
+       the unit cube before to_world applies */
+    bool use_grid_bbox = false; std::array<float, 6> bbox{ 0, 0, 0, 1, 1, 1 };
 };
 /* A version-3 float32 `.vol` file (src/textures/volume_data.h:42-102) as a GridVolume.  `bbox` (if given) receives the
    file's bounding box: min xyz, max xyz (what `use_grid_bbox` applies, grid3d.cpp:152-155). */
@@ -362,7 +365,7 @@ public:
         sc_->grids.push_back(v.data);
         o.data = sc_->grids.back().data();
         o.max_value = v.max_value >= 0 ? (double) prop(v.max_value) : (double) *std::max_element(v.data.begin(), v.data.end());
-        finish_volume(o, prop_xf(to_world));
+        finish_volume(o, prop_xf(to_world), v.use_grid_bbox ? &v.bbox : nullptr);
         return (int) sc_->volumes.size() - 1;
     }
 
@@ -699,10 +702,17 @@ private:
         return (int) sc_->media.size() - 1;
     }
     /* Volume base class: world_to_local = to_world^-1, bbox = image of the unit cube (texture.h:265-272) */
-    void finish_volume(B2vpVolume &o, const Mat4<F> &to_world) {
+    void finish_volume(B2vpVolume &o, const Mat4<F> &to_world, const std::array<float, 6> *grid_bbox = nullptr) {
         Mat4<F> w2l = to_world.inverse_f32();
+        Mat4<F> l2w = to_world;
+        if (grid_bbox) {   /* grid3d.cpp:152-155: world_to_local = scale(1 / extents) * translate(-min) * world_to_local */
+            const auto &bb = *grid_bbox;
+            const F mn[3] = { (F) bb[0], (F) bb[1], (F) bb[2] }, ex[3] = { (F) bb[3] - (F) bb[0], (F) bb[4] - (F) bb[1], (F) bb[5] - (F) bb[2] };
+            w2l = Mat4<F>::scale((F) 1 / ex[0], (F) 1 / ex[1], (F) 1 / ex[2]) * Mat4<F>::translate(-mn[0], -mn[1], -mn[2]) * w2l;
+            l2w = to_world * Mat4<F>::translate(mn[0], mn[1], mn[2]) * Mat4<F>::scale(ex[0], ex[1], ex[2]);
+        }
         o.world_to_local = w2l.pod();
-        Vec3<F> a = to_world.point({ 0, 0, 0 }), b = to_world.point({ 1, 1, 1 });
+        Vec3<F> a = l2w.point({ 0, 0, 0 }), b = l2w.point({ 1, 1, 1 });
         for (int k = 0; k < 3; ++k) { o.bbox_min[k] = std::min(a[k], b[k]); o.bbox_max[k] = std::max(a[k], b[k]); }
         sc_->volumes.push_back(o);
     }
