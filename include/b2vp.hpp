@@ -466,7 +466,7 @@ public:
         s.radius = (double) radius; s.flip_normals = flip ? 1 : 0;
         const F pi = (F) 3.14159265358979323846;
         s.inv_surface_area = (double) ((F) 1 / ((F) 4 * pi * radius * radius));
-        s.to_world = tw.pod(); s.to_object = tw.inverse_f32().pod();
+        s.to_world = tw.pod(); s.to_object = tw.inverse().pod();   /* recomposed and inverted in the variant's type (sphere.cpp:126-127) */
         expand({ center[0] - radius, center[1] - radius, center[2] - radius });
         expand({ center[0] + radius, center[1] + radius, center[2] + radius });
         sc_->shapes.push_back(s);

@@ -106,8 +106,8 @@ def test_pybind_random_scenes(pkg, oracle, variant):
     host describes (which is pinned on the reference binary by tests/test_reference_plugin.py).  This test found the
     C++ host dropping `flip_normals` of rectangles, the film (filter, crop) of the fixed-size sensors, `to_world` of
     `distant` / `directional`, and inverting transforms in double where Properties carries a single-precision inverse.
-    Tolerance 1e-8 in fp64: a sphere placed by `to_world` gets its radius from a polar decomposition in one host and
-    from a column norm in the other (4e-9 on radiance)."""
+    (a sphere, whose transform the reference recomposes and inverts in the variant's own type, is the exception:
+    sphere.cpp:126-127)."""
     import test_gpu_fuzz
     ext = _ext(pkg)
     compared = 0
@@ -118,7 +118,7 @@ def test_pybind_random_scenes(pkg, oracle, variant):
         ours = oracle.render(pkg, _as_host_scene(pkg, s), pkg.abi.SEED_WAVEFRONT)
         compared += 1
         assert ours.totals.n_rng_draws == ref.totals.n_rng_draws and ours.totals.n_intersect == ref.totals.n_intersect, seed
-        tol = 1e-8 if variant == "scalar_mono_double" else 2e-5
+        tol = 1e-11 if variant == "scalar_mono_double" else 2e-5
         for c in range(ref.film.shape[-1]):
             scale = max(np.abs(ref.film[..., c]).max(), 1e-30)
             assert np.abs(ours.film[..., c].astype(np.float64) - ref.film[..., c]).max() <= tol * scale, (seed, c)
