@@ -81,6 +81,12 @@ def random_scene(seed, variant):
         d["atm"]["scale"] = 1.5                      # homogeneous.cpp:27
     d["box"] = {"type": "cube", "to_world": T.translate([0, 0, 0.5], dt) @ T.scale([2, 2, 0.5], dt),
                 "bsdf": {"type": "null"}, "interior": {"type": "ref", "id": "atm"}}
+    if pick(False, False, False, True):
+        # a second medium in a small cube inside the atmosphere: medium transitions on both faces
+        # (interior / exterior media of a shape, shape.cpp:34-45; si.target_medium, interaction.h:360-370)
+        d["dense"] = {"type": "homogeneous", "sigma_t": 3.0, "albedo": 0.6, "phase": {"type": "hg", "g": 0.5}}
+        d["blob"] = {"type": "cube", "to_world": T.translate([-0.3, 0.4, 0.5], dt) @ T.scale(0.25, dt), "bsdf": {"type": "null"},
+                     "interior": {"type": "ref", "id": "dense"}, "exterior": {"type": "ref", "id": "atm"}}
     # ---- surfaces
     bsdf = pick({"type": "diffuse", "reflectance": 0.3}, {"type": "rpv", "rho_0": 0.1, "k": 0.7, "g": -0.1},
                 {"type": "rpv", "rho_0": 0.2, "k": 0.9, "g": 0.1, "rho_c": 0.05},
